@@ -1,0 +1,263 @@
+"""TEST INFRASTRUCTURE ONLY — not imported by the product package.
+
+CPU restatement (torch on CPU, fp32 with an fp64 twin) of the hot path of
+goodmattg/ndivplanning.  Every function cites the reference lines it follows
+(paths relative to /root/reference).  Pinned by tests/golden/*.npz which were
+produced by running the UNMODIFIED reference (oracle/make_golden.py).
+
+The arithmetic itself lives in PyTorch (nn.Linear/addmm, torch.norm, MSELoss);
+the reference pins no torch version so the effective pin is the
+torch installed in this image (2.11.0).
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+from torch.nn import functional as F
+
+__all__ = [
+    "compute_pairwise", "compute_pair_distance", "compute_pairwise_divergence",
+    "ndiv_grad_analytic", "GeneratorMLP", "LatentForward", "draw_noise",
+    "diverse_sampling", "mpc_rollout", "select_first_min", "select_topk",
+    "mpc_plan", "pack_key", "closed_loop_eval", "ndiv_fwd_bwd",
+]
+
+MARGIN = 0.8          # diversity.py:40
+MIN_ERROR_INIT = 1e10  # mpc_eval.py:122
+
+
+# ----------------------------------------------------------------------------
+# ndiv loss — diversity.py:8-41
+# ----------------------------------------------------------------------------
+def compute_pairwise(z: torch.Tensor) -> torch.Tensor:
+    """diversity.py:8-9 — [N,k,C] -> [N,k,k] Euclidean distances (diag exactly 0)."""
+    return torch.norm(z[:, :, None, :] - z[:, None, :, :], p=2, dim=3)
+
+
+def compute_pair_distance(z: torch.Tensor, weight=None) -> torch.Tensor:
+    """diversity.py:12-19 — row-normalise by the DETACHED row sum."""
+    if weight is not None:
+        d = compute_pairwise(weight) * compute_pairwise(z)
+    else:
+        d = compute_pairwise(z)
+    s = torch.sum(d, dim=2)
+    return d / s[..., None].detach()
+
+
+def compute_pairwise_divergence(recodes: torch.Tensor, codes: torch.Tensor) -> torch.Tensor:
+    """diversity.py:36-41 — outputs first, latents second; plain sum."""
+    N, k, _ = codes.size()
+    z_delta = compute_pair_distance(torch.squeeze(codes).view(N, k, -1))
+    x_delta = compute_pair_distance(torch.squeeze(recodes).view(N, k, -1))
+    return F.relu(z_delta * MARGIN - x_delta).sum()
+
+
+def ndiv_fwd_bwd(x: torch.Tensor, z: torch.Tensor):
+    """Loss + d loss / d x through autograd, exactly as train_gan.py:193-202 uses it."""
+    x = x.detach().clone().requires_grad_(True)
+    loss = compute_pairwise_divergence(x, z)
+    loss.backward()
+    return loss.detach(), x.grad.detach()
+
+
+def ndiv_grad_analytic(x: torch.Tensor, z: torch.Tensor) -> torch.Tensor:
+    """Closed-form gradient, used to cross-check autograd in fp64.
+
+    M_ij = 1[0.8 dz_ij/sz_i - dx_ij/sx_i > 0];  W_ij = -(M_ij/sx_i + M_ji/sx_j)
+    dL/dx_i = sum_j (W_ij / dx_ij) (x_i - x_j), terms with dx_ij == 0 dropped.
+    """
+    N, k = x.shape[:2]
+    x = x.reshape(N, k, -1)
+    z = z.reshape(N, k, -1)
+    dx, dz = compute_pairwise(x), compute_pairwise(z)
+    sx, sz = dx.sum(2, keepdim=True), dz.sum(2, keepdim=True)
+    M = ((MARGIN * dz / sz - dx / sx) > 0).to(x.dtype)
+    W = -(M / sx + M.transpose(1, 2) / sx.transpose(1, 2))
+    What = torch.where(dx > 0, W / dx, torch.zeros_like(W))
+    return x * What.sum(2, keepdim=True) - What @ x
+
+
+# ----------------------------------------------------------------------------
+# modules
+# ----------------------------------------------------------------------------
+class GeneratorMLP(nn.Module):
+    """models/gan.py:61-86 (`Decoder`): (256+nd)->128->64->128->256->4, ReLU, linear head."""
+
+    def __init__(self, noise_dim: int, cond_dim: int = 256):
+        super().__init__()
+        self.fc1 = nn.Linear(cond_dim + noise_dim, 128)
+        self.fc2 = nn.Linear(128, 64)
+        self.fc3 = nn.Linear(64, 128)
+        self.fc4 = nn.Linear(128, 256)
+        self.fc5 = nn.Linear(256, 4)
+
+    def forward(self, z):
+        a = F.relu(self.fc1(z))
+        a = F.relu(self.fc2(a))
+        a = F.relu(self.fc3(a))
+        a = F.relu(self.fc4(a))
+        return self.fc5(a)
+
+
+class LatentForward(nn.Module):
+    """Embedding-space forward model with ForwardAutoencoder's call contract
+    (models/forward_encoder.py:105-114): cat([code, actions],1) — state first,
+    action last; training mode returns the residual, eval mode state + residual.
+    Body defined by SURVEY.md §8a-F: fc1 Linear(E+4,H) -> ReLU -> fc2 Linear(H,E).
+    """
+
+    def __init__(self, E: int = 128, H: int = 1024, A: int = 4):
+        super().__init__()
+        self.fc1 = nn.Linear(E + A, H)
+        self.fc2 = nn.Linear(H, E)
+
+    def forward(self, state_cur, actions):
+        code = state_cur.flatten(1)
+        r = self.fc2(F.relu(self.fc1(torch.cat([code, actions], dim=1))))
+        r = r.view_as(state_cur)
+        if self.training:
+            return r
+        return state_cur + r
+
+
+# ----------------------------------------------------------------------------
+# sampling — mpc_eval.py:78-83
+# ----------------------------------------------------------------------------
+def draw_noise(T: int, K: int, nd: int, S: int = 1) -> torch.Tensor:
+    """One `torch.FloatTensor(K,S,nd).uniform_()` per rollout step, step-major
+    (mpc_eval.py:80 called from :141 inside `for ts`). Uses the global CPU RNG."""
+    return torch.stack([torch.FloatTensor(K, S, nd).uniform_() for _ in range(T)], 0)
+
+
+def diverse_sampling(code: torch.Tensor, noise: torch.Tensor) -> torch.Tensor:
+    """mpc_eval.py:78-83 with the noise passed in: noise goes in the LAST columns."""
+    S = noise.shape[1]
+    code = code[:, None, :].expand(-1, S, -1)
+    return torch.cat([code, noise], dim=2)
+
+
+# ----------------------------------------------------------------------------
+# MPC inner loop — mpc_eval.py:119-165
+# ----------------------------------------------------------------------------
+@torch.no_grad()
+def mpc_rollout(gen: nn.Module, fwd: nn.Module, e0: torch.Tensor, goal: torch.Tensor,
+                noise: torch.Tensor):
+    """e0, goal: [E]; noise: [T,K,nd] -> (state_T [K,E,1,1], a0 [K,1,4]).
+
+    Follows mpc_eval.py:124-157 with image_encoder = nn.Identity():
+      :125 repeat state K times; :133 repeat target; :137-139 cat([state,target],1).squeeze();
+      :141 diverse_sampling; :146-149 generator(view(-1,C+nd)).view(K,-1,4);
+      :150-151 keep step-0 actions; :154-157 state <- fwd(state, a.squeeze(1)).
+    """
+    T, K, nd = noise.shape
+    E = e0.numel()
+    state = e0.view(1, E, 1, 1).repeat(K, 1, 1, 1)
+    target = goal.view(1, E, 1, 1).repeat(K, 1, 1, 1)
+    a0 = None
+    for ts in range(T):
+        now_codes = torch.cat([state, target], dim=1).squeeze()
+        if now_codes.dim() == 1:  # K == 1: the reference's squeeze() would drop the batch dim
+            now_codes = now_codes[None]
+        dz = diverse_sampling(now_codes, noise[ts].view(K, 1, nd))
+        a = gen(dz.view(-1, dz.size(2))).view(K, -1, 4)
+        if ts == 0:
+            a0 = a
+        state = fwd(state, a.squeeze(1))
+    return state, a0
+
+
+@torch.no_grad()
+def candidate_costs(state_T: torch.Tensor, goal: torch.Tensor) -> torch.Tensor:
+    """mpc_eval.py:161 — nn.MSELoss()(state_T[ro], target[0]) for every ro: mean over E."""
+    K = state_T.shape[0]
+    return ((state_T.reshape(K, -1) - goal.reshape(1, -1)) ** 2).mean(dim=1)
+
+
+def select_first_min(costs) -> int:
+    """mpc_eval.py:122,159-164 — strict '<' scan from min_error = 1e10, index init 0.
+    First minimal index wins; NaN never wins; all >= 1e10 -> 0."""
+    min_error = MIN_ERROR_INIT
+    best = 0
+    for ro, c in enumerate(costs.tolist() if hasattr(costs, "tolist") else costs):
+        if c < min_error:
+            min_error = c
+            best = ro
+    return best
+
+
+def select_topk(costs: torch.Tensor, k: int) -> torch.Tensor:
+    """north_star's top-k extension: k smallest under the total
+    order (cost, index) == stable ascending sort (NaN sorts last)."""
+    return torch.sort(costs, stable=True).indices[:k]
+
+
+def pack_key(cost: float, idx: int) -> int:
+    """(ordered_bits(cost) << 32) | idx — the u64 the multi-GPU min-allreduce uses.
+    Ordered bits: flip sign bit for non-negatives, all bits for negatives; NaN -> 0xFFFFFFFF."""
+    import struct
+    if cost != cost:
+        key = 0xFFFFFFFF
+    else:
+        b = struct.unpack("<I", struct.pack("<f", cost))[0]
+        key = (b ^ 0xFFFFFFFF) if (b >> 31) else (b | 0x80000000)
+    return (key << 32) | idx
+
+
+@torch.no_grad()
+def mpc_plan(gen, fwd, e0, goal, noise, topk: int = 1):
+    """One plan: rollout + terminal cost + first-min + top-k.
+    Returns dict(cost[K], best_idx, best_action[4], topk_idx[topk], a0[K,4])."""
+    state_T, a0 = mpc_rollout(gen, fwd, e0, goal, noise)
+    cost = candidate_costs(state_T, goal)
+    best = select_first_min(cost)
+    return dict(cost=cost, best_idx=best, best_action=a0[best, 0].clone(),
+                topk_idx=select_topk(cost, topk), a0=a0[:, 0].clone(), state_T=state_T.flatten(1))
+
+
+# ----------------------------------------------------------------------------
+# whole evaluation function — mpc_eval.py:94-191 (embedding mode, batch_size=1, S=1)
+# ----------------------------------------------------------------------------
+@torch.no_grad()
+def closed_loop_eval(gen, fwd, images: torch.Tensor, actions: torch.Tensor, K: int, Th: int,
+                     nd: int, seed: int, vector_argmin: bool = False):
+    """images [n_traj, seq, E], actions [n_traj, seq, 4].  Restates the receding-horizon
+    loop (mpc_eval.py:112-176) including its quirks (Appendix B): truncated horizon near the
+    end (:127), image_error_sum reset per trajectory (:110) but divided by all (:186).
+    Returns (avg_action_error, avg_image_loss, best_indices[n_traj, seq-1])."""
+    import numpy as np
+    torch.manual_seed(seed)
+    np.random.seed(seed)
+    mse = nn.MSELoss()
+    n_traj, seq, E = images.shape
+    action_error_sum = 0
+    image_error_sum = 0
+    best_all = []
+    for i in range(n_traj):
+        state_cur = images[i, :-1]
+        goal = images[i, -1]
+        acts = actions[i, :-1]
+        image_error_sum = 0
+        chosen = []
+        best_row = []
+        cur = state_cur[0]
+        for image_num in range(seq - 1):
+            state_fut = state_cur[image_num + 1] if image_num != seq - 2 else goal
+            T_eff = min(Th, seq - 1 - image_num)
+            noise = draw_noise(T_eff, K, nd)[:, :, 0, :]
+            state_T, a0 = mpc_rollout(gen, fwd, cur, goal, noise)
+            cost = candidate_costs(state_T, goal)
+            if vector_argmin:
+                best = int(torch.argmin(torch.where(cost < MIN_ERROR_INIT, cost,
+                                                    torch.full_like(cost, float("inf")))))
+            else:
+                best = select_first_min(cost)
+            best_row.append(best)
+            best_action = a0[best]  # [1,4]
+            cur = fwd(cur.view(1, E, 1, 1), best_action).view(E)
+            chosen.append(best_action)
+            image_error_sum = image_error_sum + mse(cur, state_fut)
+        action_hat = torch.cat(chosen, dim=0)
+        action_error_sum = action_error_sum + mse(acts[None], action_hat)
+        best_all.append(best_row)
+    denom = (seq - 1) * n_traj
+    return float(action_error_sum / denom), float(image_error_sum / denom), best_all
