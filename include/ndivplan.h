@@ -1,0 +1,147 @@
+/* libndivplan — C ABI of the B200 (sm_100a) planning hot path of ndivplanning.
+ *
+ * The reference (goodmattg/ndivplanning) is pure Python/PyTorch and has no FFI
+ * layer; each entry point below names the reference lines it replaces.  Paths
+ * are relative to the reference tree.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - all tensors fp32, row-major contiguous; indices int32; packed keys uint64;
+ *   - stream is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - all work is stream-ordered, no host synchronisation inside a call;
+ *   - return 0 on success, <0 on error; text via ndp_last_error() (thread-local);
+ *   - the caller owns every buffer; the library allocates only inside handles;
+ *   - there is NO CPU code path: calls fail with NDP_ERR_DEVICE off sm_100.
+ */
+#ifndef NDIVPLAN_H_
+#define NDIVPLAN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NDP_ABI_VERSION 1
+
+enum {
+  NDP_OK = 0,
+  NDP_ERR_ARG = -1,      /* bad shape / null pointer / unsupported size */
+  NDP_ERR_CUDA = -2,     /* a CUDA runtime call failed */
+  NDP_ERR_DEVICE = -3,   /* not an sm_100 device */
+  NDP_ERR_WORKSPACE = -4,/* workspace too small */
+  NDP_ERR_NCCL = -5
+};
+
+/* arithmetic mode of the rollout kernel */
+enum {
+  NDP_PREC_FP32 = 0,     /* CUDA-core FFMA, fp32 everywhere: parity mode            */
+  NDP_PREC_F16X3 = 1,    /* tcgen05 kind::f16, 3-term hi/lo split operands, fp32 acc */
+  NDP_PREC_F16 = 2       /* tcgen05 kind::f16 single pass: bulk estimate, NOT parity */
+};
+
+typedef struct ndp_planner ndp_planner;
+typedef struct ndp_comm ndp_comm;
+
+typedef struct {
+  int E;          /* state-embedding width (128; image_autoencoder.py:27)            */
+  int nd;         /* noise_dim (evaluation.noise_dim; mpc_eval.py:65)                */
+  int A;          /* action width, must be 4 (gan.py:71)                             */
+  int H;          /* latent forward model hidden width, multiple of 128              */
+  int T;          /* mpc.time_horizon (mpc_eval.py:68)                               */
+  int precision;  /* NDP_PREC_*                                                      */
+} ndp_planner_desc;
+
+int ndp_abi_version(void);
+const char* ndp_last_error(void);
+/* 0 when the current device is sm_100 and the kernels can run on it */
+int ndp_device_check(void);
+
+/* ---- planner: generator MLP + T-step latent rollout + terminal cost -------------
+ * replaces mpc_eval.py:124-157 (rollout), :161 (per-candidate MSE) with
+ * models/gan.py:79-86 (Decoder.forward) and forward_encoder.py:105-114 semantics. */
+int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* desc);
+void ndp_planner_destroy(ndp_planner* p);
+
+/* Weights in torch nn.Linear layout [out,in] (device pointers), order:
+ *   W[0..4] = generator fc1..fc5  (fc1: [128, 2E+nd], columns = [state | goal | noise],
+ *                                  gan.py:67 + cat order mpc_eval.py:137-138,:82)
+ *   W[5]    = forward fc1 [H, E+A] (columns = [state | action], forward_encoder.py:107)
+ *   W[6]    = forward fc2 [E, H]
+ * b[i] the matching biases. Copies + prepacks on `stream`; sources may be freed after
+ * the stream reaches this point. */
+int ndp_planner_load(ndp_planner* p, const float* const* W, const float* const* b,
+                     int n_tensors, void* stream);
+
+int ndp_planner_workspace_bytes(const ndp_planner* p, int G, int K, size_t* bytes);
+
+/* e0,goal [G,E]; noise [T,G,K,nd] (step-major draw order of mpc_eval.py:80,:141);
+ * cost [G,K] = mean_E (s_T - goal)^2 (mpc_eval.py:161); a0 [G,K,4] = step-0 actions
+ * (mpc_eval.py:150-151); state_T [G,K,E] optional (NULL to skip). */
+int ndp_rollout_score(ndp_planner* p, const float* e0, const float* goal, const float* noise,
+                      int G, int K, float* cost, float* a0, float* state_T,
+                      void* ws, size_t ws_bytes, void* stream);
+
+/* one generator forward (models/gan.py:79-86): z [B, 2E+nd] -> a [B,4] */
+int ndp_generator_forward(ndp_planner* p, const float* z, int B, float* a, void* stream);
+/* one forward-model step (forward_encoder.py:105-114, eval mode: state + residual) */
+int ndp_forward_step(ndp_planner* p, const float* state, const float* action, int B,
+                     float* next_state, void* stream);
+
+/* ---- selection: replaces the python scan mpc_eval.py:122,159-165 -----------------
+ * cost [G,K]. For each segment g:
+ *   packed_min[g] = (okey(cost)<<32) | (idx_base + argmin)  with first-index tie break;
+ *                   if no cost is < 1e10 (incl. NaN) -> 0xFFFFFFFF00000000 (index 0, the
+ *                   reference's min_error=1e10 / best_act_ind=0 initialisation);
+ *   topk_idx[g,:]  = the topk smallest under the total order (cost, index), ascending
+ *                   (NaN last) == torch.sort(stable=True)[:topk]; topk<=128; may be NULL
+ *                   with topk==0; topk_cost likewise.
+ * okey = fp32 bits with the sign bit flipped (non-negative) or all bits flipped (negative).
+ * ws: ndp_select_workspace_bytes(). */
+int ndp_select_workspace_bytes(int G, int K, int topk, size_t* bytes);
+int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
+               uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
+               void* ws, size_t ws_bytes, void* stream);
+/* best_action[g,:] = a0[g, idx(packed_min[g]) - idx_base, :]   (mpc_eval.py:165) */
+int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,
+                           int64_t idx_base, float* best_action, int32_t* best_idx,
+                           void* stream);
+
+/* ---- normalized diversification loss: replaces diversity.py:8-41 -----------------
+ * x = recodes [N,k,Dx] (outputs), z = codes [N,k,Dz] (latents) — argument order of
+ * compute_pairwise_divergence(recodes, codes), diversity.py:36.
+ * loss[0] = sum relu(margin * dz_ij/sz_i - dx_ij/sx_i); sx,sz [N,k] row sums (detached
+ * normalisers, diversity.py:17-18). grad_x (nullable) = d loss / d x for grad_loss = 1.
+ * Row-block sharding (multi-GPU): rows [row0,row0+rows) of every group are owned by the
+ * caller; sx/sz must hold ALL rows before ndp_ndiv_loss_grad (allgather in between). */
+int ndp_ndiv_workspace_bytes(int N, int k, size_t* bytes);
+int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz,
+                     int row0, int rows, float* sx, float* sz, void* stream);
+int ndp_ndiv_loss_grad(const float* x, const float* z, const float* sx, const float* sz,
+                       int N, int k, int Dx, int Dz, float margin, int row0, int rows,
+                       float* loss, float* grad_x, void* ws, size_t ws_bytes, void* stream);
+/* compute_pairwise (normalise=0, diversity.py:8-9) / compute_pair_distance
+ * (normalise=1, diversity.py:12-19): v [N,k,C] -> out [N,k,k] */
+int ndp_pairwise(const float* v, int N, int k, int C, int normalise, float* out, void* stream);
+/* grad_v [N,k,C] of sum(out * grad_out) for compute_pairwise / compute_pair_distance;
+ * rowsum_ws: [N,k] scratch, required when normalise=1 */
+int ndp_pairwise_backward(const float* v, const float* grad_out, int N, int k, int C,
+                          int normalise, float* rowsum_ws, float* grad_v, void* stream);
+
+/* ---- collectives (NCCL over NVLink; libnccl is dlopen'ed on first use) ----------- */
+int ndp_comm_unique_id(void* id128_host);                       /* 128-byte ncclUniqueId */
+int ndp_comm_create(ndp_comm** out, const void* id128_host, int rank, int world);
+int ndp_comm_allreduce_min_u64(ndp_comm* c, uint64_t* buf, int count, void* stream);
+int ndp_comm_allreduce_sum_f32(ndp_comm* c, float* buf, int count, void* stream);
+int ndp_comm_allgather_f32(ndp_comm* c, const float* send, float* recv, int count_per_rank,
+                           void* stream);
+void ndp_comm_destroy(ndp_comm* c);
+
+/* number of kernels this library has launched in this process (bench gpu_launches) */
+uint64_t ndp_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NDIVPLAN_H_ */

@@ -1,0 +1,15 @@
+"""ndivplanning_b200 — B200-native (sm_100a) planning hot path of goodmattg/ndivplanning.
+
+    from ndivplanning_b200 import FusedPlanner, diversity, fetch_push_control_evaluation
+
+Everything computes through libndivplan.so (hand-written CUDA behind a C ABI,
+include/ndivplan.h); there is no CPU fallback.
+"""
+from . import diversity  # noqa: F401
+from ._lib import LIB_PATH, NdpError, launch_count  # noqa: F401
+from .models import GeneratorMLP, LatentForward  # noqa: F401
+from .mpc_eval import fetch_push_control_evaluation, sample_noise  # noqa: F401
+from .planner import FusedPlanner, Plan, select_plan, unpack_index  # noqa: F401
+
+__all__ = ["diversity", "FusedPlanner", "Plan", "select_plan", "unpack_index", "GeneratorMLP", "LatentForward",
+           "fetch_push_control_evaluation", "sample_noise", "NdpError", "launch_count", "LIB_PATH"]

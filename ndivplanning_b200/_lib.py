@@ -1,0 +1,100 @@
+"""ctypes binding of libndivplan.so (include/ndivplan.h).  No CPU fallback: if the
+library is missing or the device is not sm_100 every entry point raises."""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libndivplan.so")
+
+PREC_FP32, PREC_F16X3, PREC_F16 = 0, 1, 2
+
+
+class NdpError(RuntimeError):
+    pass
+
+
+class PlannerDesc(C.Structure):
+    _fields_ = [("E", C.c_int), ("nd", C.c_int), ("A", C.c_int), ("H", C.c_int), ("T", C.c_int),
+                ("precision", C.c_int)]
+
+
+_vp, _i, _i64, _sz, _f = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
+_PROTOS = {
+    "ndp_abi_version": (_i, []),
+    "ndp_last_error": (C.c_char_p, []),
+    "ndp_device_check": (_i, []),
+    "ndp_launch_count": (C.c_uint64, []),
+    "ndp_planner_create": (_i, [C.POINTER(_vp), C.POINTER(PlannerDesc)]),
+    "ndp_planner_destroy": (None, [_vp]),
+    "ndp_planner_load": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), _i, _vp]),
+    "ndp_planner_workspace_bytes": (_i, [_vp, _i, _i, C.POINTER(_sz)]),
+    "ndp_rollout_score": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_generator_forward": (_i, [_vp, _vp, _i, _vp, _vp]),
+    "ndp_forward_step": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "ndp_select_workspace_bytes": (_i, [_i, _i, _i, C.POINTER(_sz)]),
+    "ndp_select": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_gather_best_action": (_i, [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),
+    "ndp_ndiv_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),
+    "ndp_ndiv_rowsums": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "ndp_ndiv_loss_grad": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_pairwise": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
+    "ndp_pairwise_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "ndp_comm_unique_id": (_i, [_vp]),
+    "ndp_comm_create": (_i, [C.POINTER(_vp), _vp, _i, _i]),
+    "ndp_comm_allreduce_min_u64": (_i, [_vp, _vp, _i, _vp]),
+    "ndp_comm_allreduce_sum_f32": (_i, [_vp, _vp, _i, _vp]),
+    "ndp_comm_allgather_f32": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "ndp_comm_destroy": (None, [_vp]),
+}
+EXPORTED_SYMBOLS = tuple(_PROTOS)
+
+_lib = None
+
+
+def lib():
+    """Loads libndivplan.so once. Raises NdpError when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise NdpError(f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; "
+                           f"g.build()'` (ndivplanning_b200/csrc/build.sh). There is no CPU fallback.")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in _PROTOS.items():
+            fn = getattr(l, name)
+            fn.restype, fn.argtypes = res, args
+        if l.ndp_abi_version() != 1:
+            raise NdpError("libndivplan ABI version mismatch")
+        _lib = l
+    return _lib
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise NdpError(f"libndivplan error {rc}: {lib().ndp_last_error().decode()}")
+
+
+def ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream_ptr(device=None):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda(*tensors):
+    """The product path is CUDA-only: refuse CPU tensors loudly instead of falling back."""
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise NdpError("ndivplanning_b200 runs on sm_100a only; got a CPU tensor (no CPU fallback)")
+    if not torch.cuda.is_available():
+        raise NdpError("CUDA is not available; ndivplanning_b200 has no CPU fallback")
+
+
+def f32c(t):
+    return t.detach().to(torch.float32).contiguous()
+
+
+def launch_count() -> int:
+    return int(lib().ndp_launch_count())

@@ -1,0 +1,283 @@
+// C-ABI glue of libndivplan: error reporting, device gate, planner handle (weight prepack),
+// the single-call generator / forward-model entry points, launch counting.
+#include <stdarg.h>
+#include <string.h>
+#include "planner.cuh"
+
+namespace ndp {
+
+static thread_local char g_err[512] = "";
+std::atomic<unsigned long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int device_check() {
+  static thread_local int cached_dev = -1;
+  static thread_local int cached_rc = 0;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) {
+    cudaGetLastError();
+    set_error("no CUDA device: libndivplan has no CPU path");
+    return NDP_ERR_DEVICE;
+  }
+  if (dev == cached_dev) return cached_rc;
+  int major = 0, minor = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
+  cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev);
+  cached_dev = dev;
+  cached_rc = (major == 10) ? NDP_OK : NDP_ERR_DEVICE;
+  if (cached_rc) set_error("device %d is sm_%d%d; libndivplan is built for sm_100a only", dev, major, minor);
+  return cached_rc;
+}
+
+int num_sms() {
+  int dev = 0, n = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  return n;
+}
+
+// dst[kk*N + n] = src[(n0+n)*ld + k0 + kk]   (transpose-pack a [N x Kc] block of a torch [out,in] matrix)
+__global__ void pack_T_kernel(float* __restrict__ dst, const float* __restrict__ src, int ld, int n0, int k0,
+                              int Kc, int N) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= Kc * N) return;
+  const int kk = idx / N, n = idx % N;
+  dst[idx] = src[(size_t)(n0 + n) * ld + k0 + kk];
+}
+
+// b1g[g][n] = b1[n] + sum_e W1g[n][e] * goal[g][e]   — goal half of generator fc1, once per plan
+// (the reference recomputes it for every candidate and step: mpc_eval.py:133,136-138)
+__global__ void goal_bias_kernel(const float* __restrict__ w1g, const float* __restrict__ b1,
+                                 const float* __restrict__ goal, int E, float* __restrict__ b1g) {
+  const int g = blockIdx.x;
+  const int n = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (n >= 128) return;
+  // sequential-order friendly: each lane sums a strided subset, then tree
+  float acc = 0.f;
+  for (int e = lane; e < E; e += 32) acc = fmaf(__ldg(w1g + (size_t)n * E + e), __ldg(goal + (size_t)g * E + e), acc);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) b1g[(size_t)g * 128 + n] = acc + __ldg(b1 + n);
+}
+
+// out[r][n] = act( b[n] + sum_k in[r][k] W[n][k] ) (+ res[r][n]); one warp per output.
+// in rows are formed from up to two sources (concat): in0 [B,K0] then in1 [B,K1].
+__global__ void linear_kernel(const float* __restrict__ in0, int K0, const float* __restrict__ in1, int K1,
+                              const float* __restrict__ W, const float* __restrict__ b, int N, int B, int relu,
+                              const float* __restrict__ res, float* __restrict__ out) {
+  const long long wid = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (wid >= (long long)B * N) return;
+  const int r = (int)(wid / N), n = (int)(wid % N);
+  const int K = K0 + K1;
+  const float* w = W + (size_t)n * K;
+  float acc = 0.f;
+  for (int k = lane; k < K0; k += 32) acc = fmaf(__ldg(in0 + (size_t)r * K0 + k), __ldg(w + k), acc);
+  for (int k = lane; k < K1; k += 32) acc = fmaf(__ldg(in1 + (size_t)r * K1 + k), __ldg(w + K0 + k), acc);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) {
+    float v = acc + __ldg(b + n);
+    if (relu) v = v > 0.f ? v : 0.f;
+    if (res) v += res[(size_t)r * N + n];
+    out[(size_t)r * N + n] = v;
+  }
+}
+
+}  // namespace ndp
+
+using namespace ndp;
+
+extern "C" int ndp_abi_version(void) { return NDP_ABI_VERSION; }
+extern "C" const char* ndp_last_error(void) { return g_err; }
+extern "C" int ndp_device_check(void) { return device_check(); }
+extern "C" uint64_t ndp_launch_count(void) { return g_launches.load(); }
+
+extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) {
+  NDP_CHECK_ARG(out && d, "planner_create: null argument");
+  NDP_CHECK_ARG(d->E == 128, "planner_create: E must be 128 (got %d); the generator consumes [state 128 | goal 128 | noise] (gan.py:67)", d->E);
+  NDP_CHECK_ARG(d->A == 4, "planner_create: A must be 4 (gan.py:71)");
+  NDP_CHECK_ARG(d->nd >= 0 && d->nd <= 64, "planner_create: noise_dim must be in [0,64]");
+  NDP_CHECK_ARG(d->H >= 128 && d->H % 128 == 0 && d->H <= 8192, "planner_create: H must be a multiple of 128 in [128,8192]");
+  NDP_CHECK_ARG(d->T >= 1 && d->T <= 4096, "planner_create: T must be in [1,4096]");
+  NDP_CHECK_ARG(d->precision == NDP_PREC_FP32, "planner_create: precision mode %d not built in this version", d->precision);
+  if (int rc = device_check()) return rc;
+  ndp_planner* p = new ndp_planner();
+  memset(p, 0, sizeof(*p));
+  p->d = *d;
+  const int E = d->E, H = d->H, nd = d->nd;
+  p->nq = 32 + 16 * (H / 128);
+  const size_t sizes[] = {
+      (size_t)p->nq * 2048,      // wstream
+      (size_t)128 * E,           // w1g
+      128, (size_t)(nd > 0 ? nd : 1) * 128, 64, 128, 256, 4 * 256, 4, (size_t)4 * H, (size_t)H, (size_t)E};
+  size_t total = 0;
+  for (size_t s : sizes) total += (s + 63) / 64 * 64;
+  // torch-layout copies for single-call APIs
+  const size_t wt[7] = {(size_t)128 * (2 * E + nd), 64 * 128, 128 * 64, 256 * 128, 4 * 256, (size_t)H * (E + 4), (size_t)E * H};
+  const size_t bt[7] = {128, 64, 128, 256, 4, (size_t)H, (size_t)E};
+  for (int i = 0; i < 7; ++i) total += (wt[i] + 63) / 64 * 64 + (bt[i] + 63) / 64 * 64;
+  cudaError_t e = cudaMalloc(&p->blob, total * sizeof(float));
+  if (e != cudaSuccess) {
+    set_error("planner_create: cudaMalloc(%zu) failed: %s", total * sizeof(float), cudaGetErrorString(e));
+    delete p;
+    return NDP_ERR_CUDA;
+  }
+  p->blob_floats = total;
+  float* cur = p->blob;
+  auto take = [&](size_t n) { float* r = cur; cur += (n + 63) / 64 * 64; return r; };
+  p->wstream = take(sizes[0]); p->w1g = take(sizes[1]); p->b1 = take(sizes[2]); p->w1n = take(sizes[3]);
+  p->b2 = take(sizes[4]); p->b3 = take(sizes[5]); p->b4 = take(sizes[6]); p->w5 = take(sizes[7]);
+  p->b5 = take(sizes[8]); p->wf1a = take(sizes[9]); p->bf1 = take(sizes[10]); p->bf2 = take(sizes[11]);
+  for (int i = 0; i < 7; ++i) { p->Wt[i] = take(wt[i]); p->bt[i] = take(bt[i]); }
+  *out = p;
+  return NDP_OK;
+}
+
+extern "C" void ndp_planner_destroy(ndp_planner* p) {
+  if (!p) return;
+  if (p->blob) cudaFree(p->blob);
+  if (p->scratch) cudaFree(p->scratch);
+  delete p;
+}
+
+static int pack(cudaStream_t s, float* dst, const float* src, int ld, int n0, int k0, int Kc, int N) {
+  const int total = Kc * N;
+  pack_T_kernel<<<(total + 255) / 256, 256, 0, s>>>(dst, src, ld, n0, k0, Kc, N);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const float* const* b,
+                                int n_tensors, void* stream) {
+  NDP_CHECK_ARG(p && W && b && n_tensors == 7, "planner_load: expects 7 weight and 7 bias tensors");
+  for (int i = 0; i < 7; ++i) NDP_CHECK_ARG(W[i] && b[i], "planner_load: tensor %d is null", i);
+  if (int rc = device_check()) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int E = p->d.E, H = p->d.H, nd = p->d.nd, C1 = 2 * E + nd;
+  const size_t wt[7] = {(size_t)128 * C1, 64 * 128, 128 * 64, 256 * 128, 4 * 256, (size_t)H * (E + 4), (size_t)E * H};
+  const size_t bt[7] = {128, 64, 128, 256, 4, (size_t)H, (size_t)E};
+  for (int i = 0; i < 7; ++i) {
+    NDP_CUDA(cudaMemcpyAsync(p->Wt[i], W[i], wt[i] * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    NDP_CUDA(cudaMemcpyAsync(p->bt[i], b[i], bt[i] * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  }
+  // ---- weight stream in consumption order (see k1_rollout_f32.cu), all blocks are W^T [K][N] row-major
+  float* ws = p->wstream;
+  int rc;
+  if ((rc = pack(s, ws, p->Wt[0], C1, 0, 0, 128, 128))) return rc;  ws += 128 * 128;   // gen.fc1 state cols
+  if ((rc = pack(s, ws, p->Wt[1], 128, 0, 0, 128, 64))) return rc;  ws += 128 * 64;    // gen.fc2
+  if ((rc = pack(s, ws, p->Wt[2], 64, 0, 0, 64, 128))) return rc;   ws += 64 * 128;    // gen.fc3
+  for (int h = 0; h < 2; ++h) {                                                       // gen.fc4 halves
+    if ((rc = pack(s, ws, p->Wt[3], 128, h * 128, 0, 128, 128))) return rc;
+    ws += 128 * 128;
+  }
+  for (int c = 0; c < H / 128; ++c) {
+    if ((rc = pack(s, ws, p->Wt[5], E + 4, c * 128, 0, 128, 128))) return rc;  ws += 128 * 128;  // fwd.fc1 state cols, hidden chunk c
+    if ((rc = pack(s, ws, p->Wt[6], H, 0, c * 128, 128, 128))) return rc;      ws += 128 * 128;  // fwd.fc2 rows of hidden chunk c
+  }
+  // ---- side parameters
+  NDP_CUDA(cudaMemcpy2DAsync(p->w1g, E * sizeof(float), p->Wt[0] + E, C1 * sizeof(float), E * sizeof(float), 128,
+                             cudaMemcpyDeviceToDevice, s));                       // goal columns [128][E]
+  if (nd > 0 && (rc = pack(s, p->w1n, p->Wt[0], C1, 0, 2 * E, nd, 128))) return rc;  // noise cols -> [nd][128]
+  if ((rc = pack(s, p->wf1a, p->Wt[5], E + 4, 0, E, 4, H))) return rc;               // action cols -> [4][H]
+  NDP_CUDA(cudaMemcpyAsync(p->b1, p->bt[0], 128 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  NDP_CUDA(cudaMemcpyAsync(p->b2, p->bt[1], 64 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  NDP_CUDA(cudaMemcpyAsync(p->b3, p->bt[2], 128 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  NDP_CUDA(cudaMemcpyAsync(p->b4, p->bt[3], 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  NDP_CUDA(cudaMemcpyAsync(p->w5, p->Wt[4], 4 * 256 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  NDP_CUDA(cudaMemcpyAsync(p->b5, p->bt[4], 4 * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  NDP_CUDA(cudaMemcpyAsync(p->bf1, p->bt[5], (size_t)H * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  NDP_CUDA(cudaMemcpyAsync(p->bf2, p->bt[6], (size_t)E * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  p->loaded = true;
+  return NDP_OK;
+}
+
+extern "C" int ndp_planner_workspace_bytes(const ndp_planner* p, int G, int K, size_t* bytes) {
+  NDP_CHECK_ARG(p && bytes && G >= 0 && K >= 0, "planner_workspace_bytes: bad arguments");
+  *bytes = (size_t)(G > 0 ? G : 1) * 128 * sizeof(float) + 256;
+  return NDP_OK;
+}
+
+extern "C" int ndp_rollout_score(ndp_planner* p, const float* e0, const float* goal, const float* noise,
+                                 int G, int K, float* cost, float* a0, float* state_T,
+                                 void* ws, size_t ws_bytes, void* stream) {
+  NDP_CHECK_ARG(p && p->loaded, "rollout_score: planner has no weights (call ndp_planner_load)");
+  NDP_CHECK_ARG(G >= 0 && K >= 0, "rollout_score: bad G/K");
+  if (int rc = device_check()) return rc;
+  if (G == 0 || K == 0) return NDP_OK;
+  NDP_CHECK_ARG(e0 && goal && cost && a0, "rollout_score: null tensor");
+  NDP_CHECK_ARG(noise || p->d.nd == 0, "rollout_score: noise is required (noise_dim=%d)", p->d.nd);
+  const size_t need = (size_t)G * 128 * sizeof(float);
+  if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
+  const long long tiles = (long long)G * ((K + 127) / 128);
+  NDP_CHECK_ARG(tiles <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
+  cudaStream_t s = (cudaStream_t)stream;
+  float* b1g = reinterpret_cast<float*>(ws);
+  goal_bias_kernel<<<dim3(G, 16), 256, 0, s>>>(p->w1g, p->b1, goal, p->d.E, b1g);
+  NDP_LAUNCH_CHECK();
+  RolloutParams rp;
+  rp.wstream = p->wstream; rp.b1g = b1g; rp.w1n = p->w1n; rp.b2 = p->b2; rp.b3 = p->b3; rp.b4 = p->b4;
+  rp.w5 = p->w5; rp.b5 = p->b5; rp.wf1a = p->wf1a; rp.bf1 = p->bf1; rp.bf2 = p->bf2;
+  rp.e0 = e0; rp.goal = goal; rp.noise = noise; rp.cost = cost; rp.a0 = a0; rp.state_T = state_T;
+  rp.G = G; rp.K = K; rp.T = p->d.T; rp.nd = p->d.nd; rp.H = p->d.H;
+  rp.tiles_per_goal = (K + 127) / 128; rp.nq = p->nq;
+  return launch_rollout_f32(rp, s);
+}
+
+static int ensure_scratch(ndp_planner* p, size_t floats) {
+  if (p->scratch_floats >= floats) return NDP_OK;
+  if (p->scratch) cudaFree(p->scratch);
+  p->scratch = nullptr; p->scratch_floats = 0;
+  NDP_CUDA(cudaMalloc(&p->scratch, floats * sizeof(float)));
+  p->scratch_floats = floats;
+  return NDP_OK;
+}
+
+static int linear(cudaStream_t s, const float* in0, int K0, const float* in1, int K1, const float* W,
+                  const float* b, int N, int B, int relu, const float* res, float* out) {
+  const long long warps = (long long)B * N;
+  const long long blocks = (warps + 7) / 8;
+  NDP_CHECK_ARG(blocks <= 0x7FFFFFFF, "batch too large");
+  linear_kernel<<<(unsigned)blocks, 256, 0, s>>>(in0, K0, in1, K1, W, b, N, B, relu, res, out);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+extern "C" int ndp_generator_forward(ndp_planner* p, const float* z, int B, float* a, void* stream) {
+  NDP_CHECK_ARG(p && p->loaded, "generator_forward: planner has no weights");
+  NDP_CHECK_ARG(B >= 0, "generator_forward: bad B");
+  if (int rc = device_check()) return rc;
+  if (B == 0) return NDP_OK;
+  NDP_CHECK_ARG(z && a, "generator_forward: null tensor");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (int rc = ensure_scratch(p, (size_t)B * 512)) return rc;
+  float* h1 = p->scratch; float* h2 = h1 + (size_t)B * 256;
+  const int C1 = 2 * p->d.E + p->d.nd;
+  int rc;
+  if ((rc = linear(s, z, C1, nullptr, 0, p->Wt[0], p->bt[0], 128, B, 1, nullptr, h1))) return rc;
+  if ((rc = linear(s, h1, 128, nullptr, 0, p->Wt[1], p->bt[1], 64, B, 1, nullptr, h2))) return rc;
+  if ((rc = linear(s, h2, 64, nullptr, 0, p->Wt[2], p->bt[2], 128, B, 1, nullptr, h1))) return rc;
+  if ((rc = linear(s, h1, 128, nullptr, 0, p->Wt[3], p->bt[3], 256, B, 1, nullptr, h2))) return rc;
+  return linear(s, h2, 256, nullptr, 0, p->Wt[4], p->bt[4], 4, B, 0, nullptr, a);
+}
+
+extern "C" int ndp_forward_step(ndp_planner* p, const float* state, const float* action, int B,
+                                float* next_state, void* stream) {
+  NDP_CHECK_ARG(p && p->loaded, "forward_step: planner has no weights");
+  NDP_CHECK_ARG(B >= 0, "forward_step: bad B");
+  if (int rc = device_check()) return rc;
+  if (B == 0) return NDP_OK;
+  NDP_CHECK_ARG(state && action && next_state, "forward_step: null tensor");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (int rc = ensure_scratch(p, (size_t)B * (size_t)(p->d.H > 512 ? p->d.H : 512))) return rc;
+  int rc;
+  if ((rc = linear(s, state, p->d.E, action, 4, p->Wt[5], p->bt[5], p->d.H, B, 1, nullptr, p->scratch))) return rc;
+  return linear(s, p->scratch, p->d.H, nullptr, 0, p->Wt[6], p->bt[6], p->d.E, B, 0, state, next_state);
+}

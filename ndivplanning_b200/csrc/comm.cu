@@ -1,0 +1,132 @@
+// Thin NCCL wrapper for the two latency-bound collectives of the sharded path:
+//   plan selection : one ncclAllReduce(ncclUint64, ncclMin) over packed (cost,index) keys
+//   ndiv row sums  : ncclAllGather of [sx | sz] row blocks, ncclSum of the scalar loss
+// libnccl is dlopen'ed lazily so the library loads on machines without NCCL (no link-time
+// dependency); symbols resolve against the copy torch already loaded when hosted by PyTorch.
+#include <dlfcn.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace ndp {
+
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+enum { ncclSuccess_ = 0 };
+// values from nccl.h (stable across NCCL 2.x)
+enum { kNcclUint64 = 5, kNcclFloat32 = 7 };
+enum { kNcclSum = 0, kNcclMin = 3 };
+
+struct NcclApi {
+  void* h = nullptr;
+  int (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  int (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+
+static NcclApi* nccl() {
+  static NcclApi api;
+  static bool tried = false;
+  if (tried) return api.h ? &api : nullptr;
+  tried = true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  for (const char* n : names) {
+    api.h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (api.h) break;
+  }
+  if (!api.h) { set_error("cannot dlopen libnccl.so.2: %s", dlerror()); return nullptr; }
+#define NDP_SYM(field, name)                                                  \
+  *(void**)(&api.field) = dlsym(api.h, name);                                 \
+  if (!api.field) { set_error("libnccl lacks %s", name); api.h = nullptr; return nullptr; }
+  NDP_SYM(GetUniqueId, "ncclGetUniqueId")
+  NDP_SYM(CommInitRank, "ncclCommInitRank")
+  NDP_SYM(CommDestroy, "ncclCommDestroy")
+  NDP_SYM(AllReduce, "ncclAllReduce")
+  NDP_SYM(AllGather, "ncclAllGather")
+  NDP_SYM(GetErrorString, "ncclGetErrorString")
+#undef NDP_SYM
+  return &api;
+}
+
+}  // namespace ndp
+
+struct ndp_comm {
+  ndp::ncclComm_t comm;
+  int rank, world;
+};
+
+using namespace ndp;
+
+#define NDP_NCCL(call)                                                          \
+  do {                                                                          \
+    int r__ = (call);                                                           \
+    if (r__ != 0) {                                                             \
+      set_error("%s failed: %s", #call, api->GetErrorString(r__));              \
+      return NDP_ERR_NCCL;                                                      \
+    }                                                                           \
+  } while (0)
+
+extern "C" int ndp_comm_unique_id(void* id128_host) {
+  NDP_CHECK_ARG(id128_host, "comm_unique_id: null");
+  NcclApi* api = nccl();
+  if (!api) return NDP_ERR_NCCL;
+  ncclUniqueId id;
+  NDP_NCCL(api->GetUniqueId(&id));
+  memcpy(id128_host, &id, sizeof(id));
+  return NDP_OK;
+}
+
+extern "C" int ndp_comm_create(ndp_comm** out, const void* id128_host, int rank, int world) {
+  NDP_CHECK_ARG(out && id128_host && world >= 1 && rank >= 0 && rank < world, "comm_create: bad arguments");
+  if (int rc = device_check()) return rc;
+  NcclApi* api = nccl();
+  if (!api) return NDP_ERR_NCCL;
+  ncclUniqueId id;
+  memcpy(&id, id128_host, sizeof(id));
+  ndp_comm* c = new ndp_comm{nullptr, rank, world};
+  int r = api->CommInitRank(&c->comm, world, id, rank);
+  if (r != 0) {
+    set_error("ncclCommInitRank failed: %s", api->GetErrorString(r));
+    delete c;
+    return NDP_ERR_NCCL;
+  }
+  *out = c;
+  return NDP_OK;
+}
+
+extern "C" int ndp_comm_allreduce_min_u64(ndp_comm* c, uint64_t* buf, int count, void* stream) {
+  NDP_CHECK_ARG(c && buf && count >= 0, "allreduce_min_u64: bad arguments");
+  NcclApi* api = nccl();
+  if (!api) return NDP_ERR_NCCL;
+  NDP_NCCL(api->AllReduce(buf, buf, (size_t)count, kNcclUint64, kNcclMin, c->comm, (cudaStream_t)stream));
+  count_launch();
+  return NDP_OK;
+}
+
+extern "C" int ndp_comm_allreduce_sum_f32(ndp_comm* c, float* buf, int count, void* stream) {
+  NDP_CHECK_ARG(c && buf && count >= 0, "allreduce_sum_f32: bad arguments");
+  NcclApi* api = nccl();
+  if (!api) return NDP_ERR_NCCL;
+  NDP_NCCL(api->AllReduce(buf, buf, (size_t)count, kNcclFloat32, kNcclSum, c->comm, (cudaStream_t)stream));
+  count_launch();
+  return NDP_OK;
+}
+
+extern "C" int ndp_comm_allgather_f32(ndp_comm* c, const float* send, float* recv, int count_per_rank,
+                                      void* stream) {
+  NDP_CHECK_ARG(c && send && recv && count_per_rank >= 0, "allgather_f32: bad arguments");
+  NcclApi* api = nccl();
+  if (!api) return NDP_ERR_NCCL;
+  NDP_NCCL(api->AllGather(send, recv, (size_t)count_per_rank, kNcclFloat32, c->comm, (cudaStream_t)stream));
+  count_launch();
+  return NDP_OK;
+}
+
+extern "C" void ndp_comm_destroy(ndp_comm* c) {
+  if (!c) return;
+  NcclApi* api = nccl();
+  if (api && c->comm) api->CommDestroy(c->comm);
+  delete c;
+}

@@ -1,0 +1,248 @@
+// K3 — segmented argmin / top-k over candidate costs.
+// Replaces the per-candidate python scan of the reference (mpc_eval.py:122,159-165):
+//   strict '<' from min_error = 1e10, first minimal index wins, NaN never wins.
+// Every cost becomes a u64  (ordered_key(cost) << 32) | index  so that one unsigned min
+// implements (cost, index) lexicographic order; the same word is what the multi-GPU
+// min-allreduce exchanges.  HBM-bound: G*K*4 bytes read once, float4-vectorised.
+#include "common.cuh"
+
+namespace ndp {
+
+static constexpr int kSelThreads = 256;
+static constexpr int kSelTile = 1024;     // elements per block iteration (4 per thread)
+static constexpr int kSelBuf = 2048;      // candidate buffer entries (u64) in smem
+static constexpr unsigned long long kPadKey = ~0ull;
+
+__device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    unsigned long long t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = t < v ? t : v;
+  }
+  return v;
+}
+
+// in-place ascending bitonic sort of buf[0..kSelBuf) by the whole block
+__device__ void block_bitonic_sort(unsigned long long* buf) {
+  for (int k = 2; k <= kSelBuf; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < kSelBuf; i += kSelThreads) {
+        int ixj = i ^ j;
+        if (ixj > i) {
+          unsigned long long a = buf[i], b = buf[ixj];
+          bool up = ((i & k) == 0);
+          if ((a > b) == up) { buf[i] = b; buf[ixj] = a; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+struct TopkState {
+  unsigned long long* buf;   // [kSelBuf]
+  int* cnt;                  // pending count
+  unsigned long long* thr;   // current admission threshold (exclusive)
+};
+
+// keep the `topk` smallest of buf[0..*cnt), set threshold; block-wide
+__device__ void topk_compact(TopkState s, int topk) {
+  __syncthreads();
+  int n = *s.cnt;
+  for (int i = n + threadIdx.x; i < kSelBuf; i += kSelThreads) s.buf[i] = kPadKey;
+  __syncthreads();
+  block_bitonic_sort(s.buf);
+  if (threadIdx.x == 0) {
+    int m = n < topk ? n : topk;
+    *s.cnt = m;
+    *s.thr = (m == topk) ? s.buf[topk - 1] : kPadKey;
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void topk_offer(TopkState s, unsigned long long p) {
+  if (p < *s.thr) {
+    int pos = atomicAdd(s.cnt, 1);
+    s.buf[pos] = p;   // capacity guaranteed by the compaction schedule
+  }
+}
+
+// MODE 0: input fp32 costs;  MODE 1: input packed u64 (merge of partials)
+template <int MODE>
+__global__ void __launch_bounds__(kSelThreads)
+select_kernel(const float* __restrict__ cost, const unsigned long long* __restrict__ packed_in,
+              int K, int chunk_len, int topk, int final_stage, long long idx_base,
+              unsigned long long* __restrict__ out_min,     // [G, chunks] or [G]
+              unsigned long long* __restrict__ out_topk,    // [G, chunks, topk] partial
+              int* __restrict__ topk_idx, float* __restrict__ topk_cost) {
+  __shared__ unsigned long long s_buf[kSelBuf];
+  __shared__ unsigned long long s_warpmin[kSelThreads / 32];
+  __shared__ unsigned long long s_thr;
+  __shared__ int s_cnt;
+  const int g = blockIdx.y, chunk = blockIdx.x, chunks = gridDim.x;
+  const int begin = chunk * chunk_len;
+  int end = begin + chunk_len; if (end > K) end = K;
+  TopkState st{s_buf, &s_cnt, &s_thr};
+  if (threadIdx.x == 0) { s_cnt = 0; s_thr = kPadKey; }
+  __syncthreads();
+
+  unsigned long long best = kPadKey;
+  const size_t seg = (size_t)g * (size_t)K;
+  for (int base = begin; base < end; base += kSelTile) {
+    unsigned long long p[4];
+    const int i0 = base + threadIdx.x * 4;
+    if (MODE == 0) {
+      const float* src = cost + seg + i0;
+      float c[4];
+      if (i0 + 3 < end && ((((size_t)(seg + i0)) & 3) == 0)) {
+        float4 v = __ldg(reinterpret_cast<const float4*>(src));
+        c[0] = v.x; c[1] = v.y; c[2] = v.z; c[3] = v.w;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          p[q] = ((unsigned long long)ordered_key(c[q] + 0.0f) << 32) | (unsigned)(i0 + q);
+      } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          p[q] = (i0 + q < end)
+                     ? (((unsigned long long)ordered_key(__ldg(src + q) + 0.0f) << 32) | (unsigned)(i0 + q))
+                     : kPadKey;
+      }
+    } else {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) p[q] = (i0 + q < end) ? packed_in[seg + i0 + q] : kPadKey;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) best = p[q] < best ? p[q] : best;
+    if (topk > 0) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (p[q] != kPadKey || MODE == 0) { if (i0 + q < end) topk_offer(st, p[q]); }
+      __syncthreads();
+      const int pending = s_cnt;   // uniform: read between two barriers
+      __syncthreads();
+      if (pending + kSelTile > kSelBuf) topk_compact(st, topk);
+    }
+  }
+  // ---- argmin: warp shuffle -> smem -> thread 0
+  best = warp_min_u64(best);
+  if ((threadIdx.x & 31) == 0) s_warpmin[threadIdx.x >> 5] = best;
+  if (topk > 0) topk_compact(st, topk); else __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long m = s_warpmin[0];
+#pragma unroll
+    for (int w = 1; w < kSelThreads / 32; ++w) m = s_warpmin[w] < m ? s_warpmin[w] : m;
+    if (final_stage) {
+      // reference rule: only costs strictly below 1e10 may win (mpc_eval.py:122,161-164)
+      float c = key_to_float((uint32_t)(m >> 32));
+      if (m == kPadKey || !(c < 1e10f)) m = kInvalidPacked;
+      else m = (m & 0xFFFFFFFF00000000ull) | (unsigned long long)((long long)(m & 0xFFFFFFFFull) + idx_base);
+      out_min[g] = m;
+    } else {
+      out_min[(size_t)g * chunks + chunk] = m;
+    }
+  }
+  if (topk > 0) {
+    const int n = s_cnt;
+    for (int i = threadIdx.x; i < topk; i += kSelThreads) {
+      unsigned long long v = i < n ? s_buf[i] : kPadKey;
+      if (final_stage) {
+        if (topk_idx) topk_idx[(size_t)g * topk + i] = (i >= n) ? -1 : (int)((long long)(v & 0xFFFFFFFFull) + idx_base);
+        if (topk_cost) topk_cost[(size_t)g * topk + i] = (i >= n) ? __int_as_float(0x7fc00000) : key_to_float((uint32_t)(v >> 32));
+      } else {
+        out_topk[((size_t)g * chunks + chunk) * topk + i] = v;
+      }
+    }
+  }
+}
+
+__global__ void gather_best_kernel(const float* __restrict__ a0, const unsigned long long* __restrict__ packed,
+                                   int G, int K, long long idx_base, float* __restrict__ best_action,
+                                   int* __restrict__ best_idx) {
+  int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  unsigned long long m = packed[g];
+  long long idx = (m == kInvalidPacked) ? 0 : (long long)(m & 0xFFFFFFFFull);
+  if (best_idx) best_idx[g] = (int)idx;
+  long long local = idx - idx_base;
+  if (best_action && local >= 0 && local < K) {
+    const float4 a = *reinterpret_cast<const float4*>(a0 + ((size_t)g * K + local) * 4);
+    *reinterpret_cast<float4*>(best_action + (size_t)g * 4) = a;
+  }
+}
+
+static void plan_chunks(int G, int K, int* chunks, int* chunk_len) {
+  if (K <= 0) { *chunks = 1; *chunk_len = kSelTile; return; }
+  int want = 592 / (G > 0 ? G : 1);
+  if (want < 1) want = 1;
+  int maxc = (K + 4095) / 4096;
+  int c = want < maxc ? want : maxc;
+  if (c < 1) c = 1;
+  int len = (K + c - 1) / c;
+  len = (len + kSelTile - 1) / kSelTile * kSelTile;
+  c = (K + len - 1) / len;
+  *chunks = c < 1 ? 1 : c;
+  *chunk_len = len;
+}
+
+}  // namespace ndp
+
+using namespace ndp;
+
+extern "C" int ndp_select_workspace_bytes(int G, int K, int topk, size_t* bytes) {
+  NDP_CHECK_ARG(bytes && G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "select: bad G/K/topk (topk<=128)");
+  int chunks, len;
+  plan_chunks(G, K, &chunks, &len);
+  *bytes = chunks > 1 ? (size_t)G * chunks * (size_t)(topk + 1) * 8 + 256 : 256;
+  return NDP_OK;
+}
+
+extern "C" int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
+                          uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
+                          void* ws, size_t ws_bytes, void* stream) {
+  NDP_CHECK_ARG(G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "select: bad G/K/topk (topk<=128)");
+  NDP_CHECK_ARG(G == 0 || ((cost || K == 0) && packed_min), "select: null cost/packed_min");
+  NDP_CHECK_ARG(idx_base >= 0 && idx_base + (int64_t)K <= 0xFFFFFFFFll, "select: global index must fit 32 bits");
+  NDP_CHECK_ARG(G <= 65535, "select: G must be <= 65535 per call");
+  if (int rc = device_check()) return rc;
+  if (G == 0) return NDP_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  int chunks, len;
+  plan_chunks(G, K, &chunks, &len);
+  auto* pm = reinterpret_cast<unsigned long long*>(packed_min);
+  if (chunks <= 1) {
+    select_kernel<0><<<dim3(1, G), kSelThreads, 0, s>>>(cost, nullptr, K, len > 0 ? len : kSelTile, topk, 1,
+                                                        (long long)idx_base, pm, nullptr, topk_idx, topk_cost);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
+  size_t need = (size_t)G * chunks * (size_t)(topk + 1) * 8;
+  if (ws_bytes < need || !ws) { set_error("select: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
+  auto* part_min = reinterpret_cast<unsigned long long*>(ws);
+  auto* part_topk = part_min + (size_t)G * chunks;
+  select_kernel<0><<<dim3(chunks, G), kSelThreads, 0, s>>>(cost, nullptr, K, len, topk, 0, 0, part_min,
+                                                           part_topk, nullptr, nullptr);
+  NDP_LAUNCH_CHECK();
+  // stage 2: argmin over partial mins and top-k over partial lists (entries keep LOCAL indices)
+  if (topk > 0) {
+    // merge lists: the min of the merged list equals the min of mins, so one launch does both
+    select_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, part_topk, chunks * topk,
+                                                        ((chunks * topk + kSelTile - 1) / kSelTile) * kSelTile,
+                                                        topk, 1, (long long)idx_base, pm, nullptr, topk_idx, topk_cost);
+  } else {
+    select_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, part_min, chunks,
+                                                        kSelTile, 0, 1, (long long)idx_base, pm, nullptr, nullptr, nullptr);
+  }
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+extern "C" int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,
+                                      int64_t idx_base, float* best_action, int32_t* best_idx, void* stream) {
+  NDP_CHECK_ARG(G >= 0 && packed_min, "gather: bad args");
+  if (int rc = device_check()) return rc;
+  if (G == 0) return NDP_OK;
+  gather_best_kernel<<<(G + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+      a0, reinterpret_cast<const unsigned long long*>(packed_min), G, K, (long long)idx_base, best_action, best_idx);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}

@@ -1,0 +1,151 @@
+"""FusedPlanner — the MPC inner loop of the reference (mpc_eval.py:124-165) as three kernels:
+K1 fused generator + T-step rollout + terminal cost, K3 segmented argmin/top-k, gather.
+
+    planner = FusedPlanner(generator, fwd_model, horizon=8)
+    out = planner.plan(e0[G,E], goal[G,E], noise[T,G,K,nd], topk=16)
+    out.best_idx[G]  out.best_action[G,4]  out.topk_idx[G,topk]  out.cost[G,K]
+
+`generator` is anything with the state_dict of reference models.gan.Decoder (fc1..fc5),
+`fwd_model` anything with LatentForward's (fc1, fc2).  CUDA-only; no CPU fallback.
+"""
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import PlannerDesc, check, f32c, lib, ptr, require_cuda, stream_ptr
+
+INVALID_PACKED = 0xFFFFFFFF00000000
+
+
+@dataclass
+class Plan:
+    best_idx: torch.Tensor        # [G] int32 (global candidate index)
+    best_action: torch.Tensor     # [G,4]
+    packed_min: torch.Tensor      # [G] int64 view of the u64 (okey(cost)<<32 | idx)
+    cost: torch.Tensor            # [G,K]
+    a0: torch.Tensor              # [G,K,4]
+    topk_idx: Optional[torch.Tensor] = None    # [G,topk] int32
+    topk_cost: Optional[torch.Tensor] = None   # [G,topk]
+    state_T: Optional[torch.Tensor] = None     # [G,K,E]
+
+
+def select_plan(cost: torch.Tensor, topk: int = 0, idx_base: int = 0):
+    """K3 alone: cost [G,K] -> (packed_min[G] int64, topk_idx[G,topk] int32 | None, topk_cost | None).
+    Replaces the python scan mpc_eval.py:159-164 (strict <, first index, init 1e10, NaN loses)."""
+    require_cuda(cost)
+    c = f32c(cost)
+    G, K = c.shape
+    dev = c.device
+    packed = torch.empty(G, dtype=torch.int64, device=dev)
+    tk_idx = torch.empty(G, topk, dtype=torch.int32, device=dev) if topk > 0 else None
+    tk_cost = torch.empty(G, topk, dtype=torch.float32, device=dev) if topk > 0 else None
+    n = C.c_size_t()
+    check(lib().ndp_select_workspace_bytes(G, K, topk, C.byref(n)))
+    ws = torch.empty(max(n.value, 8), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib().ndp_select(ptr(c), G, K, topk, idx_base, ptr(packed), ptr(tk_idx), ptr(tk_cost), ptr(ws),
+                               ws.numel(), stream_ptr(dev)))
+    return packed, tk_idx, tk_cost
+
+
+def unpack_index(packed: torch.Tensor) -> torch.Tensor:
+    """index half of the packed key (invalid key decodes to 0, like best_act_ind = 0)."""
+    return (packed & 0xFFFFFFFF).to(torch.int64)
+
+
+class FusedPlanner:
+    def __init__(self, generator, fwd_model, *, horizon: int, precision: str = "fp32", device=None):
+        g, f = generator.state_dict(), fwd_model.state_dict()
+        names = ["fc1", "fc2", "fc3", "fc4", "fc5"]
+        Ws = [g[f"{n}.weight"] for n in names] + [f["fc1.weight"], f["fc2.weight"]]
+        bs = [g[f"{n}.bias"] for n in names] + [f["fc1.bias"], f["fc2.bias"]]
+        H, EA = f["fc1.weight"].shape
+        E = f["fc2.weight"].shape[0]
+        if EA != E + 4:
+            raise _lib.NdpError(f"forward model fc1 expects E+4 inputs, got {EA} for E={E}")
+        nd = g["fc1.weight"].shape[1] - 2 * E
+        if nd < 0 or tuple(g["fc5.weight"].shape) != (4, 256):
+            raise _lib.NdpError("generator does not have the models.gan.Decoder layout (gan.py:67-71)")
+        if device is None:
+            device = Ws[0].device if Ws[0].is_cuda else torch.device("cuda", torch.cuda.current_device()) \
+                if torch.cuda.is_available() else None
+        if device is None:
+            raise _lib.NdpError("CUDA is not available; FusedPlanner has no CPU fallback")
+        self.device = torch.device(device)
+        self.E, self.H, self.nd, self.T = E, H, nd, int(horizon)
+        prec = {"fp32": _lib.PREC_FP32, "f16x3": _lib.PREC_F16X3, "f16": _lib.PREC_F16}[precision]
+        self.precision = precision
+        self._h = C.c_void_p()
+        desc = PlannerDesc(E, nd, 4, H, self.T, prec)
+        with torch.cuda.device(self.device):
+            check(lib().ndp_planner_create(C.byref(self._h), C.byref(desc)))
+            Wd = [f32c(w.to(self.device)) for w in Ws]
+            bd = [f32c(b.to(self.device)) for b in bs]
+            Wp = (C.c_void_p * 7)(*[w.data_ptr() for w in Wd])
+            bp = (C.c_void_p * 7)(*[b.data_ptr() for b in bd])
+            check(lib().ndp_planner_load(self._h, Wp, bp, 7, stream_ptr(self.device)))
+            torch.cuda.current_stream(self.device).synchronize()   # sources may now be released
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                lib().ndp_planner_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    # ---- K1 ---------------------------------------------------------------------------------
+    def rollout_score(self, e0, goal, noise, want_state=False):
+        """e0, goal [G,E]; noise [T,G,K,nd] -> (cost[G,K], a0[G,K,4], state_T[G,K,E]|None)."""
+        require_cuda(e0, goal, noise)
+        e0c, gc, nz = f32c(e0), f32c(goal), f32c(noise)
+        T, G, K, nd = nz.shape
+        if T != self.T or nd != self.nd or tuple(e0c.shape) != (G, self.E) or tuple(gc.shape) != (G, self.E):
+            raise _lib.NdpError(f"shape mismatch: noise {tuple(nz.shape)} e0 {tuple(e0c.shape)} for "
+                                f"T={self.T} nd={self.nd} E={self.E}")
+        dev = self.device
+        cost = torch.empty(G, K, dtype=torch.float32, device=dev)
+        a0 = torch.empty(G, K, 4, dtype=torch.float32, device=dev)
+        sT = torch.empty(G, K, self.E, dtype=torch.float32, device=dev) if want_state else None
+        n = C.c_size_t()
+        check(lib().ndp_planner_workspace_bytes(self._h, G, K, C.byref(n)))
+        ws = torch.empty(max(n.value, 8), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().ndp_rollout_score(self._h, ptr(e0c), ptr(gc), ptr(nz), G, K, ptr(cost), ptr(a0), ptr(sT),
+                                          ptr(ws), ws.numel(), stream_ptr(dev)))
+        return cost, a0, sT
+
+    # ---- K1 + K3 + gather ---------------------------------------------------------------------
+    def plan(self, e0, goal, noise, topk: int = 0, idx_base: int = 0, want_state=False) -> Plan:
+        cost, a0, sT = self.rollout_score(e0, goal, noise, want_state)
+        packed, tk_idx, tk_cost = select_plan(cost, topk, idx_base)
+        G, K = cost.shape
+        best_action = torch.zeros(G, 4, dtype=torch.float32, device=self.device)
+        best_idx = torch.empty(G, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib().ndp_gather_best_action(ptr(a0), ptr(packed), G, K, idx_base, ptr(best_action),
+                                               ptr(best_idx), stream_ptr(self.device)))
+        return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT)
+
+    # ---- single-call module semantics (drop-in for generator(z) / fwd_model(state, a)) -------
+    def generator(self, z):
+        """models/gan.py:79-86 — z [B, 2E+nd] -> actions [B,4]."""
+        require_cuda(z)
+        zc = f32c(z)
+        out = torch.empty(zc.shape[0], 4, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            check(lib().ndp_generator_forward(self._h, ptr(zc), zc.shape[0], ptr(out), stream_ptr(self.device)))
+        return out
+
+    def forward_model(self, state, action):
+        """forward_encoder.py:105-114 (eval mode) — returns state + residual, same shape as state."""
+        require_cuda(state, action)
+        sc, ac = f32c(state).reshape(state.shape[0], -1), f32c(action)
+        out = torch.empty_like(sc)
+        with torch.cuda.device(self.device):
+            check(lib().ndp_forward_step(self._h, ptr(sc), ptr(ac), sc.shape[0], ptr(out), stream_ptr(self.device)))
+        return out.view(state.shape)

@@ -1,0 +1,157 @@
+"""GPU: K1 fused rollout (+K3 selection) against the oracle loop (mpc_eval.py:124-165) on the
+same seeded weights/inputs, and against the golden vectors of the unmodified reference.
+
+Tolerances (north_star): fp32 costs within 1e-4 relative; argmin index and top-k set
+bit-exact.  fp32 summation order differs between the kernel and MKL, so index equality is
+asserted where the fp64 arbiter's gap exceeds the fp32 error bound (class 1) and otherwise the
+chosen candidate must be fp64-optimal to 1e-6 (class 2) — SURVEY.md §7.4-1c.  On the sep30
+bench weights every case must be class 1.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ndiv_oracle as O
+from ndivplanning_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+COST_RTOL = 1e-4
+
+
+def _oracle_models(gen_p, fwd_p, nd, E, H, double=False):
+    gen, fwd = O.GeneratorMLP(nd).eval(), O.LatentForward(E, H).eval()
+    gen.load_state_dict(gen_p.state_dict()); fwd.load_state_dict(fwd_p.state_dict())
+    return (gen.double(), fwd.double()) if double else (gen, fwd)
+
+
+def _check_selection(cost_gpu, best_gpu, topk_gpu, cost64, topk):
+    """class-1/class-2 protocol; returns 1 or 2"""
+    order = np.argsort(cost64, kind="stable")
+    gap_rel = (cost64[order[1]] - cost64[order[0]]) / cost64[order[0]] if len(order) > 1 else 1.0
+    klass = 1 if gap_rel > 8 * 3e-7 else 2
+    if klass == 1:
+        assert best_gpu == order[0]
+    else:
+        assert cost64[best_gpu] <= cost64[order[0]] * (1 + 1e-6)
+    if topk and len(order) > topk:
+        bgap = (cost64[order[topk]] - cost64[order[topk - 1]]) / cost64[order[topk - 1]]
+        if bgap > 8 * 3e-7:
+            assert set(topk_gpu) == set(order[:topk].tolist())
+        else:
+            assert max(cost64[i] for i in topk_gpu) <= cost64[order[topk - 1]] * (1 + 1e-6)
+    return klass
+
+
+@pytest.mark.parametrize("G,K,T,H,nd", [(1, 64, 1, 128, 2), (1, 128, 3, 256, 2), (2, 300, 4, 256, 2),
+                                        (1, 1024, 8, 1024, 2), (3, 130, 2, 384, 5), (1, 257, 5, 128, 1)])
+def test_rollout_matches_oracle(cuda, G, K, T, H, nd):
+    from ndivplanning_b200 import FusedPlanner
+    E = 128
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
+    e0, goal, noise = synthetic.make_plan_inputs(G, K, T, nd, E, seed=K + T)
+    pl = FusedPlanner(gen_p, fwd_p, horizon=T)
+    plan = pl.plan(e0.cuda(), goal.cuda(), noise.cuda(), topk=min(8, K), want_state=True)
+    gen, fwd = _oracle_models(gen_p, fwd_p, nd, E, H)
+    g64, f64 = _oracle_models(gen_p, fwd_p, nd, E, H, double=True)
+    for g in range(G):
+        ref = O.mpc_plan(gen, fwd, e0[g], goal[g], noise[:, g], topk=min(8, K))
+        ref64 = O.mpc_plan(g64, f64, e0[g].double(), goal[g].double(), noise[:, g].double())
+        c = plan.cost[g].cpu().numpy()
+        np.testing.assert_allclose(c, ref["cost"].numpy(), rtol=COST_RTOL)
+        np.testing.assert_allclose(c, ref64["cost"].numpy(), rtol=COST_RTOL)
+        np.testing.assert_allclose(plan.a0[g].cpu().numpy(), ref["a0"].numpy(), rtol=1e-4, atol=1e-5)
+        np.testing.assert_allclose(plan.state_T[g].cpu().numpy(), ref64["state_T"].numpy(), rtol=1e-3, atol=1e-4)
+        klass = _check_selection(c, int(plan.best_idx[g]), plan.topk_idx[g].cpu().tolist(),
+                                 ref64["cost"].numpy(), min(8, K))
+        assert klass == 1, "sep30 weights must separate candidates (SURVEY §7.4-1a)"
+        # selected action = step-0 action of the winner (mpc_eval.py:150-151,165)
+        np.testing.assert_allclose(plan.best_action[g].cpu().numpy(), ref["a0"][int(plan.best_idx[g])].numpy(),
+                                   rtol=1e-4, atol=1e-5)
+        # the kernel's own argmin is exactly the first-min of the kernel's own costs
+        assert int(plan.best_idx[g]) == O.select_first_min(plan.cost[g].cpu())
+
+
+@pytest.mark.parametrize("name", ["small", "cfg1"])
+def test_plan_golden(cuda, golden, name):
+    """explicit plan from the reference's own Decoder (golden), K=64 / K=1024 (BASELINE config 1)"""
+    from ndivplanning_b200 import FusedPlanner
+    g = golden["mpc"]
+    K, Th, seq, n_traj, E, H, nd, seed = [int(v) for v in g[f"{name}_params"]]
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
+    e0, goal, noise = synthetic.make_plan_inputs(1, K, Th, nd, E, seed=21)
+    plan = FusedPlanner(gen_p, fwd_p, horizon=Th).plan(e0.cuda(), goal.cuda(), noise.cuda(), topk=8)
+    np.testing.assert_allclose(plan.cost[0].cpu().numpy(), g[f"{name}_plan_cost"], rtol=COST_RTOL)
+    np.testing.assert_allclose(plan.a0[0].cpu().numpy(), g[f"{name}_plan_a0"], rtol=1e-4, atol=1e-5)
+    assert _check_selection(plan.cost[0].cpu().numpy(), int(plan.best_idx[0]), plan.topk_idx[0].cpu().tolist(),
+                            g[f"{name}_plan_cost64"], 8) == 1
+    assert int(plan.best_idx[0]) == int(g[f"{name}_plan_best"])
+    assert set(plan.topk_idx[0].cpu().tolist()) == set(g[f"{name}_plan_topk"].tolist())
+
+
+@pytest.mark.parametrize("name", ["small", "cfg1"])
+def test_fetch_push_control_evaluation_golden(cuda, golden, name):
+    """the drop-in function reproduces the unmodified reference's return tuple"""
+    from torch import nn
+    from ndivplanning_b200 import fetch_push_control_evaluation
+    from oracle.ref_stubs import DotMap
+    g = golden["mpc"]
+    K, Th, seq, n_traj, E, H, nd, seed = [int(v) for v in g[f"{name}_params"]]
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
+    images, actions = torch.from_numpy(g[f"{name}_images"]), torch.from_numpy(g[f"{name}_actions"])
+
+    class DS(torch.utils.data.Dataset):
+        seq_length = seq
+        def __len__(self): return n_traj
+        def __getitem__(self, i):
+            return images[i][:, :, None, None], torch.zeros(seq, 25), actions[i], torch.zeros(3)
+
+    cfg = DotMap(random_seed=seed, gpu_id=0, log_port=0,
+                 evaluation=dict(num_sample=1, noise_dim=nd, batch_size=1, threshold=0.05),
+                 mpc=dict(rollouts=K, time_horizon=Th))
+    a, i, best = fetch_push_control_evaluation(nn.Identity(), fwd_p, gen_p, DS(), cfg, return_indices=True)
+    assert np.array_equal(best.numpy(), g[f"{name}_best"])
+    np.testing.assert_allclose([a, i], g[f"{name}_tuple"], rtol=1e-4)
+
+
+def test_module_semantics(cuda, golden):
+    """generator(z) and fwd_model(state, a) single-call entry points (gan.py:79-86, forward_encoder.py:105-114)"""
+    from ndivplanning_b200 import FusedPlanner
+    g = golden["gen"]
+    torch.manual_seed(0)
+    gen = synthetic.GeneratorMLP(2)
+    fwd = synthetic.LatentForward(128, 256).eval()
+    pl = FusedPlanner(gen, fwd, horizon=1)
+    a = pl.generator(torch.from_numpy(g["nd2_z"]).cuda())
+    np.testing.assert_allclose(a.cpu().numpy(), g["nd2_a"], rtol=1e-4, atol=1e-6)
+    s, act = torch.randn(9, 128, 1, 1), torch.randn(9, 4)
+    with torch.no_grad():
+        want = fwd(s, act)
+    got = pl.forward_model(s.cuda(), act.cuda())
+    assert got.shape == s.shape
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), rtol=1e-4, atol=1e-5)
+
+
+def test_full_size_properties(cuda):
+    """BASELINE config 2 size (K=65,536, T=8): size-independent checks — permutation of
+    candidates permutes costs bit-exactly; duplicated noise gives identical costs; argmin of
+    kernel costs equals a torch argmin; cross-check a 512-candidate slice against the oracle."""
+    from ndivplanning_b200 import FusedPlanner
+    K, T, nd, E, H = 65536, 8, 2, 128, 1024
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
+    e0, goal, noise = synthetic.make_plan_inputs(1, K, T, nd, E, seed=5)
+    pl = FusedPlanner(gen_p, fwd_p, horizon=T)
+    plan = pl.plan(e0.cuda(), goal.cuda(), noise.cuda(), topk=16)
+    cost = plan.cost[0]
+    assert torch.isfinite(cost).all()
+    perm = torch.randperm(K)
+    plan2 = pl.plan(e0.cuda(), goal.cuda(), noise[:, :, perm].cuda(), topk=16)
+    assert torch.equal(plan2.cost[0], cost[perm.cuda()])
+    assert int(perm[int(plan2.best_idx[0])]) == int(plan.best_idx[0])
+    assert int(plan.best_idx[0]) == int(torch.argmin(cost))
+    assert set(plan.topk_idx[0].tolist()) == set(torch.sort(cost, stable=True).indices[:16].tolist())
+    gen, fwd = _oracle_models(gen_p, fwd_p, nd, E, H, double=True)
+    sl = slice(1000, 1512)
+    ref = O.mpc_plan(gen, fwd, e0[0].double(), goal[0].double(), noise[:, 0, sl].double())
+    np.testing.assert_allclose(cost[sl].cpu().numpy(), ref["cost"].numpy(), rtol=COST_RTOL)
+    full64 = None  # whole-K fp64 oracle is too slow for CI; the winner must beat the slice optimum
+    assert float(cost.min()) <= float(ref["cost"].min()) * (1 + 1e-4)

@@ -1,0 +1,69 @@
+"""CPU: the oracle (torch-CPU restatement) against the golden vectors produced by the
+unmodified reference (oracle/make_golden.py)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ndiv_oracle as O
+from ndivplanning_b200 import synthetic
+
+NDIV_CASES = ["ref_shape", "k2", "k3", "k64", "k256", "k100_ragged"]
+
+
+@pytest.mark.parametrize("name", NDIV_CASES)
+def test_ndiv_oracle_matches_reference(golden, name):
+    g = golden["ndiv"]
+    x, z = torch.from_numpy(g[f"{name}_x"]), torch.from_numpy(g[f"{name}_z"])
+    loss, grad = O.ndiv_fwd_bwd(x, z)
+    np.testing.assert_allclose(loss.numpy(), g[f"{name}_loss"], rtol=1e-6)
+    np.testing.assert_allclose(grad.numpy(), g[f"{name}_grad"], rtol=1e-5, atol=1e-8)
+    # closed-form gradient (what the kernel implements) vs the reference's autograd, fp64
+    ga = O.ndiv_grad_analytic(x.double(), z.double())
+    np.testing.assert_allclose(ga.numpy(), g[f"{name}_grad64"], rtol=1e-9, atol=1e-12)
+    if f"{name}_pairwise" in g:
+        np.testing.assert_allclose(O.compute_pairwise(x).numpy(), g[f"{name}_pairwise"], rtol=1e-6, atol=1e-7)
+        np.testing.assert_allclose(O.compute_pair_distance(x).numpy(), g[f"{name}_pairdist"], rtol=1e-6, atol=1e-8)
+
+
+def test_ndiv_k1_is_nan():
+    x, z = torch.randn(2, 1, 4), torch.rand(2, 1, 2)
+    assert torch.isnan(O.compute_pairwise_divergence(x, z))
+
+
+@pytest.mark.parametrize("nd", [2, 16])
+def test_generator_oracle_matches_reference(golden, nd):
+    g = golden["gen"]
+    torch.manual_seed(0)
+    gen = O.GeneratorMLP(nd).eval()
+    with torch.no_grad():
+        a = gen(torch.from_numpy(g[f"nd{nd}_z"]))
+    np.testing.assert_allclose(a.numpy(), g[f"nd{nd}_a"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["small", "cfg1"])
+def test_mpc_oracle_matches_reference(golden, name):
+    g = golden["mpc"]
+    K, Th, seq, n_traj, E, H, nd, seed = [int(v) for v in g[f"{name}_params"]]
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
+    gen, fwd = O.GeneratorMLP(nd).eval(), O.LatentForward(E, H).eval()
+    gen.load_state_dict(gen_p.state_dict()); fwd.load_state_dict(fwd_p.state_dict())
+    images, actions = torch.from_numpy(g[f"{name}_images"]), torch.from_numpy(g[f"{name}_actions"])
+    a, i, best = O.closed_loop_eval(gen, fwd, images, actions, K, Th, nd, seed=seed)
+    np.testing.assert_allclose([a, i], g[f"{name}_tuple"], rtol=1e-6)
+    assert np.array_equal(np.array(best), g[f"{name}_best"])
+    e0, goal, noise = synthetic.make_plan_inputs(1, K, Th, nd, E, seed=21)
+    plan = O.mpc_plan(gen, fwd, e0[0], goal[0], noise[:, 0], topk=8)
+    np.testing.assert_allclose(plan["cost"].numpy(), g[f"{name}_plan_cost"], rtol=1e-5)
+    assert plan["best_idx"] == int(g[f"{name}_plan_best"])
+    assert set(plan["topk_idx"].tolist()) == set(g[f"{name}_plan_topk"].tolist())
+
+
+def test_select_first_min_rules():
+    inf, nan = float("inf"), float("nan")
+    assert O.select_first_min(torch.tensor([3.0, 1.0, 1.0, 2.0])) == 1        # first minimal index
+    assert O.select_first_min(torch.tensor([nan, 5.0, nan, 4.0])) == 3        # NaN never wins
+    assert O.select_first_min(torch.tensor([1e10, 2e10, inf])) == 0           # nothing < 1e10 -> 0
+    assert O.select_first_min(torch.tensor([nan, nan])) == 0
+    assert O.select_topk(torch.tensor([2.0, 1.0, nan, 1.0, 0.5]), 3).tolist() == [4, 1, 3]
+    assert O.pack_key(0.5, 7) < O.pack_key(0.75, 3) < O.pack_key(float("nan"), 0)
+    assert O.pack_key(-1.0, 9) < O.pack_key(0.0, 0)
