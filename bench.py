@@ -127,3 +127,166 @@ def run_reference(args):
                                       f"mpc_eval.py:124-165 incl. python argmin, torch {torch.__version__} CPU fp32"},
            "e2e": {"value": v, "unit": "candidate-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out))
+
+
+# --------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------
+def run_gpu(args):
+    import torch.distributed as dist
+    from ndivplanning_b200 import FusedPlanner, diversity, launch_count, synthetic
+    from ndivplanning_b200.sharded import ShardedPlanner
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world} (launch with torch.distributed.run)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    c = CFG
+    G, K, T, E, nd, topk = c["G"], c["K"], c["T"], c["E"], c["nd"], c["topk"]
+    K_total = K * world
+    gen, fwd = synthetic.make_models(nd=nd, E=E, H=c["H"])
+    planner = FusedPlanner(gen, fwd, horizon=T, device=dev)
+    sharded = ShardedPlanner(planner) if world > 1 else None
+    e0_h, goal_h, noise_h = synthetic.make_plan_inputs(G, K, T, nd, E, seed=1 + rank)
+    e0_h, goal_h, _ = synthetic.make_plan_inputs(G, 1, 1, nd, E, seed=1)       # same goal on every rank
+    e0_h, goal_h, noise_h = e0_h.pin_memory(), goal_h.pin_memory(), noise_h.pin_memory()
+    e0, goal, noise = e0_h.to(dev), goal_h.to(dev), noise_h.to(dev)
+    flush = l2_flusher(dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def plan_resident():
+        if sharded:
+            return sharded.plan(e0, goal, noise, K_total, topk=topk)
+        return planner.plan(e0, goal, noise, topk=topk)
+
+    res_h = {"idx": torch.empty(G, dtype=torch.int32).pin_memory(), "act": torch.empty(G, 4).pin_memory(),
+             "key": torch.empty(G, dtype=torch.int64).pin_memory()}
+
+    def plan_e2e():
+        # host buffers in, host result out: H2D of this step's inputs + D2H of the plan inside the timed region
+        e0_d = e0_h.to(dev, non_blocking=True); goal_d = goal_h.to(dev, non_blocking=True)
+        nz_d = noise_h.to(dev, non_blocking=True)
+        p = sharded.plan(e0_d, goal_d, nz_d, K_total, topk=topk) if sharded else planner.plan(e0_d, goal_d, nz_d, topk=topk)
+        res_h["idx"].copy_(p.best_idx, non_blocking=True)
+        res_h["act"].copy_(p.best_action, non_blocking=True)
+        res_h["key"].copy_(p.packed_min, non_blocking=True)
+        return p
+
+    def timed(fn, steps, warmup, split=False):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        tot, k1 = 0.0, 0.0
+        pairs = []
+        for _ in range(steps):
+            flush()                                   # L2 flush between timed iterations (untimed)
+            a, b = ev(), ev()
+            a.record(); fn(); b.record()
+            pairs.append((a, b))
+        barrier()
+        tot = sum(a.elapsed_time(b) for a, b in pairs) / steps
+        return tot
+
+    def timed_k1(steps):
+        pairs = []
+        for _ in range(steps):
+            flush()
+            a, b = ev(), ev()
+            a.record(); planner.rollout_score(e0, goal, noise); b.record()
+            pairs.append((a, b))
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in pairs) / steps
+
+    sampler = ClockSampler(local)
+    plan0 = plan_resident()                            # sanity: a plan exists and is finite
+    assert torch.isfinite(plan0.cost).all()
+    n_before = None
+    for _ in range(args.warmup):
+        plan_resident()
+    barrier()
+    sampler.start()
+    n_before = launch_count()
+    ms = timed(plan_resident, args.steps, 0)
+    n_launch = launch_count() - n_before
+    k1_ms = timed_k1(args.steps)
+    ms_e2e = timed(plan_e2e, args.steps, args.warmup)
+    # ---- ndiv (BASELINE config 3) fwd+bwd, rows sharded when world > 1 is not timed here (N=1 figure per rank)
+    x_h, z_h = synthetic.make_ndiv_inputs(NDIV["N"], NDIV["k"], NDIV["Dx"], NDIV["Dz"])
+    x, z = x_h.to(dev), z_h.to(dev)
+
+    def ndiv_step():
+        xg = x.detach().requires_grad_(True)
+        loss = diversity.compute_pairwise_divergence(xg, z)
+        loss.backward()
+        return loss
+
+    ndiv_ms = timed(ndiv_step, args.steps, args.warmup)
+    clocks = sampler.finish()
+
+    def maxr(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    ms, k1_ms, ms_e2e, ndiv_ms = maxr(ms), maxr(k1_ms), maxr(ms_e2e), maxr(ndiv_ms)
+    if rank == 0:
+        pk = peaks()
+        units = G * K_total * T
+        value = units / (ms * 1e-3)
+        k1_tflops = G * K * T * F_ALG / (k1_ms * 1e-3) / 1e12
+        pairs = NDIV["N"] * NDIV["k"] ** 2
+        out = {
+            "metric": "mpc_candidate_steps_per_sec", "value": value, "unit": "candidate-steps/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": dict(workload="mpc_cfg2_K65536_T8_E128_H1024_nd2", per_gpu_K=K, K_total=K_total,
+                           l2_flush_between_steps=True, precision=planner.precision, weights="default-init sep30",
+                           **{k: v for k, v in c.items() if k != "K"}),
+            "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "candidate-steps/s", "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": int(noise_h.numel() * 4 + e0_h.numel() * 4 + goal_h.numel() * 4),
+                    "d2h_bytes_per_step": int(G * (4 + 16 + 8))},
+            "gpu_launches": int(n_launch),
+            "clocks": clocks,
+            "roofline": {"kernel": "rollout_f32_kernel", "bound": "tensor", "achieved": k1_tflops, "peak": pk["bf16"],
+                         "unit": "TFLOP/s", "frac": k1_tflops / pk["bf16"], "traffic": None,
+                         "peak_source": pk["src"] + " bf16 burst (kernel timed alone)",
+                         "kernel_ms": k1_ms, "flop_per_candidate_step": F_ALG,
+                         "note": "fp32 parity mode issues FFMA on CUDA cores (no tensor pipe); fraction is vs the "
+                                 "tensor roofline the path is ultimately bound by"},
+            "ndiv": {"metric": "ndiv_pairs_per_sec_fwd_bwd", "value": pairs / (ndiv_ms * 1e-3), "unit": "ordered pairs/s",
+                     "ms_per_step": ndiv_ms, "config": NDIV},
+        }
+        if world == 1:
+            t0 = time.perf_counter()
+            threads = os.cpu_count() or 1
+            times, cu = cpu_port_plan_rate(8192, 3, threads)
+            out["cpu_baseline"] = {"value": cu / min(times), "unit": "candidate-steps/s", "cores": threads, "kind": "port",
+                                   "sample": f"8192 of {K} candidates x T={T}, best of 3 after 1 warm-up, oracle port of "
+                                             f"mpc_eval.py:124-165 incl. python argmin scan; {time.perf_counter() - t0:.1f}s"}
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    a = ap.parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_gpu(a)
