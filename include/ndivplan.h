@@ -38,7 +38,8 @@ enum {
 enum {
   NDP_PREC_FP32 = 0,     /* CUDA-core FFMA, fp32 everywhere: parity mode            */
   NDP_PREC_F16X3 = 1,    /* tcgen05 kind::f16, 3-term hi/lo split operands, fp32 acc */
-  NDP_PREC_F16 = 2       /* tcgen05 kind::f16 single pass: bulk estimate, NOT parity */
+  NDP_PREC_F16 = 2,      /* tcgen05 kind::f16 single pass: bulk estimate (cost ~2e-4 rel) */
+  NDP_PREC_F16X2 = 3     /* tcgen05 kind::f16, activations split hi/lo, weights fp16: cost ~5e-5 rel */
 };
 
 typedef struct ndp_planner ndp_planner;

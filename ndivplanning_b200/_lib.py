@@ -8,7 +8,7 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libndivplan.so")
 
-PREC_FP32, PREC_F16X3, PREC_F16 = 0, 1, 2
+PREC_FP32, PREC_F16X3, PREC_F16, PREC_F16X2 = 0, 1, 2, 3
 
 
 class NdpError(RuntimeError):

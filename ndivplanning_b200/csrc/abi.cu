@@ -107,7 +107,9 @@ extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) 
   NDP_CHECK_ARG(d->nd >= 0 && d->nd <= 64, "planner_create: noise_dim must be in [0,64]");
   NDP_CHECK_ARG(d->H >= 128 && d->H % 128 == 0 && d->H <= 8192, "planner_create: H must be a multiple of 128 in [128,8192]");
   NDP_CHECK_ARG(d->T >= 1 && d->T <= 4096, "planner_create: T must be in [1,4096]");
-  NDP_CHECK_ARG(d->precision == NDP_PREC_FP32, "planner_create: precision mode %d not built in this version", d->precision);
+  NDP_CHECK_ARG(d->precision >= NDP_PREC_FP32 && d->precision <= NDP_PREC_F16X2, "planner_create: unknown precision mode %d", d->precision);
+  if (d->precision != NDP_PREC_FP32)
+    NDP_CHECK_ARG(d->nd <= 15 && d->H <= 2048, "planner_create: tensor-core modes need noise_dim<=15 and H<=2048 (got nd=%d H=%d); use NDP_PREC_FP32", d->nd, d->H);
   if (int rc = device_check()) return rc;
   ndp_planner* p = new ndp_planner();
   memset(p, 0, sizeof(*p));
@@ -145,6 +147,7 @@ extern "C" void ndp_planner_destroy(ndp_planner* p) {
   if (!p) return;
   if (p->blob) cudaFree(p->blob);
   if (p->scratch) cudaFree(p->scratch);
+  if (p->tc) tc_plan_destroy(p->tc);
   delete p;
 }
 
@@ -195,6 +198,11 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
   NDP_CUDA(cudaMemcpyAsync(p->b5, p->bt[4], 4 * sizeof(float), cudaMemcpyDeviceToDevice, s));
   NDP_CUDA(cudaMemcpyAsync(p->bf1, p->bt[5], (size_t)H * sizeof(float), cudaMemcpyDeviceToDevice, s));
   NDP_CUDA(cudaMemcpyAsync(p->bf2, p->bt[6], (size_t)E * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  if (p->d.precision != NDP_PREC_FP32) {
+    if (p->tc) { tc_plan_destroy(p->tc); p->tc = nullptr; }
+    const int np = p->d.precision == NDP_PREC_F16 ? 1 : (p->d.precision == NDP_PREC_F16X2 ? 2 : 3);
+    if (int rc2 = tc_plan_create(&p->tc, np, E, nd, H, p->Wt, p->bt, s)) return rc2;
+  }
   p->loaded = true;
   return NDP_OK;
 }
@@ -202,6 +210,7 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
 extern "C" int ndp_planner_workspace_bytes(const ndp_planner* p, int G, int K, size_t* bytes) {
   NDP_CHECK_ARG(p && bytes && G >= 0 && K >= 0, "planner_workspace_bytes: bad arguments");
   *bytes = (size_t)(G > 0 ? G : 1) * 128 * sizeof(float) + 256;
+  if (p->tc) { const size_t t = tc_workspace_bytes(p->tc, G); if (t > *bytes) *bytes = t; }
   return NDP_OK;
 }
 
@@ -214,6 +223,8 @@ extern "C" int ndp_rollout_score(ndp_planner* p, const float* e0, const float* g
   if (G == 0 || K == 0) return NDP_OK;
   NDP_CHECK_ARG(e0 && goal && cost && a0, "rollout_score: null tensor");
   NDP_CHECK_ARG(noise || p->d.nd == 0, "rollout_score: noise is required (noise_dim=%d)", p->d.nd);
+  if (p->tc)
+    return launch_rollout_tc(p->tc, e0, goal, noise, G, K, p->d.T, cost, a0, state_T, ws, ws_bytes, (cudaStream_t)stream);
   const size_t need = (size_t)G * 128 * sizeof(float);
   if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
   const long long tiles = (long long)G * ((K + 127) / 128);

@@ -1,0 +1,612 @@
+// K1 (tensor-core modes) — fused generator MLP + T-step latent rollout + terminal cost on
+// tcgen05 / TMEM, weights streamed by the TMA engine.  Same contract as k1_rollout_f32.cu
+// (reference mpc_eval.py:124-157 + :161, gan.py:79-86, forward_encoder.py:105-114).
+//
+// One CTA owns 128 candidates (TMEM lanes = candidates) of one goal for the whole horizon.
+//   * every layer is D[128 x N] (fp32, TMEM) = A[128 x K] (fp16, TMEM) x W[N x K]^T (fp16, smem);
+//     biases, the rank-nd noise update and the rank-4 action update ride in one extra K=16
+//     "ext" slab whose A operand lives in shared memory ([noise..,1], [action..,1] or [1,0..]);
+//   * epilogue warps turn an accumulator into the next layer's A operand IN PLACE in TMEM
+//     (tcgen05.ld -> relu -> fp16 hi[/lo] -> tcgen05.st); hidden activations never touch smem/HBM;
+//   * the fp32 state lives in shared memory and is updated with an exact fp32 add per step;
+//   * precision: NP=1 single pass fp16; NP=2 activations split hi+lo (2 MMAs per slab);
+//     NP=3 activations and weights split (a_hi*w_hi + a_lo*w_hi + a_hi*w_lo): fp32-grade.
+//
+// TMEM map (512 x 32-bit columns): R0 [0,128) R1 [128,256) DR [256,384) AS [384,512).
+// Warp roles: 0-7 epilogue (lane quadrant = warp%4, column half = warp/4), 8 MMA issue, 9 TMA.
+#include <string.h>
+#include "planner.cuh"
+#include "tc_common.cuh"
+
+namespace ndp {
+
+using namespace tc;
+
+static constexpr int kTcThreads = 320;
+static constexpr uint32_t kColR0 = 0, kColR1 = 128, kColDR = 256, kColAS = 384;
+// shared memory map (bytes)
+static constexpr uint32_t kOffState = 0;                 // fp32 state, [32 col4][128 rows] float4
+static constexpr uint32_t kOffExt = 65536;               // 5 ext slabs x 4 KB: noise hi/lo, action hi/lo, ones
+static constexpr uint32_t kExtSlab = 4096;
+static constexpr uint32_t kOffRing = kOffExt + 5 * kExtSlab;
+static constexpr uint32_t kRingBytes = 122880;           // 6 x 20 KB (NP<=2) or 3 x 40 KB (NP=3)
+static constexpr uint32_t kOffItems = kOffRing + kRingBytes;
+static constexpr uint32_t kItemsBytes = kTcMaxItems * sizeof(TcItem);
+static constexpr uint32_t kOffGoal = kOffItems + kItemsBytes;      // 128 floats
+static constexpr uint32_t kOffRed = kOffGoal + 512;                // 128 floats
+static constexpr uint32_t kOffBars = kOffRed + 512;                // mbarriers
+static constexpr uint32_t kTcSmemBytes = kOffBars + 256;
+
+template <int NP> struct RingCfg { static constexpr uint32_t slot = (NP == 3) ? 40960u : 20480u, nslot = kRingBytes / slot; };
+
+// ------------------------------------------------------------------------------------------
+// weight packing: fp32 torch [out,in] -> fp16 hi (/lo) canonical K-major core-matrix layout
+//   element (n, kk) of a block with N rows -> half index ((kk/8)*(N/8) + n/8)*64 + (n%8)*8 + kk%8
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void put_split(__half* hi, __half* lo, size_t idx, float v) {
+  const __half h = __float2half_rn(v);
+  hi[idx] = h;
+  if (lo) lo[idx] = __float2half_rn(v - __half2float(h));
+}
+
+__global__ void tc_pack_main_kernel(__half* __restrict__ hi, __half* __restrict__ lo, const float* __restrict__ W,
+                                    int ld, int n0, int k0, int N, int nslab, int nvalid) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int Kc = nslab * 16;
+  if (idx >= N * Kc) return;
+  const int n = idx / Kc, kk = idx % Kc;
+  const size_t pos = ((size_t)(kk / 8) * (N / 8) + n / 8) * 64 + (n % 8) * 8 + kk % 8;
+  put_split(hi, lo, pos, n < nvalid ? W[(size_t)(n0 + n) * ld + k0 + kk] : 0.f);
+}
+
+struct ExtCols {
+  const float* p[16];   // column k of the ext slab: value for row n is p[k][n * stride[k]]; null -> 0
+  int stride[16];
+};
+
+__global__ void tc_pack_ext_kernel(__half* __restrict__ hi, __half* __restrict__ lo, int N, int nvalid, ExtCols c) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= N * 16) return;
+  const int n = idx / 16, kk = idx % 16;
+  const size_t pos = ((size_t)(kk / 8) * (N / 8) + n / 8) * 64 + (n % 8) * 8 + kk % 8;
+  const float v = (c.p[kk] && n < nvalid) ? c.p[kk][(size_t)n * c.stride[kk]] : 0.f;
+  put_split(hi, lo, pos, v);
+}
+
+// per-goal ext block of generator fc1: columns [w1 noise cols (nd) | b1 + W1g . goal | 0 ...], N = 128.
+// The goal half of fc1 is constant per plan (the reference recomputes it per candidate and step,
+// mpc_eval.py:133,136-138).  One block per goal, one warp per output row.
+__global__ void tc_goal_ext_kernel(const float* __restrict__ W1, const float* __restrict__ b1,
+                                   const float* __restrict__ goal, int E, int nd, int with_lo,
+                                   __half* __restrict__ gext, size_t stride_halfs) {
+  const int g = blockIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int C1 = 2 * E + nd;
+  __half* hi = gext + (size_t)g * stride_halfs;
+  __half* lo = with_lo ? hi + 128 * 16 : nullptr;
+  for (int n = threadIdx.x >> 5; n < 128; n += blockDim.x >> 5) {
+    float acc = 0.f;
+    for (int e = lane; e < E; e += 32)
+      acc = fmaf(__ldg(W1 + (size_t)n * C1 + E + e), __ldg(goal + (size_t)g * E + e), acc);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    const float bias = acc + __ldg(b1 + n);
+    if (lane < 16) {
+      const int kk = lane;
+      float v = 0.f;
+      if (kk < nd) v = __ldg(W1 + (size_t)n * C1 + 2 * E + kk);
+      else if (kk == nd) v = bias;
+      const size_t pos = ((size_t)(kk / 8) * 16 + n / 8) * 64 + (n % 8) * 8 + kk % 8;
+      put_split(hi, lo, pos, v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// epilogue helpers (thread = one candidate row; `lane_addr` has the TMEM lane field set)
+// ------------------------------------------------------------------------------------------
+// 64 accumulator columns -> relu -> fp16 hi[/lo] written in place: hi at [0,32), lo at [32,64)
+template <int NP>
+__device__ __forceinline__ void relu_inplace64(uint32_t addr) {
+  uint32_t v[32], w[32];
+  tmem_ld32(addr, v);
+  tmem_ld32(addr + 32, w);
+  tmem_ld_wait();
+  uint32_t hi[32];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float x0 = fmaxf(__uint_as_float(v[2 * j]), 0.f), x1 = fmaxf(__uint_as_float(v[2 * j + 1]), 0.f);
+    hi[j] = pack_hi(x0, x1);
+    if (NP >= 2) v[j] = pack_lo(x0, x1, hi[j]);   // v[j] (j<16) is dead once pair j (<= 2j) was consumed
+  }
+  // second half; lo words go to w[] the same way
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float x0 = fmaxf(__uint_as_float(w[2 * j]), 0.f), x1 = fmaxf(__uint_as_float(w[2 * j + 1]), 0.f);
+    hi[16 + j] = pack_hi(x0, x1);
+    if (NP >= 2) w[j] = pack_lo(x0, x1, hi[16 + j]);
+  }
+  tmem_st16(addr, hi);
+  tmem_st16(addr + 16, hi + 16);
+  if (NP >= 2) {
+    tmem_st16(addr + 32, v);
+    tmem_st16(addr + 48, w);
+  }
+}
+// 32 accumulator columns (N=64 layer): hi at [0,16), lo at [16,32)
+template <int NP>
+__device__ __forceinline__ void relu_inplace32(uint32_t addr) {
+  uint32_t v[32];
+  tmem_ld32(addr, v);
+  tmem_ld_wait();
+  uint32_t hi[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float x0 = fmaxf(__uint_as_float(v[2 * j]), 0.f), x1 = fmaxf(__uint_as_float(v[2 * j + 1]), 0.f);
+    hi[j] = pack_hi(x0, x1);
+    if (NP >= 2) v[j] = pack_lo(x0, x1, hi[j]);
+  }
+  tmem_st16(addr, hi);
+  if (NP >= 2) tmem_st16(addr + 16, v);
+}
+
+// state row half (64 fp32 values, already in registers as s[]) -> AS operand region (hi [0,32), lo [32,64))
+template <int NP>
+__device__ __forceinline__ void store_state_operand(uint32_t addr, const float (&s)[64]) {
+  uint32_t hi[32], lo[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    hi[j] = pack_hi(s[2 * j], s[2 * j + 1]);
+    if (NP >= 2) lo[j] = pack_lo(s[2 * j], s[2 * j + 1], hi[j]);
+  }
+  tmem_st16(addr, hi);
+  tmem_st16(addr + 16, hi + 16);
+  if (NP >= 2) {
+    tmem_st16(addr + 32, lo);
+    tmem_st16(addr + 48, lo + 16);
+  }
+}
+
+// one row of an ext slab in shared memory: 16 values -> fp16 hi (and lo) in the canonical layout
+__device__ __forceinline__ void store_ext_row(uint8_t* slab_hi, uint8_t* slab_lo, int m, const float (&x)[16], bool second_chunk) {
+  const uint32_t off = (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16;
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    if (c == 1 && !second_chunk) break;
+    uint4 h, l;
+    h.x = pack_hi(x[8 * c + 0], x[8 * c + 1]); l.x = pack_lo(x[8 * c + 0], x[8 * c + 1], h.x);
+    h.y = pack_hi(x[8 * c + 2], x[8 * c + 3]); l.y = pack_lo(x[8 * c + 2], x[8 * c + 3], h.y);
+    h.z = pack_hi(x[8 * c + 4], x[8 * c + 5]); l.z = pack_lo(x[8 * c + 4], x[8 * c + 5], h.z);
+    h.w = pack_hi(x[8 * c + 6], x[8 * c + 7]); l.w = pack_lo(x[8 * c + 6], x[8 * c + 7], h.w);
+    *reinterpret_cast<uint4*>(slab_hi + c * 2048 + off) = h;
+    *reinterpret_cast<uint4*>(slab_lo + c * 2048 + off) = l;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// the kernel
+// ------------------------------------------------------------------------------------------
+template <int NP>
+__global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr uint32_t kSlot = RingCfg<NP>::slot, kNSlot = RingCfg<NP>::nslot;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = blockIdx.x / p.tiles_per_goal;
+  const int m0 = (blockIdx.x % p.tiles_per_goal) * 128;
+
+  float4* S4 = reinterpret_cast<float4*>(smem + kOffState);
+  uint8_t* ext_noise_hi = smem + kOffExt;
+  uint8_t* ext_noise_lo = ext_noise_hi + kExtSlab;
+  uint8_t* ext_act_hi = ext_noise_lo + kExtSlab;
+  uint8_t* ext_act_lo = ext_act_hi + kExtSlab;
+  uint8_t* ext_ones = ext_act_lo + kExtSlab;
+  TcItem* items = reinterpret_cast<TcItem*>(smem + kOffItems);
+  float* s_goal = reinterpret_cast<float*>(smem + kOffGoal);
+  float* s_red = reinterpret_cast<float*>(smem + kOffRed);
+  const uint32_t bars = smem_u32(smem + kOffBars);
+  // barrier map (8 bytes each): full[0..5] empty[6..11] d_full[12,13] a_ready[14,15]; tmem base at +128
+  auto bar_full = [&](uint32_t s) { return bars + 8 * s; };
+  auto bar_empty = [&](uint32_t s) { return bars + 8 * (6 + s); };
+  auto bar_dfull = [&](uint32_t e) { return bars + 8 * (12 + (e & 1)); };
+  auto bar_aready = [&](uint32_t e) { return bars + 8 * (14 + (e & 1)); };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffBars + 128);
+
+  // ---- one-time setup ----------------------------------------------------------------------
+  for (int i = tid; i < p.n_items * 8; i += kTcThreads)
+    reinterpret_cast<uint32_t*>(items)[i] = reinterpret_cast<const uint32_t*>(p.items)[i];
+  for (int i = tid; i < 5 * (int)kExtSlab / 16; i += kTcThreads)
+    reinterpret_cast<uint4*>(smem + kOffExt)[i] = make_uint4(0, 0, 0, 0);
+  if (tid < 128) s_goal[tid] = __ldg(p.goal + (size_t)g * 128 + tid);
+  if (tid == 0) {
+    for (uint32_t s = 0; s < kNSlot; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
+    mbar_init(bar_dfull(0), 1); mbar_init(bar_dfull(1), 1);
+    mbar_init(bar_aready(0), 8); mbar_init(bar_aready(1), 8);
+    fence_mbar_init();
+  }
+  if (warp == 8) tmem_alloc512(smem_u32((const void*)tmem_slot));
+  __syncthreads();
+  // "ones" slab: element k=0 of every row is 1.0 (fp16 0x3C00); rows are 16 B apart inside a core matrix
+  if (tid < 128) *reinterpret_cast<uint16_t*>(ext_ones + (tid >> 3) * 128 + (tid & 7) * 16) = 0x3C00;
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 9) {
+    // ===================== TMA producer: stream weight blocks into the ring =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      const uint8_t* gsrc = p.gext + (size_t)g * p.gext_stride;
+      for (int t = 0; t < p.T; ++t) {
+        for (int i = 0; i < p.n_items; ++i, ++it) {
+          const uint32_t slot = it % kNSlot, par = (it / kNSlot) & 1;
+          const uint32_t bytes = items[i].bytes, eb = items[i].ext_bytes;
+          mbar_wait(bar_empty(slot), par ^ 1);
+          mbar_expect_tx(bar_full(slot), bytes + eb);
+          const uint32_t dst = smem_u32(smem + kOffRing + slot * kSlot);
+          bulk_g2s(dst, p.stream + items[i].src_off, bytes, bar_full(slot));
+          if (eb) bulk_g2s(dst + bytes, gsrc, eb, bar_full(slot));
+        }
+      }
+    }
+  } else if (warp == 8) {
+    // ===================== MMA issuer ============================================================
+    if (lane == 0) {
+      uint32_t it = 0, aw = 0, ds = 0;
+      const uint64_t ones_desc = smem_desc(smem_u32(ext_ones), 2048, 128);
+      for (int t = 0; t < p.T; ++t) {
+        for (int i = 0; i < p.n_items; ++i, ++it) {
+          const TcItem I = items[i];
+          const uint32_t slot = it % kNSlot, par = (it / kNSlot) & 1;
+          if (I.wait_a) {
+            mbar_wait(bar_aready(aw), (aw >> 1) & 1);
+            ++aw;
+          }
+          mbar_wait(bar_full(slot), par);
+          fence_after_sync();
+          const uint32_t base = smem_u32(smem + kOffRing + slot * kSlot);
+          const uint32_t N = I.N, slab = N * 32, lbo = N * 16;
+          const uint32_t idesc = idesc_f16((int)N);
+          const uint32_t main_hi = I.n_main * slab;
+          const uint32_t ext_off = (NP == 3) ? 2 * main_hi : main_hi;
+          const uint32_t d = tmem + I.d_col;
+          uint32_t acc = I.first ? 0u : 1u;
+          for (uint32_t s = 0; s < I.n_main; ++s) {
+            const uint32_t j = I.j0 + s;
+            const uint32_t a = tmem + I.a_col + (j >> I.spc_shift) * I.cph + (j & ((1u << I.spc_shift) - 1)) * 8;
+            const uint64_t bd = smem_desc(base + s * slab, lbo, 128);
+            mma_ts(d, a, bd, idesc, acc);
+            acc = 1;
+            if (NP >= 2) mma_ts(d, a + I.cph / 2, bd, idesc, 1);
+            if (NP == 3) mma_ts(d, a, smem_desc(base + main_hi + s * slab, lbo, 128), idesc, 1);
+          }
+          if (I.ext_kind) {
+            const uint64_t bd = smem_desc(base + ext_off, lbo, 128);
+            uint64_t a_hi = ones_desc, a_lo = 0;
+            if (I.ext_kind == 1) { a_hi = smem_desc(smem_u32(ext_noise_hi), 2048, 128); a_lo = smem_desc(smem_u32(ext_noise_lo), 2048, 128); }
+            if (I.ext_kind == 2) { a_hi = smem_desc(smem_u32(ext_act_hi), 2048, 128); a_lo = smem_desc(smem_u32(ext_act_lo), 2048, 128); }
+            mma_ss(d, a_hi, bd, idesc, acc);
+            if (NP >= 2 && I.ext_kind != 3) mma_ss(d, a_lo, bd, idesc, 1);
+            if (NP == 3) mma_ss(d, a_hi, smem_desc(base + ext_off + slab, lbo, 128), idesc, 1);
+          }
+          mma_commit(bar_empty(slot));
+          if (I.signal_d) {
+            mma_commit(bar_dfull(ds));
+            ++ds;
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps 0..7 =====================================================
+    const int q = warp & 3, h = warp >> 2;
+    const int m = q * 32 + lane;                       // candidate row = TMEM lane
+    const int cand = m0 + m;
+    const bool valid = cand < p.K;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    uint32_t dw = 0, ae = 0;
+    auto wait_d = [&]() {
+      mbar_wait(bar_dfull(dw), (dw >> 1) & 1);
+      ++dw;
+      fence_after_sync();
+    };
+    auto signal_a = [&]() {
+      tmem_st_wait();
+      fence_proxy_async();
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_aready(ae));
+      ++ae;
+    };
+    auto load_noise = [&](int t, float (&x)[16]) {
+#pragma unroll
+      for (int k = 0; k < 16; ++k) x[k] = 0.f;
+      if (h == 0 && t < p.T) {
+        const float* src = p.noise + (((size_t)t * p.G + g) * p.K + cand) * p.nd;
+#pragma unroll
+        for (int k = 0; k < 15; ++k)
+          if (k < p.nd && valid) x[k] = __ldg(src + k);
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          if (k == p.nd) x[k] = 1.f;
+      }
+    };
+    // ---- init event: state <- e0, AS <- split(e0), noise ext of step 0
+    {
+      float s[64];
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + c);
+        S4[(h * 16 + c) * 128 + m] = v;
+        s[4 * c] = v.x; s[4 * c + 1] = v.y; s[4 * c + 2] = v.z; s[4 * c + 3] = v.w;
+      }
+      store_state_operand<NP>(lane_base + kColAS + 64 * h, s);
+      float nz[16];
+      load_noise(0, nz);
+      if (h == 0) store_ext_row(ext_noise_hi, ext_noise_lo, m, nz, p.nd >= 8);
+      signal_a();
+    }
+    float nz[16];
+    for (int t = 0; t < p.T; ++t) {
+      load_noise(t + 1, nz);                                      // prefetch next step's noise
+      // ---- G1 (N=128, R0), G2 (N=64, R1), G3 (N=128, R0): relu -> next A operand in place
+      wait_d(); relu_inplace64<NP>(lane_base + kColR0 + 64 * h); signal_a();
+      wait_d(); relu_inplace32<NP>(lane_base + kColR1 + 32 * h); signal_a();
+      wait_d(); relu_inplace64<NP>(lane_base + kColR0 + 64 * h); signal_a();
+      // ---- G4 (two N=128 halves in R1 and DR)
+      wait_d();
+      relu_inplace64<NP>(lane_base + kColR1 + 64 * h);
+      relu_inplace64<NP>(lane_base + kColDR + 64 * h);
+      signal_a();
+      // ---- G5 (N=16 in R0, 4 real columns): action -> ext slab; step-0 actions are the plan's a0
+      wait_d();
+      if (h == 0) {
+        uint32_t av[4];
+        tmem_ld4(lane_base + kColR0, av);
+        tmem_ld_wait();
+        float x[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) x[k] = 0.f;
+        x[0] = __uint_as_float(av[0]); x[1] = __uint_as_float(av[1]);
+        x[2] = __uint_as_float(av[2]); x[3] = __uint_as_float(av[3]);
+        x[4] = 1.f;
+        store_ext_row(ext_act_hi, ext_act_lo, m, x, false);
+        if (t == 0 && valid)   // mpc_eval.py:150-151
+          *reinterpret_cast<float4*>(p.a0 + ((size_t)g * p.K + cand) * 4) = make_float4(x[0], x[1], x[2], x[3]);
+      }
+      signal_a();
+      // ---- forward model hidden chunks: F1[c] accumulator (R0/R1 alternating) -> relu -> A of F2[c]
+      for (int c = 0; c < p.n_hid_chunks; ++c) {
+        wait_d();
+        relu_inplace64<NP>(lane_base + ((c & 1) ? kColR1 : kColR0) + 64 * h);
+        signal_a();
+      }
+      // ---- END: state += residual (fp32, exact add; forward_encoder.py:113-114), new A operand, next noise
+      wait_d();
+      {
+        uint32_t r0[32], r1[32];
+        tmem_ld32(lane_base + kColDR + 64 * h, r0);
+        tmem_ld32(lane_base + kColDR + 64 * h + 32, r1);
+        tmem_ld_wait();
+        float s[64];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          float4 v = S4[(h * 16 + c) * 128 + m];
+          const uint32_t* r = (c < 8) ? (r0 + 4 * c) : (r1 + 4 * (c - 8));
+          v.x += __uint_as_float(r[0]); v.y += __uint_as_float(r[1]);
+          v.z += __uint_as_float(r[2]); v.w += __uint_as_float(r[3]);
+          S4[(h * 16 + c) * 128 + m] = v;
+          s[4 * c] = v.x; s[4 * c + 1] = v.y; s[4 * c + 2] = v.z; s[4 * c + 3] = v.w;
+        }
+        if (t + 1 < p.T) {
+          store_state_operand<NP>(lane_base + kColAS + 64 * h, s);
+          if (h == 0) store_ext_row(ext_noise_hi, ext_noise_lo, m, nz, p.nd >= 8);
+          signal_a();
+        } else {
+          // terminal cost: mean over E of squared error (nn.MSELoss, mpc_eval.py:161)
+          float cs = 0.f;
+#pragma unroll
+          for (int c = 0; c < 64; ++c) {
+            const float df = s[c] - s_goal[64 * h + c];
+            cs = fmaf(df, df, cs);
+          }
+          if (h == 1) s_red[m] = cs;
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          if (h == 0 && valid) p.cost[(size_t)g * p.K + cand] = (cs + s_red[m]) * (1.0f / 128.0f);
+          if (p.state_T && valid) {
+            float4* o = reinterpret_cast<float4*>(p.state_T + ((size_t)g * p.K + cand) * 128) + h * 16;
+#pragma unroll
+            for (int c = 0; c < 16; ++c) o[c] = make_float4(s[4 * c], s[4 * c + 1], s[4 * c + 2], s[4 * c + 3]);
+          }
+        }
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 8) tmem_dealloc512(tmem);
+}
+
+// ------------------------------------------------------------------------------------------
+// host side: weight stream + item table of one precision mode
+// ------------------------------------------------------------------------------------------
+struct TcPlan {
+  int np, nd, H, n_items, n_chunks;
+  uint8_t* stream;        // device
+  size_t stream_bytes;
+  TcItem* items;          // device
+  const float* W1;        // device, torch layout (planner-owned copies)
+  const float* b1;
+  uint32_t gext_stride;   // bytes per goal
+};
+
+namespace {
+
+struct Builder {
+  int np;
+  cudaStream_t s;
+  uint8_t* stream;
+  size_t off = 0;
+  TcItem items[kTcMaxItems];
+  int n = 0;
+  int rc = NDP_OK;
+
+  // one item: `nslab` main slabs [j0, j0+nslab) of W rows [n0, n0+N) (rows >= nvalid are zero), optional ext slab
+  void add(const float* W, int ld, int n0, int nvalid, int kcol0, int N, int j0, int nslab, int d_col, int a_col,
+           int cph, bool first, bool wait_a, bool signal_d, int ext_kind, const ExtCols* ext) {
+    if (rc) return;
+    if (n >= kTcMaxItems) { set_error("tensor-core plan: too many stream items (H too large)"); rc = NDP_ERR_ARG; return; }
+    const size_t slab = (size_t)N * 32, main_hi = slab * nslab;
+    TcItem& I = items[n++];
+    memset(&I, 0, sizeof(I));
+    I.src_off = (uint32_t)off;
+    I.n_main = (uint16_t)nslab; I.j0 = (uint16_t)j0; I.N = (uint16_t)N; I.d_col = (uint16_t)d_col;
+    I.a_col = (uint16_t)a_col; I.cph = (uint16_t)cph; I.spc_shift = (cph == 64) ? 2 : 1;
+    I.ext_kind = (uint8_t)ext_kind; I.first = first; I.wait_a = wait_a; I.signal_d = signal_d;
+    __half* hi = reinterpret_cast<__half*>(stream + off);
+    __half* lo = (np == 3) ? reinterpret_cast<__half*>(stream + off + main_hi) : nullptr;
+    const int total = N * nslab * 16;
+    tc_pack_main_kernel<<<(total + 255) / 256, 256, 0, s>>>(hi, lo, W, ld, n0, kcol0 + j0 * 16, N, nslab, nvalid);
+    count_launch();
+    size_t bytes = main_hi * (np == 3 ? 2 : 1);
+    if (ext_kind == 1) {
+      I.ext_bytes = (uint32_t)(slab * (np == 3 ? 2 : 1));       // per-goal block, built per call
+    } else if (ext_kind) {
+      __half* ehi = reinterpret_cast<__half*>(stream + off + bytes);
+      __half* elo = (np == 3) ? reinterpret_cast<__half*>(stream + off + bytes + slab) : nullptr;
+      tc_pack_ext_kernel<<<(N * 16 + 255) / 256, 256, 0, s>>>(ehi, elo, N, nvalid, *ext);
+      count_launch();
+      bytes += slab * (np == 3 ? 2 : 1);
+    }
+    I.bytes = (uint32_t)bytes;
+    off += (bytes + 127) / 128 * 128;
+    if (cudaGetLastError() != cudaSuccess) { set_error("tensor-core plan: pack kernel launch failed"); rc = NDP_ERR_CUDA; }
+  }
+};
+
+ExtCols bias_only(const float* b) {
+  ExtCols c;
+  memset(&c, 0, sizeof(c));
+  c.p[0] = b; c.stride[0] = 1;
+  return c;
+}
+
+}  // namespace
+
+int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* const* Wt, const float* const* bt,
+                   cudaStream_t s) {
+  NDP_CHECK_ARG(E == 128 && nd <= 15 && H % 128 == 0 && H <= 2048,
+                "tensor-core rollout needs E=128, noise_dim<=15, H multiple of 128 and <=2048 (use precision fp32 otherwise)");
+  const int nch = H / 128;
+  TcPlan* P = new TcPlan();
+  memset(P, 0, sizeof(*P));
+  P->np = np; P->nd = nd; P->H = H; P->n_chunks = nch; P->W1 = Wt[0]; P->b1 = bt[0];
+  P->gext_stride = 128 * 32 * (np == 3 ? 2 : 1);
+  const size_t cap = (size_t)(np == 3 ? 2 : 1) * ((size_t)(128 * 144 + 64 * 144 + 128 * 80 + 256 * 144 + 16 * 272) * 2 +
+                                                 (size_t)nch * (128 * 144 + 128 * 144) * 2) + 128 * kTcMaxItems;
+  cudaError_t e = cudaMalloc(&P->stream, cap);
+  if (e == cudaSuccess) e = cudaMalloc(&P->items, sizeof(TcItem) * kTcMaxItems);
+  if (e != cudaSuccess) {
+    set_error("tensor-core plan: cudaMalloc failed: %s", cudaGetErrorString(e));
+    tc_plan_destroy(P);
+    return NDP_ERR_CUDA;
+  }
+  cudaMemsetAsync(P->stream, 0, cap, s);
+  Builder B;
+  B.np = np; B.s = s; B.stream = P->stream;
+  const int C1 = 2 * E + nd;
+  ExtCols x;
+  // generator fc1: state columns from TMEM (AS); ext = [noise cols | per-goal bias] built per call
+  B.add(Wt[0], C1, 0, 128, 0, 128, 0, 4, kColR0, kColAS, 64, true, true, false, 0, nullptr);
+  B.add(Wt[0], C1, 0, 128, 0, 128, 4, 4, kColR0, kColAS, 64, false, false, true, 1, nullptr);
+  // fc2 (N=64), fc3 (K=64)
+  x = bias_only(bt[1]);
+  B.add(Wt[1], 128, 0, 64, 0, 64, 0, 8, kColR1, kColR0, 64, true, true, true, 3, &x);
+  x = bias_only(bt[2]);
+  B.add(Wt[2], 64, 0, 128, 0, 128, 0, 4, kColR0, kColR1, 32, true, true, true, 3, &x);
+  // fc4 as two N=128 halves (R1, DR)
+  for (int hh = 0; hh < 2; ++hh) {
+    x = bias_only(bt[3] + hh * 128);
+    B.add(Wt[3], 128, hh * 128, 128, 0, 128, 0, 4, hh ? kColDR : kColR1, kColR0, 64, true, hh == 0, false, 0, nullptr);
+    B.add(Wt[3], 128, hh * 128, 128, 0, 128, 4, 4, hh ? kColDR : kColR1, kColR0, 64, false, false, hh == 1, 3, &x);
+  }
+  // fc5 padded to N=16 (4 real rows), K=256 spanning R1|DR
+  x = bias_only(bt[4]);
+  B.add(Wt[4], 256, 0, 4, 0, 16, 0, 16, kColR0, kColR1, 64, true, true, true, 3, &x);
+  // forward model: F1[c] = fc1 rows of hidden chunk c (ext = [action cols | bias]); F2[c] = fc2 columns of chunk c
+  auto F1 = [&](int c) {
+    ExtCols a;
+    memset(&a, 0, sizeof(a));
+    for (int k = 0; k < 4; ++k) { a.p[k] = Wt[5] + (size_t)c * 128 * (E + 4) + E + k; a.stride[k] = E + 4; }
+    a.p[4] = bt[5] + c * 128; a.stride[4] = 1;
+    const int dcol = (c & 1) ? kColR1 : kColR0;
+    B.add(Wt[5], E + 4, c * 128, 128, 0, 128, 0, 4, dcol, kColAS, 64, true, c == 0, false, 0, nullptr);
+    B.add(Wt[5], E + 4, c * 128, 128, 0, 128, 4, 4, dcol, kColAS, 64, false, false, true, 2, &a);
+  };
+  auto F2 = [&](int c) {
+    const int acol = (c & 1) ? kColR1 : kColR0;
+    const bool last = (c == nch - 1);
+    ExtCols b = bias_only(bt[6]);
+    B.add(Wt[6], H, 0, 128, c * 128, 128, 0, 4, kColDR, acol, 64, c == 0, true, false, 0, nullptr);
+    B.add(Wt[6], H, 0, 128, c * 128, 128, 4, 4, kColDR, acol, 64, false, false, last, last ? 3 : 0, last ? &b : nullptr);
+  };
+  F1(0);
+  for (int c = 1; c < nch; ++c) { F1(c); F2(c - 1); }
+  F2(nch - 1);
+  if (B.rc) { tc_plan_destroy(P); return B.rc; }
+  P->n_items = B.n;
+  P->stream_bytes = B.off;
+  e = cudaMemcpyAsync(P->items, B.items, sizeof(TcItem) * B.n, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);   // B.items is on this stack frame
+  if (e != cudaSuccess) {
+    set_error("tensor-core plan: upload failed: %s", cudaGetErrorString(e));
+    tc_plan_destroy(P);
+    return NDP_ERR_CUDA;
+  }
+  *out = P;
+  return NDP_OK;
+}
+
+void tc_plan_destroy(TcPlan* p) {
+  if (!p) return;
+  if (p->stream) cudaFree(p->stream);
+  if (p->items) cudaFree(p->items);
+  delete p;
+}
+
+size_t tc_workspace_bytes(const TcPlan* p, int G) { return (size_t)(G > 0 ? G : 1) * p->gext_stride + 256; }
+
+template <int NP>
+static int launch_np(const TcParams& tp, int grid, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    NDP_CUDA(cudaFuncSetAttribute(rollout_tc_kernel<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
+    attr_set = true;
+  }
+  rollout_tc_kernel<NP><<<grid, kTcThreads, kTcSmemBytes, s>>>(tp);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const float* noise, int G, int K, int T,
+                      float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s) {
+  const size_t need = (size_t)G * P->gext_stride;
+  if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
+  NDP_CHECK_ARG(((uintptr_t)ws & 15) == 0, "rollout_score: workspace must be 16-byte aligned");
+  tc_goal_ext_kernel<<<G, 256, 0, s>>>(P->W1, P->b1, goal, 128, P->nd, P->np == 3, reinterpret_cast<__half*>(ws),
+                                        P->gext_stride / 2);
+  NDP_LAUNCH_CHECK();
+  TcParams tp;
+  tp.stream = P->stream; tp.items = P->items; tp.gext = reinterpret_cast<const uint8_t*>(ws);
+  tp.gext_stride = P->gext_stride; tp.e0 = e0; tp.goal = goal; tp.noise = noise; tp.cost = cost; tp.a0 = a0;
+  tp.state_T = state_T; tp.G = G; tp.K = K; tp.T = T; tp.nd = P->nd; tp.n_items = P->n_items;
+  tp.tiles_per_goal = (K + 127) / 128; tp.n_hid_chunks = P->n_chunks;
+  const long long grid = (long long)G * tp.tiles_per_goal;
+  NDP_CHECK_ARG(grid <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
+  if (P->np == 1) return launch_np<1>(tp, (int)grid, s);
+  if (P->np == 2) return launch_np<2>(tp, (int)grid, s);
+  return launch_np<3>(tp, (int)grid, s);
+}
+
+}  // namespace ndp

@@ -28,6 +28,50 @@ struct RolloutParams {
 int launch_rollout_f32(const RolloutParams& p, cudaStream_t s);
 int rollout_f32_smem_bytes();
 
+// ---- tensor-core rollout (k1_rollout_tc.cu) --------------------------------------------------
+// One stream item = one weight block landing in one ring slot, consumed by n_main (+1 ext) K=16 slabs.
+struct TcItem {
+  uint32_t src_off;     // byte offset of the block in the packed weight stream
+  uint32_t bytes;       // bytes taken from the stream: main hi [+ main lo] [+ ext hi [+ ext lo]]
+  uint32_t ext_bytes;   // bytes taken from the per-goal buffer instead (generator fc1 ext slab), else 0
+  uint16_t n_main;      // main slabs (A operand in TMEM)
+  uint16_t j0;          // index of the first slab inside its GEMM
+  uint16_t N;           // GEMM width
+  uint16_t d_col;       // TMEM column of the accumulator
+  uint16_t a_col;       // TMEM column of the A operand region
+  uint16_t cph;         // D columns per epilogue half that produced A (64, or 32 after an N=64 layer)
+  uint8_t spc_shift;    // log2(slabs per half) = log2(cph/16)
+  uint8_t ext_kind;     // 0 none, 1 noise, 2 action, 3 ones
+  uint8_t first;        // first item of its GEMM: first MMA overwrites the accumulator
+  uint8_t wait_a;       // wait for the next "A ready" event before issuing
+  uint8_t signal_d;     // commit the next "D full" event after issuing
+  uint8_t pad[3];
+};
+static_assert(sizeof(TcItem) == 32, "TcItem must stay 32 bytes");
+static constexpr int kTcMaxItems = 96;
+
+struct TcParams {
+  const uint8_t* stream;    // packed fp16 weight stream of one step
+  const TcItem* items;      // [n_items] (device)
+  const uint8_t* gext;      // per-goal generator-fc1 ext blocks
+  uint32_t gext_stride;     // bytes per goal
+  const float* e0;
+  const float* goal;
+  const float* noise;
+  float* cost;
+  float* a0;
+  float* state_T;
+  int G, K, T, nd, n_items, tiles_per_goal, n_hid_chunks;
+};
+
+struct TcPlan;   // host-side: packed stream + item table of one precision mode
+int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* const* Wt, const float* const* bt,
+                   cudaStream_t s);
+void tc_plan_destroy(TcPlan* p);
+size_t tc_workspace_bytes(const TcPlan* p, int G);
+int launch_rollout_tc(const TcPlan* plan, const float* e0, const float* goal, const float* noise, int G, int K,
+                      int T, float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s);
+
 }  // namespace ndp
 
 struct ndp_planner {
@@ -44,4 +88,5 @@ struct ndp_planner {
   float* scratch;         // activations for the single-call APIs, grown on demand
   size_t scratch_floats;
   int nq;
+  ndp::TcPlan* tc;     // tensor-core plan (precision != fp32), else null
 };

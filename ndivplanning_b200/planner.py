@@ -76,7 +76,8 @@ class FusedPlanner:
             raise _lib.NdpError("CUDA is not available; FusedPlanner has no CPU fallback")
         self.device = torch.device(device)
         self.E, self.H, self.nd, self.T = E, H, nd, int(horizon)
-        prec = {"fp32": _lib.PREC_FP32, "f16x3": _lib.PREC_F16X3, "f16": _lib.PREC_F16}[precision]
+        prec = {"fp32": _lib.PREC_FP32, "f16x3": _lib.PREC_F16X3, "f16x2": _lib.PREC_F16X2,
+                "f16": _lib.PREC_F16}[precision]
         self.precision = precision
         self._h = C.c_void_p()
         desc = PlannerDesc(E, nd, 4, H, self.T, prec)
