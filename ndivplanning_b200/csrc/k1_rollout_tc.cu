@@ -184,6 +184,55 @@ __device__ __forceinline__ void store_ext_row(uint8_t* slab_hi, uint8_t* slab_lo
 }
 
 // ------------------------------------------------------------------------------------------
+// MMA issue of one stream item (one ring slot): NMAIN main slabs (A in TMEM) + optional ext slab
+// (A in smem).  Everything but the slot position is a compile-time constant so the issuing lane
+// spends ~10 instructions per MMA; the item ORDER here must match the host builder's item table.
+// ------------------------------------------------------------------------------------------
+struct IssueState {
+  uint32_t slot, par;        // ring position / parity of the "full" barriers
+  uint32_t bars;             // smem address of the barrier block
+  uint32_t ring16;           // ring base >> 4
+  uint32_t ext16[5];         // (ext slab address >> 4) | LBO bits: noise hi, noise lo, action hi, action lo, ones
+  uint32_t ds;               // "D full" events signalled so far
+};
+
+template <int NP, int N, int NMAIN, int EXT, bool SIGNAL_D>
+__device__ __forceinline__ void tc_issue(IssueState& st, uint32_t d, uint32_t a, uint32_t lo_delta, uint32_t first) {
+  constexpr uint32_t kSlot = RingCfg<NP>::slot, kNSlot = RingCfg<NP>::nslot;
+  constexpr uint32_t kDescHi = 0x4000u | (128u >> 4);          // descriptor version 1, SBO = 128 B
+  constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  constexpr uint32_t step = 2 * N;                              // one slab = N*32 bytes, in 16-byte units
+  constexpr uint32_t lo_w = NMAIN * step;                       // hi -> lo weight block distance (NP=3)
+  mbar_wait(st.bars + 8 * st.slot, st.par);
+  fence_after_sync();
+  if (elect_one()) {
+    uint32_t blo = (st.ring16 + st.slot * (kSlot >> 4)) | ((uint32_t)N << 16);   // LBO = N*16 bytes
+    uint32_t acc = first ? 0u : 1u;
+#pragma unroll
+    for (int s = 0; s < NMAIN; ++s) {
+      const uint64_t bd = pack64(blo + s * step, kDescHi);
+      mma_ts(d, a + 8 * s, bd, kIdesc, acc);
+      acc = 1;
+      if (NP >= 2) mma_ts(d, a + 8 * s + lo_delta, bd, kIdesc, 1);
+      if (NP == 3) mma_ts(d, a + 8 * s, pack64(blo + s * step + lo_w, kDescHi), kIdesc, 1);
+    }
+    if (EXT) {
+      const uint32_t eb = blo + ((NP == 3) ? 2 * lo_w : lo_w);  // ext block follows [main hi][main lo]
+      const uint64_t bd = pack64(eb, kDescHi);
+      const uint64_t ad = pack64(st.ext16[EXT == 1 ? 0 : (EXT == 2 ? 2 : 4)], kDescHi);
+      mma_ss(d, ad, bd, kIdesc, acc);
+      if (NP >= 2 && EXT != 3) mma_ss(d, pack64(st.ext16[EXT == 1 ? 1 : 3], kDescHi), bd, kIdesc, 1);
+      if (NP == 3) mma_ss(d, ad, pack64(eb + step, kDescHi), kIdesc, 1);
+    }
+    mma_commit(st.bars + 8 * (6 + st.slot));
+    if (SIGNAL_D) mma_commit(st.bars + 8 * (12 + (st.ds & 1)));
+  }
+  __syncwarp();
+  if (SIGNAL_D) ++st.ds;
+  if (++st.slot == kNSlot) { st.slot = 0; st.par ^= 1; }
+}
+
+// ------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------
 template <int NP>
@@ -251,51 +300,63 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
       }
     }
   } else if (warp == 8) {
-    // ===================== MMA issuer ============================================================
-    if (lane == 0) {
-      uint32_t it = 0, aw = 0, ds = 0;
-      const uint64_t ones_desc = smem_desc(smem_u32(ext_ones), 2048, 128);
-      for (int t = 0; t < p.T; ++t) {
-        for (int i = 0; i < p.n_items; ++i, ++it) {
-          const TcItem I = items[i];
-          const uint32_t slot = it % kNSlot, par = (it / kNSlot) & 1;
-          if (I.wait_a) {
-            mbar_wait(bar_aready(aw), (aw >> 1) & 1);
-            ++aw;
-          }
-          mbar_wait(bar_full(slot), par);
-          fence_after_sync();
-          const uint32_t base = smem_u32(smem + kOffRing + slot * kSlot);
-          const uint32_t N = I.N, slab = N * 32, lbo = N * 16;
-          const uint32_t idesc = idesc_f16((int)N);
-          const uint32_t main_hi = I.n_main * slab;
-          const uint32_t ext_off = (NP == 3) ? 2 * main_hi : main_hi;
-          const uint32_t d = tmem + I.d_col;
-          uint32_t acc = I.first ? 0u : 1u;
-          for (uint32_t s = 0; s < I.n_main; ++s) {
-            const uint32_t j = I.j0 + s;
-            const uint32_t a = tmem + I.a_col + (j >> I.spc_shift) * I.cph + (j & ((1u << I.spc_shift) - 1)) * 8;
-            const uint64_t bd = smem_desc(base + s * slab, lbo, 128);
-            mma_ts(d, a, bd, idesc, acc);
-            acc = 1;
-            if (NP >= 2) mma_ts(d, a + I.cph / 2, bd, idesc, 1);
-            if (NP == 3) mma_ts(d, a, smem_desc(base + main_hi + s * slab, lbo, 128), idesc, 1);
-          }
-          if (I.ext_kind) {
-            const uint64_t bd = smem_desc(base + ext_off, lbo, 128);
-            uint64_t a_hi = ones_desc, a_lo = 0;
-            if (I.ext_kind == 1) { a_hi = smem_desc(smem_u32(ext_noise_hi), 2048, 128); a_lo = smem_desc(smem_u32(ext_noise_lo), 2048, 128); }
-            if (I.ext_kind == 2) { a_hi = smem_desc(smem_u32(ext_act_hi), 2048, 128); a_lo = smem_desc(smem_u32(ext_act_lo), 2048, 128); }
-            mma_ss(d, a_hi, bd, idesc, acc);
-            if (NP >= 2 && I.ext_kind != 3) mma_ss(d, a_lo, bd, idesc, 1);
-            if (NP == 3) mma_ss(d, a_hi, smem_desc(base + ext_off + slab, lbo, 128), idesc, 1);
-          }
-          mma_commit(bar_empty(slot));
-          if (I.signal_d) {
-            mma_commit(bar_dfull(ds));
-            ++ds;
-          }
-        }
+    // ===================== MMA issuer (whole warp converged; one elected lane issues) ===========
+    IssueState st;
+    st.slot = 0; st.par = 0; st.bars = bars; st.ring16 = smem_u32(smem + kOffRing) >> 4; st.ds = 0;
+    const uint32_t ext_lbo = (2048u >> 4) << 16;               // A ext slabs: LBO = 2 KB, SBO = 128 B
+    st.ext16[0] = (smem_u32(ext_noise_hi) >> 4) | ext_lbo; st.ext16[1] = (smem_u32(ext_noise_lo) >> 4) | ext_lbo;
+    st.ext16[2] = (smem_u32(ext_act_hi) >> 4) | ext_lbo;   st.ext16[3] = (smem_u32(ext_act_lo) >> 4) | ext_lbo;
+    st.ext16[4] = (smem_u32(ext_ones) >> 4) | ext_lbo;
+    uint32_t aw = 0;
+    auto wait_a = [&]() {
+      mbar_wait(bar_aready(aw), (aw >> 1) & 1);
+      ++aw;
+      fence_after_sync();
+    };
+    const uint32_t R0 = tmem + kColR0, R1 = tmem + kColR1, DR = tmem + kColDR, AS = tmem + kColAS;
+    const int nch = p.n_hid_chunks;
+    for (int t = 0; t < p.T; ++t) {
+      // generator fc1 (A = state operand, ext = [noise | per-goal bias])
+      wait_a();
+      tc_issue<NP, 128, 4, 0, false>(st, R0, AS, 32, 1);
+      tc_issue<NP, 128, 4, 1, true>(st, R0, AS + 64, 32, 0);
+      // fc2 (N=64)
+      wait_a();
+      tc_issue<NP, 64, 4, 0, false>(st, R1, R0, 32, 1);
+      tc_issue<NP, 64, 4, 3, true>(st, R1, R0 + 64, 32, 0);
+      // fc3 (K=64: operand halves are 32 columns wide, hi 16 + lo 16)
+      wait_a();
+      tc_issue<NP, 128, 2, 0, false>(st, R0, R1, 16, 1);
+      tc_issue<NP, 128, 2, 3, true>(st, R0, R1 + 32, 16, 0);
+      // fc4 as two N=128 halves
+      wait_a();
+      tc_issue<NP, 128, 4, 0, false>(st, R1, R0, 32, 1);
+      tc_issue<NP, 128, 4, 3, false>(st, R1, R0 + 64, 32, 0);
+      tc_issue<NP, 128, 4, 0, false>(st, DR, R0, 32, 1);
+      tc_issue<NP, 128, 4, 3, true>(st, DR, R0 + 64, 32, 0);
+      // fc5 (N=16, K=256 over R1|DR)
+      wait_a();
+      tc_issue<NP, 16, 4, 0, false>(st, R0, R1, 32, 1);
+      tc_issue<NP, 16, 4, 0, false>(st, R0, R1 + 64, 32, 0);
+      tc_issue<NP, 16, 4, 0, false>(st, R0, DR, 32, 0);
+      tc_issue<NP, 16, 4, 3, true>(st, R0, DR + 64, 32, 0);
+      // forward model: F1[0], then F1[c] / F2[c-1] interleaved, then F2[last]
+      wait_a();
+      tc_issue<NP, 128, 4, 0, false>(st, R0, AS, 32, 1);
+      tc_issue<NP, 128, 4, 2, true>(st, R0, AS + 64, 32, 0);
+      for (int c = 1; c < nch; ++c) {
+        const uint32_t Rc = (c & 1) ? R1 : R0, Rp = (c & 1) ? R0 : R1;
+        tc_issue<NP, 128, 4, 0, false>(st, Rc, AS, 32, 1);
+        tc_issue<NP, 128, 4, 2, true>(st, Rc, AS + 64, 32, 0);
+        wait_a();
+        tc_issue<NP, 128, 4, 0, false>(st, DR, Rp, 32, c == 1);
+        tc_issue<NP, 128, 4, 0, false>(st, DR, Rp + 64, 32, 0);
+      }
+      {
+        const uint32_t Rp = ((nch - 1) & 1) ? R1 : R0;
+        wait_a();
+        tc_issue<NP, 128, 4, 0, false>(st, DR, Rp, 32, nch == 1);
+        tc_issue<NP, 128, 4, 3, true>(st, DR, Rp + 64, 32, 0);
       }
     }
   } else {
@@ -452,18 +513,23 @@ struct Builder {
   int n = 0;
   int rc = NDP_OK;
 
-  // one item: `nslab` main slabs [j0, j0+nslab) of W rows [n0, n0+N) (rows >= nvalid are zero), optional ext slab
-  void add(const float* W, int ld, int n0, int nvalid, int kcol0, int N, int j0, int nslab, int d_col, int a_col,
+  // one item: `nslab` main slabs [j0, j0+nslab) of W rows [n0, n0+N) (rows >= nvalid are zero), optional ext slab.
+  // `a_reg`/`cph`: TMEM region of the A operand and the D columns per epilogue half that produced it.
+  void add(const float* W, int ld, int n0, int nvalid, int kcol0, int N, int j0, int nslab, int d_col, int a_reg,
            int cph, bool first, bool wait_a, bool signal_d, int ext_kind, const ExtCols* ext) {
     if (rc) return;
     if (n >= kTcMaxItems) { set_error("tensor-core plan: too many stream items (H too large)"); rc = NDP_ERR_ARG; return; }
+    const int spc = cph / 16;                                   // slabs per epilogue half
+    if (j0 / spc != (j0 + nslab - 1) / spc) { set_error("tensor-core plan: item straddles an operand half"); rc = NDP_ERR_ARG; return; }
     const size_t slab = (size_t)N * 32, main_hi = slab * nslab;
     TcItem& I = items[n++];
     memset(&I, 0, sizeof(I));
     I.src_off = (uint32_t)off;
-    I.n_main = (uint16_t)nslab; I.j0 = (uint16_t)j0; I.N = (uint16_t)N; I.d_col = (uint16_t)d_col;
-    I.a_col = (uint16_t)a_col; I.cph = (uint16_t)cph; I.spc_shift = (cph == 64) ? 2 : 1;
-    I.ext_kind = (uint8_t)ext_kind; I.first = first; I.wait_a = wait_a; I.signal_d = signal_d;
+    I.idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    I.N = (uint16_t)N; I.d_col = (uint16_t)d_col;
+    I.a_col = (uint16_t)(a_reg + (j0 / spc) * cph + (j0 % spc) * 8);
+    I.lo_delta = (uint16_t)(cph / 2);
+    I.n_main = (uint8_t)nslab; I.ext_kind = (uint8_t)ext_kind; I.first = first; I.wait_a = wait_a; I.signal_d = signal_d;
     __half* hi = reinterpret_cast<__half*>(stream + off);
     __half* lo = (np == 3) ? reinterpret_cast<__half*>(stream + off + main_hi) : nullptr;
     const int total = N * nslab * 16;
@@ -522,9 +588,11 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
   B.add(Wt[0], C1, 0, 128, 0, 128, 4, 4, kColR0, kColAS, 64, false, false, true, 1, nullptr);
   // fc2 (N=64), fc3 (K=64)
   x = bias_only(bt[1]);
-  B.add(Wt[1], 128, 0, 64, 0, 64, 0, 8, kColR1, kColR0, 64, true, true, true, 3, &x);
+  B.add(Wt[1], 128, 0, 64, 0, 64, 0, 4, kColR1, kColR0, 64, true, true, false, 0, nullptr);
+  B.add(Wt[1], 128, 0, 64, 0, 64, 4, 4, kColR1, kColR0, 64, false, false, true, 3, &x);
   x = bias_only(bt[2]);
-  B.add(Wt[2], 64, 0, 128, 0, 128, 0, 4, kColR0, kColR1, 32, true, true, true, 3, &x);
+  B.add(Wt[2], 64, 0, 128, 0, 128, 0, 2, kColR0, kColR1, 32, true, true, false, 0, nullptr);
+  B.add(Wt[2], 64, 0, 128, 0, 128, 2, 2, kColR0, kColR1, 32, false, false, true, 3, &x);
   // fc4 as two N=128 halves (R1, DR)
   for (int hh = 0; hh < 2; ++hh) {
     x = bias_only(bt[3] + hh * 128);
@@ -533,7 +601,9 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
   }
   // fc5 padded to N=16 (4 real rows), K=256 spanning R1|DR
   x = bias_only(bt[4]);
-  B.add(Wt[4], 256, 0, 4, 0, 16, 0, 16, kColR0, kColR1, 64, true, true, true, 3, &x);
+  for (int q4 = 0; q4 < 4; ++q4)
+    B.add(Wt[4], 256, 0, 4, 0, 16, q4 * 4, 4, kColR0, kColR1, 64, q4 == 0, q4 == 0, q4 == 3, q4 == 3 ? 3 : 0,
+          q4 == 3 ? &x : nullptr);
   // forward model: F1[c] = fc1 rows of hidden chunk c (ext = [action cols | bias]); F2[c] = fc2 columns of chunk c
   auto F1 = [&](int c) {
     ExtCols a;

@@ -34,13 +34,12 @@ struct TcItem {
   uint32_t src_off;     // byte offset of the block in the packed weight stream
   uint32_t bytes;       // bytes taken from the stream: main hi [+ main lo] [+ ext hi [+ ext lo]]
   uint32_t ext_bytes;   // bytes taken from the per-goal buffer instead (generator fc1 ext slab), else 0
-  uint16_t n_main;      // main slabs (A operand in TMEM)
-  uint16_t j0;          // index of the first slab inside its GEMM
+  uint32_t idesc;       // tcgen05 instruction descriptor (kind::f16, M=128, N)
   uint16_t N;           // GEMM width
   uint16_t d_col;       // TMEM column of the accumulator
-  uint16_t a_col;       // TMEM column of the A operand region
-  uint16_t cph;         // D columns per epilogue half that produced A (64, or 32 after an N=64 layer)
-  uint8_t spc_shift;    // log2(slabs per half) = log2(cph/16)
+  uint16_t a_col;       // TMEM column of the first main slab's hi operand (slabs are 8 columns apart)
+  uint16_t lo_delta;    // column offset from a hi slab to its lo slab
+  uint8_t n_main;       // main slabs (A operand in TMEM); never straddles an epilogue half
   uint8_t ext_kind;     // 0 none, 1 noise, 2 action, 3 ones
   uint8_t first;        // first item of its GEMM: first MMA overwrites the accumulator
   uint8_t wait_a;       // wait for the next "A ready" event before issuing
