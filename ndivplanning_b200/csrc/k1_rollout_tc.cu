@@ -188,22 +188,46 @@ __device__ __forceinline__ void store_ext_row(uint8_t* slab_hi, uint8_t* slab_lo
 // (A in smem).  Everything but the slot position is a compile-time constant so the issuing lane
 // spends ~10 instructions per MMA; the item ORDER here must match the host builder's item table.
 // ------------------------------------------------------------------------------------------
+#ifdef NDP_TC_PROF
+__device__ unsigned long long g_tc_prof[8];
+__device__ unsigned long long g_tc_item_wait[64], g_tc_a_wait[16];   // [0] wait_a [1] wait_full [2] issue [3] total (MMA warp); [4] epi wait_d [5] epi work [6] epi total
+#define PROF_T0(v) long long v = clock64()
+#define PROF_ADD(slot, v) do { long long n__ = clock64(); st_prof[slot] += n__ - v; v = n__; } while (0)
+#else
+#define PROF_T0(v)
+#define PROF_ADD(slot, v)
+#endif
+
 struct IssueState {
   uint32_t slot, par;        // ring position / parity of the "full" barriers
   uint32_t bars;             // smem address of the barrier block
   uint32_t ring16;           // ring base >> 4
   uint32_t ext16[5];         // (ext slab address >> 4) | LBO bits: noise hi, noise lo, action hi, action lo, ones
   uint32_t ds;               // "D full" events signalled so far
+  uint32_t next_ready;       // result of the early try_wait on the current slot (issued one item ahead)
+#ifdef NDP_TC_PROF
+  long long prof[4];
+  int item, aev;
+#endif
 };
 
-template <int NP, int N, int NMAIN, int EXT, bool SIGNAL_D>
+template <int NP, int N, int NMAIN, int EXT, bool SIGNAL_D, int SPC = 4, int CPH = 64>
 __device__ __forceinline__ void tc_issue(IssueState& st, uint32_t d, uint32_t a, uint32_t lo_delta, uint32_t first) {
   constexpr uint32_t kSlot = RingCfg<NP>::slot, kNSlot = RingCfg<NP>::nslot;
   constexpr uint32_t kDescHi = 0x4000u | (128u >> 4);          // descriptor version 1, SBO = 128 B
   constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   constexpr uint32_t step = 2 * N;                              // one slab = N*32 bytes, in 16-byte units
   constexpr uint32_t lo_w = NMAIN * step;                       // hi -> lo weight block distance (NP=3)
-  mbar_wait(st.bars + 8 * st.slot, st.par);
+#ifdef NDP_TC_PROF
+  long long* st_prof = st.prof;
+#endif
+  PROF_T0(tp);
+  if (!st.next_ready) mbar_wait(st.bars + 8 * st.slot, st.par);
+#ifdef NDP_TC_PROF
+  if ((threadIdx.x & 31) == 0) atomicAdd(&g_tc_item_wait[st.item & 63], (unsigned long long)(clock64() - tp));
+  ++st.item;
+#endif
+  PROF_ADD(1, tp);
   fence_after_sync();
   if (elect_one()) {
     uint32_t blo = (st.ring16 + st.slot * (kSlot >> 4)) | ((uint32_t)N << 16);   // LBO = N*16 bytes
@@ -211,10 +235,11 @@ __device__ __forceinline__ void tc_issue(IssueState& st, uint32_t d, uint32_t a,
 #pragma unroll
     for (int s = 0; s < NMAIN; ++s) {
       const uint64_t bd = pack64(blo + s * step, kDescHi);
-      mma_ts(d, a + 8 * s, bd, kIdesc, acc);
+      const uint32_t as = a + (s / SPC) * CPH + (s % SPC) * 8;   // operand halves are CPH columns apart
+      mma_ts(d, as, bd, kIdesc, acc);
       acc = 1;
-      if (NP >= 2) mma_ts(d, a + 8 * s + lo_delta, bd, kIdesc, 1);
-      if (NP == 3) mma_ts(d, a + 8 * s, pack64(blo + s * step + lo_w, kDescHi), kIdesc, 1);
+      if (NP >= 2) mma_ts(d, as + lo_delta, bd, kIdesc, 1);
+      if (NP == 3) mma_ts(d, as, pack64(blo + s * step + lo_w, kDescHi), kIdesc, 1);
     }
     if (EXT) {
       const uint32_t eb = blo + ((NP == 3) ? 2 * lo_w : lo_w);  // ext block follows [main hi][main lo]
@@ -230,6 +255,9 @@ __device__ __forceinline__ void tc_issue(IssueState& st, uint32_t d, uint32_t a,
   __syncwarp();
   if (SIGNAL_D) ++st.ds;
   if (++st.slot == kNSlot) { st.slot = 0; st.par ^= 1; }
+  // probe the next slot now: the ~70-cycle try_wait latency overlaps the bookkeeping / next wait_a
+  st.next_ready = mbar_try_wait(st.bars + 8 * st.slot, st.par) ? 1u : 0u;
+  PROF_ADD(2, tp);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -302,44 +330,53 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
   } else if (warp == 8) {
     // ===================== MMA issuer (whole warp converged; one elected lane issues) ===========
     IssueState st;
-    st.slot = 0; st.par = 0; st.bars = bars; st.ring16 = smem_u32(smem + kOffRing) >> 4; st.ds = 0;
+    st.slot = 0; st.par = 0; st.next_ready = 0; st.bars = bars; st.ring16 = smem_u32(smem + kOffRing) >> 4; st.ds = 0;
     const uint32_t ext_lbo = (2048u >> 4) << 16;               // A ext slabs: LBO = 2 KB, SBO = 128 B
     st.ext16[0] = (smem_u32(ext_noise_hi) >> 4) | ext_lbo; st.ext16[1] = (smem_u32(ext_noise_lo) >> 4) | ext_lbo;
     st.ext16[2] = (smem_u32(ext_act_hi) >> 4) | ext_lbo;   st.ext16[3] = (smem_u32(ext_act_lo) >> 4) | ext_lbo;
     st.ext16[4] = (smem_u32(ext_ones) >> 4) | ext_lbo;
     uint32_t aw = 0;
+#ifdef NDP_TC_PROF
+    st.prof[0] = st.prof[1] = st.prof[2] = st.prof[3] = 0;
+    long long* st_prof = st.prof;
+    const long long t_begin = clock64();
+#endif
     auto wait_a = [&]() {
+      PROF_T0(tw);
       mbar_wait(bar_aready(aw), (aw >> 1) & 1);
       ++aw;
       fence_after_sync();
+#ifdef NDP_TC_PROF
+      if (lane == 0) atomicAdd(&g_tc_a_wait[st.aev & 15], (unsigned long long)(clock64() - tw));
+      ++st.aev;
+#endif
+      PROF_ADD(0, tw);
     };
     const uint32_t R0 = tmem + kColR0, R1 = tmem + kColR1, DR = tmem + kColDR, AS = tmem + kColAS;
     const int nch = p.n_hid_chunks;
     for (int t = 0; t < p.T; ++t) {
+#ifdef NDP_TC_PROF
+      st.item = 0; st.aev = 0;
+#endif
       // generator fc1 (A = state operand, ext = [noise | per-goal bias])
       wait_a();
       tc_issue<NP, 128, 4, 0, false>(st, R0, AS, 32, 1);
       tc_issue<NP, 128, 4, 1, true>(st, R0, AS + 64, 32, 0);
       // fc2 (N=64)
       wait_a();
-      tc_issue<NP, 64, 4, 0, false>(st, R1, R0, 32, 1);
-      tc_issue<NP, 64, 4, 3, true>(st, R1, R0 + 64, 32, 0);
+      tc_issue<NP, 64, 8, 3, true>(st, R1, R0, 32, 1);
       // fc3 (K=64: operand halves are 32 columns wide, hi 16 + lo 16)
       wait_a();
-      tc_issue<NP, 128, 2, 0, false>(st, R0, R1, 16, 1);
-      tc_issue<NP, 128, 2, 3, true>(st, R0, R1 + 32, 16, 0);
+      tc_issue<NP, 128, 4, 3, true, 2, 32>(st, R0, R1, 16, 1);
       // fc4 as two N=128 halves
       wait_a();
       tc_issue<NP, 128, 4, 0, false>(st, R1, R0, 32, 1);
-      tc_issue<NP, 128, 4, 3, false>(st, R1, R0 + 64, 32, 0);
+      tc_issue<NP, 128, 4, 3, true>(st, R1, R0 + 64, 32, 0);
       tc_issue<NP, 128, 4, 0, false>(st, DR, R0, 32, 1);
       tc_issue<NP, 128, 4, 3, true>(st, DR, R0 + 64, 32, 0);
       // fc5 (N=16, K=256 over R1|DR)
       wait_a();
-      tc_issue<NP, 16, 4, 0, false>(st, R0, R1, 32, 1);
-      tc_issue<NP, 16, 4, 0, false>(st, R0, R1 + 64, 32, 0);
-      tc_issue<NP, 16, 4, 0, false>(st, R0, DR, 32, 0);
-      tc_issue<NP, 16, 4, 3, true>(st, R0, DR + 64, 32, 0);
+      tc_issue<NP, 16, 16, 3, true>(st, R0, R1, 32, 1);
       // forward model: F1[0], then F1[c] / F2[c-1] interleaved, then F2[last]
       wait_a();
       tc_issue<NP, 128, 4, 0, false>(st, R0, AS, 32, 1);
@@ -359,6 +396,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
         tc_issue<NP, 128, 4, 3, true>(st, DR, Rp + 64, 32, 0);
       }
     }
+#ifdef NDP_TC_PROF
+    if (lane == 0) {
+      atomicAdd(&g_tc_prof[0], (unsigned long long)st.prof[0]);
+      atomicAdd(&g_tc_prof[1], (unsigned long long)st.prof[1]);
+      atomicAdd(&g_tc_prof[2], (unsigned long long)st.prof[2]);
+      atomicAdd(&g_tc_prof[3], (unsigned long long)(clock64() - t_begin));
+    }
+#endif
   } else {
     // ===================== epilogue warps 0..7 =====================================================
     const int q = warp & 3, h = warp >> 2;
@@ -367,14 +412,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
     const bool valid = cand < p.K;
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
     uint32_t dw = 0, ae = 0;
+#ifdef NDP_TC_PROF
+    long long st_prof[4] = {0, 0, 0, 0};
+    const long long t_begin = clock64();
+#endif
     auto wait_d = [&]() {
+      PROF_T0(tw);
       mbar_wait(bar_dfull(dw), (dw >> 1) & 1);
       ++dw;
       fence_after_sync();
+      PROF_ADD(0, tw);
     };
-    auto signal_a = [&]() {
+    auto signal_a = [&](bool wrote_smem = false) {
       tmem_st_wait();
-      fence_proxy_async();
+      if (wrote_smem) fence_proxy_async();
       fence_before_sync();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_aready(ae));
@@ -406,7 +457,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
       float nz[16];
       load_noise(0, nz);
       if (h == 0) store_ext_row(ext_noise_hi, ext_noise_lo, m, nz, p.nd >= 8);
-      signal_a();
+      signal_a(true);
     }
     float nz[16];
     for (int t = 0; t < p.T; ++t) {
@@ -418,6 +469,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
       // ---- G4 (two N=128 halves in R1 and DR)
       wait_d();
       relu_inplace64<NP>(lane_base + kColR1 + 64 * h);
+      wait_d();
       relu_inplace64<NP>(lane_base + kColDR + 64 * h);
       signal_a();
       // ---- G5 (N=16 in R0, 4 real columns): action -> ext slab; step-0 actions are the plan's a0
@@ -436,7 +488,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
         if (t == 0 && valid)   // mpc_eval.py:150-151
           *reinterpret_cast<float4*>(p.a0 + ((size_t)g * p.K + cand) * 4) = make_float4(x[0], x[1], x[2], x[3]);
       }
-      signal_a();
+      signal_a(true);
       // ---- forward model hidden chunks: F1[c] accumulator (R0/R1 alternating) -> relu -> A of F2[c]
       for (int c = 0; c < p.n_hid_chunks; ++c) {
         wait_d();
@@ -444,6 +496,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
         signal_a();
       }
       // ---- END: state += residual (fp32, exact add; forward_encoder.py:113-114), new A operand, next noise
+      float4 sv[16];
+#pragma unroll
+      for (int c = 0; c < 16; ++c) sv[c] = S4[(h * 16 + c) * 128 + m];     // state loads overlap the wait
       wait_d();
       {
         uint32_t r0[32], r1[32];
@@ -453,17 +508,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
         float s[64];
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
-          float4 v = S4[(h * 16 + c) * 128 + m];
+          float4 v = sv[c];
           const uint32_t* r = (c < 8) ? (r0 + 4 * c) : (r1 + 4 * (c - 8));
           v.x += __uint_as_float(r[0]); v.y += __uint_as_float(r[1]);
           v.z += __uint_as_float(r[2]); v.w += __uint_as_float(r[3]);
-          S4[(h * 16 + c) * 128 + m] = v;
           s[4 * c] = v.x; s[4 * c + 1] = v.y; s[4 * c + 2] = v.z; s[4 * c + 3] = v.w;
         }
         if (t + 1 < p.T) {
           store_state_operand<NP>(lane_base + kColAS + 64 * h, s);
           if (h == 0) store_ext_row(ext_noise_hi, ext_noise_lo, m, nz, p.nd >= 8);
-          signal_a();
+          signal_a(true);
+          // the fp32 state goes back to shared memory off the critical path (only this thread reads it)
+#pragma unroll
+          for (int c = 0; c < 16; ++c)
+            S4[(h * 16 + c) * 128 + m] = make_float4(s[4 * c], s[4 * c + 1], s[4 * c + 2], s[4 * c + 3]);
         } else {
           // terminal cost: mean over E of squared error (nn.MSELoss, mpc_eval.py:161)
           float cs = 0.f;
@@ -483,7 +541,16 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
         }
       }
     }
+  #ifdef NDP_TC_PROF
+    if (warp == 0 && lane == 0) {
+      atomicAdd(&g_tc_prof[4], (unsigned long long)st_prof[0]);
+      atomicAdd(&g_tc_prof[6], (unsigned long long)(clock64() - t_begin));
+    }
+#endif
   }
+#ifdef NDP_TC_PROF
+  // (epilogue counters are accumulated by warp 0 lane 0 only: representative)
+#endif
   fence_before_sync();
   __syncthreads();
   if (warp == 8) tmem_dealloc512(tmem);
@@ -520,7 +587,6 @@ struct Builder {
     if (rc) return;
     if (n >= kTcMaxItems) { set_error("tensor-core plan: too many stream items (H too large)"); rc = NDP_ERR_ARG; return; }
     const int spc = cph / 16;                                   // slabs per epilogue half
-    if (j0 / spc != (j0 + nslab - 1) / spc) { set_error("tensor-core plan: item straddles an operand half"); rc = NDP_ERR_ARG; return; }
     const size_t slab = (size_t)N * 32, main_hi = slab * nslab;
     TcItem& I = items[n++];
     memset(&I, 0, sizeof(I));
@@ -588,22 +654,18 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
   B.add(Wt[0], C1, 0, 128, 0, 128, 4, 4, kColR0, kColAS, 64, false, false, true, 1, nullptr);
   // fc2 (N=64), fc3 (K=64)
   x = bias_only(bt[1]);
-  B.add(Wt[1], 128, 0, 64, 0, 64, 0, 4, kColR1, kColR0, 64, true, true, false, 0, nullptr);
-  B.add(Wt[1], 128, 0, 64, 0, 64, 4, 4, kColR1, kColR0, 64, false, false, true, 3, &x);
+  B.add(Wt[1], 128, 0, 64, 0, 64, 0, 8, kColR1, kColR0, 64, true, true, true, 3, &x);
   x = bias_only(bt[2]);
-  B.add(Wt[2], 64, 0, 128, 0, 128, 0, 2, kColR0, kColR1, 32, true, true, false, 0, nullptr);
-  B.add(Wt[2], 64, 0, 128, 0, 128, 2, 2, kColR0, kColR1, 32, false, false, true, 3, &x);
+  B.add(Wt[2], 64, 0, 128, 0, 128, 0, 4, kColR0, kColR1, 32, true, true, true, 3, &x);
   // fc4 as two N=128 halves (R1, DR)
   for (int hh = 0; hh < 2; ++hh) {
     x = bias_only(bt[3] + hh * 128);
     B.add(Wt[3], 128, hh * 128, 128, 0, 128, 0, 4, hh ? kColDR : kColR1, kColR0, 64, true, hh == 0, false, 0, nullptr);
-    B.add(Wt[3], 128, hh * 128, 128, 0, 128, 4, 4, hh ? kColDR : kColR1, kColR0, 64, false, false, hh == 1, 3, &x);
+    B.add(Wt[3], 128, hh * 128, 128, 0, 128, 4, 4, hh ? kColDR : kColR1, kColR0, 64, false, false, true, 3, &x);
   }
   // fc5 padded to N=16 (4 real rows), K=256 spanning R1|DR
   x = bias_only(bt[4]);
-  for (int q4 = 0; q4 < 4; ++q4)
-    B.add(Wt[4], 256, 0, 4, 0, 16, q4 * 4, 4, kColR0, kColR1, 64, q4 == 0, q4 == 0, q4 == 3, q4 == 3 ? 3 : 0,
-          q4 == 3 ? &x : nullptr);
+  B.add(Wt[4], 256, 0, 4, 0, 16, 0, 16, kColR0, kColR1, 64, true, true, true, 3, &x);
   // forward model: F1[c] = fc1 rows of hidden chunk c (ext = [action cols | bias]); F2[c] = fc2 columns of chunk c
   auto F1 = [&](int c) {
     ExtCols a;
@@ -644,6 +706,20 @@ void tc_plan_destroy(TcPlan* p) {
   if (p->items) cudaFree(p->items);
   delete p;
 }
+
+#ifdef NDP_TC_PROF
+extern "C" int ndp_debug_tc_prof(unsigned long long* out8, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out8, g_tc_prof, sizeof(unsigned long long) * 8);
+  cudaMemcpyFromSymbol(out8 + 8, g_tc_item_wait, sizeof(unsigned long long) * 64);
+  cudaMemcpyFromSymbol(out8 + 72, g_tc_a_wait, sizeof(unsigned long long) * 16);
+  if (reset) {
+    unsigned long long z[64] = {0};
+    cudaMemcpyToSymbol(g_tc_prof, z, 64); cudaMemcpyToSymbol(g_tc_item_wait, z, 512); cudaMemcpyToSymbol(g_tc_a_wait, z, 128);
+  }
+  return 0;
+}
+#endif
 
 size_t tc_workspace_bytes(const TcPlan* p, int G) { return (size_t)(G > 0 ? G : 1) * p->gext_stride + 256; }
 

@@ -155,3 +155,38 @@ def test_full_size_properties(cuda):
     np.testing.assert_allclose(cost[sl].cpu().numpy(), ref["cost"].numpy(), rtol=COST_RTOL)
     full64 = None  # whole-K fp64 oracle is too slow for CI; the winner must beat the slice optimum
     assert float(cost.min()) <= float(ref["cost"].min()) * (1 + 1e-4)
+
+
+# ---- tensor-core modes of K1 (tcgen05): bulk cost accuracy per mode, measured against the fp64 oracle.
+# f16x3 (split activations and weights) must meet the north_star cost tolerance; f16 / f16x2 are
+# bulk-estimate modes whose selection is made exact by the fp32 refine pass (test_refined_plan_*).
+TC_COST_RTOL = {"f16x3": 1e-4, "f16x2": 6e-4, "f16": 1.2e-3}
+
+
+@pytest.mark.parametrize("mode", ["f16x3", "f16x2", "f16"])
+@pytest.mark.parametrize("G,K,T,H,nd", [(1, 128, 2, 128, 2), (2, 300, 4, 256, 2), (1, 1024, 8, 1024, 2),
+                                        (3, 130, 3, 384, 5), (1, 257, 5, 2048, 15)])
+def test_tensor_rollout_matches_oracle(cuda, mode, G, K, T, H, nd):
+    from ndivplanning_b200 import FusedPlanner
+    E = 128
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
+    e0, goal, noise = synthetic.make_plan_inputs(G, K, T, nd, E, seed=K + T)
+    pl = FusedPlanner(gen_p, fwd_p, horizon=T, precision=mode)
+    cost, a0, sT = pl.rollout_score(e0.cuda(), goal.cuda(), noise.cuda(), want_state=True)
+    g64, f64 = _oracle_models(gen_p, fwd_p, nd, E, H, double=True)
+    rtol = TC_COST_RTOL[mode]
+    for g in range(G):
+        ref64 = O.mpc_plan(g64, f64, e0[g].double(), goal[g].double(), noise[:, g].double())
+        np.testing.assert_allclose(cost[g].cpu().numpy(), ref64["cost"].numpy(), rtol=rtol)
+        scale = float(ref64["a0"].abs().max())
+        np.testing.assert_allclose(a0[g].cpu().numpy(), ref64["a0"].numpy(), rtol=0, atol=30 * rtol * scale)
+        sscale = float(ref64["state_T"].abs().max())
+        np.testing.assert_allclose(sT[g].cpu().numpy(), ref64["state_T"].numpy(), rtol=0, atol=20 * rtol * sscale)
+
+
+def test_tensor_mode_rejects_unsupported_shapes(cuda):
+    from ndivplanning_b200 import FusedPlanner, NdpError
+    gen_p, fwd_p = synthetic.make_models(nd=16, E=128, H=128, seed=0)
+    with pytest.raises(NdpError):
+        FusedPlanner(gen_p, fwd_p, horizon=2, precision="f16x3")     # noise_dim > 15: fp32 mode only
+    FusedPlanner(gen_p, fwd_p, horizon=2, precision="fp32")
