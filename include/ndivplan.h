@@ -39,7 +39,9 @@ enum {
   NDP_PREC_FP32 = 0,     /* CUDA-core FFMA, fp32 everywhere: parity mode            */
   NDP_PREC_F16X3 = 1,    /* tcgen05 kind::f16, 3-term hi/lo split operands, fp32 acc */
   NDP_PREC_F16 = 2,      /* tcgen05 kind::f16 single pass: bulk estimate (cost ~2e-4 rel) */
-  NDP_PREC_F16X2 = 3     /* tcgen05 kind::f16, activations split hi/lo, weights fp16: cost ~5e-5 rel */
+  NDP_PREC_F16X2 = 3,    /* tcgen05 kind::f16, activations split hi/lo, weights fp16: cost ~1.5e-4 rel */
+  NDP_PREC_F16_REFINE = 4 /* ndp_plan_select only: F16 bulk estimate of all K, then the 128 best estimates are
+                             re-rolled in F16X3 and the plan is selected from those fp32-grade costs */
 };
 
 typedef struct ndp_planner ndp_planner;
@@ -104,6 +106,20 @@ int ndp_select_workspace_bytes(int G, int K, int topk, size_t* bytes);
 int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
                uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
                void* ws, size_t ws_bytes, void* stream);
+/* ---- one-call plan: rollout + selection (mpc_eval.py:124-165 minus the action gather) --------------
+ * = ndp_rollout_score followed by ndp_select for every precision; with NDP_PREC_F16_REFINE the bulk
+ * costs are single-pass estimates, the NDP_REFINE_R best estimates per goal are re-rolled with split
+ * operands (their cost / a0 entries are overwritten with the refined values) and the selection is taken
+ * from the refined costs.  verified[g] (nullable) = 1 when no candidate outside the refine list can
+ * belong to the top-k given |estimate - refined| <= eps * cost (eps <= 0: default 1e-3); always 1 for the
+ * non-refined precisions.  topk <= 64 in refine mode. */
+#define NDP_REFINE_R 128
+int ndp_plan_workspace_bytes(const ndp_planner* p, int G, int K, int topk, size_t* bytes);
+int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
+                    int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
+                    int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
+                    void* stream);
+
 /* best_action[g,:] = a0[g, idx(packed_min[g]) - idx_base, :]   (mpc_eval.py:165) */
 int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,
                            int64_t idx_base, float* best_action, int32_t* best_idx,

@@ -8,7 +8,8 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libndivplan.so")
 
-PREC_FP32, PREC_F16X3, PREC_F16, PREC_F16X2 = 0, 1, 2, 3
+PREC_FP32, PREC_F16X3, PREC_F16, PREC_F16X2, PREC_F16_REFINE = 0, 1, 2, 3, 4
+REFINE_R = 128
 
 
 class NdpError(RuntimeError):
@@ -35,6 +36,8 @@ _PROTOS = {
     "ndp_forward_step": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
     "ndp_select_workspace_bytes": (_i, [_i, _i, _i, C.POINTER(_sz)]),
     "ndp_select": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_plan_workspace_bytes": (_i, [_vp, _i, _i, _i, C.POINTER(_sz)]),
+    "ndp_plan_select": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_gather_best_action": (_i, [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),
     "ndp_ndiv_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),
     "ndp_ndiv_rowsums": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),

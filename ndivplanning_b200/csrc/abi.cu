@@ -107,7 +107,7 @@ extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) 
   NDP_CHECK_ARG(d->nd >= 0 && d->nd <= 64, "planner_create: noise_dim must be in [0,64]");
   NDP_CHECK_ARG(d->H >= 128 && d->H % 128 == 0 && d->H <= 8192, "planner_create: H must be a multiple of 128 in [128,8192]");
   NDP_CHECK_ARG(d->T >= 1 && d->T <= 4096, "planner_create: T must be in [1,4096]");
-  NDP_CHECK_ARG(d->precision >= NDP_PREC_FP32 && d->precision <= NDP_PREC_F16X2, "planner_create: unknown precision mode %d", d->precision);
+  NDP_CHECK_ARG(d->precision >= NDP_PREC_FP32 && d->precision <= NDP_PREC_F16_REFINE, "planner_create: unknown precision mode %d", d->precision);
   if (d->precision != NDP_PREC_FP32)
     NDP_CHECK_ARG(d->nd <= 15 && d->H <= 2048, "planner_create: tensor-core modes need noise_dim<=15 and H<=2048 (got nd=%d H=%d); use NDP_PREC_FP32", d->nd, d->H);
   if (int rc = device_check()) return rc;
@@ -148,6 +148,7 @@ extern "C" void ndp_planner_destroy(ndp_planner* p) {
   if (p->blob) cudaFree(p->blob);
   if (p->scratch) cudaFree(p->scratch);
   if (p->tc) tc_plan_destroy(p->tc);
+  if (p->tc_refine) tc_plan_destroy(p->tc_refine);
   delete p;
 }
 
@@ -200,8 +201,12 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
   NDP_CUDA(cudaMemcpyAsync(p->bf2, p->bt[6], (size_t)E * sizeof(float), cudaMemcpyDeviceToDevice, s));
   if (p->d.precision != NDP_PREC_FP32) {
     if (p->tc) { tc_plan_destroy(p->tc); p->tc = nullptr; }
-    const int np = p->d.precision == NDP_PREC_F16 ? 1 : (p->d.precision == NDP_PREC_F16X2 ? 2 : 3);
+    if (p->tc_refine) { tc_plan_destroy(p->tc_refine); p->tc_refine = nullptr; }
+    const int prec = p->d.precision;
+    const int np = (prec == NDP_PREC_F16 || prec == NDP_PREC_F16_REFINE) ? 1 : (prec == NDP_PREC_F16X2 ? 2 : 3);
     if (int rc2 = tc_plan_create(&p->tc, np, E, nd, H, p->Wt, p->bt, s)) return rc2;
+    if (prec == NDP_PREC_F16_REFINE)
+      if (int rc2 = tc_plan_create(&p->tc_refine, 3, E, nd, H, p->Wt, p->bt, s)) return rc2;
   }
   p->loaded = true;
   return NDP_OK;
@@ -211,6 +216,7 @@ extern "C" int ndp_planner_workspace_bytes(const ndp_planner* p, int G, int K, s
   NDP_CHECK_ARG(p && bytes && G >= 0 && K >= 0, "planner_workspace_bytes: bad arguments");
   *bytes = (size_t)(G > 0 ? G : 1) * 128 * sizeof(float) + 256;
   if (p->tc) { const size_t t = tc_workspace_bytes(p->tc, G); if (t > *bytes) *bytes = t; }
+  if (p->tc_refine) { const size_t t = tc_workspace_bytes(p->tc_refine, G); if (t > *bytes) *bytes = t; }
   return NDP_OK;
 }
 
@@ -291,4 +297,80 @@ extern "C" int ndp_forward_step(ndp_planner* p, const float* state, const float*
   int rc;
   if ((rc = linear(s, state, p->d.E, action, 4, p->Wt[5], p->bt[5], p->d.H, B, 1, nullptr, p->scratch))) return rc;
   return linear(s, p->scratch, p->d.H, nullptr, 0, p->Wt[6], p->bt[6], p->d.E, B, 0, state, next_state);
+}
+
+// ---- one-call plan ---------------------------------------------------------------------------
+static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
+
+struct PlanWs {
+  size_t rollout, select, list, est, packed, total;
+};
+static int plan_ws_layout(const ndp_planner* p, int G, int K, int topk, PlanWs* w) {
+  size_t r = 0, sel = 0;
+  if (int rc = ndp_planner_workspace_bytes(p, G, K, &r)) return rc;
+  const int tk = p->tc_refine ? NDP_REFINE_R : topk;
+  if (int rc = ndp_select_workspace_bytes(G, K, tk, &sel)) return rc;
+  w->rollout = align256(r);
+  w->select = align256(sel);
+  const size_t GR = (size_t)(G > 0 ? G : 1) * NDP_REFINE_R;
+  w->list = p->tc_refine ? align256(GR * sizeof(int)) : 0;
+  w->est = p->tc_refine ? align256(GR * sizeof(float)) : 0;
+  w->packed = p->tc_refine ? align256((GR + (size_t)(G > 0 ? G : 1)) * sizeof(unsigned long long)) : 0;
+  w->total = w->rollout + w->select + w->list + w->est + w->packed;
+  return NDP_OK;
+}
+
+extern "C" int ndp_plan_workspace_bytes(const ndp_planner* p, int G, int K, int topk, size_t* bytes) {
+  NDP_CHECK_ARG(p && bytes && G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "plan_workspace_bytes: bad arguments");
+  PlanWs w;
+  if (int rc = plan_ws_layout(p, G, K, topk, &w)) return rc;
+  *bytes = w.total;
+  return NDP_OK;
+}
+
+extern "C" int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
+                               int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
+                               int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
+                               void* stream) {
+  NDP_CHECK_ARG(p && p->loaded, "plan_select: planner has no weights (call ndp_planner_load)");
+  NDP_CHECK_ARG(G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "plan_select: bad G/K/topk");
+  NDP_CHECK_ARG(!p->tc_refine || topk <= 64, "plan_select: topk must be <= 64 in refine mode (got %d)", topk);
+  NDP_CHECK_ARG(topk == 0 || (topk_idx && topk_cost), "plan_select: topk_idx/topk_cost required when topk > 0");
+  if (int rc = device_check()) return rc;
+  if (G == 0) return NDP_OK;
+  NDP_CHECK_ARG(packed_min, "plan_select: null packed_min");
+  PlanWs w;
+  if (int rc = plan_ws_layout(p, G, K, topk, &w)) return rc;
+  if (!ws || ws_bytes < w.total) { set_error("plan_select: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
+  NDP_CHECK_ARG(((uintptr_t)ws & 255) == 0, "plan_select: workspace must be 256-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  char* base = reinterpret_cast<char*>(ws);
+  void* ws_roll = base;
+  void* ws_sel = base + w.rollout;
+  if (int rc = ndp_rollout_score(p, e0, goal, noise, G, K, cost, a0, nullptr, ws_roll, w.rollout, stream)) return rc;
+  if (!p->tc_refine) {
+    if (int rc = ndp_select(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws_sel, w.select, stream)) return rc;
+    if (verified) {
+      if (int rc = verify_refine(nullptr, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, 0,
+                                 NDP_REFINE_R, topk, 0.f, verified, s)) return rc;   // K=0 <= R -> all 1
+    }
+    return NDP_OK;
+  }
+  const int R = NDP_REFINE_R;
+  int* list = reinterpret_cast<int*>(base + w.rollout + w.select);
+  float* est = reinterpret_cast<float*>(base + w.rollout + w.select + w.list);
+  unsigned long long* packed_c = reinterpret_cast<unsigned long long*>(base + w.rollout + w.select + w.list + w.est);
+  unsigned long long* pm_est = packed_c + (size_t)G * R;
+  // 1) the R best ESTIMATES per goal (local indices, ascending; -1 padded when K < R)
+  if (int rc = ndp_select(cost, G, K, R, 0, reinterpret_cast<uint64_t*>(pm_est), list, est, ws_sel, w.select, stream)) return rc;
+  // 2) re-roll them with split operands; cost / a0 entries are overwritten, packed keys go to packed_c
+  if (int rc = launch_rollout_tc(p->tc_refine, e0, goal, noise, G, K, p->d.T, cost, a0, nullptr, ws_roll, w.rollout, s,
+                                 list, R, packed_c)) return rc;
+  // 3) the plan from the refined costs (ties -> lower candidate index, like the reference scan)
+  if (int rc = select_packed(packed_c, G, R, topk, (long long)idx_base,
+                             reinterpret_cast<unsigned long long*>(packed_min), topk_idx, topk_cost, s)) return rc;
+  if (verified)
+    if (int rc = verify_refine(est, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, K, R, topk,
+                               eps > 0.f ? eps : 1e-3f, verified, s)) return rc;
+  return NDP_OK;
 }

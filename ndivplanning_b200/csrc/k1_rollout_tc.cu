@@ -408,8 +408,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
     // ===================== epilogue warps 0..7 =====================================================
     const int q = warp & 3, h = warp >> 2;
     const int m = q * 32 + lane;                       // candidate row = TMEM lane
-    const int cand = m0 + m;
-    const bool valid = cand < p.K;
+    int cand = m0 + m;
+    bool valid = cand < p.K;
+    if (p.list) {                                         // refine pass: explicit candidate list
+      cand = (m0 + m < p.R) ? __ldg(p.list + (size_t)g * p.R + m0 + m) : -1;
+      valid = cand >= 0 && cand < p.K;
+    }
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
     uint32_t dw = 0, ae = 0;
 #ifdef NDP_TC_PROF
@@ -532,7 +536,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
           }
           if (h == 1) s_red[m] = cs;
           asm volatile("bar.sync 1, 256;" ::: "memory");
-          if (h == 0 && valid) p.cost[(size_t)g * p.K + cand] = (cs + s_red[m]) * (1.0f / 128.0f);
+          if (h == 0) {
+            const float cv = (cs + s_red[m]) * (1.0f / 128.0f);
+            if (valid) p.cost[(size_t)g * p.K + cand] = cv;
+            if (p.packed_c && m0 + m < p.R)
+              p.packed_c[(size_t)g * p.R + m0 + m] =
+                  valid ? (((unsigned long long)ordered_key(cv + 0.0f) << 32) | (unsigned)cand) : ~0ull;
+          }
           if (p.state_T && valid) {
             float4* o = reinterpret_cast<float4*>(p.state_T + ((size_t)g * p.K + cand) * 128) + h * 16;
 #pragma unroll
@@ -736,7 +746,8 @@ static int launch_np(const TcParams& tp, int grid, cudaStream_t s) {
 }
 
 int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const float* noise, int G, int K, int T,
-                      float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s) {
+                      float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s,
+                      const int* list, int R, unsigned long long* packed_c) {
   const size_t need = (size_t)G * P->gext_stride;
   if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
   NDP_CHECK_ARG(((uintptr_t)ws & 15) == 0, "rollout_score: workspace must be 16-byte aligned");
@@ -747,7 +758,8 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
   tp.stream = P->stream; tp.items = P->items; tp.gext = reinterpret_cast<const uint8_t*>(ws);
   tp.gext_stride = P->gext_stride; tp.e0 = e0; tp.goal = goal; tp.noise = noise; tp.cost = cost; tp.a0 = a0;
   tp.state_T = state_T; tp.G = G; tp.K = K; tp.T = T; tp.nd = P->nd; tp.n_items = P->n_items;
-  tp.tiles_per_goal = (K + 127) / 128; tp.n_hid_chunks = P->n_chunks;
+  tp.list = list; tp.R = R; tp.packed_c = packed_c;
+  tp.tiles_per_goal = ((list ? R : K) + 127) / 128; tp.n_hid_chunks = P->n_chunks;
   const long long grid = (long long)G * tp.tiles_per_goal;
   NDP_CHECK_ARG(grid <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
   if (P->np == 1) return launch_np<1>(tp, (int)grid, s);

@@ -22,11 +22,11 @@ __device__ __forceinline__ unsigned long long warp_min_u64(unsigned long long v)
   return v;
 }
 
-// in-place ascending bitonic sort of buf[0..kSelBuf) by the whole block
-__device__ void block_bitonic_sort(unsigned long long* buf) {
-  for (int k = 2; k <= kSelBuf; k <<= 1) {
+// in-place ascending bitonic sort of buf[0..len) by the whole block (len = power of two <= kSelBuf)
+__device__ void block_bitonic_sort(unsigned long long* buf, int len) {
+  for (int k = 2; k <= len; k <<= 1) {
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int i = threadIdx.x; i < kSelBuf; i += kSelThreads) {
+      for (int i = threadIdx.x; i < len; i += kSelThreads) {
         int ixj = i ^ j;
         if (ixj > i) {
           unsigned long long a = buf[i], b = buf[ixj];
@@ -49,9 +49,11 @@ struct TopkState {
 __device__ void topk_compact(TopkState s, int topk) {
   __syncthreads();
   int n = *s.cnt;
-  for (int i = n + threadIdx.x; i < kSelBuf; i += kSelThreads) s.buf[i] = kPadKey;
+  int len = 32;
+  while (len < n) len <<= 1;
+  for (int i = n + threadIdx.x; i < len; i += kSelThreads) s.buf[i] = kPadKey;
   __syncthreads();
-  block_bitonic_sort(s.buf);
+  block_bitonic_sort(s.buf, len);
   if (threadIdx.x == 0) {
     int m = n < topk ? n : topk;
     *s.cnt = m;
@@ -170,11 +172,32 @@ __global__ void gather_best_kernel(const float* __restrict__ a0, const unsigned 
   }
 }
 
+// verified[g] = 1 when the refined selection is provably the selection of exact costs over ALL K candidates:
+// every candidate outside the refine list has estimate >= est_last, hence exact cost >= est_last*(1-eps);
+// if the k-th exact cost inside the list is strictly below that bound nothing outside can enter the top-k.
+__global__ void verify_refine_kernel(const float* __restrict__ est_topR, const float* __restrict__ exact_topk,
+                                     const unsigned long long* __restrict__ packed_min, int G, int K, int R, int topk,
+                                     float eps, int* __restrict__ verified) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  int ok;
+  if (K <= R) {
+    ok = 1;                                            // the list holds every candidate
+  } else {
+    const float bound = est_topR[(size_t)g * R + R - 1] * (1.f - eps);
+    float kth;
+    if (topk > 0) kth = exact_topk[(size_t)g * topk + topk - 1];
+    else kth = (packed_min[g] == kInvalidPacked) ? __int_as_float(0x7fc00000) : key_to_float((uint32_t)(packed_min[g] >> 32));
+    ok = (kth < bound) ? 1 : 0;                        // NaN compares false -> unverified
+  }
+  verified[g] = ok;
+}
+
 static void plan_chunks(int G, int K, int* chunks, int* chunk_len) {
   if (K <= 0) { *chunks = 1; *chunk_len = kSelTile; return; }
-  int want = 592 / (G > 0 ? G : 1);
+  int want = 1184 / (G > 0 ? G : 1);
   if (want < 1) want = 1;
-  int maxc = (K + 4095) / 4096;
+  int maxc = (K + kSelTile - 1) / kSelTile;
   int c = want < maxc ? want : maxc;
   if (c < 1) c = 1;
   int len = (K + c - 1) / c;
@@ -235,6 +258,24 @@ extern "C" int ndp_select(const float* cost, int G, int K, int topk, int64_t idx
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
+
+namespace ndp {
+// selection over packed (okey(cost)<<32 | index) keys, n <= 1024 per goal: one block per goal
+int select_packed(const unsigned long long* packed, int G, int n, int topk, long long idx_base,
+                  unsigned long long* pm, int* topk_idx, float* topk_cost, cudaStream_t s) {
+  NDP_CHECK_ARG(n >= 1 && n <= kSelTile && topk <= 128 && G <= 65535, "select_packed: bad sizes");
+  select_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, packed, n, kSelTile, topk, 1, idx_base, pm, nullptr,
+                                                      topk_idx, topk_cost);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+int verify_refine(const float* est_topR, const float* exact_topk, const unsigned long long* pm, int G, int K, int R,
+                  int topk, float eps, int* verified, cudaStream_t s) {
+  verify_refine_kernel<<<(G + 127) / 128, 128, 0, s>>>(est_topR, exact_topk, pm, G, K, R, topk, eps, verified);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+}  // namespace ndp
 
 extern "C" int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,
                                       int64_t idx_base, float* best_action, int32_t* best_idx, void* stream) {

@@ -60,6 +60,11 @@ struct TcParams {
   float* cost;
   float* a0;
   float* state_T;
+  // list mode (refine pass): candidates of goal g are list[g*R + pos], pos < R (-1 = none); costs/actions
+  // are scattered back into cost/a0 and the packed keys (okey(cost)<<32 | candidate) go to packed_c[g*R+pos]
+  const int* list;
+  unsigned long long* packed_c;
+  int R;
   int G, K, T, nd, n_items, tiles_per_goal, n_hid_chunks;
 };
 
@@ -69,7 +74,13 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
 void tc_plan_destroy(TcPlan* p);
 size_t tc_workspace_bytes(const TcPlan* p, int G);
 int launch_rollout_tc(const TcPlan* plan, const float* e0, const float* goal, const float* noise, int G, int K,
-                      int T, float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s);
+                      int T, float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s,
+                      const int* list = nullptr, int R = 0, unsigned long long* packed_c = nullptr);
+
+int select_packed(const unsigned long long* packed, int G, int n, int topk, long long idx_base,
+                  unsigned long long* pm, int* topk_idx, float* topk_cost, cudaStream_t s);
+int verify_refine(const float* est_topR, const float* exact_topk, const unsigned long long* pm, int G, int K, int R,
+                  int topk, float eps, int* verified, cudaStream_t s);
 
 }  // namespace ndp
 
@@ -88,4 +99,5 @@ struct ndp_planner {
   size_t scratch_floats;
   int nq;
   ndp::TcPlan* tc;     // tensor-core plan (precision != fp32), else null
+  ndp::TcPlan* tc_refine;  // f16x3 plan of the refine pass (NDP_PREC_F16_REFINE), else null
 };

@@ -30,6 +30,7 @@ class Plan:
     topk_idx: Optional[torch.Tensor] = None    # [G,topk] int32
     topk_cost: Optional[torch.Tensor] = None   # [G,topk]
     state_T: Optional[torch.Tensor] = None     # [G,K,E]
+    verified: Optional[torch.Tensor] = None    # [G] int32: 1 = selection proven equal to the exact-cost selection
 
 
 def select_plan(cost: torch.Tensor, topk: int = 0, idx_base: int = 0):
@@ -77,7 +78,7 @@ class FusedPlanner:
         self.device = torch.device(device)
         self.E, self.H, self.nd, self.T = E, H, nd, int(horizon)
         prec = {"fp32": _lib.PREC_FP32, "f16x3": _lib.PREC_F16X3, "f16x2": _lib.PREC_F16X2,
-                "f16": _lib.PREC_F16}[precision]
+                "f16": _lib.PREC_F16, "f16+refine": _lib.PREC_F16_REFINE}[precision]
         self.precision = precision
         self._h = C.c_void_p()
         desc = PlannerDesc(E, nd, 4, H, self.T, prec)
@@ -101,7 +102,8 @@ class FusedPlanner:
 
     # ---- K1 ---------------------------------------------------------------------------------
     def rollout_score(self, e0, goal, noise, want_state=False):
-        """e0, goal [G,E]; noise [T,G,K,nd] -> (cost[G,K], a0[G,K,4], state_T[G,K,E]|None)."""
+        """e0, goal [G,E]; noise [T,G,K,nd] -> (cost[G,K], a0[G,K,4], state_T[G,K,E]|None).
+        With precision "f16+refine" this is the single-pass bulk estimate (no refine)."""
         require_cuda(e0, goal, noise)
         e0c, gc, nz = f32c(e0), f32c(goal), f32c(noise)
         T, G, K, nd = nz.shape
@@ -120,17 +122,46 @@ class FusedPlanner:
                                           ptr(ws), ws.numel(), stream_ptr(dev)))
         return cost, a0, sT
 
-    # ---- K1 + K3 + gather ---------------------------------------------------------------------
-    def plan(self, e0, goal, noise, topk: int = 0, idx_base: int = 0, want_state=False) -> Plan:
-        cost, a0, sT = self.rollout_score(e0, goal, noise, want_state)
-        packed, tk_idx, tk_cost = select_plan(cost, topk, idx_base)
-        G, K = cost.shape
+    # ---- K1 + K3 (+ refine) + gather: one C call for rollout and selection ------------------------------
+    def plan(self, e0, goal, noise, topk: int = 0, idx_base: int = 0, want_state=False, eps: float = 0.0) -> Plan:
+        """mpc_eval.py:124-165.  precision "f16+refine": all K candidates are scored single-pass, the 128 best
+        estimates are re-rolled with split operands and the plan is chosen from those fp32-grade costs;
+        `Plan.verified[g]` tells whether that provably equals choosing from exact costs of all K."""
+        if want_state:
+            if self.precision == "f16+refine":
+                raise _lib.NdpError("want_state is not available with precision 'f16+refine'")
+            cost, a0, sT = self.rollout_score(e0, goal, noise, True)
+            packed, tk_idx, tk_cost = select_plan(cost, topk, idx_base)
+            G, K = cost.shape
+            verified = torch.ones(G, dtype=torch.int32, device=self.device)
+        else:
+            require_cuda(e0, goal, noise)
+            e0c, gc, nz = f32c(e0), f32c(goal), f32c(noise)
+            T, G, K, nd = nz.shape
+            if T != self.T or nd != self.nd or tuple(e0c.shape) != (G, self.E) or tuple(gc.shape) != (G, self.E):
+                raise _lib.NdpError(f"shape mismatch: noise {tuple(nz.shape)} e0 {tuple(e0c.shape)} for "
+                                    f"T={self.T} nd={self.nd} E={self.E}")
+            dev = self.device
+            cost = torch.empty(G, K, dtype=torch.float32, device=dev)
+            a0 = torch.empty(G, K, 4, dtype=torch.float32, device=dev)
+            packed = torch.empty(G, dtype=torch.int64, device=dev)
+            tk_idx = torch.empty(G, topk, dtype=torch.int32, device=dev) if topk > 0 else None
+            tk_cost = torch.empty(G, topk, dtype=torch.float32, device=dev) if topk > 0 else None
+            verified = torch.empty(G, dtype=torch.int32, device=dev)
+            n = C.c_size_t()
+            check(lib().ndp_plan_workspace_bytes(self._h, G, K, topk, C.byref(n)))
+            ws = torch.empty(max(n.value, 256), dtype=torch.uint8, device=dev)
+            with torch.cuda.device(dev):
+                check(lib().ndp_plan_select(self._h, ptr(e0c), ptr(gc), ptr(nz), G, K, topk, idx_base, eps, ptr(cost),
+                                            ptr(a0), ptr(packed), ptr(tk_idx), ptr(tk_cost), ptr(verified), ptr(ws),
+                                            ws.numel(), stream_ptr(dev)))
+            sT = None
         best_action = torch.zeros(G, 4, dtype=torch.float32, device=self.device)
         best_idx = torch.empty(G, dtype=torch.int32, device=self.device)
         with torch.cuda.device(self.device):
             check(lib().ndp_gather_best_action(ptr(a0), ptr(packed), G, K, idx_base, ptr(best_action),
                                                ptr(best_idx), stream_ptr(self.device)))
-        return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT)
+        return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified)
 
     # ---- single-call module semantics (drop-in for generator(z) / fwd_model(state, a)) -------
     def generator(self, z):

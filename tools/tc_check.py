@@ -30,5 +30,10 @@ for (G, K, T, H) in CFGS:
             a_.record(); pl.rollout_score(e0, goal, noise); b_.record(); torch.cuda.synchronize()
             ts.append(a_.elapsed_time(b_))
         ms = min(ts)
+        tp = []
+        for _ in range(5):
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record(); pl.plan(e0, goal, noise, topk=16); b_.record(); torch.cuda.synchronize()
+            tp.append(a_.elapsed_time(b_))
         print(f"G={G} K={K} T={T} H={H} {mode:6s} cost maxrel={rel:.3e} a0 rel={arel:.3e} state rel={srel:.3e} "
-              f"argmin same={same} finite={bool(torch.isfinite(c).all())}  {ms:.3f} ms  {G*K*T/ms/1e6:.2f} Gsteps/s", flush=True)
+              f"argmin same={same} finite={bool(torch.isfinite(c).all())}  {ms:.3f} ms  {G*K*T/ms/1e6:.2f} Gsteps/s  plan(topk16) {min(tp):.3f} ms", flush=True)
