@@ -132,6 +132,12 @@ def run_reference(args):
 # --------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------
+K1_KERNEL = {"fp32": "rollout_f32_kernel", "f16": "rollout_tc_kernel<1>", "f16x2": "rollout_tc_kernel<2>",
+             "f16x3": "rollout_tc_kernel<3>", "f16+refine": "rollout_tc_kernel<1>"}
+MMA_PASSES = {"fp32": 0, "f16": 1, "f16x2": 2, "f16x3": 3, "f16+refine": 1}
+POOL = 40   # distinct noise sets rotated through the timed region: 40 x 4.2 MB = 168 MB > 126 MB of L2
+
+
 def run_gpu(args):
     import torch.distributed as dist
     from ndivplanning_b200 import FusedPlanner, diversity, launch_count, synthetic
@@ -148,13 +154,17 @@ def run_gpu(args):
     c = CFG
     G, K, T, E, nd, topk = c["G"], c["K"], c["T"], c["E"], c["nd"], c["topk"]
     K_total = K * world
+    prec = args.precision
     gen, fwd = synthetic.make_models(nd=nd, E=E, H=c["H"])
-    planner = FusedPlanner(gen, fwd, horizon=T, device=dev)
+    planner = FusedPlanner(gen, fwd, horizon=T, device=dev, precision=prec)
     sharded = ShardedPlanner(planner) if world > 1 else None
-    e0_h, goal_h, noise_h = synthetic.make_plan_inputs(G, K, T, nd, E, seed=1 + rank)
+    side = torch.cuda.Stream(device=dev, priority=-1) if (prec == "f16+refine" and world == 1) else None
     e0_h, goal_h, _ = synthetic.make_plan_inputs(G, 1, 1, nd, E, seed=1)       # same goal on every rank
-    e0_h, goal_h, noise_h = e0_h.pin_memory(), goal_h.pin_memory(), noise_h.pin_memory()
-    e0, goal, noise = e0_h.to(dev), goal_h.to(dev), noise_h.to(dev)
+    g_ = torch.Generator().manual_seed(100 + rank)
+    pool_h = [torch.rand(T, G, K, nd, generator=g_).pin_memory() for _ in range(POOL)]   # U[0,1) like the sampler
+    e0_h, goal_h = e0_h.pin_memory(), goal_h.pin_memory()
+    e0, goal = e0_h.to(dev), goal_h.to(dev)
+    pool = [n.to(dev) for n in pool_h]
     flush = l2_flusher(dev)
 
     def barrier():
@@ -162,63 +172,90 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def plan_resident():
+    def plan_dev(nz):
         if sharded:
-            return sharded.plan(e0, goal, noise, K_total, topk=topk)
-        return planner.plan(e0, goal, noise, topk=topk)
+            return sharded.plan(e0, goal, nz, K_total, topk=topk)
+        return planner.plan(e0, goal, nz, topk=topk, refine_stream=side)
 
-    res_h = {"idx": torch.empty(G, dtype=torch.int32).pin_memory(), "act": torch.empty(G, 4).pin_memory(),
-             "key": torch.empty(G, dtype=torch.int64).pin_memory()}
+    def run_resident(steps, first):
+        """`steps` plans back to back on device-resident inputs; one event pair around all of them"""
+        a, b = ev(), ev()
+        a.record()
+        plans = [plan_dev(pool[(first + i) % POOL]) for i in range(steps)]
+        for p_ in plans[-2:]:
+            p_.wait()
+        b.record()
+        return a, b, plans
 
-    def plan_e2e():
-        # host buffers in, host result out: H2D of this step's inputs + D2H of the plan inside the timed region
-        e0_d = e0_h.to(dev, non_blocking=True); goal_d = goal_h.to(dev, non_blocking=True)
-        nz_d = noise_h.to(dev, non_blocking=True)
-        p = sharded.plan(e0_d, goal_d, nz_d, K_total, topk=topk) if sharded else planner.plan(e0_d, goal_d, nz_d, topk=topk)
-        res_h["idx"].copy_(p.best_idx, non_blocking=True)
-        res_h["act"].copy_(p.best_action, non_blocking=True)
-        res_h["key"].copy_(p.packed_min, non_blocking=True)
-        return p
+    res_h = [{"idx": torch.empty(G, dtype=torch.int32).pin_memory(), "act": torch.empty(G, 4).pin_memory(),
+              "key": torch.empty(G, dtype=torch.int64).pin_memory()} for _ in range(2)]
 
-    def timed(fn, steps, warmup, split=False):
-        for _ in range(warmup):
-            fn()
-        barrier()
-        tot, k1 = 0.0, 0.0
+    def run_e2e(steps, first):
+        """host buffers in, host results out, every step: H2D of the step's noise/e0/goal, plan, D2H of the plan"""
+        a, b = ev(), ev()
+        a.record()
+        prev = None
+        for i in range(steps):
+            nz_d = pool_h[(first + i) % POOL].to(dev, non_blocking=True)
+            e0_d = e0_h.to(dev, non_blocking=True); goal_d = goal_h.to(dev, non_blocking=True)
+            p_ = (sharded.plan(e0_d, goal_d, nz_d, K_total, topk=topk) if sharded
+                  else planner.plan(e0_d, goal_d, nz_d, topk=topk, refine_stream=side))
+            if prev is not None:                       # results of the previous plan leave while this one runs
+                q, r = prev
+                q.wait()
+                r["idx"].copy_(q.best_idx, non_blocking=True); r["act"].copy_(q.best_action, non_blocking=True)
+                r["key"].copy_(q.packed_min, non_blocking=True)
+            prev = (p_, res_h[i & 1])
+        q, r = prev
+        q.wait()
+        r["idx"].copy_(q.best_idx, non_blocking=True); r["act"].copy_(q.best_action, non_blocking=True)
+        r["key"].copy_(q.packed_min, non_blocking=True)
+        b.record()
+        return a, b
+
+    def timed_k1(pl, steps):
         pairs = []
-        for _ in range(steps):
-            flush()                                   # L2 flush between timed iterations (untimed)
-            a, b = ev(), ev()
-            a.record(); fn(); b.record()
-            pairs.append((a, b))
-        barrier()
-        tot = sum(a.elapsed_time(b) for a, b in pairs) / steps
-        return tot
-
-    def timed_k1(steps):
-        pairs = []
-        for _ in range(steps):
+        for i in range(steps):
             flush()
             a, b = ev(), ev()
-            a.record(); planner.rollout_score(e0, goal, noise); b.record()
+            a.record(); pl.rollout_score(e0, goal, pool[i % POOL]); b.record()
             pairs.append((a, b))
         torch.cuda.synchronize()
         return sum(a.elapsed_time(b) for a, b in pairs) / steps
 
-    sampler = ClockSampler(local)
-    plan0 = plan_resident()                            # sanity: a plan exists and is finite
-    assert torch.isfinite(plan0.cost).all()
-    n_before = None
-    for _ in range(args.warmup):
-        plan_resident()
+    # ---- parity of the benchmarked configuration against the fp32 CUDA path (outside the timed region)
+    parity = None
+    if world == 1:
+        exact = FusedPlanner(gen, fwd, horizon=T, device=dev, precision="fp32").plan(e0, goal, pool[0], topk=topk)
+        got = planner.plan(e0, goal, pool[0], topk=topk)
+        torch.cuda.synchronize()
+        sel = sorted(set(got.topk_idx[0].tolist() + [int(got.best_idx[0])]))
+        rel = ((got.cost - exact.cost).abs() / exact.cost)
+        parity = {"vs": "fp32 CUDA-core path (itself parity-tested against the oracle)",
+                  "argmin_equal": bool(int(got.best_idx[0]) == int(exact.best_idx[0])),
+                  "topk_set_equal": bool(set(got.topk_idx[0].tolist()) == set(exact.topk_idx[0].tolist())),
+                  "verified": got.verified.tolist(),
+                  "cost_rel_err_selected_max": float(rel[0, sel].max()), "cost_rel_err_all_max": float(rel.max())}
+        del exact
+    for i in range(args.warmup):
+        plan_dev(pool[i % POOL]).wait()
     barrier()
+    sampler = ClockSampler(local)
     sampler.start()
     n_before = launch_count()
-    ms = timed(plan_resident, args.steps, 0)
+    a, b, plans = run_resident(args.steps, 0)
+    barrier()
+    ms = a.elapsed_time(b) / args.steps
     n_launch = launch_count() - n_before
-    k1_ms = timed_k1(args.steps)
-    ms_e2e = timed(plan_e2e, args.steps, args.warmup)
-    # ---- ndiv (BASELINE config 3) fwd+bwd, rows sharded when world > 1 is not timed here (N=1 figure per rank)
+    assert all(torch.isfinite(p_.cost).all() for p_ in plans[-1:])
+    del plans
+    k1_ms = timed_k1(planner, min(args.steps, 10))
+    run_e2e(min(args.warmup, 3), 0)
+    barrier()
+    a, b = run_e2e(args.steps, 7)
+    barrier()
+    ms_e2e = a.elapsed_time(b) / args.steps
+    # ---- ndiv (BASELINE config 3) fwd+bwd (N=1 figure per rank)
     x_h, z_h = synthetic.make_ndiv_inputs(NDIV["N"], NDIV["k"], NDIV["Dx"], NDIV["Dz"])
     x, z = x_h.to(dev), z_h.to(dev)
 
@@ -228,8 +265,36 @@ def run_gpu(args):
         loss.backward()
         return loss
 
-    ndiv_ms = timed(ndiv_step, args.steps, args.warmup)
+    for _ in range(args.warmup):
+        ndiv_step()
+    pairs_ = []
+    for _ in range(args.steps):
+        flush()
+        a, b = ev(), ev()
+        a.record(); ndiv_step(); b.record()
+        pairs_.append((a, b))
+    torch.cuda.synchronize()
+    ndiv_ms = sum(a.elapsed_time(b) for a, b in pairs_) / args.steps
     clocks = sampler.finish()
+    # ---- other precision modes of the same kernel family, for context (short runs)
+    modes = {}
+    if world == 1:
+        for m in ("f16", "f16x3", "fp32"):
+            pl = FusedPlanner(gen, fwd, horizon=T, device=dev, precision=m)
+            n_ = 3 if m == "fp32" else 10
+            for i in range(2):
+                pl.plan(e0, goal, pool[i], topk=topk)
+            torch.cuda.synchronize()
+            a, b = ev(), ev()
+            a.record()
+            for i in range(n_):
+                pl.plan(e0, goal, pool[(3 + i) % POOL], topk=topk)
+            b.record(); torch.cuda.synchronize()
+            pms = a.elapsed_time(b) / n_
+            kms = timed_k1(pl, n_)
+            modes[m] = {"plan_ms": pms, "candidate_steps_per_s": G * K * T / (pms * 1e-3), "k1_ms": kms,
+                        "k1_algorithmic_tflops": G * K * T * F_ALG / (kms * 1e-3) / 1e12}
+            del pl
 
     def maxr(v):
         if world == 1:
@@ -244,27 +309,38 @@ def run_gpu(args):
         units = G * K_total * T
         value = units / (ms * 1e-3)
         k1_tflops = G * K * T * F_ALG / (k1_ms * 1e-3) / 1e12
+        passes = MMA_PASSES[prec]
         pairs = NDIV["N"] * NDIV["k"] ** 2
         out = {
             "metric": "mpc_candidate_steps_per_sec", "value": value, "unit": "candidate-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if prec == "fp32" else "f16 operands (split hi/lo where stated), f32 accumulate/state",
+            "data": "synthetic",
             "config": dict(workload="mpc_cfg2_K65536_T8_E128_H1024_nd2", per_gpu_K=K, K_total=K_total,
-                           l2_flush_between_steps=True, precision=planner.precision, weights="default-init sep30",
+                           l2="inputs rotate through a %d MB pool (> 126 MB L2); weights stay L2-resident by design"
+                              % (POOL * T * G * K * nd * 4 >> 20),
+                           precision=prec, weights="default-init sep30",
+                           step="one plan: rollout of all K + top-%d/argmin%s" % (
+                               topk, " + split-operand refine of the 128 best, pipelined on a side stream"
+                               if prec == "f16+refine" else ""),
                            **{k: v for k, v in c.items() if k != "K"}),
             "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "candidate-steps/s", "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": int(noise_h.numel() * 4 + e0_h.numel() * 4 + goal_h.numel() * 4),
+                    "h2d_bytes_per_step": int(pool_h[0].numel() * 4 + e0_h.numel() * 4 + goal_h.numel() * 4),
                     "d2h_bytes_per_step": int(G * (4 + 16 + 8))},
             "gpu_launches": int(n_launch),
             "clocks": clocks,
-            "roofline": {"kernel": "rollout_f32_kernel", "bound": "tensor", "achieved": k1_tflops, "peak": pk["bf16"],
+            "roofline": {"kernel": K1_KERNEL[prec], "bound": "tensor", "achieved": k1_tflops, "peak": pk["bf16"],
                          "unit": "TFLOP/s", "frac": k1_tflops / pk["bf16"], "traffic": None,
-                         "peak_source": pk["src"] + " bf16 burst (kernel timed alone)",
-                         "kernel_ms": k1_ms, "flop_per_candidate_step": F_ALG,
-                         "note": "fp32 parity mode issues FFMA on CUDA cores (no tensor pipe); fraction is vs the "
-                                 "tensor roofline the path is ultimately bound by"},
+                         "peak_source": pk["src"] + " bf16 burst (kernel timed alone, L2 flushed before each launch)",
+                         "kernel_ms": k1_ms, "flop_per_candidate_step": F_ALG, "mma_passes": passes,
+                         "issued_mma_frac": (k1_tflops * max(passes, 1) / pk["bf16"]) if passes else None,
+                         "note": "achieved = algorithmic FLOP (666,112 per candidate-step) / CUDA-event time of the bulk "
+                                 "rollout kernel; fp16 and bf16 share the tcgen05 kind::f16 rate"},
             "ndiv": {"metric": "ndiv_pairs_per_sec_fwd_bwd", "value": pairs / (ndiv_ms * 1e-3), "unit": "ordered pairs/s",
                      "ms_per_step": ndiv_ms, "config": NDIV},
+            "parity": parity,
+            "modes": modes,
         }
         if world == 1:
             t0 = time.perf_counter()
@@ -285,6 +361,7 @@ if __name__ == "__main__":
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="f16+refine", choices=["fp32", "f16", "f16x2", "f16x3", "f16+refine"])
     a = ap.parse_args()
     if a.impl == "reference":
         run_reference(a)

@@ -119,6 +119,19 @@ int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const fl
                     int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
                     int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
                     void* stream);
+/* The same call split in two stream-ordered halves with identical arguments, so that a caller may overlap the
+ * (latency-bound, single-tile) refine half of plan i with the bulk half of plan i+1 on another stream:
+ *   _bulk  : rollout of all K + selection of the refine list (the whole selection when not refining);
+ *   _refine: re-roll + selection from refined costs + verification (no-op when not refining).
+ * The caller orders _refine after _bulk (event) and keeps the workspace alive across both. */
+int ndp_plan_select_bulk(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
+                         int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
+                         int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
+                         void* stream);
+int ndp_plan_select_refine(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
+                           int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
+                           int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
+                           void* stream);
 
 /* best_action[g,:] = a0[g, idx(packed_min[g]) - idx_base, :]   (mpc_eval.py:165) */
 int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,

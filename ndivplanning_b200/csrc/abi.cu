@@ -328,10 +328,12 @@ extern "C" int ndp_plan_workspace_bytes(const ndp_planner* p, int G, int K, int 
   return NDP_OK;
 }
 
-extern "C" int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
-                               int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
-                               int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
-                               void* stream) {
+// phase bit 0: bulk rollout (+ selection of the refine list, or the whole selection when not refining)
+// phase bit 1: refine pass + selection from refined costs + verification
+static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const float* goal, const float* noise, int G,
+                            int K, int topk, int64_t idx_base, float eps, float* cost, float* a0,
+                            uint64_t* packed_min, int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws,
+                            size_t ws_bytes, void* stream) {
   NDP_CHECK_ARG(p && p->loaded, "plan_select: planner has no weights (call ndp_planner_load)");
   NDP_CHECK_ARG(G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "plan_select: bad G/K/topk");
   NDP_CHECK_ARG(!p->tc_refine || topk <= 64, "plan_select: topk must be <= 64 in refine mode (got %d)", topk);
@@ -347,30 +349,56 @@ extern "C" int ndp_plan_select(ndp_planner* p, const float* e0, const float* goa
   char* base = reinterpret_cast<char*>(ws);
   void* ws_roll = base;
   void* ws_sel = base + w.rollout;
-  if (int rc = ndp_rollout_score(p, e0, goal, noise, G, K, cost, a0, nullptr, ws_roll, w.rollout, stream)) return rc;
-  if (!p->tc_refine) {
-    if (int rc = ndp_select(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws_sel, w.select, stream)) return rc;
-    if (verified) {
-      if (int rc = verify_refine(nullptr, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, 0,
-                                 NDP_REFINE_R, topk, 0.f, verified, s)) return rc;   // K=0 <= R -> all 1
-    }
-    return NDP_OK;
-  }
   const int R = NDP_REFINE_R;
   int* list = reinterpret_cast<int*>(base + w.rollout + w.select);
   float* est = reinterpret_cast<float*>(base + w.rollout + w.select + w.list);
   unsigned long long* packed_c = reinterpret_cast<unsigned long long*>(base + w.rollout + w.select + w.list + w.est);
   unsigned long long* pm_est = packed_c + (size_t)G * R;
-  // 1) the R best ESTIMATES per goal (local indices, ascending; -1 padded when K < R)
-  if (int rc = ndp_select(cost, G, K, R, 0, reinterpret_cast<uint64_t*>(pm_est), list, est, ws_sel, w.select, stream)) return rc;
-  // 2) re-roll them with split operands; cost / a0 entries are overwritten, packed keys go to packed_c
-  if (int rc = launch_rollout_tc(p->tc_refine, e0, goal, noise, G, K, p->d.T, cost, a0, nullptr, ws_roll, w.rollout, s,
-                                 list, R, packed_c)) return rc;
-  // 3) the plan from the refined costs (ties -> lower candidate index, like the reference scan)
-  if (int rc = select_packed(packed_c, G, R, topk, (long long)idx_base,
-                             reinterpret_cast<unsigned long long*>(packed_min), topk_idx, topk_cost, s)) return rc;
-  if (verified)
-    if (int rc = verify_refine(est, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, K, R, topk,
-                               eps > 0.f ? eps : 1e-3f, verified, s)) return rc;
+  if (phase & 1) {
+    if (int rc = ndp_rollout_score(p, e0, goal, noise, G, K, cost, a0, nullptr, ws_roll, w.rollout, stream)) return rc;
+    if (!p->tc_refine) {
+      if (int rc = ndp_select(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws_sel, w.select, stream)) return rc;
+      if (verified)   // K=0 <= R marks every goal verified: nothing was estimated
+        if (int rc = verify_refine(nullptr, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, 0, R,
+                                   topk, 0.f, verified, s)) return rc;
+      return NDP_OK;
+    }
+    // the R best ESTIMATES per goal (local indices, ascending; -1 padded when K < R)
+    if (int rc = ndp_select(cost, G, K, R, 0, reinterpret_cast<uint64_t*>(pm_est), list, est, ws_sel, w.select, stream)) return rc;
+  }
+  if ((phase & 2) && p->tc_refine) {
+    // re-roll them with split operands; cost / a0 entries are overwritten, packed keys go to packed_c.
+    // (the per-goal bias block is rebuilt in ws_roll: the bulk pass of THIS plan has finished with it)
+    if (int rc = launch_rollout_tc(p->tc_refine, e0, goal, noise, G, K, p->d.T, cost, a0, nullptr, ws_roll, w.rollout, s,
+                                   list, R, packed_c)) return rc;
+    // the plan from the refined costs (ties -> lower candidate index, like the reference scan)
+    if (int rc = select_packed(packed_c, G, R, topk, (long long)idx_base,
+                               reinterpret_cast<unsigned long long*>(packed_min), topk_idx, topk_cost, s)) return rc;
+    if (verified)
+      if (int rc = verify_refine(est, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, K, R, topk,
+                                 eps > 0.f ? eps : 1e-3f, verified, s)) return rc;
+  }
   return NDP_OK;
+}
+
+extern "C" int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
+                               int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
+                               int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
+                               void* stream) {
+  return plan_select_impl(3, p, e0, goal, noise, G, K, topk, idx_base, eps, cost, a0, packed_min, topk_idx, topk_cost,
+                          verified, ws, ws_bytes, stream);
+}
+extern "C" int ndp_plan_select_bulk(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G,
+                                    int K, int topk, int64_t idx_base, float eps, float* cost, float* a0,
+                                    uint64_t* packed_min, int32_t* topk_idx, float* topk_cost, int32_t* verified,
+                                    void* ws, size_t ws_bytes, void* stream) {
+  return plan_select_impl(1, p, e0, goal, noise, G, K, topk, idx_base, eps, cost, a0, packed_min, topk_idx, topk_cost,
+                          verified, ws, ws_bytes, stream);
+}
+extern "C" int ndp_plan_select_refine(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G,
+                                      int K, int topk, int64_t idx_base, float eps, float* cost, float* a0,
+                                      uint64_t* packed_min, int32_t* topk_idx, float* topk_cost, int32_t* verified,
+                                      void* ws, size_t ws_bytes, void* stream) {
+  return plan_select_impl(2, p, e0, goal, noise, G, K, topk, idx_base, eps, cost, a0, packed_min, topk_idx, topk_cost,
+                          verified, ws, ws_bytes, stream);
 }

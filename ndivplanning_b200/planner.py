@@ -31,6 +31,13 @@ class Plan:
     topk_cost: Optional[torch.Tensor] = None   # [G,topk]
     state_T: Optional[torch.Tensor] = None     # [G,K,E]
     verified: Optional[torch.Tensor] = None    # [G] int32: 1 = selection proven equal to the exact-cost selection
+    ready: Optional[torch.cuda.Event] = None   # set when the plan was finished on a side stream (refine_stream=)
+
+    def wait(self, stream=None):
+        """make `stream` (default: current) wait until the plan's tensors are final"""
+        if self.ready is not None:
+            (stream or torch.cuda.current_stream(self.cost.device)).wait_event(self.ready)
+        return self
 
 
 def select_plan(cost: torch.Tensor, topk: int = 0, idx_base: int = 0):
@@ -123,10 +130,14 @@ class FusedPlanner:
         return cost, a0, sT
 
     # ---- K1 + K3 (+ refine) + gather: one C call for rollout and selection ------------------------------
-    def plan(self, e0, goal, noise, topk: int = 0, idx_base: int = 0, want_state=False, eps: float = 0.0) -> Plan:
+    def plan(self, e0, goal, noise, topk: int = 0, idx_base: int = 0, want_state=False, eps: float = 0.0,
+             refine_stream=None) -> Plan:
         """mpc_eval.py:124-165.  precision "f16+refine": all K candidates are scored single-pass, the 128 best
         estimates are re-rolled with split operands and the plan is chosen from those fp32-grade costs;
-        `Plan.verified[g]` tells whether that provably equals choosing from exact costs of all K."""
+        `Plan.verified[g]` tells whether that provably equals choosing from exact costs of all K.
+        `refine_stream`: run the (single-tile, latency-bound) refine half on that stream so it overlaps the
+        bulk half of the next plan; the returned Plan carries a `ready` event — call `plan.wait()` before
+        reading it from another stream."""
         if want_state:
             if self.precision == "f16+refine":
                 raise _lib.NdpError("want_state is not available with precision 'f16+refine'")
@@ -151,11 +162,31 @@ class FusedPlanner:
             n = C.c_size_t()
             check(lib().ndp_plan_workspace_bytes(self._h, G, K, topk, C.byref(n)))
             ws = torch.empty(max(n.value, 256), dtype=torch.uint8, device=dev)
-            with torch.cuda.device(dev):
-                check(lib().ndp_plan_select(self._h, ptr(e0c), ptr(gc), ptr(nz), G, K, topk, idx_base, eps, ptr(cost),
-                                            ptr(a0), ptr(packed), ptr(tk_idx), ptr(tk_cost), ptr(verified), ptr(ws),
-                                            ws.numel(), stream_ptr(dev)))
+            args = (self._h, ptr(e0c), ptr(gc), ptr(nz), G, K, topk, idx_base, eps, ptr(cost), ptr(a0), ptr(packed),
+                    ptr(tk_idx), ptr(tk_cost), ptr(verified), ptr(ws), ws.numel())
             sT = None
+            best_action = torch.zeros(G, 4, dtype=torch.float32, device=dev)
+            best_idx = torch.empty(G, dtype=torch.int32, device=dev)
+            if refine_stream is not None and self.precision == "f16+refine":
+                main = torch.cuda.current_stream(dev)
+                with torch.cuda.device(dev):
+                    check(lib().ndp_plan_select_bulk(*args, C.c_void_p(main.cuda_stream)))
+                    refine_stream.wait_stream(main)
+                    side = C.c_void_p(refine_stream.cuda_stream)
+                    check(lib().ndp_plan_select_refine(*args, side))
+                    check(lib().ndp_gather_best_action(ptr(a0), ptr(packed), G, K, idx_base, ptr(best_action),
+                                                       ptr(best_idx), side))
+                for t_ in (e0c, gc, nz, cost, a0, packed, tk_idx, tk_cost, verified, ws, best_action, best_idx):
+                    if t_ is not None:
+                        t_.record_stream(refine_stream)
+                ready = torch.cuda.Event()
+                ready.record(refine_stream)
+                return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified, ready)
+            with torch.cuda.device(dev):
+                check(lib().ndp_plan_select(*args, stream_ptr(dev)))
+                check(lib().ndp_gather_best_action(ptr(a0), ptr(packed), G, K, idx_base, ptr(best_action),
+                                                   ptr(best_idx), stream_ptr(dev)))
+            return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified)
         best_action = torch.zeros(G, 4, dtype=torch.float32, device=self.device)
         best_idx = torch.empty(G, dtype=torch.int32, device=self.device)
         with torch.cuda.device(self.device):
