@@ -181,8 +181,12 @@ def run_gpu(args):
         """`steps` plans back to back on device-resident inputs; one event pair around all of them"""
         a, b = ev(), ev()
         a.record()
-        plans = [plan_dev(pool[(first + i) % POOL]) for i in range(steps)]
-        for p_ in plans[-2:]:
+        plans = []
+        for i in range(steps):                    # plans are consumed (dropped) as a planning loop would
+            plans.append(plan_dev(pool[(first + i) % POOL]))
+            if len(plans) > 2:
+                plans.pop(0)
+        for p_ in plans:
             p_.wait()
         b.record()
         return a, b, plans

@@ -121,8 +121,9 @@ int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const fl
                     void* stream);
 /* The same call split in two stream-ordered halves with identical arguments, so that a caller may overlap the
  * (latency-bound, single-tile) refine half of plan i with the bulk half of plan i+1 on another stream:
- *   _bulk  : rollout of all K + selection of the refine list (the whole selection when not refining);
- *   _refine: re-roll + selection from refined costs + verification (no-op when not refining).
+ *   _bulk  : rollout of all K (+ the whole selection when not refining);
+ *   _refine: selection of the refine list, re-roll, selection from refined costs, verification (no-op when
+ *            not refining).
  * The caller orders _refine after _bulk (event) and keeps the workspace alive across both. */
 int ndp_plan_select_bulk(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
                          int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,

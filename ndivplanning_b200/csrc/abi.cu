@@ -328,8 +328,8 @@ extern "C" int ndp_plan_workspace_bytes(const ndp_planner* p, int G, int K, int 
   return NDP_OK;
 }
 
-// phase bit 0: bulk rollout (+ selection of the refine list, or the whole selection when not refining)
-// phase bit 1: refine pass + selection from refined costs + verification
+// phase bit 0: bulk rollout (+ the whole selection when not refining)
+// phase bit 1: selection of the refine list + refine pass + selection from refined costs + verification
 static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const float* goal, const float* noise, int G,
                             int K, int topk, int64_t idx_base, float eps, float* cost, float* a0,
                             uint64_t* packed_min, int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws,
@@ -363,10 +363,10 @@ static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const fl
                                    topk, 0.f, verified, s)) return rc;
       return NDP_OK;
     }
-    // the R best ESTIMATES per goal (local indices, ascending; -1 padded when K < R)
-    if (int rc = ndp_select(cost, G, K, R, 0, reinterpret_cast<uint64_t*>(pm_est), list, est, ws_sel, w.select, stream)) return rc;
   }
   if ((phase & 2) && p->tc_refine) {
+    // the R best ESTIMATES per goal (local indices, ascending; -1 padded when K < R)
+    if (int rc = ndp_select(cost, G, K, R, 0, reinterpret_cast<uint64_t*>(pm_est), list, est, ws_sel, w.select, stream)) return rc;
     // re-roll them with split operands; cost / a0 entries are overwritten, packed keys go to packed_c.
     // (the per-goal bias block is rebuilt in ws_roll: the bulk pass of THIS plan has finished with it)
     if (int rc = launch_rollout_tc(p->tc_refine, e0, goal, noise, G, K, p->d.T, cost, a0, nullptr, ws_roll, w.rollout, s,

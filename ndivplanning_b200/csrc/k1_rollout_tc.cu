@@ -84,7 +84,8 @@ __global__ void tc_goal_ext_kernel(const float* __restrict__ W1, const float* __
   const int C1 = 2 * E + nd;
   __half* hi = gext + (size_t)g * stride_halfs;
   __half* lo = with_lo ? hi + 128 * 16 : nullptr;
-  for (int n = threadIdx.x >> 5; n < 128; n += blockDim.x >> 5) {
+  {
+    const int n = blockIdx.y * (blockDim.x >> 5) + (threadIdx.x >> 5);   // one warp per output row
     float acc = 0.f;
     for (int e = lane; e < E; e += 32)
       acc = fmaf(__ldg(W1 + (size_t)n * C1 + E + e), __ldg(goal + (size_t)g * E + e), acc);
@@ -751,7 +752,7 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
   const size_t need = (size_t)G * P->gext_stride;
   if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
   NDP_CHECK_ARG(((uintptr_t)ws & 15) == 0, "rollout_score: workspace must be 16-byte aligned");
-  tc_goal_ext_kernel<<<G, 256, 0, s>>>(P->W1, P->b1, goal, 128, P->nd, P->np == 3, reinterpret_cast<__half*>(ws),
+  tc_goal_ext_kernel<<<dim3(G, 16), 256, 0, s>>>(P->W1, P->b1, goal, 128, P->nd, P->np == 3, reinterpret_cast<__half*>(ws),
                                         P->gext_stride / 2);
   NDP_LAUNCH_CHECK();
   TcParams tp;
