@@ -78,6 +78,27 @@ class ClockSampler(threading.Thread):
                 "samples": len(s)}
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """libraries (NCCL's version banner) print to fd 1; the contract is ONE JSON line on stdout.  Everything
+    written to fd 1 from now on goes to stderr; emit() writes the JSON line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, line)
+
+
 def l2_flusher(dev):
     buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # 256 MB > 126 MB L2
     return lambda: buf.fill_(1)
@@ -126,7 +147,7 @@ def run_reference(args):
                             "sample": f"{Ks} of {CFG['K']} candidates per step x T={CFG['T']}, oracle port of "
                                       f"mpc_eval.py:124-165 incl. python argmin, torch {torch.__version__} CPU fp32"},
            "e2e": {"value": v, "unit": "candidate-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out))
+    emit(out)
 
 
 # --------------------------------------------------------------------------------------------
@@ -158,7 +179,8 @@ def run_gpu(args):
     gen, fwd = synthetic.make_models(nd=nd, E=E, H=c["H"])
     planner = FusedPlanner(gen, fwd, horizon=T, device=dev, precision=prec)
     sharded = ShardedPlanner(planner) if world > 1 else None
-    side = torch.cuda.Stream(device=dev, priority=-1) if (prec == "f16+refine" and world == 1) else None
+    # steady-state loop object: pre-allocated plan slots, tails (refine / exchange / merge) on side streams
+    ring = sharded.ring(G, K_total, topk) if sharded else planner.ring(G, K, topk)
     e0_h, goal_h, _ = synthetic.make_plan_inputs(G, 1, 1, nd, E, seed=1)       # same goal on every rank
     g_ = torch.Generator().manual_seed(100 + rank)
     pool_h = [torch.rand(T, G, K, nd, generator=g_).pin_memory() for _ in range(POOL)]   # U[0,1) like the sampler
@@ -173,19 +195,17 @@ def run_gpu(args):
         torch.cuda.synchronize()
 
     def plan_dev(nz):
-        if sharded:
-            return sharded.plan(e0, goal, nz, K_total, topk=topk)
-        return planner.plan(e0, goal, nz, topk=topk, refine_stream=side)
+        return ring.plan(e0, goal, nz)
 
     def run_resident(steps, first):
         """`steps` plans back to back on device-resident inputs; one event pair around all of them"""
         a, b = ev(), ev()
         a.record()
         plans = []
-        for i in range(steps):                    # plans are consumed (dropped) as a planning loop would
+        for i in range(steps):
             plans.append(plan_dev(pool[(first + i) % POOL]))
-            if len(plans) > 2:
-                plans.pop(0)
+            if len(plans) > 2:                      # plan i-2 is consumed (read on this stream) before plan i+1 starts
+                plans.pop(0).wait()
         for p_ in plans:
             p_.wait()
         b.record()
@@ -202,8 +222,7 @@ def run_gpu(args):
         for i in range(steps):
             nz_d = pool_h[(first + i) % POOL].to(dev, non_blocking=True)
             e0_d = e0_h.to(dev, non_blocking=True); goal_d = goal_h.to(dev, non_blocking=True)
-            p_ = (sharded.plan(e0_d, goal_d, nz_d, K_total, topk=topk) if sharded
-                  else planner.plan(e0_d, goal_d, nz_d, topk=topk, refine_stream=side))
+            p_ = ring.plan(e0_d, goal_d, nz_d)
             if prev is not None:                       # results of the previous plan leave while this one runs
                 q, r = prev
                 q.wait()
@@ -241,8 +260,7 @@ def run_gpu(args):
                   "verified": got.verified.tolist(),
                   "cost_rel_err_selected_max": float(rel[0, sel].max()), "cost_rel_err_all_max": float(rel.max())}
         del exact
-    for i in range(args.warmup):
-        plan_dev(pool[i % POOL]).wait()
+    run_resident(args.warmup, POOL - args.warmup)      # warm-up runs the same pipelined loop as the timed region
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
@@ -325,9 +343,10 @@ def run_gpu(args):
                            l2="inputs rotate through a %d MB pool (> 126 MB L2); weights stay L2-resident by design"
                               % (POOL * T * G * K * nd * 4 >> 20),
                            precision=prec, weights="default-init sep30",
-                           step="one plan: rollout of all K + top-%d/argmin%s" % (
-                               topk, " + split-operand refine of the 128 best, pipelined on a side stream"
-                               if prec == "f16+refine" else ""),
+                           step="one plan: rollout of all K + top-%d/argmin%s%s" % (
+                               topk, " + split-operand refine of the 128 best" if prec == "f16+refine" else "",
+                               "; tails (refine/select/gather%s) of consecutive plans run on 2 side streams under the next "
+                               "bulk rollouts (PlanRing, 4 slots)" % (" + record all-gather + merge" if world > 1 else "")),
                            **{k: v for k, v in c.items() if k != "K"}),
             "e2e": {"value": units / (ms_e2e * 1e-3), "unit": "candidate-steps/s", "ms_per_step": ms_e2e,
                     "h2d_bytes_per_step": int(pool_h[0].numel() * 4 + e0_h.numel() * 4 + goal_h.numel() * 4),
@@ -353,7 +372,7 @@ def run_gpu(args):
             out["cpu_baseline"] = {"value": cu / min(times), "unit": "candidate-steps/s", "cores": threads, "kind": "port",
                                    "sample": f"8192 of {K} candidates x T={T}, best of 3 after 1 warm-up, oracle port of "
                                              f"mpc_eval.py:124-165 incl. python argmin scan; {time.perf_counter() - t0:.1f}s"}
-        print(json.dumps(out))
+        emit(out)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -367,6 +386,7 @@ if __name__ == "__main__":
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="f16+refine", choices=["fp32", "f16", "f16x2", "f16x3", "f16+refine"])
     a = ap.parse_args()
+    quiet_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:

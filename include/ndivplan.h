@@ -139,6 +139,20 @@ int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, i
                            int64_t idx_base, float* best_action, int32_t* best_idx,
                            void* stream);
 
+/* ---- sharded plan exchange (replaces nothing in the reference, which is single-device) ----
+ * A rank's local plan is packed into one record of (4 + topk) u64 words per goal:
+ *   [0] packed_min, [1..2] best_action (4 x f32 bits), [3] verified, [4..) top-k keys
+ *   (okey(cost)<<32 | GLOBAL index; missing entries all ones).
+ * The caller all-gathers the records (ONE collective per plan) into rec_all [P,G,4+topk] and
+ * ndp_shard_merge reduces them: unsigned min of [0] with lowest-rank tie break (ranks own increasing
+ * index ranges, so this is the reference's first-index rule, mpc_eval.py:159-164), the owner's action,
+ * AND of verified, and the global top-k under (cost, index).  P*topk <= 1024. */
+int ndp_shard_pack(const uint64_t* packed_min, const float* best_action, const int32_t* verified,
+                   const int32_t* topk_idx, const float* topk_cost, int G, int topk, uint64_t* rec,
+                   void* stream);
+int ndp_shard_merge(const uint64_t* rec_all, int P, int G, int topk, uint64_t* packed_min, int32_t* best_idx,
+                    float* best_action, int32_t* topk_idx, float* topk_cost, int32_t* verified, void* stream);
+
 /* ---- normalized diversification loss: replaces diversity.py:8-41 -----------------
  * x = recodes [N,k,Dx] (outputs), z = codes [N,k,Dz] (latents) — argument order of
  * compute_pairwise_divergence(recodes, codes), diversity.py:36.
@@ -167,6 +181,9 @@ int ndp_comm_allreduce_min_u64(ndp_comm* c, uint64_t* buf, int count, void* stre
 int ndp_comm_allreduce_sum_f32(ndp_comm* c, float* buf, int count, void* stream);
 int ndp_comm_allgather_f32(ndp_comm* c, const float* send, float* recv, int count_per_rank,
                            void* stream);
+/* rank-major all-gather of opaque bytes (the sharded plan's record exchange) */
+int ndp_comm_allgather_bytes(ndp_comm* c, const void* send, void* recv, size_t bytes_per_rank,
+                             void* stream);
 void ndp_comm_destroy(ndp_comm* c);
 
 /* number of kernels this library has launched in this process (bench gpu_launches) */

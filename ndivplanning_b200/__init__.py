@@ -9,7 +9,7 @@ from . import diversity  # noqa: F401
 from ._lib import LIB_PATH, NdpError, launch_count  # noqa: F401
 from .models import GeneratorMLP, LatentForward  # noqa: F401
 from .mpc_eval import fetch_push_control_evaluation, sample_noise  # noqa: F401
-from .planner import FusedPlanner, Plan, select_plan, unpack_index  # noqa: F401
+from .planner import FusedPlanner, Plan, PlanRing, select_plan, unpack_index  # noqa: F401
 
-__all__ = ["diversity", "FusedPlanner", "Plan", "select_plan", "unpack_index", "GeneratorMLP", "LatentForward",
+__all__ = ["diversity", "FusedPlanner", "Plan", "PlanRing", "select_plan", "unpack_index", "GeneratorMLP", "LatentForward",
            "fetch_push_control_evaluation", "sample_noise", "NdpError", "launch_count", "LIB_PATH"]

@@ -41,6 +41,8 @@ _PROTOS = {
     "ndp_plan_select_bulk": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_select_refine": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_gather_best_action": (_i, [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),
+    "ndp_shard_pack": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
+    "ndp_shard_merge": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ndp_ndiv_workspace_bytes": (_i, [_i, _i, C.POINTER(_sz)]),
     "ndp_ndiv_rowsums": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp]),
     "ndp_ndiv_loss_grad": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _vp, _vp, _sz, _vp]),
@@ -51,6 +53,7 @@ _PROTOS = {
     "ndp_comm_allreduce_min_u64": (_i, [_vp, _vp, _i, _vp]),
     "ndp_comm_allreduce_sum_f32": (_i, [_vp, _vp, _i, _vp]),
     "ndp_comm_allgather_f32": (_i, [_vp, _vp, _vp, _i, _vp]),
+    "ndp_comm_allgather_bytes": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "ndp_comm_destroy": (None, [_vp]),
 }
 EXPORTED_SYMBOLS = tuple(_PROTOS)

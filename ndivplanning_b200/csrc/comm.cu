@@ -13,7 +13,7 @@ typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 enum { ncclSuccess_ = 0 };
 // values from nccl.h (stable across NCCL 2.x)
-enum { kNcclUint64 = 5, kNcclFloat32 = 7 };
+enum { kNcclInt8 = 0, kNcclUint64 = 5, kNcclFloat32 = 7 };
 enum { kNcclSum = 0, kNcclMin = 3 };
 
 struct NcclApi {
@@ -120,6 +120,16 @@ extern "C" int ndp_comm_allgather_f32(ndp_comm* c, const float* send, float* rec
   NcclApi* api = nccl();
   if (!api) return NDP_ERR_NCCL;
   NDP_NCCL(api->AllGather(send, recv, (size_t)count_per_rank, kNcclFloat32, c->comm, (cudaStream_t)stream));
+  count_launch();
+  return NDP_OK;
+}
+
+extern "C" int ndp_comm_allgather_bytes(ndp_comm* c, const void* send, void* recv, size_t bytes_per_rank,
+                                        void* stream) {
+  NDP_CHECK_ARG(c && send && recv, "allgather_bytes: bad arguments");
+  NcclApi* api = nccl();
+  if (!api) return NDP_ERR_NCCL;
+  NDP_NCCL(api->AllGather(send, recv, bytes_per_rank, kNcclInt8, c->comm, (cudaStream_t)stream));
   count_launch();
   return NDP_OK;
 }

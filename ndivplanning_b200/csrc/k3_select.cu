@@ -277,6 +277,110 @@ int verify_refine(const float* est_topR, const float* exact_topk, const unsigned
 }
 }  // namespace ndp
 
+// ---------------------------------------------------------------- sharded plan: record exchange
+// One u64 record per goal and rank = everything the other ranks need from a local plan
+// (SURVEY 8e): [0] packed argmin key, [1..2] the local winner's action (4 x f32), [3] verified,
+// [4..4+topk) packed top-k keys (global indices; missing entries = all ones).  A single
+// all-gather of these records replaces min-allreduce + action broadcast + two top-k gathers.
+namespace ndp {
+__global__ void shard_pack_kernel(const unsigned long long* __restrict__ packed_min, const float* __restrict__ best_action,
+                                  const int* __restrict__ verified, const int* __restrict__ topk_idx,
+                                  const float* __restrict__ topk_cost, int G, int topk,
+                                  unsigned long long* __restrict__ rec) {
+  const int W = 4 + topk;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= G * W) return;
+  const int g = t / W, w = t % W;
+  unsigned long long v;
+  if (w == 0) v = packed_min[g];
+  else if (w <= 2) {
+    const float a = best_action[(size_t)g * 4 + (w - 1) * 2], b = best_action[(size_t)g * 4 + (w - 1) * 2 + 1];
+    v = (unsigned long long)__float_as_uint(a) | ((unsigned long long)__float_as_uint(b) << 32);
+  } else if (w == 3) v = verified ? (unsigned long long)(unsigned)verified[g] : 1ull;
+  else {
+    const int i = topk_idx[(size_t)g * topk + w - 4];
+    v = i < 0 ? kPadKey : (((unsigned long long)ordered_key(topk_cost[(size_t)g * topk + w - 4]) << 32) | (unsigned)i);
+  }
+  rec[t] = v;
+}
+
+// rec [P,G,4+topk] -> the global plan.  One block per goal; P*topk <= 1024 keys ranked by counting
+// (keys are distinct: indices are global), pad keys rank last in position order.
+__global__ void __launch_bounds__(kSelThreads)
+shard_merge_kernel(const unsigned long long* __restrict__ rec, int P, int G, int topk,
+                   unsigned long long* __restrict__ packed_min, int* __restrict__ best_idx,
+                   float* __restrict__ best_action, int* __restrict__ topk_idx, float* __restrict__ topk_cost,
+                   int* __restrict__ verified) {
+  __shared__ unsigned long long keys[kSelTile];
+  const int g = blockIdx.x, W = 4 + topk, n = P * topk;
+  for (int i = threadIdx.x; i < n; i += kSelThreads)
+    keys[i] = rec[((size_t)(i / topk) * G + g) * W + 4 + i % topk];
+  if (threadIdx.x == 0) {
+    unsigned long long m = kPadKey;
+    int owner = 0, ok = 1;
+    for (int r = 0; r < P; ++r) {                        // strict '<': lowest rank == lowest index range wins ties
+      const unsigned long long* q = rec + ((size_t)r * G + g) * W;
+      if (q[0] < m) { m = q[0]; owner = r; }
+      ok &= (int)(q[3] & 1ull);
+    }
+    if (m == kInvalidPacked) owner = 0;                  // nothing valid anywhere: global index 0 (mpc_eval.py:122,159)
+    const unsigned long long* q = rec + ((size_t)owner * G + g) * W;
+    packed_min[g] = m;
+    if (best_idx) best_idx[g] = (m == kInvalidPacked) ? 0 : (int)(m & 0xFFFFFFFFull);
+    if (best_action) {
+      best_action[(size_t)g * 4 + 0] = __uint_as_float((unsigned)(q[1] & 0xFFFFFFFFull));
+      best_action[(size_t)g * 4 + 1] = __uint_as_float((unsigned)(q[1] >> 32));
+      best_action[(size_t)g * 4 + 2] = __uint_as_float((unsigned)(q[2] & 0xFFFFFFFFull));
+      best_action[(size_t)g * 4 + 3] = __uint_as_float((unsigned)(q[2] >> 32));
+    }
+    if (verified) verified[g] = ok;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += kSelThreads) {
+    const unsigned long long v = keys[i];
+    int r = 0;
+    for (int j = 0; j < n; ++j) {
+      const unsigned long long u = keys[j];
+      r += (u < v) || (u == v && j < i);
+    }
+    if (r < topk) {
+      topk_idx[(size_t)g * topk + r] = (v == kPadKey) ? -1 : (int)(v & 0xFFFFFFFFull);
+      topk_cost[(size_t)g * topk + r] = (v == kPadKey) ? __int_as_float(0x7fc00000) : key_to_float((uint32_t)(v >> 32));
+    }
+  }
+}
+}  // namespace ndp
+
+extern "C" int ndp_shard_pack(const uint64_t* packed_min, const float* best_action, const int32_t* verified,
+                              const int32_t* topk_idx, const float* topk_cost, int G, int topk, uint64_t* rec,
+                              void* stream) {
+  NDP_CHECK_ARG(G >= 0 && topk >= 0 && topk <= 128, "shard_pack: bad G/topk");
+  if (int rc = device_check()) return rc;
+  if (G == 0) return NDP_OK;
+  NDP_CHECK_ARG(packed_min && best_action && rec && (topk == 0 || (topk_idx && topk_cost)), "shard_pack: null pointer");
+  const int n = G * (4 + topk);
+  shard_pack_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const unsigned long long*>(packed_min), best_action, verified, topk_idx, topk_cost, G, topk,
+      reinterpret_cast<unsigned long long*>(rec));
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+extern "C" int ndp_shard_merge(const uint64_t* rec, int P, int G, int topk, uint64_t* packed_min, int32_t* best_idx,
+                               float* best_action, int32_t* topk_idx, float* topk_cost, int32_t* verified,
+                               void* stream) {
+  NDP_CHECK_ARG(P >= 1 && G >= 0 && topk >= 0 && topk <= 128 && (long long)P * topk <= kSelTile,
+                "shard_merge: need P*topk <= 1024 (P=%d topk=%d)", P, topk);
+  if (int rc = device_check()) return rc;
+  if (G == 0) return NDP_OK;
+  NDP_CHECK_ARG(rec && packed_min && (topk == 0 || (topk_idx && topk_cost)), "shard_merge: null pointer");
+  shard_merge_kernel<<<G, kSelThreads, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const unsigned long long*>(rec), P, G, topk, reinterpret_cast<unsigned long long*>(packed_min),
+      best_idx, best_action, topk_idx, topk_cost, verified);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
 extern "C" int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,
                                       int64_t idx_base, float* best_action, int32_t* best_idx, void* stream) {
   NDP_CHECK_ARG(G >= 0 && packed_min, "gather: bad args");

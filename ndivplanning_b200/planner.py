@@ -194,6 +194,11 @@ class FusedPlanner:
                                                ptr(best_idx), stream_ptr(self.device)))
         return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified)
 
+    def ring(self, G: int, K: int, topk: int = 0, depth: int = 4, n_streams: int = 2, idx_base: int = 0,
+             comm=None) -> "PlanRing":
+        """pre-allocated plan slots + side streams for a steady planning loop (see PlanRing)"""
+        return PlanRing(self, G, K, topk, depth, n_streams, idx_base, comm)
+
     # ---- single-call module semantics (drop-in for generator(z) / fwd_model(state, a)) -------
     def generator(self, z):
         """models/gan.py:79-86 — z [B, 2E+nd] -> actions [B,4]."""
@@ -212,3 +217,101 @@ class FusedPlanner:
         with torch.cuda.device(self.device):
             check(lib().ndp_forward_step(self._h, ptr(sc), ptr(ac), sc.shape[0], ptr(out), stream_ptr(self.device)))
         return out.view(state.shape)
+
+
+class _Slot:
+    __slots__ = ("cost", "a0", "packed", "tk_idx", "tk_cost", "verified", "ws", "best_action", "best_idx", "ready",
+                 "bulk_done", "inputs", "used", "tail", "gather", "plan", "rec", "rec_all", "pack", "merge")
+
+
+class PlanRing:
+    """Steady-state planning loop without per-plan allocations or host stalls.
+
+    `depth` slots hold every output and workspace of a plan; plan i writes slot i % depth.  The bulk
+    rollout runs on the caller's stream, everything after it (refine list selection, split-operand
+    re-roll, selection, verification, action gather and — when `comm` is given — the sharded record
+    exchange and merge) on side stream i % n_streams, so the latency-bound tails of two consecutive
+    plans overlap each other and the next bulk rollouts.  A returned Plan is valid until `depth - 1`
+    further plans have been issued on the ring; `plan.wait()` orders the current stream after it.
+    Reusing a slot makes the caller's stream wait (on the device) for the slot's previous tail."""
+
+    def __init__(self, planner: FusedPlanner, G: int, K: int, topk: int = 0, depth: int = 4, n_streams: int = 2,
+                 idx_base: int = 0, comm=None):
+        dev = planner.device
+        self.planner, self.G, self.K, self.topk, self.depth, self.idx_base, self.comm = \
+            planner, G, K, topk, depth, idx_base, comm
+        self.count = 0
+        self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(n_streams)]
+        n = C.c_size_t()
+        check(lib().ndp_plan_workspace_bytes(planner._h, G, K, topk, C.byref(n)))
+        world = comm.world if comm is not None else 1
+        if world * topk > 1024:
+            raise _lib.NdpError("sharded top-k needs world*topk <= 1024")
+        self.slots = []
+        f32, i32, i64 = torch.float32, torch.int32, torch.int64
+        for _ in range(depth):
+            s = _Slot()
+            s.cost = torch.empty(G, K, dtype=f32, device=dev)
+            s.a0 = torch.empty(G, K, 4, dtype=f32, device=dev)
+            s.packed = torch.empty(G, dtype=i64, device=dev)
+            s.tk_idx = torch.empty(G, topk, dtype=i32, device=dev) if topk else None
+            s.tk_cost = torch.empty(G, topk, dtype=f32, device=dev) if topk else None
+            s.verified = torch.empty(G, dtype=i32, device=dev)
+            s.ws = torch.empty(max(n.value, 256), dtype=torch.uint8, device=dev)
+            s.best_action = torch.zeros(G, 4, dtype=f32, device=dev)
+            s.best_idx = torch.empty(G, dtype=i32, device=dev)
+            s.ready, s.bulk_done, s.inputs, s.used = torch.cuda.Event(), torch.cuda.Event(), None, False
+            s.tail = (G, K, topk, idx_base, 0.0, ptr(s.cost), ptr(s.a0), ptr(s.packed), ptr(s.tk_idx), ptr(s.tk_cost),
+                      ptr(s.verified), ptr(s.ws), s.ws.numel())
+            s.gather = (ptr(s.a0), ptr(s.packed), G, K, idx_base, ptr(s.best_action), ptr(s.best_idx))
+            if comm is None:
+                s.plan = Plan(s.best_idx, s.best_action, s.packed, s.cost, s.a0, s.tk_idx, s.tk_cost, None, s.verified,
+                              s.ready)
+            else:
+                W = 4 + topk
+                s.rec = torch.empty(G, W, dtype=i64, device=dev)
+                s.rec_all = torch.empty(world, G, W, dtype=i64, device=dev)
+                g_packed, g_idx = torch.empty(G, dtype=i64, device=dev), torch.empty(G, dtype=i32, device=dev)
+                g_act, g_ver = torch.empty(G, 4, dtype=f32, device=dev), torch.empty(G, dtype=i32, device=dev)
+                g_tki = torch.empty(G, topk, dtype=i32, device=dev) if topk else None
+                g_tkc = torch.empty(G, topk, dtype=f32, device=dev) if topk else None
+                s.pack = (ptr(s.packed), ptr(s.best_action), ptr(s.verified), ptr(s.tk_idx), ptr(s.tk_cost), G, topk,
+                          ptr(s.rec))
+                s.merge = (ptr(s.rec_all), world, G, topk, ptr(g_packed), ptr(g_idx), ptr(g_act), ptr(g_tki),
+                           ptr(g_tkc), ptr(g_ver))
+                s.plan = Plan(g_idx, g_act, g_packed, s.cost, s.a0, g_tki, g_tkc, None, g_ver, s.ready)
+            self.slots.append(s)
+
+    def plan(self, e0, goal, noise) -> Plan:
+        """mpc_eval.py:124-165 for e0, goal [G,E] and noise [T,G,K,nd]; returns the slot's Plan (see class doc)"""
+        pl = self.planner
+        require_cuda(e0, goal, noise)
+        e0c, gc, nz = f32c(e0), f32c(goal), f32c(noise)
+        if tuple(nz.shape) != (pl.T, self.G, self.K, pl.nd) or tuple(e0c.shape) != (self.G, pl.E) \
+                or tuple(gc.shape) != (self.G, pl.E):
+            raise _lib.NdpError(f"shape mismatch: noise {tuple(nz.shape)} e0 {tuple(e0c.shape)} for ring "
+                                f"T={pl.T} G={self.G} K={self.K} nd={pl.nd} E={pl.E}")
+        i = self.count
+        self.count = i + 1
+        s = self.slots[i % self.depth]
+        side = self.streams[i % len(self.streams)]
+        dev = pl.device
+        main = torch.cuda.current_stream(dev)
+        if s.used:
+            main.wait_event(s.ready)          # the slot's previous tail (and its readers on the side streams) is done
+        s.inputs, s.used = (e0c, gc, nz), True   # keep the inputs alive until the slot is reused
+        L = lib()
+        head = (pl._h, e0c.data_ptr(), gc.data_ptr(), nz.data_ptr())
+        sp = C.c_void_p(side.cuda_stream)
+        with torch.cuda.device(dev):
+            check(L.ndp_plan_select_bulk(*head, *s.tail, C.c_void_p(main.cuda_stream)))
+            s.bulk_done.record(main)
+            side.wait_event(s.bulk_done)
+            check(L.ndp_plan_select_refine(*head, *s.tail, sp))
+            check(L.ndp_gather_best_action(*s.gather, sp))
+            if self.comm is not None:
+                check(L.ndp_shard_pack(*s.pack, sp))
+                check(L.ndp_comm_allgather_bytes(self.comm._h, ptr(s.rec), ptr(s.rec_all), s.rec.numel() * 8, sp))
+                check(L.ndp_shard_merge(*s.merge, sp))
+            s.ready.record(side)
+        return s.plan

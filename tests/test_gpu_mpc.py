@@ -239,3 +239,35 @@ def test_refined_plan_matches_oracle(cuda, G, K, T, H, topk):
         order = np.argsort(c64, kind="stable")
         if (c64[order[1]] - c64[order[0]]) / c64[order[0]] > 8 * 2e-5:
             assert best == int(exact.best_idx[g])
+
+
+@pytest.mark.parametrize("prec,G,K,T,topk", [("f16+refine", 1, 4096, 4, 16), ("fp32", 2, 300, 3, 4), ("f16x3", 1, 1000, 2, 0)])
+def test_plan_ring_equals_plain_plan(cuda, prec, G, K, T, topk):
+    """PlanRing (pre-allocated slots, tails on two side streams) must return exactly what FusedPlanner.plan
+    returns, for more plans than the ring has slots (slot reuse) and with results read late."""
+    from ndivplanning_b200 import FusedPlanner
+    gen, fwd = synthetic.make_models(nd=2, E=128, H=256)
+    pl = FusedPlanner(gen, fwd, horizon=T, precision=prec)
+    ring = pl.ring(G, K, topk, depth=3)
+    inputs = [synthetic.make_plan_inputs(G, K, T, 2, 128, seed=20 + i) for i in range(7)]
+    inputs = [tuple(t.cuda() for t in x) for x in inputs]
+    got = []
+    for i, (e0, goal, noise) in enumerate(inputs):
+        p = ring.plan(e0, goal, noise)
+        if i >= 1:                                   # read plan i-1 only after plan i has been issued
+            q = got[-1][0].wait()
+            got[-1] = tuple(t.clone() if t is not None else None for t in (q.best_idx, q.best_action, q.packed_min,
+                                                                           q.topk_idx, q.topk_cost, q.verified, q.cost))
+        got.append((p,))
+    q = got[-1][0].wait()
+    got[-1] = tuple(t.clone() if t is not None else None for t in (q.best_idx, q.best_action, q.packed_min, q.topk_idx,
+                                                                   q.topk_cost, q.verified, q.cost))
+    for (e0, goal, noise), g in zip(inputs, got):
+        w = pl.plan(e0, goal, noise, topk=topk)
+        want = (w.best_idx, w.best_action, w.packed_min, w.topk_idx, w.topk_cost, w.verified, w.cost)
+        for a, b in zip(g, want):
+            assert (a is None) == (b is None)
+            if a is not None:
+                assert torch.equal(a, b)
+    with pytest.raises(Exception):
+        ring.plan(inputs[0][0], inputs[0][1], inputs[0][2][:, :, : K - 1])

@@ -58,3 +58,45 @@ def test_select_empty_segments(cuda):
     assert [int(v) & 0xFFFFFFFFFFFFFFFF for v in packed.tolist()] == [0xFFFFFFFF00000000] * 2
     packed, _, _ = select_plan(torch.empty(0, 5, device="cuda"), 0)
     assert packed.numel() == 0
+
+
+@pytest.mark.parametrize("P,G,K,topk", [(2, 3, 1001, 8), (8, 2, 4096, 16), (4, 5, 64, 0), (8, 1, 40, 128), (3, 4, 7, 16)])
+def test_shard_records_merge_equals_global_selection(cuda, P, G, K, topk):
+    """P emulated ranks on one GPU: local K3 per shard -> ndp_shard_pack -> stacked records ->
+    ndp_shard_merge must equal the reference scan / stable top-k over ALL K candidates
+    (mpc_eval.py:159-165), incl. cross-rank ties, an all-NaN goal and short shards (K/P < topk)."""
+    from ndivplanning_b200 import select_plan
+    from ndivplanning_b200.planner import Plan
+    from ndivplanning_b200.sharded import merge_records, pack_records, shard_range
+    torch.manual_seed(P * 100 + K)
+    cost = torch.rand(G, K)
+    if G > 1:
+        cost[1, :] = float("nan")
+    if G > 2:
+        cost[2, 1] = cost[2, K - 2] = -1.0
+    a0 = torch.randn(G, K, 4)
+    recs = []
+    for r in range(P):
+        start, count = shard_range(K, r, P)
+        loc = cost[:, start:start + count].contiguous().cuda()
+        packed, tk_idx, tk_cost = select_plan(loc, topk, start)
+        li = ((packed & 0xFFFFFFFF) - start).clamp(0, max(count - 1, 0))
+        li = torch.where(packed == -0x100000000, torch.zeros_like(li), li)
+        act = a0[:, start:start + count].cuda()[torch.arange(G), li] if count else torch.zeros(G, 4).cuda()
+        ver = torch.full((G,), 1 if r != 1 else 0, dtype=torch.int32).cuda()
+        recs.append(pack_records(Plan(None, act.contiguous(), packed, loc, None, tk_idx, tk_cost, None, ver), topk))
+    packed, best_idx, best_action, tk_idx, tk_cost, verified = merge_records(torch.stack(recs).contiguous(), topk)
+    for g in range(G):
+        valid = bool((cost[g] < 1e10).any())
+        want = O.select_first_min(cost[g]) if valid else 0
+        assert int(best_idx[g]) == want
+        if valid:
+            assert (int(packed[g].item()) & 0xFFFFFFFFFFFFFFFF) == O.pack_key(float(cost[g, want]), want)
+        assert torch.equal(best_action[g].cpu(), a0[g, want])
+        if topk:
+            kk = min(topk, K)
+            wt = O.select_topk(cost[g], kk)
+            assert tk_idx[g, :kk].cpu().tolist() == wt.tolist()
+            assert torch.equal(torch.nan_to_num(tk_cost[g, :kk].cpu(), nan=-7.0), torch.nan_to_num(cost[g][wt], nan=-7.0))
+            assert (tk_idx[g, kk:] == -1).all()
+    assert verified.cpu().tolist() == [0 if P > 1 else 1] * G

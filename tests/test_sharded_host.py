@@ -49,6 +49,13 @@ def _worker(rank, world, port, K, topk):
                             select=lambda c, k: torch.sort(c, dim=1, stable=True).indices[:, :k])
         for g in (0, 2):
             assert mi[g].tolist() == O.select_topk(cost[g], topk).tolist()
+        # the product's single collective: all-gather of per-rank records, rank-major
+        from ndivplanning_b200.sharded import exchange_records
+        rec = torch.full((3, 4 + topk), rank, dtype=torch.int64) + torch.arange(4 + topk)
+        allrec = exchange_records(rec)
+        assert allrec.shape == (world, 3, 4 + topk)
+        for r in range(world):
+            assert torch.equal(allrec[r], torch.full((3, 4 + topk), r, dtype=torch.int64) + torch.arange(4 + topk))
     finally:
         dist.destroy_process_group()
 

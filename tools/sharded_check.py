@@ -1,0 +1,73 @@
+"""Multi-GPU parity check (run under torch.distributed.run, one rank per GPU, NCCL):
+the candidate-sharded plan over K_total must equal the single-GPU plan over the same K_total,
+and the row-sharded ndiv loss/grad must equal the single-GPU one.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+        --master-port 29511 tools/sharded_check.py
+"""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from ndivplanning_b200 import FusedPlanner, diversity, synthetic  # noqa: E402
+from ndivplanning_b200.sharded import ShardedPlanner, shard_range, sharded_ndiv_loss  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    ok = True
+    for prec, G, K, T, topk in (("fp32", 2, 4096, 4, 8), ("f16+refine", 1, 16384, 8, 16), ("f16x3", 3, 2000, 3, 0)):
+        gen, fwd = synthetic.make_models(nd=2, E=128, H=256)
+        e0, goal, noise = synthetic.make_plan_inputs(G, K, T, 2, 128, seed=5)
+        pl = FusedPlanner(gen, fwd, horizon=T, device=dev, precision=prec)
+        full = pl.plan(e0.to(dev), goal.to(dev), noise.to(dev), topk=topk)
+        start, count = shard_range(K, rank, world)
+        side = torch.cuda.Stream(device=dev) if prec == "f16+refine" else None
+        sp = ShardedPlanner(pl).plan(e0.to(dev), goal.to(dev), noise[:, :, start:start + count].contiguous().to(dev),
+                                     K, topk=topk, refine_stream=side).wait()
+        torch.cuda.synchronize()
+        ring = ShardedPlanner(pl).ring(G, K, topk, depth=2)
+        for _ in range(3):                          # allocation-free ring path, with slot reuse
+            rp = ring.plan(e0.to(dev), goal.to(dev), noise[:, :, start:start + count].contiguous().to(dev))
+        rp.wait()
+        torch.cuda.synchronize()
+        ring_same = torch.equal(rp.best_idx, full.best_idx) and torch.equal(rp.best_action, full.best_action) \
+            and torch.equal(rp.packed_min, full.packed_min) and torch.equal(rp.verified, sp.verified)
+        if topk:
+            ring_same = ring_same and torch.equal(rp.topk_idx, full.topk_idx) and torch.equal(rp.topk_cost, full.topk_cost)
+        ok &= ring_same
+        same = ring_same and torch.equal(sp.best_idx, full.best_idx) and torch.equal(sp.best_action, full.best_action) \
+            and torch.equal(sp.packed_min, full.packed_min)
+        if topk:
+            same = same and torch.equal(sp.topk_idx, full.topk_idx) and torch.equal(sp.topk_cost, full.topk_cost)
+        print(f"[rank {rank}] {prec} G={G} K={K} topk={topk}: sharded==single {same} best={sp.best_idx.tolist()} "
+              f"verified={sp.verified.tolist()}", flush=True)
+        ok &= same
+    x, z = synthetic.make_ndiv_inputs(2, 1000, 32, 16)
+    xg = x.to(dev).requires_grad_(True)
+    loss = diversity.compute_pairwise_divergence(xg, z.to(dev))
+    loss.backward()
+    sl, sg = sharded_ndiv_loss(x.to(dev), z.to(dev))
+    torch.cuda.synchronize()
+    lerr = abs(sl.item() - loss.item()) / abs(loss.item())
+    gerr = (sg - xg.grad).abs().max().item() / xg.grad.abs().max().item()
+    print(f"[rank {rank}] ndiv sharded vs single: loss rel {lerr:.2e} grad rel {gerr:.2e}", flush=True)
+    ok &= lerr < 1e-5 and gerr < 1e-5
+    t = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    dist.barrier()
+    dist.destroy_process_group()
+    if not int(t):
+        sys.exit(1)
+    if rank == 0:
+        print("sharded_check ok")
+
+
+if __name__ == "__main__":
+    main()
