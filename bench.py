@@ -214,15 +214,30 @@ def run_gpu(args):
     res_h = [{"idx": torch.empty(G, dtype=torch.int32).pin_memory(), "act": torch.empty(G, 4).pin_memory(),
               "key": torch.empty(G, dtype=torch.int64).pin_memory()} for _ in range(2)]
 
+    copy_stream = torch.cuda.Stream(device=dev)
+    in_d = [{"nz": torch.empty(T, G, K, nd, device=dev), "e0": torch.empty(G, E, device=dev),
+             "goal": torch.empty(G, E, device=dev), "up": torch.cuda.Event(), "free": torch.cuda.Event()}
+            for _ in range(3)]
+
     def run_e2e(steps, first):
-        """host buffers in, host results out, every step: H2D of the step's noise/e0/goal, plan, D2H of the plan"""
+        """host buffers in, host results out, every step: H2D of the step's noise/e0/goal from pinned memory
+        (copy stream, triple-buffered so it overlaps the previous plan's rollout), plan, D2H of the plan"""
         a, b = ev(), ev()
+        main = torch.cuda.current_stream(dev)
         a.record()
+        copy_stream.wait_stream(main)
         prev = None
         for i in range(steps):
-            nz_d = pool_h[(first + i) % POOL].to(dev, non_blocking=True)
-            e0_d = e0_h.to(dev, non_blocking=True); goal_d = goal_h.to(dev, non_blocking=True)
-            p_ = ring.plan(e0_d, goal_d, nz_d)
+            d = in_d[i % 3]
+            with torch.cuda.stream(copy_stream):
+                if i >= 3:
+                    copy_stream.wait_event(d["free"])          # the plan that read this buffer has finished
+                d["nz"].copy_(pool_h[(first + i) % POOL], non_blocking=True)
+                d["e0"].copy_(e0_h, non_blocking=True); d["goal"].copy_(goal_h, non_blocking=True)
+                d["up"].record(copy_stream)
+            main.wait_event(d["up"])
+            p_ = ring.plan(d["e0"], d["goal"], d["nz"])
+            d["free"] = p_.ready
             if prev is not None:                       # results of the previous plan leave while this one runs
                 q, r = prev
                 q.wait()
@@ -240,6 +255,7 @@ def run_gpu(args):
         pairs = []
         for i in range(steps):
             flush()
+            torch.cuda._sleep(600_000)                 # ~0.3 ms: the host enqueues the launch before `a` is reached
             a, b = ev(), ev()
             a.record(); pl.rollout_score(e0, goal, pool[i % POOL]); b.record()
             pairs.append((a, b))

@@ -159,10 +159,11 @@ int ndp_shard_merge(const uint64_t* rec_all, int P, int G, int topk, uint64_t* p
  * loss[0] = sum relu(margin * dz_ij/sz_i - dx_ij/sx_i); sx,sz [N,k] row sums (detached
  * normalisers, diversity.py:17-18). grad_x (nullable) = d loss / d x for grad_loss = 1.
  * Row-block sharding (multi-GPU): rows [row0,row0+rows) of every group are owned by the
- * caller; sx/sz must hold ALL rows before ndp_ndiv_loss_grad (allgather in between). */
-int ndp_ndiv_workspace_bytes(int N, int k, size_t* bytes);
+ * caller; sx/sz must hold ALL rows before ndp_ndiv_loss_grad (allgather in between).
+ * ws: ndp_ndiv_workspace_bytes() bytes, used by both passes (partial sums of the column splits). */
+int ndp_ndiv_workspace_bytes(int N, int k, int Dx, size_t* bytes);
 int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz,
-                     int row0, int rows, float* sx, float* sz, void* stream);
+                     int row0, int rows, float* sx, float* sz, void* ws, size_t ws_bytes, void* stream);
 int ndp_ndiv_loss_grad(const float* x, const float* z, const float* sx, const float* sz,
                        int N, int k, int Dx, int Dz, float margin, int row0, int rows,
                        float* loss, float* grad_x, void* ws, size_t ws_bytes, void* stream);

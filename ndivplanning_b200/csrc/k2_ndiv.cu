@@ -6,64 +6,32 @@
 //   L     = sum relu(0.8 * delta^z_ij - delta^x_ij) compute_pairwise_divergence :36-41
 //   dL/dx_i = sum_j What_ij (x_i - x_j),  What_ij = -(M_ij/sx_i + M_ji/sx_j) / dx_ij  (0 if dx_ij==0)
 //
-// Arithmetic is the reference's own (direct differences, fp32, IEEE sqrt/div) so parity
-// does not depend on a Gram-form cancellation.  Two passes over the pair tiles:
+// Arithmetic is the reference's own (direct differences, fp32, IEEE sqrt) so parity does not depend on
+// a Gram-form cancellation: the loss exists to separate NEAR-DUPLICATE outputs, exactly the regime where
+// |a|^2+|b|^2-2ab loses all digits.  Two passes over the pair tiles:
 //   pass 1  row sums sx, sz                          (ndp_ndiv_rowsums)
 //   pass 2  loss partials + What tile + What*X GEMM  (ndp_ndiv_loss_grad)
-// A block owns 32 complete rows and sweeps all j in 128-wide tiles -> no atomics,
-// deterministic sums.  Algorithmic HBM bytes: 4*N*k*(Dz+2*Dx) + 8*N*k.
+// 64 x 128 pair tiles, 4x4 register sub-tiles, every feature of a tile staged once in shared memory
+// (transposed, conflict-free), gradient product register-tiled 4 rows x 8 dims x 32 j per thread.
+// Algorithmic HBM bytes: 4*N*k*(Dz+2*Dx) + 8*N*k (nothing k x k ever leaves the SM).
 #include "common.cuh"
 
 namespace ndp {
 
-static constexpr int kTI = 32;        // rows per block
-static constexpr int kTJ = 128;       // cols per tile
-static constexpr int kDC = 16;        // feature chunk staged in smem
-static constexpr int kNdivThreads = 256;
-static constexpr int kPadI = kTI + 4;
-static constexpr int kPadJ = kTJ + 4;
-
-// stage v[rows r0..r0+R) x dims d0..d0+kDC) transposed into s[d][r] (zero padded)
-template <int R, int PAD>
-__device__ __forceinline__ void stage_chunk(float* s, const float* __restrict__ v, int k, int D,
-                                            int r0, int d0) {
-  for (int t = threadIdx.x; t < R * kDC; t += kNdivThreads) {
-    int r = t / kDC, d = t % kDC;
-    float val = 0.f;
-    if (r0 + r < k && d0 + d < D) val = __ldg(v + (size_t)(r0 + r) * D + d0 + d);
-    s[d * PAD + r] = val;
-  }
-}
-
-// accumulate squared distances of the 4x4 pair sub-tile owned by this thread
-__device__ __forceinline__ void sqdist_tile(float (&acc)[4][4], const float* __restrict__ vg, int k, int D,
-                                            int i0, int j0, float* s_i, float* s_j) {
-  const int ty = threadIdx.x >> 5, tx = threadIdx.x & 31;
-#pragma unroll
-  for (int a = 0; a < 4; ++a)
-#pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
-  for (int d0 = 0; d0 < D; d0 += kDC) {
-    __syncthreads();
-    stage_chunk<kTI, kPadI>(s_i, vg, k, D, i0, d0);
-    stage_chunk<kTJ, kPadJ>(s_j, vg, k, D, j0, d0);
-    __syncthreads();
-    const int dn = (D - d0) < kDC ? (D - d0) : kDC;
-    for (int d = 0; d < dn; ++d) {
-      const float4 vi = *reinterpret_cast<const float4*>(s_i + d * kPadI + ty * 4);
-      const float4 vj = *reinterpret_cast<const float4*>(s_j + d * kPadJ + tx * 4);
-      const float ai[4] = {vi.x, vi.y, vi.z, vi.w};
-      const float bj[4] = {vj.x, vj.y, vj.z, vj.w};
-#pragma unroll
-      for (int a = 0; a < 4; ++a)
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          const float df = ai[a] - bj[b];
-          acc[a][b] = fmaf(df, df, acc[a][b]);
-        }
-    }
-  }
-}
+// Tiling: a block owns kTI rows i and sweeps a contiguous range of kTJ-wide column tiles j (one of JS
+// "j-splits" of the row, so that k/kTI * JS * N blocks fill the 148 SMs); partial row sums / gradients of
+// the splits are added in fixed order by a small reduce kernel -> deterministic, no atomics, and a row's
+// result does not depend on how the caller blocks the rows (multi-GPU row sharding is bit-identical).
+static constexpr int kTI = 64;              // rows per block
+static constexpr int kTJ = 128;             // columns per tile
+static constexpr int kNT = 256;             // threads per block
+static constexpr int kDC = 16;              // feature dims per chunk (x and z are padded to chunks separately)
+static constexpr int kSG = 3;               // chunks staged together (48 dims: x32 | z16 in one round)
+static constexpr int kSD = kSG * kDC;
+static constexpr int kSI = kTI + 4;         // smem row strides (floats), 16-byte aligned
+static constexpr int kSJ = kTJ + 4;
+static constexpr int kGD = 32;              // gradient dims per GEMM pass
+static constexpr int kXJ = kGD + 4;
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -71,148 +39,348 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+struct NdivDims {
+  int cx, cz;        // 16-dim chunks of x / z
+  int groups;        // staging rounds of kSG chunks over the concatenated [x | z] chunk list
+};
+__host__ __device__ inline NdivDims ndiv_dims(int Dx, int Dz) {
+  NdivDims d;
+  d.cx = (Dx + kDC - 1) / kDC;
+  d.cz = (Dz + kDC - 1) / kDC;
+  d.groups = (d.cx + d.cz + kSG - 1) / kSG;
+  return d;
+}
+
+// Stage chunks [c0, c0+nc) of the concatenated chunk list of rows [r0, r0+R) transposed into s[dim][row]
+// (zero padded).  Warp item = 4 rows x 8 dims: 4 x 32-byte global segments in, bank-conflict-free smem out.
+template <int R, int STRIDE>
+__device__ __forceinline__ void stage_rows(float* __restrict__ s, const float* __restrict__ x, const float* __restrict__ z,
+                                           int k, int Dx, int Dz, int cx, int r0, int c0, int nc) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rr = lane & 3, dd = lane >> 2;
+  const int items = (R / 4) * nc * 2;                 // (row quad) x (8-dim half chunk)
+  for (int it = warp; it < items; it += kNT / 32) {
+    const int h = it % (nc * 2), rq = it / (nc * 2);
+    const int c = c0 + (h >> 1);                      // chunk in the concatenated list
+    const int dl = (h & 1) * 8 + dd;                  // dim inside the chunk
+    const int r = r0 + rq * 4 + rr;
+    float v = 0.f;
+    if (r < k) {
+      if (c < cx) { const int d = c * kDC + dl; if (d < Dx) v = __ldg(x + (size_t)r * Dx + d); }
+      else        { const int d = (c - cx) * kDC + dl; if (d < Dz) v = __ldg(z + (size_t)r * Dz + d); }
+    }
+    s[((h >> 1) * kDC + dl) * STRIDE + rq * 4 + rr] = v;
+  }
+}
+
+// squared distances of the 4x4 pair sub-tile (rows rb..rb+3, cols tx*4..+3) over one staged chunk
+__device__ __forceinline__ void sqdist_chunk(float (&acc)[4][4], const float* __restrict__ si, const float* __restrict__ sj,
+                                             int rb, int cb) {
+#pragma unroll
+  for (int d = 0; d < kDC; ++d) {
+    const float4 a4 = *reinterpret_cast<const float4*>(si + d * kSI + rb);
+    const float4 b4 = *reinterpret_cast<const float4*>(sj + d * kSJ + cb);
+    const float a[4] = {a4.x, a4.y, a4.z, a4.w}, b[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+    for (int p = 0; p < 4; ++p)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float df = a[p] - b[q];
+        acc[p][q] = fmaf(df, df, acc[p][q]);
+      }
+  }
+}
+
+// all chunks of one matrix kind present in the staged group: chunks [c0,c0+nc) of the list, x-type iff c < cx
+__device__ __forceinline__ void sqdist_group(float (&ax)[4][4], float (&az)[4][4], const float* si, const float* sj,
+                                             int cx, int c0, int nc, int rb, int cb) {
+  for (int c = 0; c < nc; ++c) {
+    if (c0 + c < cx) sqdist_chunk(ax, si + c * kDC * kSI, sj + c * kDC * kSJ, rb, cb);
+    else             sqdist_chunk(az, si + c * kDC * kSI, sj + c * kDC * kSJ, rb, cb);
+  }
+}
+
+__device__ __forceinline__ void zero44(float (&a)[4][4]) {
+#pragma unroll
+  for (int p = 0; p < 4; ++p)
+#pragma unroll
+    for (int q = 0; q < 4; ++q) a[p][q] = 0.f;
+}
+
 // ---------------------------------------------------------------- pass 1: row sums
-__global__ void __launch_bounds__(kNdivThreads)
+// grid (row blocks, JS, N).  out: psx/psz [JS][N][k] partial sums (JS == 1: the sums themselves)
+__global__ void __launch_bounds__(kNT, 2)
 ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int k, int Dx, int Dz,
-                   int row0, int rows, float* __restrict__ sx, float* __restrict__ sz) {
-  __shared__ __align__(16) float s_i[kDC * kPadI];
-  __shared__ __align__(16) float s_j[kDC * kPadJ];
-  const int n = blockIdx.y;
+                   int row0, int rows, int tps, float* __restrict__ psx, float* __restrict__ psz) {
+  __shared__ __align__(16) float si[kSD * kSI];
+  __shared__ __align__(16) float sj[kSD * kSJ];
+  const int n = blockIdx.z, js = blockIdx.y, N = gridDim.z;
   const int i0 = row0 + blockIdx.x * kTI;
+  const int iend = (row0 + rows) < k ? (row0 + rows) : k;
+  const int ntiles = (k + kTJ - 1) / kTJ;
+  const int jt0 = js * tps, jt1 = (jt0 + tps) < ntiles ? (jt0 + tps) : ntiles;
   const int ty = threadIdx.x >> 5, tx = threadIdx.x & 31;
   const float* xg = x + (size_t)n * k * Dx;
   const float* zg = z + (size_t)n * k * Dz;
-  float rsx[4] = {0, 0, 0, 0}, rsz[4] = {0, 0, 0, 0};
-  float acc[4][4];
-  for (int j0 = 0; j0 < k; j0 += kTJ) {
-    sqdist_tile(acc, xg, k, Dx, i0, j0, s_i, s_j);
+  const NdivDims nd = ndiv_dims(Dx, Dz);
+  const int nchunks = nd.cx + nd.cz;
+  const bool hoist = nd.groups == 1;                  // all dims fit one staging round: stage the i rows once
+  if (hoist) stage_rows<kTI, kSI>(si, xg, zg, k, Dx, Dz, nd.cx, i0, 0, nchunks);
+  float rsx[8], rsz[8];
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < 8; ++a) rsx[a] = rsz[a] = 0.f;
+  for (int jt = jt0; jt < jt1; ++jt) {
+    const int j0 = jt * kTJ;
 #pragma unroll
-      for (int b = 0; b < 4; ++b)
-        if (j0 + tx * 4 + b < k) rsx[a] += sqrtf(acc[a][b]);
-    sqdist_tile(acc, zg, k, Dz, i0, j0, s_i, s_j);
+    for (int half = 0; half < 2; ++half) {
+      float ax[4][4], az[4][4];
+      zero44(ax); zero44(az);
+      for (int g = 0; g < nd.groups; ++g) {
+        const int c0 = g * kSG, nc = (nchunks - c0) < kSG ? (nchunks - c0) : kSG;
+        if (half == 0 || !hoist) {                    // hoisted case: the j rows are staged once per tile
+          __syncthreads();
+          if (!hoist) stage_rows<kTI, kSI>(si, xg, zg, k, Dx, Dz, nd.cx, i0, c0, nc);
+          stage_rows<kTJ, kSJ>(sj, xg, zg, k, Dx, Dz, nd.cx, j0, c0, nc);
+          __syncthreads();
+        }
+        sqdist_group(ax, az, si, sj, nd.cx, c0, nc, ty * 8 + half * 4, tx * 4);
+      }
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
+      for (int p = 0; p < 4; ++p)
 #pragma unroll
-      for (int b = 0; b < 4; ++b)
-        if (j0 + tx * 4 + b < k) rsz[a] += sqrtf(acc[a][b]);
+        for (int q = 0; q < 4; ++q)
+          if (j0 + tx * 4 + q < k) {
+            rsx[half * 4 + p] += sqrtf(ax[p][q]);
+            rsz[half * 4 + p] += sqrtf(az[p][q]);
+          }
+    }
   }
 #pragma unroll
-  for (int a = 0; a < 4; ++a) {
+  for (int a = 0; a < 8; ++a) {
     const float vx = warp_sum(rsx[a]), vz = warp_sum(rsz[a]);
-    const int i = i0 + ty * 4 + a;
-    if (tx == 0 && i < k && i < row0 + rows) {
-      sx[(size_t)n * k + i] = vx;
-      sz[(size_t)n * k + i] = vz;
+    const int i = i0 + ty * 8 + a;
+    if (tx == 0 && i < iend) {
+      const size_t o = ((size_t)js * N + n) * k + i;
+      psx[o] = vx;
+      psz[o] = vz;
     }
   }
 }
 
+// out[n][i] = sum_js part[js][n][i] in fixed order, rows [row0,row0+rows)
+__global__ void ndiv_rowsum_reduce_kernel(const float* __restrict__ psx, const float* __restrict__ psz, int N, int k,
+                                          int JS, int row0, int rows, float* __restrict__ sx, float* __restrict__ sz) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= N * rows) return;
+  const int n = t / rows, i = row0 + t % rows;
+  float a = 0.f, b = 0.f;
+  for (int js = 0; js < JS; ++js) {
+    const size_t o = ((size_t)js * N + n) * k + i;
+    a += psx[o];
+    b += psz[o];
+  }
+  sx[(size_t)n * k + i] = a;
+  sz[(size_t)n * k + i] = b;
+}
+
 // ---------------------------------------------------------------- pass 2: loss + gradient
-// NCH = number of 16-wide feature chunks of x handled per dimension pass (grad accumulators)
-template <int NCH, bool WITH_GRAD>
-__global__ void __launch_bounds__(kNdivThreads)
-ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z,
-                      const float* __restrict__ sx, const float* __restrict__ sz, int k, int Dx, int Dz,
-                      float margin, int row0, int rows, int dpass0, float* __restrict__ loss_part,
-                      float* __restrict__ grad_x) {
-  __shared__ __align__(16) float s_i[kDC * kPadI];
-  __shared__ __align__(16) float s_j[kDC * kPadJ];
-  __shared__ __align__(16) float s_W[kTI * kPadJ];
-  __shared__ float s_red[kNdivThreads / 32];
-  const int n = blockIdx.y;
+struct NdivSmem2 {
+  float si[kSD * kSI];
+  float sj[kSD * kSJ];
+  float sW[kTI * kSJ];          // What tile; reused for the final cross-warp gradient reduction
+  float sxj[kTJ * kXJ];         // x_j rows of the current gradient dim pass, j-major
+  float2 ri[kTI];               // {1/sx_i, 1/sz_i}
+  float2 rj[kTJ];               // {1/sx_j, 1/sz_j}
+  float red[kNT / 32];
+  float sw[4 * kTI];
+};
+
+// epilogue of a 4x4 pair sub-tile: loss terms, What -> sW.  EDGE: tile touches the row/column boundary.
+template <bool EDGE, bool WITH_GRAD>
+__device__ __forceinline__ void ndiv_epilogue(const float (&ax)[4][4], const float (&az)[4][4], NdivSmem2& sm, float margin,
+                                              int rb, int cb, int i_valid, int j_valid, float& lsum) {
+  float2 cj[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) cj[q] = sm.rj[cb + q];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    const float2 ri = sm.ri[rb + p];
+    float w[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float ddx = sqrtf(ax[p][q]), ddz = sqrtf(az[p][q]);
+      // relu(margin * dz/sz_i - dx/sx_i), diversity.py:18,40 (normalisers as reciprocals)
+      const float hij = __fsub_rn(__fmul_rn(margin, __fmul_rn(ddz, ri.y)), __fmul_rn(ddx, ri.x));
+      const float hji = __fsub_rn(__fmul_rn(margin, __fmul_rn(ddz, cj[q].y)), __fmul_rn(ddx, cj[q].x));
+      const bool ok = !EDGE || ((rb + p) < i_valid && (cb + q) < j_valid);
+      if (ok) lsum += !(hij <= 0.f) ? hij : 0.f;       // NaN propagates (k == 1 -> 0/0, like the reference)
+      if (WITH_GRAD) {
+        const float wij = (hij > 0.f ? ri.x : 0.f) + (hji > 0.f ? cj[q].x : 0.f);
+        w[q] = (ok && ddx > 0.f) ? __fdividef(-wij, ddx) : 0.f;   // torch.norm subgradient: 0 at d == 0
+      }
+    }
+    if (WITH_GRAD) *reinterpret_cast<float4*>(sm.sW + (rb + p) * kSJ + cb) = make_float4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+// grid (row blocks, JS, N).  gpart [JS][N][k][Dx] (JS == 1: grad_x itself), loss_part [gridDim.x*JS*N].
+// NDP = number of 32-dim gradient passes held in registers; dims [dpass0, dpass0 + 32*NDP) are produced.
+template <int NDP, bool WITH_GRAD>
+__global__ void __launch_bounds__(kNT, NDP == 1 ? 2 : 1)
+ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, const float* __restrict__ sx,
+                      const float* __restrict__ sz, int k, int Dx, int Dz, float margin, int row0, int rows,
+                      int tps, int dpass0, float* __restrict__ loss_part, float* __restrict__ gpart) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  NdivSmem2& sm = *reinterpret_cast<NdivSmem2*>(smem_raw);
+  const int n = blockIdx.z, js = blockIdx.y, N = gridDim.z;
   const int i0 = row0 + blockIdx.x * kTI;
   const int iend = (row0 + rows) < k ? (row0 + rows) : k;
-  const int ty = threadIdx.x >> 5, tx = threadIdx.x & 31;
-  const int gi = threadIdx.x >> 3, dg = threadIdx.x & 7;
+  const int ntiles = (k + kTJ - 1) / kTJ;
+  const int jt0 = js * tps, jt1 = (jt0 + tps) < ntiles ? (jt0 + tps) : ntiles;
+  const int tid = threadIdx.x, ty = tid >> 5, tx = tid & 31;
   const float* xg = x + (size_t)n * k * Dx;
   const float* zg = z + (size_t)n * k * Dz;
   const float* sxg = sx + (size_t)n * k;
   const float* szg = sz + (size_t)n * k;
+  const NdivDims nd = ndiv_dims(Dx, Dz);
+  const int nchunks = nd.cx + nd.cz;
+  const bool hoist = nd.groups == 1;
+  // GEMM roles: warp = (j quarter, row half); lane = (row group, 8-dim group)
+  const int jq = ty & 3, rg16 = (tx >> 2) + 8 * (ty >> 2), dg = tx & 3;
 
-  float sxi[4], szi[4];
-#pragma unroll
-  for (int a = 0; a < 4; ++a) {
-    const int i = i0 + ty * 4 + a;
-    sxi[a] = i < k ? __ldg(sxg + i) : 1.f;
-    szi[a] = i < k ? __ldg(szg + i) : 1.f;
+  if (tid < kTI) {
+    const int i = i0 + tid;
+    sm.ri[tid] = i < k ? make_float2(1.f / __ldg(sxg + i), 1.f / __ldg(szg + i)) : make_float2(0.f, 0.f);
   }
-  float gacc[NCH * 2];
+  if (hoist) stage_rows<kTI, kSI>(sm.si, xg, zg, k, Dx, Dz, nd.cx, i0, 0, nchunks);
+  float gacc[NDP][4][8];
+  float swp[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int q = 0; q < NCH * 2; ++q) gacc[q] = 0.f;
-  float sumW = 0.f, lsum = 0.f;
-  float dx[4][4], dz[4][4];
+  for (int e = 0; e < NDP; ++e)
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+      for (int d = 0; d < 8; ++d) gacc[e][a][d] = 0.f;
+  float lsum = 0.f;
 
-  for (int j0 = 0; j0 < k; j0 += kTJ) {
-    sqdist_tile(dx, xg, k, Dx, i0, j0, s_i, s_j);
-    sqdist_tile(dz, zg, k, Dz, i0, j0, s_i, s_j);
-    float sxj[4], szj[4];
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int j = j0 + tx * 4 + b;
-      sxj[b] = j < k ? __ldg(sxg + j) : 1.f;
-      szj[b] = j < k ? __ldg(szg + j) : 1.f;
-    }
-#pragma unroll
-    for (int a = 0; a < 4; ++a) {
-      const int i = i0 + ty * 4 + a;
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const int j = j0 + tx * 4 + b;
-        const float ddx = sqrtf(dx[a][b]), ddz = sqrtf(dz[a][b]);
-        // (i,j): relu(margin * dz/sz_i - dx/sx_i), diversity.py:18,40
-        const float hij = __fsub_rn(__fmul_rn(margin, ddz / szi[a]), ddx / sxi[a]);
-        const float hji = __fsub_rn(__fmul_rn(margin, ddz / szj[b]), ddx / sxj[b]);
-        float w = 0.f;
-        if (i < iend && j < k) {
-          if (dpass0 == 0) lsum += (hij > 0.f) ? hij : ((hij != hij) ? hij : 0.f);
-          const float wij = (hij > 0.f ? 1.f / sxi[a] : 0.f) + (hji > 0.f ? 1.f / sxj[b] : 0.f);
-          w = ddx > 0.f ? -wij / ddx : 0.f;
+  for (int jt = jt0; jt < jt1; ++jt) {
+    const int j0 = jt * kTJ;
+    const bool edge = (i0 + kTI > iend) || (j0 + kTJ > k);
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      float ax[4][4], az[4][4];
+      zero44(ax); zero44(az);
+      for (int g = 0; g < nd.groups; ++g) {
+        const int c0 = g * kSG, nc = (nchunks - c0) < kSG ? (nchunks - c0) : kSG;
+        if (half == 0 || !hoist) {
+          __syncthreads();                             // previous tile's GEMM / previous group's readers are done
+          if (!hoist) stage_rows<kTI, kSI>(sm.si, xg, zg, k, Dx, Dz, nd.cx, i0, c0, nc);
+          stage_rows<kTJ, kSJ>(sm.sj, xg, zg, k, Dx, Dz, nd.cx, j0, c0, nc);
+          if (half == 0 && g == 0) {
+            if (tid < kTJ) {
+              const int j = j0 + tid;
+              sm.rj[tid] = j < k ? make_float2(1.f / __ldg(sxg + j), 1.f / __ldg(szg + j)) : make_float2(0.f, 0.f);
+            }
+            if (WITH_GRAD) {                           // x_j rows of gradient pass 0, j-major, float4 granules
+              for (int t = tid; t < kTJ * (kGD / 4); t += kNT) {
+                const int j = t >> 3, q = t & 7, d = dpass0 + q * 4;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (j0 + j < k) {
+                  const float* src = xg + (size_t)(j0 + j) * Dx + d;
+                  if ((Dx & 3) == 0 && d + 3 < Dx) v = __ldg(reinterpret_cast<const float4*>(src));
+                  else {
+                    if (d < Dx) v.x = __ldg(src);
+                    if (d + 1 < Dx) v.y = __ldg(src + 1);
+                    if (d + 2 < Dx) v.z = __ldg(src + 2);
+                    if (d + 3 < Dx) v.w = __ldg(src + 3);
+                  }
+                }
+                *reinterpret_cast<float4*>(sm.sxj + j * kXJ + q * 4) = v;
+              }
+            }
+          }
+          __syncthreads();
         }
-        if (WITH_GRAD) s_W[(ty * 4 + a) * kPadJ + tx * 4 + b] = w;
+        sqdist_group(ax, az, sm.si, sm.sj, nd.cx, c0, nc, ty * 8 + half * 4, tx * 4);
       }
+      if (edge) ndiv_epilogue<true, WITH_GRAD>(ax, az, sm, margin, ty * 8 + half * 4, tx * 4, iend - i0, k - j0, lsum);
+      else      ndiv_epilogue<false, WITH_GRAD>(ax, az, sm, margin, ty * 8 + half * 4, tx * 4, kTI, kTJ, lsum);
     }
     if (WITH_GRAD) {
-      // grad_i -= sum_j What_ij x_j  (a [32 x 128] x [128 x Dx] product), sumW_i = sum_j What_ij
+      // grad_i -= sum_j What_ij x_j : [64 x 128] x [128 x 32] per pass, 4 rows x 8 dims x 32 j per thread
 #pragma unroll
-      for (int cc = 0; cc < NCH; ++cc) {
-        const int d0 = dpass0 + cc * kDC;
-        if (d0 < Dx) {
-          __syncthreads();
-          stage_chunk<kTJ, kPadJ>(s_j, xg, k, Dx, j0, d0);
-          __syncthreads();
-          const float* wrow = s_W + gi * kPadJ;
-          const float* xa = s_j + (dg * 2) * kPadJ;
-          const float* xb = xa + kPadJ;
-          float g0 = 0.f, g1 = 0.f, sw = 0.f;
-#pragma unroll 8
-          for (int j = 0; j < kTJ; j += 4) {
-            const float4 w4 = *reinterpret_cast<const float4*>(wrow + j);
-            const float4 a4 = *reinterpret_cast<const float4*>(xa + j);
-            const float4 b4 = *reinterpret_cast<const float4*>(xb + j);
-            g0 = fmaf(w4.x, a4.x, g0); g0 = fmaf(w4.y, a4.y, g0); g0 = fmaf(w4.z, a4.z, g0); g0 = fmaf(w4.w, a4.w, g0);
-            g1 = fmaf(w4.x, b4.x, g1); g1 = fmaf(w4.y, b4.y, g1); g1 = fmaf(w4.z, b4.z, g1); g1 = fmaf(w4.w, b4.w, g1);
-            sw += (w4.x + w4.y) + (w4.z + w4.w);
+      for (int e = 0; e < NDP; ++e) {
+        if (e > 0) {
+          if (dpass0 + e * kGD >= Dx) break;
+          __syncthreads();                             // previous pass has consumed sxj
+          for (int t = tid; t < kTJ * (kGD / 4); t += kNT) {
+            const int j = t >> 3, q = t & 7, d = dpass0 + e * kGD + q * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (j0 + j < k) {
+              const float* src = xg + (size_t)(j0 + j) * Dx + d;
+              if ((Dx & 3) == 0 && d + 3 < Dx) v = __ldg(reinterpret_cast<const float4*>(src));
+              else {
+                if (d < Dx) v.x = __ldg(src);
+                if (d + 1 < Dx) v.y = __ldg(src + 1);
+                if (d + 2 < Dx) v.z = __ldg(src + 2);
+                if (d + 3 < Dx) v.w = __ldg(src + 3);
+              }
+            }
+            *reinterpret_cast<float4*>(sm.sxj + j * kXJ + q * 4) = v;
           }
-          gacc[cc * 2] += g0;
-          gacc[cc * 2 + 1] += g1;
-          if (cc == 0) sumW += sw;
+        }
+        __syncthreads();                               // sW complete (e == 0) / sxj staged (e > 0)
+        const float* wbase = sm.sW + rg16 * kSJ + jq * 32;
+        const float* xbase = sm.sxj + (jq * 32) * kXJ + dg * 8;
+#pragma unroll 2
+        for (int jj = 0; jj < 8; ++jj) {
+          float wv[4][4];
+#pragma unroll
+          for (int a = 0; a < 4; ++a) {
+            const float4 w4 = *reinterpret_cast<const float4*>(wbase + a * 16 * kSJ + jj * 4);
+            wv[a][0] = w4.x; wv[a][1] = w4.y; wv[a][2] = w4.z; wv[a][3] = w4.w;
+            if (e == 0) swp[a] += (w4.x + w4.y) + (w4.z + w4.w);
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 x0 = *reinterpret_cast<const float4*>(xbase + (jj * 4 + q) * kXJ);
+            const float4 x1 = *reinterpret_cast<const float4*>(xbase + (jj * 4 + q) * kXJ + 4);
+            const float xv[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+              for (int d = 0; d < 8; ++d) gacc[e][a][d] = fmaf(wv[a][q], xv[d], gacc[e][a][d]);
+          }
         }
       }
     }
   }
+  // ---- block results
   if (WITH_GRAD) {
-    const int i = i0 + gi;
-    if (i < iend) {
+    const int N_ = N;
+    for (int e = 0; e < NDP; ++e) {
+      if (dpass0 + e * kGD >= Dx) break;
+      __syncthreads();
+      float* red = sm.sW;                               // [4 jq][64 rows][32 dims]
 #pragma unroll
-      for (int cc = 0; cc < NCH; ++cc) {
+      for (int a = 0; a < 4; ++a) {
+        float* dst = red + ((jq * kTI) + rg16 + 16 * a) * kGD + dg * 8;
+        *reinterpret_cast<float4*>(dst) = make_float4(gacc[e][a][0], gacc[e][a][1], gacc[e][a][2], gacc[e][a][3]);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(gacc[e][a][4], gacc[e][a][5], gacc[e][a][6], gacc[e][a][7]);
+        if (e == 0 && dg == 0) sm.sw[jq * kTI + rg16 + 16 * a] = swp[a];
+      }
+      __syncthreads();
+      const int r = tid >> 2, d8 = (tid & 3) * 8, i = i0 + r;
+      if (i < iend) {
+        const float sumW = (sm.sw[r] + sm.sw[kTI + r]) + (sm.sw[2 * kTI + r] + sm.sw[3 * kTI + r]);
 #pragma unroll
-        for (int h = 0; h < 2; ++h) {
-          const int d = dpass0 + cc * kDC + dg * 2 + h;
-          if (d < Dx) {
-            const size_t off = ((size_t)n * k + i) * Dx + d;
-            grad_x[off] = __ldg(x + off) * sumW - gacc[cc * 2 + h];
+        for (int d = 0; d < 8; ++d) {
+          const int dim = dpass0 + e * kGD + d8 + d;
+          if (dim < Dx) {
+            const float g = (red[r * kGD + d8 + d] + red[(kTI + r) * kGD + d8 + d]) +
+                            (red[(2 * kTI + r) * kGD + d8 + d] + red[(3 * kTI + r) * kGD + d8 + d]);
+            const size_t off = ((size_t)n * k + i) * Dx + dim;
+            gpart[((size_t)js * N_) * k * Dx + off] = fmaf(__ldg(x + off), sumW, -g);
           }
         }
       }
@@ -221,15 +389,30 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z,
   if (dpass0 == 0) {
     lsum = warp_sum(lsum);
     __syncthreads();
-    if (tx == 0) s_red[ty] = lsum;
+    if (tx == 0) sm.red[ty] = lsum;
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (tid == 0) {
       float t = 0.f;
 #pragma unroll
-      for (int w = 0; w < kNdivThreads / 32; ++w) t += s_red[w];
-      loss_part[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = t;
+      for (int w = 0; w < kNT / 32; ++w) t += sm.red[w];
+      loss_part[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = t;
     }
   }
+}
+
+// grad[n][i][d] = sum_js gpart[js][n][i][d], rows [row0,row0+rows), dims [d0,d1)
+__global__ void ndiv_grad_reduce_kernel(const float* __restrict__ gpart, int N, int k, int Dx, int JS, int row0, int rows,
+                                        int d0, int d1, float* __restrict__ grad) {
+  const int nd = d1 - d0;
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (size_t)N * rows * nd) return;
+  const int d = d0 + (int)(t % nd);
+  const size_t ri = t / nd;
+  const int i = row0 + (int)(ri % rows), n = (int)(ri / rows);
+  const size_t off = ((size_t)n * k + i) * Dx + d;
+  float a = 0.f;
+  for (int js = 0; js < JS; ++js) a += gpart[(size_t)js * N * k * Dx + off];
+  grad[off] = a;
 }
 
 __global__ void ndiv_finalize_kernel(const float* __restrict__ part, int n, float* __restrict__ loss) {
@@ -243,6 +426,26 @@ __global__ void ndiv_finalize_kernel(const float* __restrict__ part, int n, floa
     __syncthreads();
   }
   if (threadIdx.x == 0) loss[0] = s[0];
+}
+
+// plain row sums of one distance matrix (normaliser of compute_pair_distance's backward): one warp per row
+__global__ void rowsum_simple_kernel(const float* __restrict__ v, int k, int C, float* __restrict__ rs) {
+  const int n = blockIdx.y;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= k) return;
+  const float* vg = v + (size_t)n * k * C;
+  float s = 0.f;
+  for (int j = lane; j < k; j += 32) {
+    float acc = 0.f;
+    for (int c = 0; c < C; ++c) {
+      const float df = __ldg(vg + (size_t)i * C + c) - __ldg(vg + (size_t)j * C + c);
+      acc = fmaf(df, df, acc);
+    }
+    s += sqrtf(acc);
+  }
+  s = warp_sum(s);
+  if (lane == 0) rs[(size_t)n * k + i] = s;
 }
 
 // ---------------------------------------------------------------- public pairwise API
@@ -309,9 +512,40 @@ __global__ void pairwise_bwd_kernel(const float* __restrict__ v, const float* __
 
 using namespace ndp;
 
-extern "C" int ndp_ndiv_workspace_bytes(int N, int k, size_t* bytes) {
-  NDP_CHECK_ARG(bytes && N >= 0 && k >= 0, "ndiv: bad N/k");
-  *bytes = (size_t)N * ((k + kTI - 1) / kTI + 1) * sizeof(float) + 256;
+namespace ndp {
+// j-split plan: depends on (N, k, Dx) only so that row-blocked (sharded) calls reproduce the full call bit for bit
+struct NdivPlan { int ntiles, tps, JS; };
+static NdivPlan ndiv_plan(int N, int k, int Dx) {
+  NdivPlan p;
+  p.ntiles = (k + kTJ - 1) / kTJ;
+  if (p.ntiles < 1) p.ntiles = 1;
+  const long long rowblocks = (long long)(N > 0 ? N : 1) * ((k + kTI - 1) / kTI > 0 ? (k + kTI - 1) / kTI : 1);
+  long long want = 592 / rowblocks;                    // ~4 blocks per SM
+  if (want < 1) want = 1;
+  if (want > p.ntiles) want = p.ntiles;
+  // keep the gradient partials below 64 MB
+  const long long per = (long long)(N > 0 ? N : 1) * (k > 0 ? k : 1) * (Dx > 0 ? Dx : 1) * 4;
+  while (want > 1 && want * per > (64ll << 20)) --want;
+  p.tps = (int)((p.ntiles + want - 1) / want);
+  p.JS = (p.ntiles + p.tps - 1) / p.tps;
+  return p;
+}
+struct NdivWs { size_t part, psum, gpart, total; };
+static NdivWs ndiv_ws(int N, int k, int Dx) {
+  const NdivPlan p = ndiv_plan(N, k, Dx);
+  NdivWs w;
+  const size_t rb = (size_t)((k + kTI - 1) / kTI + 1);
+  w.part = ((size_t)(N > 0 ? N : 1) * rb * p.JS * sizeof(float) + 255) / 256 * 256;
+  w.psum = p.JS > 1 ? ((size_t)2 * p.JS * N * k * sizeof(float) + 255) / 256 * 256 : 0;
+  w.gpart = p.JS > 1 ? ((size_t)p.JS * N * k * Dx * sizeof(float) + 255) / 256 * 256 : 0;
+  w.total = w.part + (w.psum > w.gpart ? w.psum : w.gpart) + 256;
+  return w;
+}
+}  // namespace ndp
+
+extern "C" int ndp_ndiv_workspace_bytes(int N, int k, int Dx, size_t* bytes) {
+  NDP_CHECK_ARG(bytes && N >= 0 && k >= 0 && Dx >= 1, "ndiv: bad N/k/Dx");
+  *bytes = ndiv_ws(N, k, Dx).total;
   return NDP_OK;
 }
 
@@ -324,27 +558,40 @@ static int ndiv_args_ok(const float* x, const float* z, int N, int k, int Dx, in
 }
 
 extern "C" int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz,
-                                int row0, int rows, float* sx, float* sz, void* stream) {
+                                int row0, int rows, float* sx, float* sz, void* ws, size_t ws_bytes, void* stream) {
   if (int rc = ndiv_args_ok(x, z, N, k, Dx, Dz, row0, rows)) return rc;
   if (int rc = device_check()) return rc;
   if (N == 0 || rows == 0) return NDP_OK;
   NDP_CHECK_ARG(sx && sz, "ndiv: null sx/sz");
-  dim3 grid((rows + kTI - 1) / kTI, N);
-  ndiv_rowsum_kernel<<<grid, kNdivThreads, 0, (cudaStream_t)stream>>>(x, z, k, Dx, Dz, row0, rows, sx, sz);
+  cudaStream_t s = (cudaStream_t)stream;
+  const NdivPlan p = ndiv_plan(N, k, Dx);
+  const NdivWs w = ndiv_ws(N, k, Dx);
+  dim3 grid((rows + kTI - 1) / kTI, p.JS, N);
+  if (p.JS == 1) {
+    ndiv_rowsum_kernel<<<grid, kNT, 0, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, sx, sz);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
+  if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
+  float* psx = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + w.part);
+  float* psz = psx + (size_t)p.JS * N * k;
+  ndiv_rowsum_kernel<<<grid, kNT, 0, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, psx, psz);
+  NDP_LAUNCH_CHECK();
+  ndiv_rowsum_reduce_kernel<<<(N * rows + 255) / 256, 256, 0, s>>>(psx, psz, N, k, p.JS, row0, rows, sx, sz);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
 
-template <int NCH>
-static void launch_loss_grad(dim3 grid, cudaStream_t s, const float* x, const float* z, const float* sx,
-                             const float* sz, int k, int Dx, int Dz, float margin, int row0, int rows,
-                             int dpass0, float* part, float* grad_x) {
-  if (grad_x)
-    ndiv_loss_grad_kernel<NCH, true><<<grid, kNdivThreads, 0, s>>>(x, z, sx, sz, k, Dx, Dz, margin, row0, rows,
-                                                                  dpass0, part, grad_x);
-  else
-    ndiv_loss_grad_kernel<NCH, false><<<grid, kNdivThreads, 0, s>>>(x, z, sx, sz, k, Dx, Dz, margin, row0, rows,
-                                                                   dpass0, part, grad_x);
+template <int NDP, bool WG>
+static int launch_loss_grad(dim3 grid, cudaStream_t s, const float* x, const float* z, const float* sx,
+                            const float* sz, int k, int Dx, int Dz, float margin, int row0, int rows, int tps,
+                            int dpass0, float* part, float* gpart) {
+  NDP_CUDA(cudaFuncSetAttribute(ndiv_loss_grad_kernel<NDP, WG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)sizeof(NdivSmem2)));
+  ndiv_loss_grad_kernel<NDP, WG><<<grid, kNT, sizeof(NdivSmem2), s>>>(x, z, sx, sz, k, Dx, Dz, margin, row0, rows, tps,
+                                                                      dpass0, part, gpart);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
 }
 
 extern "C" int ndp_ndiv_loss_grad(const float* x, const float* z, const float* sx, const float* sz,
@@ -359,23 +606,30 @@ extern "C" int ndp_ndiv_loss_grad(const float* x, const float* z, const float* s
     return NDP_OK;
   }
   NDP_CHECK_ARG(sx && sz, "ndiv: null sx/sz");
-  dim3 grid((rows + kTI - 1) / kTI, N);
-  const size_t nparts = (size_t)grid.x * grid.y;
-  if (!ws || ws_bytes < nparts * sizeof(float)) {
-    set_error("ndiv: workspace %zu < %zu", ws_bytes, nparts * sizeof(float));
-    return NDP_ERR_WORKSPACE;
-  }
+  const NdivPlan p = ndiv_plan(N, k, Dx);
+  const NdivWs w = ndiv_ws(N, k, Dx);
+  if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
+  dim3 grid((rows + kTI - 1) / kTI, p.JS, N);
+  const size_t nparts = (size_t)grid.x * grid.y * grid.z;
   float* part = reinterpret_cast<float*>(ws);
-  const int per_pass = 16 * kDC;
-  for (int dp = 0; dp < Dx; dp += per_pass) {
-    const int chunks = ((Dx - dp < per_pass ? Dx - dp : per_pass) + kDC - 1) / kDC;
-    if (!grad_x || chunks <= 1) launch_loss_grad<1>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, dp, part, grad_x);
-    else if (chunks <= 2) launch_loss_grad<2>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, dp, part, grad_x);
-    else if (chunks <= 4) launch_loss_grad<4>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, dp, part, grad_x);
-    else if (chunks <= 8) launch_loss_grad<8>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, dp, part, grad_x);
-    else launch_loss_grad<16>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, dp, part, grad_x);
-    NDP_LAUNCH_CHECK();
-    if (!grad_x) break;
+  float* gpart = p.JS > 1 ? reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + w.part) : grad_x;
+  if (!grad_x) {
+    if (int rc = launch_loss_grad<1, false>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, 0, part, nullptr)) return rc;
+  } else {
+    const int per_launch = 4 * kGD;
+    for (int dp = 0; dp < Dx; dp += per_launch) {
+      const int passes = ((Dx - dp < per_launch ? Dx - dp : per_launch) + kGD - 1) / kGD;
+      int rc;
+      if (passes <= 1) rc = launch_loss_grad<1, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart);
+      else if (passes <= 2) rc = launch_loss_grad<2, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart);
+      else rc = launch_loss_grad<4, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart);
+      if (rc) return rc;
+    }
+    if (p.JS > 1) {
+      const size_t tot = (size_t)N * rows * Dx;
+      ndiv_grad_reduce_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(gpart, N, k, Dx, p.JS, row0, rows, 0, Dx, grad_x);
+      NDP_LAUNCH_CHECK();
+    }
   }
   ndiv_finalize_kernel<<<1, 256, 0, s>>>(part, (int)nparts, loss);
   NDP_LAUNCH_CHECK();
@@ -402,8 +656,7 @@ extern "C" int ndp_pairwise_backward(const float* v, const float* grad_out, int 
   NDP_CHECK_ARG(v && grad_out && grad_v, "pairwise_backward: null pointer");
   dim3 grid((k + 7) / 8, N);
   if (normalise) {
-    ndiv_rowsum_kernel<<<dim3((k + kTI - 1) / kTI, N), kNdivThreads, 0, (cudaStream_t)stream>>>(
-        v, v, k, C, C, 0, k, rowsum_ws, rowsum_ws);
+    rowsum_simple_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(v, k, C, rowsum_ws);
     NDP_LAUNCH_CHECK();
   }
   pairwise_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(v, grad_out, k, C, normalise,

@@ -74,8 +74,11 @@ def ndiv_rowsums(x, z, row0=0, rows=None, sx=None, sz=None):
     if sx is None:
         sx = torch.empty(N, k, dtype=torch.float32, device=x.device)
         sz = torch.empty(N, k, dtype=torch.float32, device=x.device)
+    nbytes = C.c_size_t()
+    check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, C.byref(nbytes)))
+    ws = _ws(nbytes.value, x.device)
     with torch.cuda.device(x.device):
-        check(lib().ndp_ndiv_rowsums(ptr(x), ptr(z), N, k, Dx, Dz, row0, rows, ptr(sx), ptr(sz),
+        check(lib().ndp_ndiv_rowsums(ptr(x), ptr(z), N, k, Dx, Dz, row0, rows, ptr(sx), ptr(sz), ptr(ws), ws.numel(),
                                      stream_ptr(x.device)))
     return sx, sz
 
@@ -91,7 +94,7 @@ def ndiv_loss_grad(x, z, sx, sz, want_grad, row0=0, rows=None, margin=MARGIN):
     if want_grad:
         grad = torch.empty_like(x) if full else torch.zeros_like(x)
     nbytes = C.c_size_t()
-    check(lib().ndp_ndiv_workspace_bytes(N, k, C.byref(nbytes)))
+    check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, C.byref(nbytes)))
     ws = _ws(nbytes.value, x.device)
     with torch.cuda.device(x.device):
         check(lib().ndp_ndiv_loss_grad(ptr(x), ptr(z), ptr(sx), ptr(sz), N, k, Dx, Dz, margin, row0, rows,
