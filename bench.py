@@ -212,12 +212,22 @@ def run_gpu(args):
         return a, b, plans
 
     res_h = [{"idx": torch.empty(G, dtype=torch.int32).pin_memory(), "act": torch.empty(G, 4).pin_memory(),
-              "key": torch.empty(G, dtype=torch.int64).pin_memory()} for _ in range(2)]
+              "key": torch.empty(G, dtype=torch.int64).pin_memory(), "done": torch.cuda.Event()} for _ in range(4)]
 
     copy_stream = torch.cuda.Stream(device=dev)
     in_d = [{"nz": torch.empty(T, G, K, nd, device=dev), "e0": torch.empty(G, E, device=dev),
              "goal": torch.empty(G, E, device=dev), "up": torch.cuda.Event(), "free": torch.cuda.Event()}
             for _ in range(3)]
+
+    out_stream = torch.cuda.Stream(device=dev)
+
+    def read_back(q, r):
+        """D2H of a finished plan on its own stream: the rollout stream never waits for a tail"""
+        out_stream.wait_event(q.ready)
+        with torch.cuda.stream(out_stream):
+            r["idx"].copy_(q.best_idx, non_blocking=True); r["act"].copy_(q.best_action, non_blocking=True)
+            r["key"].copy_(q.packed_min, non_blocking=True)
+            r["done"].record(out_stream)
 
     def run_e2e(steps, first):
         """host buffers in, host results out, every step: H2D of the step's noise/e0/goal from pinned memory
@@ -236,18 +246,15 @@ def run_gpu(args):
                 d["e0"].copy_(e0_h, non_blocking=True); d["goal"].copy_(goal_h, non_blocking=True)
                 d["up"].record(copy_stream)
             main.wait_event(d["up"])
+            if i >= 4:
+                main.wait_event(res_h[i & 3]["done"])          # plan i-4 (same ring slot) has been read back
             p_ = ring.plan(d["e0"], d["goal"], d["nz"])
             d["free"] = p_.ready
             if prev is not None:                       # results of the previous plan leave while this one runs
-                q, r = prev
-                q.wait()
-                r["idx"].copy_(q.best_idx, non_blocking=True); r["act"].copy_(q.best_action, non_blocking=True)
-                r["key"].copy_(q.packed_min, non_blocking=True)
-            prev = (p_, res_h[i & 1])
-        q, r = prev
-        q.wait()
-        r["idx"].copy_(q.best_idx, non_blocking=True); r["act"].copy_(q.best_action, non_blocking=True)
-        r["key"].copy_(q.packed_min, non_blocking=True)
+                read_back(*prev)
+            prev = (p_, res_h[i & 3])
+        read_back(*prev)
+        main.wait_stream(out_stream)
         b.record()
         return a, b
 

@@ -58,22 +58,27 @@ __device__ __forceinline__ void stage_rows(float* __restrict__ s, const float* _
                                            int k, int Dx, int Dz, int cx, int r0, int c0, int nc) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int rr = lane & 3, dd = lane >> 2;
-  const int items = (R / 4) * nc * 2;                 // (row quad) x (8-dim half chunk)
-  for (int it = warp; it < items; it += kNT / 32) {
-    const int h = it % (nc * 2), rq = it / (nc * 2);
-    const int c = c0 + (h >> 1);                      // chunk in the concatenated list
-    const int dl = (h & 1) * 8 + dd;                  // dim inside the chunk
+  for (int rq = warp; rq < R / 4; rq += kNT / 32) {   // row quad
     const int r = r0 + rq * 4 + rr;
-    float v = 0.f;
-    if (r < k) {
-      if (c < cx) { const int d = c * kDC + dl; if (d < Dx) v = __ldg(x + (size_t)r * Dx + d); }
-      else        { const int d = (c - cx) * kDC + dl; if (d < Dz) v = __ldg(z + (size_t)r * Dz + d); }
+    const bool rv = r < k;
+    const float* xr = x + (size_t)r * Dx;
+    const float* zr = z + (size_t)r * Dz;
+    float* dst = s + dd * STRIDE + rq * 4 + rr;
+    for (int c = 0; c < nc; ++c) {
+      const bool isx = (c0 + c) < cx;
+      const float* src = isx ? xr : zr;
+      const int D = isx ? Dx : Dz;
+      const int d = (isx ? (c0 + c) : (c0 + c - cx)) * kDC + dd;
+      const float v0 = (rv && d < D) ? __ldg(src + d) : 0.f;
+      const float v1 = (rv && d + 8 < D) ? __ldg(src + d + 8) : 0.f;
+      dst[(c * kDC) * STRIDE] = v0;
+      dst[(c * kDC + 8) * STRIDE] = v1;
     }
-    s[((h >> 1) * kDC + dl) * STRIDE + rq * 4 + rr] = v;
   }
 }
 
-// squared distances of the 4x4 pair sub-tile (rows rb..rb+3, cols tx*4..+3) over one staged chunk
+// squared distances of the 4x4 pair sub-tile (rows rb..rb+3, cols cb..cb+3) over one staged chunk.  A warp covers
+// 16 rows x 32 cols (lane = 4 row quads x 8 col quads): both operand loads are a single 64/128-byte wavefront.
 __device__ __forceinline__ void sqdist_chunk(float (&acc)[4][4], const float* __restrict__ si, const float* __restrict__ sj,
                                              int rb, int cb) {
 #pragma unroll
@@ -119,20 +124,21 @@ ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int
   const int iend = (row0 + rows) < k ? (row0 + rows) : k;
   const int ntiles = (k + kTJ - 1) / kTJ;
   const int jt0 = js * tps, jt1 = (jt0 + tps) < ntiles ? (jt0 + tps) : ntiles;
-  const int ty = threadIdx.x >> 5, tx = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rb = (warp & 3) * 16 + (lane >> 3) * 4;    // warp = 16 rows x 32 cols, lane = (row quad, col quad)
+  const int wc = warp >> 2, lc = lane & 7;
   const float* xg = x + (size_t)n * k * Dx;
   const float* zg = z + (size_t)n * k * Dz;
   const NdivDims nd = ndiv_dims(Dx, Dz);
   const int nchunks = nd.cx + nd.cz;
   const bool hoist = nd.groups == 1;                  // all dims fit one staging round: stage the i rows once
   if (hoist) stage_rows<kTI, kSI>(si, xg, zg, k, Dx, Dz, nd.cx, i0, 0, nchunks);
-  float rsx[8], rsz[8];
-#pragma unroll
-  for (int a = 0; a < 8; ++a) rsx[a] = rsz[a] = 0.f;
+  float rsx[4] = {0.f, 0.f, 0.f, 0.f}, rsz[4] = {0.f, 0.f, 0.f, 0.f};
   for (int jt = jt0; jt < jt1; ++jt) {
     const int j0 = jt * kTJ;
-#pragma unroll
+#pragma unroll 1
     for (int half = 0; half < 2; ++half) {
+      const int cb = (wc * 2 + half) * 32 + lc * 4;
       float ax[4][4], az[4][4];
       zero44(ax); zero44(az);
       for (int g = 0; g < nd.groups; ++g) {
@@ -143,26 +149,37 @@ ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int
           stage_rows<kTJ, kSJ>(sj, xg, zg, k, Dx, Dz, nd.cx, j0, c0, nc);
           __syncthreads();
         }
-        sqdist_group(ax, az, si, sj, nd.cx, c0, nc, ty * 8 + half * 4, tx * 4);
+        sqdist_group(ax, az, si, sj, nd.cx, c0, nc, rb, cb);
       }
 #pragma unroll
       for (int p = 0; p < 4; ++p)
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-          if (j0 + tx * 4 + q < k) {
-            rsx[half * 4 + p] += sqrtf(ax[p][q]);
-            rsz[half * 4 + p] += sqrtf(az[p][q]);
+          if (j0 + cb + q < k) {
+            rsx[p] += sqrtf(ax[p][q]);
+            rsz[p] += sqrtf(az[p][q]);
           }
     }
   }
+  // row sums: 8 column-quad lanes (shuffles), then the two column halves of the block (shared memory), fixed order
+  __shared__ float srs[2][2][kTI];
 #pragma unroll
-  for (int a = 0; a < 8; ++a) {
-    const float vx = warp_sum(rsx[a]), vz = warp_sum(rsz[a]);
-    const int i = i0 + ty * 8 + a;
-    if (tx == 0 && i < iend) {
+  for (int p = 0; p < 4; ++p) {
+    float vx = rsx[p], vz = rsz[p];
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+      vx += __shfl_xor_sync(0xffffffffu, vx, o);
+      vz += __shfl_xor_sync(0xffffffffu, vz, o);
+    }
+    if (lc == 0) { srs[0][wc][rb + p] = vx; srs[1][wc][rb + p] = vz; }
+  }
+  __syncthreads();
+  if (threadIdx.x < kTI) {
+    const int i = i0 + threadIdx.x;
+    if (i < iend) {
       const size_t o = ((size_t)js * N + n) * k + i;
-      psx[o] = vx;
-      psz[o] = vz;
+      psx[o] = srs[0][0][threadIdx.x] + srs[0][1][threadIdx.x];
+      psz[o] = srs[1][0][threadIdx.x] + srs[1][1][threadIdx.x];
     }
   }
 }
@@ -238,6 +255,8 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
   const int ntiles = (k + kTJ - 1) / kTJ;
   const int jt0 = js * tps, jt1 = (jt0 + tps) < ntiles ? (jt0 + tps) : ntiles;
   const int tid = threadIdx.x, ty = tid >> 5, tx = tid & 31;
+  const int rb = (ty & 3) * 16 + (tx >> 3) * 4;        // distance phase: warp = 16 rows x 32 cols, lane = (row quad, col quad)
+  const int wc = ty >> 2, lc = tx & 7;
   const float* xg = x + (size_t)n * k * Dx;
   const float* zg = z + (size_t)n * k * Dz;
   const float* sxg = sx + (size_t)n * k;
@@ -268,6 +287,7 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
     const bool edge = (i0 + kTI > iend) || (j0 + kTJ > k);
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
+      const int cb = (wc * 2 + half) * 32 + lc * 4;
       float ax[4][4], az[4][4];
       zero44(ax); zero44(az);
       for (int g = 0; g < nd.groups; ++g) {
@@ -301,10 +321,10 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
           }
           __syncthreads();
         }
-        sqdist_group(ax, az, sm.si, sm.sj, nd.cx, c0, nc, ty * 8 + half * 4, tx * 4);
+        sqdist_group(ax, az, sm.si, sm.sj, nd.cx, c0, nc, rb, cb);
       }
-      if (edge) ndiv_epilogue<true, WITH_GRAD>(ax, az, sm, margin, ty * 8 + half * 4, tx * 4, iend - i0, k - j0, lsum);
-      else      ndiv_epilogue<false, WITH_GRAD>(ax, az, sm, margin, ty * 8 + half * 4, tx * 4, kTI, kTJ, lsum);
+      if (edge) ndiv_epilogue<true, WITH_GRAD>(ax, az, sm, margin, rb, cb, iend - i0, k - j0, lsum);
+      else      ndiv_epilogue<false, WITH_GRAD>(ax, az, sm, margin, rb, cb, kTI, kTJ, lsum);
     }
     if (WITH_GRAD) {
       // grad_i -= sum_j What_ij x_j : [64 x 128] x [128 x 32] per pass, 4 rows x 8 dims x 32 j per thread
