@@ -228,7 +228,10 @@ class PlanRing:
     """Steady-state planning loop without per-plan allocations or host stalls.
 
     `depth` slots hold every output and workspace of a plan; plan i writes slot i % depth.  The bulk
-    rollout runs on the caller's stream, everything after it (refine list selection, split-operand
+    rollout runs on ring-owned stream i % 2, ordered after the caller's stream (so its inputs are ready): two
+    consecutive rollouts may overlap, and the last, partially filled wave of 128-candidate tiles of plan i
+    shares the SMs with the first wave of plan i+1 instead of leaving them idle (512 tiles on 148 SMs are
+    3.46 waves).  Everything after the rollout (refine list selection, split-operand
     re-roll, selection, verification, action gather and — when `comm` is given — the sharded record
     exchange and merge) on side stream i % n_streams, so the latency-bound tails of two consecutive
     plans overlap each other and the next bulk rollouts.  A returned Plan is valid until `depth - 1`
@@ -242,6 +245,8 @@ class PlanRing:
             planner, G, K, topk, depth, idx_base, comm
         self.count = 0
         self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(n_streams)]
+        self.bulk_streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
+        self.inputs_ready = [torch.cuda.Event() for _ in range(depth)]
         n = C.c_size_t()
         check(lib().ndp_plan_workspace_bytes(planner._h, G, K, topk, C.byref(n)))
         world = comm.world if comm is not None else 1
@@ -297,15 +302,20 @@ class PlanRing:
         side = self.streams[i % len(self.streams)]
         dev = pl.device
         main = torch.cuda.current_stream(dev)
+        bulk = self.bulk_streams[i & 1]
         if s.used:
-            main.wait_event(s.ready)          # the slot's previous tail (and its readers on the side streams) is done
+            main.wait_event(s.ready)          # the slot's previous tail is done: its inputs may be released ...
+            bulk.wait_event(s.ready)          # ... and its outputs overwritten
         s.inputs, s.used = (e0c, gc, nz), True   # keep the inputs alive until the slot is reused
+        ir = self.inputs_ready[i % self.depth]
+        ir.record(main)
+        bulk.wait_event(ir)
         L = lib()
         head = (pl._h, e0c.data_ptr(), gc.data_ptr(), nz.data_ptr())
         sp = C.c_void_p(side.cuda_stream)
         with torch.cuda.device(dev):
-            check(L.ndp_plan_select_bulk(*head, *s.tail, C.c_void_p(main.cuda_stream)))
-            s.bulk_done.record(main)
+            check(L.ndp_plan_select_bulk(*head, *s.tail, C.c_void_p(bulk.cuda_stream)))
+            s.bulk_done.record(bulk)
             side.wait_event(s.bulk_done)
             check(L.ndp_plan_select_refine(*head, *s.tail, sp))
             check(L.ndp_gather_best_action(*s.gather, sp))
