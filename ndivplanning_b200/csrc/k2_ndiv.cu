@@ -28,7 +28,8 @@ static constexpr int kNT = 256;             // threads per block
 static constexpr int kDC = 16;              // feature dims per chunk (x and z are padded to chunks separately)
 static constexpr int kSG = 3;               // chunks staged together (48 dims: x32 | z16 in one round)
 static constexpr int kSD = kSG * kDC;
-static constexpr int kSI = kTI + 4;         // smem row strides (floats), 16-byte aligned
+static constexpr int kSI = 2 * kTI + 8;     // i rows are staged DUPLICATED ({a,a} pairs feed the packed f32x2 ops): 136
+                                            // smem row strides in floats, 16-byte aligned
 static constexpr int kSJ = kTJ + 4;
 static constexpr int kGD = 32;              // gradient dims per GEMM pass
 static constexpr int kXJ = kGD + 4;
@@ -53,7 +54,7 @@ __host__ __device__ inline NdivDims ndiv_dims(int Dx, int Dz) {
 
 // Stage chunks [c0, c0+nc) of the concatenated chunk list of rows [r0, r0+R) transposed into s[dim][row]
 // (zero padded).  Warp item = 4 rows x 8 dims: 4 x 32-byte global segments in, bank-conflict-free smem out.
-template <int R, int STRIDE>
+template <int R, int STRIDE, bool DUP>
 __device__ __forceinline__ void stage_rows(float* __restrict__ s, const float* __restrict__ x, const float* __restrict__ z,
                                            int k, int Dx, int Dz, int cx, int r0, int c0, int nc) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -63,7 +64,7 @@ __device__ __forceinline__ void stage_rows(float* __restrict__ s, const float* _
     const bool rv = r < k;
     const float* xr = x + (size_t)r * Dx;
     const float* zr = z + (size_t)r * Dz;
-    float* dst = s + dd * STRIDE + rq * 4 + rr;
+    float* dst = s + dd * STRIDE + (rq * 4 + rr) * (DUP ? 2 : 1);
     for (int c = 0; c < nc; ++c) {
       const bool isx = (c0 + c) < cx;
       const float* src = isx ? xr : zr;
@@ -71,33 +72,48 @@ __device__ __forceinline__ void stage_rows(float* __restrict__ s, const float* _
       const int d = (isx ? (c0 + c) : (c0 + c - cx)) * kDC + dd;
       const float v0 = (rv && d < D) ? __ldg(src + d) : 0.f;
       const float v1 = (rv && d + 8 < D) ? __ldg(src + d + 8) : 0.f;
-      dst[(c * kDC) * STRIDE] = v0;
-      dst[(c * kDC + 8) * STRIDE] = v1;
+      if (DUP) {
+        *reinterpret_cast<float2*>(dst + (c * kDC) * STRIDE) = make_float2(v0, v0);
+        *reinterpret_cast<float2*>(dst + (c * kDC + 8) * STRIDE) = make_float2(v1, v1);
+      } else {
+        dst[(c * kDC) * STRIDE] = v0;
+        dst[(c * kDC + 8) * STRIDE] = v1;
+      }
     }
   }
 }
 
 // squared distances of the 4x4 pair sub-tile (rows rb..rb+3, cols cb..cb+3) over one staged chunk.  A warp covers
 // 16 rows x 32 cols (lane = 4 row quads x 8 col quads): both operand loads are a single 64/128-byte wavefront.
-__device__ __forceinline__ void sqdist_chunk(float (&acc)[4][4], const float* __restrict__ si, const float* __restrict__ sj,
+typedef unsigned long long u64;   // a packed pair of fp32 (sm_100 f32x2 arithmetic: FADD2 / FFMA2 in SASS)
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) { u64 r; asm("sub.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+  u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r;
+}
+__device__ __forceinline__ u64 dup2(float v) { u64 r; asm("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(v)); return r; }
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+
+// acc[p][h] = packed squared distances of pairs (row rb+p, cols cb+2h, cb+2h+1)
+__device__ __forceinline__ void sqdist_chunk(u64 (&acc)[4][2], const float* __restrict__ si, const float* __restrict__ sj,
                                              int rb, int cb) {
 #pragma unroll
   for (int d = 0; d < kDC; ++d) {
-    const float4 a4 = *reinterpret_cast<const float4*>(si + d * kSI + rb);
-    const float4 b4 = *reinterpret_cast<const float4*>(sj + d * kSJ + cb);
-    const float a[4] = {a4.x, a4.y, a4.z, a4.w}, b[4] = {b4.x, b4.y, b4.z, b4.w};
+    const ulonglong2 a01 = *reinterpret_cast<const ulonglong2*>(si + d * kSI + rb * 2);       // {a0,a0} {a1,a1}
+    const ulonglong2 a23 = *reinterpret_cast<const ulonglong2*>(si + d * kSI + rb * 2 + 4);   // {a2,a2} {a3,a3}
+    const ulonglong2 b4 = *reinterpret_cast<const ulonglong2*>(sj + d * kSJ + cb);            // {b0,b1} {b2,b3}
+    const u64 a[4] = {a01.x, a01.y, a23.x, a23.y}, b[2] = {b4.x, b4.y};
 #pragma unroll
     for (int p = 0; p < 4; ++p)
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const float df = a[p] - b[q];
-        acc[p][q] = fmaf(df, df, acc[p][q]);
+      for (int h = 0; h < 2; ++h) {
+        const u64 df = sub2(a[p], b[h]);
+        acc[p][h] = fma2(df, df, acc[p][h]);
       }
   }
 }
 
 // all chunks of one matrix kind present in the staged group: chunks [c0,c0+nc) of the list, x-type iff c < cx
-__device__ __forceinline__ void sqdist_group(float (&ax)[4][4], float (&az)[4][4], const float* si, const float* sj,
+__device__ __forceinline__ void sqdist_group(u64 (&ax)[4][2], u64 (&az)[4][2], const float* si, const float* sj,
                                              int cx, int c0, int nc, int rb, int cb) {
   for (int c = 0; c < nc; ++c) {
     if (c0 + c < cx) sqdist_chunk(ax, si + c * kDC * kSI, sj + c * kDC * kSJ, rb, cb);
@@ -105,20 +121,24 @@ __device__ __forceinline__ void sqdist_group(float (&ax)[4][4], float (&az)[4][4
   }
 }
 
-__device__ __forceinline__ void zero44(float (&a)[4][4]) {
+__device__ __forceinline__ void zero42(u64 (&a)[4][2]) {
 #pragma unroll
-  for (int p = 0; p < 4; ++p)
+  for (int p = 0; p < 4; ++p) a[p][0] = a[p][1] = 0ull;
+}
+__device__ __forceinline__ void unpack44(const u64 (&a)[4][2], float (&f)[4][4]) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) a[p][q] = 0.f;
+  for (int p = 0; p < 4; ++p) { unpack2(a[p][0], f[p][0], f[p][1]); unpack2(a[p][1], f[p][2], f[p][3]); }
 }
 
 // ---------------------------------------------------------------- pass 1: row sums
 // grid (row blocks, JS, N).  out: psx/psz [JS][N][k] partial sums (JS == 1: the sums themselves)
-__global__ void __launch_bounds__(kNT, 2)
+__global__ void __launch_bounds__(kNT, 3)
 ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int k, int Dx, int Dz,
                    int row0, int rows, int tps, float* __restrict__ psx, float* __restrict__ psz) {
-  __shared__ __align__(16) float si[kSD * kSI];
-  __shared__ __align__(16) float sj[kSD * kSJ];
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* si = reinterpret_cast<float*>(smem_raw);
+  float* sj = si + kSD * kSI;
+  float (*srs)[2][kTI] = reinterpret_cast<float (*)[2][kTI]>(sj + kSD * kSJ);
   const int n = blockIdx.z, js = blockIdx.y, N = gridDim.z;
   const int i0 = row0 + blockIdx.x * kTI;
   const int iend = (row0 + rows) < k ? (row0 + rows) : k;
@@ -132,25 +152,27 @@ ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int
   const NdivDims nd = ndiv_dims(Dx, Dz);
   const int nchunks = nd.cx + nd.cz;
   const bool hoist = nd.groups == 1;                  // all dims fit one staging round: stage the i rows once
-  if (hoist) stage_rows<kTI, kSI>(si, xg, zg, k, Dx, Dz, nd.cx, i0, 0, nchunks);
+  if (hoist) stage_rows<kTI, kSI, true>(si, xg, zg, k, Dx, Dz, nd.cx, i0, 0, nchunks);
   float rsx[4] = {0.f, 0.f, 0.f, 0.f}, rsz[4] = {0.f, 0.f, 0.f, 0.f};
   for (int jt = jt0; jt < jt1; ++jt) {
     const int j0 = jt * kTJ;
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
       const int cb = (wc * 2 + half) * 32 + lc * 4;
-      float ax[4][4], az[4][4];
-      zero44(ax); zero44(az);
+      u64 ax2[4][2], az2[4][2];
+      zero42(ax2); zero42(az2);
       for (int g = 0; g < nd.groups; ++g) {
         const int c0 = g * kSG, nc = (nchunks - c0) < kSG ? (nchunks - c0) : kSG;
         if (half == 0 || !hoist) {                    // hoisted case: the j rows are staged once per tile
           __syncthreads();
-          if (!hoist) stage_rows<kTI, kSI>(si, xg, zg, k, Dx, Dz, nd.cx, i0, c0, nc);
-          stage_rows<kTJ, kSJ>(sj, xg, zg, k, Dx, Dz, nd.cx, j0, c0, nc);
+          if (!hoist) stage_rows<kTI, kSI, true>(si, xg, zg, k, Dx, Dz, nd.cx, i0, c0, nc);
+          stage_rows<kTJ, kSJ, false>(sj, xg, zg, k, Dx, Dz, nd.cx, j0, c0, nc);
           __syncthreads();
         }
-        sqdist_group(ax, az, si, sj, nd.cx, c0, nc, rb, cb);
+        sqdist_group(ax2, az2, si, sj, nd.cx, c0, nc, rb, cb);
       }
+      float ax[4][4], az[4][4];
+      unpack44(ax2, ax); unpack44(az2, az);
 #pragma unroll
       for (int p = 0; p < 4; ++p)
 #pragma unroll
@@ -162,7 +184,6 @@ ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int
     }
   }
   // row sums: 8 column-quad lanes (shuffles), then the two column halves of the block (shared memory), fixed order
-  __shared__ float srs[2][2][kTI];
 #pragma unroll
   for (int p = 0; p < 4; ++p) {
     float vx = rsx[p], vz = rsz[p];
@@ -271,7 +292,7 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
     const int i = i0 + tid;
     sm.ri[tid] = i < k ? make_float2(1.f / __ldg(sxg + i), 1.f / __ldg(szg + i)) : make_float2(0.f, 0.f);
   }
-  if (hoist) stage_rows<kTI, kSI>(sm.si, xg, zg, k, Dx, Dz, nd.cx, i0, 0, nchunks);
+  if (hoist) stage_rows<kTI, kSI, true>(sm.si, xg, zg, k, Dx, Dz, nd.cx, i0, 0, nchunks);
   float gacc[NDP][4][8];
   float swp[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -288,14 +309,14 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
       const int cb = (wc * 2 + half) * 32 + lc * 4;
-      float ax[4][4], az[4][4];
-      zero44(ax); zero44(az);
+      u64 ax2[4][2], az2[4][2];
+      zero42(ax2); zero42(az2);
       for (int g = 0; g < nd.groups; ++g) {
         const int c0 = g * kSG, nc = (nchunks - c0) < kSG ? (nchunks - c0) : kSG;
         if (half == 0 || !hoist) {
           __syncthreads();                             // previous tile's GEMM / previous group's readers are done
-          if (!hoist) stage_rows<kTI, kSI>(sm.si, xg, zg, k, Dx, Dz, nd.cx, i0, c0, nc);
-          stage_rows<kTJ, kSJ>(sm.sj, xg, zg, k, Dx, Dz, nd.cx, j0, c0, nc);
+          if (!hoist) stage_rows<kTI, kSI, true>(sm.si, xg, zg, k, Dx, Dz, nd.cx, i0, c0, nc);
+          stage_rows<kTJ, kSJ, false>(sm.sj, xg, zg, k, Dx, Dz, nd.cx, j0, c0, nc);
           if (half == 0 && g == 0) {
             if (tid < kTJ) {
               const int j = j0 + tid;
@@ -321,8 +342,10 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
           }
           __syncthreads();
         }
-        sqdist_group(ax, az, sm.si, sm.sj, nd.cx, c0, nc, rb, cb);
+        sqdist_group(ax2, az2, sm.si, sm.sj, nd.cx, c0, nc, rb, cb);
       }
+      float ax[4][4], az[4][4];
+      unpack44(ax2, ax); unpack44(az2, az);
       if (edge) ndiv_epilogue<true, WITH_GRAD>(ax, az, sm, margin, rb, cb, iend - i0, k - j0, lsum);
       else      ndiv_epilogue<false, WITH_GRAD>(ax, az, sm, margin, rb, cb, kTI, kTJ, lsum);
     }
@@ -587,15 +610,17 @@ extern "C" int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, in
   const NdivPlan p = ndiv_plan(N, k, Dx);
   const NdivWs w = ndiv_ws(N, k, Dx);
   dim3 grid((rows + kTI - 1) / kTI, p.JS, N);
+  const size_t smem1 = (size_t)(kSD * kSI + kSD * kSJ + 4 * kTI) * sizeof(float);
+  NDP_CUDA(cudaFuncSetAttribute(ndiv_rowsum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
   if (p.JS == 1) {
-    ndiv_rowsum_kernel<<<grid, kNT, 0, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, sx, sz);
+    ndiv_rowsum_kernel<<<grid, kNT, smem1, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, sx, sz);
     NDP_LAUNCH_CHECK();
     return NDP_OK;
   }
   if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
   float* psx = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + w.part);
   float* psz = psx + (size_t)p.JS * N * k;
-  ndiv_rowsum_kernel<<<grid, kNT, 0, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, psx, psz);
+  ndiv_rowsum_kernel<<<grid, kNT, smem1, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, psx, psz);
   NDP_LAUNCH_CHECK();
   ndiv_rowsum_reduce_kernel<<<(N * rows + 255) / 256, 256, 0, s>>>(psx, psz, N, k, p.JS, row0, rows, sx, sz);
   NDP_LAUNCH_CHECK();

@@ -22,7 +22,10 @@ def timed(fn, reps=10):
 
 
 def main():
-    for N, k, Dx, Dz in ((1, 4096, 32, 16), (1, 4096, 256, 256), (56, 6, 4, 2), (1, 1024, 32, 16), (8, 4096, 32, 16)):
+    cfgs = ((1, 4096, 32, 16), (1, 4096, 256, 256), (56, 6, 4, 2), (1, 1024, 32, 16), (8, 4096, 32, 16))
+    if len(sys.argv) > 1 and sys.argv[1] == "cfg3":
+        cfgs = cfgs[:1]
+    for N, k, Dx, Dz in cfgs:
         x, z = synthetic.make_ndiv_inputs(N, k, Dx, Dz)
         x, z = x.cuda(), z.cuda()
         sx, sz = div.ndiv_rowsums(x, z)
