@@ -133,7 +133,7 @@ def run_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    Ks = 8192
+    Ks = CFG["K"]                       # the whole cfg2 candidate set per step (~0.6 s of CPU work per step)
     # warmup W (bounded) + K timed steps; each step = one plan over a Ks-candidate sample
     cpu_port_plan_rate(Ks, max(0, min(args.warmup, 2) - 1), threads)
     times, units = cpu_port_plan_rate(Ks, args.steps, threads)
@@ -144,7 +144,7 @@ def run_reference(args):
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": dict(workload="mpc_cfg2_K65536_T8_E128_H1024_nd2", **CFG),
            "cpu_baseline": {"value": v, "unit": "candidate-steps/s", "cores": threads, "kind": "port",
-                            "sample": f"{Ks} of {CFG['K']} candidates per step x T={CFG['T']}, oracle port of "
+                            "sample": f"all {Ks} candidates per step x T={CFG['T']} (no sub-sampling), oracle port of "
                                       f"mpc_eval.py:124-165 incl. python argmin, torch {torch.__version__} CPU fp32"},
            "e2e": {"value": v, "unit": "candidate-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(out)
@@ -156,6 +156,7 @@ def run_reference(args):
 K1_KERNEL = {"fp32": "rollout_f32_kernel", "f16": "rollout_tc_kernel<1>", "f16x2": "rollout_tc_kernel<2>",
              "f16x3": "rollout_tc_kernel<3>", "f16+refine": "rollout_tc_kernel<1>"}
 MMA_PASSES = {"fp32": 0, "f16": 1, "f16x2": 2, "f16x3": 3, "f16+refine": 1}
+NCU_TRAFFIC = {"rollout_tc_kernel<1>": 4.98e6, "rollout_f32_kernel": 5.69e6}   # bytes per launch, ncu (profiles/)
 POOL = 40   # distinct noise sets rotated through the timed region: 40 x 4.2 MB = 168 MB > 126 MB of L2
 
 
@@ -315,6 +316,7 @@ def run_gpu(args):
     pairs_ = []
     for _ in range(args.steps):
         flush()
+        torch.cuda._sleep(1_000_000)                   # the step's launches are queued before `a` is reached
         a, b = ev(), ev()
         a.record(); ndiv_step(); b.record()
         pairs_.append((a, b))
@@ -377,23 +379,32 @@ def run_gpu(args):
             "gpu_launches": int(n_launch),
             "clocks": clocks,
             "roofline": {"kernel": K1_KERNEL[prec], "bound": "tensor", "achieved": k1_tflops, "peak": pk["bf16"],
-                         "unit": "TFLOP/s", "frac": k1_tflops / pk["bf16"], "traffic": None,
+                         "unit": "TFLOP/s", "frac": k1_tflops / pk["bf16"],
+                         "traffic": NCU_TRAFFIC.get(K1_KERNEL[prec]),
+                         "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed "
+                                           "ncu --set full captures (profiles/r01_summary.md); algorithmic HBM bytes per "
+                                           "launch: 4.19 MB noise + 0.7 MB fp16 weights in, 1.3 MB cost/a0 out (stays in L2)",
                          "peak_source": pk["src"] + " bf16 burst (kernel timed alone, L2 flushed before each launch)",
                          "kernel_ms": k1_ms, "flop_per_candidate_step": F_ALG, "mma_passes": passes,
                          "issued_mma_frac": (k1_tflops * max(passes, 1) / pk["bf16"]) if passes else None,
                          "note": "achieved = algorithmic FLOP (666,112 per candidate-step) / CUDA-event time of the bulk "
                                  "rollout kernel; fp16 and bf16 share the tcgen05 kind::f16 rate"},
             "ndiv": {"metric": "ndiv_pairs_per_sec_fwd_bwd", "value": pairs / (ndiv_ms * 1e-3), "unit": "ordered pairs/s",
-                     "ms_per_step": ndiv_ms, "config": NDIV},
+                     "ms_per_step": ndiv_ms, "config": NDIV,
+                     "roofline": {"bound": "fp32 lanes (direct-difference form: 2 lane-ops per pair-dim and pass)",
+                                  "floor_ms": 2 * pairs * 2 * (NDIV["Dx"] + NDIV["Dz"]) / (148 * 128 * 1.965e9) * 1e3,
+                                  "survey_mufu_floor_ms": 0.0108,
+                                  "note": "floor_ms = 2 passes x pairs x 2(Dx+Dz) lane-ops / (148 SMs x 128 lanes x 1.965 GHz); "
+                                          "SURVEY 8d's 10.8 us floor assumes Gram-form distances on tensor cores"}},
             "parity": parity,
             "modes": modes,
         }
         if world == 1:
             t0 = time.perf_counter()
             threads = os.cpu_count() or 1
-            times, cu = cpu_port_plan_rate(8192, 3, threads)
+            times, cu = cpu_port_plan_rate(K, 10, threads)
             out["cpu_baseline"] = {"value": cu / min(times), "unit": "candidate-steps/s", "cores": threads, "kind": "port",
-                                   "sample": f"8192 of {K} candidates x T={T}, best of 3 after 1 warm-up, oracle port of "
+                                   "sample": f"all {K} candidates x T={T}, best of 10 plans after 1 warm-up, oracle port of "
                                              f"mpc_eval.py:124-165 incl. python argmin scan; {time.perf_counter() - t0:.1f}s"}
         emit(out)
     if world > 1:

@@ -112,7 +112,9 @@ int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
  * operands (their cost / a0 entries are overwritten with the refined values) and the selection is taken
  * from the refined costs.  verified[g] (nullable) = 1 when no candidate outside the refine list can
  * belong to the top-k given |estimate - refined| <= eps * cost (eps <= 0: default 1e-3); always 1 for the
- * non-refined precisions.  topk <= 64 in refine mode. */
+ * non-refined precisions.  When verified is given, goals that fail the proof are re-rolled over ALL K
+ * candidates with split operands and selected from those costs (device-side mask, no host round trip);
+ * they report verified[g] = 2.  With verified == NULL no fallback runs.  topk <= 64 in refine mode. */
 #define NDP_REFINE_R 128
 int ndp_plan_workspace_bytes(const ndp_planner* p, int G, int K, int topk, size_t* bytes);
 int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,

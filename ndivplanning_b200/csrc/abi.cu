@@ -374,9 +374,21 @@ static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const fl
     // the plan from the refined costs (ties -> lower candidate index, like the reference scan)
     if (int rc = select_packed(packed_c, G, R, topk, (long long)idx_base,
                                reinterpret_cast<unsigned long long*>(packed_min), topk_idx, topk_cost, s)) return rc;
-    if (verified)
+    if (verified) {
       if (int rc = verify_refine(est, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, K, R, topk,
                                  eps > 0.f ? eps : 1e-3f, verified, s)) return rc;
+      // Goals whose refined selection could NOT be proven exact are re-rolled over ALL K candidates with split
+      // operands and selected from those costs; decided on the device (skip mask = verified), no host round trip.
+      // CTAs / blocks of verified goals exit immediately.  verified: 1 = proven by the bound, 2 = full re-roll.
+      if (K > R) {
+        if (int rc = launch_rollout_tc(p->tc_refine, e0, goal, noise, G, K, p->d.T, cost, a0, nullptr, ws_roll, w.rollout,
+                                       s, nullptr, 0, nullptr, verified)) return rc;
+        if (int rc = select_masked(cost, G, K, topk, (long long)idx_base,
+                                   reinterpret_cast<unsigned long long*>(packed_min), topk_idx, topk_cost, ws_sel,
+                                   w.select, verified, s)) return rc;
+        if (int rc = mark_fallback(verified, G, s)) return rc;
+      }
+    }
   }
   return NDP_OK;
 }

@@ -271,6 +271,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) rollout_tc_kernel(const TcParam
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = blockIdx.x / p.tiles_per_goal;
   const int m0 = (blockIdx.x % p.tiles_per_goal) * 128;
+  if (p.skip && __ldg(p.skip + g)) return;             // CTA-uniform, before any barrier / TMEM allocation
 
   float4* S4 = reinterpret_cast<float4*>(smem + kOffState);
   uint8_t* ext_noise_hi = smem + kOffExt;
@@ -748,7 +749,7 @@ static int launch_np(const TcParams& tp, int grid, cudaStream_t s) {
 
 int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const float* noise, int G, int K, int T,
                       float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s,
-                      const int* list, int R, unsigned long long* packed_c) {
+                      const int* list, int R, unsigned long long* packed_c, const int* skip) {
   const size_t need = (size_t)G * P->gext_stride;
   if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
   NDP_CHECK_ARG(((uintptr_t)ws & 15) == 0, "rollout_score: workspace must be 16-byte aligned");
@@ -759,7 +760,7 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
   tp.stream = P->stream; tp.items = P->items; tp.gext = reinterpret_cast<const uint8_t*>(ws);
   tp.gext_stride = P->gext_stride; tp.e0 = e0; tp.goal = goal; tp.noise = noise; tp.cost = cost; tp.a0 = a0;
   tp.state_T = state_T; tp.G = G; tp.K = K; tp.T = T; tp.nd = P->nd; tp.n_items = P->n_items;
-  tp.list = list; tp.R = R; tp.packed_c = packed_c;
+  tp.list = list; tp.R = R; tp.packed_c = packed_c; tp.skip = skip;
   tp.tiles_per_goal = ((list ? R : K) + 127) / 128; tp.n_hid_chunks = P->n_chunks;
   const long long grid = (long long)G * tp.tiles_per_goal;
   NDP_CHECK_ARG(grid <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");

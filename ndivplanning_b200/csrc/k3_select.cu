@@ -76,7 +76,9 @@ select_kernel(const float* __restrict__ cost, const unsigned long long* __restri
               int K, int chunk_len, int topk, int final_stage, long long idx_base,
               unsigned long long* __restrict__ out_min,     // [G, chunks] or [G]
               unsigned long long* __restrict__ out_topk,    // [G, chunks, topk] partial
-              int* __restrict__ topk_idx, float* __restrict__ topk_cost) {
+              int* __restrict__ topk_idx, float* __restrict__ topk_cost,
+              const int* __restrict__ skip) {          // skip[g] != 0: goal g keeps its previous results
+  if (skip && skip[blockIdx.y]) return;
   __shared__ unsigned long long s_buf[kSelBuf];
   __shared__ unsigned long long s_warpmin[kSelThreads / 32];
   __shared__ unsigned long long s_thr;
@@ -219,9 +221,9 @@ extern "C" int ndp_select_workspace_bytes(int G, int K, int topk, size_t* bytes)
   return NDP_OK;
 }
 
-extern "C" int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
-                          uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
-                          void* ws, size_t ws_bytes, void* stream) {
+static int select_impl(const float* cost, int G, int K, int topk, int64_t idx_base,
+                       uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
+                       void* ws, size_t ws_bytes, void* stream, const int* skip) {
   NDP_CHECK_ARG(G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "select: bad G/K/topk (topk<=128)");
   NDP_CHECK_ARG(G == 0 || ((cost || K == 0) && packed_min), "select: null cost/packed_min");
   NDP_CHECK_ARG(idx_base >= 0 && idx_base + (int64_t)K <= 0xFFFFFFFFll, "select: global index must fit 32 bits");
@@ -234,7 +236,7 @@ extern "C" int ndp_select(const float* cost, int G, int K, int topk, int64_t idx
   auto* pm = reinterpret_cast<unsigned long long*>(packed_min);
   if (chunks <= 1) {
     select_kernel<0><<<dim3(1, G), kSelThreads, 0, s>>>(cost, nullptr, K, len > 0 ? len : kSelTile, topk, 1,
-                                                        (long long)idx_base, pm, nullptr, topk_idx, topk_cost);
+                                                        (long long)idx_base, pm, nullptr, topk_idx, topk_cost, skip);
     NDP_LAUNCH_CHECK();
     return NDP_OK;
   }
@@ -243,29 +245,50 @@ extern "C" int ndp_select(const float* cost, int G, int K, int topk, int64_t idx
   auto* part_min = reinterpret_cast<unsigned long long*>(ws);
   auto* part_topk = part_min + (size_t)G * chunks;
   select_kernel<0><<<dim3(chunks, G), kSelThreads, 0, s>>>(cost, nullptr, K, len, topk, 0, 0, part_min,
-                                                           part_topk, nullptr, nullptr);
+                                                           part_topk, nullptr, nullptr, skip);
   NDP_LAUNCH_CHECK();
   // stage 2: argmin over partial mins and top-k over partial lists (entries keep LOCAL indices)
   if (topk > 0) {
     // merge lists: the min of the merged list equals the min of mins, so one launch does both
     select_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, part_topk, chunks * topk,
                                                         ((chunks * topk + kSelTile - 1) / kSelTile) * kSelTile,
-                                                        topk, 1, (long long)idx_base, pm, nullptr, topk_idx, topk_cost);
+                                                        topk, 1, (long long)idx_base, pm, nullptr, topk_idx, topk_cost, skip);
   } else {
     select_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, part_min, chunks,
-                                                        kSelTile, 0, 1, (long long)idx_base, pm, nullptr, nullptr, nullptr);
+                                                        kSelTile, 0, 1, (long long)idx_base, pm, nullptr, nullptr, nullptr, skip);
   }
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
 
+extern "C" int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
+                          uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
+                          void* ws, size_t ws_bytes, void* stream) {
+  return select_impl(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws, ws_bytes, stream, nullptr);
+}
+
 namespace ndp {
+// ndp_select restricted to the goals with skip[g] == 0 (device-side mask, no host decision)
+int select_masked(const float* cost, int G, int K, int topk, long long idx_base, unsigned long long* pm, int* topk_idx,
+                  float* topk_cost, void* ws, size_t ws_bytes, const int* skip, cudaStream_t s) {
+  return select_impl(cost, G, K, topk, idx_base, reinterpret_cast<uint64_t*>(pm), topk_idx, topk_cost, ws, ws_bytes,
+                     (void*)s, skip);
+}
+__global__ void mark_fallback_kernel(int* __restrict__ verified, int G) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g < G && verified[g] == 0) verified[g] = 2;      // 2 = recomputed over all K with split operands
+}
+int mark_fallback(int* verified, int G, cudaStream_t s) {
+  mark_fallback_kernel<<<(G + 127) / 128, 128, 0, s>>>(verified, G);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
 // selection over packed (okey(cost)<<32 | index) keys, n <= 1024 per goal: one block per goal
 int select_packed(const unsigned long long* packed, int G, int n, int topk, long long idx_base,
                   unsigned long long* pm, int* topk_idx, float* topk_cost, cudaStream_t s) {
   NDP_CHECK_ARG(n >= 1 && n <= kSelTile && topk <= 128 && G <= 65535, "select_packed: bad sizes");
   select_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, packed, n, kSelTile, topk, 1, idx_base, pm, nullptr,
-                                                      topk_idx, topk_cost);
+                                                      topk_idx, topk_cost, nullptr);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
@@ -321,7 +344,7 @@ shard_merge_kernel(const unsigned long long* __restrict__ rec, int P, int G, int
     for (int r = 0; r < P; ++r) {                        // strict '<': lowest rank == lowest index range wins ties
       const unsigned long long* q = rec + ((size_t)r * G + g) * W;
       if (q[0] < m) { m = q[0]; owner = r; }
-      ok &= (int)(q[3] & 1ull);
+      ok &= (q[3] != 0ull) ? 1 : 0;
     }
     if (m == kInvalidPacked) owner = 0;                  // nothing valid anywhere: global index 0 (mpc_eval.py:122,159)
     const unsigned long long* q = rec + ((size_t)owner * G + g) * W;

@@ -65,6 +65,7 @@ struct TcParams {
   const int* list;
   unsigned long long* packed_c;
   int R;
+  const int* skip;          // nullable [G]: CTAs of goals with skip[g] != 0 exit at once (fallback pass)
   int G, K, T, nd, n_items, tiles_per_goal, n_hid_chunks;
 };
 
@@ -75,7 +76,11 @@ void tc_plan_destroy(TcPlan* p);
 size_t tc_workspace_bytes(const TcPlan* p, int G);
 int launch_rollout_tc(const TcPlan* plan, const float* e0, const float* goal, const float* noise, int G, int K,
                       int T, float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s,
-                      const int* list = nullptr, int R = 0, unsigned long long* packed_c = nullptr);
+                      const int* list = nullptr, int R = 0, unsigned long long* packed_c = nullptr,
+                      const int* skip = nullptr);
+int select_masked(const float* cost, int G, int K, int topk, long long idx_base, unsigned long long* pm, int* topk_idx,
+                  float* topk_cost, void* ws, size_t ws_bytes, const int* skip, cudaStream_t s);
+int mark_fallback(int* verified, int G, cudaStream_t s);
 
 int select_packed(const unsigned long long* packed, int G, int n, int topk, long long idx_base,
                   unsigned long long* pm, int* topk_idx, float* topk_cost, cudaStream_t s);

@@ -271,3 +271,65 @@ def test_plan_ring_equals_plain_plan(cuda, prec, G, K, T, topk):
                 assert torch.equal(a, b)
     with pytest.raises(Exception):
         ring.plan(inputs[0][0], inputs[0][1], inputs[0][2][:, :, : K - 1])
+
+
+@pytest.mark.parametrize("prec", ["fp32", "f16+refine"])
+def test_closed_loop_sweep_matches_oracle_loop(cuda, prec):
+    """N1 driver: G goals swept together on the device == the reference's receding-horizon loop
+    (mpc_eval.py:112-176, oracle restatement) run goal by goal with the same noise, incl. the truncated
+    horizon near the end (:127)."""
+    from ndivplanning_b200.closed_loop import ClosedLoopSweep
+    G, K, Th, S, nd, E, H = 3, 256, 3, 5, 2, 128, 256
+    gen, fwd = synthetic.make_models(nd=nd, E=E, H=H)
+    og, of = _oracle_models(gen, fwd, nd, E, H)
+    torch.manual_seed(11)
+    start, goal = torch.randn(G, E), torch.randn(G, E)
+    fut = torch.randn(S, G, E)
+    aref = torch.randn(S, G, 4)
+    noises = [torch.rand(min(Th, S - s), G, K, nd) for s in range(S)]
+    sw = ClosedLoopSweep(gen, fwd, horizon=Th, rollouts=K, precision=prec)
+    res = sw.run(start.cuda(), goal.cuda(), S, state_fut=fut.cuda(), actions_ref=aref.cuda(),
+                 noise_fn=lambda s, T: noises[s])
+    assert res.candidate_steps == G * K * sum(min(Th, S - s) for s in range(S))
+    assert res.verified.cpu().min() >= 1          # 1 = proven by the bound, 2 = full split-operand re-roll
+    for g in range(G):
+        cur = start[g]
+        for s in range(S):
+            ref = O.mpc_plan(og, of, cur, goal[g], noises[s][:, g])
+            assert int(res.best_idx[s, g]) == ref["best_idx"], (g, s)
+            np.testing.assert_allclose(res.actions[s, g].cpu().numpy(), ref["best_action"].numpy(), rtol=2e-3, atol=1e-5)
+            with torch.no_grad():
+                cur = of(cur.view(1, E, 1, 1), ref["best_action"][None]).view(E)
+            np.testing.assert_allclose(res.states[s, g].cpu().numpy(), cur.numpy(), rtol=2e-3, atol=2e-4)
+            np.testing.assert_allclose(float(res.image_err[s, g]), float(((cur - fut[s, g]) ** 2).mean()), rtol=2e-3)
+    want_ae = ((aref - res.actions.cpu()) ** 2).mean(dim=(0, 2))
+    np.testing.assert_allclose(res.action_err.cpu().numpy(), want_ae.numpy(), rtol=1e-5)
+    # device sampler path: runs without host noise and is reproducible under a seeded device generator
+    g1 = torch.Generator(device="cuda").manual_seed(5)
+    g2 = torch.Generator(device="cuda").manual_seed(5)
+    r1 = sw.run(start.cuda(), goal.cuda(), S, generator=g1)
+    r2 = sw.run(start.cuda(), goal.cuda(), S, generator=g2)
+    assert torch.equal(r1.best_idx, r2.best_idx) and torch.equal(r1.actions, r2.actions)
+
+
+def test_refine_fallback_rerolls_unverified_goals(cuda):
+    """Goals whose refined selection cannot be proven exact (costs too close: short horizon, weak separation)
+    are re-rolled over all K with split operands on the device: verified == 2 and the goal's costs, argmin and
+    top-k are exactly those of the f16x3 planner; verified == 1 goals keep the refined plan."""
+    from ndivplanning_b200 import FusedPlanner
+    G, K, T, topk = 8, 512, 1, 8
+    gen, fwd = synthetic.make_models(nd=2, E=128, H=256, sep=1.0)
+    e0, goal, noise = synthetic.make_plan_inputs(G, K, T, 2, 128, seed=4)
+    e0, goal, noise = e0.cuda(), goal.cuda(), noise.cuda()
+    plan = FusedPlanner(gen, fwd, horizon=T, precision="f16+refine").plan(e0, goal, noise, topk=topk)
+    full = FusedPlanner(gen, fwd, horizon=T, precision="f16x3").plan(e0, goal, noise, topk=topk)
+    ver = plan.verified.cpu().tolist()
+    assert set(ver) <= {1, 2} and 2 in ver, ver
+    for g in range(G):
+        if ver[g] == 2:
+            assert torch.equal(plan.cost[g], full.cost[g])
+            assert int(plan.best_idx[g]) == int(full.best_idx[g])
+            assert torch.equal(plan.topk_idx[g], full.topk_idx[g]) and torch.equal(plan.topk_cost[g], full.topk_cost[g])
+            assert torch.equal(plan.best_action[g], full.best_action[g])
+        else:
+            assert set(plan.topk_idx[g].tolist()) == set(full.topk_idx[g].tolist())
