@@ -112,9 +112,11 @@ int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
  * operands (their cost / a0 entries are overwritten with the refined values) and the selection is taken
  * from the refined costs.  verified[g] (nullable) = 1 when no candidate outside the refine list can
  * belong to the top-k given |estimate - refined| <= eps * cost (eps <= 0: default 1e-3); always 1 for the
- * non-refined precisions.  When verified is given, goals that fail the proof are re-rolled over ALL K
- * candidates with split operands and selected from those costs (device-side mask, no host round trip);
- * they report verified[g] = 2.  With verified == NULL no fallback runs.  topk <= 64 in refine mode. */
+ * non-refined precisions.  topk <= 64 in refine mode.
+ * ndp_plan_fallback (same arguments, call after ndp_plan_select / _refine on the same stream): goals with
+ * verified[g] == 0 are re-rolled over ALL K candidates with split operands and selected from those costs;
+ * the decision is a device-side mask (no host round trip; thread blocks of verified goals exit at once) and
+ * such goals then report verified[g] = 2.  No-op for the non-refined precisions. */
 #define NDP_REFINE_R 128
 int ndp_plan_workspace_bytes(const ndp_planner* p, int G, int K, int topk, size_t* bytes);
 int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
@@ -127,6 +129,10 @@ int ndp_plan_select(ndp_planner* p, const float* e0, const float* goal, const fl
  *   _refine: selection of the refine list, re-roll, selection from refined costs, verification (no-op when
  *            not refining).
  * The caller orders _refine after _bulk (event) and keeps the workspace alive across both. */
+int ndp_plan_fallback(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
+                      int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
+                      int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
+                      void* stream);
 int ndp_plan_select_bulk(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
                          int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
                          int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,

@@ -38,6 +38,7 @@ _PROTOS = {
     "ndp_select": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_workspace_bytes": (_i, [_vp, _i, _i, _i, C.POINTER(_sz)]),
     "ndp_plan_select": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_plan_fallback": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_select_bulk": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_select_refine": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_gather_best_action": (_i, [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),

@@ -364,6 +364,17 @@ static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const fl
       return NDP_OK;
     }
   }
+  if ((phase & 4) && p->tc_refine && verified && K > R) {
+    // Exact fallback: goals whose refined selection could NOT be proven (verified[g] == 0) are re-rolled over ALL K
+    // candidates with split operands and selected from those costs; decided on the device (skip mask = verified),
+    // no host round trip.  CTAs / blocks of verified goals exit immediately.  1 = proven by the bound, 2 = re-rolled.
+    if (int rc = launch_rollout_tc(p->tc_refine, e0, goal, noise, G, K, p->d.T, cost, a0, nullptr, ws_roll, w.rollout,
+                                   s, nullptr, 0, nullptr, verified)) return rc;
+    if (int rc = select_masked(cost, G, K, topk, (long long)idx_base, reinterpret_cast<unsigned long long*>(packed_min),
+                               topk_idx, topk_cost, ws_sel, w.select, verified, s)) return rc;
+    if (int rc = mark_fallback(verified, G, s)) return rc;
+    return NDP_OK;
+  }
   if ((phase & 2) && p->tc_refine) {
     // the R best ESTIMATES per goal (local indices, ascending; -1 padded when K < R)
     if (int rc = ndp_select(cost, G, K, R, 0, reinterpret_cast<uint64_t*>(pm_est), list, est, ws_sel, w.select, stream)) return rc;
@@ -377,17 +388,6 @@ static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const fl
     if (verified) {
       if (int rc = verify_refine(est, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, K, R, topk,
                                  eps > 0.f ? eps : 1e-3f, verified, s)) return rc;
-      // Goals whose refined selection could NOT be proven exact are re-rolled over ALL K candidates with split
-      // operands and selected from those costs; decided on the device (skip mask = verified), no host round trip.
-      // CTAs / blocks of verified goals exit immediately.  verified: 1 = proven by the bound, 2 = full re-roll.
-      if (K > R) {
-        if (int rc = launch_rollout_tc(p->tc_refine, e0, goal, noise, G, K, p->d.T, cost, a0, nullptr, ws_roll, w.rollout,
-                                       s, nullptr, 0, nullptr, verified)) return rc;
-        if (int rc = select_masked(cost, G, K, topk, (long long)idx_base,
-                                   reinterpret_cast<unsigned long long*>(packed_min), topk_idx, topk_cost, ws_sel,
-                                   w.select, verified, s)) return rc;
-        if (int rc = mark_fallback(verified, G, s)) return rc;
-      }
     }
   }
   return NDP_OK;
@@ -398,6 +398,13 @@ extern "C" int ndp_plan_select(ndp_planner* p, const float* e0, const float* goa
                                int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
                                void* stream) {
   return plan_select_impl(3, p, e0, goal, noise, G, K, topk, idx_base, eps, cost, a0, packed_min, topk_idx, topk_cost,
+                          verified, ws, ws_bytes, stream);
+}
+extern "C" int ndp_plan_fallback(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G, int K,
+                                 int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
+                                 int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
+                                 void* stream) {
+  return plan_select_impl(4, p, e0, goal, noise, G, K, topk, idx_base, eps, cost, a0, packed_min, topk_idx, topk_cost,
                           verified, ws, ws_bytes, stream);
 }
 extern "C" int ndp_plan_select_bulk(ndp_planner* p, const float* e0, const float* goal, const float* noise, int G,

@@ -131,13 +131,15 @@ class FusedPlanner:
 
     # ---- K1 + K3 (+ refine) + gather: one C call for rollout and selection ------------------------------
     def plan(self, e0, goal, noise, topk: int = 0, idx_base: int = 0, want_state=False, eps: float = 0.0,
-             refine_stream=None) -> Plan:
+             refine_stream=None, fallback: bool = True) -> Plan:
         """mpc_eval.py:124-165.  precision "f16+refine": all K candidates are scored single-pass, the 128 best
         estimates are re-rolled with split operands and the plan is chosen from those fp32-grade costs;
         `Plan.verified[g]` tells whether that provably equals choosing from exact costs of all K.
         `refine_stream`: run the (single-tile, latency-bound) refine half on that stream so it overlaps the
         bulk half of the next plan; the returned Plan carries a `ready` event — call `plan.wait()` before
-        reading it from another stream."""
+        reading it from another stream.
+        `fallback` (f16+refine): goals whose refined selection cannot be proven exact are re-rolled over all K with
+        split operands on the device (ndp_plan_fallback; `verified` 2 instead of 0)."""
         if want_state:
             if self.precision == "f16+refine":
                 raise _lib.NdpError("want_state is not available with precision 'f16+refine'")
@@ -174,6 +176,8 @@ class FusedPlanner:
                     refine_stream.wait_stream(main)
                     side = C.c_void_p(refine_stream.cuda_stream)
                     check(lib().ndp_plan_select_refine(*args, side))
+                    if fallback:
+                        check(lib().ndp_plan_fallback(*args, side))
                     check(lib().ndp_gather_best_action(ptr(a0), ptr(packed), G, K, idx_base, ptr(best_action),
                                                        ptr(best_idx), side))
                 for t_ in (e0c, gc, nz, cost, a0, packed, tk_idx, tk_cost, verified, ws, best_action, best_idx):
@@ -184,6 +188,8 @@ class FusedPlanner:
                 return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified, ready)
             with torch.cuda.device(dev):
                 check(lib().ndp_plan_select(*args, stream_ptr(dev)))
+                if fallback and self.precision == "f16+refine":
+                    check(lib().ndp_plan_fallback(*args, stream_ptr(dev)))
                 check(lib().ndp_gather_best_action(ptr(a0), ptr(packed), G, K, idx_base, ptr(best_action),
                                                    ptr(best_idx), stream_ptr(dev)))
             return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified)
@@ -195,9 +201,9 @@ class FusedPlanner:
         return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified)
 
     def ring(self, G: int, K: int, topk: int = 0, depth: int = 4, n_streams: int = 2, idx_base: int = 0,
-             comm=None) -> "PlanRing":
+             comm=None, fallback: bool = False) -> "PlanRing":
         """pre-allocated plan slots + side streams for a steady planning loop (see PlanRing)"""
-        return PlanRing(self, G, K, topk, depth, n_streams, idx_base, comm)
+        return PlanRing(self, G, K, topk, depth, n_streams, idx_base, comm, fallback)
 
     # ---- single-call module semantics (drop-in for generator(z) / fwd_model(state, a)) -------
     def generator(self, z):
@@ -221,7 +227,7 @@ class FusedPlanner:
 
 class _Slot:
     __slots__ = ("cost", "a0", "packed", "tk_idx", "tk_cost", "verified", "ws", "best_action", "best_idx", "ready",
-                 "bulk_done", "inputs", "used", "tail", "gather", "plan", "rec", "rec_all", "pack", "merge")
+                 "bulk_done", "inputs", "used", "tail", "gather", "plan", "rec", "rec_all", "pack", "merge", "head", "side")
 
 
 class PlanRing:
@@ -239,8 +245,12 @@ class PlanRing:
     Reusing a slot makes the caller's stream wait (on the device) for the slot's previous tail."""
 
     def __init__(self, planner: FusedPlanner, G: int, K: int, topk: int = 0, depth: int = 4, n_streams: int = 2,
-                 idx_base: int = 0, comm=None):
+                 idx_base: int = 0, comm=None, fallback: bool = False):
         dev = planner.device
+        # fallback=True appends ndp_plan_fallback to every tail.  Off by default in the pipelined loop: its (instantly
+        # exiting) 213 KB-smem thread blocks can only be placed on SMs a bulk rollout has vacated, which stalls the
+        # tail and steals slots from the next rollout; read `plan.verified` and call `ring.fallback(plan)` instead.
+        self.fallback_always = fallback
         self.planner, self.G, self.K, self.topk, self.depth, self.idx_base, self.comm = \
             planner, G, K, topk, depth, idx_base, comm
         self.count = 0
@@ -313,11 +323,14 @@ class PlanRing:
         L = lib()
         head = (pl._h, e0c.data_ptr(), gc.data_ptr(), nz.data_ptr())
         sp = C.c_void_p(side.cuda_stream)
+        s.head, s.side = head, side
         with torch.cuda.device(dev):
             check(L.ndp_plan_select_bulk(*head, *s.tail, C.c_void_p(bulk.cuda_stream)))
             s.bulk_done.record(bulk)
             side.wait_event(s.bulk_done)
             check(L.ndp_plan_select_refine(*head, *s.tail, sp))
+            if self.fallback_always and pl.precision == "f16+refine":
+                check(L.ndp_plan_fallback(*head, *s.tail, sp))
             check(L.ndp_gather_best_action(*s.gather, sp))
             if self.comm is not None:
                 check(L.ndp_shard_pack(*s.pack, sp))
@@ -325,3 +338,19 @@ class PlanRing:
                 check(L.ndp_shard_merge(*s.merge, sp))
             s.ready.record(side)
         return s.plan
+
+    def fallback(self, plan: Plan) -> Plan:
+        """Consumer-initiated exact path for a plan of this ring whose `verified` holds zeros (f16+refine): re-rolls the
+        unverified goals over all K with split operands on the plan's tail stream (ndp_plan_fallback), gathers the
+        action again and re-records `plan.ready`.  Call before 3 further plans have been issued."""
+        if self.comm is not None:
+            raise _lib.NdpError("ring.fallback is not available on a sharded ring; build it with fallback=True")
+        for s in self.slots:
+            if s.plan is plan and s.used:
+                sp = C.c_void_p(s.side.cuda_stream)
+                with torch.cuda.device(self.planner.device):
+                    check(lib().ndp_plan_fallback(*s.head, *s.tail, sp))
+                    check(lib().ndp_gather_best_action(*s.gather, sp))
+                    s.ready.record(s.side)
+                return plan
+        raise _lib.NdpError("plan does not belong to this ring (or its slot has been reused)")

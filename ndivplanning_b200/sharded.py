@@ -142,11 +142,11 @@ class ShardedPlanner:
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.comm = Comm(planner.device, group)
 
-    def ring(self, G: int, K_total: int, topk: int = 0, depth: int = 4, n_streams: int = 2):
+    def ring(self, G: int, K_total: int, topk: int = 0, depth: int = 4, n_streams: int = 2, fallback: bool = False):
         """PlanRing over this rank's shard of K_total candidates: allocation-free steady-state loop with the
         refine tail, the record exchange (on libndivplan's own communicator) and the merge on side streams"""
         start, count = shard_range(K_total, self.rank, self.world)
-        return self.planner.ring(G, count, topk, depth, n_streams, idx_base=start, comm=self.comm)
+        return self.planner.ring(G, count, topk, depth, n_streams, idx_base=start, comm=self.comm, fallback=fallback)
 
     def plan(self, e0, goal, noise_local, K_total: int, topk: int = 0, refine_stream=None) -> Plan:
         start, count = shard_range(K_total, self.rank, self.world)

@@ -263,7 +263,7 @@ def test_plan_ring_equals_plain_plan(cuda, prec, G, K, T, topk):
     got[-1] = tuple(t.clone() if t is not None else None for t in (q.best_idx, q.best_action, q.packed_min, q.topk_idx,
                                                                    q.topk_cost, q.verified, q.cost))
     for (e0, goal, noise), g in zip(inputs, got):
-        w = pl.plan(e0, goal, noise, topk=topk)
+        w = pl.plan(e0, goal, noise, topk=topk, fallback=False)      # the ring leaves unverified goals flagged
         want = (w.best_idx, w.best_action, w.packed_min, w.topk_idx, w.topk_cost, w.verified, w.cost)
         for a, b in zip(g, want):
             assert (a is None) == (b is None)
@@ -333,3 +333,22 @@ def test_refine_fallback_rerolls_unverified_goals(cuda):
             assert torch.equal(plan.best_action[g], full.best_action[g])
         else:
             assert set(plan.topk_idx[g].tolist()) == set(full.topk_idx[g].tolist())
+
+
+def test_ring_fallback_consumer_initiated(cuda):
+    """PlanRing leaves unverified goals flagged (verified == 0); ring.fallback(plan) turns them into the exact plan"""
+    from ndivplanning_b200 import FusedPlanner
+    G, K, T, topk = 8, 512, 1, 8
+    gen, fwd = synthetic.make_models(nd=2, E=128, H=256, sep=1.0)
+    e0, goal, noise = (t.cuda() for t in synthetic.make_plan_inputs(G, K, T, 2, 128, seed=4))
+    pl = FusedPlanner(gen, fwd, horizon=T, precision="f16+refine")
+    ring = pl.ring(G, K, topk)
+    p = ring.plan(e0, goal, noise).wait()
+    torch.cuda.synchronize()
+    assert 0 in p.verified.cpu().tolist()
+    ring.fallback(p).wait()
+    want = pl.plan(e0, goal, noise, topk=topk)
+    torch.cuda.synchronize()
+    assert torch.equal(p.verified, want.verified) and 2 in p.verified.cpu().tolist()
+    assert torch.equal(p.best_idx, want.best_idx) and torch.equal(p.best_action, want.best_action)
+    assert torch.equal(p.topk_idx, want.topk_idx) and torch.equal(p.cost, want.cost)
