@@ -169,12 +169,17 @@ int ndp_shard_merge(const uint64_t* rec_all, int P, int G, int topk, uint64_t* p
  * Row-block sharding (multi-GPU): rows [row0,row0+rows) of every group are owned by the
  * caller; sx/sz must hold ALL rows before ndp_ndiv_loss_grad (allgather in between).
  * ws: ndp_ndiv_workspace_bytes() bytes, used by both passes (partial sums of the column splits). */
-int ndp_ndiv_workspace_bytes(int N, int k, int Dx, size_t* bytes);
+int ndp_ndiv_workspace_bytes(int N, int k, int Dx, int Dz, size_t* bytes);
 int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz,
                      int row0, int rows, float* sx, float* sz, void* ws, size_t ws_bytes, void* stream);
 int ndp_ndiv_loss_grad(const float* x, const float* z, const float* sx, const float* sz,
                        int N, int k, int Dx, int Dz, float margin, int row0, int rows,
                        float* loss, float* grad_x, void* ws, size_t ws_bytes, void* stream);
+/* both passes over all rows in one call (single-GPU autograd step; operands are packed once):
+ * sx, sz [N,k] out, loss[0], grad_x nullable */
+int ndp_ndiv_forward_backward(const float* x, const float* z, int N, int k, int Dx, int Dz, float margin,
+                              float* sx, float* sz, float* loss, float* grad_x, void* ws, size_t ws_bytes,
+                              void* stream);
 /* compute_pairwise (normalise=0, diversity.py:8-9) / compute_pair_distance
  * (normalise=1, diversity.py:12-19): v [N,k,C] -> out [N,k,k] */
 int ndp_pairwise(const float* v, int N, int k, int C, int normalise, float* out, void* stream);

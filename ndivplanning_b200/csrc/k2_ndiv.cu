@@ -134,7 +134,9 @@ __device__ __forceinline__ void unpack44(const u64 (&a)[4][2], float (&f)[4][4])
 // grid (row blocks, JS, N).  out: psx/psz [JS][N][k] partial sums (JS == 1: the sums themselves)
 __global__ void __launch_bounds__(kNT, 3)
 ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int k, int Dx, int Dz,
-                   int row0, int rows, int tps, float* __restrict__ psx, float* __restrict__ psz) {
+                   int row0, int rows, int tps, float* __restrict__ psx, float* __restrict__ psz,
+                   const int* __restrict__ run_if) {     // nullable: the whole grid exits when *run_if == 0
+  if (run_if && *run_if == 0) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* si = reinterpret_cast<float*>(smem_raw);
   float* sj = si + kSD * kSI;
@@ -207,7 +209,9 @@ ndiv_rowsum_kernel(const float* __restrict__ x, const float* __restrict__ z, int
 
 // out[n][i] = sum_js part[js][n][i] in fixed order, rows [row0,row0+rows)
 __global__ void ndiv_rowsum_reduce_kernel(const float* __restrict__ psx, const float* __restrict__ psz, int N, int k,
-                                          int JS, int row0, int rows, float* __restrict__ sx, float* __restrict__ sz) {
+                                          int JS, int row0, int rows, float* __restrict__ sx, float* __restrict__ sz,
+                                          const int* __restrict__ run_if) {
+  if (run_if && *run_if == 0) return;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= N * rows) return;
   const int n = t / rows, i = row0 + t % rows;
@@ -267,7 +271,9 @@ template <int NDP, bool WITH_GRAD>
 __global__ void __launch_bounds__(kNT, NDP == 1 ? 2 : 1)
 ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, const float* __restrict__ sx,
                       const float* __restrict__ sz, int k, int Dx, int Dz, float margin, int row0, int rows,
-                      int tps, int dpass0, float* __restrict__ loss_part, float* __restrict__ gpart) {
+                      int tps, int dpass0, float* __restrict__ loss_part, float* __restrict__ gpart,
+                      const int* __restrict__ run_if) {
+  if (run_if && *run_if == 0) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   NdivSmem2& sm = *reinterpret_cast<NdivSmem2*>(smem_raw);
   const int n = blockIdx.z, js = blockIdx.y, N = gridDim.z;
@@ -445,7 +451,9 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
 
 // grad[n][i][d] = sum_js gpart[js][n][i][d], rows [row0,row0+rows), dims [d0,d1)
 __global__ void ndiv_grad_reduce_kernel(const float* __restrict__ gpart, int N, int k, int Dx, int JS, int row0, int rows,
-                                        int d0, int d1, float* __restrict__ grad) {
+                                        int d0, int d1, float* __restrict__ grad,
+                                        const int* __restrict__ run_if) {
+  if (run_if && *run_if == 0) return;
   const int nd = d1 - d0;
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (size_t)N * rows * nd) return;
@@ -458,7 +466,9 @@ __global__ void ndiv_grad_reduce_kernel(const float* __restrict__ gpart, int N, 
   grad[off] = a;
 }
 
-__global__ void ndiv_finalize_kernel(const float* __restrict__ part, int n, float* __restrict__ loss) {
+__global__ void ndiv_finalize_kernel(const float* __restrict__ part, int n, float* __restrict__ loss,
+                                     const int* __restrict__ run_if) {
+  if (run_if && *run_if == 0) return;
   __shared__ float s[256];
   float t = 0.f;
   for (int i = threadIdx.x; i < n; i += 256) t += part[i];
@@ -556,6 +566,17 @@ __global__ void pairwise_bwd_kernel(const float* __restrict__ v, const float* __
 using namespace ndp;
 
 namespace ndp {
+// ---- tensor-core Gram fast path (k2_ndiv_tc.cu)
+bool gram_eligible(int N, int k, int Dx, int Dz, int row0);
+size_t gram_ws_bytes(int N, int k, int Dx, int Dz);
+int gram_loss_parts(int N, int k);
+int gram_js(int N, int k);
+int gram_prepare(const float* x, const float* z, int N, int k, int Dx, int Dz, void* ws, cudaStream_t s);
+int* gram_flag(void* ws);
+int gram_rowsums(int N, int k, int Dx, int Dz, int row0, int rows, void* ws, float* psx, float* psz, cudaStream_t s);
+int gram_loss_grad(const float* x, const float* sx, const float* sz, int N, int k, int Dx, int Dz, float margin, int row0,
+                   int rows, void* ws, float* loss_part, float* gpart, cudaStream_t s);
+
 // j-split plan: depends on (N, k, Dx) only so that row-blocked (sharded) calls reproduce the full call bit for bit
 struct NdivPlan { int ntiles, tps, JS; };
 static NdivPlan ndiv_plan(int N, int k, int Dx) {
@@ -573,22 +594,30 @@ static NdivPlan ndiv_plan(int N, int k, int Dx) {
   p.JS = (p.ntiles + p.tps - 1) / p.tps;
   return p;
 }
-struct NdivWs { size_t part, psum, gpart, total; };
-static NdivWs ndiv_ws(int N, int k, int Dx) {
+// workspace: [loss partials | partial sums (row sums or gradients) of the column splits | Gram-path images]
+struct NdivWs { size_t part, psum, gram, total; };
+static NdivWs ndiv_ws(int N, int k, int Dx, int Dz) {
   const NdivPlan p = ndiv_plan(N, k, Dx);
+  const bool tc = gram_eligible(N, k, Dx, Dz, 0);
+  const int JS = tc && gram_js(N, k) > p.JS ? gram_js(N, k) : p.JS;
   NdivWs w;
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   const size_t rb = (size_t)((k + kTI - 1) / kTI + 1);
-  w.part = ((size_t)(N > 0 ? N : 1) * rb * p.JS * sizeof(float) + 255) / 256 * 256;
-  w.psum = p.JS > 1 ? ((size_t)2 * p.JS * N * k * sizeof(float) + 255) / 256 * 256 : 0;
-  w.gpart = p.JS > 1 ? ((size_t)p.JS * N * k * Dx * sizeof(float) + 255) / 256 * 256 : 0;
-  w.total = w.part + (w.psum > w.gpart ? w.psum : w.gpart) + 256;
+  size_t parts = (size_t)(N > 0 ? N : 1) * rb * p.JS;
+  if (tc && (size_t)gram_loss_parts(N, k) > parts) parts = (size_t)gram_loss_parts(N, k);
+  w.part = al(parts * sizeof(float));
+  const size_t ps = JS > 1 ? (size_t)2 * JS * N * k * sizeof(float) : 0;
+  const size_t gp = JS > 1 ? (size_t)JS * N * k * Dx * sizeof(float) : 0;
+  w.psum = al(ps > gp ? ps : gp);
+  w.gram = tc ? gram_ws_bytes(N, k, Dx, Dz) : 0;
+  w.total = w.part + w.psum + w.gram + 256;
   return w;
 }
 }  // namespace ndp
 
-extern "C" int ndp_ndiv_workspace_bytes(int N, int k, int Dx, size_t* bytes) {
-  NDP_CHECK_ARG(bytes && N >= 0 && k >= 0 && Dx >= 1, "ndiv: bad N/k/Dx");
-  *bytes = ndiv_ws(N, k, Dx).total;
+extern "C" int ndp_ndiv_workspace_bytes(int N, int k, int Dx, int Dz, size_t* bytes) {
+  NDP_CHECK_ARG(bytes && N >= 0 && k >= 0 && Dx >= 1 && Dz >= 1, "ndiv: bad N/k/Dx/Dz");
+  *bytes = ndiv_ws(N, k, Dx, Dz).total;
   return NDP_OK;
 }
 
@@ -600,6 +629,60 @@ static int ndiv_args_ok(const float* x, const float* z, int N, int k, int Dx, in
   return NDP_OK;
 }
 
+// exact direct-difference pass 1; run_if (nullable, device) gates the whole pass
+static int exact_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz, int row0, int rows, float* sx,
+                         float* sz, char* ws, const NdivWs& w, const int* run_if, cudaStream_t s) {
+  const NdivPlan p = ndiv_plan(N, k, Dx);
+  dim3 grid((rows + kTI - 1) / kTI, p.JS, N);
+  const size_t smem1 = (size_t)(kSD * kSI + kSD * kSJ + 4 * kTI) * sizeof(float);
+  NDP_CUDA(cudaFuncSetAttribute(ndiv_rowsum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+  if (p.JS == 1) {
+    ndiv_rowsum_kernel<<<grid, kNT, smem1, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, sx, sz, run_if);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
+  float* psx = reinterpret_cast<float*>(ws + w.part);
+  float* psz = psx + (size_t)p.JS * N * k;
+  ndiv_rowsum_kernel<<<grid, kNT, smem1, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, psx, psz, run_if);
+  NDP_LAUNCH_CHECK();
+  ndiv_rowsum_reduce_kernel<<<(N * rows + 255) / 256, 256, 0, s>>>(psx, psz, N, k, p.JS, row0, rows, sx, sz, run_if);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+// tensor-core pass 1 on prepared images (gram_prepare): partial sums of the column splits, then their reduction
+static int tc_rowsums(int N, int k, int Dx, int Dz, int row0, int rows, float* sx, float* sz, char* b, const NdivWs& w,
+                      cudaStream_t s) {
+  void* gws = b + w.part + w.psum;
+  const int JS = gram_js(N, k);
+  float* psx = JS > 1 ? reinterpret_cast<float*>(b + w.part) : sx;
+  float* psz = JS > 1 ? psx + (size_t)JS * N * k : sz;
+  if (int rc = gram_rowsums(N, k, Dx, Dz, row0, rows, gws, psx, psz, s)) return rc;
+  if (JS > 1) {
+    ndiv_rowsum_reduce_kernel<<<(N * rows + 255) / 256, 256, 0, s>>>(psx, psz, N, k, JS, row0, rows, sx, sz, nullptr);
+    NDP_LAUNCH_CHECK();
+  }
+  return NDP_OK;
+}
+
+// tensor-core pass 2 on prepared images: loss partials + gradient partials, their reductions
+static int tc_loss_grad(const float* x, const float* sx, const float* sz, int N, int k, int Dx, int Dz, float margin,
+                        int row0, int rows, float* loss, float* grad_x, char* b, const NdivWs& w, cudaStream_t s) {
+  void* gws = b + w.part + w.psum;
+  const int JS = gram_js(N, k);
+  float* part = reinterpret_cast<float*>(b);
+  float* gpart = !grad_x ? nullptr : (JS > 1 ? reinterpret_cast<float*>(b + w.part) : grad_x);
+  if (int rc = gram_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, gws, part, gpart, s)) return rc;
+  if (grad_x && JS > 1) {
+    const size_t tot = (size_t)N * rows * Dx;
+    ndiv_grad_reduce_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(gpart, N, k, Dx, JS, row0, rows, 0, Dx, grad_x, nullptr);
+    NDP_LAUNCH_CHECK();
+  }
+  ndiv_finalize_kernel<<<1, 256, 0, s>>>(part, N * JS * ((rows + 127) / 128), loss, nullptr);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
 extern "C" int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz,
                                 int row0, int rows, float* sx, float* sz, void* ws, size_t ws_bytes, void* stream) {
   if (int rc = ndiv_args_ok(x, z, N, k, Dx, Dz, row0, rows)) return rc;
@@ -607,34 +690,61 @@ extern "C" int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, in
   if (N == 0 || rows == 0) return NDP_OK;
   NDP_CHECK_ARG(sx && sz, "ndiv: null sx/sz");
   cudaStream_t s = (cudaStream_t)stream;
-  const NdivPlan p = ndiv_plan(N, k, Dx);
-  const NdivWs w = ndiv_ws(N, k, Dx);
-  dim3 grid((rows + kTI - 1) / kTI, p.JS, N);
-  const size_t smem1 = (size_t)(kSD * kSI + kSD * kSJ + 4 * kTI) * sizeof(float);
-  NDP_CUDA(cudaFuncSetAttribute(ndiv_rowsum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-  if (p.JS == 1) {
-    ndiv_rowsum_kernel<<<grid, kNT, smem1, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, sx, sz);
-    NDP_LAUNCH_CHECK();
-    return NDP_OK;
+  const NdivWs w = ndiv_ws(N, k, Dx, Dz);
+  const bool tc = gram_eligible(N, k, Dx, Dz, row0);
+  const bool need_ws = tc || ndiv_plan(N, k, Dx).JS > 1;
+  if (need_ws && (!ws || ws_bytes < w.total)) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
+  char* b = reinterpret_cast<char*>(ws);
+  const int* run_if = nullptr;
+  if (tc) {
+    // proposal on tensor cores (Gram form); the exact pass behind it runs only if a pair was ill-conditioned
+    void* gws = b + w.part + w.psum;
+    if (int rc = gram_prepare(x, z, N, k, Dx, Dz, gws, s)) return rc;
+    if (int rc = tc_rowsums(N, k, Dx, Dz, row0, rows, sx, sz, b, w, s)) return rc;
+    run_if = gram_flag(gws);
   }
-  if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
-  float* psx = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + w.part);
-  float* psz = psx + (size_t)p.JS * N * k;
-  ndiv_rowsum_kernel<<<grid, kNT, smem1, s>>>(x, z, k, Dx, Dz, row0, rows, p.tps, psx, psz);
-  NDP_LAUNCH_CHECK();
-  ndiv_rowsum_reduce_kernel<<<(N * rows + 255) / 256, 256, 0, s>>>(psx, psz, N, k, p.JS, row0, rows, sx, sz);
-  NDP_LAUNCH_CHECK();
-  return NDP_OK;
+  return exact_rowsums(x, z, N, k, Dx, Dz, row0, rows, sx, sz, b, w, run_if, s);
 }
 
 template <int NDP, bool WG>
 static int launch_loss_grad(dim3 grid, cudaStream_t s, const float* x, const float* z, const float* sx,
                             const float* sz, int k, int Dx, int Dz, float margin, int row0, int rows, int tps,
-                            int dpass0, float* part, float* gpart) {
+                            int dpass0, float* part, float* gpart, const int* run_if) {
   NDP_CUDA(cudaFuncSetAttribute(ndiv_loss_grad_kernel<NDP, WG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)sizeof(NdivSmem2)));
   ndiv_loss_grad_kernel<NDP, WG><<<grid, kNT, sizeof(NdivSmem2), s>>>(x, z, sx, sz, k, Dx, Dz, margin, row0, rows, tps,
-                                                                      dpass0, part, gpart);
+                                                                      dpass0, part, gpart, run_if);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+static int exact_loss_grad(const float* x, const float* z, const float* sx, const float* sz, int N, int k, int Dx, int Dz,
+                           float margin, int row0, int rows, float* loss, float* grad_x, char* ws, const NdivWs& w,
+                           const int* run_if, cudaStream_t s) {
+  const NdivPlan p = ndiv_plan(N, k, Dx);
+  dim3 grid((rows + kTI - 1) / kTI, p.JS, N);
+  const size_t nparts = (size_t)grid.x * grid.y * grid.z;
+  float* part = reinterpret_cast<float*>(ws);
+  float* gpart = p.JS > 1 ? reinterpret_cast<float*>(ws + w.part) : grad_x;
+  if (!grad_x) {
+    if (int rc = launch_loss_grad<1, false>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, 0, part, nullptr, run_if)) return rc;
+  } else {
+    const int per_launch = 4 * kGD;
+    for (int dp = 0; dp < Dx; dp += per_launch) {
+      const int passes = ((Dx - dp < per_launch ? Dx - dp : per_launch) + kGD - 1) / kGD;
+      int rc;
+      if (passes <= 1) rc = launch_loss_grad<1, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart, run_if);
+      else if (passes <= 2) rc = launch_loss_grad<2, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart, run_if);
+      else rc = launch_loss_grad<4, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart, run_if);
+      if (rc) return rc;
+    }
+    if (p.JS > 1) {
+      const size_t tot = (size_t)N * rows * Dx;
+      ndiv_grad_reduce_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(gpart, N, k, Dx, p.JS, row0, rows, 0, Dx, grad_x, run_if);
+      NDP_LAUNCH_CHECK();
+    }
+  }
+  ndiv_finalize_kernel<<<1, 256, 0, s>>>(part, (int)nparts, loss, run_if);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
@@ -651,34 +761,47 @@ extern "C" int ndp_ndiv_loss_grad(const float* x, const float* z, const float* s
     return NDP_OK;
   }
   NDP_CHECK_ARG(sx && sz, "ndiv: null sx/sz");
-  const NdivPlan p = ndiv_plan(N, k, Dx);
-  const NdivWs w = ndiv_ws(N, k, Dx);
+  const NdivWs w = ndiv_ws(N, k, Dx, Dz);
   if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
-  dim3 grid((rows + kTI - 1) / kTI, p.JS, N);
-  const size_t nparts = (size_t)grid.x * grid.y * grid.z;
-  float* part = reinterpret_cast<float*>(ws);
-  float* gpart = p.JS > 1 ? reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + w.part) : grad_x;
-  if (!grad_x) {
-    if (int rc = launch_loss_grad<1, false>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, 0, part, nullptr)) return rc;
-  } else {
-    const int per_launch = 4 * kGD;
-    for (int dp = 0; dp < Dx; dp += per_launch) {
-      const int passes = ((Dx - dp < per_launch ? Dx - dp : per_launch) + kGD - 1) / kGD;
-      int rc;
-      if (passes <= 1) rc = launch_loss_grad<1, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart);
-      else if (passes <= 2) rc = launch_loss_grad<2, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart);
-      else rc = launch_loss_grad<4, true>(grid, s, x, z, sx, sz, k, Dx, Dz, margin, row0, rows, p.tps, dp, part, gpart);
-      if (rc) return rc;
-    }
-    if (p.JS > 1) {
-      const size_t tot = (size_t)N * rows * Dx;
-      ndiv_grad_reduce_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(gpart, N, k, Dx, p.JS, row0, rows, 0, Dx, grad_x);
-      NDP_LAUNCH_CHECK();
-    }
+  char* b = reinterpret_cast<char*>(ws);
+  const int* run_if = nullptr;
+  if (gram_eligible(N, k, Dx, Dz, row0)) {
+    void* gws = b + w.part + w.psum;
+    if (int rc = gram_prepare(x, z, N, k, Dx, Dz, gws, s)) return rc;
+    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, s)) return rc;
+    run_if = gram_flag(gws);
   }
-  ndiv_finalize_kernel<<<1, 256, 0, s>>>(part, (int)nparts, loss);
-  NDP_LAUNCH_CHECK();
-  return NDP_OK;
+  return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, run_if, s);
+}
+
+// Both passes over all rows in one call (the single-GPU autograd step): operands are pre-packed once.
+extern "C" int ndp_ndiv_forward_backward(const float* x, const float* z, int N, int k, int Dx, int Dz, float margin,
+                                         float* sx, float* sz, float* loss, float* grad_x, void* ws, size_t ws_bytes,
+                                         void* stream) {
+  if (int rc = ndiv_args_ok(x, z, N, k, Dx, Dz, 0, k)) return rc;
+  if (int rc = device_check()) return rc;
+  NDP_CHECK_ARG(loss, "ndiv: null loss");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (N == 0 || k == 0) {
+    NDP_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), s));
+    return NDP_OK;
+  }
+  NDP_CHECK_ARG(sx && sz, "ndiv: null sx/sz");
+  const NdivWs w = ndiv_ws(N, k, Dx, Dz);
+  if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
+  char* b = reinterpret_cast<char*>(ws);
+  const int* run_if = nullptr;
+  const bool tc = gram_eligible(N, k, Dx, Dz, 0);
+  if (tc) {
+    void* gws = b + w.part + w.psum;
+    if (int rc = gram_prepare(x, z, N, k, Dx, Dz, gws, s)) return rc;
+    if (int rc = tc_rowsums(N, k, Dx, Dz, 0, k, sx, sz, b, w, s)) return rc;
+    run_if = gram_flag(gws);
+  }
+  if (int rc = exact_rowsums(x, z, N, k, Dx, Dz, 0, k, sx, sz, b, w, run_if, s)) return rc;
+  if (tc)
+    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, s)) return rc;
+  return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, run_if, s);
 }
 
 extern "C" int ndp_pairwise(const float* v, int N, int k, int C, int normalise, float* out, void* stream) {

@@ -75,7 +75,7 @@ def ndiv_rowsums(x, z, row0=0, rows=None, sx=None, sz=None):
         sx = torch.empty(N, k, dtype=torch.float32, device=x.device)
         sz = torch.empty(N, k, dtype=torch.float32, device=x.device)
     nbytes = C.c_size_t()
-    check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, C.byref(nbytes)))
+    check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, Dz, C.byref(nbytes)))
     ws = _ws(nbytes.value, x.device)
     with torch.cuda.device(x.device):
         check(lib().ndp_ndiv_rowsums(ptr(x), ptr(z), N, k, Dx, Dz, row0, rows, ptr(sx), ptr(sz), ptr(ws), ws.numel(),
@@ -94,11 +94,29 @@ def ndiv_loss_grad(x, z, sx, sz, want_grad, row0=0, rows=None, margin=MARGIN):
     if want_grad:
         grad = torch.empty_like(x) if full else torch.zeros_like(x)
     nbytes = C.c_size_t()
-    check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, C.byref(nbytes)))
+    check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, Dz, C.byref(nbytes)))
     ws = _ws(nbytes.value, x.device)
     with torch.cuda.device(x.device):
         check(lib().ndp_ndiv_loss_grad(ptr(x), ptr(z), ptr(sx), ptr(sz), N, k, Dx, Dz, margin, row0, rows,
                                        ptr(loss), ptr(grad), ptr(ws), ws.numel(), stream_ptr(x.device)))
+    return loss, grad
+
+
+def ndiv_forward_backward(x, z, want_grad, margin=MARGIN):
+    """Both passes in one C call (ndp_ndiv_forward_backward): (loss[1], grad_x or None)."""
+    N, k, Dx = x.shape
+    Dz = z.shape[2]
+    dev = x.device
+    sx = torch.empty(N, k, dtype=torch.float32, device=dev)
+    sz = torch.empty(N, k, dtype=torch.float32, device=dev)
+    loss = torch.empty(1, dtype=torch.float32, device=dev)
+    grad = torch.empty_like(x) if want_grad else None
+    nbytes = C.c_size_t()
+    check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, Dz, C.byref(nbytes)))
+    ws = _ws(nbytes.value, dev)
+    with torch.cuda.device(dev):
+        check(lib().ndp_ndiv_forward_backward(ptr(x), ptr(z), N, k, Dx, Dz, margin, ptr(sx), ptr(sz), ptr(loss), ptr(grad),
+                                              ptr(ws), ws.numel(), stream_ptr(dev)))
     return loss, grad
 
 
@@ -107,9 +125,8 @@ class _NdivLoss(torch.autograd.Function):
     def forward(ctx, recodes, codes):
         require_cuda(recodes, codes)
         x, z = f32c(recodes), f32c(codes)
-        sx, sz = ndiv_rowsums(x, z)
         want = bool(ctx.needs_input_grad[0])
-        loss, grad = ndiv_loss_grad(x, z, sx, sz, want)
+        loss, grad = ndiv_forward_backward(x, z, want)
         if want:
             ctx.save_for_backward(grad)   # d loss / d recodes for grad_output = 1
         ctx.in_dtype = recodes.dtype
