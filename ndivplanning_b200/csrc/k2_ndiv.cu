@@ -575,7 +575,7 @@ int gram_prepare(const float* x, const float* z, int N, int k, int Dx, int Dz, v
 int* gram_flag(void* ws);
 int gram_rowsums(int N, int k, int Dx, int Dz, int row0, int rows, void* ws, float* psx, float* psz, cudaStream_t s);
 int gram_loss_grad(const float* x, const float* sx, const float* sz, int N, int k, int Dx, int Dz, float margin, int row0,
-                   int rows, void* ws, float* loss_part, float* gpart, cudaStream_t s);
+                   int rows, void* ws, float* loss_part, float* gpart, bool check, cudaStream_t s);
 
 // j-split plan: depends on (N, k, Dx) only so that row-blocked (sharded) calls reproduce the full call bit for bit
 struct NdivPlan { int ntiles, tps, JS; };
@@ -667,12 +667,13 @@ static int tc_rowsums(int N, int k, int Dx, int Dz, int row0, int rows, float* s
 
 // tensor-core pass 2 on prepared images: loss partials + gradient partials, their reductions
 static int tc_loss_grad(const float* x, const float* sx, const float* sz, int N, int k, int Dx, int Dz, float margin,
-                        int row0, int rows, float* loss, float* grad_x, char* b, const NdivWs& w, cudaStream_t s) {
+                        int row0, int rows, float* loss, float* grad_x, char* b, const NdivWs& w, bool check,
+                        cudaStream_t s) {
   void* gws = b + w.part + w.psum;
   const int JS = gram_js(N, k);
   float* part = reinterpret_cast<float*>(b);
   float* gpart = !grad_x ? nullptr : (JS > 1 ? reinterpret_cast<float*>(b + w.part) : grad_x);
-  if (int rc = gram_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, gws, part, gpart, s)) return rc;
+  if (int rc = gram_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, gws, part, gpart, check, s)) return rc;
   if (grad_x && JS > 1) {
     const size_t tot = (size_t)N * rows * Dx;
     ndiv_grad_reduce_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(gpart, N, k, Dx, JS, row0, rows, 0, Dx, grad_x, nullptr);
@@ -768,7 +769,7 @@ extern "C" int ndp_ndiv_loss_grad(const float* x, const float* z, const float* s
   if (gram_eligible(N, k, Dx, Dz, row0)) {
     void* gws = b + w.part + w.psum;
     if (int rc = gram_prepare(x, z, N, k, Dx, Dz, gws, s)) return rc;
-    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, s)) return rc;
+    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, true, s)) return rc;
     run_if = gram_flag(gws);
   }
   return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, run_if, s);
@@ -800,7 +801,7 @@ extern "C" int ndp_ndiv_forward_backward(const float* x, const float* z, int N, 
   }
   if (int rc = exact_rowsums(x, z, N, k, Dx, Dz, 0, k, sx, sz, b, w, run_if, s)) return rc;
   if (tc)
-    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, s)) return rc;
+    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, false, s)) return rc;
   return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, run_if, s);
 }
 

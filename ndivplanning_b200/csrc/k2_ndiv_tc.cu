@@ -158,7 +158,14 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
 
 // MUFU.SQRT (<= 1 ulp-class error, same order as the Gram form's own rounding); IEEE sqrtf runs at 9.7 /clk/SM against
 // 15.8 for the approximation (tools/fp32_probe.cu) and the epilogue is MUFU-bound.  The exact kernels keep sqrtf.
-__device__ __forceinline__ float sqrt_approx(float v) { float r; asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ float sqrt_approx(float v) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+
+typedef unsigned long long u64;   // packed fp32 pair (FFMA2)
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+  u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r;
+}
+__device__ __forceinline__ u64 dup2(float v) { u64 r; asm("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(v)); return r; }
+__device__ __forceinline__ void unpack2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
 
 struct GramParams {
   const uint8_t* imgA;
@@ -177,8 +184,54 @@ struct GramParams {
   int* ill;                    // raised when a pair fails the conditioning test
 };
 
+struct GramAcc {
+  float rsx, rsz, lsum, sumW, illm;
+  u64 g2[16];                                          // gradient accumulators, packed pairs of dims
+};
+
+// one pair (i, j): distances from the two Gram accumulators, then row sums (pass 1) or hinge / What / gradient
+// (pass 2).  EDGE: the tile contains the diagonal, padded columns or rows outside the caller's block.
+template <bool PASS2, bool EDGE, bool CHECK>
+__device__ __forceinline__ void gram_pair(GramAcc& a, float accx, float accz, float2 ni, float2 nj, float cx, float cz,
+                                          float2 ri, float2 rj, float margin, bool valid, bool ivalid, bool off,
+                                          bool grad, const float* __restrict__ xrow, int Dx) {
+  const float sxn = ni.x + nj.x, szn = ni.y + nj.y;
+  float d2x = fmaf(cx, accx, sxn);
+  float d2z = fmaf(cz, accz, szn);
+  if (CHECK) {                                         // conditioning: min over pairs of d2 - tau (n_i + n_j)
+    const float m = fminf(fmaf(-kIllTau, sxn, d2x), fmaf(-kIllTau, szn, d2z));
+    a.illm = fminf(a.illm, (!EDGE || (valid && ivalid && off)) ? m : 0.f);
+  }
+  d2x = fmaxf(d2x, 0.f);
+  d2z = fmaxf(d2z, 0.f);
+  if (EDGE && !off) { d2x = 0.f; d2z = 0.f; }          // the diagonal is exactly 0
+  const float ddx = sqrt_approx(d2x), ddz = sqrt_approx(d2z);
+  if (!PASS2) {
+    if (!EDGE || valid) { a.rsx += ddx; a.rsz += ddz; }
+  } else {
+    const float hij = __fsub_rn(__fmul_rn(margin, __fmul_rn(ddz, ri.y)), __fmul_rn(ddx, ri.x));
+    const float hji = __fsub_rn(__fmul_rn(margin, __fmul_rn(ddz, rj.y)), __fmul_rn(ddx, rj.x));
+    const bool ok = !EDGE || (valid && ivalid);
+    if (ok) a.lsum += !(hij <= 0.f) ? hij : 0.f;
+    if (grad) {
+      const float wij = (hij > 0.f ? ri.x : 0.f) + (hji > 0.f ? rj.x : 0.f);
+      const float w = (ok && ddx > 0.f) ? __fdividef(-wij, ddx) : 0.f;
+      a.sumW += w;
+      const ulonglong2* xr = reinterpret_cast<const ulonglong2*>(xrow);
+      const u64 w2 = dup2(w);
+#pragma unroll
+      for (int d4 = 0; d4 < 8; ++d4)
+        if (d4 * 4 < Dx) {
+          const ulonglong2 xv = xr[d4];                // {x0,x1} {x2,x3}
+          a.g2[d4 * 2 + 0] = fma2(w2, xv.x, a.g2[d4 * 2 + 0]);
+          a.g2[d4 * 2 + 1] = fma2(w2, xv.y, a.g2[d4 * 2 + 1]);
+        }
+    }
+  }
+}
+
 // grid (row tiles of the call, JS, N), 256 threads, 2 CTAs / SM
-template <bool PASS2>
+template <bool PASS2, bool CHECK>
 __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const GramDims gd = gram_dims(p.Dx, p.Dz);
@@ -229,11 +282,11 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
   const uint32_t idesc = idesc_f16(128);
   const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
 
-  float rsx = 0.f, rsz = 0.f, lsum = 0.f, sumW = 0.f;
-  float g[32];
+  GramAcc acc;
+  acc.rsx = acc.rsz = acc.lsum = acc.sumW = acc.illm = 0.f;
 #pragma unroll
-  for (int d = 0; d < 32; ++d) g[d] = 0.f;
-  bool illc = false;
+  for (int d = 0; d < 16; ++d) acc.g2[d] = 0ull;
+  const bool rows_full = itile * kGT >= p.row0 && itile * kGT + kGT <= iend;
   uint32_t ph = 0;
 
   for (int jt = jt0; jt < jt1; ++jt) {
@@ -272,48 +325,29 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
     fence_after_sync();
     const float2 sJ = snj[kGT];                        // accumulators carry s_I * s_J (powers of two: exact)
     const float cx = -2.f / (sI.x * sJ.x), cz = -2.f / (sI.y * sJ.y);
+    const bool edge = (jt == itile) || (j0 + kGT > p.k) || !rows_full;      // CTA-uniform
 #pragma unroll 1
-    for (int c16 = 0; c16 < 4; ++c16) {
-      const int col = hf * 64 + c16 * 16;
+    for (int cc = 0; cc < 4; ++cc) {
+      const int col = hf * 64 + cc * 16;
       uint32_t ux[16], uz[16];
       tmem_ld16(lane_base + col, ux);
       tmem_ld16(lane_base + 128 + col, uz);
       tmem_ld_wait();
+      if (edge) {
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const int jl = col + c, j = j0 + jl;
-        const float2 nj = snj[jl];
-        const float sxn = ni.x + nj.x, szn = ni.y + nj.y;
-        float d2x = fmaf(cx, __uint_as_float(ux[c]), sxn);
-        float d2z = fmaf(cz, __uint_as_float(uz[c]), szn);
-        const bool valid = j < p.k, off = j != i;
-        illc |= valid && ivalid && off && (d2x < kIllTau * sxn || d2z < kIllTau * szn);
-        d2x = off ? fmaxf(d2x, 0.f) : 0.f;             // the diagonal is exactly 0
-        d2z = off ? fmaxf(d2z, 0.f) : 0.f;
-        const float ddx = sqrt_approx(d2x), ddz = sqrt_approx(d2z);
-        if (!PASS2) {
-          if (valid) { rsx += ddx; rsz += ddz; }
-        } else {
-          const float2 rj = srj[jl];
-          const float hij = __fsub_rn(__fmul_rn(p.margin, __fmul_rn(ddz, ri.y)), __fmul_rn(ddx, ri.x));
-          const float hji = __fsub_rn(__fmul_rn(p.margin, __fmul_rn(ddz, rj.y)), __fmul_rn(ddx, rj.x));
-          const bool ok = valid && ivalid;
-          if (ok) lsum += !(hij <= 0.f) ? hij : 0.f;
-          if (grad) {
-            const float wij = (hij > 0.f ? ri.x : 0.f) + (hji > 0.f ? rj.x : 0.f);
-            const float w = (ok && ddx > 0.f) ? __fdividef(-wij, ddx) : 0.f;
-            sumW += w;
-            const float4* xr = reinterpret_cast<const float4*>(sxj + jl * p.Dx);
+        for (int c = 0; c < 16; ++c) {
+          const int jl = col + c, j = j0 + jl;
+          gram_pair<PASS2, true, CHECK>(acc, __uint_as_float(ux[c]), __uint_as_float(uz[c]), ni, snj[jl], cx, cz, ri,
+                                        PASS2 ? srj[jl] : make_float2(0.f, 0.f), p.margin, j < p.k, ivalid, j != i, grad,
+                                        sxj + jl * p.Dx, p.Dx);
+        }
+      } else {
 #pragma unroll
-            for (int d4 = 0; d4 < 8; ++d4)
-              if (d4 * 4 < p.Dx) {
-                const float4 xv = xr[d4];
-                g[d4 * 4 + 0] = fmaf(w, xv.x, g[d4 * 4 + 0]);
-                g[d4 * 4 + 1] = fmaf(w, xv.y, g[d4 * 4 + 1]);
-                g[d4 * 4 + 2] = fmaf(w, xv.z, g[d4 * 4 + 2]);
-                g[d4 * 4 + 3] = fmaf(w, xv.w, g[d4 * 4 + 3]);
-              }
-          }
+        for (int c = 0; c < 16; ++c) {
+          const int jl = col + c;
+          gram_pair<PASS2, false, CHECK>(acc, __uint_as_float(ux[c]), __uint_as_float(uz[c]), ni, snj[jl], cx, cz, ri,
+                                         PASS2 ? srj[jl] : make_float2(0.f, 0.f), p.margin, true, true, true, grad,
+                                         sxj + jl * p.Dx, p.Dx);
         }
       }
     }
@@ -322,9 +356,9 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
     ph ^= 1;
   }
 
-  if (illc) atomicOr(p.ill, 1);
+  if (CHECK && acc.illm < 0.f) atomicOr(p.ill, 1);
   if (!PASS2) {
-    sred[hf * kGT + row] = make_float2(rsx, rsz);
+    sred[hf * kGT + row] = make_float2(acc.rsx, acc.rsz);
     __syncthreads();
     if (tid < kGT) {
       const int ii = itile * kGT + tid;
@@ -335,12 +369,17 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       }
     }
   } else {
+    float lsum = acc.lsum;
+    const float sumW = acc.sumW;
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 16);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 8);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 4);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 2);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 1);
     if (lane == 0) slos[warp] = lsum;
+    float g[32];
+#pragma unroll
+    for (int d = 0; d < 16; ++d) unpack2(acc.g2[d], g[2 * d], g[2 * d + 1]);
     if (grad) {
       float* gs = reinterpret_cast<float*>(sB);        // [128 rows][33]: partial gradient of column half 1
       if (hf == 1) {
@@ -387,7 +426,7 @@ GramPlan gram_plan(int N, int k) {
 bool gram_eligible(int N, int k, int Dx, int Dz, int row0) {
   static const bool off = getenv("NDP_NDIV_EXACT") != nullptr;      // diagnostics: force the exact kernels
   if (off) return false;
-  return N >= 1 && k >= 256 && Dx >= 1 && Dx <= 32 && (Dx % 4) == 0 && Dz >= 1 && Dz <= 32 && (row0 % kGT) == 0;
+  return N >= 1 && (long long)N * k >= 1536 && k >= 256 && Dx >= 1 && Dx <= 32 && (Dx % 4) == 0 && Dz >= 1 && Dz <= 32 && (row0 % kGT) == 0;
 }
 
 struct GramWs { size_t flag, norms, imgA, imgB, total; };
@@ -444,22 +483,28 @@ int gram_rowsums(int N, int k, int Dx, int Dz, int row0, int rows, void* ws, flo
   p.psx = psx; p.psz = psz;
   const GramPlan g = gram_plan(N, k);
   const size_t sm = gram_smem(Dx, Dz, false);
-  NDP_CUDA(cudaFuncSetAttribute(ndiv_gram_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  ndiv_gram_kernel<false><<<dim3((rows + kGT - 1) / kGT, g.JS, N), kGNT, sm, s>>>(p);
+  NDP_CUDA(cudaFuncSetAttribute(ndiv_gram_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  ndiv_gram_kernel<false, true><<<dim3((rows + kGT - 1) / kGT, g.JS, N), kGNT, sm, s>>>(p);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
 
 // pass 2 on tensor cores: loss partials [gram_loss_parts] and gradient partials gpart [JS][N][k][Dx] (nullable)
 int gram_loss_grad(const float* x, const float* sx, const float* sz, int N, int k, int Dx, int Dz, float margin, int row0,
-                   int rows, void* ws, float* loss_part, float* gpart, cudaStream_t s) {
+                   int rows, void* ws, float* loss_part, float* gpart, bool check, cudaStream_t s) {
   GramParams p{};
   gram_fill(p, N, k, Dx, Dz, ws, row0, rows);
   p.x = x; p.sx = sx; p.sz = sz; p.margin = margin; p.loss_part = loss_part; p.gpart = gpart;
   const GramPlan g = gram_plan(N, k);
   const size_t sm = gram_smem(Dx, Dz, true);
-  NDP_CUDA(cudaFuncSetAttribute(ndiv_gram_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-  ndiv_gram_kernel<true><<<dim3((rows + kGT - 1) / kGT, g.JS, N), kGNT, sm, s>>>(p);
+  const dim3 grid((rows + kGT - 1) / kGT, g.JS, N);
+  if (check) {
+    NDP_CUDA(cudaFuncSetAttribute(ndiv_gram_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    ndiv_gram_kernel<true, true><<<grid, kGNT, sm, s>>>(p);
+  } else {                                             // same pairs were checked by pass 1 of the same call
+    NDP_CUDA(cudaFuncSetAttribute(ndiv_gram_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    ndiv_gram_kernel<true, false><<<grid, kGNT, sm, s>>>(p);
+  }
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
