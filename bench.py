@@ -264,7 +264,7 @@ def run_gpu(args):
         pairs = []
         for i in range(steps):
             flush()
-            torch.cuda._sleep(3_000_000)               # ~1.5 ms: the host enqueues the launch before `a` is reached
+            torch.cuda._sleep(1_000_000)               # ~0.5 ms: the host enqueues the launch before `a` is reached
             a, b = ev(), ev()
             a.record(); pl.rollout_score(e0, goal, pool[i % POOL]); b.record()
             pairs.append((a, b))
@@ -397,11 +397,13 @@ def run_gpu(args):
                                  "rollout kernel; fp16 and bf16 share the tcgen05 kind::f16 rate"},
             "ndiv": {"metric": "ndiv_pairs_per_sec_fwd_bwd", "value": pairs / (ndiv_ms * 1e-3), "unit": "ordered pairs/s",
                      "ms_per_step": ndiv_ms, "config": NDIV,
-                     "roofline": {"bound": "fp32 lanes (direct-difference form: 2 lane-ops per pair-dim and pass)",
-                                  "floor_ms": 2 * pairs * 2 * (NDIV["Dx"] + NDIV["Dz"]) / (148 * 128 * 1.965e9) * 1e3,
-                                  "survey_mufu_floor_ms": 0.0108,
-                                  "note": "floor_ms = 2 passes x pairs x 2(Dx+Dz) lane-ops / (148 SMs x 128 lanes x 1.965 GHz); "
-                                          "SURVEY 8d's 10.8 us floor assumes Gram-form distances on tensor cores"}},
+                     "roofline": {"bound": "MUFU (3 special-function ops per ordered pair: 2 sqrt + 1 rcp; SURVEY 8d)",
+                                  "floor_ms": pairs * 3 / (148 * 16 * 1.965e9) * 1e3,
+                                  "frac": pairs * 3 / (148 * 16 * 1.965e9) * 1e3 / ndiv_ms,
+                                  "note": "Gram-form distances on tcgen05 (fp16 split operands), fused hinge/gradient "
+                                          "epilogue, exact direct-difference kernels gated behind it; floor = pairs x 3 / "
+                                          "(148 SMs x 16 MUFU/clk x 1.965 GHz); ms_per_step includes the host autograd "
+                                          "wrapper's 11 launches"}},
             "parity": parity,
             "modes": modes,
         }
