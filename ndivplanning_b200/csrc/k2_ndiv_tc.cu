@@ -41,6 +41,7 @@ __host__ __device__ inline GramDims gram_dims(int Dx, int Dz) {
   return g;
 }
 
+static constexpr int kXTBytes = 16384;          // per tile: transposed x operand of the gradient product, hi + lo
 static constexpr int kGNS = 130;                // float2 entries per tile in the norms array: 128 rows {nx, nz},
                                                 // entry 128 = the tile's operand scales {sx, sz}, entry 129 = pad
 __device__ __forceinline__ float pick_scale(float m) {   // 2^(9 - e) with m = f * 2^e, f in [0.5, 1); degenerate data -> 1
@@ -65,8 +66,8 @@ __device__ __forceinline__ uint32_t img_off(int slab0, int r, int kk) {
 // divides the accumulator by s_I * s_J.
 __global__ void __launch_bounds__(256)
 ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, int k, int Dx, int Dz,
-                    uint8_t* __restrict__ imgA, uint8_t* __restrict__ imgB, float2* __restrict__ norms,
-                    int* __restrict__ ill) {
+                    uint8_t* __restrict__ imgA, uint8_t* __restrict__ imgB, uint8_t* __restrict__ imgT,
+                    float* __restrict__ mu_out, float2* __restrict__ norms, int* __restrict__ ill) {
   const int n = blockIdx.y, tile = blockIdx.x, tiles = gridDim.x;
   if (n == 0 && tile == 0 && threadIdx.x == 0) *ill = 0;      // the main kernels raise it (stream order)
   const GramDims gd = gram_dims(Dx, Dz);
@@ -143,6 +144,27 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
     *reinterpret_cast<uint4*>(B + img_off(slab0, r, Dp + kk)) = L;
     *reinterpret_cast<uint4*>(B + img_off(slab0, r, 2 * Dp + kk)) = H;
   }
+  // B operand of the gradient product  G[i, d] = sum_j What_ij c_j[d]:  rows = d (N = 32), K = j (128), K-major core
+  // matrices [j/8][d/8][8 d][8 j]; fp16 hi (8 KB) then lo (8 KB) of the same scaled centred values as above.
+  if (imgT) {
+    uint8_t* T = imgT + ((size_t)n * tiles + tile) * kXTBytes;
+    for (int it = threadIdx.x; it < 16 * 32; it += blockDim.x) {
+      const int d = it & 31, jg = it >> 5;
+      uint32_t hi[4], lo[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int r0 = tile * kGT + jg * 8 + 2 * e;
+        const float c0 = (r0 < k && d < Dx) ? (__ldg(x + ((size_t)n * k + r0) * Dx + d) - mu[d]) * s_sc[0] : 0.f;
+        const float c1 = (r0 + 1 < k && d < Dx) ? (__ldg(x + ((size_t)n * k + r0 + 1) * Dx + d) - mu[d]) * s_sc[0] : 0.f;
+        hi[e] = pack_hi(c0, c1);
+        lo[e] = pack_lo(c0, c1, hi[e]);
+      }
+      const uint32_t off = (uint32_t)((jg * 4 + (d >> 3)) * 128 + (d & 7) * 16);
+      *reinterpret_cast<uint4*>(T + off) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      *reinterpret_cast<uint4*>(T + 8192 + off) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+    if (tile == 0 && threadIdx.x < 64) mu_out[(size_t)n * 64 + threadIdx.x] = threadIdx.x < Dx ? mu[threadIdx.x] : 0.f;
+  }
   if (threadIdx.x < kGT) {                           // centred squared norms, fixed summation order
     const int row = tile * kGT + threadIdx.x;
     float nx = 0.f, nz = 0.f;
@@ -171,7 +193,9 @@ struct GramParams {
   const uint8_t* imgA;
   const uint8_t* imgB;
   const float2* norms;
-  const float* x;              // original outputs (gradient product, pass 2)
+  const uint8_t* imgT;         // transposed x operand images (gradient product, pass 2)
+  const float* mu;             // [N][64] centre of the x features
+  const float* x;              // original outputs (pass 2)
   const float* sx;             // row sums (pass 2)
   const float* sz;
   int k, Dx, Dz, tiles, tps;
@@ -186,7 +210,7 @@ struct GramParams {
 
 struct GramAcc {
   float rsx, rsz, lsum, sumW, illm;
-  u64 g2[16];                                          // gradient accumulators, packed pairs of dims
+  float g[16];                                         // gradient accumulators: dims hf*16 .. hf*16+15 of this row
 };
 
 // one pair (i, j): distances from the two Gram accumulators, then row sums (pass 1) or hinge / What / gradient
@@ -194,7 +218,7 @@ struct GramAcc {
 template <bool PASS2, bool EDGE, bool CHECK>
 __device__ __forceinline__ void gram_pair(GramAcc& a, float accx, float accz, float2 ni, float2 nj, float cx, float cz,
                                           float2 ri, float2 rj, float margin, bool valid, bool ivalid, bool off,
-                                          bool grad, const float* __restrict__ xrow, int Dx) {
+                                          bool grad, float alpha, float& ws) {
   const float sxn = ni.x + nj.x, szn = ni.y + nj.y;
   float d2x = fmaf(cx, accx, sxn);
   float d2z = fmaf(cz, accz, szn);
@@ -217,15 +241,8 @@ __device__ __forceinline__ void gram_pair(GramAcc& a, float accx, float accz, fl
       const float wij = (hij > 0.f ? ri.x : 0.f) + (hji > 0.f ? rj.x : 0.f);
       const float w = (ok && ddx > 0.f) ? __fdividef(-wij, ddx) : 0.f;
       a.sumW += w;
-      const ulonglong2* xr = reinterpret_cast<const ulonglong2*>(xrow);
-      const u64 w2 = dup2(w);
-#pragma unroll
-      for (int d4 = 0; d4 < 8; ++d4)
-        if (d4 * 4 < Dx) {
-          const ulonglong2 xv = xr[d4];                // {x0,x1} {x2,x3}
-          a.g2[d4 * 2 + 0] = fma2(w2, xv.x, a.g2[d4 * 2 + 0]);
-          a.g2[d4 * 2 + 1] = fma2(w2, xv.y, a.g2[d4 * 2 + 1]);
-        }
+      ws = w * alpha;                                  // row-scaled to O(1) for the fp16 A operand of the product
+      a.illm = fminf(a.illm, 60000.f - fabsf(ws));     // would not fit fp16: let the exact kernels take the call
     }
   }
 }
@@ -244,22 +261,21 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
 
   uint8_t* sA = smem;
   uint8_t* sB = smem + gd.img_bytes;
-  float* sxj = reinterpret_cast<float*>(smem + 2 * gd.img_bytes);            // [128][Dx] fp32 x_j rows (pass 2)
-  const uint32_t xj_bytes = PASS2 ? (uint32_t)(kGT * p.Dx * 4) : 0u;
+  uint8_t* sXT = smem + 2 * gd.img_bytes;                                    // transposed x_j operand (pass 2)
+  const uint32_t xj_bytes = PASS2 ? (uint32_t)kXTBytes : 0u;
   float2* snj = reinterpret_cast<float2*>(smem + 2 * gd.img_bytes + xj_bytes);   // {nx_j, nz_j}
   float2* srj = snj + kGNS;                                                  // {1/sx_j, 1/sz_j}
   float2* sred = srj + kGT;                                                  // [2 halves][128 rows]
   float* slos = reinterpret_cast<float*>(sred + 2 * kGT);                    // [8 warps]
   uint8_t* sbar = reinterpret_cast<uint8_t*>(slos + 8);
-  const uint32_t bar_a = smem_u32(sbar), bar_full = bar_a + 8, bar_d = bar_a + 16;
+  const uint32_t bar_a = smem_u32(sbar), bar_full = bar_a + 8, bar_d = bar_a + 16, bar_g = bar_a + 24;
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sbar + 32);
 
   if (tid == 0) {
-    mbar_init(bar_a, 1); mbar_init(bar_full, 1); mbar_init(bar_d, 1);
+    mbar_init(bar_a, 1); mbar_init(bar_full, 1); mbar_init(bar_d, 1); mbar_init(bar_g, 1);
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc256(smem_u32((const void*)tmem_slot));
-  if (PASS2) for (int i = tid; i < kGT * p.Dx; i += kGNT) sxj[i] = 0.f;      // rows past k stay finite
   fence_proxy_async();
   fence_before_sync();
   __syncthreads();
@@ -279,25 +295,30 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
   const float2 sI = __ldg(p.norms + ((size_t)n * p.tiles + itile) * kGNS + kGT);   // operand scales of the i tile
   float2 ri = make_float2(0.f, 0.f);
   if (PASS2 && i < p.k) ri = make_float2(1.f / __ldg(p.sx + (size_t)n * p.k + i), 1.f / __ldg(p.sz + (size_t)n * p.k + i));
+  float alpha = 1.f;                                   // power of two ~ sx_i^2 / k: What * alpha = O(mean d / d)
+  if (PASS2 && i < p.k) {
+    const float sxi = __ldg(p.sx + (size_t)n * p.k + i);
+    const float t = sxi * sxi / (float)p.k;
+    if (t > 0.f && t < 3e38f) { int e; frexpf(t, &e); e = e > 100 ? 100 : (e < -100 ? -100 : e); alpha = ldexpf(1.f, e - 1); }
+  }
   const uint32_t idesc = idesc_f16(128);
   const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
 
   GramAcc acc;
   acc.rsx = acc.rsz = acc.lsum = acc.sumW = acc.illm = 0.f;
 #pragma unroll
-  for (int d = 0; d < 16; ++d) acc.g2[d] = 0ull;
+  for (int d = 0; d < 16; ++d) acc.g[d] = 0.f;
   const bool rows_full = itile * kGT >= p.row0 && itile * kGT + kGT <= iend;
   uint32_t ph = 0;
 
   for (int jt = jt0; jt < jt1; ++jt) {
     const int j0 = jt * kGT;
     if (tid == 0) {
-      const int vrows = (p.k - j0) < kGT ? (p.k - j0) : kGT;
-      const uint32_t xb = PASS2 ? (uint32_t)(vrows * p.Dx * 4) : 0u;
+      const uint32_t xb = grad ? (uint32_t)kXTBytes : 0u;
       mbar_expect_tx(bar_full, (uint32_t)gd.img_bytes + kGNS * 8 + xb);
       bulk_g2s(smem_u32(sB), p.imgB + ((size_t)n * p.tiles + jt) * gd.img_bytes, (uint32_t)gd.img_bytes, bar_full);
       bulk_g2s(smem_u32(snj), p.norms + ((size_t)n * p.tiles + jt) * kGNS, kGNS * 8, bar_full);
-      if (PASS2) bulk_g2s(smem_u32(sxj), p.x + ((size_t)n * p.k + j0) * p.Dx, xb, bar_full);
+      if (grad) bulk_g2s(smem_u32(sXT), p.imgT + ((size_t)n * p.tiles + jt) * kXTBytes, xb, bar_full);
     }
     if (PASS2 && tid < kGT) {
       const int j = j0 + tid;
@@ -333,30 +354,77 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       tmem_ld16(lane_base + col, ux);
       tmem_ld16(lane_base + 128 + col, uz);
       tmem_ld_wait();
+      float wch[16];
       if (edge) {
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
           const int jl = col + c, j = j0 + jl;
+          wch[c] = 0.f;
           gram_pair<PASS2, true, CHECK>(acc, __uint_as_float(ux[c]), __uint_as_float(uz[c]), ni, snj[jl], cx, cz, ri,
                                         PASS2 ? srj[jl] : make_float2(0.f, 0.f), p.margin, j < p.k, ivalid, j != i, grad,
-                                        sxj + jl * p.Dx, p.Dx);
+                                        alpha, wch[c]);
         }
       } else {
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
           const int jl = col + c;
+          wch[c] = 0.f;
           gram_pair<PASS2, false, CHECK>(acc, __uint_as_float(ux[c]), __uint_as_float(uz[c]), ni, snj[jl], cx, cz, ri,
                                          PASS2 ? srj[jl] : make_float2(0.f, 0.f), p.margin, true, true, true, grad,
-                                         sxj + jl * p.Dx, p.Dx);
+                                         alpha, wch[c]);
         }
       }
+      if (grad) {
+        // What (16 consecutive j of this row) -> fp16 hi / lo A-operand columns, written over accumulator columns
+        // this warp has already consumed: hi into the x accumulator block, lo into the z block.
+        uint32_t whi[8], wlo[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          whi[e] = pack_hi(wch[2 * e], wch[2 * e + 1]);
+          wlo[e] = pack_lo(wch[2 * e], wch[2 * e + 1], whi[e]);
+        }
+        const uint32_t wcol = lane_base + hf * 64 + cc * 8;
+        tmem_st8(wcol, whi);
+        tmem_st8(wcol + 128, wlo);
+      }
+    }
+    if (grad) {
+      // G[128 x 32] = What[128 x 128] * C_j[128 x 32] on the tensor pipe (A from TMEM, B = transposed x image)
+      tmem_st_wait();
+      fence_before_sync();
+      __syncthreads();
+      if (warp == 0) {
+        if (elect_one()) {
+          fence_after_sync();
+          const uint32_t t0 = smem_u32(sXT);
+          const uint32_t idg = idesc_f16(32);
+#pragma unroll 1
+          for (int sl = 0; sl < 8; ++sl) {             // K slabs of 16 j: packed columns 8*sl (j < 64) or 64 + 8*(sl-4)
+            const uint32_t acol = tmem + (sl < 4 ? sl * 8 : 64 + (sl - 4) * 8);
+            const uint64_t bh = smem_desc(t0 + sl * 1024, 512, 128), bl = smem_desc(t0 + 8192 + sl * 1024, 512, 128);
+            mma_ts(tmem + 32, acol, bh, idg, sl > 0);          // hi * hi
+            mma_ts(tmem + 32, acol + 128, bh, idg, 1);         // lo * hi
+            mma_ts(tmem + 32, acol, bl, idg, 1);               // hi * lo
+          }
+          mma_commit(bar_g);
+        }
+        __syncwarp();
+      }
+      mbar_wait(bar_g, ph);
+      fence_after_sync();
+      uint32_t ug[16];
+      tmem_ld16(lane_base + 32 + hf * 16, ug);
+      tmem_ld_wait();
+      const float isj = 1.f / snj[kGT].x;              // the tile's operand scale (power of two)
+#pragma unroll
+      for (int d = 0; d < 16; ++d) acc.g[d] = fmaf(__uint_as_float(ug[d]), isj, acc.g[d]);
     }
     fence_before_sync();
     __syncthreads();                                   // TMEM and the tile's shared buffers may be overwritten
     ph ^= 1;
   }
 
-  if (CHECK && acc.illm < 0.f) atomicOr(p.ill, 1);
+  if ((CHECK || grad) && acc.illm < 0.f) atomicOr(p.ill, 1);
   if (!PASS2) {
     sred[hf * kGT + row] = make_float2(acc.rsx, acc.rsz);
     __syncthreads();
@@ -377,31 +445,25 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 2);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 1);
     if (lane == 0) slos[warp] = lsum;
-    float g[32];
-#pragma unroll
-    for (int d = 0; d < 16; ++d) unpack2(acc.g2[d], g[2 * d], g[2 * d + 1]);
-    if (grad) {
-      float* gs = reinterpret_cast<float*>(sB);        // [128 rows][33]: partial gradient of column half 1
-      if (hf == 1) {
-#pragma unroll
-        for (int d = 0; d < 32; ++d) gs[row * 33 + d] = g[d];
-        gs[row * 33 + 32] = sumW;
-      }
-    }
+    if (grad) sred[hf * kGT + row] = make_float2(sumW, 0.f);      // What row sums of the two column halves
     __syncthreads();
     if (tid == 0) {
       float t = 0.f;
       for (int w = 0; w < 8; ++w) t += slos[w];
       p.loss_part[((size_t)n * gridDim.y + js) * gridDim.x + blockIdx.x] = t;
     }
-    if (grad && hf == 0 && ivalid) {
-      const float* gs = reinterpret_cast<const float*>(sB);
-      const float sw = sumW + gs[row * 33 + 32];
+    if (grad && ivalid) {
+      // grad_i = c_i * sum_j What_ij - sum_j What_ij c_j ; this thread owns dims hf*16 .. hf*16+15 of row i
+      const float sw = sred[row].x + sred[kGT + row].x;
+      const float ia = 1.f / alpha;
       const size_t off = ((size_t)n * p.k + i) * p.Dx;
       float* dst = p.gpart + (size_t)js * N * p.k * p.Dx + off;
+      const float* mu = p.mu + (size_t)n * 64;
 #pragma unroll
-      for (int d = 0; d < 32; ++d)
-        if (d < p.Dx) dst[d] = fmaf(__ldg(p.x + off + d), sw, -(g[d] + gs[row * 33 + d]));
+      for (int d = 0; d < 16; ++d) {
+        const int dim = hf * 16 + d;
+        if (dim < p.Dx) dst[dim] = fmaf(__ldg(p.x + off + dim) - __ldg(mu + dim), sw, -acc.g[d] * ia);
+      }
     }
   }
   fence_before_sync();
@@ -429,17 +491,19 @@ bool gram_eligible(int N, int k, int Dx, int Dz, int row0) {
   return N >= 1 && (long long)N * k >= 1536 && k >= 256 && Dx >= 1 && Dx <= 32 && (Dx % 4) == 0 && Dz >= 1 && Dz <= 32 && (row0 % kGT) == 0;
 }
 
-struct GramWs { size_t flag, norms, imgA, imgB, total; };
+struct GramWs { size_t flag, mu, norms, imgA, imgB, imgT, total; };
 static GramWs gram_ws_layout(int N, int k, int Dx, int Dz) {
   const GramDims gd = gram_dims(Dx, Dz);
   const size_t tiles = (size_t)(k + kGT - 1) / kGT;
   auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   GramWs w;
   w.flag = 0;
-  w.norms = 256;
+  w.mu = 256;
+  w.norms = w.mu + al((size_t)N * 64 * 4);
   w.imgA = w.norms + al((size_t)N * tiles * kGNS * 8);
   w.imgB = w.imgA + al((size_t)N * tiles * gd.img_bytes);
-  w.total = w.imgB + al((size_t)N * tiles * gd.img_bytes);
+  w.imgT = w.imgB + al((size_t)N * tiles * gd.img_bytes);
+  w.total = w.imgT + al((size_t)N * tiles * kXTBytes);
   return w;
 }
 size_t gram_ws_bytes(int N, int k, int Dx, int Dz) { return gram_ws_layout(N, k, Dx, Dz).total; }
@@ -447,7 +511,7 @@ int gram_loss_parts(int N, int k) { const GramPlan g = gram_plan(N, k); return N
 int gram_js(int N, int k) { return gram_plan(N, k).JS; }
 
 static size_t gram_smem(int Dx, int Dz, bool pass2) {
-  return (size_t)2 * gram_dims(Dx, Dz).img_bytes + (pass2 ? (size_t)kGT * Dx * 4 : 0) + 4096 + 256;
+  return (size_t)2 * gram_dims(Dx, Dz).img_bytes + (pass2 ? (size_t)kXTBytes : 0) + 4096 + 256;
 }
 
 // mean -> scale -> operand images + norms; clears the ill-conditioning flag.  ws: gram_ws_bytes()
@@ -457,6 +521,8 @@ int gram_prepare(const float* x, const float* z, int N, int k, int Dx, int Dz, v
   const int tiles = (k + kGT - 1) / kGT;
   ndiv_prepack_kernel<<<dim3(tiles, N), 256, 0, s>>>(x, z, k, Dx, Dz, reinterpret_cast<uint8_t*>(b + w.imgA),
                                                      reinterpret_cast<uint8_t*>(b + w.imgB),
+                                                     reinterpret_cast<uint8_t*>(b + w.imgT),
+                                                     reinterpret_cast<float*>(b + w.mu),
                                                      reinterpret_cast<float2*>(b + w.norms),
                                                      reinterpret_cast<int*>(b + w.flag));
   NDP_LAUNCH_CHECK();
@@ -472,6 +538,8 @@ static void gram_fill(GramParams& p, int N, int k, int Dx, int Dz, void* ws, int
   p.imgA = reinterpret_cast<const uint8_t*>(b + w.imgA);
   p.imgB = reinterpret_cast<const uint8_t*>(b + w.imgB);
   p.norms = reinterpret_cast<const float2*>(b + w.norms);
+  p.imgT = reinterpret_cast<const uint8_t*>(b + w.imgT);
+  p.mu = reinterpret_cast<const float*>(b + w.mu);
   p.k = k; p.Dx = Dx; p.Dz = Dz; p.tiles = g.tiles; p.tps = g.tps; p.row0 = row0; p.rows = rows;
   p.ill = reinterpret_cast<int*>(b + w.flag);
 }
