@@ -69,7 +69,7 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
                     uint8_t* __restrict__ imgA, uint8_t* __restrict__ imgB, uint8_t* __restrict__ imgT,
                     float* __restrict__ mu_out, float2* __restrict__ norms, int* __restrict__ ill) {
   const int n = blockIdx.y, tile = blockIdx.x, tiles = gridDim.x;
-  if (n == 0 && tile == 0 && threadIdx.x == 0) *ill = 0;      // the main kernels raise it (stream order)
+  if (n == 0 && tile == 0 && blockIdx.z == 0 && threadIdx.x == 0) *ill = 0;   // the main kernels raise it (stream order)
   const GramDims gd = gram_dims(Dx, Dz);
   uint8_t* A = imgA + ((size_t)n * tiles + tile) * gd.img_bytes;
   uint8_t* B = imgB + ((size_t)n * tiles + tile) * gd.img_bytes;
@@ -109,13 +109,16 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
     }
     if (threadIdx.x == 0) {
       s_sc[0] = pick_scale(s_mx[0]); s_sc[1] = pick_scale(s_mz[0]);
-      norms[((size_t)n * tiles + tile) * kGNS + kGT] = make_float2(s_sc[0], s_sc[1]);
-      norms[((size_t)n * tiles + tile) * kGNS + kGT + 1] = make_float2(0.f, 0.f);
+      if (blockIdx.z == 0) {
+        norms[((size_t)n * tiles + tile) * kGNS + kGT] = make_float2(s_sc[0], s_sc[1]);
+        norms[((size_t)n * tiles + tile) * kGNS + kGT + 1] = make_float2(0.f, 0.f);
+      }
     }
     __syncthreads();
   }
   const int gx = (Dx + 15) / 16 * 2, gz = (Dz + 15) / 16 * 2;       // 8-dim groups per row (padded)
-  for (int it = threadIdx.x; it < kGT * (gx + gz); it += blockDim.x) {
+  const bool role_t = blockIdx.z == 1;                // second block of the tile: transposed image only
+  for (int it = threadIdx.x; !role_t && it < kGT * (gx + gz); it += blockDim.x) {
     const int r = it % kGT, g = it / kGT;
     const bool isx = g < gx;
     const int g8 = isx ? g : g - gx;
@@ -146,7 +149,7 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
   }
   // B operand of the gradient product  G[i, d] = sum_j What_ij c_j[d]:  rows = d (N = 32), K = j (128), K-major core
   // matrices [j/8][d/8][8 d][8 j]; fp16 hi (8 KB) then lo (8 KB) of the same scaled centred values as above.
-  if (imgT) {
+  if (role_t) {
     uint8_t* T = imgT + ((size_t)n * tiles + tile) * kXTBytes;
     for (int it = threadIdx.x; it < 16 * 32; it += blockDim.x) {
       const int d = it & 31, jg = it >> 5;
@@ -165,7 +168,7 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
     }
     if (tile == 0 && threadIdx.x < 64) mu_out[(size_t)n * 64 + threadIdx.x] = threadIdx.x < Dx ? mu[threadIdx.x] : 0.f;
   }
-  if (threadIdx.x < kGT) {                           // centred squared norms, fixed summation order
+  if (!role_t && threadIdx.x < kGT) {                // centred squared norms, fixed summation order
     const int row = tile * kGT + threadIdx.x;
     float nx = 0.f, nz = 0.f;
     if (row < k) {
@@ -519,7 +522,7 @@ int gram_prepare(const float* x, const float* z, int N, int k, int Dx, int Dz, v
   const GramWs w = gram_ws_layout(N, k, Dx, Dz);
   char* b = reinterpret_cast<char*>(ws);
   const int tiles = (k + kGT - 1) / kGT;
-  ndiv_prepack_kernel<<<dim3(tiles, N), 256, 0, s>>>(x, z, k, Dx, Dz, reinterpret_cast<uint8_t*>(b + w.imgA),
+  ndiv_prepack_kernel<<<dim3(tiles, N, 2), 256, 0, s>>>(x, z, k, Dx, Dz, reinterpret_cast<uint8_t*>(b + w.imgA),
                                                      reinterpret_cast<uint8_t*>(b + w.imgB),
                                                      reinterpret_cast<uint8_t*>(b + w.imgT),
                                                      reinterpret_cast<float*>(b + w.mu),
