@@ -120,7 +120,8 @@ def test_ndiv_row_sharded_equals_full(cuda):
     assert torch.equal(grad, full_grad)
 
 
-@pytest.mark.parametrize("N,k,Dx,Dz", [(1, 2048, 32, 16), (2, 1000, 32, 16), (1, 1600, 4, 2), (3, 700, 12, 5)])
+@pytest.mark.parametrize("N,k,Dx,Dz", [(1, 2048, 32, 16), (2, 1000, 32, 16), (1, 1600, 4, 2), (3, 700, 12, 5),
+                                       (1, 1536, 32, 32), (2, 900, 8, 31), (6, 256, 16, 16)])
 def test_ndiv_gram_fast_path_vs_oracle(cuda, N, k, Dx, Dz):
     """shapes that take the tensor-core Gram path (N*k >= 1536, D <= 32): loss within 1e-4 of the fp64 oracle,
     row sums within 1e-5, gradient within 1e-4 of its max"""
@@ -152,6 +153,17 @@ def test_ndiv_gram_falls_back_on_near_duplicates(cuda):
     # this k, so compare the row sums of the duplicated rows: exact zeros on the diagonal and between duplicates)
     d = div.compute_pairwise(x.cuda())
     assert float(d[0, 100, 7]) == 0.0 and float(d[0, 7, 7]) == 0.0
+
+
+def test_ndiv_gram_scale_invariance(cuda):
+    """operand scaling: tiny and huge data magnitudes go through the fp16-split Gram path without losing digits
+    (per-tile power-of-two scales), loss is scale invariant (normalised distances)"""
+    x, z = synthetic.make_ndiv_inputs(1, 1536, 32, 16, seed=5)
+    base, _ = _run(x, z)
+    for sxf, szf in ((1e-6, 1e4), (3e5, 1e-5)):
+        loss, grad = _run(x * sxf, z * szf)
+        np.testing.assert_allclose(loss.numpy(), base.numpy(), rtol=RTOL)
+        assert torch.isfinite(grad).all()
 
 
 def test_ndiv_gram_row_sharded_equals_full(cuda):
