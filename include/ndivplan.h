@@ -188,6 +188,45 @@ int ndp_pairwise(const float* v, int N, int k, int C, int normalise, float* out,
 int ndp_pairwise_backward(const float* v, const float* grad_out, int N, int k, int C,
                           int normalise, float* rowsum_ws, float* grad_v, void* stream);
 
+/* ---- GAN training step around the ndiv loss -----------------
+ * One ndp_gan_train_step == one iteration of the loop body train_gan.py:159-203 on encoded inputs:
+ *   a_hat = G([codes | noise])  (Decoder, gan.py:63-86);  d_steps x { D_loss = BCE(D(actions, codes), 1) +
+ *   BCE(D(a_hat, codes), 0); Adam(D) }  (Discriminator, gan.py:89-110; train_gan.py:172-184);  G_loss =
+ *   BCE(D(a_hat, codes), 1) (:187-190);  div = compute_pairwise_divergence(a_hat[F,S,A], noise[F,S,nd]) (:193-196);
+ *   Adam(G) on G_loss + div_factor * div (:198-203).  Optimisers: torch.optim.Adam(lr, betas) of :98-104 (the
+ *   encoder parameters in G_optimizer never receive a gradient: its outputs are detached, :152-153).
+ * The handle owns parameters, Adam state and all scratch (sized for max_F codes); all work is stream-ordered
+ * without host synchronisation (capturable in a CUDA graph).  The layer widths are the reference's:
+ * G: C+nd -> 128 -> 64 -> 128 -> 256 -> A (ReLU), D: A+C -> 64 -> 128 -> 256 -> 1 (leaky ReLU 0.01). */
+typedef struct ndp_gan ndp_gan;
+typedef struct {
+  int32_t C;        /* conditioning width (256 = state | goal embedding) */
+  int32_t nd;       /* noise_dim */
+  int32_t A;        /* action dim (4) */
+  int32_t S;        /* num_sample: samples per code, the ndiv group size k */
+  int32_t max_F;    /* largest number of codes per step (batch_size * (seq_length-1)) */
+  int32_t d_steps;  /* discrim_steps_per_gen */
+  float margin;     /* 0.8 (diversity.py:40) */
+  float div_factor; /* pairwise_div_factor */
+  double lr, beta1, beta2, eps;   /* Adam: 2e-4, 0.5, 0.999, 1e-8 */
+} ndp_gan_desc;
+int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d);
+void ndp_gan_destroy(ndp_gan* g);
+/* device pointers to torch [out,in] weights / biases: 5 generator layers, 4 discriminator layers; copies them
+ * and resets both optimisers (step 0, zero moments) */
+int ndp_gan_load(ndp_gan* g, const float* const* gW, const float* const* gb, const float* const* dW,
+                 const float* const* db, void* stream);
+int ndp_gan_export(ndp_gan* g, float* const* gW, float* const* gb, float* const* dW, float* const* db,
+                   void* stream);
+/* codes [F,C], actions [F,A], noise [F,S,nd]; losses[3] = {D_loss, G_loss, pair_div_loss} (all device fp32) */
+int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, const float* noise, int F,
+                       float* losses, void* stream);
+int ndp_gan_set_lr(ndp_gan* g, double lr, void* stream);        /* StepLR (train_gan.py:105) lives in the caller */
+/* inspection: flat [W0|b0|W1|b1|...] gradients of the last step (either may be NULL), a_hat [F*S,A] */
+int ndp_gan_param_counts(const ndp_gan* g, size_t* n_gen, size_t* n_dis);
+int ndp_gan_grads(ndp_gan* g, float* gen_flat, float* dis_flat, void* stream);
+int ndp_gan_last_actions(ndp_gan* g, float* a_hat, int F, void* stream);
+
 /* ---- collectives (NCCL over NVLink; libnccl is dlopen'ed on first use) ----------- */
 int ndp_comm_unique_id(void* id128_host);                       /* 128-byte ncclUniqueId */
 int ndp_comm_create(ndp_comm** out, const void* id128_host, int rank, int world);

@@ -21,6 +21,12 @@ class PlannerDesc(C.Structure):
                 ("precision", C.c_int)]
 
 
+class GanDesc(C.Structure):
+    _fields_ = [("C", C.c_int32), ("nd", C.c_int32), ("A", C.c_int32), ("S", C.c_int32), ("max_F", C.c_int32),
+                ("d_steps", C.c_int32), ("margin", C.c_float), ("div_factor", C.c_float), ("lr", C.c_double),
+                ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
+
+
 _vp, _i, _i64, _sz, _f = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
 _PROTOS = {
     "ndp_abi_version": (_i, []),
@@ -50,6 +56,15 @@ _PROTOS = {
     "ndp_ndiv_forward_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_pairwise": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "ndp_pairwise_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "ndp_gan_create": (_i, [C.POINTER(_vp), C.POINTER(GanDesc)]),
+    "ndp_gan_destroy": (None, [_vp]),
+    "ndp_gan_load": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _vp]),
+    "ndp_gan_export": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _vp]),
+    "ndp_gan_train_step": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "ndp_gan_set_lr": (_i, [_vp, C.c_double, _vp]),
+    "ndp_gan_param_counts": (_i, [_vp, C.POINTER(_sz), C.POINTER(_sz)]),
+    "ndp_gan_grads": (_i, [_vp, _vp, _vp, _vp]),
+    "ndp_gan_last_actions": (_i, [_vp, _vp, _i, _vp]),
     "ndp_comm_unique_id": (_i, [_vp]),
     "ndp_comm_create": (_i, [C.POINTER(_vp), _vp, _i, _i]),
     "ndp_comm_allreduce_min_u64": (_i, [_vp, _vp, _i, _vp]),

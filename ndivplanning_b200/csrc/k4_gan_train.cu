@@ -1,0 +1,558 @@
+// K4 — the GAN training step around the ndiv loss (train_gan.py:159-203), device resident:
+//
+//   a_hat  = G([codes | noise])                                    train_gan.py:159-165   (gan.py:79-86)
+//   repeat d_steps:  D_loss = BCE(D(a, codes), 1) + BCE(D(a_hat, codes), 0);  Adam(D)      :172-184
+//   G_loss = BCE(D(a_hat, codes), 1)                               :187-190  (discriminator AFTER its update)
+//   div    = compute_pairwise_divergence(a_hat[F,S,4], noise[F,S,nd])   :193-196  (K2, k2_ndiv.cu)
+//   total  = G_loss + div_factor * div;  Adam(G)                   :198-203
+//
+// Everything is stream-ordered with no host synchronisation, so a caller may capture one step in a CUDA graph.
+// This file is the exact-arithmetic (fp32 FFMA) implementation: every dense layer, its input gradient and its
+// weight gradient go through ONE smem-tiled kernel template (gemm_kernel<MODE,TJ>) whose operand loaders
+// express the three products without materialising a concatenation, a repeat_interleave or a transpose:
+//
+//   FWD  Y[m,n]   = act( sum_k X(m,k) W[n,k] + b[n] )               X(m,k) = [P0[m/div0] | P1[m/div1]]
+//   DX   dP'[m,k] = ( sum_n dP[m,n] W[n,k0+k] ) * act'(H[m,k]) (+ s * addend[m,k])
+//   DW   dW[n,k]  = sum_m dP[m,n] X(m,k),  db[n] = sum_m dP[m,n]    rows split over blockIdx.z, partials summed
+//                                                                   in a fixed order by the Adam kernel
+//
+// Algebra the reference leaves on the table and this step uses: the "real" discriminator batch is S identical
+// copies of F distinct rows (repeat_interleave at :139-141), and BCE is a mean, so loss and gradients are
+// evaluated on the F distinct rows only; torch.cat / repeat_interleave inputs are read through (row / div)
+// index maps.  Weight gradients are deterministic (no atomics).
+#include <math.h>
+#include <vector>
+#include "common.cuh"
+
+namespace ndp {
+namespace gan {
+
+enum { FWD = 0, DX = 1, DW = 2 };
+enum { ACT_NONE = 0, ACT_RELU = 1, ACT_LEAKY = 2 };
+constexpr int kTI = 64, kTC = 16, kThreads = 256;
+constexpr float kLeaky = 0.01f;   // F.leaky_relu default negative_slope (gan.py:103-105)
+
+struct RowSrc {   // logical [M x (k0+k1)] matrix assembled from two row-indexed sources
+  const float* p0; int k0, ld0, div0;
+  const float* p1; int k1, ld1, div1;
+  __device__ __forceinline__ float at(int r, int k) const {
+    return k < k0 ? __ldg(p0 + (size_t)(r / div0) * ld0 + k) : __ldg(p1 + (size_t)(r / div1) * ld1 + (k - k0));
+  }
+};
+static RowSrc row_src(const float* p0, int k0, int div0, const float* p1 = nullptr, int k1 = 0, int div1 = 1) {
+  RowSrc r; r.p0 = p0; r.k0 = k0; r.ld0 = k0; r.div0 = div0; r.p1 = p1; r.k1 = k1; r.ld1 = k1; r.div1 = div1;
+  return r;
+}
+
+struct GemmP {
+  int I, J, Cn;            // output rows, output cols, contraction length
+  RowSrc x;                // FWD: A operand; DW: B operand
+  const float* W; int ldw, wk0;
+  const float* b; int act;
+  const float* dP; int ldp;
+  const float* hprev; int ldh, act_prev;
+  const float* addend; float add_scale;
+  float* out; int ldo;
+  int rows_per_split; size_t split_stride; float* db_out;
+};
+
+__device__ __forceinline__ float act_fwd(float v, int act) {
+  if (act == ACT_RELU) return fmaxf(v, 0.f);
+  if (act == ACT_LEAKY) return v > 0.f ? v : v * kLeaky;
+  return v;
+}
+// derivative from the saved post-activation value (sign(h) == sign(pre-activation) for both)
+__device__ __forceinline__ float act_bwd(float h, int act) {
+  if (act == ACT_RELU) return h > 0.f ? 1.f : 0.f;
+  if (act == ACT_LEAKY) return h > 0.f ? 1.f : kLeaky;
+  return 1.f;
+}
+
+template <int MODE, int TJ>
+__global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
+  constexpr int RJ = TJ / 16;
+  __shared__ __align__(16) float As[kTC][kTI + 4];
+  __shared__ __align__(16) float Bs[kTC][TJ + 4];
+  const int t = threadIdx.x;
+  const int i0 = blockIdx.x * kTI, j0 = blockIdx.y * TJ;
+  int c_begin = 0, c_end = p.Cn;
+  if (MODE == DW) {
+    c_begin = blockIdx.z * p.rows_per_split;
+    c_end = min(p.Cn, c_begin + p.rows_per_split);
+  }
+  const int ti = t >> 4, tj = t & 15;
+  float acc[4][RJ];
+#pragma unroll
+  for (int a = 0; a < 4; a++)
+#pragma unroll
+    for (int b = 0; b < RJ; b++) acc[a][b] = 0.f;
+  float bsum = 0.f;
+
+  for (int c0 = c_begin; c0 < c_end; c0 += kTC) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const int e = t + q * kThreads;
+      int i, c;
+      if (MODE == DW) { i = e & (kTI - 1); c = e >> 6; } else { c = e & (kTC - 1); i = e >> 4; }
+      const int gi = i0 + i, gc = c0 + c;
+      float v = 0.f;
+      if (gi < p.I && gc < c_end) {
+        if (MODE == FWD) v = p.x.at(gi, gc);
+        else if (MODE == DX) v = __ldg(p.dP + (size_t)gi * p.ldp + gc);
+        else v = __ldg(p.dP + (size_t)gc * p.ldp + gi);
+      }
+      As[c][i] = v;
+    }
+    for (int e = t; e < TJ * kTC; e += kThreads) {
+      int j, c;
+      if (MODE == FWD) { c = e & (kTC - 1); j = e >> 4; } else { j = e % TJ; c = e / TJ; }
+      const int gj = j0 + j, gc = c0 + c;
+      float v = 0.f;
+      if (gj < p.J && gc < c_end) {
+        if (MODE == FWD) v = __ldg(p.W + (size_t)gj * p.ldw + gc);
+        else if (MODE == DX) v = __ldg(p.W + (size_t)gc * p.ldw + p.wk0 + gj);
+        else v = p.x.at(gc, gj);
+      }
+      Bs[c][j] = v;
+    }
+    __syncthreads();
+    if (MODE == DW && blockIdx.y == 0 && t < kTI) {
+#pragma unroll
+      for (int c = 0; c < kTC; c++) bsum += As[c][t];
+    }
+#pragma unroll
+    for (int c = 0; c < kTC; c++) {
+      const float4 av = *reinterpret_cast<const float4*>(&As[c][ti * 4]);
+      const float a[4] = {av.x, av.y, av.z, av.w};
+      float b[RJ];
+      if (RJ == 4) {
+        const float4 bv = *reinterpret_cast<const float4*>(&Bs[c][tj * 4]);
+        b[0] = bv.x; b[1 % RJ] = bv.y; b[2 % RJ] = bv.z; b[3 % RJ] = bv.w;
+      } else {
+        b[0] = Bs[c][tj];
+      }
+#pragma unroll
+      for (int x = 0; x < 4; x++)
+#pragma unroll
+        for (int y = 0; y < RJ; y++) acc[x][y] = fmaf(a[x], b[y], acc[x][y]);
+    }
+    __syncthreads();
+  }
+
+  float* out = p.out;
+  if (MODE == DW) out += (size_t)blockIdx.z * p.split_stride;
+#pragma unroll
+  for (int x = 0; x < 4; x++) {
+    const int gi = i0 + ti * 4 + x;
+    if (gi >= p.I) continue;
+#pragma unroll
+    for (int y = 0; y < RJ; y++) {
+      const int gj = j0 + tj * RJ + y;
+      if (gj >= p.J) continue;
+      float v = acc[x][y];
+      if (MODE == FWD) {
+        v = act_fwd(v + __ldg(p.b + gj), p.act);
+      } else if (MODE == DX) {
+        if (p.hprev) v *= act_bwd(__ldg(p.hprev + (size_t)gi * p.ldh + gj), p.act_prev);
+        if (p.addend) v = fmaf(p.add_scale, __ldg(p.addend + (size_t)gi * p.J + gj), v);
+      }
+      out[(size_t)gi * p.ldo + gj] = v;
+    }
+  }
+  if (MODE == DW && blockIdx.y == 0 && t < kTI && i0 + t < p.I)
+    p.db_out[(size_t)blockIdx.z * p.split_stride + i0 + t] = bsum;
+}
+
+template <int MODE>
+static int launch_gemm(const GemmP& p, int splits, cudaStream_t s) {
+  const dim3 block(kThreads);
+  if (p.J >= 64) {
+    const dim3 grid((p.I + kTI - 1) / kTI, (p.J + 63) / 64, splits);
+    gemm_kernel<MODE, 64><<<grid, block, 0, s>>>(p);
+  } else {
+    const dim3 grid((p.I + kTI - 1) / kTI, (p.J + 15) / 16, splits);
+    gemm_kernel<MODE, 16><<<grid, block, 0, s>>>(p);
+  }
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+// ---- BCE-with-logits (mean) for up to two (logits, target) sets; writes the summed loss and d loss / d logit.
+// nn.BCEWithLogitsLoss: l = (1-y) x + max(-x,0) + log(exp(-max(-x,0)) + exp(-x-max(-x,0))) = (1-y) x + softplus(-x).
+// One block: the reduction order is fixed.  Also advances the Adam step counter of the optimiser that consumes
+// these gradients (each optimiser step in train_gan.py is preceded by exactly one loss evaluation).
+__global__ void __launch_bounds__(1024) bce_kernel(const float* __restrict__ x0, int n0, float y0,
+                                                    float* __restrict__ dl0, const float* __restrict__ x1, int n1,
+                                                    float y1, float* __restrict__ dl1, float* __restrict__ loss_out,
+                                                    int* __restrict__ step_counter) {
+  __shared__ float red[32];
+  float tot = 0.f;
+  for (int set = 0; set < 2; set++) {
+    const float* x = set ? x1 : x0;
+    const int n = set ? n1 : n0;
+    const float y = set ? y1 : y0;
+    float* dl = set ? dl1 : dl0;
+    if (n <= 0) continue;
+    const float inv = 1.f / (float)n;
+    float s = 0.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+      const float v = x[i];
+      const float e = expf(-fabsf(v));
+      s += (1.f - y) * v + fmaxf(-v, 0.f) + log1pf(e);
+      const float sig = v >= 0.f ? 1.f / (1.f + e) : e / (1.f + e);
+      dl[i] = (sig - y) * inv;
+    }
+    tot += s * inv;
+  }
+  for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = tot;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0) {
+      *loss_out = v;
+      *step_counter += 1;
+    }
+  }
+}
+
+// ---- Adam (torch.optim.Adam defaults: no weight decay, no amsgrad; train_gan.py:98-104) over one flat parameter
+// buffer; the gradient is the fixed-order sum of the DW partial slots.  hp = {lr, beta1, beta2, eps} in double,
+// as the Python floats the reference passes.
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, float* __restrict__ m,
+                                                   float* __restrict__ v, const float* __restrict__ part,
+                                                   int nparts, size_t stride, int P, const double* __restrict__ hp,
+                                                   const int* __restrict__ step, float* __restrict__ grad_out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  float g = 0.f;
+  for (int s = 0; s < nparts; s++) g += part[(size_t)s * stride + i];
+  if (grad_out) grad_out[i] = g;
+  const double lr = hp[0], b1 = hp[1], b2 = hp[2], eps = hp[3];
+  const int t = *step;
+  const double bc1 = 1.0 - pow(b1, (double)t), bc2 = 1.0 - pow(b2, (double)t);
+  const float step_size = (float)(lr / bc1), bc2_sqrt = (float)sqrt(bc2);
+  const float w1 = (float)(1.0 - b1);
+  float mi = m[i], vi = v[i];
+  mi = w1 < 0.5f ? mi + w1 * (g - mi) : g - (g - mi) * (1.f - w1);     // exp_avg.lerp_(grad, 1 - beta1)
+  vi = vi * (float)b2 + (float)(1.0 - b2) * g * g;                      // mul_(beta2).addcmul_(grad, grad, 1-beta2)
+  const float denom = sqrtf(vi) / bc2_sqrt + (float)eps;
+  p[i] = p[i] - step_size * (mi / denom);
+  m[i] = mi;
+  v[i] = vi;
+}
+
+// ---- network description: flat parameter buffer [W0 | b0 | W1 | b1 | ...], torch [out,in] weights
+struct Net {
+  int L;
+  int in[5], out[5];
+  size_t w_off[5], b_off[5];
+  size_t P;
+  void init(int L_, const int* in_, const int* out_) {
+    L = L_;
+    P = 0;
+    for (int l = 0; l < L; l++) {
+      in[l] = in_[l]; out[l] = out_[l];
+      w_off[l] = P; P += (size_t)in[l] * out[l];
+      b_off[l] = P; P += out[l];
+    }
+  }
+};
+
+static void split_plan(int M, int* splits, int* rows_per_split) {
+  int s = (M + 63) / 64;
+  if (s > 32) s = 32;
+  if (s < 1) s = 1;
+  int rps = (M + s - 1) / s;
+  rps = (rps + kTC - 1) / kTC * kTC;
+  *rows_per_split = rps;
+  *splits = (M + rps - 1) / rps;
+}
+
+// acts[l] = output of layer l ([M x out[l]]); hidden activation `act`, none on the last layer
+static int mlp_forward(const Net& n, const float* params, const RowSrc& x0, int M, float* const* acts, int act,
+                       cudaStream_t s) {
+  for (int l = 0; l < n.L; l++) {
+    GemmP p = {};
+    p.I = M; p.J = n.out[l]; p.Cn = n.in[l];
+    p.x = l == 0 ? x0 : row_src(acts[l - 1], n.in[l], 1);
+    p.W = params + n.w_off[l]; p.ldw = n.in[l];
+    p.b = params + n.b_off[l];
+    p.act = l + 1 < n.L ? act : ACT_NONE;
+    p.out = acts[l]; p.ldo = n.out[l];
+    int rc = launch_gemm<FWD>(p, 1, s);
+    if (rc) return rc;
+  }
+  return NDP_OK;
+}
+
+// d_out = d loss / d (last layer output) [M x out[L-1]].  part != NULL: weight/bias gradient partials into slots
+// [slot0, slot0+splits) of part (slot stride n.P).  dx0 != NULL: d loss / d input columns [col0, col0+ncols) of
+// layer 0 (+ add_scale * addend).  bufA/bufB: [M x max hidden width] ping-pong scratch.
+static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int M, float* const* acts,
+                        const float* d_out, float* bufA, float* bufB, int act, float* part, int slot0,
+                        float* dx0, int col0, int ncols, const float* addend, float add_scale, cudaStream_t s) {
+  int splits, rps;
+  split_plan(M, &splits, &rps);
+  const float* cur = d_out;
+  float* nxt = bufA;
+  for (int l = n.L - 1; l >= 0; l--) {
+    if (part) {
+      GemmP p = {};
+      p.I = n.out[l]; p.J = n.in[l]; p.Cn = M;
+      p.dP = cur; p.ldp = n.out[l];
+      p.x = l == 0 ? x0 : row_src(acts[l - 1], n.in[l], 1);
+      p.out = part + (size_t)slot0 * n.P + n.w_off[l]; p.ldo = n.in[l];
+      p.db_out = part + (size_t)slot0 * n.P + n.b_off[l];
+      p.rows_per_split = rps; p.split_stride = n.P;
+      int rc = launch_gemm<DW>(p, splits, s);
+      if (rc) return rc;
+    }
+    if (l > 0 || dx0) {
+      GemmP p = {};
+      p.I = M; p.Cn = n.out[l];
+      p.dP = cur; p.ldp = n.out[l];
+      p.W = params + n.w_off[l]; p.ldw = n.in[l];
+      if (l > 0) {
+        p.J = n.in[l]; p.wk0 = 0;
+        p.hprev = acts[l - 1]; p.ldh = n.in[l]; p.act_prev = act;
+        p.out = nxt; p.ldo = n.in[l];
+      } else {
+        p.J = ncols; p.wk0 = col0;
+        p.addend = addend; p.add_scale = add_scale;
+        p.out = dx0; p.ldo = ncols;
+      }
+      int rc = launch_gemm<DX>(p, 1, s);
+      if (rc) return rc;
+      cur = nxt;
+      nxt = (nxt == bufA) ? bufB : bufA;
+    }
+  }
+  return NDP_OK;
+}
+
+}  // namespace gan
+}  // namespace ndp
+
+// ---- handle ------------------------------------------------------------------------------------------------
+using namespace ndp;
+using namespace ndp::gan;
+
+struct ndp_gan {
+  ndp_gan_desc d;
+  Net G, D;
+  int B_max;
+  void* arena;
+  float *gp, *gm, *gv, *gg, *dp, *dm, *dv, *dg;
+  double* hp;        // {lr, beta1, beta2, eps}
+  int* steps;        // [0] discriminator, [1] generator optimiser step counts
+  float* g_act[5];   // generator layer outputs, B rows; g_act[4] = a_hat
+  float* dr_act[4];  // discriminator on the F distinct real rows
+  float* df_act[4];  // discriminator on the B generated rows
+  float *dl_real, *dl_fake, *bufA, *bufB, *g_div, *da, *sx, *sz;
+  float *g_part, *d_part;
+  void* ndiv_ws;
+  size_t ndiv_ws_bytes;
+};
+
+__global__ void set_hp_kernel(double* hp, double lr, double b1, double b2, double eps, int mask) {
+  if (mask & 1) hp[0] = lr;
+  if (mask & 2) hp[1] = b1;
+  if (mask & 4) hp[2] = b2;
+  if (mask & 8) hp[3] = eps;
+}
+
+static size_t carve(size_t& off, size_t bytes) {
+  const size_t o = off;
+  off += (bytes + 255) & ~(size_t)255;
+  return o;
+}
+
+extern "C" {
+
+int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
+  NDP_CHECK_ARG(out && d, "ndp_gan_create: null argument");
+  int rc = device_check();
+  if (rc) return rc;
+  NDP_CHECK_ARG(d->C > 0 && d->nd > 0 && d->A > 0 && d->S > 0 && d->max_F > 0, "ndp_gan_create: bad sizes");
+  NDP_CHECK_ARG(d->d_steps >= 0, "ndp_gan_create: d_steps < 0");
+  NDP_CHECK_ARG((long long)d->max_F * d->S < (1ll << 24), "ndp_gan_create: max_F * S must stay below 2^24 rows");
+  ndp_gan* g = new ndp_gan();
+  g->d = *d;
+  const int gin[5] = {d->C + d->nd, 128, 64, 128, 256}, gout[5] = {128, 64, 128, 256, d->A};   // gan.py:67-71
+  const int din[4] = {d->A + d->C, 64, 128, 256}, dout[4] = {64, 128, 256, 1};                 // gan.py:93-96
+  g->G.init(5, gin, gout);
+  g->D.init(4, din, dout);
+  const size_t F = d->max_F, B = F * d->S;
+  g->B_max = (int)B;
+  size_t ndiv_bytes = 0;
+  rc = ndp_ndiv_workspace_bytes(d->max_F, d->S, d->A, d->nd, &ndiv_bytes);
+  if (rc) { delete g; return rc; }
+  g->ndiv_ws_bytes = ndiv_bytes;
+
+  size_t off = 0;
+  const size_t PG = g->G.P, PD = g->D.P;
+  const size_t o_gp = carve(off, 4 * PG * 4), o_dp = carve(off, 4 * PD * 4);
+  const size_t o_hp = carve(off, 4 * sizeof(double)), o_steps = carve(off, 2 * sizeof(int));
+  size_t o_g[5], o_dr[4], o_df[4];
+  for (int l = 0; l < 5; l++) o_g[l] = carve(off, B * gout[l] * 4);
+  for (int l = 0; l < 4; l++) o_dr[l] = carve(off, F * dout[l] * 4);
+  for (int l = 0; l < 4; l++) o_df[l] = carve(off, B * dout[l] * 4);
+  const size_t o_dlr = carve(off, F * 4), o_dlf = carve(off, B * 4);
+  const size_t o_bA = carve(off, B * 256 * 4), o_bB = carve(off, B * 256 * 4);
+  const size_t o_gdiv = carve(off, B * d->A * 4), o_da = carve(off, B * d->A * 4);
+  const size_t o_sx = carve(off, B * 4), o_sz = carve(off, B * 4);
+  const size_t o_gpart = carve(off, 32 * PG * 4), o_dpart = carve(off, 64 * PD * 4);
+  const size_t o_ws = carve(off, ndiv_bytes);
+  cudaError_t e = cudaMalloc(&g->arena, off);
+  if (e != cudaSuccess) {
+    set_error("ndp_gan_create: cudaMalloc(%zu) failed: %s", off, cudaGetErrorString(e));
+    delete g;
+    return NDP_ERR_CUDA;
+  }
+  char* base = (char*)g->arena;
+  g->gp = (float*)(base + o_gp); g->gm = g->gp + PG; g->gv = g->gm + PG; g->gg = g->gv + PG;
+  g->dp = (float*)(base + o_dp); g->dm = g->dp + PD; g->dv = g->dm + PD; g->dg = g->dv + PD;
+  g->hp = (double*)(base + o_hp); g->steps = (int*)(base + o_steps);
+  for (int l = 0; l < 5; l++) g->g_act[l] = (float*)(base + o_g[l]);
+  for (int l = 0; l < 4; l++) { g->dr_act[l] = (float*)(base + o_dr[l]); g->df_act[l] = (float*)(base + o_df[l]); }
+  g->dl_real = (float*)(base + o_dlr); g->dl_fake = (float*)(base + o_dlf);
+  g->bufA = (float*)(base + o_bA); g->bufB = (float*)(base + o_bB);
+  g->g_div = (float*)(base + o_gdiv); g->da = (float*)(base + o_da);
+  g->sx = (float*)(base + o_sx); g->sz = (float*)(base + o_sz);
+  g->g_part = (float*)(base + o_gpart); g->d_part = (float*)(base + o_dpart);
+  g->ndiv_ws = base + o_ws;
+  *out = g;
+  return NDP_OK;
+}
+
+void ndp_gan_destroy(ndp_gan* g) {
+  if (!g) return;
+  cudaFree(g->arena);
+  delete g;
+}
+
+// Copies the parameters (torch [out,in] weights, device pointers) into the handle and resets both optimisers.
+int ndp_gan_load(ndp_gan* g, const float* const* gW, const float* const* gb, const float* const* dW,
+                 const float* const* db, void* stream) {
+  NDP_CHECK_ARG(g && gW && gb && dW && db, "ndp_gan_load: null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int l = 0; l < g->G.L; l++) {
+    NDP_CUDA(cudaMemcpyAsync(g->gp + g->G.w_off[l], gW[l], (size_t)g->G.in[l] * g->G.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+    NDP_CUDA(cudaMemcpyAsync(g->gp + g->G.b_off[l], gb[l], (size_t)g->G.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  for (int l = 0; l < g->D.L; l++) {
+    NDP_CUDA(cudaMemcpyAsync(g->dp + g->D.w_off[l], dW[l], (size_t)g->D.in[l] * g->D.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+    NDP_CUDA(cudaMemcpyAsync(g->dp + g->D.b_off[l], db[l], (size_t)g->D.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  NDP_CUDA(cudaMemsetAsync(g->gm, 0, 3 * g->G.P * 4, s));
+  NDP_CUDA(cudaMemsetAsync(g->dm, 0, 3 * g->D.P * 4, s));
+  NDP_CUDA(cudaMemsetAsync(g->steps, 0, 2 * sizeof(int), s));
+  set_hp_kernel<<<1, 1, 0, s>>>(g->hp, g->d.lr, g->d.beta1, g->d.beta2, g->d.eps, 15);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+int ndp_gan_export(ndp_gan* g, float* const* gW, float* const* gb, float* const* dW, float* const* db,
+                   void* stream) {
+  NDP_CHECK_ARG(g && gW && gb && dW && db, "ndp_gan_export: null argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int l = 0; l < g->G.L; l++) {
+    NDP_CUDA(cudaMemcpyAsync(gW[l], g->gp + g->G.w_off[l], (size_t)g->G.in[l] * g->G.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+    NDP_CUDA(cudaMemcpyAsync(gb[l], g->gp + g->G.b_off[l], (size_t)g->G.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  for (int l = 0; l < g->D.L; l++) {
+    NDP_CUDA(cudaMemcpyAsync(dW[l], g->dp + g->D.w_off[l], (size_t)g->D.in[l] * g->D.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+    NDP_CUDA(cudaMemcpyAsync(db[l], g->dp + g->D.b_off[l], (size_t)g->D.out[l] * 4, cudaMemcpyDeviceToDevice, s));
+  }
+  return NDP_OK;
+}
+
+// Gradients of the last step in the flat layout [W0 | b0 | W1 | b1 | ...]: generator (of G_loss + factor*div),
+// discriminator (of D_loss, last discriminator step).  Either pointer may be NULL.
+int ndp_gan_param_counts(const ndp_gan* g, size_t* n_gen, size_t* n_dis) {
+  NDP_CHECK_ARG(g && n_gen && n_dis, "ndp_gan_param_counts: null argument");
+  *n_gen = g->G.P;
+  *n_dis = g->D.P;
+  return NDP_OK;
+}
+int ndp_gan_grads(ndp_gan* g, float* gen_flat, float* dis_flat, void* stream) {
+  NDP_CHECK_ARG(g, "ndp_gan_grads: null handle");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (gen_flat) NDP_CUDA(cudaMemcpyAsync(gen_flat, g->gg, g->G.P * 4, cudaMemcpyDeviceToDevice, s));
+  if (dis_flat) NDP_CUDA(cudaMemcpyAsync(dis_flat, g->dg, g->D.P * 4, cudaMemcpyDeviceToDevice, s));
+  return NDP_OK;
+}
+
+int ndp_gan_set_lr(ndp_gan* g, double lr, void* stream) {
+  NDP_CHECK_ARG(g && lr >= 0.0, "ndp_gan_set_lr: bad argument");
+  set_hp_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(g->hp, lr, 0, 0, 0, 1);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+static int adam(float* p, float* m, float* v, float* grad, const float* part, int nparts, size_t P, const double* hp,
+                const int* step, cudaStream_t s) {
+  adam_kernel<<<(unsigned)((P + 255) / 256), 256, 0, s>>>(p, m, v, part, nparts, P, (int)P, hp, step, grad);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
+
+// One iteration of the loop body train_gan.py:159-203 for F (state, goal) codes with S samples each.
+// codes [F,C], actions [F,A], noise [F,S,nd] (device, fp32); losses [3] (device) = {D_loss, G_loss, pair_div_loss}.
+int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, const float* noise, int F,
+                       float* losses, void* stream) {
+  NDP_CHECK_ARG(g && codes && actions && noise && losses, "ndp_gan_train_step: null argument");
+  NDP_CHECK_ARG(F > 0 && F <= g->d.max_F, "ndp_gan_train_step: F=%d outside (0, max_F=%d]", F, g->d.max_F);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int S = g->d.S, C = g->d.C, A = g->d.A, nd = g->d.nd, B = F * S;
+  int rc;
+#define NDP_TRY(x) do { rc = (x); if (rc) return rc; } while (0)
+  // generator forward on [codes repeated S times | noise]                      (train_gan.py:159-165)
+  const RowSrc xg = row_src(codes, C, S, noise, nd, 1);
+  NDP_TRY(mlp_forward(g->G, g->gp, xg, B, g->g_act, ACT_RELU, s));
+  const float* a_hat = g->g_act[4];
+  const RowSrc x_real = row_src(actions, A, 1, codes, C, 1);     // cat([action, state_code]) gan.py:102
+  const RowSrc x_fake = row_src(a_hat, A, 1, codes, C, S);
+  int sr, sf, rps;
+  split_plan(F, &sr, &rps);
+  split_plan(B, &sf, &rps);
+  for (int it = 0; it < g->d.d_steps; it++) {                    // :172-184
+    NDP_TRY(mlp_forward(g->D, g->dp, x_real, F, g->dr_act, ACT_LEAKY, s));
+    NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, s));
+    bce_kernel<<<1, 1024, 0, s>>>(g->dr_act[3], F, 1.f, g->dl_real, g->df_act[3], B, 0.f, g->dl_fake, losses + 0,
+                                  g->steps + 0);
+    NDP_LAUNCH_CHECK();
+    NDP_TRY(mlp_backward(g->D, g->dp, x_real, F, g->dr_act, g->dl_real, g->bufA, g->bufB, ACT_LEAKY, g->d_part, 0,
+                         nullptr, 0, 0, nullptr, 0.f, s));
+    NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, g->d_part, sr,
+                         nullptr, 0, 0, nullptr, 0.f, s));
+    NDP_TRY(adam(g->dp, g->dm, g->dv, g->dg, g->d_part, sr + sf, g->D.P, g->hp, g->steps + 0, s));
+  }
+  // generator loss through the UPDATED discriminator                            (:187-190)
+  NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, s));
+  bce_kernel<<<1, 1024, 0, s>>>(g->df_act[3], B, 1.f, g->dl_fake, nullptr, 0, 0.f, nullptr, losses + 1, g->steps + 1);
+  NDP_LAUNCH_CHECK();
+  // normalized diversification of the S samples of every code                   (:193-196)
+  NDP_TRY(ndp_ndiv_forward_backward(a_hat, noise, F, S, A, nd, g->d.margin, g->sx, g->sz, losses + 2, g->g_div,
+                                    g->ndiv_ws, g->ndiv_ws_bytes, stream));
+  // d total / d a_hat = dD/da_hat (first A input columns of discriminator fc1) + div_factor * d div / d a_hat
+  NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, nullptr, 0, g->da,
+                       0, A, g->g_div, g->d.div_factor, s));
+  NDP_TRY(mlp_backward(g->G, g->gp, xg, B, g->g_act, g->da, g->bufA, g->bufB, ACT_RELU, g->g_part, 0, nullptr, 0, 0,
+                       nullptr, 0.f, s));
+  NDP_TRY(adam(g->gp, g->gm, g->gv, g->gg, g->g_part, sf, g->G.P, g->hp, g->steps + 1, s));   // :198-203
+#undef NDP_TRY
+  return NDP_OK;
+}
+
+// a_hat of the last step ([F*S, A]) — what train_gan.py:165 calls action_hat
+int ndp_gan_last_actions(ndp_gan* g, float* a_hat, int F, void* stream) {
+  NDP_CHECK_ARG(g && a_hat && F > 0 && F <= g->d.max_F, "ndp_gan_last_actions: bad argument");
+  NDP_CUDA(cudaMemcpyAsync(a_hat, g->g_act[4], (size_t)F * g->d.S * g->d.A * 4, cudaMemcpyDeviceToDevice,
+                           (cudaStream_t)stream));
+  return NDP_OK;
+}
+
+}  // extern "C"

@@ -12,6 +12,9 @@ the modules stay usable in the reference's own scripts.
   ``ForwardAutoencoder.forward`` (reference models/forward_encoder.py:105-114):
   ``cat([code, actions], 1)`` (state first), eval mode returns ``state + residual``.
   The reference has no latent dynamics module; body per SURVEY.md §8a-F.
+* ``ActionDiscriminator`` has the layout of ``models.gan.Discriminator`` (reference
+  models/gan.py:89-110): fc1..fc4, (256+4)->64->128->256->1, leaky ReLU, input
+  ``cat([action, state_code], 1)``.  Weight container for ``GanTrainer``.
 """
 import torch
 from torch import nn
@@ -45,3 +48,18 @@ class LatentForward(nn.Module):
         x = torch.cat([state_cur.flatten(1), actions], dim=1)
         r = self.fc2(F.relu(self.fc1(x))).view_as(state_cur)
         return r if self.training else state_cur + r
+
+
+class ActionDiscriminator(nn.Module):
+    def __init__(self, cond_dim: int = 256, A: int = 4):
+        super().__init__()
+        self.fc1 = nn.Linear(cond_dim + A, 64)
+        self.fc2 = nn.Linear(64, 128)
+        self.fc3 = nn.Linear(128, 256)
+        self.fc4 = nn.Linear(256, 1)
+
+    def forward(self, action, state_code):
+        h = F.leaky_relu(self.fc1(torch.cat([action, state_code], dim=1)))
+        h = F.leaky_relu(self.fc2(h))
+        h = F.leaky_relu(self.fc3(h))
+        return self.fc4(h)

@@ -10,6 +10,9 @@ What is pinned:
                N=56,k=6,Dx=4,Dz=2 (train_gan.py:193-196), duplicates, k=2/k=3 cases.
   gen_*.npz    models.gan.Decoder forward on seeded inputs + proof that the product's
                GeneratorMLP gets bit-identical default-init weights under the same seed.
+  gan.npz      train_gan.py:126-203 loop body run with the reference's own models.gan.Decoder / Discriminator,
+               diversity.compute_pairwise_divergence and torch.optim.Adam (:98-104): per-step losses, first-step
+               action_hat and generator gradient, parameters after the last step; fp32 and fp64.
   mpc_*.npz    mpc_eval.fetch_push_control_evaluation (unmodified, embedding mode:
                nn.Identity encoder) return tuple for a fake in-memory dataset, plus
                per-plan costs/argmin from the reference's modules via the restated loop.
@@ -147,6 +150,65 @@ def golden_mpc(mpc_eval, RefDecoder):
     print("mpc.npz", len(out), "arrays")
 
 
+GAN_STRIDE64 = 4
+
+
+def flat_params(m):
+    return torch.cat([p.detach().reshape(-1) for p in m.parameters()])
+
+
+def flat_grads(m):
+    return torch.cat([p.grad.detach().reshape(-1) for p in m.parameters()])
+
+
+def golden_gan(div, RefDecoder, RefDiscriminator):
+    """train_gan.py:126-203 with the reference's OWN Decoder / Discriminator / diversity modules and
+    torch.optim.Adam as constructed at :98-104; the restated step (oracle.gan_train_step) is the loop body."""
+    out = {}
+    cases = {"ref_shape": (56, 6, 2, 1, 3, 31),      # batch 8 x (seq 8 - 1), num_sample 6 (config/default.yaml)
+             "s16": (40, 16, 2, 2, 2, 32),            # two discriminator steps per generator step
+             "nd4": (9, 5, 4, 1, 2, 33)}              # ragged sizes, wider noise
+    for name, (Fb, S, nd, dsteps, nsteps, seed) in cases.items():
+        gen_p, dis_p = synthetic.make_gan_models(nd, seed=0)
+        results = {}
+        for dt in (torch.float32, torch.float64):
+            torch.manual_seed(0)
+            gen, dis = RefDecoder(noise_dim=nd), RefDiscriminator()
+            gen.weight_init(mean=0.0, std=0.02); dis.weight_init(mean=0.0, std=0.02)   # train_gan.py:91-92 (no-ops)
+            for (n1, p1), (n2, p2) in zip(gen.state_dict().items(), gen_p.state_dict().items()):
+                assert n1 == n2 and torch.equal(p1, p2)
+            for (n1, p1), (n2, p2) in zip(dis.state_dict().items(), dis_p.state_dict().items()):
+                assert n1 == n2 and torch.equal(p1, p2)
+            gen, dis = gen.to(dt).train(), dis.to(dt).train()
+            G_opt, D_opt = O.gan_optimizers(gen, dis, lr=2e-4)
+            losses = []
+            for it in range(nsteps):
+                codes, actions, noise = synthetic.make_gan_batch(Fb, S, nd, seed=seed + 100 * it)
+                dl, gl, pl, a_hat = O.gan_train_step(gen, dis, G_opt, D_opt, codes.to(dt), actions.to(dt), noise.to(dt),
+                                                     div_factor=0.1, discrim_steps_per_gen=dsteps,
+                                                     divergence=div.compute_pairwise_divergence)
+                losses.append([float(dl), float(gl), float(pl)])
+                if it == 0:
+                    results[dt, "a_hat0"] = a_hat.numpy()
+                    results[dt, "ggrad0"] = flat_grads(gen).numpy()
+            results[dt, "losses"] = np.array(losses, dtype=np.float64)
+            results[dt, "gparams"] = flat_params(gen).numpy()
+            results[dt, "dparams"] = flat_params(dis).numpy()
+        # keep the fixture small: fp64 parameters every 4th element (GAN_STRIDE64), first-step gradient only for
+        # the reference shape
+        for (dt, key), v in results.items():
+            is64 = dt == torch.float64
+            if key == "ggrad0" and name != "ref_shape":
+                continue
+            if is64 and key in ("gparams", "dparams"):
+                v = v[::GAN_STRIDE64]
+            out[f"{name}_{key}{'64' if is64 else ''}"] = v
+        out[f"{name}_cfg"] = np.array([Fb, S, nd, dsteps, nsteps, seed], dtype=np.int64)
+        print(f"gan {name}: losses {results[torch.float32, 'losses'][-1]}")
+    np.savez_compressed(os.path.join(OUT, "gan.npz"), **out)
+    print("gan.npz", len(out), "arrays")
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
@@ -154,3 +216,5 @@ if __name__ == "__main__":
     golden_ndiv(div)
     golden_gen(RefDecoder)
     golden_mpc(mpc_eval, RefDecoder)
+    from models.gan import Discriminator as RefDiscriminator  # type: ignore  # noqa: E402
+    golden_gan(div, RefDecoder, RefDiscriminator)

@@ -19,7 +19,8 @@ __all__ = [
     "compute_pairwise", "compute_pair_distance", "compute_pairwise_divergence",
     "ndiv_grad_analytic", "GeneratorMLP", "LatentForward", "draw_noise",
     "diverse_sampling", "mpc_rollout", "select_first_min", "select_topk",
-    "mpc_plan", "pack_key", "closed_loop_eval", "ndiv_fwd_bwd",
+    "mpc_plan", "pack_key", "closed_loop_eval", "ndiv_fwd_bwd", "ActionDiscriminator", "gan_optimizers",
+    "gan_train_step",
 ]
 
 MARGIN = 0.8          # diversity.py:40
@@ -261,3 +262,61 @@ def closed_loop_eval(gen, fwd, images: torch.Tensor, actions: torch.Tensor, K: i
         best_all.append(best_row)
     denom = (seq - 1) * n_traj
     return float(action_error_sum / denom), float(image_error_sum / denom), best_all
+
+
+# ----------------------------------------------------------------------------
+# GAN training step around the ndiv loss — train_gan.py:126-203
+# ----------------------------------------------------------------------------
+class ActionDiscriminator(nn.Module):
+    """models/gan.py:89-110 (Discriminator), same parameter names."""
+
+    def __init__(self, cond_dim: int = 256, A: int = 4):
+        super().__init__()
+        self.fc1 = nn.Linear(cond_dim + A, 64)
+        self.fc2 = nn.Linear(64, 128)
+        self.fc3 = nn.Linear(128, 256)
+        self.fc4 = nn.Linear(256, 1)
+
+    def forward(self, action, state_code):
+        state_action = torch.cat([action, state_code], dim=1)          # gan.py:102
+        h = F.leaky_relu(self.fc1(state_action))
+        h = F.leaky_relu(self.fc2(h))
+        h = F.leaky_relu(self.fc3(h))
+        return self.fc4(h)
+
+
+def gan_optimizers(decoder, discriminator, lr: float = 2e-4):
+    """train_gan.py:98-104 (the encoder group of G_optimizer never gets a gradient: :152-153 detach)."""
+    G_opt = torch.optim.Adam([{"params": decoder.parameters()}], lr=lr, betas=(0.5, 0.999))
+    D_opt = torch.optim.Adam(discriminator.parameters(), lr=lr, betas=(0.5, 0.999))
+    return G_opt, D_opt
+
+
+def gan_train_step(decoder, discriminator, G_opt, D_opt, codes, actions, noise, div_factor: float = 0.1,
+                   discrim_steps_per_gen: int = 1, divergence=compute_pairwise_divergence):
+    """One iteration of train_gan.py:126-203 on encoded inputs.  codes [F,256] = cat([encoder(state_cur),
+    encoder(state_target)], 1) (:152-155); actions [F,4] (:137); noise [F,S,nd] = the uniform draw of
+    diverse_sampling (:43-47).  Returns (D_loss, G_loss, pair_div_loss, action_hat) as detached tensors."""
+    Fb, S, nd = noise.shape
+    bce = nn.BCEWithLogitsLoss()
+    action_unsqueeze = torch.repeat_interleave(actions, repeats=S, dim=0)         # :140-142
+    codes_unsqueeze = torch.repeat_interleave(codes, repeats=S, dim=0)            # :156
+    code = codes[:, None, :].expand(-1, S, -1)                                    # :45
+    diverse_codes = torch.cat([code, noise], dim=2)                               # :46
+    action_hat = decoder(diverse_codes.reshape(-1, diverse_codes.size(2)))        # :165
+    DIV = Fb * S
+    ones, zeros = torch.ones(DIV, dtype=codes.dtype), torch.zeros(DIV, dtype=codes.dtype)
+    D_loss = torch.zeros(())
+    for _ in range(discrim_steps_per_gen):                                        # :172-184
+        D_loss = bce(torch.squeeze(discriminator(action_unsqueeze, codes_unsqueeze)), ones) + \
+            bce(torch.squeeze(discriminator(action_hat, codes_unsqueeze)), zeros)
+        D_opt.zero_grad()
+        D_loss.backward(retain_graph=True)
+        D_opt.step()
+    G_loss = bce(torch.squeeze(discriminator(action_hat, codes_unsqueeze)), ones)  # :187-190
+    pair_div_loss = divergence(action_hat.view(Fb, S, -1), noise)                 # :193-196
+    total_loss = G_loss + div_factor * pair_div_loss                              # :198-200
+    G_opt.zero_grad()
+    total_loss.backward()
+    G_opt.step()                                                                  # :201-203
+    return D_loss.detach(), G_loss.detach(), pair_div_loss.detach(), action_hat.detach()

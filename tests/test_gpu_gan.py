@@ -1,0 +1,124 @@
+"""GPU parity of the device-resident GAN training step (csrc/k4_gan_train.cu through
+ndp_gan_train_step) against tests/golden/gan.npz — train_gan.py:126-203 run with the reference's own
+Decoder / Discriminator / diversity modules and torch.optim.Adam — and against the oracle restatement.
+
+Adam's first updates are sign-like (m/sqrt(v) = +-1), and the ndiv hinge is discontinuous, so two fp32
+implementations legitimately differ by isolated 2*lr jumps (the reference's own fp32 and fp64 runs do: max
+parameter difference 4e-4, golden).  The protocol therefore arbitrates against the fp64 run: the kernels' error
+must stay within a small multiple of the reference-fp32 error in max, rms and outlier count."""
+import numpy as np
+import pytest
+import torch
+
+from ndivplanning_b200 import GanTrainer, synthetic
+from ndivplanning_b200.gan_train import D_LAYERS, G_LAYERS
+from oracle import ndiv_oracle as O
+
+pytestmark = pytest.mark.gpu
+S64 = 4     # stride of the fp64 parameter samples in the fixture (oracle/make_golden.py GAN_STRIDE64)
+
+
+def _flat_sd(sd, layers):
+    return torch.cat([sd[f"{n}.{k}"].reshape(-1) for n in layers for k in ("weight", "bias")]).cpu().numpy()
+
+
+def _arbiter(mine, ref32, ref64, what, floor=1e-7):
+    e_m, e_r = np.abs(mine.astype(np.float64) - ref64), np.abs(ref32.astype(np.float64) - ref64)
+    assert e_m.max() <= max(4 * e_r.max(), 50 * floor), (what, "max", e_m.max(), e_r.max())
+    rms_m, rms_r = np.sqrt((e_m ** 2).mean()), np.sqrt((e_r ** 2).mean())
+    assert rms_m <= 4 * rms_r + floor, (what, "rms", rms_m, rms_r)
+    thr = 100 * floor
+    assert (e_m > thr).mean() <= 4 * (e_r > thr).mean() + 1e-3, (what, "outliers", (e_m > thr).mean(), (e_r > thr).mean())
+    assert np.median(e_m) <= 4 * np.median(e_r) + floor, (what, "median", np.median(e_m), np.median(e_r))
+
+
+def _run(cuda, name, golden, graph=False):
+    g = golden["gan"]
+    Fb, S, nd, dsteps, nsteps, seed = [int(v) for v in g[f"{name}_cfg"]]
+    gen, dis = synthetic.make_gan_models(nd, seed=0)
+    tr = GanTrainer(gen, dis, num_sample=S, noise_dim=nd, max_codes=Fb, learning_rate=2e-4, betas=(0.5, 0.999),
+                    pairwise_div_factor=0.1, discrim_steps_per_gen=dsteps, device=cuda)
+    losses, extra = [], {}
+    static = [t.to(cuda) for t in synthetic.make_gan_batch(Fb, S, nd, seed=seed)]
+    cg = tr.capture(*static) if graph else None
+    if graph:           # capture does not execute; reset nothing, the first replay is step 1
+        pass
+    for it in range(nsteps):
+        batch = [t.to(cuda) for t in synthetic.make_gan_batch(Fb, S, nd, seed=seed + 100 * it)]
+        if graph:
+            for dst, src in zip(static, batch):
+                dst.copy_(src)
+            cg.replay()
+            l = tr.losses
+        else:
+            l = tr.step(*batch)
+        losses.append(l.cpu().numpy().astype(np.float64))
+        if it == 0:
+            extra["a_hat0"] = tr.last_actions(Fb).cpu().numpy()
+            extra["ggrad0"] = tr.grads()[0].cpu().numpy()
+    gsd, dsd = tr.state_dicts()
+    return np.array(losses), _flat_sd(gsd, G_LAYERS), _flat_sd(dsd, D_LAYERS), extra
+
+
+@pytest.mark.parametrize("name", ["ref_shape", "s16", "nd4"])
+def test_gan_step_matches_reference_run(cuda, golden, name):
+    g = golden["gan"]
+    losses, gp, dp, extra = _run(cuda, name, golden)
+    # before any parameter moved: generator forward and the first discriminator loss are plain fp32 arithmetic
+    np.testing.assert_allclose(extra["a_hat0"], g[f"{name}_a_hat0"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(losses[0, 0], g[f"{name}_losses"][0, 0], rtol=1e-5)
+    np.testing.assert_allclose(losses[0, 1], g[f"{name}_losses"][0, 1], rtol=2e-5)
+    np.testing.assert_allclose(losses[0, 2], g[f"{name}_losses"][0, 2], rtol=1e-4)
+    l32, l64 = g[f"{name}_losses"], g[f"{name}_losses64"]
+    assert np.all(np.abs(losses - l64) <= 4 * np.abs(l32 - l64) + 1e-4 * np.abs(l64)), (losses, l32, l64)
+    if name == "ref_shape":
+        gg32, gg64 = g[f"{name}_ggrad0"], g[f"{name}_ggrad064"]
+        scale = np.abs(gg64).max()
+        _arbiter(extra["ggrad0"] / scale, gg32 / scale, gg64 / scale, "generator gradient", floor=1e-7)
+    _arbiter(gp[::S64], g[f"{name}_gparams"][::S64], g[f"{name}_gparams64"], "generator parameters")
+    _arbiter(dp[::S64], g[f"{name}_dparams"][::S64], g[f"{name}_dparams64"], "discriminator parameters")
+
+
+def test_gan_step_graph_replay_is_bit_identical(cuda, golden):
+    """the step is deterministic (no atomics) and stream-ordered: CUDA-graph replays == eager steps, bit for bit"""
+    a = _run(cuda, "ref_shape", golden, graph=False)
+    b = _run(cuda, "ref_shape", golden, graph=True)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+
+
+def test_gan_step_large_batch_vs_oracle(cuda):
+    """F=2048 codes x S=16 samples (32,768 generator rows): one step against the oracle restatement on the CPU"""
+    Fb, S, nd = 2048, 16, 2
+    gen, dis = synthetic.make_gan_models(nd, seed=1)
+    codes, actions, noise = synthetic.make_gan_batch(Fb, S, nd, seed=9)
+    tr = GanTrainer(gen, dis, num_sample=S, noise_dim=nd, max_codes=Fb, device=cuda)
+    l = tr.step(codes.to(cuda), actions.to(cuda), noise.to(cuda)).cpu().numpy()
+    gg, dg = [t.cpu().numpy() for t in tr.grads()]
+    res = {}
+    for dt in (torch.float32, torch.float64):
+        og, od = O.GeneratorMLP(nd).to(dt), O.ActionDiscriminator().to(dt)
+        og.load_state_dict({k: v.to(dt) for k, v in gen.state_dict().items()})
+        od.load_state_dict({k: v.to(dt) for k, v in dis.state_dict().items()})
+        G_opt, D_opt = O.gan_optimizers(og, od)
+        # discriminator gradient of the D step: read it before the generator backward overwrites .grad
+        dl, gl, pl, _ = O.gan_train_step(og, od, G_opt, D_opt, codes.to(dt), actions.to(dt), noise.to(dt))
+        res[dt] = (np.array([float(dl), float(gl), float(pl)]),
+                   torch.cat([p.grad.reshape(-1) for p in og.parameters()]).numpy())
+    l32, l64 = res[torch.float32][0], res[torch.float64][0]
+    assert np.all(np.abs(l - l64) <= 4 * np.abs(l32 - l64) + 1e-4 * np.abs(l64)), (l, l32, l64)
+    g32, g64 = res[torch.float32][1], res[torch.float64][1]
+    scale = np.abs(g64).max()
+    _arbiter(gg / scale, g32 / scale, g64 / scale, "generator gradient (large)", floor=1e-7)
+
+
+def test_gan_trainer_refuses_cpu_and_bad_shapes(cuda):
+    gen, dis = synthetic.make_gan_models(2, seed=0)
+    tr = GanTrainer(gen, dis, num_sample=4, noise_dim=2, max_codes=8, device=cuda)
+    c, a, n = synthetic.make_gan_batch(8, 4, 2)
+    with pytest.raises(Exception):
+        tr.step(c, a, n)                                   # CPU tensors: no fallback
+    with pytest.raises(Exception):
+        tr.step(c.to(cuda)[:, :100], a.to(cuda), n.to(cuda))
+    c16, a16, n16 = [t.to(cuda) for t in synthetic.make_gan_batch(16, 4, 2)]
+    with pytest.raises(Exception):
+        tr.step(c16, a16, n16)                             # F > max_codes

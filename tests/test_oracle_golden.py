@@ -67,3 +67,32 @@ def test_select_first_min_rules():
     assert O.select_topk(torch.tensor([2.0, 1.0, nan, 1.0, 0.5]), 3).tolist() == [4, 1, 3]
     assert O.pack_key(0.5, 7) < O.pack_key(0.75, 3) < O.pack_key(float("nan"), 0)
     assert O.pack_key(-1.0, 9) < O.pack_key(0.0, 0)
+
+
+GAN_CASES = ["ref_shape", "s16", "nd4"]
+
+
+def _flat(m, grad=False):
+    return torch.cat([(p.grad if grad else p.detach()).reshape(-1) for p in m.parameters()])
+
+
+@pytest.mark.parametrize("name", GAN_CASES)
+def test_gan_step_oracle_matches_reference(golden, name):
+    """restated train_gan.py:126-203 loop body (oracle containers) vs the run with the reference's own modules"""
+    g = golden["gan"]
+    Fb, S, nd, dsteps, nsteps, seed = [int(v) for v in g[f"{name}_cfg"]]
+    torch.manual_seed(0)
+    gen, dis = O.GeneratorMLP(nd).train(), O.ActionDiscriminator().train()
+    G_opt, D_opt = O.gan_optimizers(gen, dis, lr=2e-4)
+    losses = []
+    for it in range(nsteps):
+        codes, actions, noise = synthetic.make_gan_batch(Fb, S, nd, seed=seed + 100 * it)
+        dl, gl, pl, a_hat = O.gan_train_step(gen, dis, G_opt, D_opt, codes, actions, noise, 0.1, dsteps)
+        losses.append([float(dl), float(gl), float(pl)])
+        if it == 0:
+            np.testing.assert_allclose(a_hat.numpy(), g[f"{name}_a_hat0"], rtol=1e-5, atol=1e-7)
+            if name == "ref_shape":
+                np.testing.assert_allclose(_flat(gen, True).numpy(), g[f"{name}_ggrad0"], rtol=1e-4, atol=1e-8)
+    np.testing.assert_allclose(np.array(losses), g[f"{name}_losses"], rtol=1e-5)
+    np.testing.assert_allclose(_flat(gen).numpy(), g[f"{name}_gparams"], rtol=1e-4, atol=2e-6)
+    np.testing.assert_allclose(_flat(dis).numpy(), g[f"{name}_dparams"], rtol=1e-4, atol=2e-6)
