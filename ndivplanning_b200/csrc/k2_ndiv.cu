@@ -265,6 +265,18 @@ __device__ __forceinline__ void ndiv_epilogue(const float (&ax)[4][4], const flo
   }
 }
 
+// The gradient product x_i * sum_j What_ij - sum_j What_ij x_j is evaluated on rows centred on the group's first row
+// (x - x_0): the two terms cancel to O(|x_i - x_j|), so without centring a tight cluster far from the origin (the S
+// samples of one code during GAN training) would lose |x| / |x_i - x_j| in relative accuracy.
+__device__ __forceinline__ float4 centre4(const float* __restrict__ xg, int d, int Dx) {
+  float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (d < Dx) c.x = __ldg(xg + d);
+  if (d + 1 < Dx) c.y = __ldg(xg + d + 1);
+  if (d + 2 < Dx) c.z = __ldg(xg + d + 2);
+  if (d + 3 < Dx) c.w = __ldg(xg + d + 3);
+  return c;
+}
+
 // grid (row blocks, JS, N).  gpart [JS][N][k][Dx] (JS == 1: grad_x itself), loss_part [gridDim.x*JS*N].
 // NDP = number of 32-dim gradient passes held in registers; dims [dpass0, dpass0 + 32*NDP) are produced.
 template <int NDP, bool WITH_GRAD>
@@ -341,6 +353,8 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
                     if (d + 2 < Dx) v.z = __ldg(src + 2);
                     if (d + 3 < Dx) v.w = __ldg(src + 3);
                   }
+                  const float4 c = centre4(xg, d, Dx);
+                  v.x -= c.x; v.y -= c.y; v.z -= c.z; v.w -= c.w;
                 }
                 *reinterpret_cast<float4*>(sm.sxj + j * kXJ + q * 4) = v;
               }
@@ -374,6 +388,8 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
                 if (d + 2 < Dx) v.z = __ldg(src + 2);
                 if (d + 3 < Dx) v.w = __ldg(src + 3);
               }
+              const float4 c = centre4(xg, d, Dx);
+              v.x -= c.x; v.y -= c.y; v.z -= c.z; v.w -= c.w;
             }
             *reinterpret_cast<float4*>(sm.sxj + j * kXJ + q * 4) = v;
           }
@@ -429,7 +445,7 @@ ndiv_loss_grad_kernel(const float* __restrict__ x, const float* __restrict__ z, 
             const float g = (red[r * kGD + d8 + d] + red[(kTI + r) * kGD + d8 + d]) +
                             (red[(2 * kTI + r) * kGD + d8 + d] + red[(3 * kTI + r) * kGD + d8 + d]);
             const size_t off = ((size_t)n * k + i) * Dx + dim;
-            gpart[((size_t)js * N_) * k * Dx + off] = fmaf(__ldg(x + off), sumW, -g);
+            gpart[((size_t)js * N_) * k * Dx + off] = fmaf(__ldg(x + off) - __ldg(xg + dim), sumW, -g);
           }
         }
       }

@@ -33,14 +33,19 @@ constexpr int kTI = 64, kTC = 16, kThreads = 256;
 constexpr float kLeaky = 0.01f;   // F.leaky_relu default negative_slope (gan.py:103-105)
 
 struct RowSrc {   // logical [M x (k0+k1)] matrix assembled from two row-indexed sources
-  const float* p0; int k0, ld0, div0;
-  const float* p1; int k1, ld1, div1;
-  __device__ __forceinline__ float at(int r, int k) const {
-    return k < k0 ? __ldg(p0 + (size_t)(r / div0) * ld0 + k) : __ldg(p1 + (size_t)(r / div1) * ld1 + (k - k0));
+  const float* p0; int k0, ld0, div0; unsigned mul0;
+  const float* p1; int k1, ld1, div1; unsigned mul1;
+  // r / div for r < 2^24, div < 2^8 via one multiply-high (mul = floor(2^32/div) + 1); div == 1 passes through
+  static __device__ __forceinline__ int fdiv(int r, int div, unsigned mul) {
+    return div == 1 ? r : (int)__umulhi((unsigned)r, mul);
+  }
+  __device__ __forceinline__ const float* ptr(int r, int k) const {
+    return k < k0 ? p0 + (size_t)fdiv(r, div0, mul0) * ld0 + k : p1 + (size_t)fdiv(r, div1, mul1) * ld1 + (k - k0);
   }
 };
 static RowSrc row_src(const float* p0, int k0, int div0, const float* p1 = nullptr, int k1 = 0, int div1 = 1) {
   RowSrc r; r.p0 = p0; r.k0 = k0; r.ld0 = k0; r.div0 = div0; r.p1 = p1; r.k1 = k1; r.ld1 = k1; r.div1 = div1;
+  r.mul0 = (unsigned)((1ull << 32) / (unsigned)div0 + 1); r.mul1 = (unsigned)((1ull << 32) / (unsigned)div1 + 1);
   return r;
 }
 
@@ -68,11 +73,23 @@ __device__ __forceinline__ float act_bwd(float h, int act) {
   return 1.f;
 }
 
+// 4-byte async copy global -> shared; src_bytes == 0 zero-fills (out-of-range elements)
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* src, bool valid) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int n = valid ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+constexpr int kStages = 4;
+
 template <int MODE, int TJ>
 __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
   constexpr int RJ = TJ / 16;
-  __shared__ __align__(16) float As[kTC][kTI + 4];
-  __shared__ __align__(16) float Bs[kTC][TJ + 4];
+  __shared__ __align__(16) float As[kStages][kTC][kTI + 4];
+  __shared__ __align__(16) float Bs[kStages][kTC][TJ + 4];
   const int t = threadIdx.x;
   const int i0 = blockIdx.x * kTI, j0 = blockIdx.y * TJ;
   int c_begin = 0, c_end = p.Cn;
@@ -88,55 +105,71 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
     for (int b = 0; b < RJ; b++) acc[a][b] = 0.f;
   float bsum = 0.f;
 
-  for (int c0 = c_begin; c0 < c_end; c0 += kTC) {
+  // the chunk [c0, c0+kTC) of both operands goes global -> shared as element-wise async copies (the layouts are
+  // transposed / gathered on the way), kStages-1 chunks in flight
+  auto issue = [&](int stage, int c0) {
 #pragma unroll
     for (int q = 0; q < 4; q++) {
       const int e = t + q * kThreads;
       int i, c;
       if (MODE == DW) { i = e & (kTI - 1); c = e >> 6; } else { c = e & (kTC - 1); i = e >> 4; }
       const int gi = i0 + i, gc = c0 + c;
-      float v = 0.f;
-      if (gi < p.I && gc < c_end) {
-        if (MODE == FWD) v = p.x.at(gi, gc);
-        else if (MODE == DX) v = __ldg(p.dP + (size_t)gi * p.ldp + gc);
-        else v = __ldg(p.dP + (size_t)gc * p.ldp + gi);
+      const bool ok = gi < p.I && gc < c_end;
+      const float* src = MODE == FWD ? p.x.p0 : p.dP;
+      if (ok) {
+        if (MODE == FWD) src = p.x.ptr(gi, gc);
+        else if (MODE == DX) src = p.dP + (size_t)gi * p.ldp + gc;
+        else src = p.dP + (size_t)gc * p.ldp + gi;
       }
-      As[c][i] = v;
+      cp_async4(&As[stage][c][i], src, ok);
     }
     for (int e = t; e < TJ * kTC; e += kThreads) {
       int j, c;
       if (MODE == FWD) { c = e & (kTC - 1); j = e >> 4; } else { j = e % TJ; c = e / TJ; }
       const int gj = j0 + j, gc = c0 + c;
-      float v = 0.f;
-      if (gj < p.J && gc < c_end) {
-        if (MODE == FWD) v = __ldg(p.W + (size_t)gj * p.ldw + gc);
-        else if (MODE == DX) v = __ldg(p.W + (size_t)gc * p.ldw + p.wk0 + gj);
-        else v = p.x.at(gc, gj);
+      const bool ok = gj < p.J && gc < c_end;
+      const float* src = MODE == DW ? p.x.p0 : p.W;
+      if (ok) {
+        if (MODE == FWD) src = p.W + (size_t)gj * p.ldw + gc;
+        else if (MODE == DX) src = p.W + (size_t)gc * p.ldw + p.wk0 + gj;
+        else src = p.x.ptr(gc, gj);
       }
-      Bs[c][j] = v;
+      cp_async4(&Bs[stage][c][j], src, ok);
     }
-    __syncthreads();
+  };
+
+  const int nchunks = (c_end - c_begin + kTC - 1) / kTC;
+#pragma unroll
+  for (int st = 0; st < kStages - 1; st++) {
+    if (st < nchunks) issue(st, c_begin + st * kTC);
+    cp_async_commit();
+  }
+  for (int n = 0; n < nchunks; n++) {
+    const int st = n % kStages;
+    cp_async_wait<kStages - 2>();
+    __syncthreads();          // chunk n landed for every thread; everyone is done reading stage (n-1) % kStages
+    if (n + kStages - 1 < nchunks) issue((n + kStages - 1) % kStages, c_begin + (n + kStages - 1) * kTC);
+    cp_async_commit();
     if (MODE == DW && blockIdx.y == 0 && t < kTI) {
 #pragma unroll
-      for (int c = 0; c < kTC; c++) bsum += As[c][t];
+      for (int c = 0; c < kTC; c++) bsum += As[st][c][t];
     }
 #pragma unroll
     for (int c = 0; c < kTC; c++) {
-      const float4 av = *reinterpret_cast<const float4*>(&As[c][ti * 4]);
+      const float4 av = *reinterpret_cast<const float4*>(&As[st][c][ti * 4]);
       const float a[4] = {av.x, av.y, av.z, av.w};
       float b[RJ];
       if (RJ == 4) {
-        const float4 bv = *reinterpret_cast<const float4*>(&Bs[c][tj * 4]);
+        const float4 bv = *reinterpret_cast<const float4*>(&Bs[st][c][tj * 4]);
         b[0] = bv.x; b[1 % RJ] = bv.y; b[2 % RJ] = bv.z; b[3 % RJ] = bv.w;
       } else {
-        b[0] = Bs[c][tj];
+        b[0] = Bs[st][c][tj];
       }
 #pragma unroll
       for (int x = 0; x < 4; x++)
 #pragma unroll
         for (int y = 0; y < RJ; y++) acc[x][y] = fmaf(a[x], b[y], acc[x][y]);
     }
-    __syncthreads();
   }
 
   float* out = p.out;

@@ -55,7 +55,10 @@ class GanTrainer:
     def __del__(self):
         h = getattr(self, "_h", None)
         if h is not None and h.value:
-            _lib.lib().ndp_gan_destroy(h)
+            try:
+                _lib.lib().ndp_gan_destroy(h)
+            except Exception:       # interpreter shutdown
+                pass
             self._h = None
 
     # ---- parameters ----------------------------------------------------------------------------------------

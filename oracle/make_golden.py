@@ -165,10 +165,11 @@ def golden_gan(div, RefDecoder, RefDiscriminator):
     """train_gan.py:126-203 with the reference's OWN Decoder / Discriminator / diversity modules and
     torch.optim.Adam as constructed at :98-104; the restated step (oracle.gan_train_step) is the loop body."""
     out = {}
-    cases = {"ref_shape": (56, 6, 2, 1, 3, 31),      # batch 8 x (seq 8 - 1), num_sample 6 (config/default.yaml)
-             "s16": (40, 16, 2, 2, 2, 32),            # two discriminator steps per generator step
-             "nd4": (9, 5, 4, 1, 2, 33)}              # ragged sizes, wider noise
-    for name, (Fb, S, nd, dsteps, nsteps, seed) in cases.items():
+    cases = {"ref_shape": (56, 6, 2, 1, 3, 31, 0.1),      # batch 8 x (seq 8 - 1), num_sample 6 (config/default.yaml)
+             "s16": (40, 16, 2, 2, 2, 32, 0.1),            # two discriminator steps per generator step
+             "nd4": (9, 5, 4, 1, 2, 33, 0.1),              # ragged sizes, wider noise
+             "nodiv": (56, 6, 2, 1, 5, 34, 0.0)}           # pairwise_div_factor 0: the smooth part of the recurrence
+    for name, (Fb, S, nd, dsteps, nsteps, seed, divf) in cases.items():
         gen_p, dis_p = synthetic.make_gan_models(nd, seed=0)
         results = {}
         for dt in (torch.float32, torch.float64):
@@ -184,26 +185,29 @@ def golden_gan(div, RefDecoder, RefDiscriminator):
             losses = []
             for it in range(nsteps):
                 codes, actions, noise = synthetic.make_gan_batch(Fb, S, nd, seed=seed + 100 * it)
+                probe = {}
                 dl, gl, pl, a_hat = O.gan_train_step(gen, dis, G_opt, D_opt, codes.to(dt), actions.to(dt), noise.to(dt),
-                                                     div_factor=0.1, discrim_steps_per_gen=dsteps,
-                                                     divergence=div.compute_pairwise_divergence)
+                                                     div_factor=divf, discrim_steps_per_gen=dsteps,
+                                                     divergence=div.compute_pairwise_divergence, probe=probe)
                 losses.append([float(dl), float(gl), float(pl)])
                 if it == 0:
                     results[dt, "a_hat0"] = a_hat.numpy()
                     results[dt, "ggrad0"] = flat_grads(gen).numpy()
+                    results[dt, "dgrad0"] = probe["d_grad"].numpy()
             results[dt, "losses"] = np.array(losses, dtype=np.float64)
             results[dt, "gparams"] = flat_params(gen).numpy()
             results[dt, "dparams"] = flat_params(dis).numpy()
-        # keep the fixture small: fp64 parameters every 4th element (GAN_STRIDE64), first-step gradient only for
-        # the reference shape
+        # keep the fixture small: parameters every 4th element (GAN_STRIDE64) except the fp32 ones of the reference
+        # shape, first-step gradients only for the reference shape
         for (dt, key), v in results.items():
             is64 = dt == torch.float64
-            if key == "ggrad0" and name != "ref_shape":
+            if key in ("ggrad0", "dgrad0") and name != "ref_shape":
                 continue
-            if is64 and key in ("gparams", "dparams"):
+            if key in ("gparams", "dparams") and (is64 or name != "ref_shape"):
                 v = v[::GAN_STRIDE64]
             out[f"{name}_{key}{'64' if is64 else ''}"] = v
         out[f"{name}_cfg"] = np.array([Fb, S, nd, dsteps, nsteps, seed], dtype=np.int64)
+        out[f"{name}_divf"] = np.array(divf, dtype=np.float64)
         print(f"gan {name}: losses {results[torch.float32, 'losses'][-1]}")
     np.savez_compressed(os.path.join(OUT, "gan.npz"), **out)
     print("gan.npz", len(out), "arrays")

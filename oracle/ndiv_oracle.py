@@ -293,7 +293,7 @@ def gan_optimizers(decoder, discriminator, lr: float = 2e-4):
 
 
 def gan_train_step(decoder, discriminator, G_opt, D_opt, codes, actions, noise, div_factor: float = 0.1,
-                   discrim_steps_per_gen: int = 1, divergence=compute_pairwise_divergence):
+                   discrim_steps_per_gen: int = 1, divergence=compute_pairwise_divergence, probe=None):
     """One iteration of train_gan.py:126-203 on encoded inputs.  codes [F,256] = cat([encoder(state_cur),
     encoder(state_target)], 1) (:152-155); actions [F,4] (:137); noise [F,S,nd] = the uniform draw of
     diverse_sampling (:43-47).  Returns (D_loss, G_loss, pair_div_loss, action_hat) as detached tensors."""
@@ -312,6 +312,8 @@ def gan_train_step(decoder, discriminator, G_opt, D_opt, codes, actions, noise, 
             bce(torch.squeeze(discriminator(action_hat, codes_unsqueeze)), zeros)
         D_opt.zero_grad()
         D_loss.backward(retain_graph=True)
+        if probe is not None:   # discriminator gradient of the D step (the G backward below accumulates onto .grad)
+            probe["d_grad"] = torch.cat([p.grad.detach().reshape(-1).clone() for p in discriminator.parameters()])
         D_opt.step()
     G_loss = bce(torch.squeeze(discriminator(action_hat, codes_unsqueeze)), ones)  # :187-190
     pair_div_loss = divergence(action_hat.view(Fb, S, -1), noise)                 # :193-196

@@ -2,10 +2,15 @@
 ndp_gan_train_step) against tests/golden/gan.npz — train_gan.py:126-203 run with the reference's own
 Decoder / Discriminator / diversity modules and torch.optim.Adam — and against the oracle restatement.
 
-Adam's first updates are sign-like (m/sqrt(v) = +-1), and the ndiv hinge is discontinuous, so two fp32
-implementations legitimately differ by isolated 2*lr jumps (the reference's own fp32 and fp64 runs do: max
-parameter difference 4e-4, golden).  The protocol therefore arbitrates against the fp64 run: the kernels' error
-must stay within a small multiple of the reference-fp32 error in max, rms and outlier count."""
+Protocol.  Adam's first update is sign-like (m/sqrt(v) = +-1): a parameter whose gradient is within round-off of
+zero moves by +-lr depending on the last bit, in ANY fp32 implementation (the reference's own fp32 and fp64 runs
+differ by 4e-4 = 2*lr in a few parameters after one step, golden).  With the ndiv term on, those jumps are then
+amplified chaotically (the S samples of a code sit ~1e-3 apart, the normalised distances and the hinge mask react to
+1e-4 shifts): after two steps the reference's fp32 and fp64 generator gradients differ by 6 % of their scale.  So:
+  * the FIRST step — forward, all three losses, both gradients — is compared tightly (arbitrated by the fp64 run);
+  * the optimiser recurrence over several steps is compared tightly on the 'nodiv' case (pairwise_div_factor = 0),
+    where the reference's fp32 run stays within 5e-7 of its fp64 run;
+  * multi-step runs WITH the ndiv term must stay within a multiple of the reference's own fp32-vs-fp64 drift."""
 import numpy as np
 import pytest
 import torch
@@ -22,14 +27,14 @@ def _flat_sd(sd, layers):
     return torch.cat([sd[f"{n}.{k}"].reshape(-1) for n in layers for k in ("weight", "bias")]).cpu().numpy()
 
 
-def _arbiter(mine, ref32, ref64, what, floor=1e-7):
+def _arbiter(mine, ref32, ref64, what, floor=1e-7, k=4):
     e_m, e_r = np.abs(mine.astype(np.float64) - ref64), np.abs(ref32.astype(np.float64) - ref64)
-    assert e_m.max() <= max(4 * e_r.max(), 50 * floor), (what, "max", e_m.max(), e_r.max())
+    assert e_m.max() <= max(k * e_r.max(), 50 * floor), (what, "max", e_m.max(), e_r.max())
     rms_m, rms_r = np.sqrt((e_m ** 2).mean()), np.sqrt((e_r ** 2).mean())
-    assert rms_m <= 4 * rms_r + floor, (what, "rms", rms_m, rms_r)
+    assert rms_m <= k * rms_r + floor, (what, "rms", rms_m, rms_r)
     thr = 100 * floor
-    assert (e_m > thr).mean() <= 4 * (e_r > thr).mean() + 1e-3, (what, "outliers", (e_m > thr).mean(), (e_r > thr).mean())
-    assert np.median(e_m) <= 4 * np.median(e_r) + floor, (what, "median", np.median(e_m), np.median(e_r))
+    assert (e_m > thr).mean() <= k * (e_r > thr).mean() + 1e-3, (what, "outliers", (e_m > thr).mean(), (e_r > thr).mean())
+    assert np.median(e_m) <= k * np.median(e_r) + floor, (what, "median", np.median(e_m), np.median(e_r))
 
 
 def _run(cuda, name, golden, graph=False):
@@ -37,7 +42,7 @@ def _run(cuda, name, golden, graph=False):
     Fb, S, nd, dsteps, nsteps, seed = [int(v) for v in g[f"{name}_cfg"]]
     gen, dis = synthetic.make_gan_models(nd, seed=0)
     tr = GanTrainer(gen, dis, num_sample=S, noise_dim=nd, max_codes=Fb, learning_rate=2e-4, betas=(0.5, 0.999),
-                    pairwise_div_factor=0.1, discrim_steps_per_gen=dsteps, device=cuda)
+                    pairwise_div_factor=float(g[f"{name}_divf"]), discrim_steps_per_gen=dsteps, device=cuda)
     losses, extra = [], {}
     static = [t.to(cuda) for t in synthetic.make_gan_batch(Fb, S, nd, seed=seed)]
     cg = tr.capture(*static) if graph else None
@@ -55,28 +60,34 @@ def _run(cuda, name, golden, graph=False):
         losses.append(l.cpu().numpy().astype(np.float64))
         if it == 0:
             extra["a_hat0"] = tr.last_actions(Fb).cpu().numpy()
-            extra["ggrad0"] = tr.grads()[0].cpu().numpy()
+            extra["ggrad0"], extra["dgrad0"] = [t.cpu().numpy() for t in tr.grads()]
     gsd, dsd = tr.state_dicts()
     return np.array(losses), _flat_sd(gsd, G_LAYERS), _flat_sd(dsd, D_LAYERS), extra
 
 
-@pytest.mark.parametrize("name", ["ref_shape", "s16", "nd4"])
+@pytest.mark.parametrize("name", ["ref_shape", "s16", "nd4", "nodiv"])
 def test_gan_step_matches_reference_run(cuda, golden, name):
     g = golden["gan"]
     losses, gp, dp, extra = _run(cuda, name, golden)
-    # before any parameter moved: generator forward and the first discriminator loss are plain fp32 arithmetic
+    st = 1 if name == "ref_shape" else S64
+    # ---- first step: plain fp32 arithmetic on identical parameters
     np.testing.assert_allclose(extra["a_hat0"], g[f"{name}_a_hat0"], rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(losses[0, 0], g[f"{name}_losses"][0, 0], rtol=1e-5)
     np.testing.assert_allclose(losses[0, 1], g[f"{name}_losses"][0, 1], rtol=2e-5)
     np.testing.assert_allclose(losses[0, 2], g[f"{name}_losses"][0, 2], rtol=1e-4)
-    l32, l64 = g[f"{name}_losses"], g[f"{name}_losses64"]
-    assert np.all(np.abs(losses - l64) <= 4 * np.abs(l32 - l64) + 1e-4 * np.abs(l64)), (losses, l32, l64)
     if name == "ref_shape":
-        gg32, gg64 = g[f"{name}_ggrad0"], g[f"{name}_ggrad064"]
-        scale = np.abs(gg64).max()
-        _arbiter(extra["ggrad0"] / scale, gg32 / scale, gg64 / scale, "generator gradient", floor=1e-7)
-    _arbiter(gp[::S64], g[f"{name}_gparams"][::S64], g[f"{name}_gparams64"], "generator parameters")
-    _arbiter(dp[::S64], g[f"{name}_dparams"][::S64], g[f"{name}_dparams64"], "discriminator parameters")
+        for key in ("ggrad0", "dgrad0"):
+            r32, r64 = g[f"{name}_{key}"], g[f"{name}_{key}64"]
+            scale = np.abs(r64).max()
+            _arbiter(extra[key] / scale, r32 / scale, r64 / scale, key, floor=1e-7)
+    # ---- all steps
+    l32, l64 = g[f"{name}_losses"], g[f"{name}_losses64"]
+    smooth = name == "nodiv"
+    k = 4 if smooth else 12
+    ref_err = np.abs(l32 - l64).max(axis=0, keepdims=True)
+    assert np.all(np.abs(losses - l64) <= k * ref_err + (2e-6 if smooth else 1e-4) * np.abs(l64)), (losses, l32, l64)
+    _arbiter(gp[::S64], g[f"{name}_gparams"][::S64 // st], g[f"{name}_gparams64"], "generator parameters", k=k)
+    _arbiter(dp[::S64], g[f"{name}_dparams"][::S64 // st], g[f"{name}_dparams64"], "discriminator parameters", k=k)
 
 
 def test_gan_step_graph_replay_is_bit_identical(cuda, golden):

@@ -188,3 +188,23 @@ def test_ndiv_gram_row_sharded_equals_full(cuda):
     xg = x.detach().requires_grad_(True)
     div.compute_pairwise_divergence(xg, z).backward()
     assert torch.equal(xg.grad, full_grad)
+
+
+@pytest.mark.parametrize("N,k,Dx,Dz", [(56, 6, 4, 2), (3, 300, 32, 16), (1, 1536, 32, 16)])
+def test_ndiv_tight_cluster_far_from_origin(cuda, N, k, Dx, Dz):
+    """the S samples of one code during GAN training: |x_i - x_j| ~ 1e-2 around a mean of size ~3.  The gradient
+    product x_i * sum(What) - What x cancels to O(|x_i - x_j|); both paths centre the rows first, so the error
+    must not scale with the offset (the reference's autograd differentiates the differences directly)."""
+    x, z = synthetic.make_ndiv_inputs(N, k, Dx, Dz, seed=7 + k)
+    torch.manual_seed(k)
+    x = 3.0 * torch.randn(N, 1, Dx) + 1e-2 * x
+    loss, grad = _run(x, z)
+    l64, g64 = O.ndiv_fwd_bwd(x.double(), z.double())
+    l32, g32 = O.ndiv_fwd_bwd(x, z)
+    np.testing.assert_allclose(loss.numpy(), l64.numpy(), rtol=RTOL)
+    _grad_close_arbiter(grad, x, z, g64.numpy(), rtol=RTOL)
+    # and the column sums, which cancel exactly in exact arithmetic (translation invariance), stay as small as
+    # the reference's own
+    cs, cs32 = grad.sum(1).abs().max().item(), g32.sum(1).abs().max().item()
+    scale = g64.abs().max().item()
+    assert cs <= max(8 * cs32, 2e-5 * scale * np.sqrt(k)), (cs, cs32, scale)
