@@ -497,6 +497,79 @@ __global__ void ndiv_finalize_kernel(const float* __restrict__ part, int n, floa
   if (threadIdx.x == 0) loss[0] = s[0];
 }
 
+// ---------------------------------------------------------------- small groups (k <= 32): one warp per group
+// The reference's own call shape (train_gan.py:193-196: N = batch*(seq-1) groups of k = num_sample = 6 samples,
+// Dx = 4, Dz = 2) and every GAN-training shape: a 64x128 pair tile would be >95 % padding.  Lane = row i; the group's
+// rows sit in shared memory (odd row stride); row sums, loss and gradient in ONE launch, same arithmetic as the
+// tiled exact path (direct differences, IEEE sqrt / divide, hinge in the reference's operation order).
+constexpr int kSmallWarps = 4;
+__global__ void __launch_bounds__(kSmallWarps * 32)
+ndiv_small_kernel(const float* __restrict__ x, const float* __restrict__ z, int N, int k, int Dx, int Dz, float margin,
+                  float* __restrict__ sx_out, float* __restrict__ sz_out, float* __restrict__ loss_part,
+                  float* __restrict__ grad_x) {
+  extern __shared__ float sm_small[];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n = blockIdx.x * kSmallWarps + w;
+  if (n >= N) return;                                   // warps are independent: only __syncwarp below
+  const int ldx = Dx | 1, ldz = Dz | 1;
+  float* xs = sm_small + (size_t)w * (32 * (ldx + ldz) + 32 * ldx + 64);
+  float* zs = xs + 32 * ldx;
+  float* gs = zs + 32 * ldz;                            // gradient accumulators, lane-private rows
+  float* rx = gs + 32 * ldx;                            // 1 / sx_j
+  float* rz = rx + 32;                                  // 1 / sz_j
+  const float* xg = x + (size_t)n * k * Dx;
+  const float* zg = z + (size_t)n * k * Dz;
+  for (int e = lane; e < k * Dx; e += 32) xs[(e / Dx) * ldx + e % Dx] = __ldg(xg + e);
+  for (int e = lane; e < k * Dz; e += 32) zs[(e / Dz) * ldz + e % Dz] = __ldg(zg + e);
+  __syncwarp();
+  const bool live = lane < k;
+  const float* xi = xs + lane * ldx;
+  const float* zi = zs + lane * ldz;
+  float sxi = 0.f, szi = 0.f;
+  if (live) {
+    for (int j = 0; j < k; ++j) {
+      float ax = 0.f, az = 0.f;
+      for (int d = 0; d < Dx; ++d) { const float t = xi[d] - xs[j * ldx + d]; ax = fmaf(t, t, ax); }
+      for (int d = 0; d < Dz; ++d) { const float t = zi[d] - zs[j * ldz + d]; az = fmaf(t, t, az); }
+      sxi += sqrtf(ax);
+      szi += sqrtf(az);
+    }
+    sx_out[(size_t)n * k + lane] = sxi;
+    sz_out[(size_t)n * k + lane] = szi;
+    rx[lane] = 1.f / sxi;
+    rz[lane] = 1.f / szi;
+    for (int d = 0; d < Dx; ++d) gs[lane * ldx + d] = 0.f;
+  }
+  __syncwarp();
+  float lsum = 0.f;
+  if (live) {
+    const float rxi = rx[lane], rzi = rz[lane];
+    for (int j = 0; j < k; ++j) {
+      float ax = 0.f, az = 0.f;
+      for (int d = 0; d < Dx; ++d) { const float t = xi[d] - xs[j * ldx + d]; ax = fmaf(t, t, ax); }
+      for (int d = 0; d < Dz; ++d) { const float t = zi[d] - zs[j * ldz + d]; az = fmaf(t, t, az); }
+      const float ddx = sqrtf(ax), ddz = sqrtf(az);
+      const float hij = __fsub_rn(__fmul_rn(margin, __fmul_rn(ddz, rzi)), __fmul_rn(ddx, rxi));
+      const float hji = __fsub_rn(__fmul_rn(margin, __fmul_rn(ddz, rz[j])), __fmul_rn(ddx, rx[j]));
+      lsum += !(hij <= 0.f) ? hij : 0.f;                // NaN propagates (k == 1 -> 0/0, like the reference)
+      if (grad_x) {
+        const float wij = (hij > 0.f ? rxi : 0.f) + (hji > 0.f ? rx[j] : 0.f);
+        const float wh = ddx > 0.f ? -wij / ddx : 0.f;  // torch.norm subgradient: 0 at d == 0
+        for (int d = 0; d < Dx; ++d) gs[lane * ldx + d] = fmaf(wh, xi[d] - xs[j * ldx + d], gs[lane * ldx + d]);
+      }
+    }
+  }
+  lsum = warp_sum(lsum);
+  if (lane == 0) loss_part[n] = lsum;
+  __syncwarp();
+  if (grad_x)
+    for (int e = lane; e < k * Dx; e += 32) grad_x[(size_t)n * k * Dx + e] = gs[(e / Dx) * ldx + e % Dx];
+}
+static bool small_eligible(int k, int Dx, int Dz) { return k >= 1 && k <= 32 && Dx + Dz <= 64; }
+static size_t small_smem(int Dx, int Dz) {
+  return (size_t)kSmallWarps * (32 * ((Dx | 1) + (Dz | 1)) + 32 * (Dx | 1) + 64) * sizeof(float);
+}
+
 // plain row sums of one distance matrix (normaliser of compute_pair_distance's backward): one warp per row
 __global__ void rowsum_simple_kernel(const float* __restrict__ v, int k, int C, float* __restrict__ rs) {
   const int n = blockIdx.y;
@@ -807,6 +880,20 @@ extern "C" int ndp_ndiv_forward_backward(const float* x, const float* z, int N, 
   const NdivWs w = ndiv_ws(N, k, Dx, Dz);
   if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
   char* b = reinterpret_cast<char*>(ws);
+  if (small_eligible(k, Dx, Dz)) {
+    float* part = reinterpret_cast<float*>(b);          // N loss partials (ndiv_ws reserves >= 2N)
+    static bool attr_set = false;
+    if (!attr_set) {
+      NDP_CUDA(cudaFuncSetAttribute(ndiv_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)small_smem(62, 2)));
+      attr_set = true;
+    }
+    ndiv_small_kernel<<<(N + kSmallWarps - 1) / kSmallWarps, kSmallWarps * 32, small_smem(Dx, Dz), s>>>(
+        x, z, N, k, Dx, Dz, margin, sx, sz, part, grad_x);
+    NDP_LAUNCH_CHECK();
+    ndiv_finalize_kernel<<<1, 256, 0, s>>>(part, N, loss, nullptr);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
   const int* run_if = nullptr;
   const bool tc = gram_eligible(N, k, Dx, Dz, 0);
   if (tc) {
