@@ -84,23 +84,28 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 constexpr int kStages = 4;
+static int num_sms_cached() {
+  static int n = 0;
+  if (!n) n = num_sms();
+  return n;
+}
 
-template <int MODE, int TJ>
+template <int MODE, int TI, int TJ>
 __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
-  constexpr int RJ = TJ / 16;
-  __shared__ __align__(16) float As[kStages][kTC][kTI + 4];
+  constexpr int RI = TI / 16, RJ = TJ / 16;
+  __shared__ __align__(16) float As[kStages][kTC][TI + 4];
   __shared__ __align__(16) float Bs[kStages][kTC][TJ + 4];
   const int t = threadIdx.x;
-  const int i0 = blockIdx.x * kTI, j0 = blockIdx.y * TJ;
+  const int i0 = blockIdx.x * TI, j0 = blockIdx.y * TJ;
   int c_begin = 0, c_end = p.Cn;
   if (MODE == DW) {
     c_begin = blockIdx.z * p.rows_per_split;
     c_end = min(p.Cn, c_begin + p.rows_per_split);
   }
   const int ti = t >> 4, tj = t & 15;
-  float acc[4][RJ];
+  float acc[RI][RJ];
 #pragma unroll
-  for (int a = 0; a < 4; a++)
+  for (int a = 0; a < RI; a++)
 #pragma unroll
     for (int b = 0; b < RJ; b++) acc[a][b] = 0.f;
   float bsum = 0.f;
@@ -109,10 +114,10 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
   // transposed / gathered on the way), kStages-1 chunks in flight
   auto issue = [&](int stage, int c0) {
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
+    for (int q = 0; q < TI * kTC / kThreads; q++) {
       const int e = t + q * kThreads;
       int i, c;
-      if (MODE == DW) { i = e & (kTI - 1); c = e >> 6; } else { c = e & (kTC - 1); i = e >> 4; }
+      if (MODE == DW) { i = e % TI; c = e / TI; } else { c = e & (kTC - 1); i = e >> 4; }
       const int gi = i0 + i, gc = c0 + c;
       const bool ok = gi < p.I && gc < c_end;
       const float* src = MODE == FWD ? p.x.p0 : p.dP;
@@ -150,14 +155,19 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
     __syncthreads();          // chunk n landed for every thread; everyone is done reading stage (n-1) % kStages
     if (n + kStages - 1 < nchunks) issue((n + kStages - 1) % kStages, c_begin + (n + kStages - 1) * kTC);
     cp_async_commit();
-    if (MODE == DW && blockIdx.y == 0 && t < kTI) {
+    if (MODE == DW && blockIdx.y == 0 && t < TI) {
 #pragma unroll
       for (int c = 0; c < kTC; c++) bsum += As[st][c][t];
     }
 #pragma unroll
     for (int c = 0; c < kTC; c++) {
-      const float4 av = *reinterpret_cast<const float4*>(&As[st][c][ti * 4]);
-      const float a[4] = {av.x, av.y, av.z, av.w};
+      float a[RI];
+      if (RI == 4) {
+        const float4 av = *reinterpret_cast<const float4*>(&As[st][c][ti * 4]);
+        a[0] = av.x; a[1 % RI] = av.y; a[2 % RI] = av.z; a[3 % RI] = av.w;
+      } else {
+        a[0] = As[st][c][ti];
+      }
       float b[RJ];
       if (RJ == 4) {
         const float4 bv = *reinterpret_cast<const float4*>(&Bs[st][c][tj * 4]);
@@ -166,7 +176,7 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
         b[0] = Bs[st][c][tj];
       }
 #pragma unroll
-      for (int x = 0; x < 4; x++)
+      for (int x = 0; x < RI; x++)
 #pragma unroll
         for (int y = 0; y < RJ; y++) acc[x][y] = fmaf(a[x], b[y], acc[x][y]);
     }
@@ -175,8 +185,8 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
   float* out = p.out;
   if (MODE == DW) out += (size_t)blockIdx.z * p.split_stride;
 #pragma unroll
-  for (int x = 0; x < 4; x++) {
-    const int gi = i0 + ti * 4 + x;
+  for (int x = 0; x < RI; x++) {
+    const int gi = i0 + ti * RI + x;
     if (gi >= p.I) continue;
 #pragma unroll
     for (int y = 0; y < RJ; y++) {
@@ -192,19 +202,26 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
       out[(size_t)gi * p.ldo + gj] = v;
     }
   }
-  if (MODE == DW && blockIdx.y == 0 && t < kTI && i0 + t < p.I)
+  if (MODE == DW && blockIdx.y == 0 && t < TI && i0 + t < p.I)
     p.db_out[(size_t)blockIdx.z * p.split_stride + i0 + t] = bsum;
 }
 
+// 64-row tiles when they fill the GPU, 16-row tiles (4x the blocks, a quarter of the serial work each) otherwise:
+// at the reference's batch (336 rows) a layer is a handful of 64x64 tiles and the step is latency-bound.
 template <int MODE>
 static int launch_gemm(const GemmP& p, int splits, cudaStream_t s) {
   const dim3 block(kThreads);
-  if (p.J >= 64) {
-    const dim3 grid((p.I + kTI - 1) / kTI, (p.J + 63) / 64, splits);
-    gemm_kernel<MODE, 64><<<grid, block, 0, s>>>(p);
+  const int tj = p.J >= 64 ? 64 : 16;
+  const long long big_tiles = (long long)((p.I + 63) / 64) * ((p.J + tj - 1) / tj) * splits;
+  const bool small = big_tiles < num_sms_cached() && (MODE != DW || p.Cn <= 4096);
+  const int ti = small ? 16 : 64;
+  const dim3 grid((p.I + ti - 1) / ti, (p.J + tj - 1) / tj, splits);
+  if (tj == 64) {
+    if (small) gemm_kernel<MODE, 16, 64><<<grid, block, 0, s>>>(p);
+    else gemm_kernel<MODE, 64, 64><<<grid, block, 0, s>>>(p);
   } else {
-    const dim3 grid((p.I + kTI - 1) / kTI, (p.J + 15) / 16, splits);
-    gemm_kernel<MODE, 16><<<grid, block, 0, s>>>(p);
+    if (small) gemm_kernel<MODE, 16, 16><<<grid, block, 0, s>>>(p);
+    else gemm_kernel<MODE, 64, 16><<<grid, block, 0, s>>>(p);
   }
   NDP_LAUNCH_CHECK();
   return NDP_OK;
