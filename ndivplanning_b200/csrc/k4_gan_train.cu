@@ -21,8 +21,10 @@
 // evaluated on the F distinct rows only; torch.cat / repeat_interleave inputs are read through (row / div)
 // index maps.  Weight gradients are deterministic (no atomics).
 #include <math.h>
+#include <stdlib.h>
 #include <vector>
 #include "common.cuh"
+#include "tc_common.cuh"
 
 namespace ndp {
 namespace gan {
@@ -59,6 +61,9 @@ struct GemmP {
   const float* addend; float add_scale;
   float* out; int ldo;
   int rows_per_split; size_t split_stride; float* db_out;
+  const unsigned* amax_in;   // tensor path: max |dP| of the A operand (bits of a non-negative float), NULL = unscaled
+  unsigned* amax_out;        // DX: max |output| is accumulated here (atomicMax on the float bits), may be NULL
+  int use_tc;
 };
 
 __device__ __forceinline__ float act_fwd(float v, int act) {
@@ -184,6 +189,7 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
 
   float* out = p.out;
   if (MODE == DW) out += (size_t)blockIdx.z * p.split_stride;
+  float vmax = 0.f;
 #pragma unroll
   for (int x = 0; x < RI; x++) {
     const int gi = i0 + ti * RI + x;
@@ -200,16 +206,280 @@ __global__ void __launch_bounds__(kThreads) gemm_kernel(const GemmP p) {
         if (p.addend) v = fmaf(p.add_scale, __ldg(p.addend + (size_t)gi * p.J + gj), v);
       }
       out[(size_t)gi * p.ldo + gj] = v;
+      if (MODE == DX) vmax = fmaxf(vmax, fabsf(v));
     }
+  }
+  if (MODE == DX && p.amax_out) {
+    for (int o = 16; o; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    if ((t & 31) == 0 && vmax > 0.f) atomicMax(p.amax_out, __float_as_uint(vmax));
   }
   if (MODE == DW && blockIdx.y == 0 && t < TI && i0 + t < p.I)
     p.db_out[(size_t)blockIdx.z * p.split_stride + i0 + t] = bsum;
+}
+
+// ---- tensor-core variant of the three products (tcgen05, kind::f16, split-fp16 operands) ---------------------
+// Same operand semantics as gemm_kernel, 128 x 128 output tile per block, contraction in chunks of 64.  The block's
+// threads read the fp32 operands (through the same index maps), split every value into fp16 hi + fp16 lo (exact
+// residual) and write both halves straight into the K-major core-matrix image the MMA reads (the layout of
+// k2_ndiv_tc.cu: slab of K=16 = 4096 B, 8x16 B core matrices, LBO 2048, SBO 128); one thread issues
+// hi*hi + lo*hi + hi*lo per slab (22-bit products, fp32 accumulation in TMEM) while the block stages the next chunk
+// into the other buffer.  Gradient operands (dP ~ 1/batch) are multiplied by a power of two taken from the running
+// max |dP| of the producing kernel so that their lo halves stay normal fp16 numbers; the epilogue divides it out.
+using namespace ndp::tc;
+constexpr int kTcK = 32;                 // contraction elements per chunk (2 slabs of K = 16)
+constexpr int kTcU = kTcK / 16;          // (row, 8-group) units per thread and operand: 128 * kTcK / 8 / 256
+constexpr int kTcHalf = 128 * kTcK * 2;  // one 128 x kTcK fp16 image
+constexpr int kTcOp = 2 * kTcHalf;       // hi + lo
+constexpr int kTcStage = 2 * kTcOp;      // A + B
+constexpr int kTcTile = 128 * 132 * 4;   // fp32 epilogue tile (aliases the operand buffers)
+constexpr int kTcBuf = 2 * kTcStage > kTcTile ? 2 * kTcStage : kTcTile;
+constexpr int kTcSmem = kTcBuf + 1024 + 64;   // ~69 KB: two to three blocks per SM hide each other's load latency
+
+constexpr float kUnitScale = 256.f;
+__device__ __forceinline__ float pow2_scale(const unsigned* amax) {
+  if (!amax) return kUnitScale;
+  const float m = __uint_as_float(*amax);
+  if (!(m > 0.f) || !(m < 3e38f)) return kUnitScale;
+  int e;
+  frexpf(m, &e);                          // m = f * 2^e, f in [0.5, 1)
+  int sh = 9 - e;                         // m * 2^sh in [256, 512)
+  sh = sh > 100 ? 100 : (sh < -100 ? -100 : sh);
+  return ldexpf(1.f, sh);
+}
+
+// 8 consecutive contraction elements starting at `base` (nvalid of them in range), vectorised when aligned
+__device__ __forceinline__ void load8(const float* base, int nvalid, float (&v)[8]) {
+  if (nvalid >= 8 && ((reinterpret_cast<uintptr_t>(base) & 15) == 0)) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(base)), b = __ldg(reinterpret_cast<const float4*>(base) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; e++) v[e] = e < nvalid ? __ldg(base + e) : 0.f;
+  }
+}
+// row r of a RowSrc, columns [c, c+8) clipped to c_end
+__device__ __forceinline__ void load8_rowsrc(const RowSrc& x, int r, int c, int c_end, float (&v)[8]) {
+  const int n = c_end - c;
+  if (c + 8 <= x.k0) {
+    load8(x.p0 + (size_t)RowSrc::fdiv(r, x.div0, x.mul0) * x.ld0 + c, n, v);
+  } else if (c >= x.k0) {
+    const int rem = x.k0 + x.k1 - c;
+    load8(x.p1 + (size_t)RowSrc::fdiv(r, x.div1, x.mul1) * x.ld1 + (c - x.k0), n < rem ? n : rem, v);
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; e++) v[e] = (e < n && c + e < x.k0 + x.k1) ? __ldg(x.ptr(r, c + e)) : 0.f;
+  }
+}
+
+// (row, 8-group) unit of a 128 x 64 operand chunk -> hi / lo core-matrix rows
+__device__ __forceinline__ void store_unit(uint8_t* op, int r, int g, const float (&v)[8], float scale) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    const float a = v[2 * q] * scale, b = v[2 * q + 1] * scale;
+    h[q] = pack_hi(a, b);
+    l[q] = pack_lo(a, b, h[q]);
+  }
+  const uint32_t off = (uint32_t)((g >> 1) * 4096 + (g & 1) * 2048 + (r >> 3) * 128 + (r & 7) * 16);
+  *reinterpret_cast<uint4*>(op + off) = make_uint4(h[0], h[1], h[2], h[3]);
+  *reinterpret_cast<uint4*>(op + kTcHalf + off) = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
+  extern __shared__ __align__(128) uint8_t tc_smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int i0 = blockIdx.x * 128, j0 = blockIdx.y * 128;
+  int c_begin = 0, c_end = p.Cn;
+  if (MODE == DW) {
+    c_begin = blockIdx.z * p.rows_per_split;
+    c_end = min(p.Cn, c_begin + p.rows_per_split);
+  }
+  const int nchunks = (c_end - c_begin + kTcK - 1) / kTcK;
+  float* sbsum = reinterpret_cast<float*>(tc_smem + kTcBuf);                 // [256]
+  uint8_t* sbar = tc_smem + kTcBuf + 1024;
+  const uint32_t bar0 = smem_u32(sbar);                                        // bar_done[2]
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sbar + 32);
+  if (tid == 0) {
+    mbar_init(bar0, 1); mbar_init(bar0 + 8, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc128(smem_u32((const void*)tmem_slot));
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+  // operands without a tracked maximum (inputs, activations, weights: O(1e-3 .. 10)) are multiplied by 2^8 so that
+  // their lo halves are normal fp16 numbers (|v| must stay below 255, as in K1's tensor modes)
+  const float a_scale = MODE == FWD ? kUnitScale : pow2_scale(p.amax_in);
+  const float b_scale = kUnitScale;
+  const int nb = (p.J - j0) <= 64 ? 64 : 128;
+  const uint32_t idesc = idesc_f16(nb);
+
+  // unit maps.  C: source contiguous along the contraction -> quarter-warps own 8 consecutive rows of one 8-group
+  // (conflict-free 16 B stores).  R: source contiguous along the operand rows -> a warp owns 32 consecutive rows.
+  constexpr bool A_C = MODE != DW, B_C = MODE == FWD;
+  float va[kTcU][8], vb[kTcU][8];
+  float bsum = 0.f;
+  auto unit = [&](bool cmap, int q, int& r, int& g) {
+    const int u = tid + q * kThreads;
+    if (cmap) { r = ((u >> 5) << 3) | (u & 7); g = (u >> 3) & 3; } else { r = u & 127; g = u >> 7; }
+  };
+  auto fetch = [&](int n) {
+    const int cb = c_begin + n * kTcK;
+#pragma unroll
+    for (int q = 0; q < kTcU; q++) {
+      int r, g;
+      unit(A_C, q, r, g);
+      const int gi = i0 + r, c = cb + g * 8;
+      if (gi >= p.I || c >= c_end) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) va[q][e] = 0.f;
+      } else if (MODE == FWD) {
+        load8_rowsrc(p.x, gi, c, c_end, va[q]);
+      } else if (MODE == DX) {
+        load8(p.dP + (size_t)gi * p.ldp + c, c_end - c, va[q]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; e++) va[q][e] = c + e < c_end ? __ldg(p.dP + (size_t)(c + e) * p.ldp + gi) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < kTcU; q++) {
+      int r, g;
+      unit(B_C, q, r, g);
+      const int gj = j0 + r, c = cb + g * 8;
+      if (gj >= p.J || c >= c_end) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) vb[q][e] = 0.f;
+      } else if (MODE == FWD) {
+        load8(p.W + (size_t)gj * p.ldw + c, c_end - c, vb[q]);
+      } else if (MODE == DX) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) vb[q][e] = c + e < c_end ? __ldg(p.W + (size_t)(c + e) * p.ldw + p.wk0 + gj) : 0.f;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; e++) vb[q][e] = c + e < c_end ? __ldg(p.x.ptr(c + e, gj)) : 0.f;
+      }
+    }
+  };
+
+  if (nchunks > 0) fetch(0);
+  for (int n = 0; n < nchunks; n++) {
+    const int st = n & 1;
+    uint8_t* stage = tc_smem + st * kTcStage;
+    if (n >= 2) mbar_wait(bar0 + 8 * st, ((n >> 1) - 1) & 1);      // MMAs of chunk n-2 have consumed this buffer
+#pragma unroll
+    for (int q = 0; q < kTcU; q++) {
+      int r, g;
+      unit(A_C, q, r, g);
+      store_unit(stage, r, g, va[q], a_scale);
+      if (MODE == DW && blockIdx.y == 0) {
+#pragma unroll
+        for (int e = 0; e < 8; e++) bsum += va[q][e];
+      }
+      unit(B_C, q, r, g);
+      store_unit(stage + kTcOp, r, g, vb[q], b_scale);
+    }
+    fence_proxy_async();
+    if (n + 1 < nchunks) fetch(n + 1);                               // in flight across the barrier and the MMAs
+    __syncthreads();
+    if (tid == 0) {
+      fence_after_sync();
+      const uint32_t a_hi = smem_u32(stage), a_lo = a_hi + kTcHalf, b_hi = a_hi + kTcOp, b_lo = b_hi + kTcHalf;
+      const int rem = c_end - (c_begin + n * kTcK);
+      const int nsl = rem >= kTcK ? kTcK / 16 : (rem + 15) / 16;
+      for (int sl = 0; sl < nsl; sl++) {
+        const uint32_t o = sl * 4096;
+        mma_ss(tmem, smem_desc(a_hi + o, 2048, 128), smem_desc(b_hi + o, 2048, 128), idesc, (n > 0 || sl > 0) ? 1u : 0u);
+        mma_ss(tmem, smem_desc(a_lo + o, 2048, 128), smem_desc(b_hi + o, 2048, 128), idesc, 1u);
+        mma_ss(tmem, smem_desc(a_hi + o, 2048, 128), smem_desc(b_lo + o, 2048, 128), idesc, 1u);
+      }
+      mma_commit(bar0 + 8 * st);
+    }
+  }
+  if (MODE == DW && blockIdx.y == 0) sbsum[tid] = bsum;               // row r = tid & 127, two threads per row
+  if (nchunks > 0) {
+    const int last = nchunks - 1;
+    mbar_wait(bar0 + 8 * (last & 1), (last >> 1) & 1);
+  }
+  fence_after_sync();
+  __syncthreads();
+
+  // epilogue, phase 1: TMEM (lane = output row; warp w: lane quadrant w & 3, column half w >> 2) -> fp32 tile in
+  // the (now idle) operand buffers, row stride 132 floats (conflict-free 16 B stores)
+  constexpr int kLd = 132;
+  float* tile = reinterpret_cast<float*>(tc_smem);
+  const int q4 = warp & 3, hf = warp >> 2, row = q4 * 32 + lane;
+  const uint32_t lane_base = tmem + ((uint32_t)(q4 * 32) << 16);
+  const float inv = 1.f / (a_scale * b_scale);
+  if (nchunks > 0 && (nb == 128 || hf == 0)) {
+#pragma unroll 1
+    for (int cc = 0; cc < 4; cc++) {
+      const int col = hf * 64 + cc * 16;
+      uint32_t u[16];
+      tmem_ld16(lane_base + col, u);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 16; e += 4)
+        *reinterpret_cast<float4*>(tile + row * kLd + col + e) =
+            make_float4(__uint_as_float(u[e]) * inv, __uint_as_float(u[e + 1]) * inv, __uint_as_float(u[e + 2]) * inv,
+                        __uint_as_float(u[e + 3]) * inv);
+    }
+  }
+  __syncthreads();
+  // phase 2: lanes along the output columns -> coalesced reads of bias / saved activations / addend and writes
+  float* out = p.out;
+  if (MODE == DW) out += (size_t)blockIdx.z * p.split_stride;
+  float vmax = 0.f;
+  const int ncol = nb;
+  for (int idx = tid; idx < 128 * ncol; idx += kThreads) {
+    const int r = nb == 128 ? idx >> 7 : idx >> 6, cidx = idx & (ncol - 1);
+    const int gi = i0 + r, gj = j0 + cidx;
+    if (gi >= p.I || gj >= p.J) continue;
+    float v = nchunks > 0 ? tile[r * kLd + cidx] : 0.f;
+    if (MODE == FWD) {
+      v = act_fwd(v + __ldg(p.b + gj), p.act);
+    } else if (MODE == DX) {
+      if (p.hprev) v *= act_bwd(__ldg(p.hprev + (size_t)gi * p.ldh + gj), p.act_prev);
+      if (p.addend) v = fmaf(p.add_scale, __ldg(p.addend + (size_t)gi * p.J + gj), v);
+      vmax = fmaxf(vmax, fabsf(v));
+    }
+    out[(size_t)gi * p.ldo + gj] = v;
+  }
+  if (MODE == DX && p.amax_out) {
+    for (int o = 16; o; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+    if (lane == 0 && vmax > 0.f) atomicMax(p.amax_out, __float_as_uint(vmax));
+  }
+  if (MODE == DW && blockIdx.y == 0 && tid < 128 && i0 + tid < p.I)
+    p.db_out[(size_t)blockIdx.z * p.split_stride + i0 + tid] = sbsum[tid] + sbsum[tid + 128];
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc128(tmem);
+}
+
+template <int MODE>
+static int launch_gemm_tc(const GemmP& p, int splits, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    NDP_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
+    attr_set = true;
+  }
+  const dim3 grid((p.I + 127) / 128, (p.J + 127) / 128, splits);
+  gemm_tc_kernel<MODE><<<grid, kThreads, kTcSmem, s>>>(p);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
 }
 
 // 64-row tiles when they fill the GPU, 16-row tiles (4x the blocks, a quarter of the serial work each) otherwise:
 // at the reference's batch (336 rows) a layer is a handful of 64x64 tiles and the step is latency-bound.
 template <int MODE>
 static int launch_gemm(const GemmP& p, int splits, cudaStream_t s) {
+  // tensor path: wide layers at large batch (thin layers -- fc5, the logit, the 4 action columns -- stay on FFMA)
+  const bool tc = p.use_tc && p.J >= 64 && p.Cn >= 64 &&
+                  (MODE == DW ? (p.I >= 64 && p.Cn >= 2048 && p.rows_per_split % kTcK == 0) : p.I >= 2048);
+  if (tc) return launch_gemm_tc<MODE>(p, splits, s);
   const dim3 block(kThreads);
   const int tj = p.J >= 64 ? 64 : 16;
   const long long big_tiles = (long long)((p.I + 63) / 64) * ((p.J + tj - 1) / tj) * splits;
@@ -310,19 +580,24 @@ struct Net {
   }
 };
 
+constexpr int kMaxSplits = 128;
+// batch rows -> partial slots of the weight-gradient products: 64-row slots while the batch is small (the step is
+// latency-bound there), >= 512-row slots at large batch so that (output tiles x splits) fills the GPU twice over
 static void split_plan(int M, int* splits, int* rows_per_split) {
-  int s = (M + 63) / 64;
-  if (s > 32) s = 32;
+  int s = M <= 4096 ? (M + 63) / 64 : (M + 511) / 512;
+  const int cap = M <= 4096 ? 32 : kMaxSplits;
+  if (s > cap) s = cap;
+  if (M > 4096 && s < 32) s = 32;
   if (s < 1) s = 1;
   int rps = (M + s - 1) / s;
-  rps = (rps + kTC - 1) / kTC * kTC;
+  rps = (rps + 63) / 64 * 64;
   *rows_per_split = rps;
   *splits = (M + rps - 1) / rps;
 }
 
 // acts[l] = output of layer l ([M x out[l]]); hidden activation `act`, none on the last layer
 static int mlp_forward(const Net& n, const float* params, const RowSrc& x0, int M, float* const* acts, int act,
-                       cudaStream_t s) {
+                       int use_tc, cudaStream_t s) {
   for (int l = 0; l < n.L; l++) {
     GemmP p = {};
     p.I = M; p.J = n.out[l]; p.Cn = n.in[l];
@@ -331,6 +606,7 @@ static int mlp_forward(const Net& n, const float* params, const RowSrc& x0, int 
     p.b = params + n.b_off[l];
     p.act = l + 1 < n.L ? act : ACT_NONE;
     p.out = acts[l]; p.ldo = n.out[l];
+    p.use_tc = use_tc;
     int rc = launch_gemm<FWD>(p, 1, s);
     if (rc) return rc;
   }
@@ -342,11 +618,13 @@ static int mlp_forward(const Net& n, const float* params, const RowSrc& x0, int 
 // layer 0 (+ add_scale * addend).  bufA/bufB: [M x max hidden width] ping-pong scratch.
 static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int M, float* const* acts,
                         const float* d_out, float* bufA, float* bufB, int act, float* part, int slot0,
-                        float* dx0, int col0, int ncols, const float* addend, float add_scale, cudaStream_t s) {
+                        float* dx0, int col0, int ncols, const float* addend, float add_scale, int use_tc,
+                        unsigned* amax, int* amax_used, cudaStream_t s) {
   int splits, rps;
   split_plan(M, &splits, &rps);
   const float* cur = d_out;
   float* nxt = bufA;
+  const unsigned* cur_amax = nullptr;     // d_out feeds thin (FFMA) products only; every dP made here gets a slot
   for (int l = n.L - 1; l >= 0; l--) {
     if (part) {
       GemmP p = {};
@@ -356,6 +634,7 @@ static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int
       p.out = part + (size_t)slot0 * n.P + n.w_off[l]; p.ldo = n.in[l];
       p.db_out = part + (size_t)slot0 * n.P + n.b_off[l];
       p.rows_per_split = rps; p.split_stride = n.P;
+      p.use_tc = use_tc; p.amax_in = cur_amax;
       int rc = launch_gemm<DW>(p, splits, s);
       if (rc) return rc;
     }
@@ -364,7 +643,11 @@ static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int
       p.I = M; p.Cn = n.out[l];
       p.dP = cur; p.ldp = n.out[l];
       p.W = params + n.w_off[l]; p.ldw = n.in[l];
+      p.use_tc = use_tc; p.amax_in = cur_amax;
+      unsigned* slot = nullptr;
       if (l > 0) {
+        slot = amax + (*amax_used)++;
+        p.amax_out = slot;
         p.J = n.in[l]; p.wk0 = 0;
         p.hprev = acts[l - 1]; p.ldh = n.in[l]; p.act_prev = act;
         p.out = nxt; p.ldo = n.in[l];
@@ -376,6 +659,7 @@ static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int
       int rc = launch_gemm<DX>(p, 1, s);
       if (rc) return rc;
       cur = nxt;
+      cur_amax = slot;
       nxt = (nxt == bufA) ? bufB : bufA;
     }
   }
@@ -395,6 +679,9 @@ struct ndp_gan {
   int B_max;
   void* arena;
   float *gp, *gm, *gv, *gg, *dp, *dm, *dv, *dg;
+  int use_tc;        // tcgen05 products for wide layers at large batch (NDP_GAN_EXACT=1 keeps everything on FFMA)
+  unsigned* amax;    // running max |dP| slots of one step (operand scales of the tensor path)
+  int n_amax;
   double* hp;        // {lr, beta1, beta2, eps}
   int* steps;        // [0] discriminator, [1] generator optimiser step counts
   float* g_act[5];   // generator layer outputs, B rows; g_act[4] = a_hat
@@ -445,6 +732,10 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   const size_t PG = g->G.P, PD = g->D.P;
   const size_t o_gp = carve(off, 4 * PG * 4), o_dp = carve(off, 4 * PD * 4);
   const size_t o_hp = carve(off, 4 * sizeof(double)), o_steps = carve(off, 2 * sizeof(int));
+  g->n_amax = 8 * d->d_steps + 16;
+  const size_t o_amax = carve(off, (size_t)g->n_amax * sizeof(unsigned));
+  const char* ex = getenv("NDP_GAN_EXACT");
+  g->use_tc = !(ex && ex[0] == '1');
   size_t o_g[5], o_dr[4], o_df[4];
   for (int l = 0; l < 5; l++) o_g[l] = carve(off, B * gout[l] * 4);
   for (int l = 0; l < 4; l++) o_dr[l] = carve(off, F * dout[l] * 4);
@@ -453,7 +744,7 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   const size_t o_bA = carve(off, B * 256 * 4), o_bB = carve(off, B * 256 * 4);
   const size_t o_gdiv = carve(off, B * d->A * 4), o_da = carve(off, B * d->A * 4);
   const size_t o_sx = carve(off, B * 4), o_sz = carve(off, B * 4);
-  const size_t o_gpart = carve(off, 32 * PG * 4), o_dpart = carve(off, 64 * PD * 4);
+  const size_t o_gpart = carve(off, (size_t)kMaxSplits * PG * 4), o_dpart = carve(off, (size_t)2 * kMaxSplits * PD * 4);
   const size_t o_ws = carve(off, ndiv_bytes);
   cudaError_t e = cudaMalloc(&g->arena, off);
   if (e != cudaSuccess) {
@@ -465,6 +756,7 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   g->gp = (float*)(base + o_gp); g->gm = g->gp + PG; g->gv = g->gm + PG; g->gg = g->gv + PG;
   g->dp = (float*)(base + o_dp); g->dm = g->dp + PD; g->dv = g->dm + PD; g->dg = g->dv + PD;
   g->hp = (double*)(base + o_hp); g->steps = (int*)(base + o_steps);
+  g->amax = (unsigned*)(base + o_amax);
   for (int l = 0; l < 5; l++) g->g_act[l] = (float*)(base + o_g[l]);
   for (int l = 0; l < 4; l++) { g->dr_act[l] = (float*)(base + o_dr[l]); g->df_act[l] = (float*)(base + o_df[l]); }
   g->dl_real = (float*)(base + o_dlr); g->dl_fake = (float*)(base + o_dlf);
@@ -557,11 +849,13 @@ int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, con
   NDP_CHECK_ARG(F > 0 && F <= g->d.max_F, "ndp_gan_train_step: F=%d outside (0, max_F=%d]", F, g->d.max_F);
   cudaStream_t s = (cudaStream_t)stream;
   const int S = g->d.S, C = g->d.C, A = g->d.A, nd = g->d.nd, B = F * S;
-  int rc;
+  int rc, used = 0;
+  const int tc = g->use_tc;
+  NDP_CUDA(cudaMemsetAsync(g->amax, 0, (size_t)g->n_amax * sizeof(unsigned), s));
 #define NDP_TRY(x) do { rc = (x); if (rc) return rc; } while (0)
   // generator forward on [codes repeated S times | noise]                      (train_gan.py:159-165)
   const RowSrc xg = row_src(codes, C, S, noise, nd, 1);
-  NDP_TRY(mlp_forward(g->G, g->gp, xg, B, g->g_act, ACT_RELU, s));
+  NDP_TRY(mlp_forward(g->G, g->gp, xg, B, g->g_act, ACT_RELU, tc, s));
   const float* a_hat = g->g_act[4];
   const RowSrc x_real = row_src(actions, A, 1, codes, C, 1);     // cat([action, state_code]) gan.py:102
   const RowSrc x_fake = row_src(a_hat, A, 1, codes, C, S);
@@ -569,19 +863,19 @@ int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, con
   split_plan(F, &sr, &rps);
   split_plan(B, &sf, &rps);
   for (int it = 0; it < g->d.d_steps; it++) {                    // :172-184
-    NDP_TRY(mlp_forward(g->D, g->dp, x_real, F, g->dr_act, ACT_LEAKY, s));
-    NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, s));
+    NDP_TRY(mlp_forward(g->D, g->dp, x_real, F, g->dr_act, ACT_LEAKY, tc, s));
+    NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
     bce_kernel<<<1, 1024, 0, s>>>(g->dr_act[3], F, 1.f, g->dl_real, g->df_act[3], B, 0.f, g->dl_fake, losses + 0,
                                   g->steps + 0);
     NDP_LAUNCH_CHECK();
     NDP_TRY(mlp_backward(g->D, g->dp, x_real, F, g->dr_act, g->dl_real, g->bufA, g->bufB, ACT_LEAKY, g->d_part, 0,
-                         nullptr, 0, 0, nullptr, 0.f, s));
+                         nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
     NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, g->d_part, sr,
-                         nullptr, 0, 0, nullptr, 0.f, s));
+                         nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
     NDP_TRY(adam(g->dp, g->dm, g->dv, g->dg, g->d_part, sr + sf, g->D.P, g->hp, g->steps + 0, s));
   }
   // generator loss through the UPDATED discriminator                            (:187-190)
-  NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, s));
+  NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
   bce_kernel<<<1, 1024, 0, s>>>(g->df_act[3], B, 1.f, g->dl_fake, nullptr, 0, 0.f, nullptr, losses + 1, g->steps + 1);
   NDP_LAUNCH_CHECK();
   // normalized diversification of the S samples of every code                   (:193-196)
@@ -589,9 +883,9 @@ int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, con
                                     g->ndiv_ws, g->ndiv_ws_bytes, stream));
   // d total / d a_hat = dD/da_hat (first A input columns of discriminator fc1) + div_factor * d div / d a_hat
   NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, nullptr, 0, g->da,
-                       0, A, g->g_div, g->d.div_factor, s));
+                       0, A, g->g_div, g->d.div_factor, tc, g->amax, &used, s));
   NDP_TRY(mlp_backward(g->G, g->gp, xg, B, g->g_act, g->da, g->bufA, g->bufB, ACT_RELU, g->g_part, 0, nullptr, 0, 0,
-                       nullptr, 0.f, s));
+                       nullptr, 0.f, tc, g->amax, &used, s));
   NDP_TRY(adam(g->gp, g->gm, g->gv, g->gg, g->g_part, sf, g->G.P, g->hp, g->steps + 1, s));   // :198-203
 #undef NDP_TRY
   return NDP_OK;

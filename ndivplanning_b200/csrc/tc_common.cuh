@@ -67,6 +67,14 @@ __device__ __forceinline__ void tmem_dealloc256(uint32_t base) {
   asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(base) : "memory");
 }
 
+__device__ __forceinline__ void tmem_alloc128(uint32_t dst_smem) {   // up to four co-resident CTAs per SM
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" ::"r"(dst_smem) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc128(uint32_t base) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" ::"r"(base) : "memory");
+}
+
 // ---- descriptors --------------------------------------------------------------------------
 // smem operand, K-major, no swizzle: core matrix = 8 rows x 16 B (128 contiguous bytes);
 // lbo = bytes between the two K-chunks of one K=16 slab, sbo = bytes between 8-row groups.
