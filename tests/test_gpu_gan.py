@@ -167,5 +167,7 @@ def test_gan_step_tensor_path_matches_exact_path(cuda, monkeypatch, divf):
         if name == "generator" and divf > 0:
             assert rms < 1e-3 and np.median(err) < 1e-4, (name, err.max(), rms)
         else:
-            # isolated larger entries: (leaky-)ReLU derivative of units whose pre-activation is within round-off of 0
-            assert rms < 2e-6 and np.median(err) < 2e-7 and err.max() < 3e-4, (name, err.max(), rms, np.median(err))
+            # 22-bit products through a chain of up to eight layer products (the discriminator's chain is three:
+            # median 2e-8); isolated larger entries are (leaky-)ReLU derivatives of units whose pre-activation is
+            # within round-off of 0 and lands on the other side
+            assert rms < 1e-5 and np.median(err) < 2e-6 and err.max() < 2e-3, (name, err.max(), rms, np.median(err))
