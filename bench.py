@@ -329,6 +329,35 @@ def run_gpu(args):
     torch.cuda.synchronize()
     ndiv_ms = sum(a.elapsed_time(b) for a, b in pairs_) / args.steps
     clocks = sampler.finish()
+    # ---- GAN training step around ndiv (context, rank 0 at N=1): CUDA-graph replays of one
+    # ndp_gan_train_step at the reference's batch (F=56 codes x S=6 samples) and at F=4096 x S=16
+    gan_steps = {}
+    if world == 1:
+        from ndivplanning_b200 import GanTrainer
+        for Fg, Sg in ((56, 6), (4096, 16)):
+            ggen, gdis = synthetic.make_gan_models(2, seed=0)
+            tr = GanTrainer(ggen, gdis, num_sample=Sg, noise_dim=2, max_codes=Fg, device=dev)
+            gb = [t.to(dev) for t in synthetic.make_gan_batch(Fg, Sg, 2, seed=5)]
+            for _ in range(2):
+                tr.step(*gb)
+            l0 = launch_count()
+            tr.step(*gb)
+            per_step = launch_count() - l0
+            cg = tr.capture(*gb)
+            for _ in range(3):
+                cg.replay()
+            torch.cuda.synchronize()
+            n_ = 20
+            a, b = ev(), ev()
+            a.record()
+            for _ in range(n_):
+                cg.replay()
+            b.record(); torch.cuda.synchronize()
+            g_ms = a.elapsed_time(b) / n_
+            gan_steps[f"F{Fg}_S{Sg}"] = {"ms_per_step": g_ms, "samples_per_s": Fg * Sg / (g_ms * 1e-3),
+                                         "kernel_launches_per_step": per_step,
+                                         "losses_D_G_div": [float(v) for v in tr.losses.cpu()]}
+            del cg, tr
     # ---- other precision modes of the same kernel family, for context (short runs)
     modes = {}
     if world == 1:
@@ -406,6 +435,9 @@ def run_gpu(args):
                                           "wrapper's 11 launches"}},
             "parity": parity,
             "modes": modes,
+            "gan_train_step": {"what": "one iteration of train_gan.py:159-203 on encoded inputs (generator + discriminator "
+                                       "forward/backward, BCE, ndiv, two Adam updates), CUDA-graph replay",
+                               "shapes": gan_steps},
         }
         if world == 1:
             t0 = time.perf_counter()

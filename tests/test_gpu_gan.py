@@ -171,3 +171,39 @@ def test_gan_step_tensor_path_matches_exact_path(cuda, monkeypatch, divf):
             # median 2e-8); isolated larger entries are (leaky-)ReLU derivatives of units whose pre-activation is
             # within round-off of 0 and lands on the other side
             assert rms < 1e-5 and np.median(err) < 2e-6 and err.max() < 2e-3, (name, err.max(), rms, np.median(err))
+
+
+def test_gan_step_edge_shapes_and_lr(cuda):
+    """one code, two samples; zero discriminator steps; learning-rate change between steps — against the oracle"""
+    for Fb, S, nd, dsteps in ((1, 2, 2, 1), (3, 4, 15, 0), (5, 32, 3, 1)):
+        gen, dis = synthetic.make_gan_models(nd, seed=4)
+        c, a, z = synthetic.make_gan_batch(Fb, S, nd, seed=6)
+        tr = GanTrainer(gen, dis, num_sample=S, noise_dim=nd, max_codes=max(Fb, 8), discrim_steps_per_gen=dsteps, device=cuda)
+        og, od = O.GeneratorMLP(nd), O.ActionDiscriminator()
+        og.load_state_dict(gen.state_dict()); od.load_state_dict(dis.state_dict())
+        G_opt, D_opt = O.gan_optimizers(og, od)
+        for it, lr in enumerate((2e-4, 5e-5)):
+            tr.set_lr(lr)
+            for opt in (G_opt, D_opt):
+                for grp in opt.param_groups:
+                    grp["lr"] = lr
+            l = tr.step(c.to(cuda), a.to(cuda), z.to(cuda)).cpu().numpy()
+            dl, gl, pl, _ = O.gan_train_step(og, od, G_opt, D_opt, c, a, z, 0.1, dsteps)
+            if dsteps:
+                np.testing.assert_allclose(l[0], float(dl), rtol=1e-5)
+            np.testing.assert_allclose(l[1], float(gl), rtol=1e-4 if it else 2e-5)
+            np.testing.assert_allclose(l[2], float(pl), rtol=2e-3 if it else 1e-4)
+        gsd, dsd = tr.state_dicts()
+        gp = _flat_sd(gsd, G_LAYERS)
+        rp = torch.cat([p.detach().reshape(-1) for p in og.parameters()]).numpy()
+        # lr-sized sign jumps of parameters with round-off-sized gradients are allowed (see the module docstring)
+        assert np.median(np.abs(gp - rp)) < 1e-7 and np.abs(gp - rp).max() <= 2.2 * (2e-4 + 5e-5), (Fb, S, np.abs(gp - rp).max())
+
+
+def test_gan_single_sample_groups_are_nan_like_the_reference(cuda):
+    """num_sample = 1: the normalised distance of a one-point group is 0/0 (diversity.py:17-18) -> NaN loss"""
+    gen, dis = synthetic.make_gan_models(2, seed=0)
+    c, a, z = synthetic.make_gan_batch(4, 1, 2, seed=6)
+    tr = GanTrainer(gen, dis, num_sample=1, noise_dim=2, max_codes=4, device=cuda)
+    l = tr.step(c.to(cuda), a.to(cuda), z.to(cuda)).cpu().numpy()
+    assert np.isfinite(l[0]) and np.isfinite(l[1]) and np.isnan(l[2])
