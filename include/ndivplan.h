@@ -221,6 +221,10 @@ int ndp_gan_export(ndp_gan* g, float* const* gW, float* const* gb, float* const*
 /* codes [F,C], actions [F,A], noise [F,S,nd]; losses[3] = {D_loss, G_loss, pair_div_loss} (all device fp32) */
 int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, const float* noise, int F,
                        float* losses, void* stream);
+/* data-parallel variant (SURVEY.md 8e for this row): same parameters on every rank, F codes of a world*F global
+ * batch per rank; ONE all-reduce of the flat gradient per optimiser step + one of the 3 loss scalars, on `stream` */
+int ndp_gan_train_step_dp(ndp_gan* g, ndp_comm* comm, int world, const float* codes, const float* actions,
+                          const float* noise, int F, float* losses, void* stream);
 int ndp_gan_set_lr(ndp_gan* g, double lr, void* stream);        /* StepLR (train_gan.py:105) lives in the caller */
 /* inspection: flat [W0|b0|W1|b1|...] gradients of the last step (either may be NULL), a_hat [F*S,A] */
 int ndp_gan_param_counts(const ndp_gan* g, size_t* n_gen, size_t* n_dis);

@@ -61,6 +61,7 @@ _PROTOS = {
     "ndp_gan_load": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _vp]),
     "ndp_gan_export": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _vp]),
     "ndp_gan_train_step": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _vp]),
+    "ndp_gan_train_step_dp": (_i, [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp]),
     "ndp_gan_set_lr": (_i, [_vp, C.c_double, _vp]),
     "ndp_gan_param_counts": (_i, [_vp, C.POINTER(_sz), C.POINTER(_sz)]),
     "ndp_gan_grads": (_i, [_vp, _vp, _vp, _vp]),

@@ -504,7 +504,7 @@ static int launch_gemm(const GemmP& p, int splits, cudaStream_t s) {
 __global__ void __launch_bounds__(1024) bce_kernel(const float* __restrict__ x0, int n0, float y0,
                                                     float* __restrict__ dl0, const float* __restrict__ x1, int n1,
                                                     float y1, float* __restrict__ dl1, float* __restrict__ loss_out,
-                                                    int* __restrict__ step_counter) {
+                                                    int* __restrict__ step_counter, float world) {
   __shared__ float red[32];
   float tot = 0.f;
   for (int set = 0; set < 2; set++) {
@@ -513,7 +513,7 @@ __global__ void __launch_bounds__(1024) bce_kernel(const float* __restrict__ x0,
     const float y = set ? y1 : y0;
     float* dl = set ? dl1 : dl0;
     if (n <= 0) continue;
-    const float inv = 1.f / (float)n;
+    const float inv = 1.f / ((float)n * world);   // data parallel: mean over the GLOBAL batch (equal shards)
     float s = 0.f;
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
       const float v = x[i];
@@ -561,6 +561,16 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, float*
   p[i] = p[i] - step_size * (mi / denom);
   m[i] = mi;
   v[i] = vi;
+}
+
+// data-parallel step: fixed-order sum of the partial slots into the flat gradient (then summed over ranks by NCCL)
+__global__ void __launch_bounds__(256) reduce_parts_kernel(const float* __restrict__ part, int nparts, size_t stride,
+                                                           int P, float* __restrict__ grad) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  float g = 0.f;
+  for (int s = 0; s < nparts; s++) g += part[(size_t)s * stride + i];
+  grad[i] = g;
 }
 
 // ---- network description: flat parameter buffer [W0 | b0 | W1 | b1 | ...], torch [out,in] weights
@@ -834,17 +844,27 @@ int ndp_gan_set_lr(ndp_gan* g, double lr, void* stream) {
   return NDP_OK;
 }
 
+// gradient = fixed-order sum of the partial slots; with a communicator, additionally summed over the ranks
+// (ONE all-reduce per optimiser step, on the caller's stream) before the update
 static int adam(float* p, float* m, float* v, float* grad, const float* part, int nparts, size_t P, const double* hp,
-                const int* step, cudaStream_t s) {
-  adam_kernel<<<(unsigned)((P + 255) / 256), 256, 0, s>>>(p, m, v, part, nparts, P, (int)P, hp, step, grad);
+                const int* step, ndp_comm* comm, cudaStream_t s) {
+  const unsigned blocks = (unsigned)((P + 255) / 256);
+  if (comm) {
+    reduce_parts_kernel<<<blocks, 256, 0, s>>>(part, nparts, P, (int)P, grad);
+    NDP_LAUNCH_CHECK();
+    if (int rc = ndp_comm_allreduce_sum_f32(comm, grad, (int)P, s)) return rc;
+    adam_kernel<<<blocks, 256, 0, s>>>(p, m, v, grad, 1, 0, (int)P, hp, step, nullptr);
+  } else {
+    adam_kernel<<<blocks, 256, 0, s>>>(p, m, v, part, nparts, P, (int)P, hp, step, grad);
+  }
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
 
 // One iteration of the loop body train_gan.py:159-203 for F (state, goal) codes with S samples each.
 // codes [F,C], actions [F,A], noise [F,S,nd] (device, fp32); losses [3] (device) = {D_loss, G_loss, pair_div_loss}.
-int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, const float* noise, int F,
-                       float* losses, void* stream) {
+static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* codes, const float* actions,
+                           const float* noise, int F, float* losses, void* stream) {
   NDP_CHECK_ARG(g && codes && actions && noise && losses, "ndp_gan_train_step: null argument");
   NDP_CHECK_ARG(F > 0 && F <= g->d.max_F, "ndp_gan_train_step: F=%d outside (0, max_F=%d]", F, g->d.max_F);
   cudaStream_t s = (cudaStream_t)stream;
@@ -866,17 +886,18 @@ int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, con
     NDP_TRY(mlp_forward(g->D, g->dp, x_real, F, g->dr_act, ACT_LEAKY, tc, s));
     NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
     bce_kernel<<<1, 1024, 0, s>>>(g->dr_act[3], F, 1.f, g->dl_real, g->df_act[3], B, 0.f, g->dl_fake, losses + 0,
-                                  g->steps + 0);
+                                  g->steps + 0, (float)world);
     NDP_LAUNCH_CHECK();
     NDP_TRY(mlp_backward(g->D, g->dp, x_real, F, g->dr_act, g->dl_real, g->bufA, g->bufB, ACT_LEAKY, g->d_part, 0,
                          nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
     NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, g->d_part, sr,
                          nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
-    NDP_TRY(adam(g->dp, g->dm, g->dv, g->dg, g->d_part, sr + sf, g->D.P, g->hp, g->steps + 0, s));
+    NDP_TRY(adam(g->dp, g->dm, g->dv, g->dg, g->d_part, sr + sf, g->D.P, g->hp, g->steps + 0, comm, s));
   }
   // generator loss through the UPDATED discriminator                            (:187-190)
   NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
-  bce_kernel<<<1, 1024, 0, s>>>(g->df_act[3], B, 1.f, g->dl_fake, nullptr, 0, 0.f, nullptr, losses + 1, g->steps + 1);
+  bce_kernel<<<1, 1024, 0, s>>>(g->df_act[3], B, 1.f, g->dl_fake, nullptr, 0, 0.f, nullptr, losses + 1, g->steps + 1,
+                                (float)world);
   NDP_LAUNCH_CHECK();
   // normalized diversification of the S samples of every code                   (:193-196)
   NDP_TRY(ndp_ndiv_forward_backward(a_hat, noise, F, S, A, nd, g->d.margin, g->sx, g->sz, losses + 2, g->g_div,
@@ -886,9 +907,25 @@ int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, con
                        0, A, g->g_div, g->d.div_factor, tc, g->amax, &used, s));
   NDP_TRY(mlp_backward(g->G, g->gp, xg, B, g->g_act, g->da, g->bufA, g->bufB, ACT_RELU, g->g_part, 0, nullptr, 0, 0,
                        nullptr, 0.f, tc, g->amax, &used, s));
-  NDP_TRY(adam(g->gp, g->gm, g->gv, g->gg, g->g_part, sf, g->G.P, g->hp, g->steps + 1, s));   // :198-203
+  NDP_TRY(adam(g->gp, g->gm, g->gv, g->gg, g->g_part, sf, g->G.P, g->hp, g->steps + 1, comm, s));   // :198-203
+  if (comm) NDP_TRY(ndp_comm_allreduce_sum_f32(comm, losses, 3, s));   // partial means / partial ndiv sum -> global
 #undef NDP_TRY
   return NDP_OK;
+}
+
+int ndp_gan_train_step(ndp_gan* g, const float* codes, const float* actions, const float* noise, int F,
+                       float* losses, void* stream) {
+  return train_step_impl(g, nullptr, 1, codes, actions, noise, F, losses, stream);
+}
+
+// Data-parallel step: every rank holds the same parameters and optimiser state and F of the world * F codes of the
+// global batch (equal shards).  Local forward/backward, ONE NCCL all-reduce of the flat gradient per optimiser step
+// (discriminator: 58,305 floats, generator: 83,780 + nd*128) and one of the three loss scalars; the ndiv groups
+// are rank-local.  Parameters stay bit-identical across ranks (same reduced gradient, same update).
+int ndp_gan_train_step_dp(ndp_gan* g, ndp_comm* comm, int world, const float* codes, const float* actions,
+                          const float* noise, int F, float* losses, void* stream) {
+  NDP_CHECK_ARG(comm && world >= 1, "ndp_gan_train_step_dp: needs a communicator and world >= 1");
+  return train_step_impl(g, comm, world, codes, actions, noise, F, losses, stream);
 }
 
 // a_hat of the last step ([F*S, A]) — what train_gan.py:165 calls action_hat

@@ -104,17 +104,24 @@ class GanTrainer:
             _lib.check(_lib.lib().ndp_gan_set_lr(self._h, self.lr, _lib.stream_ptr(self.device)))
 
     # ---- the step --------------------------------------------------------------------------------------------
-    def step(self, codes: torch.Tensor, actions: torch.Tensor, noise: torch.Tensor) -> torch.Tensor:
+    def step(self, codes: torch.Tensor, actions: torch.Tensor, noise: torch.Tensor, comm=None) -> torch.Tensor:
         """codes [F,C], actions [F,A], noise [F,S,nd] (CUDA fp32) -> losses [3] = (D_loss, G_loss, pair_div_loss),
-        a device tensor owned by the trainer (overwritten by the next step; no host sync here)."""
+        a device tensor owned by the trainer (overwritten by the next step; no host sync here).
+        comm (ndivplanning_b200.sharded.Comm): data-parallel step — this rank's F codes of a world*F global batch,
+        one NCCL all-reduce of the flat gradient per optimiser step; the losses are those of the global batch."""
         _lib.require_cuda(codes, actions, noise)
         F = codes.shape[0]
         codes, actions, noise = _lib.f32c(codes), _lib.f32c(actions), _lib.f32c(noise)
         if codes.shape != (F, self.C) or actions.shape != (F, self.A) or noise.shape != (F, self.S, self.nd):
             raise ValueError(f"expected codes [F,{self.C}], actions [F,{self.A}], noise [F,{self.S},{self.nd}]")
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().ndp_gan_train_step(self._h, _lib.ptr(codes), _lib.ptr(actions), _lib.ptr(noise), F,
-                                                     _lib.ptr(self.losses), _lib.stream_ptr(self.device)))
+            if comm is None:
+                _lib.check(_lib.lib().ndp_gan_train_step(self._h, _lib.ptr(codes), _lib.ptr(actions), _lib.ptr(noise), F,
+                                                         _lib.ptr(self.losses), _lib.stream_ptr(self.device)))
+            else:
+                _lib.check(_lib.lib().ndp_gan_train_step_dp(self._h, comm._h, comm.world, _lib.ptr(codes), _lib.ptr(actions),
+                                                            _lib.ptr(noise), F, _lib.ptr(self.losses),
+                                                            _lib.stream_ptr(self.device)))
         return self.losses
 
     def capture(self, codes: torch.Tensor, actions: torch.Tensor, noise: torch.Tensor) -> "torch.cuda.CUDAGraph":
