@@ -434,19 +434,65 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
   if (MODE == DW) out += (size_t)blockIdx.z * p.split_stride;
   float vmax = 0.f;
   const int ncol = nb;
-  for (int idx = tid; idx < 128 * ncol; idx += kThreads) {
-    const int r = nb == 128 ? idx >> 7 : idx >> 6, cidx = idx & (ncol - 1);
-    const int gi = i0 + r, gj = j0 + cidx;
-    if (gi >= p.I || gj >= p.J) continue;
-    float v = nchunks > 0 ? tile[r * kLd + cidx] : 0.f;
-    if (MODE == FWD) {
-      v = act_fwd(v + __ldg(p.b + gj), p.act);
-    } else if (MODE == DX) {
-      if (p.hprev) v *= act_bwd(__ldg(p.hprev + (size_t)gi * p.ldh + gj), p.act_prev);
-      if (p.addend) v = fmaf(p.add_scale, __ldg(p.addend + (size_t)gi * p.J + gj), v);
-      vmax = fmaxf(vmax, fabsf(v));
+  const bool vec = (p.ldo & 3) == 0 && (p.J & 3) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0 &&
+                   (MODE != FWD || (reinterpret_cast<uintptr_t>(p.b) & 15) == 0) &&
+                   (MODE != DX || ((!p.hprev || ((p.ldh & 3) == 0 && (reinterpret_cast<uintptr_t>(p.hprev) & 15) == 0)) &&
+                                   !p.addend));
+  if (vec) {
+    // float4 per lane, four independent (row, column-quad) items per thread in flight: the saved-activation reads
+    // of the DX epilogue are issued together instead of one dependent load per element
+    const int q4n = ncol >> 2, total = 128 * q4n, sh = nb == 128 ? 5 : 4;
+    constexpr int kB = 4;
+    for (int base = tid; base < total; base += kThreads * kB) {
+      float4 h[kB];
+      int gi_[kB], gj_[kB];
+      bool ok[kB];
+#pragma unroll
+      for (int bb = 0; bb < kB; bb++) {
+        const int idx = base + bb * kThreads;
+        const int r = idx >> sh, c4 = (idx & (q4n - 1)) << 2;
+        gi_[bb] = i0 + r; gj_[bb] = j0 + c4;
+        ok[bb] = idx < total && gi_[bb] < p.I && gj_[bb] < p.J;
+        h[bb] = make_float4(1.f, 1.f, 1.f, 1.f);
+        if (ok[bb]) {
+          if (MODE == DX && p.hprev) h[bb] = __ldg(reinterpret_cast<const float4*>(p.hprev + (size_t)gi_[bb] * p.ldh + gj_[bb]));
+          if (MODE == FWD) h[bb] = __ldg(reinterpret_cast<const float4*>(p.b + gj_[bb]));
+        }
+      }
+#pragma unroll
+      for (int bb = 0; bb < kB; bb++) {
+        if (!ok[bb]) continue;
+        const int idx = base + bb * kThreads;
+        const int r = idx >> sh, c4 = (idx & (q4n - 1)) << 2;
+        float4 v = nchunks > 0 ? *reinterpret_cast<const float4*>(tile + r * kLd + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (MODE == FWD) {
+          v.x = act_fwd(v.x + h[bb].x, p.act); v.y = act_fwd(v.y + h[bb].y, p.act);
+          v.z = act_fwd(v.z + h[bb].z, p.act); v.w = act_fwd(v.w + h[bb].w, p.act);
+        } else if (MODE == DX) {
+          if (p.hprev) {
+            v.x *= act_bwd(h[bb].x, p.act_prev); v.y *= act_bwd(h[bb].y, p.act_prev);
+            v.z *= act_bwd(h[bb].z, p.act_prev); v.w *= act_bwd(h[bb].w, p.act_prev);
+          }
+          vmax = fmaxf(vmax, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+        }
+        *reinterpret_cast<float4*>(out + (size_t)gi_[bb] * p.ldo + gj_[bb]) = v;
+      }
     }
-    out[(size_t)gi * p.ldo + gj] = v;
+  } else {
+    for (int idx = tid; idx < 128 * ncol; idx += kThreads) {
+      const int r = nb == 128 ? idx >> 7 : idx >> 6, cidx = idx & (ncol - 1);
+      const int gi = i0 + r, gj = j0 + cidx;
+      if (gi >= p.I || gj >= p.J) continue;
+      float v = nchunks > 0 ? tile[r * kLd + cidx] : 0.f;
+      if (MODE == FWD) {
+        v = act_fwd(v + __ldg(p.b + gj), p.act);
+      } else if (MODE == DX) {
+        if (p.hprev) v *= act_bwd(__ldg(p.hprev + (size_t)gi * p.ldh + gj), p.act_prev);
+        if (p.addend) v = fmaf(p.add_scale, __ldg(p.addend + (size_t)gi * p.J + gj), v);
+        vmax = fmaxf(vmax, fabsf(v));
+      }
+      out[(size_t)gi * p.ldo + gj] = v;
+    }
   }
   if (MODE == DX && p.amax_out) {
     for (int o = 16; o; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
