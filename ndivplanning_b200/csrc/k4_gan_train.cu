@@ -64,6 +64,8 @@ struct GemmP {
   const unsigned* amax_in;   // tensor path: max |dP| of the A operand (bits of a non-negative float), NULL = unscaled
   unsigned* amax_out;        // DX: max |output| is accumulated here (atomicMax on the float bits), may be NULL
   int use_tc;
+  const uint8_t* b_img;      // tensor path, FWD / DX: pre-split weight image (pack_weights_kernel), NULL = split on the fly
+  int b_chunks;              // contraction chunks per 128-row tile of that image
 };
 
 __device__ __forceinline__ float act_fwd(float v, int act) {
@@ -300,8 +302,9 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
   uint8_t* sbar = tc_smem + kTcBuf + 1024;
   const uint32_t bar0 = smem_u32(sbar);                                        // bar_done[2]
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sbar + 32);
+  const uint32_t barf = bar0 + 16;                                             // bar_full[2]: weight image landed
   if (tid == 0) {
-    mbar_init(bar0, 1); mbar_init(bar0 + 8, 1);
+    mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); mbar_init(barf, 1); mbar_init(barf + 8, 1);
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc128(smem_u32((const void*)tmem_slot));
@@ -320,6 +323,9 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
   // unit maps.  C: source contiguous along the contraction -> quarter-warps own 8 consecutive rows of one 8-group
   // (conflict-free 16 B stores).  R: source contiguous along the operand rows -> a warp owns 32 consecutive rows.
   constexpr bool A_C = MODE != DW, B_C = MODE == FWD;
+  // FWD / DX: the B operand is a weight matrix, identical for every block -> split once per optimiser step by
+  // pack_weights_kernel and bulk-copied (TMA engine) as a ready 16 KB hi|lo image per chunk
+  const bool bimg = MODE != DW && p.b_img != nullptr;
   float va[kTcU][8], vb[kTcU][8];
   float bsum = 0.f;
   auto unit = [&](bool cmap, int q, int& r, int& g) {
@@ -345,6 +351,7 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
         for (int e = 0; e < 8; e++) va[q][e] = c + e < c_end ? __ldg(p.dP + (size_t)(c + e) * p.ldp + gi) : 0.f;
       }
     }
+    if (!bimg)
 #pragma unroll
     for (int q = 0; q < kTcU; q++) {
       int r, g;
@@ -370,6 +377,10 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
     const int st = n & 1;
     uint8_t* stage = tc_smem + st * kTcStage;
     if (n >= 2) mbar_wait(bar0 + 8 * st, ((n >> 1) - 1) & 1);      // MMAs of chunk n-2 have consumed this buffer
+    if (bimg && tid == 0) {
+      mbar_expect_tx(barf + 8 * st, kTcOp);
+      bulk_g2s(smem_u32(stage + kTcOp), p.b_img + ((size_t)blockIdx.y * p.b_chunks + n) * kTcOp, kTcOp, barf + 8 * st);
+    }
 #pragma unroll
     for (int q = 0; q < kTcU; q++) {
       int r, g;
@@ -379,13 +390,16 @@ __global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
 #pragma unroll
         for (int e = 0; e < 8; e++) bsum += va[q][e];
       }
-      unit(B_C, q, r, g);
-      store_unit(stage + kTcOp, r, g, vb[q], b_scale);
+      if (!bimg) {
+        unit(B_C, q, r, g);
+        store_unit(stage + kTcOp, r, g, vb[q], b_scale);
+      }
     }
     fence_proxy_async();
     if (n + 1 < nchunks) fetch(n + 1);                               // in flight across the barrier and the MMAs
     __syncthreads();
     if (tid == 0) {
+      if (bimg) mbar_wait(barf + 8 * st, (n >> 1) & 1);
       fence_after_sync();
       const uint32_t a_hi = smem_u32(stage), a_lo = a_hi + kTcHalf, b_hi = a_hi + kTcOp, b_lo = b_hi + kTcHalf;
       const int rem = c_end - (c_begin + n * kTcK);
@@ -619,22 +633,85 @@ __global__ void __launch_bounds__(256) reduce_parts_kernel(const float* __restri
   grad[i] = g;
 }
 
-// ---- network description: flat parameter buffer [W0 | b0 | W1 | b1 | ...], torch [out,in] weights
+// ---- network description: flat parameter buffer [W0 | b0 | W1 | b1 | ...], torch [out,in] weights; weight images
+// of the tensor path: per layer a FWD image (operand rows = out features, contraction = in) and a DX image (rows =
+// in features, contraction = out), each [row tile][chunk][hi 8 KB | lo 8 KB], values x 2^8
 struct Net {
   int L;
   int in[5], out[5];
   size_t w_off[5], b_off[5];
   size_t P;
+  size_t fwd_off[5], dx_off[5];     // byte offsets into img; (size_t)-1 = layer stays on the exact kernel
+  int fwd_chunks[5], dx_chunks[5];
+  size_t img_bytes;
+  uint8_t* img;
   void init(int L_, const int* in_, const int* out_) {
     L = L_;
     P = 0;
+    img_bytes = 0;
+    img = nullptr;
     for (int l = 0; l < L; l++) {
       in[l] = in_[l]; out[l] = out_[l];
       w_off[l] = P; P += (size_t)in[l] * out[l];
       b_off[l] = P; P += out[l];
+      const bool wide = in[l] >= 64 && out[l] >= 64;
+      fwd_chunks[l] = (in[l] + kTcK - 1) / kTcK;
+      dx_chunks[l] = (out[l] + kTcK - 1) / kTcK;
+      fwd_off[l] = dx_off[l] = (size_t)-1;
+      if (wide) {
+        fwd_off[l] = img_bytes; img_bytes += (size_t)((out[l] + 127) / 128) * fwd_chunks[l] * kTcOp;
+        dx_off[l] = img_bytes; img_bytes += (size_t)((in[l] + 127) / 128) * dx_chunks[l] * kTcOp;
+      }
     }
   }
 };
+
+struct PackDesc {
+  int L;
+  int in[5], out[5];
+  size_t w_off[5], fwd_off[5], dx_off[5];
+};
+// grid (units / 256, 2 * L): blockIdx.y = 2 * layer + kind (0 FWD image, 1 DX image); one (row, 8-group) unit per
+// thread, lanes along the operand rows
+__global__ void __launch_bounds__(256) pack_weights_kernel(const float* __restrict__ params, uint8_t* __restrict__ img,
+                                                           const PackDesc d) {
+  const int l = blockIdx.y >> 1, kind = blockIdx.y & 1;
+  const size_t off = kind ? d.dx_off[l] : d.fwd_off[l];
+  if (off == (size_t)-1) return;
+  const int R = kind ? d.in[l] : d.out[l], K = kind ? d.out[l] : d.in[l];
+  const int chunks = (K + kTcK - 1) / kTcK, rtiles = (R + 127) / 128;
+  const int u = blockIdx.x * 256 + threadIdx.x;
+  const int per_tile = 128 * (kTcK / 8);
+  if (u >= rtiles * chunks * per_tile) return;
+  const int tile = u / per_tile, w = u % per_tile;
+  const int r = w & 127, g = w >> 7;
+  const int rt = tile / chunks, ch = tile % chunks;
+  const int gr = rt * 128 + r, k0 = ch * kTcK + g * 8;
+  const float* W = params + d.w_off[l];
+  float v[8];
+#pragma unroll
+  for (int e = 0; e < 8; e++) {
+    const int k = k0 + e;
+    v[e] = (gr < R && k < K) ? (kind ? W[(size_t)k * d.in[l] + gr] : W[(size_t)gr * d.in[l] + k]) : 0.f;
+  }
+  store_unit(img + off + (size_t)tile * kTcOp, r, g, v, kUnitScale);
+}
+static int pack_weights(const Net& n, const float* params, cudaStream_t s) {
+  if (!n.img || !n.img_bytes) return NDP_OK;
+  PackDesc d;
+  d.L = n.L;
+  int max_units = 0;
+  for (int l = 0; l < n.L; l++) {
+    d.in[l] = n.in[l]; d.out[l] = n.out[l]; d.w_off[l] = n.w_off[l]; d.fwd_off[l] = n.fwd_off[l]; d.dx_off[l] = n.dx_off[l];
+    const int uf = ((n.out[l] + 127) / 128) * n.fwd_chunks[l] * 128 * (kTcK / 8);
+    const int ud = ((n.in[l] + 127) / 128) * n.dx_chunks[l] * 128 * (kTcK / 8);
+    max_units = max_units > uf ? max_units : uf;
+    max_units = max_units > ud ? max_units : ud;
+  }
+  pack_weights_kernel<<<dim3((max_units + 255) / 256, 2 * n.L), 256, 0, s>>>(params, n.img, d);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}
 
 constexpr int kMaxSplits = 128;
 // batch rows -> partial slots of the weight-gradient products: 64-row slots while the batch is small (the step is
@@ -663,6 +740,7 @@ static int mlp_forward(const Net& n, const float* params, const RowSrc& x0, int 
     p.act = l + 1 < n.L ? act : ACT_NONE;
     p.out = acts[l]; p.ldo = n.out[l];
     p.use_tc = use_tc;
+    if (n.img && n.fwd_off[l] != (size_t)-1) { p.b_img = n.img + n.fwd_off[l]; p.b_chunks = n.fwd_chunks[l]; }
     int rc = launch_gemm<FWD>(p, 1, s);
     if (rc) return rc;
   }
@@ -705,6 +783,7 @@ static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int
         slot = amax + (*amax_used)++;
         p.amax_out = slot;
         p.J = n.in[l]; p.wk0 = 0;
+        if (n.img && n.dx_off[l] != (size_t)-1) { p.b_img = n.img + n.dx_off[l]; p.b_chunks = n.dx_chunks[l]; }
         p.hprev = acts[l - 1]; p.ldh = n.in[l]; p.act_prev = act;
         p.out = nxt; p.ldo = n.in[l];
       } else {
@@ -802,6 +881,7 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   const size_t o_sx = carve(off, B * 4), o_sz = carve(off, B * 4);
   const size_t o_gpart = carve(off, (size_t)kMaxSplits * PG * 4), o_dpart = carve(off, (size_t)2 * kMaxSplits * PD * 4);
   const size_t o_ws = carve(off, ndiv_bytes);
+  const size_t o_gimg = carve(off, g->G.img_bytes), o_dimg = carve(off, g->D.img_bytes);
   cudaError_t e = cudaMalloc(&g->arena, off);
   if (e != cudaSuccess) {
     set_error("ndp_gan_create: cudaMalloc(%zu) failed: %s", off, cudaGetErrorString(e));
@@ -821,6 +901,10 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   g->sx = (float*)(base + o_sx); g->sz = (float*)(base + o_sz);
   g->g_part = (float*)(base + o_gpart); g->d_part = (float*)(base + o_dpart);
   g->ndiv_ws = base + o_ws;
+  if (g->use_tc) {
+    g->G.img = (uint8_t*)(base + o_gimg);
+    g->D.img = (uint8_t*)(base + o_dimg);
+  }
   *out = g;
   return NDP_OK;
 }
@@ -849,6 +933,8 @@ int ndp_gan_load(ndp_gan* g, const float* const* gW, const float* const* gb, con
   NDP_CUDA(cudaMemsetAsync(g->steps, 0, 2 * sizeof(int), s));
   set_hp_kernel<<<1, 1, 0, s>>>(g->hp, g->d.lr, g->d.beta1, g->d.beta2, g->d.eps, 15);
   NDP_LAUNCH_CHECK();
+  if (int rc = pack_weights(g->G, g->gp, s)) return rc;
+  if (int rc = pack_weights(g->D, g->dp, s)) return rc;
   return NDP_OK;
 }
 
@@ -939,6 +1025,7 @@ static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* c
     NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, g->d_part, sr,
                          nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
     NDP_TRY(adam(g->dp, g->dm, g->dv, g->dg, g->d_part, sr + sf, g->D.P, g->hp, g->steps + 0, comm, s));
+    NDP_TRY(pack_weights(g->D, g->dp, s));         // images always follow the parameters (F may change per call)
   }
   // generator loss through the UPDATED discriminator                            (:187-190)
   NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
@@ -954,6 +1041,7 @@ static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* c
   NDP_TRY(mlp_backward(g->G, g->gp, xg, B, g->g_act, g->da, g->bufA, g->bufB, ACT_RELU, g->g_part, 0, nullptr, 0, 0,
                        nullptr, 0.f, tc, g->amax, &used, s));
   NDP_TRY(adam(g->gp, g->gm, g->gv, g->gg, g->g_part, sf, g->G.P, g->hp, g->steps + 1, comm, s));   // :198-203
+  NDP_TRY(pack_weights(g->G, g->gp, s));
   if (comm) NDP_TRY(ndp_comm_allreduce_sum_f32(comm, losses, 3, s));   // partial means / partial ndiv sum -> global
 #undef NDP_TRY
   return NDP_OK;
