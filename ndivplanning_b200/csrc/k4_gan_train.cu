@@ -288,7 +288,7 @@ __device__ __forceinline__ void store_unit(uint8_t* op, int r, int g, const floa
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, 2) gemm_tc_kernel(const GemmP p) {
+__global__ void __launch_bounds__(kThreads, 3) gemm_tc_kernel(const GemmP p) {
   extern __shared__ __align__(128) uint8_t tc_smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int i0 = blockIdx.x * 128, j0 = blockIdx.y * 128;
@@ -532,6 +532,86 @@ static int launch_gemm_tc(const GemmP& p, int splits, cudaStream_t s) {
   return NDP_OK;
 }
 
+// ---- thin layers at large batch (fc5: 256 -> 4 actions, the logit: 256 -> 1): bandwidth-bound row sweeps -----------
+// FWD, J <= 8: one warp per row, lanes along the contraction, W in shared memory
+__global__ void __launch_bounds__(256) thin_fwd_kernel(const GemmP p) {
+  extern __shared__ float thin_w[];                 // [J][Cn]
+  const int J = p.J, K = p.Cn;
+  for (int e = threadIdx.x; e < J * K; e += 256) thin_w[e] = __ldg(p.W + (size_t)(e / K) * p.ldw + e % K);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int m = blockIdx.x * 8 + warp; m < p.I; m += gridDim.x * 8) {
+    const float* xr = p.x.p0 + (size_t)m * p.x.ld0;
+    float acc[8];
+#pragma unroll
+    for (int n = 0; n < 8; n++) acc[n] = 0.f;
+    for (int k = lane; k < K; k += 32) {
+      const float xv = __ldg(xr + k);
+#pragma unroll
+      for (int n = 0; n < 8; n++)
+        if (n < J) acc[n] = fmaf(xv, thin_w[n * K + k], acc[n]);
+    }
+#pragma unroll
+    for (int n = 0; n < 8; n++) {
+      if (n >= J) break;
+      float v = acc[n];
+      for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) p.out[(size_t)m * p.ldo + n] = act_fwd(v + __ldg(p.b + n), p.act);
+    }
+  }
+}
+// DW, I <= 8 output features: a warp sweeps rows of the split (8 warps -> 8 rows in flight, coalesced reads of X, the
+// I gradient values of the row broadcast), lanes own 8 of the block's 256 input columns; the warps' partial sums are
+// added in warp order (deterministic)
+__global__ void __launch_bounds__(256) thin_dw_kernel(const GemmP p) {
+  __shared__ float tile[8][256];
+  __shared__ float sb[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k0 = blockIdx.x * 256;
+  const int c_begin = blockIdx.z * p.rows_per_split, c_end = min(p.Cn, c_begin + p.rows_per_split);
+  float acc[8][8], bs[8];
+#pragma unroll
+  for (int n = 0; n < 8; n++) {
+    bs[n] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[n][j] = 0.f;
+  }
+#pragma unroll 2
+  for (int m = c_begin + warp; m < c_end; m += 8) {
+    const float* xr = p.x.p0 + (size_t)m * p.x.ld0 + k0;
+    float xv[8], d[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) xv[j] = (k0 + lane + 32 * j) < p.J ? __ldg(xr + lane + 32 * j) : 0.f;
+#pragma unroll
+    for (int n = 0; n < 8; n++) d[n] = n < p.I ? __ldg(p.dP + (size_t)m * p.ldp + n) : 0.f;
+#pragma unroll
+    for (int n = 0; n < 8; n++) {
+      bs[n] += d[n];
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[n][j] = fmaf(d[n], xv[j], acc[n][j]);
+    }
+  }
+  for (int w = 0; w < 8; w++) {
+    if (warp == w) {
+#pragma unroll
+      for (int n = 0; n < 8; n++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+          if (w == 0) tile[n][lane + 32 * j] = acc[n][j]; else tile[n][lane + 32 * j] += acc[n][j];
+        }
+        if (lane == 0) { if (w == 0) sb[n] = bs[n]; else sb[n] += bs[n]; }
+      }
+    }
+    __syncthreads();
+  }
+  float* out = p.out + (size_t)blockIdx.z * p.split_stride;
+  for (int e = threadIdx.x; e < p.I * 256; e += 256) {
+    const int n = e >> 8, k = k0 + (e & 255);
+    if (k < p.J) out[(size_t)n * p.ldo + k] = tile[n][e & 255];
+  }
+  if (blockIdx.x == 0 && threadIdx.x < p.I) p.db_out[(size_t)blockIdx.z * p.split_stride + threadIdx.x] = sb[threadIdx.x];
+}
+
 // 64-row tiles when they fill the GPU, 16-row tiles (4x the blocks, a quarter of the serial work each) otherwise:
 // at the reference's batch (336 rows) a layer is a handful of 64x64 tiles and the step is latency-bound.
 template <int MODE>
@@ -540,6 +620,18 @@ static int launch_gemm(const GemmP& p, int splits, cudaStream_t s) {
   const bool tc = p.use_tc && p.J >= 64 && p.Cn >= 64 &&
                   (MODE == DW ? (p.I >= 64 && p.Cn >= 2048 && p.rows_per_split % kTcK == 0) : p.I >= 2048);
   if (tc) return launch_gemm_tc<MODE>(p, splits, s);
+  const bool plain_x = p.x.k1 == 0 && p.x.div0 == 1;
+  if (MODE == FWD && p.J <= 8 && p.I >= 2048 && plain_x && (size_t)p.J * p.Cn * 4 <= 40960) {
+    const int blocks = (p.I + 7) / 8 < 8 * num_sms_cached() ? (p.I + 7) / 8 : 8 * num_sms_cached();
+    thin_fwd_kernel<<<blocks, 256, (size_t)p.J * p.Cn * 4, s>>>(p);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
+  if (MODE == DW && p.I <= 8 && p.Cn >= 2048 && plain_x) {
+    thin_dw_kernel<<<dim3((p.J + 255) / 256, 1, splits), 256, 0, s>>>(p);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
   const dim3 block(kThreads);
   const int tj = p.J >= 64 ? 64 : 16;
   const long long big_tiles = (long long)((p.I + 63) / 64) * ((p.J + tj - 1) / tj) * splits;
@@ -561,11 +653,14 @@ static int launch_gemm(const GemmP& p, int splits, cudaStream_t s) {
 // nn.BCEWithLogitsLoss: l = (1-y) x + max(-x,0) + log(exp(-max(-x,0)) + exp(-x-max(-x,0))) = (1-y) x + softplus(-x).
 // One block: the reduction order is fixed.  Also advances the Adam step counter of the optimiser that consumes
 // these gradients (each optimiser step in train_gan.py is preceded by exactly one loss evaluation).
+constexpr int kBceBlocks = 64;
 __global__ void __launch_bounds__(1024) bce_kernel(const float* __restrict__ x0, int n0, float y0,
                                                     float* __restrict__ dl0, const float* __restrict__ x1, int n1,
                                                     float y1, float* __restrict__ dl1, float* __restrict__ loss_out,
-                                                    int* __restrict__ step_counter, float world) {
+                                                    int* __restrict__ step_counter, float world,
+                                                    float* __restrict__ partial, unsigned* __restrict__ ticket) {
   __shared__ float red[32];
+  __shared__ bool last;
   float tot = 0.f;
   for (int set = 0; set < 2; set++) {
     const float* x = set ? x1 : x0;
@@ -575,7 +670,7 @@ __global__ void __launch_bounds__(1024) bce_kernel(const float* __restrict__ x0,
     if (n <= 0) continue;
     const float inv = 1.f / ((float)n * world);   // data parallel: mean over the GLOBAL batch (equal shards)
     float s = 0.f;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
       const float v = x[i];
       const float e = expf(-fabsf(v));
       s += (1.f - y) * v + fmaxf(-v, 0.f) + log1pf(e);
@@ -591,9 +686,19 @@ __global__ void __launch_bounds__(1024) bce_kernel(const float* __restrict__ x0,
     float v = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
     for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     if (threadIdx.x == 0) {
-      *loss_out = v;
-      *step_counter += 1;
+      partial[blockIdx.x] = v;
+      __threadfence();
+      last = atomicAdd(ticket, 1u) == gridDim.x - 1;
     }
+  }
+  __syncthreads();
+  if (last && threadIdx.x == 0) {           // fixed-order sum of the block partials: deterministic
+    __threadfence();
+    float v = 0.f;
+    for (int i = 0; i < (int)gridDim.x; i++) v += __ldcg(partial + i);
+    *loss_out = v;
+    *step_counter += 1;
+    *ticket = 0;
   }
 }
 
@@ -823,6 +928,8 @@ struct ndp_gan {
   float* dr_act[4];  // discriminator on the F distinct real rows
   float* df_act[4];  // discriminator on the B generated rows
   float *dl_real, *dl_fake, *bufA, *bufB, *g_div, *da, *sx, *sz;
+  float* bce_part;       // [kBceBlocks] block partials of the loss mean
+  unsigned* bce_ticket;  // last-block ticket (self-resetting)
   float *g_part, *d_part;
   void* ndiv_ws;
   size_t ndiv_ws_bytes;
@@ -876,6 +983,7 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   for (int l = 0; l < 4; l++) o_dr[l] = carve(off, F * dout[l] * 4);
   for (int l = 0; l < 4; l++) o_df[l] = carve(off, B * dout[l] * 4);
   const size_t o_dlr = carve(off, F * 4), o_dlf = carve(off, B * 4);
+  const size_t o_bcep = carve(off, kBceBlocks * 4), o_bcet = carve(off, 4);
   const size_t o_bA = carve(off, B * 256 * 4), o_bB = carve(off, B * 256 * 4);
   const size_t o_gdiv = carve(off, B * d->A * 4), o_da = carve(off, B * d->A * 4);
   const size_t o_sx = carve(off, B * 4), o_sz = carve(off, B * 4);
@@ -896,6 +1004,8 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   for (int l = 0; l < 5; l++) g->g_act[l] = (float*)(base + o_g[l]);
   for (int l = 0; l < 4; l++) { g->dr_act[l] = (float*)(base + o_dr[l]); g->df_act[l] = (float*)(base + o_df[l]); }
   g->dl_real = (float*)(base + o_dlr); g->dl_fake = (float*)(base + o_dlf);
+  g->bce_part = (float*)(base + o_bcep); g->bce_ticket = (unsigned*)(base + o_bcet);
+  cudaMemset(g->bce_ticket, 0, 4);
   g->bufA = (float*)(base + o_bA); g->bufB = (float*)(base + o_bB);
   g->g_div = (float*)(base + o_gdiv); g->da = (float*)(base + o_da);
   g->sx = (float*)(base + o_sx); g->sz = (float*)(base + o_sz);
@@ -1003,6 +1113,7 @@ static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* c
   const int S = g->d.S, C = g->d.C, A = g->d.A, nd = g->d.nd, B = F * S;
   int rc, used = 0;
   const int tc = g->use_tc;
+  const int bce_blocks = B <= 1024 ? 1 : (B / 1024 < kBceBlocks ? B / 1024 : kBceBlocks);
   NDP_CUDA(cudaMemsetAsync(g->amax, 0, (size_t)g->n_amax * sizeof(unsigned), s));
 #define NDP_TRY(x) do { rc = (x); if (rc) return rc; } while (0)
   // generator forward on [codes repeated S times | noise]                      (train_gan.py:159-165)
@@ -1017,8 +1128,8 @@ static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* c
   for (int it = 0; it < g->d.d_steps; it++) {                    // :172-184
     NDP_TRY(mlp_forward(g->D, g->dp, x_real, F, g->dr_act, ACT_LEAKY, tc, s));
     NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
-    bce_kernel<<<1, 1024, 0, s>>>(g->dr_act[3], F, 1.f, g->dl_real, g->df_act[3], B, 0.f, g->dl_fake, losses + 0,
-                                  g->steps + 0, (float)world);
+    bce_kernel<<<bce_blocks, 1024, 0, s>>>(g->dr_act[3], F, 1.f, g->dl_real, g->df_act[3], B, 0.f, g->dl_fake,
+                                           losses + 0, g->steps + 0, (float)world, g->bce_part, g->bce_ticket);
     NDP_LAUNCH_CHECK();
     NDP_TRY(mlp_backward(g->D, g->dp, x_real, F, g->dr_act, g->dl_real, g->bufA, g->bufB, ACT_LEAKY, g->d_part, 0,
                          nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
@@ -1029,8 +1140,8 @@ static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* c
   }
   // generator loss through the UPDATED discriminator                            (:187-190)
   NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
-  bce_kernel<<<1, 1024, 0, s>>>(g->df_act[3], B, 1.f, g->dl_fake, nullptr, 0, 0.f, nullptr, losses + 1, g->steps + 1,
-                                (float)world);
+  bce_kernel<<<bce_blocks, 1024, 0, s>>>(g->df_act[3], B, 1.f, g->dl_fake, nullptr, 0, 0.f, nullptr, losses + 1,
+                                         g->steps + 1, (float)world, g->bce_part, g->bce_ticket);
   NDP_LAUNCH_CHECK();
   // normalized diversification of the S samples of every code                   (:193-196)
   NDP_TRY(ndp_ndiv_forward_backward(a_hat, noise, F, S, A, nd, g->d.margin, g->sx, g->sz, losses + 2, g->g_div,
