@@ -852,19 +852,36 @@ static int mlp_forward(const Net& n, const float* params, const RowSrc& x0, int 
   return NDP_OK;
 }
 
+// event pool for the fork/join edges between the step's streams (record + wait pairs; reused round-robin)
+struct EvPool {
+  cudaEvent_t e[64];
+  int n;
+};
+static int hop(EvPool& ev, cudaStream_t from, cudaStream_t to) {   // `to` continues after everything queued on `from`
+  if (from == to) return NDP_OK;
+  cudaEvent_t e = ev.e[ev.n++ & 63];
+  NDP_CUDA(cudaEventRecord(e, from));
+  NDP_CUDA(cudaStreamWaitEvent(to, e, 0));
+  return NDP_OK;
+}
+
 // d_out = d loss / d (last layer output) [M x out[L-1]].  part != NULL: weight/bias gradient partials into slots
 // [slot0, slot0+splits) of part (slot stride n.P).  dx0 != NULL: d loss / d input columns [col0, col0+ncols) of
-// layer 0 (+ add_scale * addend).  bufA/bufB: [M x max hidden width] ping-pong scratch.
+// layer 0 (+ add_scale * addend).  dbuf[l]: d loss / d (output of layer l), l < L-1 (one buffer per layer, so the
+// weight-gradient products may trail the dX chain on another stream).  The dX chain runs on s, the dW products on
+// s_dw (== s: everything in order on one stream); the caller joins s_dw before it consumes the partials.
 static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int M, float* const* acts,
-                        const float* d_out, float* bufA, float* bufB, int act, float* part, int slot0,
+                        const float* d_out, float* const* dbuf, int act, float* part, int slot0,
                         float* dx0, int col0, int ncols, const float* addend, float add_scale, int use_tc,
-                        unsigned* amax, int* amax_used, cudaStream_t s) {
+                        unsigned* amax, int* amax_used, cudaStream_t s, cudaStream_t s_dw, EvPool& ev) {
   int splits, rps;
   split_plan(M, &splits, &rps);
-  const float* cur = d_out;
-  float* nxt = bufA;
   const unsigned* cur_amax = nullptr;     // d_out feeds thin (FFMA) products only; every dP made here gets a slot
+  const bool side = part && s_dw != s;
+  if (side)
+    if (int rc = hop(ev, s, s_dw)) return rc;       // d_out and the saved activations are ready
   for (int l = n.L - 1; l >= 0; l--) {
+    const float* cur = l == n.L - 1 ? d_out : dbuf[l];
     if (part) {
       GemmP p = {};
       p.I = n.out[l]; p.J = n.in[l]; p.Cn = M;
@@ -874,7 +891,7 @@ static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int
       p.db_out = part + (size_t)slot0 * n.P + n.b_off[l];
       p.rows_per_split = rps; p.split_stride = n.P;
       p.use_tc = use_tc; p.amax_in = cur_amax;
-      int rc = launch_gemm<DW>(p, splits, s);
+      int rc = launch_gemm<DW>(p, splits, s_dw);
       if (rc) return rc;
     }
     if (l > 0 || dx0) {
@@ -890,7 +907,7 @@ static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int
         p.J = n.in[l]; p.wk0 = 0;
         if (n.img && n.dx_off[l] != (size_t)-1) { p.b_img = n.img + n.dx_off[l]; p.b_chunks = n.dx_chunks[l]; }
         p.hprev = acts[l - 1]; p.ldh = n.in[l]; p.act_prev = act;
-        p.out = nxt; p.ldo = n.in[l];
+        p.out = dbuf[l - 1]; p.ldo = n.in[l];
       } else {
         p.J = ncols; p.wk0 = col0;
         p.addend = addend; p.add_scale = add_scale;
@@ -898,9 +915,9 @@ static int mlp_backward(const Net& n, const float* params, const RowSrc& x0, int
       }
       int rc = launch_gemm<DX>(p, 1, s);
       if (rc) return rc;
-      cur = nxt;
       cur_amax = slot;
-      nxt = (nxt == bufA) ? bufB : bufA;
+      if (side && l > 0)
+        if (int rc2 = hop(ev, s, s_dw)) return rc2;   // dP of layer l-1 is ready for its dW product
     }
   }
   return NDP_OK;
@@ -927,7 +944,13 @@ struct ndp_gan {
   float* g_act[5];   // generator layer outputs, B rows; g_act[4] = a_hat
   float* dr_act[4];  // discriminator on the F distinct real rows
   float* df_act[4];  // discriminator on the B generated rows
-  float *dl_real, *dl_fake, *bufA, *bufB, *g_div, *da, *sx, *sz;
+  float *dl_real, *dl_fake, *g_div, *da, *sx, *sz;
+  float* gd[4];      // d loss / d (generator layer l output), B rows
+  float* fd[3];      // the same for the discriminator on the generated rows
+  float* rd[3];      // ... and on the real rows (F rows)
+  cudaStream_t s_real, s_dw, s_nd;   // side streams of the small-batch schedule (real branch, dW products, ndiv)
+  EvPool ev;
+  int multi_stream;
   float* bce_part;       // [kBceBlocks] block partials of the loss mean
   unsigned* bce_ticket;  // last-block ticket (self-resetting)
   float *g_part, *d_part;
@@ -984,7 +1007,9 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   for (int l = 0; l < 4; l++) o_df[l] = carve(off, B * dout[l] * 4);
   const size_t o_dlr = carve(off, F * 4), o_dlf = carve(off, B * 4);
   const size_t o_bcep = carve(off, kBceBlocks * 4), o_bcet = carve(off, 4);
-  const size_t o_bA = carve(off, B * 256 * 4), o_bB = carve(off, B * 256 * 4);
+  size_t o_gd[4], o_fd[3], o_rd[3];
+  for (int l = 0; l < 4; l++) o_gd[l] = carve(off, B * gout[l] * 4);
+  for (int l = 0; l < 3; l++) { o_fd[l] = carve(off, B * dout[l] * 4); o_rd[l] = carve(off, F * dout[l] * 4); }
   const size_t o_gdiv = carve(off, B * d->A * 4), o_da = carve(off, B * d->A * 4);
   const size_t o_sx = carve(off, B * 4), o_sz = carve(off, B * 4);
   const size_t o_gpart = carve(off, (size_t)kMaxSplits * PG * 4), o_dpart = carve(off, (size_t)2 * kMaxSplits * PD * 4);
@@ -1006,7 +1031,15 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   g->dl_real = (float*)(base + o_dlr); g->dl_fake = (float*)(base + o_dlf);
   g->bce_part = (float*)(base + o_bcep); g->bce_ticket = (unsigned*)(base + o_bcet);
   cudaMemset(g->bce_ticket, 0, 4);
-  g->bufA = (float*)(base + o_bA); g->bufB = (float*)(base + o_bB);
+  for (int l = 0; l < 4; l++) g->gd[l] = (float*)(base + o_gd[l]);
+  for (int l = 0; l < 3; l++) { g->fd[l] = (float*)(base + o_fd[l]); g->rd[l] = (float*)(base + o_rd[l]); }
+  const char* ss = getenv("NDP_GAN_SINGLE_STREAM");
+  g->multi_stream = !(ss && ss[0] == '1');
+  cudaStreamCreateWithFlags(&g->s_real, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&g->s_dw, cudaStreamNonBlocking);
+  cudaStreamCreateWithFlags(&g->s_nd, cudaStreamNonBlocking);
+  for (int i = 0; i < 64; i++) cudaEventCreateWithFlags(&g->ev.e[i], cudaEventDisableTiming);
+  g->ev.n = 0;
   g->g_div = (float*)(base + o_gdiv); g->da = (float*)(base + o_da);
   g->sx = (float*)(base + o_sx); g->sz = (float*)(base + o_sz);
   g->g_part = (float*)(base + o_gpart); g->d_part = (float*)(base + o_dpart);
@@ -1021,6 +1054,8 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
 
 void ndp_gan_destroy(ndp_gan* g) {
   if (!g) return;
+  cudaStreamDestroy(g->s_real); cudaStreamDestroy(g->s_dw); cudaStreamDestroy(g->s_nd);
+  for (int i = 0; i < 64; i++) cudaEventDestroy(g->ev.e[i]);
   cudaFree(g->arena);
   delete g;
 }
@@ -1125,16 +1160,32 @@ static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* c
   int sr, sf, rps;
   split_plan(F, &sr, &rps);
   split_plan(B, &sf, &rps);
+  // Small batches are latency-bound (every kernel is a handful of blocks), so independent work runs side by side:
+  // the real-row branch of the discriminator, the weight-gradient products (off the dX chain) and the ndiv loss each
+  // get a side stream, forked from and joined into the caller's stream with events (capturable in a CUDA graph).
+  // Large batches fill the GPU kernel by kernel and stay on one stream.
+  const bool ms = g->multi_stream && B <= 8192;
+  cudaStream_t s_real = ms ? g->s_real : s, s_dw = ms ? g->s_dw : s, s_nd = ms ? g->s_nd : s;
+  EvPool& ev = g->ev;
+  // normalized diversification of the S samples of every code                   (:193-196)
+  NDP_TRY(hop(ev, s, s_nd));
+  NDP_TRY(ndp_ndiv_forward_backward(a_hat, noise, F, S, A, nd, g->d.margin, g->sx, g->sz, losses + 2, g->g_div,
+                                    g->ndiv_ws, g->ndiv_ws_bytes, (void*)s_nd));
   for (int it = 0; it < g->d.d_steps; it++) {                    // :172-184
-    NDP_TRY(mlp_forward(g->D, g->dp, x_real, F, g->dr_act, ACT_LEAKY, tc, s));
+    NDP_TRY(hop(ev, s, s_real));
+    NDP_TRY(mlp_forward(g->D, g->dp, x_real, F, g->dr_act, ACT_LEAKY, tc, s_real));
     NDP_TRY(mlp_forward(g->D, g->dp, x_fake, B, g->df_act, ACT_LEAKY, tc, s));
+    NDP_TRY(hop(ev, s_real, s));
     bce_kernel<<<bce_blocks, 1024, 0, s>>>(g->dr_act[3], F, 1.f, g->dl_real, g->df_act[3], B, 0.f, g->dl_fake,
                                            losses + 0, g->steps + 0, (float)world, g->bce_part, g->bce_ticket);
     NDP_LAUNCH_CHECK();
-    NDP_TRY(mlp_backward(g->D, g->dp, x_real, F, g->dr_act, g->dl_real, g->bufA, g->bufB, ACT_LEAKY, g->d_part, 0,
-                         nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
-    NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, g->d_part, sr,
-                         nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s));
+    NDP_TRY(hop(ev, s, s_real));
+    NDP_TRY(mlp_backward(g->D, g->dp, x_real, F, g->dr_act, g->dl_real, g->rd, ACT_LEAKY, g->d_part, 0,
+                         nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s_real, s_real, ev));
+    NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->fd, ACT_LEAKY, g->d_part, sr,
+                         nullptr, 0, 0, nullptr, 0.f, tc, g->amax, &used, s, s_dw, ev));
+    NDP_TRY(hop(ev, s_real, s));
+    NDP_TRY(hop(ev, s_dw, s));
     NDP_TRY(adam(g->dp, g->dm, g->dv, g->dg, g->d_part, sr + sf, g->D.P, g->hp, g->steps + 0, comm, s));
     NDP_TRY(pack_weights(g->D, g->dp, s));         // images always follow the parameters (F may change per call)
   }
@@ -1143,14 +1194,13 @@ static int train_step_impl(ndp_gan* g, ndp_comm* comm, int world, const float* c
   bce_kernel<<<bce_blocks, 1024, 0, s>>>(g->df_act[3], B, 1.f, g->dl_fake, nullptr, 0, 0.f, nullptr, losses + 1,
                                          g->steps + 1, (float)world, g->bce_part, g->bce_ticket);
   NDP_LAUNCH_CHECK();
-  // normalized diversification of the S samples of every code                   (:193-196)
-  NDP_TRY(ndp_ndiv_forward_backward(a_hat, noise, F, S, A, nd, g->d.margin, g->sx, g->sz, losses + 2, g->g_div,
-                                    g->ndiv_ws, g->ndiv_ws_bytes, stream));
+  NDP_TRY(hop(ev, s_nd, s));                                     // d div / d a_hat is needed from here on
   // d total / d a_hat = dD/da_hat (first A input columns of discriminator fc1) + div_factor * d div / d a_hat
-  NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->bufA, g->bufB, ACT_LEAKY, nullptr, 0, g->da,
-                       0, A, g->g_div, g->d.div_factor, tc, g->amax, &used, s));
-  NDP_TRY(mlp_backward(g->G, g->gp, xg, B, g->g_act, g->da, g->bufA, g->bufB, ACT_RELU, g->g_part, 0, nullptr, 0, 0,
-                       nullptr, 0.f, tc, g->amax, &used, s));
+  NDP_TRY(mlp_backward(g->D, g->dp, x_fake, B, g->df_act, g->dl_fake, g->fd, ACT_LEAKY, nullptr, 0, g->da,
+                       0, A, g->g_div, g->d.div_factor, tc, g->amax, &used, s, s, ev));
+  NDP_TRY(mlp_backward(g->G, g->gp, xg, B, g->g_act, g->da, g->gd, ACT_RELU, g->g_part, 0, nullptr, 0, 0,
+                       nullptr, 0.f, tc, g->amax, &used, s, s_dw, ev));
+  NDP_TRY(hop(ev, s_dw, s));
   NDP_TRY(adam(g->gp, g->gm, g->gv, g->gg, g->g_part, sf, g->G.P, g->hp, g->steps + 1, comm, s));   // :198-203
   NDP_TRY(pack_weights(g->G, g->gp, s));
   if (comm) NDP_TRY(ndp_comm_allreduce_sum_f32(comm, losses, 3, s));   // partial means / partial ndiv sum -> global
