@@ -89,3 +89,27 @@ class ClosedLoopSweep:
         if actions_ref is not None:
             action_err = ((actions_ref.to(dev) - actions) ** 2).mean(dim=(0, 2))                  # :178-181
         return SweepResult(actions, best_idx, states, image_err, action_err, verified, work)
+
+    def capture(self, start: torch.Tensor, goal: torch.Tensor, steps: int, state_fut: Optional[torch.Tensor] = None,
+                actions_ref: Optional[torch.Tensor] = None, noise_fn: Optional[Callable[[int, int], torch.Tensor]] = None,
+                receding: bool = True):
+        """The whole closed loop — `steps` plans, forward-model steps and error accumulations — as ONE CUDA graph
+        (SURVEY.md 8f N1).  `start`, `goal` (and `state_fut`, `actions_ref`, the tensors `noise_fn` returns) are the
+        graph's static inputs: refill them in place and `graph.replay()`; the returned SweepResult holds the static
+        outputs.  Without `noise_fn` the noise comes from the device generator inside the graph (a fresh draw per
+        replay: torch advances the Philox offset of captured generators).  One warm-up run is executed eagerly."""
+        dev = self.device
+        _lib.require_cuda(start, goal)
+        S = int(steps)
+        for s_ in range(S):                                   # weights are packed outside the capture
+            self.planner(min(self.Th, S - s_) if receding else self.Th)
+        self.run(start, goal, S, state_fut, actions_ref, noise_fn, None, receding)
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                res = self.run(start, goal, S, state_fut, actions_ref, noise_fn, None, receding)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        return g, res

@@ -312,6 +312,38 @@ def test_closed_loop_sweep_matches_oracle_loop(cuda, prec):
     assert torch.equal(r1.best_idx, r2.best_idx) and torch.equal(r1.actions, r2.actions)
 
 
+@pytest.mark.parametrize("prec", ["f16+refine", "fp32"])
+def test_closed_loop_sweep_as_one_cuda_graph(cuda, prec):
+    """the whole receding-horizon loop captured as ONE CUDA graph: replays with refilled static inputs
+    equal the eager sweep bit for bit; with the in-graph device sampler every replay draws fresh noise"""
+    from ndivplanning_b200.closed_loop import ClosedLoopSweep
+    G, K, Th, S, nd, E, H = 4, 512, 3, 4, 2, 128, 256
+    gen, fwd = synthetic.make_models(nd=nd, E=E, H=H)
+    torch.manual_seed(12)
+    start, goal = torch.randn(G, E).cuda(), torch.randn(G, E).cuda()
+    fut, aref = torch.randn(S, G, E).cuda(), torch.randn(S, G, 4).cuda()
+    noises = [torch.rand(min(Th, S - s), G, K, nd).cuda() for s in range(S)]
+    sw = ClosedLoopSweep(gen, fwd, horizon=Th, rollouts=K, precision=prec)
+    graph, res = sw.capture(start, goal, S, state_fut=fut, actions_ref=aref, noise_fn=lambda s, T: noises[s])
+    for trial in range(2):                                   # second trial: new goals and noise in the same buffers
+        if trial:
+            goal.copy_(torch.randn(G, E))
+            for n_ in noises:
+                n_.copy_(torch.rand(n_.shape))
+        graph.replay()
+        torch.cuda.synchronize()
+        got = [t.clone() for t in (res.best_idx, res.actions, res.states, res.image_err, res.action_err, res.verified)]
+        ref = sw.run(start, goal, S, state_fut=fut, actions_ref=aref, noise_fn=lambda s, T: noises[s])
+        want = (ref.best_idx, ref.actions, ref.states, ref.image_err, ref.action_err, ref.verified)
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+    g2, r2 = sw.capture(start, goal, S)                      # device sampler inside the graph
+    g2.replay(); torch.cuda.synchronize()
+    first = r2.actions.clone()
+    g2.replay(); torch.cuda.synchronize()
+    assert not torch.equal(first, r2.actions) and bool(torch.isfinite(r2.actions).all())
+
+
 def test_refine_fallback_rerolls_unverified_goals(cuda):
     """Goals whose refined selection cannot be proven exact (costs too close: short horizon, weak separation)
     are re-rolled over all K with split operands on the device: verified == 2 and the goal's costs, argmin and
