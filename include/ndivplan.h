@@ -180,6 +180,15 @@ int ndp_ndiv_loss_grad(const float* x, const float* z, const float* sx, const fl
 int ndp_ndiv_forward_backward(const float* x, const float* z, int N, int k, int Dx, int Dz, float margin,
                               float* sx, float* sz, float* loss, float* grad_x, void* ws, size_t ws_bytes,
                               void* stream);
+/* the operator as a forward / backward pair (what a torch.autograd.Function binds):
+ * forward  -> loss[0] + the saved normalisers sx, sz [N,k];
+ * backward -> grad_x = grad_loss[0] * d loss / d x (grad_loss: device scalar, NULL = 1); grad_z must be NULL (the call
+ *             site never differentiates the latent codes: train_gan.py:193-196); loss_scratch: one device float */
+int ndp_ndiv_forward(const float* x, const float* z, int N, int k, int Dx, int Dz, float margin, float* loss,
+                     float* sx, float* sz, void* ws, size_t ws_bytes, void* stream);
+int ndp_ndiv_backward(const float* x, const float* z, const float* sx, const float* sz, int N, int k, int Dx, int Dz,
+                      float margin, const float* grad_loss, float* grad_x, float* grad_z, float* loss_scratch,
+                      void* ws, size_t ws_bytes, void* stream);
 /* compute_pairwise (normalise=0, diversity.py:8-9) / compute_pair_distance
  * (normalise=1, diversity.py:12-19): v [N,k,C] -> out [N,k,k] */
 int ndp_pairwise(const float* v, int N, int k, int C, int normalise, float* out, void* stream);

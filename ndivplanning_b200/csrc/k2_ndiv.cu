@@ -908,6 +908,34 @@ extern "C" int ndp_ndiv_forward_backward(const float* x, const float* z, int N, 
   return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, run_if, s);
 }
 
+// ---- forward / backward split of the operator (SURVEY.md 8b names): what a torch.autograd.Function binds --------
+// forward: loss[0] and the saved normalisers sx, sz [N,k]
+extern "C" int ndp_ndiv_forward(const float* x, const float* z, int N, int k, int Dx, int Dz, float margin, float* loss,
+                                float* sx, float* sz, void* ws, size_t ws_bytes, void* stream) {
+  return ndp_ndiv_forward_backward(x, z, N, k, Dx, Dz, margin, sx, sz, loss, nullptr, ws, ws_bytes, stream);
+}
+__global__ void ndiv_scale_kernel(float* __restrict__ g, const float* __restrict__ scale, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) g[i] *= scale[0];
+}
+// backward: grad_x = grad_loss[0] * d loss / d x from the saved normalisers (grad_loss: device scalar, NULL = 1).
+// grad_z must be NULL: the call site never differentiates the latent codes (train_gan.py:193-196, noise has no grad).
+// loss_scratch: device float the kernels may overwrite (the loss is recomputed on the way).
+extern "C" int ndp_ndiv_backward(const float* x, const float* z, const float* sx, const float* sz, int N, int k, int Dx,
+                                 int Dz, float margin, const float* grad_loss, float* grad_x, float* grad_z,
+                                 float* loss_scratch, void* ws, size_t ws_bytes, void* stream) {
+  NDP_CHECK_ARG(grad_z == nullptr, "ndp_ndiv_backward: the gradient w.r.t. the latent codes is not provided (pass NULL)");
+  NDP_CHECK_ARG(grad_x && loss_scratch, "ndp_ndiv_backward: null grad_x / loss_scratch");
+  if (int rc = ndp_ndiv_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss_scratch, grad_x, ws, ws_bytes, stream))
+    return rc;
+  if (grad_loss && N > 0 && k > 0) {
+    const size_t n = (size_t)N * k * Dx;
+    ndiv_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(grad_x, grad_loss, n);
+    NDP_LAUNCH_CHECK();
+  }
+  return NDP_OK;
+}
+
 extern "C" int ndp_pairwise(const float* v, int N, int k, int C, int normalise, float* out, void* stream) {
   NDP_CHECK_ARG(N >= 0 && k >= 0 && C >= 1 && N <= 65535, "pairwise: bad shape");
   if (int rc = device_check()) return rc;

@@ -208,3 +208,32 @@ def test_ndiv_tight_cluster_far_from_origin(cuda, N, k, Dx, Dz):
     cs, cs32 = grad.sum(1).abs().max().item(), g32.sum(1).abs().max().item()
     scale = g64.abs().max().item()
     assert cs <= max(8 * cs32, 2e-5 * scale * np.sqrt(k)), (cs, cs32, scale)
+
+
+@pytest.mark.parametrize("N,k,Dx,Dz", [(56, 6, 4, 2), (2, 300, 12, 5), (1, 1536, 32, 16)])
+def test_ndiv_forward_backward_abi_pair(cuda, N, k, Dx, Dz):
+    """ndp_ndiv_forward / ndp_ndiv_backward (the forward/backward split a torch.autograd.Function binds)
+    against the oracle, with an upstream gradient scalar"""
+    import ctypes as C
+    from ndivplanning_b200 import _lib
+    x, z = synthetic.make_ndiv_inputs(N, k, Dx, Dz, seed=3 + k)
+    xd, zd = x.cuda(), z.cuda()
+    n = C.c_size_t()
+    _lib.check(_lib.lib().ndp_ndiv_workspace_bytes(N, k, Dx, Dz, C.byref(n)))
+    ws = torch.empty(max(n.value, 256), dtype=torch.uint8, device="cuda")
+    loss, sx, sz = torch.empty(1, device="cuda"), torch.empty(N, k, device="cuda"), torch.empty(N, k, device="cuda")
+    st = _lib.stream_ptr(xd.device)
+    _lib.check(_lib.lib().ndp_ndiv_forward(_lib.ptr(xd), _lib.ptr(zd), N, k, Dx, Dz, 0.8, _lib.ptr(loss), _lib.ptr(sx),
+                                          _lib.ptr(sz), _lib.ptr(ws), ws.numel(), st))
+    gl = torch.tensor([0.1], device="cuda")            # pairwise_div_factor flowing in from the total loss
+    grad, scratch = torch.empty_like(xd), torch.empty(1, device="cuda")
+    _lib.check(_lib.lib().ndp_ndiv_backward(_lib.ptr(xd), _lib.ptr(zd), _lib.ptr(sx), _lib.ptr(sz), N, k, Dx, Dz, 0.8,
+                                           _lib.ptr(gl), _lib.ptr(grad), None, _lib.ptr(scratch), _lib.ptr(ws), ws.numel(), st))
+    l64, g64 = O.ndiv_fwd_bwd(x.double(), z.double())
+    np.testing.assert_allclose(loss.item(), l64.item(), rtol=RTOL)
+    np.testing.assert_allclose(scratch.item(), l64.item(), rtol=RTOL)
+    _grad_close_arbiter((grad / 0.1).cpu(), x, z, g64.numpy(), rtol=RTOL)
+    with pytest.raises(Exception):                         # gradient w.r.t. the latent codes is not provided
+        _lib.check(_lib.lib().ndp_ndiv_backward(_lib.ptr(xd), _lib.ptr(zd), _lib.ptr(sx), _lib.ptr(sz), N, k, Dx, Dz, 0.8,
+                                               None, _lib.ptr(grad), _lib.ptr(grad), _lib.ptr(scratch), _lib.ptr(ws),
+                                               ws.numel(), st))
