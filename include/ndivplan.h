@@ -92,6 +92,11 @@ int ndp_generator_forward(ndp_planner* p, const float* z, int B, float* a, void*
 int ndp_forward_step(ndp_planner* p, const float* state, const float* action, int B,
                      float* next_state, void* stream);
 
+/* ---- sampler: replaces torch.FloatTensor(N,S,nd).uniform_() of diverse_sampling (mpc_eval.py:78-83) on the device.
+ * out[i] = (philox4x32_10(counter = {i/4, offset}, key = seed)[i & 3] >> 8) * 2^-24 in [0,1); reproducible from
+ * (seed, offset), independent of launch geometry.  Fill noise [T,G,K,nd] with it and pass it to the plan calls. */
+int ndp_sample_uniform(uint64_t seed, uint64_t offset, float* out, size_t n, void* stream);
+
 /* ---- selection: replaces the python scan mpc_eval.py:122,159-165 -----------------
  * cost [G,K]. For each segment g:
  *   packed_min[g] = (okey(cost)<<32) | (idx_base + argmin)  with first-index tie break;

@@ -40,6 +40,7 @@ _PROTOS = {
     "ndp_rollout_score": (_i, [_vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_generator_forward": (_i, [_vp, _vp, _i, _vp, _vp]),
     "ndp_forward_step": (_i, [_vp, _vp, _vp, _i, _vp, _vp]),
+    "ndp_sample_uniform": (_i, [C.c_uint64, C.c_uint64, _vp, _sz, _vp]),
     "ndp_select_workspace_bytes": (_i, [_i, _i, _i, C.POINTER(_sz)]),
     "ndp_select": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_workspace_bytes": (_i, [_vp, _i, _i, _i, C.POINTER(_sz)]),

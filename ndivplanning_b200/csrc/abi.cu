@@ -421,3 +421,42 @@ extern "C" int ndp_plan_select_refine(ndp_planner* p, const float* e0, const flo
   return plan_select_impl(2, p, e0, goal, noise, G, K, topk, idx_base, eps, cost, a0, packed_min, topk_idx, topk_cost,
                           verified, ws, ws_bytes, stream);
 }
+
+// ---- device sampler: U[0,1) noise of diverse_sampling (mpc_eval.py:78-83) drawn next to its
+// consumer.  Counter-based Philox4x32-10 (Salmon et al., SC'11): value i is word (i & 3) of
+// philox(counter = {i/4 lo, i/4 hi, offset lo, offset hi}, key = {seed lo, seed hi}), mapped to [0,1) by its top
+// 24 bits -- reproducible from (seed, offset) alone, independent of launch geometry.
+namespace ndp {
+__device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint32_t k1) {
+  const uint32_t hi0 = __umulhi(0xD2511F53u, c[0]), lo0 = 0xD2511F53u * c[0];
+  const uint32_t hi1 = __umulhi(0xCD9E8D57u, c[2]), lo1 = 0xCD9E8D57u * c[2];
+  const uint32_t n0 = hi1 ^ c[1] ^ k0, n2 = hi0 ^ c[3] ^ k1;
+  c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
+}
+__global__ void sample_uniform_kernel(unsigned long long seed, unsigned long long offset, float* __restrict__ out,
+                                      size_t n) {
+  const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;      // one Philox block = 4 values
+  if (q * 4 >= n) return;
+  uint32_t c[4] = {(uint32_t)q, (uint32_t)(q >> 32), (uint32_t)offset, (uint32_t)(offset >> 32)};
+  uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+  for (int r = 0; r < 10; r++) {
+    philox_round(c, k0, k1);
+    k0 += 0x9E3779B9u;
+    k1 += 0xBB67AE85u;
+  }
+#pragma unroll
+  for (int j = 0; j < 4; j++)
+    if (q * 4 + j < n) out[q * 4 + j] = (float)(c[j] >> 8) * (1.0f / 16777216.0f);
+}
+}  // namespace ndp
+
+extern "C" int ndp_sample_uniform(uint64_t seed, uint64_t offset, float* out, size_t n, void* stream) {
+  NDP_CHECK_ARG(out || n == 0, "ndp_sample_uniform: null output");
+  if (int rc = ndp::device_check()) return rc;
+  if (n == 0) return NDP_OK;
+  const size_t q = (n + 3) / 4;
+  ndp::sample_uniform_kernel<<<(unsigned)((q + 255) / 256), 256, 0, (cudaStream_t)stream>>>(seed, offset, out, n);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}

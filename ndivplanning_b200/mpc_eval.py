@@ -21,6 +21,22 @@ def sample_noise(T: int, K: int, nd: int, num_sample: int = 1) -> torch.Tensor:
     return torch.stack([torch.FloatTensor(K, num_sample, nd).uniform_()[:, 0] for _ in range(T)], 0)
 
 
+def sample_noise_device(T: int, G: int, K: int, nd: int, seed: int, offset: int = 0, device=None) -> torch.Tensor:
+    """The sampler next to its consumer: noise [T,G,K,nd] ~ U[0,1) drawn on the GPU by the library's counter-based
+    Philox4x32-10 (ndp_sample_uniform) — reproducible from (seed, offset), no host RNG, no H2D copy.  Use a fresh
+    `offset` (or seed) per plan.  Not bit-compatible with the reference's CPU mt19937 stream (nothing on a GPU is):
+    parity tests feed the reference's own draws through `sample_noise` instead."""
+    import ctypes as C
+    dev = torch.device(device if device is not None else torch.cuda.current_device())
+    if dev.type != "cuda":
+        raise _lib.NdpError("sample_noise_device draws on the GPU; there is no CPU fallback")
+    out = torch.empty(T, G, K, nd, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().ndp_sample_uniform(C.c_uint64(seed & (2 ** 64 - 1)), C.c_uint64(offset & (2 ** 64 - 1)),
+                                                 _lib.ptr(out), out.numel(), _lib.stream_ptr(dev)))
+    return out
+
+
 def fetch_push_control_evaluation(image_encoder, fwd_model_autoencoder, generator, dataset, config,
                                   return_indices: bool = False):
     if not isinstance(image_encoder, nn.Identity):

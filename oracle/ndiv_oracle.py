@@ -322,3 +322,31 @@ def gan_train_step(decoder, discriminator, G_opt, D_opt, codes, actions, noise, 
     total_loss.backward()
     G_opt.step()                                                                  # :201-203
     return D_loss.detach(), G_loss.detach(), pair_div_loss.detach(), action_hat.detach()
+
+
+# ----------------------------------------------------------------------------
+# device sampler — counter-based Philox4x32-10 (Salmon, Moraes, Dror, Shaw: "Parallel random numbers: as easy as
+# 1, 2, 3", SC'11; Random123 reference constants), as ndp_sample_uniform defines its stream
+# ----------------------------------------------------------------------------
+def philox4x32_10(counter, key):
+    """counter [n,4] uint32, key [2] -> [n,4] uint32 (numpy)."""
+    import numpy as np
+    c = np.array(counter, dtype=np.uint64).reshape(-1, 4).copy()
+    k0, k1 = np.uint64(key[0]), np.uint64(key[1])
+    M0, M1, W0, W1, MASK = np.uint64(0xD2511F53), np.uint64(0xCD9E8D57), np.uint64(0x9E3779B9), np.uint64(0xBB67AE85), np.uint64(0xFFFFFFFF)
+    for _ in range(10):
+        p0, p1 = M0 * c[:, 0], M1 * c[:, 2]
+        hi0, lo0, hi1, lo1 = p0 >> np.uint64(32), p0 & MASK, p1 >> np.uint64(32), p1 & MASK
+        c = np.stack([hi1 ^ c[:, 1] ^ k0, lo1, hi0 ^ c[:, 3] ^ k1, lo0], axis=1)
+        k0, k1 = (k0 + W0) & MASK, (k1 + W1) & MASK
+    return c.astype(np.uint32)
+
+
+def sample_uniform(seed: int, offset: int, n: int):
+    """ndp_sample_uniform(seed, offset, out, n): value i = word (i & 3) of philox({i/4, offset}, seed), top 24 bits."""
+    import numpy as np
+    q = np.arange((n + 3) // 4, dtype=np.uint64)
+    ctr = np.stack([q & np.uint64(0xFFFFFFFF), q >> np.uint64(32),
+                    np.full_like(q, offset & 0xFFFFFFFF), np.full_like(q, (offset >> 32) & 0xFFFFFFFF)], axis=1)
+    w = philox4x32_10(ctr, (seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)).reshape(-1)[:n]
+    return (w >> np.uint32(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)

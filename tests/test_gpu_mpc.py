@@ -384,3 +384,25 @@ def test_ring_fallback_consumer_initiated(cuda):
     assert torch.equal(p.verified, want.verified) and 2 in p.verified.cpu().tolist()
     assert torch.equal(p.best_idx, want.best_idx) and torch.equal(p.best_action, want.best_action)
     assert torch.equal(p.topk_idx, want.topk_idx) and torch.equal(p.cost, want.cost)
+
+
+def test_device_sampler_matches_philox_oracle(cuda):
+    """ndp_sample_uniform (row A on the device) is bit-exact against the numpy Philox4x32-10 oracle, which is pinned
+    by the Random123 known-answer vectors (tests/test_oracle_golden.py); and it drives a plan"""
+    from ndivplanning_b200 import FusedPlanner, sample_noise_device
+    for seed, offset, shape in ((0, 0, (1, 1, 5, 3)), (1234567890123456789, 2 ** 40 + 17, (2, 3, 257, 2)),
+                                (2 ** 64 - 1, 2 ** 63, (8, 1, 4096, 2))):
+        got = sample_noise_device(*shape, seed=seed, offset=offset, device=cuda).cpu().numpy().reshape(-1)
+        want = O.sample_uniform(seed, offset, got.size)
+        assert np.array_equal(got, want), (seed, offset)
+        assert got.min() >= 0.0 and got.max() < 1.0
+    a = sample_noise_device(4, 1, 1024, 2, seed=5, offset=0, device=cuda)
+    b = sample_noise_device(4, 1, 1024, 2, seed=5, offset=1, device=cuda)
+    assert not torch.equal(a, b)
+    gen, fwd = synthetic.make_models(nd=2, E=128, H=256)
+    e0, goal, _ = synthetic.make_plan_inputs(1, 1024, 4, 2, 128, seed=2)
+    pl = FusedPlanner(gen, fwd, horizon=4, precision="fp32")
+    p1 = pl.plan(e0.cuda(), goal.cuda(), a)
+    og, of = _oracle_models(gen, fwd, 2, 128, 256)
+    ref = O.mpc_plan(og, of, e0[0], goal[0], a.cpu()[:, 0])
+    assert int(p1.best_idx[0]) == ref["best_idx"]

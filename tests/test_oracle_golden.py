@@ -100,3 +100,16 @@ def test_gan_step_oracle_matches_reference(golden, name):
     st = 1 if name == "ref_shape" else 4        # GAN_STRIDE64 of oracle/make_golden.py
     np.testing.assert_allclose(_flat(gen).numpy()[::st], g[f"{name}_gparams"], rtol=1e-4, atol=2e-6)
     np.testing.assert_allclose(_flat(dis).numpy()[::st], g[f"{name}_dparams"], rtol=1e-4, atol=2e-6)
+
+
+def test_philox_known_answers():
+    """Philox4x32-10 known-answer vectors of the Random123 distribution (kat_vectors): the oracle of the device sampler"""
+    kat = [((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff, 0xffffffff), (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1))]
+    for ctr, key, want in kat:
+        got = O.philox4x32_10([ctr], key)[0]
+        assert tuple(int(v) for v in got) == want, (ctr, [hex(int(v)) for v in got])
+    u = O.sample_uniform(7, 3, 10001)
+    assert u.shape == (10001,) and u.min() >= 0.0 and u.max() < 1.0 and abs(float(u.mean()) - 0.5) < 0.02
