@@ -1030,16 +1030,22 @@ int ndp_gan_create(ndp_gan** out, const ndp_gan_desc* d) {
   for (int l = 0; l < 4; l++) { g->dr_act[l] = (float*)(base + o_dr[l]); g->df_act[l] = (float*)(base + o_df[l]); }
   g->dl_real = (float*)(base + o_dlr); g->dl_fake = (float*)(base + o_dlf);
   g->bce_part = (float*)(base + o_bcep); g->bce_ticket = (unsigned*)(base + o_bcet);
-  cudaMemset(g->bce_ticket, 0, 4);
+  NDP_CUDA(cudaMemset(g->bce_ticket, 0, 4));
   for (int l = 0; l < 4; l++) g->gd[l] = (float*)(base + o_gd[l]);
   for (int l = 0; l < 3; l++) { g->fd[l] = (float*)(base + o_fd[l]); g->rd[l] = (float*)(base + o_rd[l]); }
   const char* ss = getenv("NDP_GAN_SINGLE_STREAM");
   g->multi_stream = !(ss && ss[0] == '1');
-  cudaStreamCreateWithFlags(&g->s_real, cudaStreamNonBlocking);
-  cudaStreamCreateWithFlags(&g->s_dw, cudaStreamNonBlocking);
-  cudaStreamCreateWithFlags(&g->s_nd, cudaStreamNonBlocking);
-  for (int i = 0; i < 64; i++) cudaEventCreateWithFlags(&g->ev.e[i], cudaEventDisableTiming);
+  bool ok = cudaStreamCreateWithFlags(&g->s_real, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&g->s_dw, cudaStreamNonBlocking) == cudaSuccess &&
+            cudaStreamCreateWithFlags(&g->s_nd, cudaStreamNonBlocking) == cudaSuccess;
+  for (int i = 0; i < 64 && ok; i++) ok = cudaEventCreateWithFlags(&g->ev.e[i], cudaEventDisableTiming) == cudaSuccess;
   g->ev.n = 0;
+  if (!ok) {
+    set_error("ndp_gan_create: stream / event creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    cudaFree(g->arena);
+    delete g;
+    return NDP_ERR_CUDA;
+  }
   g->g_div = (float*)(base + o_gdiv); g->da = (float*)(base + o_da);
   g->sx = (float*)(base + o_sx); g->sz = (float*)(base + o_sz);
   g->g_part = (float*)(base + o_gpart); g->d_part = (float*)(base + o_dpart);
