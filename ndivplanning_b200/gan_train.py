@@ -158,3 +158,35 @@ class GanTrainer:
 def flatten_grads(module, layers) -> torch.Tensor:
     """module .grad tensors in the flat [W0|b0|W1|b1|...] layout of ndp_gan_grads"""
     return torch.cat([t.grad.reshape(-1) for n in layers for t in (getattr(module, n).weight, getattr(module, n).bias)])
+
+
+def unpack_trajectories(images: torch.Tensor, actions: torch.Tensor, seq_length: int):
+    """train_gan.py:126-137: images [b,seq,...], actions [b,seq,A] -> (state_cur [b*(seq-1),...],
+    state_target [b*(seq-1),...] (the last frame of each trajectory, repeated), actions [b*(seq-1),A])."""
+    state_cur, state_target = torch.split(images, split_size_or_sections=[seq_length - 1, 1], dim=1)
+    state_cur = state_cur.reshape(-1, *state_cur.shape[2:])
+    state_target = torch.repeat_interleave(state_target.squeeze(dim=1), repeats=seq_length - 1, dim=0)
+    acts = actions[:, :-1].reshape(-1, actions.shape[-1])
+    return state_cur, state_target, acts
+
+
+@torch.no_grad()
+def train_gan_epoch(trainer: "GanTrainer", loader, encoder, seq_length: int, noise_fn=None):
+    """One epoch of the reference's GAN training loop (train_gan.py:114-207) with the loop body on the device:
+    per batch — unpack the trajectories (:126-137), encode current and target frames with the (frozen, detached)
+    `encoder` (:152-155), draw the noise (:43-47; `noise_fn(F) -> [F,S,nd]` overrides the device generator), one
+    `trainer.step`.  The three losses are accumulated on the device (the reference syncs `.cpu()` three times per
+    batch, :203-205) and returned as (D_loss_avg, G_loss_avg, pair_div_loss_avg) (:207-209), one sync at the end."""
+    dev = trainer.device
+    sums = torch.zeros(3, dtype=torch.float32, device=dev)
+    n_batches = 0
+    for images, _states, actions, _goal in loader:
+        images, actions = images.float().to(dev), actions.float().to(dev)
+        state_cur, state_target, acts = unpack_trajectories(images, actions, seq_length)
+        codes = torch.cat([encoder(state_cur), encoder(state_target)], dim=1).reshape(state_cur.shape[0], -1)
+        F = codes.shape[0]
+        noise = noise_fn(F).to(dev) if noise_fn is not None else torch.rand(F, trainer.S, trainer.nd, device=dev)
+        sums += trainer.step(codes, acts, noise)
+        n_batches += 1
+    avg = (sums / max(n_batches, 1)).cpu()
+    return float(avg[0]), float(avg[1]), float(avg[2])

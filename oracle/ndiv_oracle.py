@@ -20,7 +20,7 @@ __all__ = [
     "ndiv_grad_analytic", "GeneratorMLP", "LatentForward", "draw_noise",
     "diverse_sampling", "mpc_rollout", "select_first_min", "select_topk",
     "mpc_plan", "pack_key", "closed_loop_eval", "ndiv_fwd_bwd", "ActionDiscriminator", "gan_optimizers",
-    "gan_train_step",
+    "gan_train_step", "gan_train_epoch", "philox4x32_10", "sample_uniform",
 ]
 
 MARGIN = 0.8          # diversity.py:40
@@ -350,3 +350,26 @@ def sample_uniform(seed: int, offset: int, n: int):
                     np.full_like(q, offset & 0xFFFFFFFF), np.full_like(q, (offset >> 32) & 0xFFFFFFFF)], axis=1)
     w = philox4x32_10(ctr, (seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)).reshape(-1)[:n]
     return (w >> np.uint32(8)).astype(np.float32) * np.float32(1.0 / 16777216.0)
+
+
+def gan_train_epoch(decoder, discriminator, G_opt, D_opt, loader, encoder, seq_length: int, num_sample: int,
+                    noise_dim: int, div_factor: float = 0.1, discrim_steps_per_gen: int = 1, noises=None):
+    """train_gan.py:114-209 for one epoch on the CPU (encoder frozen/detached, :152-153).  `noises`: optional list
+    of [F,S,nd] tensors, one per batch (else the reference's draw, :43-44).  Returns the three loss averages."""
+    D_sum = G_sum = P_sum = 0.0
+    for i, (images, states, actions, goal) in enumerate(loader):
+        images, actions = images.float(), actions.float()
+        state_cur, state_target = torch.split(images, split_size_or_sections=[seq_length - 1, 1], dim=1)      # :127
+        state_cur = state_cur.reshape(-1, *(state_cur.size()[2:]))                                             # :131
+        state_target = torch.repeat_interleave(state_target.squeeze(dim=1), repeats=seq_length - 1, dim=0)     # :133
+        acts = actions[:, :-1].reshape(-1, actions.size()[-1])                                                 # :137
+        state_codes = encoder(state_cur).detach()                                                              # :152
+        target_codes = encoder(state_target).detach()
+        codes = torch.cat([state_codes, target_codes], dim=1).squeeze()                                        # :155
+        codes = codes.reshape(state_cur.shape[0], -1)
+        noise = noises[i] if noises is not None else torch.FloatTensor(codes.shape[0], num_sample, noise_dim).uniform_()
+        dl, gl, pl, _ = gan_train_step(decoder, discriminator, G_opt, D_opt, codes, acts, noise, div_factor,
+                                       discrim_steps_per_gen)
+        D_sum, G_sum, P_sum = D_sum + float(dl), G_sum + float(gl), P_sum + float(pl)
+    n = max(len(loader), 1)
+    return D_sum / n, G_sum / n, P_sum / n

@@ -207,3 +207,49 @@ def test_gan_single_sample_groups_are_nan_like_the_reference(cuda):
     tr = GanTrainer(gen, dis, num_sample=1, noise_dim=2, max_codes=4, device=cuda)
     l = tr.step(c.to(cuda), a.to(cuda), z.to(cuda)).cpu().numpy()
     assert np.isfinite(l[0]) and np.isfinite(l[1]) and np.isnan(l[2])
+
+
+class _Traj(torch.utils.data.Dataset):
+    """duck-typed PushDataset (utils/trajectory_loader.py:38-72) in embedding space: images are [seq,E,1,1] codes"""
+
+    def __init__(self, n, seq, E=128, seed=0):
+        g = torch.Generator().manual_seed(seed)
+        self.images = torch.randn(n, seq, E, 1, 1, generator=g)
+        self.actions = torch.randn(n, seq, 4, generator=g)
+        self.seq_length = seq
+
+    def __len__(self):
+        return self.images.shape[0]
+
+    def __getitem__(self, i):
+        return self.images[i], torch.zeros(self.seq_length, 25), self.actions[i], torch.zeros(3)
+
+
+def test_train_gan_epoch_matches_oracle_epoch(cuda):
+    """the epoch loop around the step (train_gan.py:114-209: unpack trajectories, encode, sample, step, average the
+    losses) against the oracle's CPU epoch with the same batches and noise; pairwise_div_factor = 0 keeps the
+    comparison out of the chaotic regime (see the module docstring)"""
+    from ndivplanning_b200 import train_gan_epoch
+    seq, bs, S, nd = 8, 8, 6, 2
+    ds = _Traj(24, seq)
+    loader = torch.utils.data.DataLoader(ds, batch_size=bs, shuffle=False)
+    enc = torch.nn.Identity()
+    F = bs * (seq - 1)
+    torch.manual_seed(3)
+    noises = [torch.rand(F, S, nd) for _ in range(len(loader))]
+    gen, dis = synthetic.make_gan_models(nd, seed=0)
+    tr = GanTrainer(gen, dis, num_sample=S, noise_dim=nd, max_codes=F, pairwise_div_factor=0.0, device=cuda)
+    it = iter(noises)
+    got = train_gan_epoch(tr, loader, enc, seq, noise_fn=lambda F_: next(it))
+    og, od = O.GeneratorMLP(nd), O.ActionDiscriminator()
+    og.load_state_dict(gen.state_dict()); od.load_state_dict(dis.state_dict())
+    G_opt, D_opt = O.gan_optimizers(og, od)
+    want = O.gan_train_epoch(og, od, G_opt, D_opt, loader, enc, seq, S, nd, div_factor=0.0, noises=noises)
+    np.testing.assert_allclose(got[:2], want[:2], rtol=2e-5)
+    np.testing.assert_allclose(got[2], want[2], rtol=2e-3)
+    gsd, _ = tr.state_dicts()
+    rp = torch.cat([p.detach().reshape(-1) for p in og.parameters()]).numpy()
+    assert np.median(np.abs(_flat_sd(gsd, G_LAYERS) - rp)) < 1e-7
+    # device sampler path runs too
+    d2 = train_gan_epoch(tr, loader, enc, seq)
+    assert all(np.isfinite(v) for v in d2)
