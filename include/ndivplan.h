@@ -245,6 +245,16 @@ int ndp_gan_param_counts(const ndp_gan* g, size_t* n_gen, size_t* n_dis);
 int ndp_gan_grads(ndp_gan* g, float* gen_flat, float* dis_flat, void* stream);
 int ndp_gan_last_actions(ndp_gan* g, float* a_hat, int F, void* stream);
 
+/* ---- image-encoder front end: models/image_autoencoder.py:14-49 (Encoder) in eval mode,
+ * [B,3,128,128] NCHW frames -> [B,128] codes (the reference's [B,128,1,1]); replaces image_encoder(x) at
+ * mpc_eval.py:135-136 / train_gan.py:152-153.  ndp_encoder_load takes, per layer, weights permuted to
+ * [Cout][KH][KW][Cin] with the eval-mode BatchNorm of conv1..conv3 folded in, and the folded biases. */
+typedef struct ndp_encoder ndp_encoder;
+int ndp_encoder_create(ndp_encoder** out, int max_images, int img /* 128 */);
+void ndp_encoder_destroy(ndp_encoder* e);
+int ndp_encoder_load(ndp_encoder* e, const float* const* W /*[6]*/, const float* const* b /*[6]*/, void* stream);
+int ndp_encoder_forward(ndp_encoder* e, const float* images, int B, float* codes, void* stream);
+
 /* ---- collectives (NCCL over NVLink; libnccl is dlopen'ed on first use) ----------- */
 int ndp_comm_unique_id(void* id128_host);                       /* 128-byte ncclUniqueId */
 int ndp_comm_create(ndp_comm** out, const void* id128_host, int rank, int world);

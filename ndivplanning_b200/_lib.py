@@ -69,6 +69,10 @@ _PROTOS = {
     "ndp_gan_param_counts": (_i, [_vp, C.POINTER(_sz), C.POINTER(_sz)]),
     "ndp_gan_grads": (_i, [_vp, _vp, _vp, _vp]),
     "ndp_gan_last_actions": (_i, [_vp, _vp, _i, _vp]),
+    "ndp_encoder_create": (_i, [C.POINTER(_vp), _i, _i]),
+    "ndp_encoder_destroy": (None, [_vp]),
+    "ndp_encoder_load": (_i, [_vp, C.POINTER(_vp), C.POINTER(_vp), _vp]),
+    "ndp_encoder_forward": (_i, [_vp, _vp, _i, _vp, _vp]),
     "ndp_comm_unique_id": (_i, [_vp]),
     "ndp_comm_create": (_i, [C.POINTER(_vp), _vp, _i, _i]),
     "ndp_comm_allreduce_min_u64": (_i, [_vp, _vp, _i, _vp]),

@@ -3,7 +3,7 @@
 set -e
 cd "$(dirname "$0")"
 OUT=../libndivplan.so
-SRCS="abi.cu k1_rollout_f32.cu k1_rollout_tc.cu k2_ndiv.cu k2_ndiv_tc.cu k3_select.cu k4_gan_train.cu comm.cu"
+SRCS="abi.cu k1_rollout_f32.cu k1_rollout_tc.cu k2_ndiv.cu k2_ndiv_tc.cu k3_select.cu k4_gan_train.cu k5_encoder.cu comm.cu"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 mkdir -p ../_build
 OBJS=""

@@ -15,6 +15,10 @@ the modules stay usable in the reference's own scripts.
 * ``ActionDiscriminator`` has the layout of ``models.gan.Discriminator`` (reference
   models/gan.py:89-110): fc1..fc4, (256+4)->64->128->256->1, leaky ReLU, input
   ``cat([action, state_code], 1)``.  Weight container for ``GanTrainer``.
+* ``ImageEncoder`` has the layout of ``models.image_autoencoder.Encoder`` (reference
+  models/image_autoencoder.py:14-49): conv1..conv5 3x3 stride 2 (3->64->128->256->512->1024),
+  BatchNorm applied after conv1..conv3 only (conv4_bn / conv5_bn exist as parameters and are never
+  applied, as in the reference), conv6 4x4 valid 1024->128.  Weight container for ``FusedEncoder``.
 """
 import torch
 from torch import nn
@@ -63,3 +67,20 @@ class ActionDiscriminator(nn.Module):
         h = F.leaky_relu(self.fc2(h))
         h = F.leaky_relu(self.fc3(h))
         return self.fc4(h)
+
+
+class ImageEncoder(nn.Module):
+    WIDTHS = (3, 64, 128, 256, 512, 1024)
+
+    def __init__(self):
+        super().__init__()
+        for i in range(5):          # conv_i then conv_i_bn: the reference's registration (and RNG draw) order
+            setattr(self, f"conv{i + 1}", nn.Conv2d(self.WIDTHS[i], self.WIDTHS[i + 1], 3, 2, 1))
+            setattr(self, f"conv{i + 1}_bn", nn.BatchNorm2d(self.WIDTHS[i + 1]))
+        self.conv6 = nn.Conv2d(1024, 128, 4, 1, 0)
+
+    def forward(self, x):
+        for i in (1, 2, 3):
+            x = F.relu(getattr(self, f"conv{i}_bn")(getattr(self, f"conv{i}")(x)))
+        x = F.relu(self.conv5(F.relu(self.conv4(x))))
+        return self.conv6(x)

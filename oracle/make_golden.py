@@ -213,6 +213,43 @@ def golden_gan(div, RefDecoder, RefDiscriminator):
     print("gan.npz", len(out), "arrays")
 
 
+def golden_enc():
+    """models/image_autoencoder.py Encoder in eval mode, fp32 and fp64, on seeded frames.  The weights (13 M floats)
+    are not committed: synthetic.make_image_encoder(seed) rebuilds them; a checksum guards the RNG stream."""
+    from models.image_autoencoder import Encoder as RefEncoder  # type: ignore
+    out = {}
+    for name, (B, seed) in {"b1": (1, 41), "b2": (2, 42), "b5": (5, 43)}.items():
+        enc_p = synthetic.make_image_encoder(seed=7)
+        ref = RefEncoder()
+        missing = ref.load_state_dict(enc_p.state_dict(), strict=True)          # same names, same shapes
+        assert not missing.missing_keys and not missing.unexpected_keys
+        assert list(ref.state_dict().keys()) == list(enc_p.state_dict().keys())
+        ref.eval()
+        frames = synthetic.make_frames(B, seed=seed)
+        with torch.no_grad():
+            y32 = ref(frames)
+            y64 = ref.double()(frames.double())
+            mine = O.encoder_forward(enc_p.state_dict(), frames.double())
+        assert y32.shape == (B, 128, 1, 1)
+        err = float((mine - y64).abs().max() / y64.abs().max())
+        assert err < 1e-12, err
+        out[f"{name}_cfg"] = np.array([B, seed, 7], dtype=np.int64)
+        out[f"{name}_codes"] = y32.view(B, 128).numpy()
+        out[f"{name}_codes64"] = y64.view(B, 128).numpy()
+        out[f"{name}_frame_sum"] = np.array(frames.double().sum().item())
+        print(f"enc {name}: |codes| max {float(y64.abs().max()):.4f}, fp32-vs-fp64 {float((y32.double() - y64).abs().max()):.3e}, "
+              f"oracle-vs-ref(fp64) {err:.2e}")
+    # default-initialised container draws the same parameters as the reference class under the same seed
+    from ndivplanning_b200.models import ImageEncoder
+    torch.manual_seed(3); a = RefEncoder()
+    torch.manual_seed(3); b = ImageEncoder()
+    for (n1, p1), (n2, p2) in zip(a.state_dict().items(), b.state_dict().items()):
+        assert n1 == n2 and torch.equal(p1, p2), n1
+    out["param_sum"] = np.array(sum(float(v.double().sum()) for v in synthetic.make_image_encoder(seed=7).state_dict().values()))
+    np.savez_compressed(os.path.join(OUT, "enc.npz"), **out)
+    print("enc.npz", len(out), "arrays")
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     torch.set_num_threads(8)
@@ -222,3 +259,4 @@ if __name__ == "__main__":
     golden_mpc(mpc_eval, RefDecoder)
     from models.gan import Discriminator as RefDiscriminator  # type: ignore  # noqa: E402
     golden_gan(div, RefDecoder, RefDiscriminator)
+    golden_enc()

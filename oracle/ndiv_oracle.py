@@ -373,3 +373,31 @@ def gan_train_epoch(decoder, discriminator, G_opt, D_opt, loader, encoder, seq_l
         D_sum, G_sum, P_sum = D_sum + float(dl), G_sum + float(gl), P_sum + float(pl)
     n = max(len(loader), 1)
     return D_sum / n, G_sum / n, P_sum / n
+
+
+# ---- image encoder: models/image_autoencoder.py:14-49, eval mode ----------------------
+def _conv2d(x, W, b, stride: int, pad: int):
+    """nn.Conv2d as im2col + matmul: out[b,o,i,j] = bias[o] + sum_{c,u,v} W[o,c,u,v] x[b,c,i*s-p+u,j*s-p+v]."""
+    cols = F.unfold(x, kernel_size=W.shape[2:], stride=stride, padding=pad)          # [B, C*KH*KW, OH*OW]
+    OH = (x.shape[2] + 2 * pad - W.shape[2]) // stride + 1
+    y = W.flatten(1) @ cols + b.view(1, -1, 1)
+    return y.view(x.shape[0], W.shape[0], OH, -1)
+
+
+def _bn_eval(x, sd, name: str, eps: float = 1e-5):
+    """nn.BatchNorm2d in eval mode: (x - running_mean) / sqrt(running_var + eps) * weight + bias."""
+    v = lambda k: sd[f"{name}.{k}"].view(1, -1, 1, 1).to(x.dtype)
+    return (x - v("running_mean")) / torch.sqrt(v("running_var") + eps) * v("weight") + v("bias")
+
+
+def encoder_forward(sd, images: torch.Tensor) -> torch.Tensor:
+    """Encoder.forward (image_autoencoder.py:35-49) from a state dict: BatchNorm after conv1..conv3 only; conv4_bn and
+    conv5_bn are parameters the forward never applies.  Computes in images.dtype."""
+    dt = images.dtype
+    x = images
+    for i in (1, 2, 3, 4, 5):
+        x = _conv2d(x, sd[f"conv{i}.weight"].to(dt), sd[f"conv{i}.bias"].to(dt), 2, 1)
+        if i <= 3:
+            x = _bn_eval(x, sd, f"conv{i}_bn")
+        x = F.relu(x)
+    return _conv2d(x, sd["conv6.weight"].to(dt), sd["conv6.bias"].to(dt), 1, 0)

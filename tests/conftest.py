@@ -16,7 +16,7 @@ def pytest_configure(config):
 def golden():
     import numpy as np
     d = os.path.join(ROOT, "tests", "golden")
-    return {n: np.load(os.path.join(d, f"{n}.npz")) for n in ("ndiv", "gen", "mpc", "gan")}
+    return {n: np.load(os.path.join(d, f"{n}.npz")) for n in ("ndiv", "gen", "mpc", "gan", "enc")}
 
 
 @pytest.fixture(scope="session")

@@ -113,3 +113,40 @@ def test_philox_known_answers():
         assert tuple(int(v) for v in got) == want, (ctr, [hex(int(v)) for v in got])
     u = O.sample_uniform(7, 3, 10001)
     assert u.shape == (10001,) and u.min() >= 0.0 and u.max() < 1.0 and abs(float(u.mean()) - 0.5) < 0.02
+
+
+@pytest.mark.parametrize("name", ["b1", "b2", "b5"])
+def test_encoder_oracle_matches_reference(golden, name):
+    """oracle.encoder_forward vs the reference Encoder (models/image_autoencoder.py:35-49, eval mode) run by
+    oracle/make_golden.py::golden_enc on the same seeded frames and parameters."""
+    g = golden["enc"]
+    B, seed, pseed = (int(v) for v in g[f"{name}_cfg"])
+    enc = synthetic.make_image_encoder(seed=pseed)
+    psum = sum(float(v.double().sum()) for v in enc.state_dict().values())
+    assert abs(psum - float(g["param_sum"])) < 1e-9 * abs(float(g["param_sum"])) + 1e-9     # same RNG stream as the fixture
+    frames = synthetic.make_frames(B, seed=seed)
+    assert abs(float(frames.double().sum()) - float(g[f"{name}_frame_sum"])) < 1e-6
+    with torch.no_grad():
+        y64 = O.encoder_forward(enc.state_dict(), frames.double()).view(B, 128).numpy()
+        y32 = O.encoder_forward(enc.state_dict(), frames).view(B, 128).numpy()
+        ymod = enc(frames).view(B, 128).numpy()          # the container's reference-style forward
+    ref64, ref32 = g[f"{name}_codes64"], g[f"{name}_codes"]
+    assert np.abs(y64 - ref64).max() < 1e-12
+    assert np.abs(y32 - ref64).max() < 4 * np.abs(ref32 - ref64).max() + 1e-6
+    assert np.abs(ymod - ref32).max() < 2e-6
+
+
+def test_encoder_fold_matches_unfolded():
+    """BatchNorm folding (ndivplanning_b200/encoder.py::fold_state_dict) is an identity on the eval-mode forward."""
+    from ndivplanning_b200.encoder import fold_state_dict
+    enc = synthetic.make_image_encoder(seed=11)
+    frames = synthetic.make_frames(2, seed=5).double()
+    with torch.no_grad():
+        want = O.encoder_forward(enc.state_dict(), frames)
+        x = frames
+        for i, (W, b) in enumerate(fold_state_dict({k: v.double() for k, v in enc.state_dict().items()})):
+            W = W.double().permute(0, 3, 1, 2)        # back to [Cout,Cin,KH,KW]
+            x = torch.nn.functional.conv2d(x, W, b.double(), stride=2 if i < 5 else 1, padding=1 if i < 5 else 0)
+            if i < 5:
+                x = torch.relu(x)
+    assert float((x - want).abs().max()) < 2e-6       # folded weights are rounded to fp32 once
