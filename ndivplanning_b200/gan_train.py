@@ -20,6 +20,7 @@ from typing import Optional
 import torch
 
 from . import _lib
+from .encoder import FusedEncoder
 
 G_LAYERS = ("fc1", "fc2", "fc3", "fc4", "fc5")     # models/gan.py:67-71
 D_LAYERS = ("fc1", "fc2", "fc3", "fc4")            # models/gan.py:93-96
@@ -183,7 +184,13 @@ def train_gan_epoch(trainer: "GanTrainer", loader, encoder, seq_length: int, noi
     for images, _states, actions, _goal in loader:
         images, actions = images.float().to(dev), actions.float().to(dev)
         state_cur, state_target, acts = unpack_trajectories(images, actions, seq_length)
-        codes = torch.cat([encoder(state_cur), encoder(state_target)], dim=1).reshape(state_cur.shape[0], -1)
+        if isinstance(encoder, FusedEncoder):
+            # frames -> codes on the device (csrc/k5_encoder.cu); each trajectory's target frame is encoded once and
+            # its code repeated, where the reference encodes the seq-1 repeated copies (:133, :153)
+            tgt = encoder(images[:, -1]).repeat_interleave(seq_length - 1, dim=0)
+            codes = torch.cat([encoder(state_cur), tgt], dim=1).reshape(state_cur.shape[0], -1)
+        else:
+            codes = torch.cat([encoder(state_cur), encoder(state_target)], dim=1).reshape(state_cur.shape[0], -1)
         F = codes.shape[0]
         noise = noise_fn(F).to(dev) if noise_fn is not None else torch.rand(F, trainer.S, trainer.nd, device=dev)
         sums += trainer.step(codes, acts, noise)

@@ -5,7 +5,10 @@ the fused sm_100a kernels through ``FusedPlanner``; the receding-horizon bookkee
 it reproduces the reference's quirks.
 
 Embedding mode = ``image_encoder`` is ``nn.Identity`` and dataset "images" are [seq,E,1,1]
-(or [seq,E]) embeddings.  Real image encoders are out of scope.
+(or [seq,E]) embeddings.  Frame mode (first slice) = ``image_encoder`` is a reference
+``image_autoencoder.Encoder`` / ``ImageEncoder`` / ``FusedEncoder`` and dataset images are [seq,3,128,128]
+frames: they are encoded once per trajectory by csrc/k5_encoder.cu and the loop plans on the codes with the
+embedding-space forward model.  The reference's image-space U-net forward model stays out of scope.
 """
 import numpy as np
 import torch
@@ -39,12 +42,21 @@ def sample_noise_device(T: int, G: int, K: int, nd: int, seed: int, offset: int 
 
 def fetch_push_control_evaluation(image_encoder, fwd_model_autoencoder, generator, dataset, config,
                                   return_indices: bool = False):
-    if not isinstance(image_encoder, nn.Identity):
-        raise _lib.NdpError("ndivplanning_b200 plans in embedding space: pass nn.Identity() as image_encoder "
-                            "and embeddings as dataset images")
     if not torch.cuda.is_available():
         raise _lib.NdpError("CUDA is not available; there is no CPU fallback")
-    image_encoder.eval(); fwd_model_autoencoder.eval(); generator.eval()      # mpc_eval.py:58-60
+    from .encoder import FusedEncoder
+    fused_encoder = None
+    if isinstance(image_encoder, FusedEncoder):
+        fused_encoder = image_encoder
+    elif isinstance(image_encoder, nn.Module) and hasattr(image_encoder, "conv6"):
+        image_encoder.eval()                                                  # mpc_eval.py:58
+        fused_encoder = "build"
+    elif not isinstance(image_encoder, nn.Identity):
+        raise _lib.NdpError("image_encoder must be nn.Identity() (dataset images are embeddings), an "
+                            "image_autoencoder.Encoder-layout module or a FusedEncoder (dataset images are frames)")
+    else:
+        image_encoder.eval()
+    fwd_model_autoencoder.eval(); generator.eval()                            # mpc_eval.py:59-60
     num_sample = config.evaluation.num_sample
     nd = config.evaluation.noise_dim
     K = config.mpc.rollouts
@@ -53,6 +65,8 @@ def fetch_push_control_evaluation(image_encoder, fwd_model_autoencoder, generato
         raise _lib.NdpError("the reference loop is only well-formed for num_sample=1, batch_size=1 "
                             "(mpc_eval.py:155,161)")
     dev = torch.device("cuda", int(config.gpu_id) if str(config.gpu_id).isdigit() else torch.cuda.current_device())
+    if fused_encoder == "build":
+        fused_encoder = FusedEncoder(image_encoder, max_images=max(2, int(dataset.seq_length)), device=dev)
     torch.manual_seed(config.random_seed)                                     # mpc_eval.py:75-76
     np.random.seed(config.random_seed)
 
@@ -70,7 +84,12 @@ def fetch_push_control_evaluation(image_encoder, fwd_model_autoencoder, generato
     all_best = []
     for i in range(n_traj):
         images, _states, actions, _goal = dataset[i]
-        images = torch.as_tensor(images).float().reshape(seq, -1).to(dev)      # [seq,E]
+        images = torch.as_tensor(images).float().to(dev)
+        if fused_encoder is not None:
+            # frames -> codes ONCE per trajectory (the reference re-encodes the K-times repeated goal inside every
+            # rollout step, mpc_eval.py:135-136; the codes are the same every time)
+            images = fused_encoder(images.reshape(seq, 3, 128, 128))
+        images = images.reshape(seq, -1)                                       # [seq,E]
         actions = torch.as_tensor(actions).float().to(dev)[:-1]                # mpc_eval.py:107
         state_cur, goal = images[:-1], images[-1:]                             # mpc_eval.py:103-105
         image_error_sum = torch.zeros((), device=dev)                          # reset per trajectory (:110)

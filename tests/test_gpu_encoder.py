@@ -83,3 +83,64 @@ def test_encoder_feeds_planner_codes(cuda, fused):
     frames = synthetic.make_frames(2, seed=21).to(cuda)
     codes = fe(frames).flatten(1)
     assert codes.shape == (2, 128) and codes.is_contiguous() and torch.isfinite(codes).all()
+
+
+def test_closed_loop_from_frames_matches_oracle(cuda):
+    """fetch_push_control_evaluation in frame mode: dataset images are camera frames, encoded by the device encoder;
+    the oracle runs the same receding-horizon loop (mpc_eval.py:112-176) on the oracle's codes."""
+    from ndivplanning_b200 import fetch_push_control_evaluation
+    from oracle.ref_stubs import DotMap
+    K, Th, seq, n_traj, nd, seed = 64, 3, 4, 2, 2, 13
+    enc = synthetic.make_image_encoder(seed=7)
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=128, H=256, seed=0)
+    frames = synthetic.make_frames(n_traj * seq, seed=17).view(n_traj, seq, 3, 128, 128)
+    actions = torch.rand(n_traj, seq, 4, generator=torch.Generator().manual_seed(3))
+    with torch.no_grad():
+        codes = O.encoder_forward(enc.state_dict(), frames.flatten(0, 1)).view(n_traj, seq, 128)
+        want_a, want_i, want_best = O.closed_loop_eval(gen_p, fwd_p, codes, actions, K, Th, nd, seed)
+
+    class DS(torch.utils.data.Dataset):
+        seq_length = seq
+        def __len__(self): return n_traj
+        def __getitem__(self, i):
+            return frames[i], torch.zeros(seq, 25), actions[i], torch.zeros(3)
+
+    cfg = DotMap(random_seed=seed, gpu_id=0, log_port=0,
+                 evaluation=dict(num_sample=1, noise_dim=nd, batch_size=1, threshold=0.05),
+                 mpc=dict(rollouts=K, time_horizon=Th))
+    a, i, best = fetch_push_control_evaluation(enc, fwd_p, gen_p, DS(), cfg, return_indices=True)
+    assert best.numpy().tolist() == [list(r) for r in want_best]
+    np.testing.assert_allclose([a, i], [want_a, want_i], rtol=1e-4)
+
+
+def test_gan_epoch_from_frames_matches_oracle(cuda, fused):
+    """train_gan.py:114-209 with a real image encoder in front of the step (:152-155): FusedEncoder feeds
+    GanTrainer on the device; the oracle epoch encodes with oracle.encoder_forward on the CPU."""
+    from ndivplanning_b200 import GanTrainer, train_gan_epoch
+    enc, fe = fused
+    seq, bs, n, S, nd = 4, 2, 4, 6, 2
+    frames = synthetic.make_frames(n * seq, seed=23).view(n, seq, 3, 128, 128)
+    actions = torch.randn(n, seq, 4, generator=torch.Generator().manual_seed(1))
+
+    class DS(torch.utils.data.Dataset):
+        seq_length = seq
+        def __len__(self): return n
+        def __getitem__(self, i):
+            return frames[i], torch.zeros(seq, 25), actions[i], torch.zeros(3)
+
+    loader = torch.utils.data.DataLoader(DS(), batch_size=bs, shuffle=False)
+    F = bs * (seq - 1)
+    torch.manual_seed(3)
+    noises = [torch.rand(F, S, nd) for _ in range(len(loader))]
+    gen, dis = synthetic.make_gan_models(nd, seed=0)
+    tr = GanTrainer(gen, dis, num_sample=S, noise_dim=nd, max_codes=F, pairwise_div_factor=0.0, device=cuda)
+    it = iter(noises)
+    got = train_gan_epoch(tr, loader, fe, seq, noise_fn=lambda F_: next(it))
+    og, od = O.GeneratorMLP(nd), O.ActionDiscriminator()
+    og.load_state_dict(gen.state_dict()); od.load_state_dict(dis.state_dict())
+    G_opt, D_opt = O.gan_optimizers(og, od)
+    sd = enc.state_dict()
+    want = O.gan_train_epoch(og, od, G_opt, D_opt, loader, lambda x: O.encoder_forward(sd, x), seq, S, nd,
+                             div_factor=0.0, noises=noises)
+    np.testing.assert_allclose(got[:2], want[:2], rtol=2e-5)
+    np.testing.assert_allclose(got[2], want[2], rtol=5e-3)
