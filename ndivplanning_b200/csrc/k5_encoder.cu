@@ -123,6 +123,113 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const ConvP p) {
   }
 }
 
+// Large-batch variant for the NHWC layers (Cin % 16 == 0: a 16-wide k chunk stays inside one kernel cell, so its 16
+// input channels are contiguous and (kh, kw) is uniform over the CTA).  128 x 128 tile, 8 x 8 outputs per thread
+// (rows ti + 16 x, columns tj + 16 y: conflict-free 16-B shared loads with a 20-float row pitch), 16-B zero-fill
+// async copies, 4 stages, 2 CTAs per SM.  With one split the bias + ReLU epilogue writes the activation directly.
+constexpr int kBM = 128, kBN = 128, kBLD = 20, kBStages = 4;
+constexpr int kBStageFloats = (kBM + kBN) * kBLD;
+constexpr int kBSmem = kBStages * kBStageFloats * 4;
+
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* src, bool valid) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int n = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 2)
+conv_gemm_big_kernel(const ConvP p, const float* __restrict__ bias, int relu, float* __restrict__ direct_out) {
+  extern __shared__ __align__(16) float smem[];
+  const int t = threadIdx.x;
+  const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
+  const int k_begin = blockIdx.z * p.k_per_split;
+  const int k_end = min(p.K, k_begin + p.k_per_split);
+  const int ti = t >> 4, tj = t & 15;
+  const int lr = t >> 2, lv = (t & 3) * 4;          // loader: rows lr, lr + 64; floats lv..lv+3 of the chunk
+  float acc[8][8];
+#pragma unroll
+  for (int a = 0; a < 8; a++)
+#pragma unroll
+    for (int b = 0; b < 8; b++) acc[a][b] = 0.f;
+
+  int ih0[2], iw0[2];
+  const float* abase[2];
+  const float* wbase[2];
+  bool wok[2];
+#pragma unroll
+  for (int q = 0; q < 2; q++) {
+    const int m = m0 + lr + 64 * q;
+    if (m < p.M) {
+      const int b = m / (p.OH * p.OW), r = m % (p.OH * p.OW);
+      ih0[q] = (r / p.OW) * p.stride - p.pad; iw0[q] = (r % p.OW) * p.stride - p.pad;
+      abase[q] = p.in + (size_t)b * p.H * p.W * p.Cin + lv;
+    } else {
+      ih0[q] = -(1 << 20); iw0[q] = 0; abase[q] = p.in;
+    }
+    const int n = n0 + lr + 64 * q;
+    wok[q] = n < p.Cout;
+    wbase[q] = wok[q] ? p.Wt + (size_t)n * p.K + lv : p.Wt;
+  }
+  auto issue = [&](int stage, int k0) {
+    float* As = smem + stage * kBStageFloats;
+    float* Bs = As + kBM * kBLD;
+    const int cell = k0 / p.Cin, ci0 = k0 - cell * p.Cin;
+    const int kh = cell / p.KW, kw = cell - kh * p.KW;
+#pragma unroll
+    for (int q = 0; q < 2; q++) {
+      const int ih = ih0[q] + kh, iw = iw0[q] + kw;
+      const bool ok = ih >= 0 && ih < p.H && iw >= 0 && iw < p.W;
+      cp_async16(As + (lr + 64 * q) * kBLD + lv, ok ? abase[q] + ((size_t)ih * p.W + iw) * p.Cin + ci0 : p.in, ok);
+      cp_async16(Bs + (lr + 64 * q) * kBLD + lv, wok[q] ? wbase[q] + k0 : p.Wt, wok[q]);
+    }
+  };
+
+  const int nchunks = (k_end - k_begin) / kTK;
+#pragma unroll
+  for (int st = 0; st < kBStages - 1; st++) {
+    if (st < nchunks) issue(st, k_begin + st * kTK);
+    cp_async_commit();
+  }
+  for (int c = 0; c < nchunks; c++) {
+    cp_async_wait<kBStages - 2>();
+    __syncthreads();
+    if (c + kBStages - 1 < nchunks) issue((c + kBStages - 1) % kBStages, k_begin + (c + kBStages - 1) * kTK);
+    cp_async_commit();
+    const float* As = smem + (c % kBStages) * kBStageFloats;
+    const float* Bs = As + kBM * kBLD;
+#pragma unroll
+    for (int kq = 0; kq < 4; kq++) {
+      float4 a[8];
+#pragma unroll
+      for (int x = 0; x < 8; x++) a[x] = *reinterpret_cast<const float4*>(As + (ti + 16 * x) * kBLD + kq * 4);
+#pragma unroll
+      for (int y = 0; y < 8; y++) {
+        const float4 b = *reinterpret_cast<const float4*>(Bs + (tj + 16 * y) * kBLD + kq * 4);
+#pragma unroll
+        for (int x = 0; x < 8; x++) {
+          float v = acc[x][y];
+          v = fmaf(a[x].x, b.x, v); v = fmaf(a[x].y, b.y, v); v = fmaf(a[x].z, b.z, v); v = fmaf(a[x].w, b.w, v);
+          acc[x][y] = v;
+        }
+      }
+    }
+  }
+  float* out = direct_out ? direct_out : p.part + (size_t)blockIdx.z * p.M * p.Cout;
+#pragma unroll
+  for (int x = 0; x < 8; x++) {
+    const int m = m0 + ti + 16 * x;
+    if (m >= p.M) continue;
+#pragma unroll
+    for (int y = 0; y < 8; y++) {
+      const int n = n0 + tj + 16 * y;
+      if (n >= p.Cout) continue;
+      float v = acc[x][y];
+      if (direct_out) { v += __ldg(bias + n); if (relu) v = fmaxf(v, 0.f); }
+      out[(size_t)m * p.Cout + n] = v;
+    }
+  }
+}
+
 // out[m][n] = act( sum_s part[s][m][n] + bias[n] ), splits added in order
 __global__ void __launch_bounds__(256) conv_finalize_kernel(const float* __restrict__ part, int splits, size_t MN, int N,
                                                             const float* __restrict__ bias, int relu,
@@ -243,13 +350,38 @@ int ndp_encoder_forward(ndp_encoder* e, const float* images, int B, float* codes
     p.Wt = e->params + y.w_off;
     p.part = e->part;
     p.M = B * y.OH * y.OW; p.K = y.KH * y.KW * y.Cin;
+    float* out = l == e->L - 1 ? codes : e->act[l & 1];
+    const size_t MN = (size_t)p.M * p.Cout;
+    const int big_tiles = ((p.M + kBM - 1) / kBM) * ((p.Cout + kBN - 1) / kBN);
+    if (!p.nchw && p.Cin % kTK == 0 && big_tiles >= 32) {
+      static bool attr_set = false;
+      if (!attr_set) {
+        NDP_CUDA(cudaFuncSetAttribute(conv_gemm_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBSmem));
+        attr_set = true;
+      }
+      int splits = (2 * num_sms() + big_tiles - 1) / big_tiles;      // two resident CTAs per SM
+      if (big_tiles >= num_sms()) splits = 1;
+      const int max_by_k = p.K / (8 * kTK) > 0 ? p.K / (8 * kTK) : 1;
+      if (splits > max_by_k) splits = max_by_k;
+      while (splits > 1 && (size_t)splits * MN > e->part_floats) --splits;
+      p.k_per_split = ((p.K + splits - 1) / splits + kTK - 1) / kTK * kTK;
+      const int zs = (p.K + p.k_per_split - 1) / p.k_per_split;
+      conv_gemm_big_kernel<<<dim3((p.M + kBM - 1) / kBM, (p.Cout + kBN - 1) / kBN, zs), kThreads, kBSmem, s>>>(
+          p, e->params + y.b_off, y.relu, zs == 1 ? out : nullptr);
+      NDP_LAUNCH_CHECK();
+      if (zs > 1) {
+        conv_finalize_kernel<<<(unsigned)((MN + 255) / 256), 256, 0, s>>>(e->part, zs, MN, p.Cout,
+                                                                          e->params + y.b_off, y.relu, out);
+        NDP_LAUNCH_CHECK();
+      }
+      in = out;
+      continue;
+    }
     const int splits = plan_splits(p.M, p.Cout, p.K, e->part_floats);
     p.k_per_split = ((p.K + splits - 1) / splits + kTK - 1) / kTK * kTK;
     const int zs = (p.K + p.k_per_split - 1) / p.k_per_split;
     conv_gemm_kernel<<<dim3((p.M + kTM - 1) / kTM, (p.Cout + kTN - 1) / kTN, zs), kThreads, 0, s>>>(p);
     NDP_LAUNCH_CHECK();
-    float* out = l == e->L - 1 ? codes : e->act[l & 1];
-    const size_t MN = (size_t)p.M * p.Cout;
     conv_finalize_kernel<<<(unsigned)((MN + 255) / 256), 256, 0, s>>>(e->part, zs, MN, p.Cout, e->params + y.b_off,
                                                                       y.relu, out);
     NDP_LAUNCH_CHECK();

@@ -144,3 +144,17 @@ def test_gan_epoch_from_frames_matches_oracle(cuda, fused):
                              div_factor=0.0, noises=noises)
     np.testing.assert_allclose(got[:2], want[:2], rtol=2e-5)
     np.testing.assert_allclose(got[2], want[2], rtol=5e-3)
+
+
+def test_encoder_large_batch_kernels(cuda):
+    """B = 32 and a ragged B = 27 take the 128x128-tile kernel (fused bias + ReLU epilogue, split-K on the deep
+    layers); same bound against the fp64 oracle."""
+    enc = synthetic.make_image_encoder(seed=7)
+    fe = FusedEncoder(enc, max_images=32, device=cuda)
+    frames = synthetic.make_frames(32, seed=31)
+    with torch.no_grad():
+        want = O.encoder_forward(enc.state_dict(), frames.double()).view(32, 128)
+    got = fe(frames.to(cuda)).view(32, 128).cpu().double()
+    assert float((got - want).abs().max()) < 4 * FLOOR
+    got27 = fe(frames[:27].to(cuda)).view(27, 128).cpu().double()
+    assert float((got27 - want[:27]).abs().max()) < 4 * FLOOR
