@@ -39,7 +39,8 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-__global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const ConvP p) {
+__global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const ConvP p, const float* __restrict__ bias, int relu,
+                                                             float* __restrict__ direct_out) {
   __shared__ __align__(16) float As[kStages][kTK][kTM + 4];
   __shared__ __align__(16) float Bs[kStages][kTK][kTN + 4];
   const int t = threadIdx.x;
@@ -110,7 +111,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const ConvP p) {
         for (int y = 0; y < 4; y++) acc[x][y] = fmaf(a[x], b[y], acc[x][y]);
     }
   }
-  float* out = p.part + (size_t)blockIdx.z * p.M * p.Cout;
+  float* out = direct_out ? direct_out : p.part + (size_t)blockIdx.z * p.M * p.Cout;   // direct: one split, epilogue here
 #pragma unroll
   for (int x = 0; x < 4; x++) {
     const int m = m0 + ti * 4 + x;
@@ -118,7 +119,10 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const ConvP p) {
 #pragma unroll
     for (int y = 0; y < 4; y++) {
       const int n = n0 + tj * 4 + y;
-      if (n < p.Cout) out[(size_t)m * p.Cout + n] = acc[x][y];
+      if (n >= p.Cout) continue;
+      float v = acc[x][y];
+      if (direct_out) { v += __ldg(bias + n); if (relu) v = fmaxf(v, 0.f); }
+      out[(size_t)m * p.Cout + n] = v;
     }
   }
 }
@@ -240,6 +244,28 @@ __global__ void __launch_bounds__(256) conv_finalize_kernel(const float* __restr
   for (int s = 0; s < splits; s++) v += part[(size_t)s * MN + i];
   v += __ldg(bias + i % N);
   out[i] = relu ? fmaxf(v, 0.f) : v;
+}
+
+// same, for many splits over few outputs (conv6: up to 147 splits): a block takes 32 consecutive outputs, warp w adds
+// splits w, w + 8, ... (coalesced 128-B rows), then the 8 warp sums are added in warp order
+__global__ void __launch_bounds__(256) conv_finalize_wide_kernel(const float* __restrict__ part, int splits, size_t MN,
+                                                                 int N, const float* __restrict__ bias, int relu,
+                                                                 float* __restrict__ out) {
+  __shared__ float sm[8][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const size_t i = (size_t)blockIdx.x * 32 + lane;
+  float v = 0.f;
+  if (i < MN)
+    for (int s = w; s < splits; s += 8) v += part[(size_t)s * MN + i];
+  sm[w][lane] = v;
+  __syncthreads();
+  if (w == 0 && i < MN) {
+    float t = sm[0][lane];
+#pragma unroll
+    for (int k = 1; k < 8; k++) t += sm[k][lane];
+    t += __ldg(bias + i % N);
+    out[i] = relu ? fmaxf(t, 0.f) : t;
+  }
 }
 
 struct Layer {
@@ -380,10 +406,16 @@ int ndp_encoder_forward(ndp_encoder* e, const float* images, int B, float* codes
     const int splits = plan_splits(p.M, p.Cout, p.K, e->part_floats);
     p.k_per_split = ((p.K + splits - 1) / splits + kTK - 1) / kTK * kTK;
     const int zs = (p.K + p.k_per_split - 1) / p.k_per_split;
-    conv_gemm_kernel<<<dim3((p.M + kTM - 1) / kTM, (p.Cout + kTN - 1) / kTN, zs), kThreads, 0, s>>>(p);
+    conv_gemm_kernel<<<dim3((p.M + kTM - 1) / kTM, (p.Cout + kTN - 1) / kTN, zs), kThreads, 0, s>>>(
+        p, e->params + y.b_off, y.relu, zs == 1 ? out : nullptr);
     NDP_LAUNCH_CHECK();
-    conv_finalize_kernel<<<(unsigned)((MN + 255) / 256), 256, 0, s>>>(e->part, zs, MN, p.Cout, e->params + y.b_off,
-                                                                      y.relu, out);
+    if (zs == 1) { in = out; continue; }
+    if (zs >= 16)
+      conv_finalize_wide_kernel<<<(unsigned)((MN + 31) / 32), 256, 0, s>>>(e->part, zs, MN, p.Cout,
+                                                                          e->params + y.b_off, y.relu, out);
+    else
+      conv_finalize_kernel<<<(unsigned)((MN + 255) / 256), 256, 0, s>>>(e->part, zs, MN, p.Cout, e->params + y.b_off,
+                                                                        y.relu, out);
     NDP_LAUNCH_CHECK();
     in = out;
   }
