@@ -201,7 +201,7 @@ conv_gemm_big_kernel(const ConvP p, const float* __restrict__ bias, int relu, fl
     cp_async_commit();
     const float* As = smem + (c % kBStages) * kBStageFloats;
     const float* Bs = As + kBM * kBLD;
-#pragma unroll
+#pragma unroll 1
     for (int kq = 0; kq < 4; kq++) {
       float4 a[8];
 #pragma unroll
