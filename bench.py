@@ -358,6 +358,32 @@ def run_gpu(args):
                                          "kernel_launches_per_step": per_step,
                                          "losses_D_G_div": [float(v) for v in tr.losses.cpu()]}
             del cg, tr
+    # ---- image encoder in front of the path (first slice; context, rank 0 at N=1): CUDA-graph replays
+    # of ndp_encoder_forward at a plan's two frames, a trajectory's 8 and a GAN batch's 64
+    enc_runs = {}
+    if world == 1:
+        from ndivplanning_b200.encoder import FusedEncoder
+        fe = FusedEncoder(synthetic.make_image_encoder(seed=7), max_images=64, device=dev)
+        for Be in (2, 8, 64):
+            fr = synthetic.make_frames(Be, seed=3).to(dev)
+            l0 = launch_count()
+            fe(fr)
+            per_call = launch_count() - l0
+            cg, _codes = fe.capture(fr)
+            for _ in range(3):
+                cg.replay()
+            torch.cuda.synchronize()
+            n_ = 20
+            a, b = ev(), ev()
+            a.record()
+            for _ in range(n_):
+                cg.replay()
+            b.record(); torch.cuda.synchronize()
+            e_ms = a.elapsed_time(b) / n_
+            enc_runs[f"B{Be}"] = {"ms": e_ms, "images_per_s": Be / (e_ms * 1e-3),
+                                  "fp32_tflops": Be * 0.6224e9 / (e_ms * 1e-3) / 1e12, "kernel_launches": per_call}
+            del cg
+        del fe
     # ---- other precision modes of the same kernel family, for context (short runs)
     modes = {}
     if world == 1:
@@ -438,6 +464,9 @@ def run_gpu(args):
             "gan_train_step": {"what": "one iteration of train_gan.py:159-203 on encoded inputs (generator + discriminator "
                                        "forward/backward, BCE, ndiv, two Adam updates), CUDA-graph replay",
                                "shapes": gan_steps},
+            "image_encoder": {"what": "models/image_autoencoder.py Encoder forward (eval), [B,3,128,128] -> [B,128], exact "
+                                      "fp32 implicit-GEMM kernels, CUDA-graph replay; 0.622 GFLOP per image",
+                              "batches": enc_runs},
         }
         if world == 1:
             t0 = time.perf_counter()

@@ -88,3 +88,18 @@ class FusedEncoder:
                                                           C.c_void_p(codes[lo:lo + n].data_ptr()),
                                                           C.c_void_p(st.cuda_stream)))
         return codes.view(B, 128, 1, 1)
+
+    def capture(self, images: torch.Tensor):
+        """(graph, codes): one forward over the static `images` tensor as a CUDA graph; refill `images` in place and
+        replay() — `codes` [B,128,1,1] is overwritten by every replay.  B must be <= max_images."""
+        if images.shape[0] > self.max_images:
+            raise ValueError("capture: B=%d > max_images=%d" % (images.shape[0], self.max_images))
+        self(images)                                    # warm: one-time function attributes are set outside capture
+        g = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream(self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side):
+                codes = self(images)
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        return g, codes

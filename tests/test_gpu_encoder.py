@@ -158,3 +158,15 @@ def test_encoder_large_batch_kernels(cuda):
     assert float((got - want).abs().max()) < 4 * FLOOR
     got27 = fe(frames[:27].to(cuda)).view(27, 128).cpu().double()
     assert float((got27 - want[:27]).abs().max()) < 4 * FLOOR
+
+
+def test_encoder_cuda_graph_replay(cuda, fused):
+    """the forward is capturable: replays over refilled static frames are bit-identical to eager calls"""
+    enc, fe = fused
+    frames = synthetic.make_frames(8, seed=51).to(cuda)
+    static = frames[:2].clone()
+    g, codes = fe.capture(static)
+    for lo in (0, 2, 4):
+        static.copy_(frames[lo:lo + 2])
+        g.replay()
+        assert torch.equal(codes, fe(frames[lo:lo + 2]))
