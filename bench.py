@@ -292,8 +292,8 @@ def run_gpu(args):
     sampler = ClockSampler(local)
     sampler.start()
     run_resident(args.warmup, POOL - args.warmup)      # W warm-up steps: the same pipelined loop as the timed region
-    barrier()
-    gc.collect(); gc.disable()                         # no collector pauses inside the timed regions
+    gc.collect(); gc.disable()                         # no collector pauses inside the timed regions; collected BEFORE
+    barrier()                                          # the barrier so the ranks enter the timed region together
     n_before = launch_count()
     a, b, plans = run_resident(args.steps, 0)
     barrier()
