@@ -115,9 +115,16 @@ int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
  * = ndp_rollout_score followed by ndp_select for every precision; with NDP_PREC_F16_REFINE the bulk
  * costs are single-pass estimates, the NDP_REFINE_R best estimates per goal are re-rolled with split
  * operands (their cost / a0 entries are overwritten with the refined values) and the selection is taken
- * from the refined costs.  verified[g] (nullable) = 1 when no candidate outside the refine list can
- * belong to the top-k given |estimate - refined| <= eps * cost (eps <= 0: default 1e-3); always 1 for the
- * non-refined precisions.  topk <= 64 in refine mode.
+ * from the refined costs.  verified[g] (nullable) = 1 when no candidate outside the refine list can belong to the
+ * top-k under the error model of the estimate: |sqrt(estimate) - sqrt(exact)| <= eta for every candidate (an absolute
+ * bound on the terminal-state error, valid however close a candidate comes to the goal), with
+ *   eta = max( 4 x the largest |sqrt(estimate) - sqrt(refined)| observed on the NDP_REFINE_R re-rolled candidates of
+ *              this plan,  an a-priori first-order rounding floor from the forward model's row norms and T,
+ *              0.5 * eps * sqrt(estimate_R) when eps > 0 )
+ * and the test sqrt(k-th refined cost) < sqrt(R-th estimate) - eta.  eps <= 0: no caller floor (the default); eps > 0
+ * can only make the test stricter.  Always 1 for the non-refined precisions.  topk <= 64 in refine mode.
+ * The bound is derived from the data of the plan, not proven a priori: goals that fail it are NOT silently accepted
+ * (verified = 0) and ndp_plan_fallback re-rolls them exactly.
  * ndp_plan_fallback (same arguments, call after ndp_plan_select / _refine on the same stream): goals with
  * verified[g] == 0 are re-rolled over ALL K candidates with split operands and selected from those costs;
  * the decision is a device-side mask (no host round trip; thread blocks of verified goals exit at once) and
@@ -146,6 +153,11 @@ int ndp_plan_select_refine(ndp_planner* p, const float* e0, const float* goal, c
                            int topk, int64_t idx_base, float eps, float* cost, float* a0, uint64_t* packed_min,
                            int32_t* topk_idx, float* topk_cost, int32_t* verified, void* ws, size_t ws_bytes,
                            void* stream);
+
+/* after ndp_plan_select / _refine on `stream` with the same (G, K, topk, ws): info[g] = {margin, eta} in sqrt-cost
+ * units — margin = sqrt(R-th estimate) - eta - sqrt(k-th refined cost) (> 0 <=> verified), eta as defined above */
+int ndp_plan_verify_info(const ndp_planner* p, int G, int K, int topk, const void* ws, size_t ws_bytes, float* info,
+                         void* stream);
 
 /* best_action[g,:] = a0[g, idx(packed_min[g]) - idx_base, :]   (mpc_eval.py:165) */
 int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,

@@ -48,6 +48,7 @@ _PROTOS = {
     "ndp_plan_fallback": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_select_bulk": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_select_refine": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_plan_verify_info": (_i, [_vp, _i, _i, _i, _vp, _sz, _vp, _vp]),
     "ndp_gather_best_action": (_i, [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),
     "ndp_shard_pack": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
     "ndp_shard_merge": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -91,6 +91,39 @@ __global__ void linear_kernel(const float* __restrict__ in0, int K0, const float
   }
 }
 
+// errc[0] = a-priori floor of the single-pass (fp16 operand) estimate's error in sqrt-cost space per unit of state
+// RMS, first-order random-rounding model of the forward model:
+//   one step adds, per state element, a residual error of RMS  u * (2/sqrt 3) * rho1 * rho2 * x_rms
+//   (u = 2^-11 fp16 unit round-off; operands and weights of both layers rounded; rho1 = RMS row 2-norm of fwd.fc1,
+//   rho2 = max row 2-norm of fwd.fc2), T steps add in quadrature, sqrt(cost) = |s_T - goal| / sqrt(E) sees it / sqrt(E);
+//   kFloorSigmas of that.  The generator's share and the gain of the dynamics are left to the data-derived term.
+static constexpr float kFloorSigmas = 4.0f;
+__global__ void __launch_bounds__(1024)
+error_floor_kernel(const float* __restrict__ W1, const float* __restrict__ W2, int E, int H, int T, float* __restrict__ errc) {
+  __shared__ float s_sum[32], s_max[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  float sum1 = 0.f, max2 = 0.f;
+  for (size_t i = tid; i < (size_t)H * (E + 4); i += 1024) { const float v = W1[i]; sum1 = fmaf(v, v, sum1); }
+  for (int n = warp; n < E; n += 32) {                   // one warp per row of fwd.fc2 [E, H]
+    float r = 0.f;
+    for (int k = lane; k < H; k += 32) { const float v = W2[(size_t)n * H + k]; r = fmaf(v, v, r); }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    max2 = fmaxf(max2, r);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum1 += __shfl_xor_sync(0xffffffffu, sum1, o);
+  if (lane == 0) { s_sum[warp] = sum1; s_max[warp] = max2; }
+  __syncthreads();
+  if (tid == 0) {
+    float a = 0.f, m = 0.f;
+    for (int w = 0; w < 32; ++w) { a += s_sum[w]; m = fmaxf(m, s_max[w]); }
+    const float rho1 = sqrtf(a / (float)H), rho2 = sqrtf(m);
+    const float u = 1.f / 2048.f;
+    errc[0] = kFloorSigmas * u * 1.1547005f * rho1 * rho2 * sqrtf((float)T / (float)E);
+  }
+}
+
 }  // namespace ndp
 
 using namespace ndp;
@@ -119,7 +152,8 @@ extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) 
   const size_t sizes[] = {
       (size_t)p->nq * 2048,      // wstream
       (size_t)128 * E,           // w1g
-      128, (size_t)(nd > 0 ? nd : 1) * 128, 64, 128, 256, 4 * 256, 4, (size_t)4 * H, (size_t)H, (size_t)E};
+      128, (size_t)(nd > 0 ? nd : 1) * 128, 64, 128, 256, 4 * 256, 4, (size_t)4 * H, (size_t)H, (size_t)E,
+      64};                       // errc
   size_t total = 0;
   for (size_t s : sizes) total += (s + 63) / 64 * 64;
   // torch-layout copies for single-call APIs
@@ -138,6 +172,7 @@ extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) 
   p->wstream = take(sizes[0]); p->w1g = take(sizes[1]); p->b1 = take(sizes[2]); p->w1n = take(sizes[3]);
   p->b2 = take(sizes[4]); p->b3 = take(sizes[5]); p->b4 = take(sizes[6]); p->w5 = take(sizes[7]);
   p->b5 = take(sizes[8]); p->wf1a = take(sizes[9]); p->bf1 = take(sizes[10]); p->bf2 = take(sizes[11]);
+  p->errc = take(sizes[12]);
   for (int i = 0; i < 7; ++i) { p->Wt[i] = take(wt[i]); p->bt[i] = take(bt[i]); }
   *out = p;
   return NDP_OK;
@@ -199,6 +234,8 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
   NDP_CUDA(cudaMemcpyAsync(p->b5, p->bt[4], 4 * sizeof(float), cudaMemcpyDeviceToDevice, s));
   NDP_CUDA(cudaMemcpyAsync(p->bf1, p->bt[5], (size_t)H * sizeof(float), cudaMemcpyDeviceToDevice, s));
   NDP_CUDA(cudaMemcpyAsync(p->bf2, p->bt[6], (size_t)E * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  error_floor_kernel<<<1, 1024, 0, s>>>(p->Wt[5], p->Wt[6], E, H, p->d.T, p->errc);
+  NDP_LAUNCH_CHECK();
   if (p->d.precision != NDP_PREC_FP32) {
     if (p->tc) { tc_plan_destroy(p->tc); p->tc = nullptr; }
     if (p->tc_refine) { tc_plan_destroy(p->tc_refine); p->tc_refine = nullptr; }
@@ -303,7 +340,7 @@ extern "C" int ndp_forward_step(ndp_planner* p, const float* state, const float*
 static size_t align256(size_t v) { return (v + 255) / 256 * 256; }
 
 struct PlanWs {
-  size_t rollout, select, list, est, packed, total;
+  size_t rollout, select, list, est, packed, margin, total;
 };
 static int plan_ws_layout(const ndp_planner* p, int G, int K, int topk, PlanWs* w) {
   size_t r = 0, sel = 0;
@@ -316,7 +353,8 @@ static int plan_ws_layout(const ndp_planner* p, int G, int K, int topk, PlanWs* 
   w->list = p->tc_refine ? align256(GR * sizeof(int)) : 0;
   w->est = p->tc_refine ? align256(GR * sizeof(float)) : 0;
   w->packed = p->tc_refine ? align256((GR + (size_t)(G > 0 ? G : 1)) * sizeof(unsigned long long)) : 0;
-  w->total = w->rollout + w->select + w->list + w->est + w->packed;
+  w->margin = align256((size_t)(G > 0 ? G : 1) * 2 * sizeof(float));
+  w->total = w->rollout + w->select + w->list + w->est + w->packed + w->margin;
   return NDP_OK;
 }
 
@@ -354,13 +392,14 @@ static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const fl
   float* est = reinterpret_cast<float*>(base + w.rollout + w.select + w.list);
   unsigned long long* packed_c = reinterpret_cast<unsigned long long*>(base + w.rollout + w.select + w.list + w.est);
   unsigned long long* pm_est = packed_c + (size_t)G * R;
+  float* margin = reinterpret_cast<float*>(base + w.rollout + w.select + w.list + w.est + w.packed);
   if (phase & 1) {
     if (int rc = ndp_rollout_score(p, e0, goal, noise, G, K, cost, a0, nullptr, ws_roll, w.rollout, stream)) return rc;
     if (!p->tc_refine) {
       if (int rc = ndp_select(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws_sel, w.select, stream)) return rc;
       if (verified)   // K=0 <= R marks every goal verified: nothing was estimated
-        if (int rc = verify_refine(nullptr, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, 0, R,
-                                   topk, 0.f, verified, s)) return rc;
+        if (int rc = verify_refine(nullptr, nullptr, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min),
+                                   nullptr, p->d.E, p->errc, 0.f, G, 0, R, topk, verified, margin, s)) return rc;
       return NDP_OK;
     }
   }
@@ -386,8 +425,8 @@ static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const fl
     if (int rc = select_packed(packed_c, G, R, topk, (long long)idx_base,
                                reinterpret_cast<unsigned long long*>(packed_min), topk_idx, topk_cost, s)) return rc;
     if (verified) {
-      if (int rc = verify_refine(est, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), G, K, R, topk,
-                                 eps > 0.f ? eps : 1e-3f, verified, s)) return rc;
+      if (int rc = verify_refine(est, packed_c, topk_cost, reinterpret_cast<const unsigned long long*>(packed_min), goal,
+                                 p->d.E, p->errc, eps, G, K, R, topk, verified, margin, s)) return rc;
     }
   }
   return NDP_OK;
@@ -420,6 +459,19 @@ extern "C" int ndp_plan_select_refine(ndp_planner* p, const float* e0, const flo
                                       void* ws, size_t ws_bytes, void* stream) {
   return plan_select_impl(2, p, e0, goal, noise, G, K, topk, idx_base, eps, cost, a0, packed_min, topk_idx, topk_cost,
                           verified, ws, ws_bytes, stream);
+}
+
+extern "C" int ndp_plan_verify_info(const ndp_planner* p, int G, int K, int topk, const void* ws, size_t ws_bytes,
+                                    float* info, void* stream) {
+  NDP_CHECK_ARG(p && info && G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "plan_verify_info: bad arguments");
+  if (int rc = device_check()) return rc;
+  if (G == 0) return NDP_OK;
+  PlanWs w;
+  if (int rc = plan_ws_layout(p, G, K, topk, &w)) return rc;
+  if (!ws || ws_bytes < w.total) { set_error("plan_verify_info: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
+  const char* src = reinterpret_cast<const char*>(ws) + w.rollout + w.select + w.list + w.est + w.packed;
+  NDP_CUDA(cudaMemcpyAsync(info, src, (size_t)G * 2 * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return NDP_OK;
 }
 
 // ---- device sampler: U[0,1) noise of diverse_sampling (mpc_eval.py:78-83) drawn next to its

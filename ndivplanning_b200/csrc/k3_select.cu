@@ -174,25 +174,64 @@ __global__ void gather_best_kernel(const float* __restrict__ a0, const unsigned 
   }
 }
 
-// verified[g] = 1 when the refined selection is provably the selection of exact costs over ALL K candidates:
-// every candidate outside the refine list has estimate >= est_last, hence exact cost >= est_last*(1-eps);
-// if the k-th exact cost inside the list is strictly below that bound nothing outside can enter the top-k.
-__global__ void verify_refine_kernel(const float* __restrict__ est_topR, const float* __restrict__ exact_topk,
-                                     const unsigned long long* __restrict__ packed_min, int G, int K, int R, int topk,
-                                     float eps, int* __restrict__ verified) {
-  const int g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= G) return;
-  int ok;
-  if (K <= R) {
-    ok = 1;                                            // the list holds every candidate
-  } else {
-    const float bound = est_topR[(size_t)g * R + R - 1] * (1.f - eps);
+// verified[g] = 1 when the refined selection equals the selection from exact costs over ALL K candidates under the
+// error model of the single-pass estimate.  The model is an ABSOLUTE bound on the error of the
+// terminal state, i.e. an additive bound eta in sqrt-cost space (cost = |s_T - goal|^2 / E, so
+// |sqrt(est) - sqrt(exact)| <= |delta s_T| / sqrt(E) whatever the distance to the goal; a relative cost bound would
+// be unbounded as s_T approaches the goal).  eta is taken from THIS plan:
+//   eta = max( kVerifySafety * max_i |sqrt(est_i) - sqrt(refined_i)|   over the R refined candidates,
+//              errc * (rms(goal) + sqrt(est_R))                          a-priori first-order rounding floor,
+//              0.5 * eps * sqrt(est_R) )                                 caller's relative floor (eps <= 0: none)
+// Every candidate outside the list has estimate >= est_R, hence sqrt(exact) >= sqrt(est_R) - eta; if the k-th refined
+// cost is strictly below that bound nothing outside can enter the top-k.  One block of 128 threads per goal.
+static constexpr float kVerifySafety = 4.0f;
+__global__ void __launch_bounds__(128)
+verify_refine_kernel(const float* __restrict__ est_topR, const unsigned long long* __restrict__ packed_c,
+                     const float* __restrict__ exact_topk, const unsigned long long* __restrict__ packed_min,
+                     const float* __restrict__ goal, int E, const float* __restrict__ errc, float eps, int G, int K, int R,
+                     int topk, int* __restrict__ verified, float* __restrict__ margin) {
+  const int g = blockIdx.x, tid = threadIdx.x;
+  if (K <= R) {                                        // the list holds every candidate (or nothing was estimated)
+    if (tid == 0) { verified[g] = 1; if (margin) { margin[2 * g] = 0.f; margin[2 * g + 1] = 0.f; } }
+    return;
+  }
+  __shared__ float s_dev[4], s_g2[4];
+  __shared__ int s_bad[4];
+  float dev = 0.f, g2 = 0.f;
+  int bad = 0;
+  for (int i = tid; i < R; i += 128) {
+    const unsigned long long pc = packed_c[(size_t)g * R + i];
+    const float e = est_topR[(size_t)g * R + i];
+    if (pc == kPadKey) { bad = 1; continue; }          // K > R: every list slot must hold a candidate
+    const float r = key_to_float((uint32_t)(pc >> 32));
+    const float d = fabsf(sqrtf(e) - sqrtf(r));
+    if (!(d == d) || !(d < 3e38f)) bad = 1;            // NaN / inf anywhere: no proof
+    dev = fmaxf(dev, d);
+  }
+  for (int i = tid; i < E; i += 128) { const float v = __ldg(goal + (size_t)g * E + i); g2 = fmaf(v, v, g2); }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    dev = fmaxf(dev, __shfl_xor_sync(0xffffffffu, dev, o));
+    g2 += __shfl_xor_sync(0xffffffffu, g2, o);
+    bad |= __shfl_xor_sync(0xffffffffu, bad, o);
+  }
+  if ((tid & 31) == 0) { s_dev[tid >> 5] = dev; s_g2[tid >> 5] = g2; s_bad[tid >> 5] = bad; }
+  __syncthreads();
+  if (tid == 0) {
+    dev = fmaxf(fmaxf(s_dev[0], s_dev[1]), fmaxf(s_dev[2], s_dev[3]));
+    g2 = (s_g2[0] + s_g2[1]) + (s_g2[2] + s_g2[3]);
+    bad = s_bad[0] | s_bad[1] | s_bad[2] | s_bad[3];
+    const float sR = sqrtf(est_topR[(size_t)g * R + R - 1]);
+    float eta = kVerifySafety * dev;
+    eta = fmaxf(eta, __ldg(errc) * (sqrtf(g2 / (float)E) + sR));
+    if (eps > 0.f) eta = fmaxf(eta, 0.5f * eps * sR);
     float kth;
     if (topk > 0) kth = exact_topk[(size_t)g * topk + topk - 1];
     else kth = (packed_min[g] == kInvalidPacked) ? __int_as_float(0x7fc00000) : key_to_float((uint32_t)(packed_min[g] >> 32));
-    ok = (kth < bound) ? 1 : 0;                        // NaN compares false -> unverified
+    const float bound = sR - eta;
+    verified[g] = (!bad && sqrtf(kth) < bound) ? 1 : 0;     // NaN compares false -> unverified
+    if (margin) { margin[2 * g] = bound - sqrtf(kth); margin[2 * g + 1] = eta; }
   }
-  verified[g] = ok;
 }
 
 static void plan_chunks(int G, int K, int* chunks, int* chunk_len) {
@@ -292,9 +331,11 @@ int select_packed(const unsigned long long* packed, int G, int n, int topk, long
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
-int verify_refine(const float* est_topR, const float* exact_topk, const unsigned long long* pm, int G, int K, int R,
-                  int topk, float eps, int* verified, cudaStream_t s) {
-  verify_refine_kernel<<<(G + 127) / 128, 128, 0, s>>>(est_topR, exact_topk, pm, G, K, R, topk, eps, verified);
+int verify_refine(const float* est_topR, const unsigned long long* packed_c, const float* exact_topk,
+                  const unsigned long long* pm, const float* goal, int E, const float* errc, float eps, int G, int K, int R,
+                  int topk, int* verified, float* margin, cudaStream_t s) {
+  verify_refine_kernel<<<G, 128, 0, s>>>(est_topR, packed_c, exact_topk, pm, goal, E, errc, eps, G, K, R, topk, verified,
+                                         margin);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }

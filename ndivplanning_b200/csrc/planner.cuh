@@ -84,8 +84,9 @@ int mark_fallback(int* verified, int G, cudaStream_t s);
 
 int select_packed(const unsigned long long* packed, int G, int n, int topk, long long idx_base,
                   unsigned long long* pm, int* topk_idx, float* topk_cost, cudaStream_t s);
-int verify_refine(const float* est_topR, const float* exact_topk, const unsigned long long* pm, int G, int K, int R,
-                  int topk, float eps, int* verified, cudaStream_t s);
+int verify_refine(const float* est_topR, const unsigned long long* packed_c, const float* exact_topk,
+                  const unsigned long long* pm, const float* goal, int E, const float* errc, float eps, int G, int K, int R,
+                  int topk, int* verified, float* margin, cudaStream_t s);
 
 }  // namespace ndp
 
@@ -103,6 +104,8 @@ struct ndp_planner {
   float* scratch;         // activations for the single-call APIs, grown on demand
   size_t scratch_floats;
   int nq;
+  float* errc;            // device scalar: a-priori rounding floor of the single-pass estimate in sqrt-cost space, per unit
+                          // of state RMS (computed from the forward model's row norms at load; see verify_refine_kernel)
   ndp::TcPlan* tc;     // tensor-core plan (precision != fp32), else null
   ndp::TcPlan* tc_refine;  // f16x3 plan of the refine pass (NDP_PREC_F16_REFINE), else null
 };

@@ -32,6 +32,20 @@ class Plan:
     state_T: Optional[torch.Tensor] = None     # [G,K,E]
     verified: Optional[torch.Tensor] = None    # [G] int32: 1 = selection proven equal to the exact-cost selection
     ready: Optional[torch.cuda.Event] = None   # set when the plan was finished on a side stream (refine_stream=)
+    _info: Optional[tuple] = None              # (planner handle, G, K, topk, workspace) for verify_info()
+
+    def verify_info(self):
+        """[G,2] float32 {margin, eta} of the refine proof in sqrt-cost units (ndp_plan_verify_info): margin > 0 <=>
+        verified == 1; eta = the error bound assumed for the single-pass estimate.  None for non-refined plans."""
+        if self._info is None:
+            return None
+        h, G, K, topk, ws = self._info
+        dev = self.cost.device
+        self.wait()
+        out = torch.empty(G, 2, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(lib().ndp_plan_verify_info(h, G, K, topk, ptr(ws), ws.numel(), ptr(out), stream_ptr(dev)))
+        return out
 
     def wait(self, stream=None):
         """make `stream` (default: current) wait until the plan's tensors are final"""
@@ -65,7 +79,11 @@ def unpack_index(packed: torch.Tensor) -> torch.Tensor:
 
 
 class FusedPlanner:
-    def __init__(self, generator, fwd_model, *, horizon: int, precision: str = "fp32", device=None):
+    def __init__(self, generator, fwd_model, *, horizon: int, precision: Optional[str] = None, device=None):
+        """precision: None (default) = "f16+refine" — tcgen05 bulk estimate of all K, split-operand re-roll of the 128
+        best, data-derived proof per goal, exact re-roll of the goals that cannot be proven (`plan(fallback=True)`) —
+        whenever the shape is one the tensor-core kernels take (E=128, noise_dim<=15, H a multiple of 128 up to
+        2048), else "fp32".  "fp32" (CUDA-core, every cost fp32), "f16x3", "f16x2", "f16" by request."""
         g, f = generator.state_dict(), fwd_model.state_dict()
         names = ["fc1", "fc2", "fc3", "fc4", "fc5"]
         Ws = [g[f"{n}.weight"] for n in names] + [f["fc1.weight"], f["fc2.weight"]]
@@ -84,6 +102,8 @@ class FusedPlanner:
             raise _lib.NdpError("CUDA is not available; FusedPlanner has no CPU fallback")
         self.device = torch.device(device)
         self.E, self.H, self.nd, self.T = E, H, nd, int(horizon)
+        if precision is None:
+            precision = "f16+refine" if (E == 128 and 0 <= nd <= 15 and H % 128 == 0 and H <= 2048) else "fp32"
         prec = {"fp32": _lib.PREC_FP32, "f16x3": _lib.PREC_F16X3, "f16x2": _lib.PREC_F16X2,
                 "f16": _lib.PREC_F16, "f16+refine": _lib.PREC_F16_REFINE}[precision]
         self.precision = precision
@@ -185,14 +205,16 @@ class FusedPlanner:
                         t_.record_stream(refine_stream)
                 ready = torch.cuda.Event()
                 ready.record(refine_stream)
-                return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified, ready)
+                return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified, ready,
+                            (self._h, G, K, topk, ws) if self.precision == "f16+refine" else None)
             with torch.cuda.device(dev):
                 check(lib().ndp_plan_select(*args, stream_ptr(dev)))
                 if fallback and self.precision == "f16+refine":
                     check(lib().ndp_plan_fallback(*args, stream_ptr(dev)))
                 check(lib().ndp_gather_best_action(ptr(a0), ptr(packed), G, K, idx_base, ptr(best_action),
                                                    ptr(best_idx), stream_ptr(dev)))
-            return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified)
+            return Plan(best_idx, best_action, packed, cost, a0, tk_idx, tk_cost, sT, verified, None,
+                        (self._h, G, K, topk, ws) if self.precision == "f16+refine" else None)
         best_action = torch.zeros(G, 4, dtype=torch.float32, device=self.device)
         best_idx = torch.empty(G, dtype=torch.int32, device=self.device)
         with torch.cuda.device(self.device):
@@ -254,6 +276,7 @@ class PlanRing:
         self.planner, self.G, self.K, self.topk, self.depth, self.idx_base, self.comm = \
             planner, G, K, topk, depth, idx_base, comm
         self.count = 0
+        self.vlog = None                              # optional [n,G] int32 log of every plan's `verified` (log_verified)
         self.streams = [torch.cuda.Stream(device=dev, priority=-1) for _ in range(n_streams)]
         self.bulk_streams = [torch.cuda.Stream(device=dev) for _ in range(2)]
         self.inputs_ready = [torch.cuda.Event() for _ in range(depth)]
@@ -281,7 +304,7 @@ class PlanRing:
             s.gather = (ptr(s.a0), ptr(s.packed), G, K, idx_base, ptr(s.best_action), ptr(s.best_idx))
             if comm is None:
                 s.plan = Plan(s.best_idx, s.best_action, s.packed, s.cost, s.a0, s.tk_idx, s.tk_cost, None, s.verified,
-                              s.ready)
+                              s.ready, (planner._h, G, K, topk, s.ws) if planner.precision == "f16+refine" else None)
             else:
                 W = 4 + topk
                 s.rec = torch.empty(G, W, dtype=i64, device=dev)
@@ -296,6 +319,14 @@ class PlanRing:
                            ptr(g_tkc), ptr(g_ver))
                 s.plan = Plan(g_idx, g_act, g_packed, s.cost, s.a0, g_tki, g_tkc, None, g_ver, s.ready)
             self.slots.append(s)
+
+    def log_verified(self, n: int) -> torch.Tensor:
+        """keep the `verified` flags of the next n plans: plan i's tail copies its [G] flags into row i % n of the
+        returned device tensor (one 4*G-byte device copy on the tail stream, no host synchronisation), so a pipelined
+        loop can account for every plan after the fact although slots are reused"""
+        self.vlog = torch.full((int(n), self.G), -1, dtype=torch.int32, device=self.planner.device)
+        self.vlog_base = self.count
+        return self.vlog
 
     def plan(self, e0, goal, noise) -> Plan:
         """mpc_eval.py:124-165 for e0, goal [G,E] and noise [T,G,K,nd]; returns the slot's Plan (see class doc)"""
@@ -336,6 +367,9 @@ class PlanRing:
                 check(L.ndp_shard_pack(*s.pack, sp))
                 check(L.ndp_comm_allgather_bytes(self.comm._h, ptr(s.rec), ptr(s.rec_all), s.rec.numel() * 8, sp))
                 check(L.ndp_shard_merge(*s.merge, sp))
+            if self.vlog is not None:
+                with torch.cuda.stream(side):
+                    self.vlog[(i - self.vlog_base) % self.vlog.shape[0]].copy_(s.plan.verified, non_blocking=True)
             s.ready.record(side)
         return s.plan
 

@@ -8,8 +8,9 @@ MPC, one goal  : candidates are independent until the argmin (mpc_eval.py:125,15
                  (allreduce_min_packed / merge_topk are the same reduction written with stock
                  collectives; the gloo tests use them to pin the key/tie-break semantics.)
 MPC, many goals: shard goals, no collective.
-ndiv           : rows are sharded; row sums are all-gathered between pass 1 and pass 2
-                 (the backward needs s_j for every j), loss/grad partials are summed.
+ndiv           : rows are sharded in 128-aligned blocks; the [sx|sz] row sums are all-gathered between pass 1 and
+                 pass 2 (the backward needs s_j for every j), then ONE all-gather of [grad rows | loss partial]
+                 (ShardedNdiv; libndivplan's own communicator, caller's stream).
 The collectives are latency-bound (8 B .. 0.5 MB).
 """
 import torch
@@ -170,19 +171,87 @@ class ShardedPlanner:
         return Plan(best_idx, best_action, packed, p.cost, p.a0, tk_idx, tk_cost, p.state_T, verified, ready)
 
 
-def sharded_ndiv_loss(x: torch.Tensor, z: torch.Tensor, group=None, want_grad: bool = True):
-    """Row-sharded ndiv forward+backward: x [N,k,Dx], z [N,k,Dz] replicated on every rank.
-    Returns (loss[()] summed over all rows, grad_x [N,k,Dx] complete on every rank)."""
-    rank, world = dist.get_rank(group), dist.get_world_size(group)
-    N, k, _ = x.shape
-    row0, rows = shard_range(k, rank, world)
-    sx = torch.zeros(N, k, dtype=torch.float32, device=x.device)
-    sz = torch.zeros_like(sx)
-    _div.ndiv_rowsums(x, z, row0, rows, sx, sz)
-    s = torch.stack([sx, sz])                        # rows outside the block are 0 -> sum == gather
-    dist.all_reduce(s, group=group)                  # 2*N*k*4 bytes (32 KB at k=4096)
-    loss, grad = _div.ndiv_loss_grad(x, z, s[0].contiguous(), s[1].contiguous(), want_grad, row0, rows)
-    dist.all_reduce(loss, group=group)
-    if want_grad:
-        dist.all_reduce(grad, group=group)           # row blocks are disjoint: sum == gather
-    return loss.reshape(()), grad
+def ndiv_row_block(k: int, rank: int, world: int):
+    """row block of rank `rank`: equal blocks rounded up to 128 rows (the Gram kernels' tile; keeps the tensor-core
+    path), the last ranks may own fewer rows or none.  Returns (row0, rows, block)."""
+    block = (-(-k // world) + 127) // 128 * 128
+    row0 = min(k, rank * block)
+    return row0, min(k, row0 + block) - row0, block
+
+
+class ShardedNdiv:
+    """Row-sharded ndiv loss forward + backward (reference diversity.py:12-19,36-41): x, z are
+    replicated, rank r owns a 128-aligned row block.  Two collectives per call, both on libndivplan's own NCCL
+    communicator and on the CALLER's stream (CUDA-graph capturable, no torch.distributed in the data path):
+
+        pass 1 (ndp_ndiv_rowsums, local rows)      -> all-gather of the rank's [sx | sz] block  (8*N*block bytes)
+        pass 2 (ndp_ndiv_loss_grad, local rows)    -> all-gather of [grad_x rows | loss partial] (4*N*block*Dx + 4)
+
+    The loss is the sum of the gathered partials in rank order, so every rank holds the same bits (no all-reduce
+    rounding-order ambiguity) and — row blocks being 128-aligned — the same bits as the single-GPU call.  Buffers are
+    allocated once per (N, k, Dx, Dz)."""
+
+    def __init__(self, comm: Comm, N: int, k: int, Dx: int, Dz: int):
+        import ctypes as C
+        self.comm, self.N, self.k, self.Dx, self.Dz = comm, N, k, Dx, Dz
+        dev = comm.device
+        self.row0, self.rows, self.block = ndiv_row_block(k, comm.rank, comm.world)
+        W, B, f32 = comm.world, self.block, torch.float32
+        self.sx = torch.zeros(N, W * B, dtype=f32, device=dev)          # padded to W*B rows; [:, :k] is the result
+        self.sz = torch.zeros(N, W * B, dtype=f32, device=dev)
+        self.s_send = torch.zeros(2, N, B, dtype=f32, device=dev)
+        self.s_recv = torch.empty(W, 2, N, B, dtype=f32, device=dev)
+        self.g_send = torch.zeros(N * B * Dx + 1, dtype=f32, device=dev)
+        self.g_recv = torch.empty(W, N * B * Dx + 1, dtype=f32, device=dev)
+        self.grad = torch.zeros(N, k, Dx, dtype=f32, device=dev)        # local rows written by pass 2
+        self.loss_part = torch.zeros(1, dtype=f32, device=dev)
+        n = C.c_size_t()
+        check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, Dz, C.byref(n)))
+        self.ws = torch.empty(max(n.value, 256), dtype=torch.uint8, device=dev)
+
+    def __call__(self, x: torch.Tensor, z: torch.Tensor, want_grad: bool = True):
+        """x [N,k,Dx], z [N,k,Dz] on this rank's device -> (loss[()], grad_x [N,k,Dx] | None), complete on every rank"""
+        N, k, Dx, Dz, B, W = self.N, self.k, self.Dx, self.Dz, self.block, self.comm.world
+        dev = self.comm.device
+        L, st = lib(), stream_ptr(dev)
+        r0, rows = self.row0, self.rows
+        sxk, szk = self.sx[:, :k], self.sz[:, :k]
+        with torch.cuda.device(dev):
+            if rows > 0:
+                sx_l = torch.empty(N, k, dtype=torch.float32, device=dev)
+                sz_l = torch.empty(N, k, dtype=torch.float32, device=dev)
+                check(L.ndp_ndiv_rowsums(ptr(x), ptr(z), N, k, Dx, Dz, r0, rows, ptr(sx_l), ptr(sz_l), ptr(self.ws),
+                                         self.ws.numel(), st))
+                self.s_send[0, :, :rows].copy_(sx_l[:, r0:r0 + rows])
+                self.s_send[1, :, :rows].copy_(sz_l[:, r0:r0 + rows])
+            check(L.ndp_comm_allgather_f32(self.comm._h, ptr(self.s_send), ptr(self.s_recv), self.s_send.numel(), st))
+            sx = self.s_recv[:, 0].permute(1, 0, 2).reshape(N, W * B)[:, :k].contiguous()
+            sz = self.s_recv[:, 1].permute(1, 0, 2).reshape(N, W * B)[:, :k].contiguous()
+            if rows > 0:
+                check(L.ndp_ndiv_loss_grad(ptr(x), ptr(z), ptr(sx), ptr(sz), N, k, Dx, Dz, _div.MARGIN, r0, rows,
+                                           ptr(self.loss_part), ptr(self.grad) if want_grad else None, ptr(self.ws),
+                                           self.ws.numel(), st))
+                if want_grad:
+                    self.g_send[:-1].view(N, B, Dx)[:, :rows].copy_(self.grad[:, r0:r0 + rows])
+                self.g_send[-1:].copy_(self.loss_part)
+            else:
+                self.g_send.zero_()
+            cnt = self.g_send.numel() if want_grad else 1
+            send = self.g_send if want_grad else self.g_send[-1:]
+            recv = self.g_recv if want_grad else self.g_recv.view(-1)[:W]
+            check(L.ndp_comm_allgather_f32(self.comm._h, ptr(send), ptr(recv), cnt, st))
+            if want_grad:
+                parts = self.g_recv[:, -1]
+                grad = self.g_recv[:, :-1].view(W, N, B, Dx).permute(1, 0, 2, 3).reshape(N, W * B, Dx)[:, :k].contiguous()
+            else:
+                parts, grad = recv, None
+            loss = parts[0].clone()
+            for r in range(1, W):                       # fixed (rank) order: identical bits on every rank
+                loss = loss + parts[r]
+        return loss.reshape(()), grad
+
+
+def sharded_ndiv_loss(x: torch.Tensor, z: torch.Tensor, comm: Comm, want_grad: bool = True):
+    """one-shot convenience around ShardedNdiv (allocates its buffers per call)"""
+    N, k, Dx = x.shape
+    return ShardedNdiv(comm, N, k, Dx, z.shape[2])(x, z, want_grad)

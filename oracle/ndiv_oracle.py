@@ -17,7 +17,7 @@ from torch.nn import functional as F
 
 __all__ = [
     "compute_pairwise", "compute_pair_distance", "compute_pairwise_divergence",
-    "ndiv_grad_analytic", "GeneratorMLP", "LatentForward", "draw_noise",
+    "ndiv_grad_analytic", "ndiv_fwd_bwd_chunked", "GeneratorMLP", "LatentForward", "draw_noise",
     "diverse_sampling", "mpc_rollout", "select_first_min", "select_topk",
     "mpc_plan", "pack_key", "closed_loop_eval", "ndiv_fwd_bwd", "ActionDiscriminator", "gan_optimizers",
     "gan_train_step", "gan_train_epoch", "philox4x32_10", "sample_uniform",
@@ -76,6 +76,43 @@ def ndiv_grad_analytic(x: torch.Tensor, z: torch.Tensor) -> torch.Tensor:
     W = -(M / sx + M.transpose(1, 2) / sx.transpose(1, 2))
     What = torch.where(dx > 0, W / dx, torch.zeros_like(W))
     return x * What.sum(2, keepdim=True) - What @ x
+
+
+@torch.no_grad()
+def ndiv_fwd_bwd_chunked(x: torch.Tensor, z: torch.Tensor, block: int = 512, want_grad_z: bool = False):
+    """compute_pairwise_divergence + its gradient (diversity.py:36-41 under autograd) for ONE group at sizes where
+    the reference's [k,k,C] difference tensor does not fit in RAM (BASELINE cfg3: k=4096 -> 4.3 GB in fp64):
+    same formulas as ndiv_grad_analytic, evaluated in row blocks of `block` rows.  x [k,Dx], z [k,Dz] (any float
+    dtype; use fp64 for the arbiter).  Returns (loss, grad_x, sx, sz[, grad_z]); pinned against autograd by
+    tests/test_oracle_golden.py::test_chunked_ndiv_equals_autograd."""
+    k = x.shape[0]
+    sx = torch.empty(k, dtype=x.dtype)
+    sz = torch.empty(k, dtype=x.dtype)
+    for r0 in range(0, k, block):
+        r1 = min(k, r0 + block)
+        sx[r0:r1] = torch.norm(x[r0:r1, None, :] - x[None, :, :], p=2, dim=2).sum(1)
+        sz[r0:r1] = torch.norm(z[r0:r1, None, :] - z[None, :, :], p=2, dim=2).sum(1)
+    loss = torch.zeros((), dtype=x.dtype)
+    gx = torch.zeros_like(x)
+    gz = torch.zeros_like(z)
+    for r0 in range(0, k, block):
+        r1 = min(k, r0 + block)
+        dx = torch.norm(x[r0:r1, None, :] - x[None, :, :], p=2, dim=2)          # [b,k]
+        dz = torch.norm(z[r0:r1, None, :] - z[None, :, :], p=2, dim=2)
+        h_ij = MARGIN * dz / sz[r0:r1, None] - dx / sx[r0:r1, None]               # row i normalisers
+        h_ji = MARGIN * dz / sz[None, :] - dx / sx[None, :]                       # d is symmetric: h_ji uses row j's
+        loss = loss + F.relu(h_ij).sum()
+        M_ij, M_ji = (h_ij > 0).to(x.dtype), (h_ji > 0).to(x.dtype)
+        W = -(M_ij / sx[r0:r1, None] + M_ji / sx[None, :])
+        What = torch.where(dx > 0, W / dx, torch.zeros_like(W))
+        gx[r0:r1] = x[r0:r1] * What.sum(1, keepdim=True) - What @ x
+        if want_grad_z:
+            Wz = MARGIN * (M_ij / sz[r0:r1, None] + M_ji / sz[None, :])
+            Wzh = torch.where(dz > 0, Wz / dz, torch.zeros_like(Wz))
+            gz[r0:r1] = z[r0:r1] * Wzh.sum(1, keepdim=True) - Wzh @ z
+    if want_grad_z:
+        return loss, gx, sx, sz, gz
+    return loss, gx, sx, sz
 
 
 # ----------------------------------------------------------------------------

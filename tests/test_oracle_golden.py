@@ -150,3 +150,18 @@ def test_encoder_fold_matches_unfolded():
             if i < 5:
                 x = torch.relu(x)
     assert float((x - want).abs().max()) < 2e-6       # folded weights are rounded to fp32 once
+
+
+def test_chunked_ndiv_equals_autograd():
+    """the row-blocked fp64 evaluation used as the arbiter at BASELINE cfg3 size equals diversity.py under autograd
+    (restated in oracle.compute_pairwise_divergence, itself pinned on the reference above), incl. d loss / d codes"""
+    torch.manual_seed(3)
+    x = torch.randn(1, 300, 12, dtype=torch.float64, requires_grad=True)
+    z = torch.rand(1, 300, 5, dtype=torch.float64, requires_grad=True)
+    loss = O.compute_pairwise_divergence(x, z)
+    loss.backward()
+    l2, gx, sx, sz, gz = O.ndiv_fwd_bwd_chunked(x.detach()[0], z.detach()[0], block=64, want_grad_z=True)
+    np.testing.assert_allclose(l2.item(), loss.item(), rtol=1e-12)
+    np.testing.assert_allclose(gx.numpy(), x.grad[0].numpy(), rtol=1e-9, atol=1e-14)
+    np.testing.assert_allclose(gz.numpy(), z.grad[0].numpy(), rtol=1e-9, atol=1e-14)
+    np.testing.assert_allclose(sx.numpy(), O.compute_pairwise(x.detach())[0].sum(1).numpy(), rtol=1e-12)

@@ -13,7 +13,7 @@ import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from ndivplanning_b200 import FusedPlanner, diversity, synthetic  # noqa: E402
-from ndivplanning_b200.sharded import ShardedPlanner, shard_range, sharded_ndiv_loss  # noqa: E402
+from ndivplanning_b200.sharded import Comm, ShardedNdiv, ShardedPlanner, shard_range  # noqa: E402
 
 
 def main():
@@ -49,16 +49,25 @@ def main():
         print(f"[rank {rank}] {prec} G={G} K={K} topk={topk}: sharded==single {same} best={sp.best_idx.tolist()} "
               f"verified={sp.verified.tolist()}", flush=True)
         ok &= same
-    x, z = synthetic.make_ndiv_inputs(2, 1000, 32, 16)
-    xg = x.to(dev).requires_grad_(True)
-    loss = diversity.compute_pairwise_divergence(xg, z.to(dev))
-    loss.backward()
-    sl, sg = sharded_ndiv_loss(x.to(dev), z.to(dev))
-    torch.cuda.synchronize()
-    lerr = abs(sl.item() - loss.item()) / abs(loss.item())
-    gerr = (sg - xg.grad).abs().max().item() / xg.grad.abs().max().item()
-    print(f"[rank {rank}] ndiv sharded vs single: loss rel {lerr:.2e} grad rel {gerr:.2e}", flush=True)
-    ok &= lerr < 1e-5 and gerr < 1e-5
+    comm = Comm(dev)
+    for (N, k, Dx, Dz) in ((2, 1000, 32, 16), (1, 4096, 32, 16), (3, 200, 12, 5)):
+        x, z = synthetic.make_ndiv_inputs(N, k, Dx, Dz)
+        xg = x.to(dev).requires_grad_(True)
+        loss = diversity.compute_pairwise_divergence(xg, z.to(dev))
+        loss.backward()
+        op = ShardedNdiv(comm, N, k, Dx, Dz)
+        sl, sg = op(x.to(dev), z.to(dev))
+        sl2, _ = op(x.to(dev), z.to(dev), want_grad=False)
+        torch.cuda.synchronize()
+        lerr = abs(sl.item() - loss.item()) / abs(loss.item())
+        gerr = (sg - xg.grad).abs().max().item() / xg.grad.abs().max().item()
+        bit = torch.equal(sg, xg.grad)
+        print(f"[rank {rank}] ndiv N={N} k={k} sharded vs single: loss rel {lerr:.2e} grad rel {gerr:.2e} "
+              f"grad bit-equal {bit} loss-only equal {sl2.item() == sl.item()}", flush=True)
+        ok &= lerr < 1e-5 and gerr < 1e-5 and sl2.item() == sl.item()
+        if k >= 256 and Dx <= 32:              # Gram path, 128-aligned row blocks: same bits as the single-GPU call
+            ok &= bit
+    comm.close()
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     dist.barrier()
