@@ -433,7 +433,7 @@ def run_gpu(args):
     # every timed plan accounted for; unverified ones are re-planned with the exact fallback and their cost reported
     verify = {"plans": args.steps * G, "verified1": vflags.count(1), "fallback2": vflags.count(2),
               "unverified0": vflags.count(0), "not_logged": vflags.count(-1),
-              "bound": "eta = max(4 x max |sqrt(est)-sqrt(refined)| over the 128 re-rolled candidates, a-priori rounding floor) "
+              "bound": "eta = max(3 x max |sqrt(est)-sqrt(refined)| over the 128 re-rolled candidates, a-priori rounding floor) "
                        "in sqrt-cost units (DESIGN.md 3.1); {margin, eta} of the last timed plan",
               "last_plan_margin_eta": vinfo}
     if verify["unverified0"] and world == 1:

@@ -118,7 +118,7 @@ int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
  * from the refined costs.  verified[g] (nullable) = 1 when no candidate outside the refine list can belong to the
  * top-k under the error model of the estimate: |sqrt(estimate) - sqrt(exact)| <= eta for every candidate (an absolute
  * bound on the terminal-state error, valid however close a candidate comes to the goal), with
- *   eta = max( 4 x the largest |sqrt(estimate) - sqrt(refined)| observed on the NDP_REFINE_R re-rolled candidates of
+ *   eta = max( 3 x the largest |sqrt(estimate) - sqrt(refined)| observed on the NDP_REFINE_R re-rolled candidates of
  *              this plan,  an a-priori first-order rounding floor from the forward model's row norms and T,
  *              0.5 * eps * sqrt(estimate_R) when eps > 0 )
  * and the test sqrt(k-th refined cost) < sqrt(R-th estimate) - eta.  eps <= 0: no caller floor (the default); eps > 0
@@ -199,8 +199,12 @@ int ndp_ndiv_forward_backward(const float* x, const float* z, int N, int k, int 
                               void* stream);
 /* the operator as a forward / backward pair (what a torch.autograd.Function binds):
  * forward  -> loss[0] + the saved normalisers sx, sz [N,k];
- * backward -> grad_x = grad_loss[0] * d loss / d x (grad_loss: device scalar, NULL = 1); grad_z must be NULL (the call
- *             site never differentiates the latent codes: train_gan.py:193-196); loss_scratch: one device float */
+ * backward -> grad_x (nullable) = grad_loss[0] * d loss / d x (grad_loss: device scalar, NULL = 1); grad_z (nullable) =
+ *             grad_loss[0] * d loss / d z, i.e. what autograd gives when `codes.requires_grad` (diversity.py:36-41; the
+ *             reference's own call site passes raw noise and never asks for it, train_gan.py:193-196) — exact direct
+ *             differences through an [N,k,k] scratch: ws must then hold ndp_ndiv_gradz_workspace_bytes();
+ *             loss_scratch: one device float */
+int ndp_ndiv_gradz_workspace_bytes(int N, int k, int Dx, int Dz, size_t* bytes);
 int ndp_ndiv_forward(const float* x, const float* z, int N, int k, int Dx, int Dz, float margin, float* loss,
                      float* sx, float* sz, void* ws, size_t ws_bytes, void* stream);
 int ndp_ndiv_backward(const float* x, const float* z, const float* sx, const float* sz, int N, int k, int Dx, int Dz,

@@ -57,6 +57,7 @@ _PROTOS = {
     "ndp_ndiv_loss_grad": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "ndp_ndiv_forward_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_ndiv_forward": (_i, [_vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_ndiv_gradz_workspace_bytes": (_i, [_i, _i, _i, _i, C.POINTER(_sz)]),
     "ndp_ndiv_backward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_pairwise": (_i, [_vp, _i, _i, _i, _i, _vp, _vp]),
     "ndp_pairwise_backward": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),

@@ -661,10 +661,11 @@ size_t gram_ws_bytes(int N, int k, int Dx, int Dz);
 int gram_loss_parts(int N, int k);
 int gram_js(int N, int k);
 int gram_prepare(const float* x, const float* z, int N, int k, int Dx, int Dz, void* ws, cudaStream_t s);
-int* gram_flag(void* ws);
-int gram_rowsums(int N, int k, int Dx, int Dz, int row0, int rows, void* ws, float* psx, float* psz, cudaStream_t s);
-int gram_loss_grad(const float* x, const float* sx, const float* sz, int N, int k, int Dx, int Dz, float margin, int row0,
-                   int rows, void* ws, float* loss_part, float* gpart, bool check, cudaStream_t s);
+int gram_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz, int row0, int rows, void* ws, float* sx,
+                 float* sz, float* psx, float* psz, cudaStream_t s);
+int gram_loss_grad(const float* x, const float* z, const float* sx, const float* sz, int N, int k, int Dx, int Dz,
+                   float margin, int row0, int rows, void* ws, float* loss_part, float* gpart, float* loss, float* grad_x,
+                   cudaStream_t s);
 
 // j-split plan: depends on (N, k, Dx) only so that row-blocked (sharded) calls reproduce the full call bit for bit
 struct NdivPlan { int ntiles, tps, JS; };
@@ -739,38 +740,25 @@ static int exact_rowsums(const float* x, const float* z, int N, int k, int Dx, i
   return NDP_OK;
 }
 
-// tensor-core pass 1 on prepared images (gram_prepare): partial sums of the column splits, then their reduction
-static int tc_rowsums(int N, int k, int Dx, int Dz, int row0, int rows, float* sx, float* sz, char* b, const NdivWs& w,
-                      cudaStream_t s) {
+// tensor-core pass 1 on prepared images (gram_prepare): ONE launch, final row sums (the column splits are combined by
+// the last CTA of each row tile)
+static int tc_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz, int row0, int rows, float* sx,
+                      float* sz, char* b, const NdivWs& w, cudaStream_t s) {
   void* gws = b + w.part + w.psum;
   const int JS = gram_js(N, k);
-  float* psx = JS > 1 ? reinterpret_cast<float*>(b + w.part) : sx;
-  float* psz = JS > 1 ? psx + (size_t)JS * N * k : sz;
-  if (int rc = gram_rowsums(N, k, Dx, Dz, row0, rows, gws, psx, psz, s)) return rc;
-  if (JS > 1) {
-    ndiv_rowsum_reduce_kernel<<<(N * rows + 255) / 256, 256, 0, s>>>(psx, psz, N, k, JS, row0, rows, sx, sz, nullptr);
-    NDP_LAUNCH_CHECK();
-  }
-  return NDP_OK;
+  float* psx = reinterpret_cast<float*>(b + w.part);
+  float* psz = psx + (size_t)JS * N * k;
+  return gram_rowsums(x, z, N, k, Dx, Dz, row0, rows, gws, sx, sz, psx, psz, s);
 }
 
-// tensor-core pass 2 on prepared images: loss partials + gradient partials, their reductions
-static int tc_loss_grad(const float* x, const float* sx, const float* sz, int N, int k, int Dx, int Dz, float margin,
-                        int row0, int rows, float* loss, float* grad_x, char* b, const NdivWs& w, bool check,
+// tensor-core pass 2 on prepared images: ONE launch, final loss and gradient
+static int tc_loss_grad(const float* x, const float* z, const float* sx, const float* sz, int N, int k, int Dx, int Dz,
+                        float margin, int row0, int rows, float* loss, float* grad_x, char* b, const NdivWs& w,
                         cudaStream_t s) {
   void* gws = b + w.part + w.psum;
-  const int JS = gram_js(N, k);
   float* part = reinterpret_cast<float*>(b);
-  float* gpart = !grad_x ? nullptr : (JS > 1 ? reinterpret_cast<float*>(b + w.part) : grad_x);
-  if (int rc = gram_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, gws, part, gpart, check, s)) return rc;
-  if (grad_x && JS > 1) {
-    const size_t tot = (size_t)N * rows * Dx;
-    ndiv_grad_reduce_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(gpart, N, k, Dx, JS, row0, rows, 0, Dx, grad_x, nullptr);
-    NDP_LAUNCH_CHECK();
-  }
-  ndiv_finalize_kernel<<<1, 256, 0, s>>>(part, N * JS * ((rows + 127) / 128), loss, nullptr);
-  NDP_LAUNCH_CHECK();
-  return NDP_OK;
+  float* gpart = reinterpret_cast<float*>(b + w.part);
+  return gram_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, row0, rows, gws, part, gpart, loss, grad_x, s);
 }
 
 extern "C" int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, int Dx, int Dz,
@@ -785,15 +773,13 @@ extern "C" int ndp_ndiv_rowsums(const float* x, const float* z, int N, int k, in
   const bool need_ws = tc || ndiv_plan(N, k, Dx).JS > 1;
   if (need_ws && (!ws || ws_bytes < w.total)) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
   char* b = reinterpret_cast<char*>(ws);
-  const int* run_if = nullptr;
   if (tc) {
-    // proposal on tensor cores (Gram form); the exact pass behind it runs only if a pair was ill-conditioned
+    // Gram form on tensor cores; ill-conditioned pairs are recomputed exactly inside the kernel (k2_ndiv_tc.cu)
     void* gws = b + w.part + w.psum;
     if (int rc = gram_prepare(x, z, N, k, Dx, Dz, gws, s)) return rc;
-    if (int rc = tc_rowsums(N, k, Dx, Dz, row0, rows, sx, sz, b, w, s)) return rc;
-    run_if = gram_flag(gws);
+    return tc_rowsums(x, z, N, k, Dx, Dz, row0, rows, sx, sz, b, w, s);
   }
-  return exact_rowsums(x, z, N, k, Dx, Dz, row0, rows, sx, sz, b, w, run_if, s);
+  return exact_rowsums(x, z, N, k, Dx, Dz, row0, rows, sx, sz, b, w, nullptr, s);
 }
 
 template <int NDP, bool WG>
@@ -854,14 +840,12 @@ extern "C" int ndp_ndiv_loss_grad(const float* x, const float* z, const float* s
   const NdivWs w = ndiv_ws(N, k, Dx, Dz);
   if (!ws || ws_bytes < w.total) { set_error("ndiv: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
   char* b = reinterpret_cast<char*>(ws);
-  const int* run_if = nullptr;
   if (gram_eligible(N, k, Dx, Dz, row0)) {
     void* gws = b + w.part + w.psum;
     if (int rc = gram_prepare(x, z, N, k, Dx, Dz, gws, s)) return rc;
-    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, true, s)) return rc;
-    run_if = gram_flag(gws);
+    return tc_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, s);
   }
-  return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, run_if, s);
+  return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, row0, rows, loss, grad_x, b, w, nullptr, s);
 }
 
 // Both passes over all rows in one call (the single-GPU autograd step): operands are pre-packed once.
@@ -894,18 +878,14 @@ extern "C" int ndp_ndiv_forward_backward(const float* x, const float* z, int N, 
     NDP_LAUNCH_CHECK();
     return NDP_OK;
   }
-  const int* run_if = nullptr;
-  const bool tc = gram_eligible(N, k, Dx, Dz, 0);
-  if (tc) {
+  if (gram_eligible(N, k, Dx, Dz, 0)) {               // three launches: pre-pack, row sums, loss + gradient
     void* gws = b + w.part + w.psum;
     if (int rc = gram_prepare(x, z, N, k, Dx, Dz, gws, s)) return rc;
-    if (int rc = tc_rowsums(N, k, Dx, Dz, 0, k, sx, sz, b, w, s)) return rc;
-    run_if = gram_flag(gws);
+    if (int rc = tc_rowsums(x, z, N, k, Dx, Dz, 0, k, sx, sz, b, w, s)) return rc;
+    return tc_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, s);
   }
-  if (int rc = exact_rowsums(x, z, N, k, Dx, Dz, 0, k, sx, sz, b, w, run_if, s)) return rc;
-  if (tc)
-    if (int rc = tc_loss_grad(x, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, false, s)) return rc;
-  return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, run_if, s);
+  if (int rc = exact_rowsums(x, z, N, k, Dx, Dz, 0, k, sx, sz, b, w, nullptr, s)) return rc;
+  return exact_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss, grad_x, b, w, nullptr, s);
 }
 
 // ---- forward / backward split of the operator (SURVEY.md 8b names): what a torch.autograd.Function binds --------
@@ -918,20 +898,70 @@ __global__ void ndiv_scale_kernel(float* __restrict__ g, const float* __restrict
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) g[i] *= scale[0];
 }
+// d loss / d dz_ij = margin * M_ij / sz_i  (M_ij = hinge active; normalisers detached, diversity.py:17-18): one warp per
+// row i writes row i of G [N,k,k]; ndp_pairwise_backward's kernel then turns G into d loss / d z.  Secondary path
+// (the reference call site never differentiates the latent codes): direct differences, k x k scratch.
+__global__ void ndiv_hinge_dz_kernel(const float* __restrict__ x, const float* __restrict__ z, const float* __restrict__ sx,
+                                     const float* __restrict__ sz, int k, int Dx, int Dz, float margin,
+                                     float* __restrict__ G) {
+  const int n = blockIdx.y;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (i >= k) return;
+  const float* xg = x + (size_t)n * k * Dx;
+  const float* zg = z + (size_t)n * k * Dz;
+  const float sxi = __ldg(sx + (size_t)n * k + i), szi = __ldg(sz + (size_t)n * k + i);
+  for (int j = lane; j < k; j += 32) {
+    float ax = 0.f, az = 0.f;
+    for (int c = 0; c < Dx; ++c) { const float df = __ldg(xg + (size_t)i * Dx + c) - __ldg(xg + (size_t)j * Dx + c); ax = fmaf(df, df, ax); }
+    for (int c = 0; c < Dz; ++c) { const float df = __ldg(zg + (size_t)i * Dz + c) - __ldg(zg + (size_t)j * Dz + c); az = fmaf(df, df, az); }
+    const float h = __fsub_rn(__fmul_rn(__fdiv_rn(sqrtf(az), szi), margin), __fdiv_rn(sqrtf(ax), sxi));   // diversity.py:40
+    G[((size_t)n * k + i) * k + j] = h > 0.f ? __fdiv_rn(margin, szi) : 0.f;
+  }
+}
+
+extern "C" int ndp_ndiv_gradz_workspace_bytes(int N, int k, int Dx, int Dz, size_t* bytes) {
+  NDP_CHECK_ARG(bytes && N >= 0 && k >= 0 && Dx >= 1 && Dz >= 1, "ndiv: bad N/k/Dx/Dz");
+  *bytes = (ndiv_ws(N, k, Dx, Dz).total + 255) / 256 * 256 + (size_t)N * k * k * sizeof(float);
+  return NDP_OK;
+}
+
 // backward: grad_x = grad_loss[0] * d loss / d x from the saved normalisers (grad_loss: device scalar, NULL = 1).
-// grad_z must be NULL: the call site never differentiates the latent codes (train_gan.py:193-196, noise has no grad).
+// grad_z (nullable) = grad_loss[0] * d loss / d z — what autograd gives a caller that sets codes.requires_grad
+// (diversity.py:36-41); needs ws of ndp_ndiv_gradz_workspace_bytes() (an [N,k,k] scratch behind the usual workspace).
 // loss_scratch: device float the kernels may overwrite (the loss is recomputed on the way).
 extern "C" int ndp_ndiv_backward(const float* x, const float* z, const float* sx, const float* sz, int N, int k, int Dx,
                                  int Dz, float margin, const float* grad_loss, float* grad_x, float* grad_z,
                                  float* loss_scratch, void* ws, size_t ws_bytes, void* stream) {
-  NDP_CHECK_ARG(grad_z == nullptr, "ndp_ndiv_backward: the gradient w.r.t. the latent codes is not provided (pass NULL)");
-  NDP_CHECK_ARG(grad_x && loss_scratch, "ndp_ndiv_backward: null grad_x / loss_scratch");
-  if (int rc = ndp_ndiv_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss_scratch, grad_x, ws, ws_bytes, stream))
-    return rc;
-  if (grad_loss && N > 0 && k > 0) {
-    const size_t n = (size_t)N * k * Dx;
-    ndiv_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(grad_x, grad_loss, n);
+  NDP_CHECK_ARG((grad_x || grad_z) && loss_scratch, "ndp_ndiv_backward: null grad_x and grad_z / loss_scratch");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (grad_x) {
+    if (int rc = ndp_ndiv_loss_grad(x, z, sx, sz, N, k, Dx, Dz, margin, 0, k, loss_scratch, grad_x, ws, ws_bytes, stream))
+      return rc;
+    if (grad_loss && N > 0 && k > 0) {
+      const size_t n = (size_t)N * k * Dx;
+      ndiv_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(grad_x, grad_loss, n);
+      NDP_LAUNCH_CHECK();
+    }
+  }
+  if (grad_z && N > 0 && k > 0) {
+    if (int rc = ndiv_args_ok(x, z, N, k, Dx, Dz, 0, k)) return rc;
+    if (int rc = device_check()) return rc;
+    NDP_CHECK_ARG(sx && sz, "ndiv: null sx/sz");
+    size_t need = 0;
+    ndp_ndiv_gradz_workspace_bytes(N, k, Dx, Dz, &need);
+    if (!ws || ws_bytes < need) { set_error("ndiv backward (grad_z): workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
+    float* G = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + (need - (size_t)N * k * k * sizeof(float)));
+    dim3 grid((k + 7) / 8, N);
+    ndiv_hinge_dz_kernel<<<grid, 256, 0, s>>>(x, z, sx, sz, k, Dx, Dz, margin, G);
     NDP_LAUNCH_CHECK();
+    pairwise_bwd_kernel<<<grid, 256, 0, s>>>(z, G, k, Dz, 0, z, grad_z);
+    NDP_LAUNCH_CHECK();
+    if (grad_loss) {
+      const size_t n = (size_t)N * k * Dz;
+      ndiv_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(grad_z, grad_loss, n);
+      NDP_LAUNCH_CHECK();
+    }
   }
   return NDP_OK;
 }

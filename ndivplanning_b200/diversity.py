@@ -125,25 +125,55 @@ class _NdivLoss(torch.autograd.Function):
     def forward(ctx, recodes, codes):
         require_cuda(recodes, codes)
         x, z = f32c(recodes), f32c(codes)
-        want = bool(ctx.needs_input_grad[0])
-        loss, grad = ndiv_forward_backward(x, z, want)
-        if want:
-            ctx.save_for_backward(grad)   # d loss / d recodes for grad_output = 1
-        ctx.in_dtype = recodes.dtype
+        want_x, want_z = bool(ctx.needs_input_grad[0]), bool(ctx.needs_input_grad[1])
+        N, k, Dx = x.shape
+        Dz = z.shape[2]
+        dev = x.device
+        sx = torch.empty(N, k, dtype=torch.float32, device=dev)
+        sz = torch.empty(N, k, dtype=torch.float32, device=dev)
+        loss = torch.empty(1, dtype=torch.float32, device=dev)
+        grad = torch.empty_like(x) if want_x else None
+        nbytes = C.c_size_t()
+        check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, Dz, C.byref(nbytes)))
+        ws = _ws(nbytes.value, dev)
+        with torch.cuda.device(dev):
+            check(lib().ndp_ndiv_forward_backward(ptr(x), ptr(z), N, k, Dx, Dz, MARGIN, ptr(sx), ptr(sz), ptr(loss),
+                                                  ptr(grad), ptr(ws), ws.numel(), stream_ptr(dev)))
+        ctx.save_for_backward(*([grad] if want_x else []), *([x, z, sx, sz] if want_z else []))
+        ctx.want = (want_x, want_z)
+        ctx.in_dtypes = (recodes.dtype, codes.dtype)
         return loss.reshape(())
 
     @staticmethod
     def backward(ctx, grad_out):
-        (grad,) = ctx.saved_tensors
-        return (grad * grad_out).to(ctx.in_dtype), None
+        want_x, want_z = ctx.want
+        saved = list(ctx.saved_tensors)
+        gx = gz = None
+        if want_x:
+            gx = (saved.pop(0) * grad_out).to(ctx.in_dtypes[0])      # d loss / d recodes was produced with the forward
+        if want_z:
+            # d loss / d codes (what autograd gives when codes.requires_grad, diversity.py:36-41): exact secondary path
+            x, z, sx, sz = saved
+            N, k, Dx = x.shape
+            Dz = z.shape[2]
+            dev = x.device
+            nbytes = C.c_size_t()
+            check(lib().ndp_ndiv_gradz_workspace_bytes(N, k, Dx, Dz, C.byref(nbytes)))
+            ws = _ws(nbytes.value, dev)
+            gz = torch.empty_like(z)
+            scratch = torch.empty(1, dtype=torch.float32, device=dev)
+            gl = f32c(grad_out).reshape(1)
+            with torch.cuda.device(dev):
+                check(lib().ndp_ndiv_backward(ptr(x), ptr(z), ptr(sx), ptr(sz), N, k, Dx, Dz, MARGIN, ptr(gl), None, ptr(gz),
+                                              ptr(scratch), ptr(ws), ws.numel(), stream_ptr(dev)))
+            gz = gz.to(ctx.in_dtypes[1])
+        return gx, gz
 
 
 def compute_pairwise_divergence(recodes, codes):
-    """diversity.py:36-41 — ``relu(0.8 * delta_z - delta_x).sum()``; outputs first, latents second."""
+    """diversity.py:36-41 — ``relu(0.8 * delta_z - delta_x).sum()``; outputs first, latents second.  Differentiable
+    w.r.t. both arguments like the reference under autograd (the reference's own call site only needs recodes)."""
     N, k, _ = codes.size()
-    if codes.requires_grad:
-        raise _lib.NdpError("compute_pairwise_divergence: gradient w.r.t. `codes` (latents) is not provided; "
-                            "the reference call site passes raw noise (train_gan.py:193-196)")
     z = torch.squeeze(codes).view(N, k, -1)
     x = torch.squeeze(recodes).view(N, k, -1)
     return _NdivLoss.apply(x, z)

@@ -233,7 +233,33 @@ def test_ndiv_forward_backward_abi_pair(cuda, N, k, Dx, Dz):
     np.testing.assert_allclose(loss.item(), l64.item(), rtol=RTOL)
     np.testing.assert_allclose(scratch.item(), l64.item(), rtol=RTOL)
     _grad_close_arbiter((grad / 0.1).cpu(), x, z, g64.numpy(), rtol=RTOL)
-    with pytest.raises(Exception):                         # gradient w.r.t. the latent codes is not provided
+    with pytest.raises(Exception):                         # grad_z needs the larger workspace (ndp_ndiv_gradz_workspace_bytes)
         _lib.check(_lib.lib().ndp_ndiv_backward(_lib.ptr(xd), _lib.ptr(zd), _lib.ptr(sx), _lib.ptr(sz), N, k, Dx, Dz, 0.8,
-                                               None, _lib.ptr(grad), _lib.ptr(grad), _lib.ptr(scratch), _lib.ptr(ws),
-                                               ws.numel(), st))
+                                               None, _lib.ptr(grad), _lib.ptr(torch.empty_like(zd)), _lib.ptr(scratch),
+                                               _lib.ptr(ws[:64]), 64, st))
+
+
+@pytest.mark.parametrize("N,k,Dx,Dz", [(56, 6, 4, 2), (2, 300, 12, 5), (1, 1536, 32, 16), (3, 40, 300, 2)])
+def test_ndiv_gradient_wrt_codes(cuda, N, k, Dx, Dz):
+    """codes.requires_grad works like the reference under autograd (diversity.py:36-41): d loss / d codes against the
+    fp64 autograd of the oracle; hinge-boundary pairs get the arbiter slack (a flip moves W^z_ij by 0.8 / sz_i)"""
+    from ndivplanning_b200 import diversity as div
+    x, z = synthetic.make_ndiv_inputs(N, k, Dx, Dz, seed=11 + k)
+    xg, zg = x.cuda().requires_grad_(True), z.cuda().requires_grad_(True)
+    (0.5 * div.compute_pairwise_divergence(xg, zg)).backward()
+    x64, z64 = x.double().requires_grad_(True), z.double().requires_grad_(True)
+    (0.5 * O.compute_pairwise_divergence(x64, z64)).backward()
+    _grad_close_arbiter(xg.grad.cpu() / 0.5, x, z, x64.grad.numpy() / 0.5)
+    dx, dz = torch.cdist(x.double(), x.double()), torch.cdist(z.double(), z.double())
+    sx, sz = dx.sum(-1, keepdim=True), dz.sum(-1, keepdim=True)
+    h = 0.8 * dz / sz - dx / sx
+    amb = (h.abs() < 4e-6 * (dx / sx)) & (dx > 0)
+    inv = (0.8 / sz).expand_as(h)
+    slack = ((amb * inv).sum(-1) + (amb * inv).sum(-2)).numpy()
+    want = z64.grad.numpy() / 0.5
+    err = np.abs(zg.grad.cpu().numpy().astype(np.float64) / 0.5 - want).max(axis=-1)
+    assert (err <= RTOL * (np.abs(want).max() + 1e-30) + slack).all(), float((err - slack).max())
+    # only codes requires grad
+    zg2 = z.cuda().requires_grad_(True)
+    div.compute_pairwise_divergence(x.cuda(), zg2).backward()
+    assert torch.allclose(zg2.grad, zg.grad / 0.5, rtol=1e-6, atol=1e-9)

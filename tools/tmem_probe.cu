@@ -36,7 +36,8 @@ __global__ void __launch_bounds__(512, 1) ldst_kernel(int reps, int slot) {
       tmem_ld32(base, v);
       tmem_ld32(base + 32, w);
       tmem_ld_wait();
-      acc += v[r & 31] + w[(r + 7) & 31];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) acc ^= v[i] ^ w[i];
     } else {
       tmem_st16(base, v); tmem_st16(base + 16, v + 16);
       tmem_st16(base + 32, w); tmem_st16(base + 48, w + 16);
