@@ -36,8 +36,9 @@ static constexpr int kGT = 128;                 // rows / columns per tile
 static constexpr int kGNT = 256;                // threads per CTA
 static constexpr float kIllTau = 1.f / 64.f;    // conditioning threshold d2 >= tau * (n_i + n_j)
 static constexpr int kXTBytes = 16384;          // per tile: transposed x operand of the gradient product, hi + lo
-static constexpr int kGNS = 130;                // float2 entries per tile in the norms array: 128 rows {nx, nz},
-                                                // entry 128 = the tile's operand scales {sx, sz}, entry 129 = pad
+static constexpr int kGNS = 130;                // 8-byte entries per tile in the norms array (1040 B): floats nx[128] |
+                                                // nz[128] | {scale_x, scale_z, 0, 0}  (structure of arrays: two adjacent
+                                                // columns' norms load as one 64-bit word for the packed f32x2 epilogue)
 static constexpr int kNormBytes = 1056;         // kGNS * 8 rounded up to a multiple of 32 (shared-memory slot)
 
 struct GramDims {
@@ -67,7 +68,7 @@ __device__ __forceinline__ uint32_t img_off(int slab0, int r, int kk) {
 }
 
 // grid (4 * tiles, N), 256 threads; block = 32 rows of one tile.  img: [N][tiles][img_bytes]; norms: [N][tiles][kGNS]
-// float2; imgT: [N][tiles][kXTBytes].  Centre = mean of the group's first min(k,128) rows (any fixed vector is exact —
+// float2; imgT: [N][tiles][kXTBytes].  Centre = mean of the group's first min(k,32) rows (any fixed vector is exact —
 // distances are translation invariant — it only has to be central enough to keep ||c||^2 comparable to d^2); every
 // block recomputes it in the same order, so all tiles agree bit for bit.  Operand scale: a power of two PER TILE
 // (max |c| * s in [256, 512)), so the fp16 "lo" halves stay normal numbers whatever the magnitude of the data; the
@@ -88,7 +89,7 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
   __shared__ float s_sc[2];
   {
     const int d = tid & 63, rq = tid >> 6, D = Dx + Dz;
-    const int ns = k < kGT ? k : kGT;
+    const int ns = k < 32 ? k : 32;
     float acc = 0.f;
     if (d < D) {
       const float* v = d < Dx ? x + (size_t)n * k * Dx + d : z + (size_t)n * k * Dz + (d - Dx);
@@ -122,8 +123,8 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
       for (int w = 0; w < 8; ++w) { a = fmaxf(a, s_mx[w]); b = fmaxf(b, s_mz[w]); }
       s_sc[0] = pick_scale(a); s_sc[1] = pick_scale(b);
       if (sub == 0) {
-        norms[((size_t)n * tiles + tile) * kGNS + kGT] = make_float2(s_sc[0], s_sc[1]);
-        norms[((size_t)n * tiles + tile) * kGNS + kGT + 1] = make_float2(0.f, 0.f);
+        float* nf = reinterpret_cast<float*>(norms + ((size_t)n * tiles + tile) * kGNS);
+        nf[2 * kGT] = s_sc[0]; nf[2 * kGT + 1] = s_sc[1]; nf[2 * kGT + 2] = 0.f; nf[2 * kGT + 3] = 0.f;
       }
     }
     __syncthreads();
@@ -181,7 +182,9 @@ ndiv_prepack_kernel(const float* __restrict__ x, const float* __restrict__ z, in
       for (int d = 0; d < Dx; ++d) { const float c = __ldg(xr + d) - mu[d]; nx = fmaf(c, c, nx); }
       for (int d = 0; d < Dz; ++d) { const float c = __ldg(zr + d) - mu[Dx + d]; nz = fmaf(c, c, nz); }
     }
-    norms[((size_t)n * tiles + tile) * kGNS + sub * 32 + tid] = make_float2(nx, nz);
+    float* nf = reinterpret_cast<float*>(norms + ((size_t)n * tiles + tile) * kGNS);
+    nf[sub * 32 + tid] = nx;
+    nf[kGT + sub * 32 + tid] = nz;
   }
 }
 
@@ -219,6 +222,165 @@ __device__ __noinline__ float exact_d2(const float* __restrict__ a, const float*
   return s;
 }
 
+// packed fp32 pairs (one issue slot for two lanes' worth of work: the epilogue is issue-bound)
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void up2(u64 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ float rsqrt_approx(float v) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+
+static constexpr float kTinyD2 = 1e-30f;              // pass 2 clamps d^2 here so that rsqrt stays finite
+
+// per-thread state of the epilogue (one row i of the tile, one half of its columns)
+template <bool PASS2>
+struct RowState {
+  float rsx, rsz;                                     // pass 1: row sums
+  float lsum, sumW, wmax;                             // pass 2: loss, sum_j What_ij, max |What * alpha| of the chunk
+  float* gdir;                                        // pass 2: directly accumulated gradient terms (all 32 dims; an
+                                                      // array in LOCAL memory: only the rare slow path touches it)
+  bool any_direct;
+};
+
+// 16 consecutive columns [col, col+16) of row i: squared distances from the two Gram accumulators (+ the exact slow
+// path for ill-conditioned pairs), then row sums (pass 1) or hinge / loss / What (pass 2).  EDGE: the tile contains
+// the diagonal, padded columns or rows outside the caller's block (CTA-uniform).  wch: What of the 16 pairs.
+template <bool PASS2, bool EDGE>
+__device__ __forceinline__ void gram_chunk(RowState<PASS2>& st, const uint32_t (&ux)[16], const uint32_t (&uz)[16],
+                                           const float* __restrict__ snx, const float* __restrict__ snz,
+                                           const float* __restrict__ srx, const float* __restrict__ srz,
+                                           int col, float nix, float niz, float cx, float cz, float rix, float mriz,
+                                           float alpha, bool grad, bool ivalid, int i, int j0, int k,
+                                           const float* __restrict__ xi, const float* __restrict__ zi,
+                                           const float* __restrict__ xg, const float* __restrict__ zg, int Dx, int Dz,
+                                           float (&wch)[16]) {
+  float d2x[16], d2z[16];
+  float illm = 1.f;                                    // running min of d2 - tau (n_i + n_j) over the chunk
+  {
+    const u64 nix2 = pk2(nix, nix), niz2 = pk2(niz, niz), cx2 = pk2(cx, cx), cz2 = pk2(cz, cz);
+    const u64 ntau2 = pk2(-kIllTau, -kIllTau);
+#pragma unroll
+    for (int pq = 0; pq < 8; ++pq) {
+      const u64 sxn = add2(nix2, *reinterpret_cast<const u64*>(snx + col + 2 * pq));
+      const u64 szn = add2(niz2, *reinterpret_cast<const u64*>(snz + col + 2 * pq));
+      const u64 vx = fma2(cx2, pk2(__uint_as_float(ux[2 * pq]), __uint_as_float(ux[2 * pq + 1])), sxn);
+      const u64 vz = fma2(cz2, pk2(__uint_as_float(uz[2 * pq]), __uint_as_float(uz[2 * pq + 1])), szn);
+      float a0, a1, b0, b1, e0, e1, f0, f1;
+      up2(vx, a0, a1); up2(vz, b0, b1);
+      up2(fma2(ntau2, sxn, vx), e0, e1); up2(fma2(ntau2, szn, vz), f0, f1);
+      if (EDGE) {                                      // only live pairs take part in the conditioning test
+        const int j = j0 + col + 2 * pq;
+        const bool l0 = ivalid && j < k && j != i, l1 = ivalid && j + 1 < k && j + 1 != i;
+        e0 = l0 ? e0 : 1.f; f0 = l0 ? f0 : 1.f; e1 = l1 ? e1 : 1.f; f1 = l1 ? f1 : 1.f;
+        if (j == i) { a0 = 0.f; b0 = 0.f; }            // the diagonal is exactly 0
+        if (j + 1 == i) { a1 = 0.f; b1 = 0.f; }
+      }
+      illm = fminf(illm, fminf(fminf(e0, e1), fminf(f0, f1)));
+      const float lo = PASS2 ? kTinyD2 : 0.f;
+      d2x[2 * pq] = fmaxf(a0, lo); d2x[2 * pq + 1] = fmaxf(a1, lo);
+      d2z[2 * pq] = fmaxf(b0, lo); d2z[2 * pq + 1] = fmaxf(b1, lo);
+    }
+  }
+  uint32_t direct = 0;                                 // pairs whose gradient term is accumulated directly
+  if (!(illm > 0.f)) {                                 // rare: near-duplicate rows -> the reference's own difference form
+#pragma unroll 1
+    for (int c = 0; c < 16; ++c) {
+      const int j = j0 + col + c;
+      if (EDGE && !(ivalid && j < k && j != i)) continue;
+      float vx = 0.f, vz = 0.f;
+#pragma unroll
+      for (int c2 = 0; c2 < 16; ++c2)
+        if (c2 == c) { vx = d2x[c2]; vz = d2z[c2]; }
+      const float sxn = nix + snx[col + c], szn = niz + snz[col + c];
+      if (vx > kIllTau * sxn && vz > kIllTau * szn) continue;
+      const float ex = exact_d2(xi, xg + (size_t)j * Dx, Dx), ez = exact_d2(zi, zg + (size_t)j * Dz, Dz);
+#pragma unroll
+      for (int c2 = 0; c2 < 16; ++c2)
+        if (c2 == c) { d2x[c2] = PASS2 ? fmaxf(ex, kTinyD2) : ex; d2z[c2] = PASS2 ? fmaxf(ez, kTinyD2) : ez; }
+      direct |= 1u << c;
+    }
+  }
+  if (!PASS2) {
+    u64 rs2x = pk2(0.f, 0.f), rs2z = pk2(0.f, 0.f);
+#pragma unroll
+    for (int pq = 0; pq < 8; ++pq) {
+      float ax = sqrt_approx(d2x[2 * pq]), bx = sqrt_approx(d2x[2 * pq + 1]);
+      float az = sqrt_approx(d2z[2 * pq]), bz = sqrt_approx(d2z[2 * pq + 1]);
+      if (EDGE) {
+        const int j = j0 + col + 2 * pq;
+        if (j >= k) { ax = 0.f; az = 0.f; }
+        if (j + 1 >= k) { bx = 0.f; bz = 0.f; }
+      }
+      rs2x = add2(rs2x, pk2(ax, bx));
+      rs2z = add2(rs2z, pk2(az, bz));
+    }
+    float a, b;
+    up2(rs2x, a, b); st.rsx += a + b;
+    up2(rs2z, a, b); st.rsz += a + b;
+  } else {
+    const u64 rix2 = pk2(rix, rix), mriz2 = pk2(mriz, mriz), nalpha2 = pk2(-alpha, -alpha);
+    float wm = 0.f;
+    u64 ls2 = pk2(0.f, 0.f), sw2 = pk2(0.f, 0.f);
+#pragma unroll
+    for (int pq = 0; pq < 8; ++pq) {
+      // d = d2 * rsqrt(d2); 1/d = rsqrt(d2): one MUFU per matrix, no reciprocal
+      const float r0 = rsqrt_approx(d2x[2 * pq]), r1 = rsqrt_approx(d2x[2 * pq + 1]);
+      const u64 ddx = mul2(pk2(d2x[2 * pq], d2x[2 * pq + 1]), pk2(r0, r1));
+      const u64 ddz = mul2(pk2(d2z[2 * pq], d2z[2 * pq + 1]),
+                           pk2(rsqrt_approx(d2z[2 * pq]), rsqrt_approx(d2z[2 * pq + 1])));
+      // hinge arguments h_ij (row i's normalisers) and h_ji (row j's): margin dz / sz - dx / sx
+      const u64 rjx = *reinterpret_cast<const u64*>(srx + col + 2 * pq);
+      const u64 hij = fma2(ddz, mriz2, mul2(ddx, pk2(-rix, -rix)));
+      const u64 hji = fma2(ddz, *reinterpret_cast<const u64*>(srz + col + 2 * pq), mul2(ddx, rjx ^ 0x8000000080000000ull));
+      float h0, h1, g0, g1, q0, q1;
+      up2(hij, h0, h1); up2(hji, g0, g1); up2(rjx, q0, q1);
+      bool ok0 = true, ok1 = true;
+      if (EDGE) {
+        const int j = j0 + col + 2 * pq;
+        ok0 = ivalid && j < k && j != i; ok1 = ivalid && j + 1 < k && j + 1 != i;
+      }
+      const float l0 = (ok0 && h0 > 0.f) ? h0 : 0.f, l1 = (ok1 && h1 > 0.f) ? h1 : 0.f;
+      ls2 = add2(ls2, pk2(l0, l1));
+      if (grad) {
+        float w0 = (h0 > 0.f ? rix : 0.f) + (g0 > 0.f ? q0 : 0.f);
+        float w1 = (h1 > 0.f ? rix : 0.f) + (g1 > 0.f ? q1 : 0.f);
+        w0 = ok0 ? -w0 * r0 : 0.f;                     // What = W / d
+        w1 = ok1 ? -w1 * r1 : 0.f;
+        wch[2 * pq] = w0; wch[2 * pq + 1] = w1;
+        wm = fmaxf(wm, fmaxf(fabsf(w0), fabsf(w1)));
+      }
+    }
+    float a, b;
+    up2(ls2, a, b); st.lsum += a + b;
+    if (grad) {
+      if (wm * alpha >= 60000.f) {                     // would not fit the fp16 operand of the gradient product
+#pragma unroll
+        for (int c = 0; c < 16; ++c)
+          if (fabsf(wch[c]) * alpha >= 60000.f) direct |= 1u << c;
+      }
+      if (direct) {                                    // rare: What_ij (x_i - x_j) in fp32, kept out of the fp16 product
+        st.any_direct = true;
+#pragma unroll 1
+        for (uint32_t m = direct; m; m &= m - 1) {
+          const int c = __ffs(m) - 1, j = j0 + col + c;
+          float w = 0.f;
+#pragma unroll
+          for (int c2 = 0; c2 < 16; ++c2)
+            if (c2 == c) { w = wch[c2]; wch[c2] = 0.f; }
+          if (!(fabsf(w) < 1e29f)) w = 0.f;            // d clamped at 1e-15 (exact duplicates): subgradient 0, as torch.norm
+          const float* xj = xg + (size_t)j * Dx;
+#pragma unroll 1
+          for (int d = 0; d < Dx; ++d) st.gdir[d] = fmaf(w, __ldg(xi + d) - __ldg(xj + d), st.gdir[d]);
+        }
+      }
+#pragma unroll
+      for (int pq = 0; pq < 8; ++pq) sw2 = add2(sw2, pk2(wch[2 * pq], wch[2 * pq + 1]));
+      up2(sw2, a, b); st.sumW += a + b;
+    }
+  }
+}
+
 // grid (row tiles of the call, JS, N), 256 threads, 2 CTAs / SM
 template <bool PASS2>
 __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) {
@@ -232,12 +394,13 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
   const int ntl = jt1 - jt0;
   const bool grad = PASS2 && p.grad != nullptr;
 
-  // shared memory: A image | 2 x { B image, norms, [XT] } | srj | sred | slos | barriers
+  // shared memory: A image | 2 x { B image, norms, [XT] } | srx, srz | sred | slos | barriers
   const uint32_t buf_bytes = (uint32_t)gd.img_bytes + kNormBytes + (PASS2 ? (uint32_t)kXTBytes : 0u);
   uint8_t* sA = smem;
   uint8_t* sBuf = smem + gd.img_bytes;
-  float2* srj = reinterpret_cast<float2*>(sBuf + 2 * buf_bytes);             // {1/sx_j, 1/sz_j}
-  float2* sred = srj + kGT;                                                  // [2 halves][128 rows]
+  float* srx = reinterpret_cast<float*>(sBuf + 2 * buf_bytes);               // 1/sx_j            [128]
+  float* srz = srx + kGT;                                                    // margin / sz_j     [128]
+  float2* sred = reinterpret_cast<float2*>(srz + kGT);                       // [2 halves][128 rows]
   float* slos = reinterpret_cast<float*>(sred + 2 * kGT);                    // [8 warps]
   uint8_t* sbar = reinterpret_cast<uint8_t*>(slos + 8);
   const uint32_t bar_a = smem_u32(sbar), bar_full0 = bar_a + 8, bar_d = bar_a + 24, bar_g = bar_a + 32;
@@ -275,36 +438,50 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
   const int q = warp & 3, hf = warp >> 2, row = q * 32 + lane;
   const int i = itile * kGT + row;
   const bool ivalid = i >= p.row0 && i < iend;
-  const float2 ni = __ldg(p.norms + ((size_t)n * p.tiles + itile) * kGNS + row);
-  const float2 sI = __ldg(p.norms + ((size_t)n * p.tiles + itile) * kGNS + kGT);   // operand scales of the i tile
-  float2 ri = make_float2(0.f, 0.f);
+  const float* nfi = reinterpret_cast<const float*>(p.norms + ((size_t)n * p.tiles + itile) * kGNS);
+  const float nix = __ldg(nfi + row), niz = __ldg(nfi + kGT + row);
+  const float sIx = __ldg(nfi + 2 * kGT), sIz = __ldg(nfi + 2 * kGT + 1);      // operand scales of the i tile
+  float rix = 0.f, mriz = 0.f, nanprobe = 0.f;
   float alpha = 1.f;                                   // power of two ~ sx_i^2 / k: What * alpha = O(mean d / d)
   if (PASS2 && i < p.k) {
-    const float sxi = __ldg(p.sx + (size_t)n * p.k + i);
-    ri = make_float2(1.f / sxi, 1.f / __ldg(p.sz + (size_t)n * p.k + i));
+    const float sxi = __ldg(p.sx + (size_t)n * p.k + i), szi = __ldg(p.sz + (size_t)n * p.k + i);
+    rix = 1.f / sxi; mriz = p.margin / szi;
+    nanprobe = 0.f * (sxi + szi);                      // NaN / inf normalisers make the loss NaN like the reference
     const float t = sxi * sxi / (float)p.k;
     if (t > 0.f && t < 3e38f) { int e; frexpf(t, &e); e = e > 100 ? 100 : (e < -100 ? -100 : e); alpha = ldexpf(1.f, e - 1); }
   }
-  const float* xi = p.x + ((size_t)n * p.k + (i < p.k ? i : 0)) * p.Dx;
-  const float* zi = p.z + ((size_t)n * p.k + (i < p.k ? i : 0)) * p.Dz;
+  const float* xg = p.x + (size_t)n * p.k * p.Dx;
+  const float* zg = p.z + (size_t)n * p.k * p.Dz;
+  const float* xi = xg + (size_t)(i < p.k ? i : 0) * p.Dx;
+  const float* zi = zg + (size_t)(i < p.k ? i : 0) * p.Dz;
   const uint32_t idesc = idesc_f16(128);
   const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
 
-  float rsx = 0.f, rsz = 0.f, lsum = 0.f, sumW = 0.f;
-  float g[16], gdir[16];                               // gradient accumulators: dims hf*16 .. hf*16+15 of this row
+  RowState<PASS2> st;
+  st.rsx = st.rsz = st.lsum = st.sumW = st.wmax = 0.f;
+  st.any_direct = false;
+  float gdir_local[32];
+  st.gdir = gdir_local;
+  if (PASS2) {
+#pragma unroll 1
+    for (int d = 0; d < 32; ++d) gdir_local[d] = 0.f;
+  }
+  float g[16];                                         // gradient accumulators: dims hf*16 .. hf*16+15 of this row
 #pragma unroll
-  for (int d = 0; d < 16; ++d) { g[d] = 0.f; gdir[d] = 0.f; }
+  for (int d = 0; d < 16; ++d) g[d] = 0.f;
+  if (PASS2 && hf == 0 && ivalid) st.lsum = nanprobe;
   const bool rows_full = itile * kGT >= p.row0 && itile * kGT + kGT <= iend;
 
   for (int t = 0; t < ntl; ++t) {
     const int jt = jt0 + t, j0 = jt * kGT;
     const uint32_t ph = (uint32_t)(t & 1), bar_full = bar_full0 + 8 * (t & 1), phf = (uint32_t)((t >> 1) & 1);
     uint8_t* sB = sBuf + (t & 1) * buf_bytes;
-    const float2* snj = reinterpret_cast<const float2*>(sB + gd.img_bytes);
+    const float* snx = reinterpret_cast<const float*>(sB + gd.img_bytes);
+    const float* snz = snx + kGT;
     if (PASS2 && tid < kGT) {
       const int j = j0 + tid;
-      srj[tid] = j < p.k ? make_float2(1.f / __ldg(p.sx + (size_t)n * p.k + j), 1.f / __ldg(p.sz + (size_t)n * p.k + j))
-                         : make_float2(0.f, 0.f);
+      srx[tid] = j < p.k ? 1.f / __ldg(p.sx + (size_t)n * p.k + j) : 0.f;
+      srz[tid] = j < p.k ? p.margin / __ldg(p.sz + (size_t)n * p.k + j) : 0.f;
     }
     if (warp == 0) {
       if (elect_one()) {
@@ -333,11 +510,11 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       __syncwarp();
     }
     mbar_wait(bar_full, phf);                          // norms landed (every thread reads them)
-    __syncthreads();                                   // srj visible
+    __syncthreads();                                   // srx / srz visible
     mbar_wait(bar_d, ph);
     fence_after_sync();
-    const float2 sJ = snj[kGT];                        // accumulators carry s_I * s_J (powers of two: exact)
-    const float cx = -2.f / (sI.x * sJ.x), cz = -2.f / (sI.y * sJ.y);
+    const float sJx = snx[2 * kGT], sJz = snx[2 * kGT + 1];   // accumulators carry s_I * s_J (powers of two: exact)
+    const float cx = -2.f / (sIx * sJx), cz = -2.f / (sIz * sJz);
     const bool edge = (jt == itile) || (j0 + kGT > p.k) || !rows_full;      // CTA-uniform
 #pragma unroll 1
     for (int cc = 0; cc < 4; ++cc) {
@@ -346,91 +523,24 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       tmem_ld16(lane_base + col, ux);
       tmem_ld16(lane_base + 128 + col, uz);
       tmem_ld_wait();
-      // ---- squared distances of 16 pairs + conditioning test
-      float d2x[16], d2z[16];
-      uint32_t ill = 0;
-#pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const float2 nj = snj[col + c];
-        const float sxn = ni.x + nj.x, szn = ni.y + nj.y;
-        const float vx = fmaf(cx, __uint_as_float(ux[c]), sxn), vz = fmaf(cz, __uint_as_float(uz[c]), szn);
-        ill |= (fminf(fmaf(-kIllTau, sxn, vx), fmaf(-kIllTau, szn, vz)) < 0.f) ? (1u << c) : 0u;
-        d2x[c] = fmaxf(vx, 0.f);
-        d2z[c] = fmaxf(vz, 0.f);
-      }
-      uint32_t direct = 0;                             // pairs whose gradient term is accumulated directly
-      if (edge) {
-        uint32_t live = 0;
-#pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          const int j = j0 + col + c;
-          if (j < p.k && ivalid && j != i) live |= 1u << c;
-          if (j == i) { d2x[c] = 0.f; d2z[c] = 0.f; }    // the diagonal is exactly 0
-        }
-        ill &= live;
-      }
-      if (ill) {                                       // rare: near-duplicate rows -> the reference's own difference form
-#pragma unroll 1
-        for (uint32_t m = ill; m; m &= m - 1) {
-          const int c = __ffs(m) - 1, j = j0 + col + c;
-          const float ex = exact_d2(xi, p.x + ((size_t)n * p.k + j) * p.Dx, p.Dx);
-          const float ez = exact_d2(zi, p.z + ((size_t)n * p.k + j) * p.Dz, p.Dz);
-#pragma unroll
-          for (int c2 = 0; c2 < 16; ++c2)
-            if (c2 == c) { d2x[c2] = ex; d2z[c2] = ez; }
-        }
-        direct = ill;
-      }
       float wch[16];
 #pragma unroll
-      for (int c = 0; c < 16; ++c) {
-        const int jl = col + c;
-        const bool valid = !edge || (j0 + jl < p.k);
-        const float ddx = sqrt_approx(d2x[c]), ddz = sqrt_approx(d2z[c]);
-        wch[c] = 0.f;
-        if (!PASS2) {
-          if (valid) { rsx += ddx; rsz += ddz; }
-        } else {
-          const float2 rj = srj[jl];
-          const float hij = __fsub_rn(__fmul_rn(p.margin, __fmul_rn(ddz, ri.y)), __fmul_rn(ddx, ri.x));
-          const float hji = __fsub_rn(__fmul_rn(p.margin, __fmul_rn(ddz, rj.y)), __fmul_rn(ddx, rj.x));
-          const bool ok = !edge || (valid && ivalid);
-          if (ok) lsum += !(hij <= 0.f) ? hij : 0.f;
-          if (grad) {
-            const float wij = (hij > 0.f ? ri.x : 0.f) + (hji > 0.f ? rj.x : 0.f);
-            const float w = (ok && ddx > 0.f) ? __fdividef(-wij, ddx) : 0.f;
-            const float ws = w * alpha;                // row-scaled to O(1) for the fp16 A operand of the product
-            if (fabsf(ws) >= 60000.f) direct |= 1u << c;        // would not fit fp16
-            wch[c] = w;
-          }
-        }
-      }
+      for (int c = 0; c < 16; ++c) wch[c] = 0.f;
+      if (edge)
+        gram_chunk<PASS2, true>(st, ux, uz, snx, snz, srx, srz, col, nix, niz, cx, cz, rix, mriz, alpha, grad, ivalid, i,
+                                j0, p.k, xi, zi, xg, zg, p.Dx, p.Dz, wch);
+      else
+        gram_chunk<PASS2, false>(st, ux, uz, snx, snz, srx, srz, col, nix, niz, cx, cz, rix, mriz, alpha, grad, true, i,
+                                 j0, p.k, xi, zi, xg, zg, p.Dx, p.Dz, wch);
       if (grad) {
-        if (direct) {                                  // rare: What_ij (x_i - x_j) in fp32, kept out of the fp16 product
-#pragma unroll 1
-          for (uint32_t m = direct; m; m &= m - 1) {
-            const int c = __ffs(m) - 1, j = j0 + col + c;
-            float w = 0.f;
-#pragma unroll
-            for (int c2 = 0; c2 < 16; ++c2)
-              if (c2 == c) { w = wch[c2]; wch[c2] = 0.f; }
-            const float* xj = p.x + ((size_t)n * p.k + j) * p.Dx;
-#pragma unroll
-            for (int d = 0; d < 16; ++d) {
-              const int dim = hf * 16 + d;
-              if (dim < p.Dx) gdir[d] = fmaf(w, __ldg(xi + dim) - __ldg(xj + dim), gdir[d]);
-            }
-          }
-        }
         // What (16 consecutive j of this row) -> fp16 hi / lo A-operand columns, written over accumulator columns
         // this warp has already consumed: hi into the x accumulator block, lo into the z block.
         uint32_t whi[8], wlo[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const float w0 = wch[2 * e], w1 = wch[2 * e + 1];
-          sumW += w0 + w1;
-          whi[e] = pack_hi(w0 * alpha, w1 * alpha);
-          wlo[e] = pack_lo(w0 * alpha, w1 * alpha, whi[e]);
+          const float w0 = wch[2 * e] * alpha, w1 = wch[2 * e + 1] * alpha;
+          whi[e] = pack_hi(w0, w1);
+          wlo[e] = pack_lo(w0, w1, whi[e]);
         }
         const uint32_t wcol = lane_base + hf * 64 + cc * 8;
         tmem_st8(wcol, whi);
@@ -464,7 +574,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       uint32_t ug[16];
       tmem_ld16(lane_base + 32 + hf * 16, ug);
       tmem_ld_wait();
-      const float isj = 1.f / snj[kGT].x;              // the tile's operand scale (power of two)
+      const float isj = 1.f / sJx;                     // the tile's operand scale (power of two)
 #pragma unroll
       for (int d = 0; d < 16; ++d) g[d] = fmaf(__uint_as_float(ug[d]), isj, g[d]);
     }
@@ -476,7 +586,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
   // ---- per-CTA results, then the LAST CTA of the row tile combines the column splits in fixed order
   const size_t tk_row = (size_t)(PASS2 ? N * p.tiles : 0) + (size_t)n * p.tiles + itile;
   if (!PASS2) {
-    sred[hf * kGT + row] = make_float2(rsx, rsz);
+    sred[hf * kGT + row] = make_float2(st.rsx, st.rsz);
     __syncthreads();
     if (tid < kGT) {
       const int ii = itile * kGT + tid;
@@ -507,14 +617,23 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       }
     }
   } else {
+    float lsum = st.lsum;
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 16);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 8);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 4);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 2);
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 1);
     if (lane == 0) slos[warp] = lsum;
-    if (grad) sred[hf * kGT + row] = make_float2(sumW, 0.f);      // What row sums of the two column halves
-    __syncthreads();
+    if (grad) sred[hf * kGT + row] = make_float2(st.sumW, 0.f);   // What row sums of the two column halves
+    // the directly accumulated terms cover all 32 dims of this thread's COLUMNS; the two column halves of a row
+    // meet through the (now dead) operand buffers: gx[half][row][32]
+    float* gxch = reinterpret_cast<float*>(sBuf);
+    const int any_direct = grad ? __syncthreads_or(st.any_direct ? 1 : 0) : (__syncthreads(), 0);
+    if (any_direct) {
+#pragma unroll 1
+      for (int d = 0; d < 32; ++d) gxch[(hf * kGT + row) * 33 + d] = st.gdir[d];
+      __syncthreads();
+    }
     const int n_parts = N * (int)gridDim.y * (int)gridDim.x;
     if (tid == 0) {
       float t = 0.f;
@@ -531,7 +650,11 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
 #pragma unroll
       for (int d = 0; d < 16; ++d) {
         const int dim = hf * 16 + d;
-        if (dim < p.Dx) dst[dim] = fmaf(__ldg(p.x + off + dim) - __ldg(mu + dim), sw, -g[d] * ia) + gdir[d];
+        if (dim < p.Dx) {
+          float v = fmaf(__ldg(p.x + off + dim) - __ldg(mu + dim), sw, -g[d] * ia);
+          if (any_direct) v += gxch[row * 33 + dim] + gxch[(kGT + row) * 33 + dim];
+          dst[dim] = v;
+        }
       }
     }
     __threadfence();
@@ -559,6 +682,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       float t = 0.f;
       for (int e = tid; e < n_parts; e += kGNT) t += __ldcg(p.loss_part + e);
       float* sf = reinterpret_cast<float*>(sred);
+      __syncthreads();
       sf[tid] = t;
       __syncthreads();
       for (int o = kGNT / 2; o > 0; o >>= 1) {

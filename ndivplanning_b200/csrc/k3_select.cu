@@ -4,6 +4,7 @@
 // Every cost becomes a u64  (ordered_key(cost) << 32) | index  so that one unsigned min
 // implements (cost, index) lexicographic order; the same word is what the multi-GPU
 // min-allreduce exchanges.  HBM-bound: G*K*4 bytes read once, float4-vectorised.
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace ndp {
@@ -237,6 +238,225 @@ verify_refine_kernel(const float* __restrict__ est_topR, const unsigned long lon
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Single-launch selection (the fast path): one block = one chunk of <= 4096 keys held in REGISTERS (16 per thread,
+// coalesced float4 loads issued back to back), block-wide radix select of the topk-th smallest packed key (8-bit
+// digits from the top, leading bytes shared by the block's min and max key skipped, histogram updates aggregated per
+// warp with match.any), gather of the <= topk survivors and a rank-by-counting sort.  When a goal has several chunks
+// the LAST block of the goal (atomic ticket) merges the chunks' survivors the same way: one launch replaces the
+// chunk + merge pair.  Bytes: G*K*4 read once, G*(8 + 8*topk) written — the HBM-bound stage of cfg5.
+// ------------------------------------------------------------------------------------------------------------
+static constexpr int kS2Ept = 16;                       // keys per thread
+static constexpr int kS2Chunk = kSelThreads * kS2Ept;   // 4096 keys per block
+
+struct S2Shared {
+  unsigned hist[256];
+  unsigned long long list[128];
+  unsigned long long wmin[kSelThreads / 32], wmax[kSelThreads / 32];
+  unsigned long long prefix, bmin, bmax;
+  int need, done, cnt, nreal;
+  unsigned ticket;
+};
+
+// keys: distinct packed values (pads = kPadKey).  On return sh.list[0..n) holds the n = min(topk, #real) smallest keys
+// in ascending order (block-wide; every thread returns n).  *block_min = smallest key (kPadKey if none).
+__device__ int block_topk(unsigned long long (&key)[kS2Ept], int topk, S2Shared& sh, unsigned long long* block_min) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned long long mn = kPadKey, mx = 0ull;
+  int nreal = 0;
+#pragma unroll
+  for (int e = 0; e < kS2Ept; ++e) {
+    const bool real = key[e] != kPadKey;
+    mn = key[e] < mn ? key[e] : mn;
+    mx = (real && key[e] > mx) ? key[e] : mx;
+    nreal += real ? 1 : 0;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long a = __shfl_xor_sync(0xffffffffu, mn, o), b = __shfl_xor_sync(0xffffffffu, mx, o);
+    mn = a < mn ? a : mn;
+    mx = b > mx ? b : mx;
+    nreal += __shfl_xor_sync(0xffffffffu, nreal, o);
+  }
+  if (lane == 0) { sh.wmin[warp] = mn; sh.wmax[warp] = mx; sh.hist[warp] = (unsigned)nreal; }
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long a = sh.wmin[0], b = sh.wmax[0];
+    int n = (int)sh.hist[0];
+    for (int w = 1; w < kSelThreads / 32; ++w) {
+      a = sh.wmin[w] < a ? sh.wmin[w] : a;
+      b = sh.wmax[w] > b ? sh.wmax[w] : b;
+      n += (int)sh.hist[w];
+    }
+    sh.bmin = a; sh.bmax = b; sh.nreal = n; sh.cnt = 0;
+  }
+  __syncthreads();
+  *block_min = sh.bmin;
+  const int n_out = sh.nreal < topk ? sh.nreal : topk;
+  if (n_out == 0) return 0;
+  unsigned long long thr;
+  if (sh.nreal <= topk) {
+    thr = sh.bmax;                                       // everything real is selected
+  } else {
+    // ---- radix select of the topk-th smallest key: 8-bit digits from the top
+    const unsigned long long kmin = sh.bmin, kmax = sh.bmax;
+    unsigned long long prefix = 0ull;
+    int need = topk, done = 0, shift = 56;
+    for (; shift >= 0 && (((kmin ^ kmax) >> shift) == 0ull); shift -= 8) {}   // bytes shared by ALL real keys
+    if (shift < 56) prefix = (kmin >> (shift + 8)) << (shift + 8);
+    for (; shift >= 0 && !done; shift -= 8) {
+      sh.hist[tid] = 0u;
+      __syncthreads();
+#pragma unroll
+      for (int e = 0; e < kS2Ept; ++e) {
+        const unsigned long long kv = key[e];
+        const bool act = kv != kPadKey && (shift == 56 || ((kv ^ prefix) >> (shift + 8)) == 0ull);
+        const unsigned digit = (unsigned)(kv >> shift) & 255u;
+        const unsigned peers = __match_any_sync(0xffffffffu, act ? digit : 256u + (unsigned)lane);
+        if (act && lane == __ffs(peers) - 1) atomicAdd(&sh.hist[digit], (unsigned)__popc(peers));
+      }
+      __syncthreads();
+      if (warp == 0) {
+        unsigned c[8], tot = 0;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) { c[b] = sh.hist[lane * 8 + b]; tot += c[b]; }
+        unsigned incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        const unsigned hit = __ballot_sync(0xffffffffu, incl >= (unsigned)need);
+        if (lane == __ffs(hit) - 1) {
+          unsigned before = incl - tot;
+          int b = 0;
+          for (; b < 7; ++b) {
+            if (before + c[b] >= (unsigned)need) break;
+            before += c[b];
+          }
+          sh.prefix = prefix | ((unsigned long long)(lane * 8 + b) << shift);
+          sh.need = need - (int)before;
+          sh.done = ((unsigned)(need - (int)before) == c[b]) ? 1 : 0;
+        }
+      }
+      __syncthreads();
+      prefix = sh.prefix; need = sh.need; done = sh.done;
+      __syncthreads();
+    }
+    // done at some digit: every key of the chosen bin is selected -> lower bits all ones; else prefix is the exact key
+    thr = done ? (prefix | ((shift + 8 > 0) ? ((1ull << (shift + 8)) - 1ull) : 0ull)) : prefix;
+  }
+#pragma unroll
+  for (int e = 0; e < kS2Ept; ++e)
+    if (key[e] != kPadKey && key[e] <= thr) {
+      const int pos = atomicAdd(&sh.cnt, 1);
+      if (pos < 128) sh.list[pos] = key[e];
+    }
+  __syncthreads();
+  const int n = sh.cnt < 128 ? sh.cnt : 128;
+  unsigned long long mine = kPadKey;
+  int rank = 0;
+  if (tid < n) {
+    mine = sh.list[tid];
+    for (int j = 0; j < n; ++j) rank += (sh.list[j] < mine) ? 1 : 0;
+  }
+  __syncthreads();
+  if (tid < n) sh.list[rank] = mine;
+  __syncthreads();
+  return n;
+}
+
+// MODE 0: fp32 costs [G,K];  MODE 1: packed u64 keys [G,K] (K <= 4096, single chunk)
+template <int MODE>
+__global__ void __launch_bounds__(kSelThreads, 4)
+select2_kernel(const float* __restrict__ cost, const unsigned long long* __restrict__ packed_in, int K, int topk,
+               long long idx_base, unsigned long long* __restrict__ out_min, int* __restrict__ topk_idx,
+               float* __restrict__ topk_cost, unsigned long long* __restrict__ part,   // [G][chunks][max(topk,1)]
+               unsigned* __restrict__ tickets, const int* __restrict__ skip) {
+  if (skip && skip[blockIdx.y]) return;
+  __shared__ S2Shared sh;
+  const int g = blockIdx.y, chunk = blockIdx.x, chunks = gridDim.x, tid = threadIdx.x;
+  const int begin = chunk * kS2Chunk;
+  const size_t seg = (size_t)g * (size_t)K;
+  unsigned long long key[kS2Ept];
+  if (MODE == 0) {
+    const float* src = cost + seg;
+    float c[kS2Ept];
+    const bool vec = ((K & 3) == 0) && ((reinterpret_cast<uintptr_t>(cost) & 15) == 0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int i0 = begin + q * 1024 + tid * 4;
+      if (vec && i0 + 3 < K) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(src + i0));
+        c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
+      } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) c[4 * q + r] = (i0 + r < K) ? __ldg(src + i0 + r) : 0.f;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int i = begin + q * 1024 + tid * 4 + r;
+        key[4 * q + r] = i < K ? (((unsigned long long)ordered_key(c[4 * q + r] + 0.0f) << 32) | (unsigned)i) : kPadKey;
+      }
+  } else {
+#pragma unroll
+    for (int e = 0; e < kS2Ept; ++e) {
+      const int i = begin + e * kSelThreads + tid;
+      key[e] = i < K ? packed_in[seg + i] : kPadKey;
+    }
+  }
+  unsigned long long bmin;
+  int n = block_topk(key, topk, sh, &bmin);
+  if (chunks > 1) {
+    // publish this chunk's survivors; the last block of the goal merges all chunks
+    const int W = topk > 0 ? topk : 1;
+    unsigned long long* dst = part + ((size_t)g * chunks + chunk) * W;
+    if (topk > 0) { for (int i = tid; i < topk; i += kSelThreads) dst[i] = i < n ? sh.list[i] : kPadKey; }
+    else if (tid == 0) dst[0] = bmin;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) sh.ticket = atomicAdd(tickets + g, 1u);
+    __syncthreads();
+    if (sh.ticket != (unsigned)(chunks - 1)) return;
+    if (tid == 0) tickets[g] = 0u;                       // self-cleaning for the next call
+    __threadfence();
+    const unsigned long long* src = part + (size_t)g * chunks * W;
+    const int total = chunks * W;                        // <= 4096 (host-checked)
+#pragma unroll
+    for (int e = 0; e < kS2Ept; ++e) {
+      const int i = e * kSelThreads + tid;
+      key[e] = i < total ? __ldcg(src + i) : kPadKey;
+    }
+    __syncthreads();
+    n = block_topk(key, topk, sh, &bmin);
+  }
+  if (tid == 0) {
+    unsigned long long m = bmin;
+    // reference rule: only costs strictly below 1e10 may win (mpc_eval.py:122,161-164)
+    const float c = key_to_float((uint32_t)(m >> 32));
+    if (m == kPadKey || !(c < 1e10f)) m = kInvalidPacked;
+    else m = (m & 0xFFFFFFFF00000000ull) | (unsigned long long)((long long)(m & 0xFFFFFFFFull) + idx_base);
+    out_min[g] = m;
+  }
+  for (int i = tid; i < topk; i += kSelThreads) {
+    const unsigned long long v = i < n ? sh.list[i] : kPadKey;
+    if (topk_idx) topk_idx[(size_t)g * topk + i] = (i >= n) ? -1 : (int)((long long)(v & 0xFFFFFFFFull) + idx_base);
+    if (topk_cost) topk_cost[(size_t)g * topk + i] = (i >= n) ? __int_as_float(0x7fc00000) : key_to_float((uint32_t)(v >> 32));
+  }
+}
+
+// the single-launch path takes: K <= 4096 per goal (one chunk), or chunks * max(topk,1) <= 4096 (in-kernel merge)
+static bool select2_eligible(int G, int K, int topk, int* chunks) {
+  static const bool off = getenv("NDP_SELECT_OLD") != nullptr;     // diagnostics: force the two-stage kernels
+  const int c = (K + kS2Chunk - 1) / kS2Chunk;
+  *chunks = c < 1 ? 1 : c;
+  if (off || K <= 0) return false;
+  return (long long)(*chunks) * (topk > 0 ? topk : 1) <= kS2Chunk && *chunks <= 65535;
+}
+
 static void plan_chunks(int G, int K, int* chunks, int* chunk_len) {
   if (K <= 0) { *chunks = 1; *chunk_len = kSelTile; return; }
   int want = 1184 / (G > 0 ? G : 1);
@@ -260,6 +480,11 @@ extern "C" int ndp_select_workspace_bytes(int G, int K, int topk, size_t* bytes)
   int chunks, len;
   plan_chunks(G, K, &chunks, &len);
   *bytes = chunks > 1 ? (size_t)G * chunks * (size_t)(topk + 1) * 8 + 256 : 256;
+  int c2;
+  if (select2_eligible(G, K, topk, &c2) && c2 > 1) {    // tickets [G] + survivors [G][chunks][max(topk,1)]
+    const size_t b2 = ((size_t)G * 4 + 255) / 256 * 256 + (size_t)G * c2 * (size_t)(topk > 0 ? topk : 1) * 8 + 256;
+    if (b2 > *bytes) *bytes = b2;
+  }
   return NDP_OK;
 }
 
@@ -274,8 +499,26 @@ static int select_impl(const float* cost, int G, int K, int topk, int64_t idx_ba
   if (G == 0) return NDP_OK;
   cudaStream_t s = (cudaStream_t)stream;
   int chunks, len;
-  plan_chunks(G, K, &chunks, &len);
   auto* pm = reinterpret_cast<unsigned long long*>(packed_min);
+  int c2;
+  if (select2_eligible(G, K, topk, &c2)) {              // ONE launch: chunk pass + in-kernel merge by the last block
+    unsigned* tickets = nullptr;
+    unsigned long long* part = nullptr;
+    if (c2 > 1) {
+      const size_t toff = ((size_t)G * 4 + 255) / 256 * 256;
+      const size_t need2 = toff + (size_t)G * c2 * (size_t)(topk > 0 ? topk : 1) * 8;
+      if (ws_bytes < need2 || !ws) { set_error("select: workspace %zu < %zu", ws_bytes, need2); return NDP_ERR_WORKSPACE; }
+      NDP_CHECK_ARG(((uintptr_t)ws & 7) == 0, "select: workspace must be 8-byte aligned");
+      tickets = reinterpret_cast<unsigned*>(ws);
+      part = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ws) + toff);
+      NDP_CUDA(cudaMemsetAsync(tickets, 0, (size_t)G * 4, s));
+    }
+    select2_kernel<0><<<dim3(c2, G), kSelThreads, 0, s>>>(cost, nullptr, K, topk, (long long)idx_base, pm, topk_idx, topk_cost,
+                                                         part, tickets, skip);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
+  plan_chunks(G, K, &chunks, &len);
   if (chunks <= 1) {
     select_kernel<0><<<dim3(1, G), kSelThreads, 0, s>>>(cost, nullptr, K, len > 0 ? len : kSelTile, topk, 1,
                                                         (long long)idx_base, pm, nullptr, topk_idx, topk_cost, skip);
@@ -329,8 +572,8 @@ int mark_fallback(int* verified, int G, cudaStream_t s) {
 int select_packed(const unsigned long long* packed, int G, int n, int topk, long long idx_base,
                   unsigned long long* pm, int* topk_idx, float* topk_cost, cudaStream_t s) {
   NDP_CHECK_ARG(n >= 1 && n <= kSelTile && topk <= 128 && G <= 65535, "select_packed: bad sizes");
-  select_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, packed, n, kSelTile, topk, 1, idx_base, pm, nullptr,
-                                                      topk_idx, topk_cost, nullptr);
+  select2_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, packed, n, topk, idx_base, pm, topk_idx, topk_cost, nullptr,
+                                                       nullptr, nullptr);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }

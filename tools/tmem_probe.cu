@@ -93,6 +93,49 @@ __global__ void __launch_bounds__(128, 1) mma_rate_kernel(int reps, int slot) {
   if (warp == 0) tmem_dealloc512(tmem);
 }
 
+// ---- 3b: MMA issue floor: descriptors precomputed in registers, accumulate flag constant, NI issuing warps (one
+// elected thread each) streaming into disjoint D regions concurrently
+template <int N, int NI>
+__global__ void __launch_bounds__(128, 1) mma_issue_kernel(int reps, int slot) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint32_t tmem_slot;
+  __shared__ __align__(8) unsigned long long bar[4];
+  const int warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < (65536 + 4096) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3C003C00u;
+  if (warp == 0) tmem_alloc512(smem_u32(&tmem_slot));
+  if (threadIdx.x == 0) { for (int i = 0; i < 4; ++i) mbar_init(smem_u32(&bar[i]), 1); fence_mbar_init(); }
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const long long t0 = clock64();
+  if (warp < NI && (threadIdx.x & 31) == 0) {
+    const uint32_t idesc = idesc_f16(N);
+    const uint32_t b0 = smem_u32(smem);
+    uint64_t bd[8];
+#pragma unroll
+    for (int s = 0; s < 8; ++s) bd[s] = smem_desc(b0 + s * (N >= 128 ? 4096 : N * 32), N * 16, 128);
+    const uint32_t D = tmem + warp * 128, A = tmem + 256 + warp * 64;
+    for (int r = 0; r < reps; ++r) {
+#pragma unroll
+      for (int s = 0; s < 8; ++s)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, 1, 0;\n\t"
+                     "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(D), "r"(A + s * 8),
+                     "l"(bd[s]), "r"(idesc)
+                     : "memory");
+    }
+    mma_commit(smem_u32(&bar[warp]));
+    mbar_wait(smem_u32(&bar[warp]), 0);
+  }
+  __syncthreads();
+  const long long t1 = clock64();
+  if (threadIdx.x == 0) g_out[slot] = (unsigned long long)(t1 - t0);
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc512(tmem);
+}
+
 // ---- 4: layer-event round trip -------------------------------------------------------------------
 // NT tiles (1 or 2); per event and tile: 8 MMAs (N=128, K=16, TS) into D_t, commit -> 8 epilogue warps per tile:
 // ld 64 cols, relu, cvt fp16, st 32 cols in place, arrive -> issuer.  Issue order with two tiles: A, B, A, B ...
@@ -187,6 +230,14 @@ int main() {
   printf("mma N=%3d %s: %6.1f clk/MMA total, %6.1f clk/MMA issue  (floor N/2 = %d)\n", N, TS ? "TS" : "SS",  \
          (double)out[2] / 1600, (double)out[3] / 1600, N / 2);
   RATE(16, 1) RATE(64, 1) RATE(128, 1) RATE(256, 1) RATE(64, 0) RATE(128, 0)
+#define ISSUE(N, NI)                                                                                        \
+  CK(cudaFuncSetAttribute(mma_issue_kernel<N, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem3));    \
+  mma_issue_kernel<N, NI><<<1, 128, smem3>>>(200, 6);                                                       \
+  CK(cudaDeviceSynchronize());                                                                              \
+  CK(cudaMemcpyFromSymbol(out, g_out, sizeof(out)));                                                        \
+  printf("mma issue floor N=%3d, %d issuer warp(s), descriptors in registers: %6.1f clk per MMA per issuer, %6.1f clk per MMA aggregate\n", \
+         N, NI, (double)out[6] / 1600, (double)out[6] / 1600 / NI);
+  ISSUE(16, 1) ISSUE(64, 1) ISSUE(128, 1) ISSUE(16, 2) ISSUE(64, 2) ISSUE(128, 2)
   // 4
   CK(cudaFuncSetAttribute(event_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
   CK(cudaFuncSetAttribute(event_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
