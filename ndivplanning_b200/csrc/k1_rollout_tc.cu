@@ -14,6 +14,7 @@
 //
 // TMEM map (512 x 32-bit columns): R0 [0,128) R1 [128,256) DR [256,384) AS [384,512).
 // Warp roles: 0-7 epilogue (lane quadrant = warp%4, column half = warp/4), 8 MMA issue, 9 TMA.
+#include <stdlib.h>
 #include <string.h>
 #include "planner.cuh"
 #include "tc_common.cuh"
@@ -579,6 +580,10 @@ struct TcPlan {
   const float* W1;        // device, torch layout (planner-owned copies)
   const float* b1;
   uint32_t gext_stride;   // bytes per goal
+  // two-tile bulk kernel (np == 1): its own item order / chunking (rollout_tc2_kernel)
+  uint8_t* stream2;
+  TcItem* items2;
+  int n_items2, n_chunks2;
 };
 
 namespace {
@@ -712,10 +717,457 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
   return NDP_OK;
 }
 
+
+// ==========================================================================================================
+// Two-tile bulk kernel (NP = 1, the single-pass estimate of "f16" / "f16+refine"): TWO 128-candidate tiles of one
+// goal per CTA, 256 TMEM columns each, one MMA-issuing warp per tile.
+//
+// Why: with one tile per SM the tensor pipe idles ~40 % of the time behind the strictly serial generator chain
+// (every layer's MMAs wait for the previous layer's TMEM -> ReLU -> fp16 -> TMEM epilogue, ~675 clk per round trip,
+// tools/tmem_probe.cu) and one issuing thread cannot feed N = 64 MMAs faster than one per ~45 clk.  Two independent
+// tiles hide each other's round trips, and two issuing threads reach the N/2-cycle floor also for N = 64 (probe:
+// 32.1 clk per N=64 MMA aggregate).  Both tiles consume the SAME weight ring slot (the slot is released when both
+// issuers have committed), so the L2 -> shared-memory weight traffic per candidate halves.
+//
+// TMEM per tile (base 256 * tile):  AS [0,64) state operand (fp16, K = 128) | P [64,192) | Q [192,256)
+//   G1  D=P[128] <- AS            epilogue P -> Q (64 cols, compact)
+//   G2  D=P[0,64) <- Q            epilogue P[0,64) -> Q[0,32)
+//   G3  D=P[128] <- Q[0,32)       epilogue P -> Q
+//   G4  four N=64 quarters  D=P[0,64) <- Q, epilogue -> P[64,96);  fc5 accumulates per quarter: D5=P[96,112) <- P[64,96)
+//   F1[c] (hidden chunk of 64)  D=Q <- AS, epilogue in place;  F2[c]  DR=P[128] += Q (K = 64)
+// The fp32 state of each tile stays in shared memory (2 x 64 KB) and is advanced with an exact fp32 add per step.
+// Same arithmetic per element as rollout_tc_kernel<1> (same products, same accumulation order).
+// ==========================================================================================================
+static constexpr int kT2Threads = 608;                   // 16 epilogue warps, 2 MMA issuers (16, 17), TMA producer (18)
+static constexpr uint32_t kT2AS = 0, kT2P = 64, kT2Q = 192;
+static constexpr uint32_t kT2OffState = 0;               // 2 tiles x [32 col4][128 rows] float4
+static constexpr uint32_t kT2OffExt = 131072;            // noise[2], action[2], ones: 5 x 4 KB
+static constexpr uint32_t kT2OffRing = kT2OffExt + 5 * kExtSlab;
+static constexpr uint32_t kT2Slot = 20480, kT2NSlot = 3;
+static constexpr uint32_t kT2OffItems = kT2OffRing + kT2NSlot * kT2Slot;
+static constexpr uint32_t kT2OffGoal = kT2OffItems + kItemsBytes;
+static constexpr uint32_t kT2OffRed = kT2OffGoal + 512;          // 2 x 128 floats
+static constexpr uint32_t kT2OffBars = kT2OffRed + 1024;
+static constexpr uint32_t kT2SmemBytes = kT2OffBars + 256;
+
+struct Iss2 {
+  uint32_t slot, par;        // ring position / parity of the "full" barriers
+  uint32_t bars, ring16;
+  uint32_t tile, tb;         // tile index, TMEM base of the tile
+  uint32_t ext_noise, ext_act, ext_ones;   // (ext slab address >> 4) | LBO bits
+  uint32_t ds, aw;           // "D full" events signalled / "A ready" events consumed
+  uint32_t next_ready;
+};
+
+// MMAs of one weight group: NMAIN main slabs (A from TMEM at a + (s/SPC)*CPH + (s%SPC)*8) + optional ext slab (A from smem)
+template <int N, int NMAIN, int EXT, int SPC, int CPH>
+__device__ __forceinline__ void t2_group(const Iss2& st, uint32_t b16, uint32_t d, uint32_t a, uint32_t first) {
+  constexpr uint32_t kDescHi = 0x4000u | (128u >> 4);
+  constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  constexpr uint32_t step = 2 * N;                              // one slab = N*32 bytes, in 16-byte units
+  const uint32_t blo = b16 | ((uint32_t)N << 16);               // LBO = N*16 bytes
+  uint32_t acc = first ? 0u : 1u;
+#pragma unroll
+  for (int s = 0; s < NMAIN; ++s) {
+    mma_ts(d, a + (s / SPC) * CPH + (s % SPC) * 8, pack64(blo + s * step, kDescHi), kIdesc, acc);
+    acc = 1;
+  }
+  if (EXT) {
+    const uint32_t ea = EXT == 1 ? st.ext_noise : (EXT == 2 ? st.ext_act : st.ext_ones);
+    mma_ss(d, pack64(ea, kDescHi), pack64(blo + NMAIN * step, kDescHi), kIdesc, acc);
+  }
+}
+
+__device__ __forceinline__ void t2_begin(Iss2& st, uint32_t bar_aready0, bool wait_a) {
+  if (wait_a) {
+    mbar_wait(bar_aready0 + 8 * (st.aw & 1), (st.aw >> 1) & 1);
+    ++st.aw;
+  }
+  if (!st.next_ready) mbar_wait(st.bars + 8 * st.slot, st.par);
+  fence_after_sync();
+}
+__device__ __forceinline__ void t2_end(Iss2& st, bool signal_d, bool elected) {
+  if (elected) {
+    mma_commit(st.bars + 8 * (3 + st.slot));                    // slot is free when BOTH issuers have committed
+    if (signal_d) mma_commit(st.bars + 8 * (6 + 2 * st.tile + (st.ds & 1)));
+  }
+  __syncwarp();
+  if (signal_d) ++st.ds;
+  if (++st.slot == kT2NSlot) { st.slot = 0; st.par ^= 1; }
+  st.next_ready = mbar_try_wait(st.bars + 8 * st.slot, st.par) ? 1u : 0u;
+}
+__device__ __forceinline__ uint32_t t2_slot16(const Iss2& st) { return st.ring16 + st.slot * (kT2Slot >> 4); }
+
+// 32 accumulator columns -> relu -> 16 packed fp16 columns
+__device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
+  uint32_t v[32];
+  tmem_ld32(src, v);
+  tmem_ld_wait();
+  uint32_t hi[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j)
+    hi[j] = pack_hi(fmaxf(__uint_as_float(v[2 * j]), 0.f), fmaxf(__uint_as_float(v[2 * j + 1]), 0.f));
+  tmem_st16(dst, hi);
+}
+
+__global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = blockIdx.x / p.tiles_per_goal;                  // tiles_per_goal counts tile PAIRS here
+  const int pair = blockIdx.x % p.tiles_per_goal;
+
+  uint8_t* ext_base = smem + kT2OffExt;                         // noise0, noise1, act0, act1, ones
+  uint8_t* ext_ones = ext_base + 4 * kExtSlab;
+  TcItem* items = reinterpret_cast<TcItem*>(smem + kT2OffItems);
+  float* s_goal = reinterpret_cast<float*>(smem + kT2OffGoal);
+  float* s_red = reinterpret_cast<float*>(smem + kT2OffRed);
+  const uint32_t bars = smem_u32(smem + kT2OffBars);
+  // barrier map (8 bytes each): full[0..2] empty[3..5] d_full[tile][2] @6..9  a_ready[tile][2] @10..13; tmem base at +128
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kT2OffBars + 128);
+
+  for (int i = tid; i < p.n_items * 8; i += kT2Threads)
+    reinterpret_cast<uint32_t*>(items)[i] = reinterpret_cast<const uint32_t*>(p.items)[i];
+  for (int i = tid; i < 5 * (int)kExtSlab / 16; i += kT2Threads)
+    reinterpret_cast<uint4*>(ext_base)[i] = make_uint4(0, 0, 0, 0);
+  if (tid < 128) s_goal[tid] = __ldg(p.goal + (size_t)g * 128 + tid);
+  if (tid == 0) {
+    for (uint32_t s = 0; s < kT2NSlot; ++s) { mbar_init(bars + 8 * s, 1); mbar_init(bars + 8 * (3 + s), 2); }
+    for (uint32_t e = 0; e < 4; ++e) { mbar_init(bars + 8 * (6 + e), 1); mbar_init(bars + 8 * (10 + e), 8); }
+    fence_mbar_init();
+  }
+  if (warp == 16) tmem_alloc512(smem_u32((const void*)tmem_slot));
+  __syncthreads();
+  if (tid < 128) *reinterpret_cast<uint16_t*>(ext_ones + (tid >> 3) * 128 + (tid & 7) * 16) = 0x3C00;   // k=0 column = 1.0
+  fence_proxy_async();
+  fence_before_sync();
+  __syncthreads();
+  fence_after_sync();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 18) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      const uint8_t* gsrc = p.gext + (size_t)g * p.gext_stride;
+      for (int t = 0; t < p.T; ++t) {
+        for (int i = 0; i < p.n_items; ++i, ++it) {
+          const uint32_t slot = it % kT2NSlot, par = (it / kT2NSlot) & 1;
+          const uint32_t bytes = items[i].bytes, eb = items[i].ext_bytes;
+          mbar_wait(bars + 8 * (3 + slot), par ^ 1);
+          mbar_expect_tx(bars + 8 * slot, bytes + eb);
+          const uint32_t dst = smem_u32(smem + kT2OffRing + slot * kT2Slot);
+          bulk_g2s(dst, p.stream + items[i].src_off, bytes, bars + 8 * slot);
+          if (eb) bulk_g2s(dst + bytes, gsrc, eb, bars + 8 * slot);
+        }
+      }
+    }
+  } else if (warp >= 16) {
+    // ===================== MMA issuers: warp 16 -> tile 0, warp 17 -> tile 1 =====================
+    Iss2 st;
+    st.tile = (uint32_t)(warp - 16);
+    st.tb = tmem + 256 * st.tile;
+    st.slot = 0; st.par = 0; st.next_ready = 0; st.bars = bars; st.ring16 = smem_u32(smem + kT2OffRing) >> 4;
+    st.ds = 0; st.aw = 0;
+    const uint32_t ext_lbo = (2048u >> 4) << 16;               // A ext slabs: LBO = 2 KB, SBO = 128 B
+    st.ext_noise = (smem_u32(ext_base + st.tile * kExtSlab) >> 4) | ext_lbo;
+    st.ext_act = (smem_u32(ext_base + (2 + st.tile) * kExtSlab) >> 4) | ext_lbo;
+    st.ext_ones = (smem_u32(ext_ones) >> 4) | ext_lbo;
+    const uint32_t bar_a = bars + 8 * (10 + 2 * st.tile);
+    const uint32_t AS = st.tb + kT2AS, P = st.tb + kT2P, Q = st.tb + kT2Q;
+    const int nch = p.n_hid_chunks;                             // hidden chunks of 64
+    for (int t = 0; t < p.T; ++t) {
+      bool el;
+      // ---- generator fc1 (two items: state columns 0..63, then 64..127 + [noise | per-goal bias])
+      t2_begin(st, bar_a, true);
+      if ((el = elect_one())) t2_group<128, 4, 0, 16, 0>(st, t2_slot16(st), P, AS, 1);
+      t2_end(st, false, el);
+      t2_begin(st, bar_a, false);
+      if ((el = elect_one())) t2_group<128, 4, 1, 16, 0>(st, t2_slot16(st), P, AS + 32, 0);
+      t2_end(st, true, el);
+      // ---- fc2 (N = 64)
+      t2_begin(st, bar_a, true);
+      if ((el = elect_one())) t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
+      t2_end(st, true, el);
+      // ---- fc3 (K = 64)
+      t2_begin(st, bar_a, true);
+      if ((el = elect_one())) t2_group<128, 4, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
+      t2_end(st, true, el);
+      // ---- fc4 quarter 0
+      t2_begin(st, bar_a, true);
+      if ((el = elect_one())) t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
+      t2_end(st, true, el);
+      // ---- [fc5 part i | fc4 quarter i+1], i = 0..2
+#pragma unroll 1
+      for (int i = 0; i < 3; ++i) {
+        t2_begin(st, bar_a, true);
+        if ((el = elect_one())) {
+          t2_group<16, 4, 0, 16, 0>(st, t2_slot16(st), P + 96, P + 64, i == 0);
+          t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st) + (2048 >> 4), P, Q, 1);
+        }
+        t2_end(st, true, el);
+      }
+      // ---- fc5 part 3 + bias
+      t2_begin(st, bar_a, true);
+      if ((el = elect_one())) t2_group<16, 4, 3, 16, 0>(st, t2_slot16(st), P + 96, P + 64, 0);
+      t2_end(st, true, el);
+      // ---- forward model: F1[0]; then F2[c], F1[c+1]
+      t2_begin(st, bar_a, true);
+      if ((el = elect_one())) t2_group<64, 8, 2, 16, 0>(st, t2_slot16(st), Q, AS, 1);
+      t2_end(st, true, el);
+#pragma unroll 1
+      for (int c = 0; c < nch; ++c) {
+        const bool last = (c == nch - 1);
+        t2_begin(st, bar_a, true);
+        if ((el = elect_one())) {
+          if (last) t2_group<128, 4, 3, 2, 32>(st, t2_slot16(st), P, Q, c == 0);
+          else t2_group<128, 4, 0, 2, 32>(st, t2_slot16(st), P, Q, c == 0);
+        }
+        t2_end(st, last, el);
+        if (!last) {
+          t2_begin(st, bar_a, false);
+          if ((el = elect_one())) t2_group<64, 8, 2, 16, 0>(st, t2_slot16(st), Q, AS, 1);
+          t2_end(st, true, el);
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue warps: tile = warp / 8 =====================
+    const int tile = warp >> 3, q = warp & 3, h = (warp >> 2) & 1;
+    const int m = q * 32 + lane;                                // candidate row = TMEM lane
+    const int cand = (pair * 2 + tile) * 128 + m;
+    const bool valid = cand < p.K;
+    float4* S4 = reinterpret_cast<float4*>(smem + kT2OffState) + tile * 4096;
+    uint8_t* ext_noise = ext_base + tile * kExtSlab;
+    uint8_t* ext_act = ext_base + (2 + tile) * kExtSlab;
+    const uint32_t lane_base = tmem + 256 * tile + ((uint32_t)(q * 32) << 16);
+    const uint32_t AS = lane_base + kT2AS, P = lane_base + kT2P, Q = lane_base + kT2Q;
+    const uint32_t bar_d = bars + 8 * (6 + 2 * tile), bar_a = bars + 8 * (10 + 2 * tile);
+    uint32_t dw = 0, ae = 0;
+    auto wait_d = [&]() {
+      mbar_wait(bar_d + 8 * (dw & 1), (dw >> 1) & 1);
+      ++dw;
+      fence_after_sync();
+    };
+    auto signal_a = [&](bool wrote_smem = false) {
+      tmem_st_wait();
+      if (wrote_smem) fence_proxy_async();
+      fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_a + 8 * (ae & 1));
+      ++ae;
+    };
+    auto noise_row = [&](int t) {                               // ext row [noise.., 1] of step t (h == 0 threads)
+      float x[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) x[k] = 0.f;
+      if (t < p.T) {
+        const float* src = p.noise + (((size_t)t * p.G + g) * p.K + cand) * p.nd;
+#pragma unroll
+        for (int k = 0; k < 15; ++k)
+          if (k < p.nd && valid) x[k] = __ldg(src + k);
+#pragma unroll
+        for (int k = 0; k < 16; ++k)
+          if (k == p.nd) x[k] = 1.f;
+      }
+      const uint32_t off = (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        if (c == 1 && p.nd < 8) break;
+        uint4 hv;
+        hv.x = pack_hi(x[8 * c + 0], x[8 * c + 1]); hv.y = pack_hi(x[8 * c + 2], x[8 * c + 3]);
+        hv.z = pack_hi(x[8 * c + 4], x[8 * c + 5]); hv.w = pack_hi(x[8 * c + 6], x[8 * c + 7]);
+        *reinterpret_cast<uint4*>(ext_noise + c * 2048 + off) = hv;
+      }
+    };
+    // ---- init: state <- e0, AS <- fp16(e0), noise ext of step 0
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      uint32_t hi[16];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + u * 8 + c);
+        S4[(h * 16 + u * 8 + c) * 128 + m] = v;
+        hi[2 * c] = pack_hi(v.x, v.y); hi[2 * c + 1] = pack_hi(v.z, v.w);
+      }
+      tmem_st16(AS + 32 * h + 16 * u, hi);
+    }
+    if (h == 0) noise_row(0);
+    signal_a(true);
+    for (int t = 0; t < p.T; ++t) {
+      // ---- G1 (N=128 in P) -> Q ; G2 (N=64 in P[0,64)) -> Q[0,32) ; G3 (N=128 in P) -> Q
+      wait_d(); t2_relu32(P + 64 * h, Q + 32 * h); t2_relu32(P + 64 * h + 32, Q + 32 * h + 16); signal_a();
+      wait_d(); t2_relu32(P + 32 * h, Q + 16 * h); signal_a();
+      wait_d(); t2_relu32(P + 64 * h, Q + 32 * h); t2_relu32(P + 64 * h + 32, Q + 32 * h + 16); signal_a();
+      // ---- G4 quarters (N=64 in P[0,64)) -> P[64,96)
+#pragma unroll 1
+      for (int i = 0; i < 4; ++i) { wait_d(); t2_relu32(P + 32 * h, P + 64 + 16 * h); signal_a(); }
+      // ---- G5 (4 real columns in P[96,100)): action -> ext slab; step-0 actions are the plan's a0
+      wait_d();
+      if (h == 0) {
+        uint32_t av[4];
+        tmem_ld4(P + 96, av);
+        tmem_ld_wait();
+        const float a0 = __uint_as_float(av[0]), a1 = __uint_as_float(av[1]), a2 = __uint_as_float(av[2]), a3 = __uint_as_float(av[3]);
+        uint4 hv;
+        hv.x = pack_hi(a0, a1); hv.y = pack_hi(a2, a3); hv.z = pack_hi(1.f, 0.f); hv.w = 0u;
+        *reinterpret_cast<uint4*>(ext_act + (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16) = hv;
+        if (t == 0 && valid)   // mpc_eval.py:150-151
+          *reinterpret_cast<float4*>(p.a0 + ((size_t)g * p.K + cand) * 4) = make_float4(a0, a1, a2, a3);
+      }
+      signal_a(true);
+      // ---- forward model hidden chunks of 64: F1[c] accumulator in Q -> relu -> A of F2[c], in place
+#pragma unroll 1
+      for (int c = 0; c < p.n_hid_chunks; ++c) { wait_d(); t2_relu32(Q + 32 * h, Q + 32 * h); signal_a(); }
+      // ---- END: state += residual (fp32, exact add; forward_encoder.py:113-114), new A operand, next noise
+      wait_d();
+      const bool more = t + 1 < p.T;
+      float cs = 0.f;
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        uint32_t r[32];
+        tmem_ld32(P + 64 * h + 32 * u, r);
+        float4 sv[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) sv[c] = S4[(h * 16 + u * 8 + c) * 128 + m];
+        tmem_ld_wait();
+        uint32_t hi[16];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          float4 v = sv[c];
+          v.x += __uint_as_float(r[4 * c]); v.y += __uint_as_float(r[4 * c + 1]);
+          v.z += __uint_as_float(r[4 * c + 2]); v.w += __uint_as_float(r[4 * c + 3]);
+          sv[c] = v;
+          hi[2 * c] = pack_hi(v.x, v.y); hi[2 * c + 1] = pack_hi(v.z, v.w);
+        }
+        if (more) {
+          tmem_st16(AS + 32 * h + 16 * u, hi);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) S4[(h * 16 + u * 8 + c) * 128 + m] = sv[c];
+        } else {
+          // terminal cost: mean over E of squared error (nn.MSELoss, mpc_eval.py:161); same summation order as
+          // rollout_tc_kernel: one running fma chain over this thread's 64 columns
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const float* gl = s_goal + 64 * h + 32 * u + 4 * c;
+            float df = sv[c].x - gl[0]; cs = fmaf(df, df, cs);
+            df = sv[c].y - gl[1]; cs = fmaf(df, df, cs);
+            df = sv[c].z - gl[2]; cs = fmaf(df, df, cs);
+            df = sv[c].w - gl[3]; cs = fmaf(df, df, cs);
+          }
+          if (p.state_T && valid) {
+            float4* o = reinterpret_cast<float4*>(p.state_T + ((size_t)g * p.K + cand) * 128) + h * 16 + u * 8;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) o[c] = sv[c];
+          }
+        }
+      }
+      if (more) {
+        if (h == 0) noise_row(t + 1);
+        signal_a(true);
+      } else {
+        if (h == 1) s_red[tile * 128 + m] = cs;
+        if (tile == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
+        else asm volatile("bar.sync 2, 256;" ::: "memory");
+        if (h == 0 && valid) p.cost[(size_t)g * p.K + cand] = (cs + s_red[tile * 128 + m]) * (1.0f / 128.0f);
+      }
+    }
+  }
+  fence_before_sync();
+  __syncthreads();
+  if (warp == 16) tmem_dealloc512(tmem);
+}
+
+// host side: weight stream of the two-tile kernel (fp16 hi only), items in the kernel's consumption order
+static int tc2_build(TcPlan* P, int E, int nd, int H, const float* const* Wt, const float* const* bt, cudaStream_t s) {
+  const int nch = H / 64;
+  P->n_chunks2 = nch;
+  const size_t cap = (size_t)(2 * 16384 + 18432 + 20480 + 18432 + 3 * 20480 + 4096) + (size_t)nch * (18432 + 20480) + 128 * kTcMaxItems;
+  cudaError_t e = cudaMalloc(&P->stream2, cap);
+  if (e == cudaSuccess) e = cudaMalloc(&P->items2, sizeof(TcItem) * kTcMaxItems);
+  if (e != cudaSuccess) { set_error("two-tile plan: cudaMalloc failed: %s", cudaGetErrorString(e)); return NDP_ERR_CUDA; }
+  cudaMemsetAsync(P->stream2, 0, cap, s);
+  TcItem items[kTcMaxItems];
+  int n = 0;
+  size_t off = 0;
+  const int C1 = 2 * E + nd;
+  auto main_blk = [&](const float* W, int ld, int n0, int nvalid, int k0, int N, int nslab, size_t at) {
+    const int total = N * nslab * 16;
+    tc_pack_main_kernel<<<(total + 255) / 256, 256, 0, s>>>(reinterpret_cast<__half*>(P->stream2 + at), nullptr, W, ld, n0, k0, N, nslab, nvalid);
+    count_launch();
+    return (size_t)N * 32 * nslab;
+  };
+  auto ext_blk = [&](int N, int nvalid, const ExtCols& c, size_t at) {
+    tc_pack_ext_kernel<<<(N * 16 + 255) / 256, 256, 0, s>>>(reinterpret_cast<__half*>(P->stream2 + at), nullptr, N, nvalid, c);
+    count_launch();
+    return (size_t)N * 32;
+  };
+  auto close_item = [&](size_t bytes, uint32_t ext_bytes) -> int {
+    if (n >= kTcMaxItems) { set_error("two-tile plan: too many stream items (H too large)"); return NDP_ERR_ARG; }
+    if (bytes + ext_bytes > kT2Slot) { set_error("two-tile plan: item of %zu bytes exceeds the ring slot", bytes + ext_bytes); return NDP_ERR_ARG; }
+    TcItem& I = items[n++];
+    memset(&I, 0, sizeof(I));
+    I.src_off = (uint32_t)off; I.bytes = (uint32_t)bytes; I.ext_bytes = ext_bytes;
+    off += (bytes + 127) / 128 * 128;
+    return NDP_OK;
+  };
+  int rc;
+  size_t b;
+  ExtCols x;
+  // G1a, G1b (+ per-goal ext block from the workspace)
+  b = main_blk(Wt[0], C1, 0, 128, 0, 128, 4, off);
+  if ((rc = close_item(b, 0))) return rc;
+  b = main_blk(Wt[0], C1, 0, 128, 64, 128, 4, off);
+  if ((rc = close_item(b, 128 * 32))) return rc;
+  // G2 (N=64), G3 (K=64)
+  b = main_blk(Wt[1], 128, 0, 64, 0, 64, 8, off); x = bias_only(bt[1]); b += ext_blk(64, 64, x, off + b);
+  if ((rc = close_item(b, 0))) return rc;
+  b = main_blk(Wt[2], 64, 0, 128, 0, 128, 4, off); x = bias_only(bt[2]); b += ext_blk(128, 128, x, off + b);
+  if ((rc = close_item(b, 0))) return rc;
+  // G4 quarter 0; [G5 part i | G4 quarter i+1]; G5 part 3 + bias
+  b = main_blk(Wt[3], 128, 0, 64, 0, 64, 8, off); x = bias_only(bt[3]); b += ext_blk(64, 64, x, off + b);
+  if ((rc = close_item(b, 0))) return rc;
+  for (int i = 0; i < 3; ++i) {
+    b = main_blk(Wt[4], 256, 0, 4, 64 * i, 16, 4, off);                    // fc5 padded to N=16, K slice of quarter i
+    b += main_blk(Wt[3], 128, 64 * (i + 1), 64, 0, 64, 8, off + b);
+    x = bias_only(bt[3] + 64 * (i + 1)); b += ext_blk(64, 64, x, off + b);
+    if ((rc = close_item(b, 0))) return rc;
+  }
+  b = main_blk(Wt[4], 256, 0, 4, 192, 16, 4, off); x = bias_only(bt[4]); b += ext_blk(16, 4, x, off + b);
+  if ((rc = close_item(b, 0))) return rc;
+  // forward model: F1[c] = fc1 rows of hidden chunk c (ext = [action cols | bias]); F2[c] = fc2 columns of chunk c
+  auto F1 = [&](int c) -> int {
+    ExtCols a;
+    memset(&a, 0, sizeof(a));
+    for (int k = 0; k < 4; ++k) { a.p[k] = Wt[5] + (size_t)c * 64 * (E + 4) + E + k; a.stride[k] = E + 4; }
+    a.p[4] = bt[5] + c * 64; a.stride[4] = 1;
+    size_t bb = main_blk(Wt[5], E + 4, c * 64, 64, 0, 64, 8, off);
+    bb += ext_blk(64, 64, a, off + bb);
+    return close_item(bb, 0);
+  };
+  auto F2 = [&](int c) -> int {
+    size_t bb = main_blk(Wt[6], H, 0, 128, c * 64, 128, 4, off);
+    if (c == nch - 1) { ExtCols bc = bias_only(bt[6]); bb += ext_blk(128, 128, bc, off + bb); }
+    return close_item(bb, 0);
+  };
+  if ((rc = F1(0))) return rc;
+  for (int c = 0; c < nch; ++c) {
+    if ((rc = F2(c))) return rc;
+    if (c + 1 < nch && (rc = F1(c + 1))) return rc;
+  }
+  if (cudaGetLastError() != cudaSuccess) { set_error("two-tile plan: pack kernel launch failed"); return NDP_ERR_CUDA; }
+  P->n_items2 = n;
+  e = cudaMemcpyAsync(P->items2, items, sizeof(TcItem) * n, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);                     // `items` is on this stack frame
+  if (e != cudaSuccess) { set_error("two-tile plan: upload failed: %s", cudaGetErrorString(e)); return NDP_ERR_CUDA; }
+  return NDP_OK;
+}
+
 void tc_plan_destroy(TcPlan* p) {
   if (!p) return;
   if (p->stream) cudaFree(p->stream);
   if (p->items) cudaFree(p->items);
+  if (p->stream2) cudaFree(p->stream2);
+  if (p->items2) cudaFree(p->items2);
   delete p;
 }
 
@@ -762,6 +1214,23 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
   tp.state_T = state_T; tp.G = G; tp.K = K; tp.T = T; tp.nd = P->nd; tp.n_items = P->n_items;
   tp.list = list; tp.R = R; tp.packed_c = packed_c; tp.skip = skip;
   tp.tiles_per_goal = ((list ? R : K) + 127) / 128; tp.n_hid_chunks = P->n_chunks;
+  if (P->np == 1 && P->stream2 && !list && !skip) {
+    // bulk estimate: two tiles per CTA (rollout_tc2_kernel)
+    tp.stream = P->stream2; tp.items = P->items2; tp.n_items = P->n_items2; tp.n_hid_chunks = P->n_chunks2;
+    tp.tiles_per_goal = (tp.tiles_per_goal + 1) / 2;            // tile pairs
+    const long long grid2 = (long long)G * tp.tiles_per_goal;
+    NDP_CHECK_ARG(grid2 <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
+    int dev = 0;
+    NDP_CUDA(cudaGetDevice(&dev));
+    static unsigned long long attr_mask = 0;
+    if (!(attr_mask >> (dev & 63) & 1ull)) {
+      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
+      attr_mask |= 1ull << (dev & 63);
+    }
+    rollout_tc2_kernel<<<(int)grid2, kT2Threads, kT2SmemBytes, s>>>(tp);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
   const long long grid = (long long)G * tp.tiles_per_goal;
   NDP_CHECK_ARG(grid <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
   if (P->np == 1) return launch_np<1>(tp, (int)grid, s);

@@ -250,7 +250,7 @@ static constexpr int kS2Ept = 16;                       // keys per thread
 static constexpr int kS2Chunk = kSelThreads * kS2Ept;   // 4096 keys per block
 
 struct S2Shared {
-  unsigned hist[256];
+  unsigned hist[kSelThreads / 32][256];                 // one histogram per warp: plain shared atomics, no cross-warp contention
   unsigned long long list[128];
   unsigned long long wmin[kSelThreads / 32], wmax[kSelThreads / 32];
   unsigned long long prefix, bmin, bmax;
@@ -278,15 +278,15 @@ __device__ int block_topk(unsigned long long (&key)[kS2Ept], int topk, S2Shared&
     mx = b > mx ? b : mx;
     nreal += __shfl_xor_sync(0xffffffffu, nreal, o);
   }
-  if (lane == 0) { sh.wmin[warp] = mn; sh.wmax[warp] = mx; sh.hist[warp] = (unsigned)nreal; }
+  if (lane == 0) { sh.wmin[warp] = mn; sh.wmax[warp] = mx; sh.hist[0][warp] = (unsigned)nreal; }
   __syncthreads();
   if (tid == 0) {
     unsigned long long a = sh.wmin[0], b = sh.wmax[0];
-    int n = (int)sh.hist[0];
+    int n = (int)sh.hist[0][0];
     for (int w = 1; w < kSelThreads / 32; ++w) {
       a = sh.wmin[w] < a ? sh.wmin[w] : a;
       b = sh.wmax[w] > b ? sh.wmax[w] : b;
-      n += (int)sh.hist[w];
+      n += (int)sh.hist[0][w];
     }
     sh.bmin = a; sh.bmax = b; sh.nreal = n; sh.cnt = 0;
   }
@@ -305,21 +305,25 @@ __device__ int block_topk(unsigned long long (&key)[kS2Ept], int topk, S2Shared&
     for (; shift >= 0 && (((kmin ^ kmax) >> shift) == 0ull); shift -= 8) {}   // bytes shared by ALL real keys
     if (shift < 56) prefix = (kmin >> (shift + 8)) << (shift + 8);
     for (; shift >= 0 && !done; shift -= 8) {
-      sh.hist[tid] = 0u;
+#pragma unroll
+      for (int w = 0; w < kSelThreads / 32; ++w) sh.hist[w][tid] = 0u;
       __syncthreads();
 #pragma unroll
       for (int e = 0; e < kS2Ept; ++e) {
         const unsigned long long kv = key[e];
         const bool act = kv != kPadKey && (shift == 56 || ((kv ^ prefix) >> (shift + 8)) == 0ull);
-        const unsigned digit = (unsigned)(kv >> shift) & 255u;
-        const unsigned peers = __match_any_sync(0xffffffffu, act ? digit : 256u + (unsigned)lane);
-        if (act && lane == __ffs(peers) - 1) atomicAdd(&sh.hist[digit], (unsigned)__popc(peers));
+        if (act) atomicAdd(&sh.hist[warp][(unsigned)(kv >> shift) & 255u], 1u);
       }
       __syncthreads();
       if (warp == 0) {
         unsigned c[8], tot = 0;
 #pragma unroll
-        for (int b = 0; b < 8; ++b) { c[b] = sh.hist[lane * 8 + b]; tot += c[b]; }
+        for (int b = 0; b < 8; ++b) {
+          unsigned v = 0;
+#pragma unroll
+          for (int w = 0; w < kSelThreads / 32; ++w) v += sh.hist[w][lane * 8 + b];
+          c[b] = v; tot += v;
+        }
         unsigned incl = tot;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -367,8 +371,8 @@ __device__ int block_topk(unsigned long long (&key)[kS2Ept], int topk, S2Shared&
 }
 
 // MODE 0: fp32 costs [G,K];  MODE 1: packed u64 keys [G,K] (K <= 4096, single chunk)
-template <int MODE>
-__global__ void __launch_bounds__(kSelThreads, 4)
+template <int MODE, bool ARGMIN_ONLY>
+__global__ void __launch_bounds__(kSelThreads, ARGMIN_ONLY ? 6 : 4)
 select2_kernel(const float* __restrict__ cost, const unsigned long long* __restrict__ packed_in, int K, int topk,
                long long idx_base, unsigned long long* __restrict__ out_min, int* __restrict__ topk_idx,
                float* __restrict__ topk_cost, unsigned long long* __restrict__ part,   // [G][chunks][max(topk,1)]
@@ -394,13 +398,27 @@ select2_kernel(const float* __restrict__ cost, const unsigned long long* __restr
         for (int r = 0; r < 4; ++r) c[4 * q + r] = (i0 + r < K) ? __ldg(src + i0 + r) : 0.f;
       }
     }
+    if (ARGMIN_ONLY) {                                   // fold to one running minimum: no key array kept live
+      unsigned long long m = kPadKey;
 #pragma unroll
-    for (int q = 0; q < 4; ++q)
+      for (int q = 0; q < 4; ++q)
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int i = begin + q * 1024 + tid * 4 + r;
-        key[4 * q + r] = i < K ? (((unsigned long long)ordered_key(c[4 * q + r] + 0.0f) << 32) | (unsigned)i) : kPadKey;
-      }
+        for (int r = 0; r < 4; ++r) {
+          const int i = begin + q * 1024 + tid * 4 + r;
+          const unsigned long long kv = i < K ? (((unsigned long long)ordered_key(c[4 * q + r] + 0.0f) << 32) | (unsigned)i) : kPadKey;
+          m = kv < m ? kv : m;
+        }
+#pragma unroll
+      for (int e = 0; e < kS2Ept; ++e) key[e] = m;
+    } else {
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const int i = begin + q * 1024 + tid * 4 + r;
+          key[4 * q + r] = i < K ? (((unsigned long long)ordered_key(c[4 * q + r] + 0.0f) << 32) | (unsigned)i) : kPadKey;
+        }
+    }
   } else {
 #pragma unroll
     for (int e = 0; e < kS2Ept; ++e) {
@@ -409,7 +427,22 @@ select2_kernel(const float* __restrict__ cost, const unsigned long long* __restr
     }
   }
   unsigned long long bmin;
-  int n = block_topk(key, topk, sh, &bmin);
+  int n = 0;
+  if (ARGMIN_ONLY || topk == 0) {                       // argmin only: warp shuffles + one barrier
+    unsigned long long m = key[0];
+#pragma unroll
+    for (int e = 1; e < kS2Ept; ++e) m = key[e] < m ? key[e] : m;
+    m = warp_min_u64(m);
+    if ((tid & 31) == 0) sh.wmin[tid >> 5] = m;
+    __syncthreads();
+    m = sh.wmin[0];
+#pragma unroll
+    for (int w = 1; w < kSelThreads / 32; ++w) m = sh.wmin[w] < m ? sh.wmin[w] : m;
+    bmin = m;
+    __syncthreads();
+  } else {
+    n = block_topk(key, topk, sh, &bmin);
+  }
   if (chunks > 1) {
     // publish this chunk's survivors; the last block of the goal merges all chunks
     const int W = topk > 0 ? topk : 1;
@@ -431,7 +464,20 @@ select2_kernel(const float* __restrict__ cost, const unsigned long long* __restr
       key[e] = i < total ? __ldcg(src + i) : kPadKey;
     }
     __syncthreads();
-    n = block_topk(key, topk, sh, &bmin);
+    if (ARGMIN_ONLY) {
+      unsigned long long m = key[0];
+#pragma unroll
+      for (int e = 1; e < kS2Ept; ++e) m = key[e] < m ? key[e] : m;
+      m = warp_min_u64(m);
+      if ((tid & 31) == 0) sh.wmin[tid >> 5] = m;
+      __syncthreads();
+      m = sh.wmin[0];
+#pragma unroll
+      for (int w = 1; w < kSelThreads / 32; ++w) m = sh.wmin[w] < m ? sh.wmin[w] : m;
+      bmin = m;
+    } else {
+      n = block_topk(key, topk, sh, &bmin);
+    }
   }
   if (tid == 0) {
     unsigned long long m = bmin;
@@ -513,8 +559,12 @@ static int select_impl(const float* cost, int G, int K, int topk, int64_t idx_ba
       part = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ws) + toff);
       NDP_CUDA(cudaMemsetAsync(tickets, 0, (size_t)G * 4, s));
     }
-    select2_kernel<0><<<dim3(c2, G), kSelThreads, 0, s>>>(cost, nullptr, K, topk, (long long)idx_base, pm, topk_idx, topk_cost,
-                                                         part, tickets, skip);
+    if (topk == 0)
+      select2_kernel<0, true><<<dim3(c2, G), kSelThreads, 0, s>>>(cost, nullptr, K, 0, (long long)idx_base, pm, nullptr, nullptr,
+                                                                 part, tickets, skip);
+    else
+      select2_kernel<0, false><<<dim3(c2, G), kSelThreads, 0, s>>>(cost, nullptr, K, topk, (long long)idx_base, pm, topk_idx,
+                                                                  topk_cost, part, tickets, skip);
     NDP_LAUNCH_CHECK();
     return NDP_OK;
   }
@@ -572,8 +622,8 @@ int mark_fallback(int* verified, int G, cudaStream_t s) {
 int select_packed(const unsigned long long* packed, int G, int n, int topk, long long idx_base,
                   unsigned long long* pm, int* topk_idx, float* topk_cost, cudaStream_t s) {
   NDP_CHECK_ARG(n >= 1 && n <= kSelTile && topk <= 128 && G <= 65535, "select_packed: bad sizes");
-  select2_kernel<1><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, packed, n, topk, idx_base, pm, topk_idx, topk_cost, nullptr,
-                                                       nullptr, nullptr);
+  select2_kernel<1, false><<<dim3(1, G), kSelThreads, 0, s>>>(nullptr, packed, n, topk, idx_base, pm, topk_idx, topk_cost,
+                                                              nullptr, nullptr, nullptr);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }

@@ -1,0 +1,55 @@
+"""Dev check of the two-tile bulk kernel (rollout_tc2_kernel): costs / actions / terminal states must equal the one-tile
+kernel rollout_tc_kernel<1> BIT FOR BIT (same products, same accumulation order), for full, ragged and multi-goal shapes.
+The one-tile reference runs in a child process with NDP_TC_ONE_TILE=1 (the switch is read once per process)."""
+import os
+import subprocess
+import sys
+import tempfile
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+from ndivplanning_b200 import FusedPlanner, synthetic  # noqa: E402
+
+CFGS = [(1, 256, 1, 128, 2), (1, 256, 3, 256, 2), (2, 300, 4, 256, 2), (1, 1024, 8, 1024, 2), (3, 130, 3, 384, 5),
+        (1, 257, 5, 2048, 15), (1, 65536, 8, 1024, 2)]
+
+
+def run(path):
+    out = {}
+    for i, (G, K, T, H, nd) in enumerate(CFGS):
+        gen, fwd = synthetic.make_models(nd=nd, E=128, H=H)
+        e0, goal, noise = (t.cuda() for t in synthetic.make_plan_inputs(G, K, T, nd, 128, seed=5))
+        pl = FusedPlanner(gen, fwd, horizon=T, precision="f16")
+        c, a, s = pl.rollout_score(e0, goal, noise, want_state=(K <= 4096))
+        torch.cuda.synchronize()
+        out[i] = (c.cpu(), a.cpu(), s.cpu() if s is not None else None)
+        if K == 65536:
+            ts = []
+            for _ in range(10):
+                a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a_.record(); pl.rollout_score(e0, goal, noise); b_.record(); torch.cuda.synchronize()
+                ts.append(a_.elapsed_time(b_))
+            print(f"[{os.environ.get('NDP_TC_ONE_TILE', 'two-tile')}] K=65536 T=8 rollout: min {min(ts):.4f} ms "
+                  f"({G * K * T / min(ts) / 1e6:.3f} Gsteps/s)", flush=True)
+    torch.save(out, path)
+
+
+if __name__ == "__main__":
+    if len(sys.argv) > 1:
+        run(sys.argv[1])
+        sys.exit(0)
+    with tempfile.TemporaryDirectory() as d:
+        a, b = os.path.join(d, "two.pt"), os.path.join(d, "one.pt")
+        run(a)
+        env = dict(os.environ, NDP_TC_ONE_TILE="1")
+        subprocess.check_call([sys.executable, os.path.abspath(__file__), b], env=env)
+        two, one = torch.load(a), torch.load(b)
+        ok = True
+        for i, cfg in enumerate(CFGS):
+            same = all((x is None and y is None) or torch.equal(x, y) for x, y in zip(two[i], one[i]))
+            rel = ((two[i][0] - one[i][0]).abs() / one[i][0].abs()).max().item()
+            print(f"cfg {cfg}: bit-equal {same} (cost max rel diff {rel:.2e}) finite {bool(torch.isfinite(two[i][0]).all())}", flush=True)
+            ok &= same
+        print("tc2_check", "ok" if ok else "MISMATCH")
+        sys.exit(0 if ok else 1)
