@@ -6,7 +6,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libndivplan.so")
+LIB_PATH = os.environ.get("NDP_LIB_PATH") or os.path.join(_HERE, "libndivplan.so")   # NDP_LIB_PATH: dev builds (profiling counters)
 
 PREC_FP32, PREC_F16X3, PREC_F16, PREC_F16X2, PREC_F16_REFINE = 0, 1, 2, 3, 4
 REFINE_R = 128

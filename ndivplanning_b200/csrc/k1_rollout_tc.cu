@@ -778,12 +778,32 @@ __device__ __forceinline__ void t2_group(const Iss2& st, uint32_t b16, uint32_t 
   }
 }
 
-__device__ __forceinline__ void t2_begin(Iss2& st, uint32_t bar_aready0, bool wait_a) {
+#ifdef NDP_TC_PROF
+__device__ unsigned long long g_t2_prof[8];   // issuer of tile 0: [0] wait_a [1] wait_full [2] total; epilogue warp 0: [4] wait_d [5] total
+#define T2_PROF_DECL long long t2p_a = 0, t2p_f = 0
+#define T2_PROF_ARGS , t2p_a, t2p_f
+#define T2_PROF_PARAMS , long long& t2p_a, long long& t2p_f
+#else
+#define T2_PROF_DECL
+#define T2_PROF_ARGS
+#define T2_PROF_PARAMS
+#endif
+__device__ __forceinline__ void t2_begin(Iss2& st, uint32_t bar_aready0, bool wait_a T2_PROF_PARAMS) {
+#ifdef NDP_TC_PROF
+  long long c0 = clock64();
+#endif
   if (wait_a) {
     mbar_wait(bar_aready0 + 8 * (st.aw & 1), (st.aw >> 1) & 1);
     ++st.aw;
   }
+#ifdef NDP_TC_PROF
+  long long c1 = clock64();
+  t2p_a += c1 - c0;
+#endif
   if (!st.next_ready) mbar_wait(st.bars + 8 * st.slot, st.par);
+#ifdef NDP_TC_PROF
+  t2p_f += clock64() - c1;
+#endif
   fence_after_sync();
 }
 __device__ __forceinline__ void t2_end(Iss2& st, bool signal_d, bool elected) {
@@ -875,31 +895,35 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     const uint32_t bar_a = bars + 8 * (10 + 2 * st.tile);
     const uint32_t AS = st.tb + kT2AS, P = st.tb + kT2P, Q = st.tb + kT2Q;
     const int nch = p.n_hid_chunks;                             // hidden chunks of 64
+    T2_PROF_DECL;
+#ifdef NDP_TC_PROF
+    const long long t2p_begin = clock64();
+#endif
     for (int t = 0; t < p.T; ++t) {
       bool el;
       // ---- generator fc1 (two items: state columns 0..63, then 64..127 + [noise | per-goal bias])
-      t2_begin(st, bar_a, true);
+      t2_begin(st, bar_a, true T2_PROF_ARGS);
       if ((el = elect_one())) t2_group<128, 4, 0, 16, 0>(st, t2_slot16(st), P, AS, 1);
       t2_end(st, false, el);
-      t2_begin(st, bar_a, false);
+      t2_begin(st, bar_a, false T2_PROF_ARGS);
       if ((el = elect_one())) t2_group<128, 4, 1, 16, 0>(st, t2_slot16(st), P, AS + 32, 0);
       t2_end(st, true, el);
       // ---- fc2 (N = 64)
-      t2_begin(st, bar_a, true);
+      t2_begin(st, bar_a, true T2_PROF_ARGS);
       if ((el = elect_one())) t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
       t2_end(st, true, el);
       // ---- fc3 (K = 64)
-      t2_begin(st, bar_a, true);
+      t2_begin(st, bar_a, true T2_PROF_ARGS);
       if ((el = elect_one())) t2_group<128, 4, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
       t2_end(st, true, el);
       // ---- fc4 quarter 0
-      t2_begin(st, bar_a, true);
+      t2_begin(st, bar_a, true T2_PROF_ARGS);
       if ((el = elect_one())) t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
       t2_end(st, true, el);
       // ---- [fc5 part i | fc4 quarter i+1], i = 0..2
 #pragma unroll 1
       for (int i = 0; i < 3; ++i) {
-        t2_begin(st, bar_a, true);
+        t2_begin(st, bar_a, true T2_PROF_ARGS);
         if ((el = elect_one())) {
           t2_group<16, 4, 0, 16, 0>(st, t2_slot16(st), P + 96, P + 64, i == 0);
           t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st) + (2048 >> 4), P, Q, 1);
@@ -907,29 +931,36 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         t2_end(st, true, el);
       }
       // ---- fc5 part 3 + bias
-      t2_begin(st, bar_a, true);
+      t2_begin(st, bar_a, true T2_PROF_ARGS);
       if ((el = elect_one())) t2_group<16, 4, 3, 16, 0>(st, t2_slot16(st), P + 96, P + 64, 0);
       t2_end(st, true, el);
       // ---- forward model: F1[0]; then F2[c], F1[c+1]
-      t2_begin(st, bar_a, true);
+      t2_begin(st, bar_a, true T2_PROF_ARGS);
       if ((el = elect_one())) t2_group<64, 8, 2, 16, 0>(st, t2_slot16(st), Q, AS, 1);
       t2_end(st, true, el);
 #pragma unroll 1
       for (int c = 0; c < nch; ++c) {
         const bool last = (c == nch - 1);
-        t2_begin(st, bar_a, true);
+        t2_begin(st, bar_a, true T2_PROF_ARGS);
         if ((el = elect_one())) {
           if (last) t2_group<128, 4, 3, 2, 32>(st, t2_slot16(st), P, Q, c == 0);
           else t2_group<128, 4, 0, 2, 32>(st, t2_slot16(st), P, Q, c == 0);
         }
         t2_end(st, last, el);
         if (!last) {
-          t2_begin(st, bar_a, false);
+          t2_begin(st, bar_a, false T2_PROF_ARGS);
           if ((el = elect_one())) t2_group<64, 8, 2, 16, 0>(st, t2_slot16(st), Q, AS, 1);
           t2_end(st, true, el);
         }
       }
     }
+#ifdef NDP_TC_PROF
+    if (warp == 16 && lane == 0) {
+      atomicAdd(&g_t2_prof[0], (unsigned long long)t2p_a);
+      atomicAdd(&g_t2_prof[1], (unsigned long long)t2p_f);
+      atomicAdd(&g_t2_prof[2], (unsigned long long)(clock64() - t2p_begin));
+    }
+#endif
   } else {
     // ===================== epilogue warps: tile = warp / 8 =====================
     const int tile = warp >> 3, q = warp & 3, h = (warp >> 2) & 1;
@@ -943,10 +974,20 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     const uint32_t AS = lane_base + kT2AS, P = lane_base + kT2P, Q = lane_base + kT2Q;
     const uint32_t bar_d = bars + 8 * (6 + 2 * tile), bar_a = bars + 8 * (10 + 2 * tile);
     uint32_t dw = 0, ae = 0;
+#ifdef NDP_TC_PROF
+    long long t2p_d = 0;
+    const long long t2p_e0 = clock64();
+#endif
     auto wait_d = [&]() {
+#ifdef NDP_TC_PROF
+      const long long c0 = clock64();
+#endif
       mbar_wait(bar_d + 8 * (dw & 1), (dw >> 1) & 1);
       ++dw;
       fence_after_sync();
+#ifdef NDP_TC_PROF
+      t2p_d += clock64() - c0;
+#endif
     };
     auto signal_a = [&](bool wrote_smem = false) {
       tmem_st_wait();
@@ -1071,6 +1112,12 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         if (h == 0 && valid) p.cost[(size_t)g * p.K + cand] = (cs + s_red[tile * 128 + m]) * (1.0f / 128.0f);
       }
     }
+#ifdef NDP_TC_PROF
+    if (warp == 0 && lane == 0) {
+      atomicAdd(&g_t2_prof[4], (unsigned long long)t2p_d);
+      atomicAdd(&g_t2_prof[5], (unsigned long long)(clock64() - t2p_e0));
+    }
+#endif
   }
   fence_before_sync();
   __syncthreads();
@@ -1177,9 +1224,11 @@ extern "C" int ndp_debug_tc_prof(unsigned long long* out8, int reset) {
   cudaMemcpyFromSymbol(out8, g_tc_prof, sizeof(unsigned long long) * 8);
   cudaMemcpyFromSymbol(out8 + 8, g_tc_item_wait, sizeof(unsigned long long) * 64);
   cudaMemcpyFromSymbol(out8 + 72, g_tc_a_wait, sizeof(unsigned long long) * 16);
+  cudaMemcpyFromSymbol(out8 + 88, g_t2_prof, sizeof(unsigned long long) * 8);
   if (reset) {
     unsigned long long z[64] = {0};
     cudaMemcpyToSymbol(g_tc_prof, z, 64); cudaMemcpyToSymbol(g_tc_item_wait, z, 512); cudaMemcpyToSymbol(g_tc_a_wait, z, 128);
+    cudaMemcpyToSymbol(g_t2_prof, z, 64);
   }
   return 0;
 }
