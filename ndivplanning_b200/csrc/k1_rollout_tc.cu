@@ -643,6 +643,8 @@ ExtCols bias_only(const float* b) {
 
 }  // namespace
 
+static int tc2_build(TcPlan* P, int E, int nd, int H, const float* const* Wt, const float* const* bt, cudaStream_t s);
+
 int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* const* Wt, const float* const* bt,
                    cudaStream_t s) {
   NDP_CHECK_ARG(E == 128 && nd <= 15 && H % 128 == 0 && H <= 2048,
@@ -713,6 +715,9 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
     tc_plan_destroy(P);
     return NDP_ERR_CUDA;
   }
+  static const bool one_tile = getenv("NDP_TC_ONE_TILE") != nullptr;     // diagnostics: keep the one-tile kernel
+  if (np == 1 && !one_tile && H % 64 == 0)
+    if (int rc2 = tc2_build(P, E, nd, H, Wt, bt, s)) { tc_plan_destroy(P); return rc2; }
   *out = P;
   return NDP_OK;
 }
