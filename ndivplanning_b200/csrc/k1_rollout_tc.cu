@@ -716,36 +716,41 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
     return NDP_ERR_CUDA;
   }
   static const bool one_tile = getenv("NDP_TC_ONE_TILE") != nullptr;     // diagnostics: keep the one-tile kernel
-  if (np == 1 && !one_tile && H % 64 == 0)
+  if (np == 1 && !one_tile && H % 128 == 0)
     if (int rc2 = tc2_build(P, E, nd, H, Wt, bt, s)) { tc_plan_destroy(P); return rc2; }
   *out = P;
   return NDP_OK;
 }
 
-
 // ==========================================================================================================
 // Two-tile bulk kernel (NP = 1, the single-pass estimate of "f16" / "f16+refine"): TWO 128-candidate tiles of one
 // goal per CTA, 256 TMEM columns each, one MMA-issuing warp per tile.
 //
-// Why: with one tile per SM the tensor pipe idles ~40 % of the time behind the strictly serial generator chain
-// (every layer's MMAs wait for the previous layer's TMEM -> ReLU -> fp16 -> TMEM epilogue, ~675 clk per round trip,
-// tools/tmem_probe.cu) and one issuing thread cannot feed N = 64 MMAs faster than one per ~45 clk.  Two independent
-// tiles hide each other's round trips, and two issuing threads reach the N/2-cycle floor also for N = 64 (probe:
-// 32.1 clk per N=64 MMA aggregate).  Both tiles consume the SAME weight ring slot (the slot is released when both
-// issuers have committed), so the L2 -> shared-memory weight traffic per candidate halves.
+// Why: with one tile per SM the tensor pipe idles ~40 % of the time behind the strictly serial layer chain (every
+// layer's MMAs wait for the previous layer's TMEM -> ReLU -> fp16 -> TMEM epilogue; the round trip costs ~1100 clk in
+// this kernel, tools/tc2_prof.py) and one issuing thread cannot feed small-N MMAs faster than one per ~45 clk
+// (tools/tmem_probe.cu: two issuing threads reach the N/2-cycle floor).  Two independent tiles hide each other's round
+// trips as long as one tile's MMA burst is about as long as the other's round trip, so every event is made as large
+// as TMEM allows: N = 128 everywhere but fc2 / fc5, and 128-wide hidden chunks in the forward model.  That needs the
+// state operand OUT of TMEM: the state lives in shared memory as an fp16 pair hi + lo (22 significand bits; the
+// per-step rounding of 2^-22 is far below the fp16 rounding of the activations), and `hi` IS the MMA A operand
+// (canonical K-major core-matrix layout, SS-mode MMAs for generator fc1 and forward fc1) — same 64 KB per tile as an
+// fp32 state, no TMEM columns.  Both tiles consume the SAME weight ring slot (released when both issuers have
+// committed), so the L2 -> shared-memory weight traffic per candidate halves.
 //
-// TMEM per tile (base 256 * tile):  AS [0,64) state operand (fp16, K = 128) | P [64,192) | Q [192,256)
-//   G1  D=P[128] <- AS            epilogue P -> Q (64 cols, compact)
-//   G2  D=P[0,64) <- Q            epilogue P[0,64) -> Q[0,32)
-//   G3  D=P[128] <- Q[0,32)       epilogue P -> Q
-//   G4  four N=64 quarters  D=P[0,64) <- Q, epilogue -> P[64,96);  fc5 accumulates per quarter: D5=P[96,112) <- P[64,96)
-//   F1[c] (hidden chunk of 64)  D=Q <- AS, epilogue in place;  F2[c]  DR=P[128] += Q (K = 64)
-// The fp32 state of each tile stays in shared memory (2 x 64 KB) and is advanced with an exact fp32 add per step.
-// Same arithmetic per element as rollout_tc_kernel<1> (same products, same accumulation order).
+// TMEM per tile (base 256 * tile):  P [0,128)  Q [128,256)
+//   G1  D=P <- state(smem)             epilogue P -> Q[0,64)
+//   G2  D=P[0,64) <- Q[0,64)           epilogue     -> Q[64,96)
+//   G3  D=P <- Q[64,96)                epilogue P -> Q[0,64)
+//   G4a D=P <- Q[0,64)                 epilogue P -> Q[64,128)      (fc4 outputs 0..127)
+//   G4b D=P <- Q[0,64)                 epilogue P -> Q[0,64)        (fc4 outputs 128..255)
+//   G5  D=P[0,16) <- Q[64,128) | Q[0,64)
+//   F1[c] (hidden chunk of 128)  D=Q <- state(smem), epilogue in place;  F2[c]  DR=P += Q
+// Products and accumulation order per element equal rollout_tc_kernel<1>; only the state carries 22 instead of 24 bits.
 // ==========================================================================================================
 static constexpr int kT2Threads = 608;                   // 16 epilogue warps, 2 MMA issuers (16, 17), TMA producer (18)
-static constexpr uint32_t kT2AS = 0, kT2P = 64, kT2Q = 192;
-static constexpr uint32_t kT2OffState = 0;               // 2 tiles x [32 col4][128 rows] float4
+static constexpr uint32_t kT2P = 0, kT2Q = 128;
+static constexpr uint32_t kT2OffState = 0;               // per tile: hi image 32 KB (A operand layout) | lo image 32 KB
 static constexpr uint32_t kT2OffExt = 131072;            // noise[2], action[2], ones: 5 x 4 KB
 static constexpr uint32_t kT2OffRing = kT2OffExt + 5 * kExtSlab;
 static constexpr uint32_t kT2Slot = 20480, kT2NSlot = 3;
@@ -760,12 +765,14 @@ struct Iss2 {
   uint32_t bars, ring16;
   uint32_t tile, tb;         // tile index, TMEM base of the tile
   uint32_t ext_noise, ext_act, ext_ones;   // (ext slab address >> 4) | LBO bits
+  uint32_t state16;          // (state hi image address >> 4) | LBO bits: A operand of the SS-mode MMAs
   uint32_t ds, aw;           // "D full" events signalled / "A ready" events consumed
   uint32_t next_ready;
 };
 
-// MMAs of one weight group: NMAIN main slabs (A from TMEM at a + (s/SPC)*CPH + (s%SPC)*8) + optional ext slab (A from smem)
-template <int N, int NMAIN, int EXT, int SPC, int CPH>
+// MMAs of one weight group: NMAIN main slabs + optional ext slab (A from smem).
+// AMODE 0: A from TMEM at a + (s/SPC)*CPH + (s%SPC)*8;  AMODE 1: A = state hi image in smem, slabs a .. a+NMAIN-1
+template <int N, int NMAIN, int EXT, int AMODE, int SPC, int CPH>
 __device__ __forceinline__ void t2_group(const Iss2& st, uint32_t b16, uint32_t d, uint32_t a, uint32_t first) {
   constexpr uint32_t kDescHi = 0x4000u | (128u >> 4);
   constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
@@ -774,7 +781,9 @@ __device__ __forceinline__ void t2_group(const Iss2& st, uint32_t b16, uint32_t 
   uint32_t acc = first ? 0u : 1u;
 #pragma unroll
   for (int s = 0; s < NMAIN; ++s) {
-    mma_ts(d, a + (s / SPC) * CPH + (s % SPC) * 8, pack64(blo + s * step, kDescHi), kIdesc, acc);
+    const uint64_t bd = pack64(blo + s * step, kDescHi);
+    if (AMODE == 0) mma_ts(d, a + (s / SPC) * CPH + (s % SPC) * 8, bd, kIdesc, acc);
+    else mma_ss(d, pack64(st.state16 + (a + s) * 256, kDescHi), bd, kIdesc, acc);     // 4 KB per K=16 slab
     acc = 1;
   }
   if (EXT) {
@@ -823,6 +832,22 @@ __device__ __forceinline__ void t2_end(Iss2& st, bool signal_d, bool elected) {
 }
 __device__ __forceinline__ uint32_t t2_slot16(const Iss2& st) { return st.ring16 + st.slot * (kT2Slot >> 4); }
 
+// 64 accumulator columns (src, src+32) -> relu -> 32 packed fp16 columns (dst, dst+16); both loads in flight at once
+__device__ __forceinline__ void t2_relu64(uint32_t src, uint32_t dst) {
+  uint32_t v[32], w[32];
+  tmem_ld32(src, v);
+  tmem_ld32(src + 32, w);
+  tmem_ld_wait();
+  uint32_t hi[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j)
+    hi[j] = pack_hi(fmaxf(__uint_as_float(v[2 * j]), 0.f), fmaxf(__uint_as_float(v[2 * j + 1]), 0.f));
+  tmem_st16(dst, hi);
+#pragma unroll
+  for (int j = 0; j < 16; ++j)
+    hi[j] = pack_hi(fmaxf(__uint_as_float(w[2 * j]), 0.f), fmaxf(__uint_as_float(w[2 * j + 1]), 0.f));
+  tmem_st16(dst + 16, hi);
+}
 // 32 accumulator columns -> relu -> 16 packed fp16 columns
 __device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
   uint32_t v[32];
@@ -893,68 +918,77 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     st.tb = tmem + 256 * st.tile;
     st.slot = 0; st.par = 0; st.next_ready = 0; st.bars = bars; st.ring16 = smem_u32(smem + kT2OffRing) >> 4;
     st.ds = 0; st.aw = 0;
-    const uint32_t ext_lbo = (2048u >> 4) << 16;               // A ext slabs: LBO = 2 KB, SBO = 128 B
+    const uint32_t ext_lbo = (2048u >> 4) << 16;               // smem A operands: LBO = 2 KB, SBO = 128 B
     st.ext_noise = (smem_u32(ext_base + st.tile * kExtSlab) >> 4) | ext_lbo;
     st.ext_act = (smem_u32(ext_base + (2 + st.tile) * kExtSlab) >> 4) | ext_lbo;
     st.ext_ones = (smem_u32(ext_ones) >> 4) | ext_lbo;
+    st.state16 = (smem_u32(smem + kT2OffState + st.tile * 65536) >> 4) | ext_lbo;
     const uint32_t bar_a = bars + 8 * (10 + 2 * st.tile);
-    const uint32_t AS = st.tb + kT2AS, P = st.tb + kT2P, Q = st.tb + kT2Q;
-    const int nch = p.n_hid_chunks;                             // hidden chunks of 64
+    const uint32_t P = st.tb + kT2P, Q = st.tb + kT2Q;
+    const int nch = p.n_hid_chunks;                             // hidden chunks of 128
     T2_PROF_DECL;
 #ifdef NDP_TC_PROF
     const long long t2p_begin = clock64();
 #endif
     for (int t = 0; t < p.T; ++t) {
       bool el;
-      // ---- generator fc1 (two items: state columns 0..63, then 64..127 + [noise | per-goal bias])
+      // ---- generator fc1: state slabs 0..3, then 4..7 + [noise | per-goal bias]
       t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 0, 16, 0>(st, t2_slot16(st), P, AS, 1);
+      if ((el = elect_one())) t2_group<128, 4, 0, 1, 1, 0>(st, t2_slot16(st), P, 0, 1);
       t2_end(st, false, el);
       t2_begin(st, bar_a, false T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 1, 16, 0>(st, t2_slot16(st), P, AS + 32, 0);
+      if ((el = elect_one())) t2_group<128, 4, 1, 1, 1, 0>(st, t2_slot16(st), P, 4, 0);
       t2_end(st, true, el);
-      // ---- fc2 (N = 64)
+      // ---- fc2 (N = 64): A1 = Q[0,64)
       t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
+      if ((el = elect_one())) t2_group<64, 8, 3, 0, 16, 0>(st, t2_slot16(st), P, Q, 1);
       t2_end(st, true, el);
-      // ---- fc3 (K = 64)
+      // ---- fc3 (K = 64): A2 = Q[64,96)
       t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
+      if ((el = elect_one())) t2_group<128, 4, 3, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 1);
       t2_end(st, true, el);
-      // ---- fc4 quarter 0
-      t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st), P, Q, 1);
-      t2_end(st, true, el);
-      // ---- [fc5 part i | fc4 quarter i+1], i = 0..2
+      // ---- fc4 halves (outputs 0..127, 128..255): A3 = Q[0,64), two items each
 #pragma unroll 1
-      for (int i = 0; i < 3; ++i) {
+      for (int hh = 0; hh < 2; ++hh) {
         t2_begin(st, bar_a, true T2_PROF_ARGS);
-        if ((el = elect_one())) {
-          t2_group<16, 4, 0, 16, 0>(st, t2_slot16(st), P + 96, P + 64, i == 0);
-          t2_group<64, 8, 3, 16, 0>(st, t2_slot16(st) + (2048 >> 4), P, Q, 1);
-        }
+        if ((el = elect_one())) t2_group<128, 4, 0, 0, 16, 0>(st, t2_slot16(st), P, Q, 1);
+        t2_end(st, false, el);
+        t2_begin(st, bar_a, false T2_PROF_ARGS);
+        if ((el = elect_one())) t2_group<128, 4, 3, 0, 16, 0>(st, t2_slot16(st), P, Q + 32, 0);
         t2_end(st, true, el);
       }
-      // ---- fc5 part 3 + bias
+      // ---- fc5 (N = 16, K = 256): A4a = Q[64,128) (k 0..127), A4b = Q[0,64) (k 128..255)
       t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<16, 4, 3, 16, 0>(st, t2_slot16(st), P + 96, P + 64, 0);
+      if ((el = elect_one())) {
+        t2_group<16, 8, 0, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 1);
+        t2_group<16, 8, 3, 0, 16, 0>(st, t2_slot16(st) + (4096 >> 4), P, Q, 0);
+      }
       t2_end(st, true, el);
-      // ---- forward model: F1[0]; then F2[c], F1[c+1]
+      // ---- forward model: F1[0]; then F2[c], F1[c+1]   (two ring items per GEMM)
       t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<64, 8, 2, 16, 0>(st, t2_slot16(st), Q, AS, 1);
+      if ((el = elect_one())) t2_group<128, 4, 0, 1, 1, 0>(st, t2_slot16(st), Q, 0, 1);
+      t2_end(st, false, el);
+      t2_begin(st, bar_a, false T2_PROF_ARGS);
+      if ((el = elect_one())) t2_group<128, 4, 2, 1, 1, 0>(st, t2_slot16(st), Q, 4, 0);
       t2_end(st, true, el);
 #pragma unroll 1
       for (int c = 0; c < nch; ++c) {
         const bool last = (c == nch - 1);
         t2_begin(st, bar_a, true T2_PROF_ARGS);
+        if ((el = elect_one())) t2_group<128, 4, 0, 0, 16, 0>(st, t2_slot16(st), P, Q, c == 0);          // Ah k 0..63: Q[0,32)
+        t2_end(st, false, el);
+        t2_begin(st, bar_a, false T2_PROF_ARGS);
         if ((el = elect_one())) {
-          if (last) t2_group<128, 4, 3, 2, 32>(st, t2_slot16(st), P, Q, c == 0);
-          else t2_group<128, 4, 0, 2, 32>(st, t2_slot16(st), P, Q, c == 0);
+          if (last) t2_group<128, 4, 3, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 0);                     // k 64..127: Q[64,96)
+          else t2_group<128, 4, 0, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 0);
         }
         t2_end(st, last, el);
         if (!last) {
           t2_begin(st, bar_a, false T2_PROF_ARGS);
-          if ((el = elect_one())) t2_group<64, 8, 2, 16, 0>(st, t2_slot16(st), Q, AS, 1);
+          if ((el = elect_one())) t2_group<128, 4, 0, 1, 1, 0>(st, t2_slot16(st), Q, 0, 1);
+          t2_end(st, false, el);
+          t2_begin(st, bar_a, false T2_PROF_ARGS);
+          if ((el = elect_one())) t2_group<128, 4, 2, 1, 1, 0>(st, t2_slot16(st), Q, 4, 0);
           t2_end(st, true, el);
         }
       }
@@ -972,11 +1006,13 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     const int m = q * 32 + lane;                                // candidate row = TMEM lane
     const int cand = (pair * 2 + tile) * 128 + m;
     const bool valid = cand < p.K;
-    float4* S4 = reinterpret_cast<float4*>(smem + kT2OffState) + tile * 4096;
+    // state images of this tile: element (row m, k) at (k/8)*2048 + (m/8)*128 + (m%8)*16 + (k%8)*2
+    uint8_t* SH = smem + kT2OffState + tile * 65536 + (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16;
+    uint8_t* SL = SH + 32768;
     uint8_t* ext_noise = ext_base + tile * kExtSlab;
     uint8_t* ext_act = ext_base + (2 + tile) * kExtSlab;
     const uint32_t lane_base = tmem + 256 * tile + ((uint32_t)(q * 32) << 16);
-    const uint32_t AS = lane_base + kT2AS, P = lane_base + kT2P, Q = lane_base + kT2Q;
+    const uint32_t P = lane_base + kT2P, Q = lane_base + kT2Q;
     const uint32_t bar_d = bars + 8 * (6 + 2 * tile), bar_a = bars + 8 * (10 + 2 * tile);
     uint32_t dw = 0, ae = 0;
 #ifdef NDP_TC_PROF
@@ -1025,33 +1061,38 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         *reinterpret_cast<uint4*>(ext_noise + c * 2048 + off) = hv;
       }
     };
-    // ---- init: state <- e0, AS <- fp16(e0), noise ext of step 0
+    // 8 consecutive state values (k = 8*kc .. 8*kc+7) -> hi / lo images
+    auto put_state8 = [&](int kc, const float (&s)[8]) {
+      uint4 hv, lv;
+      hv.x = pack_hi(s[0], s[1]); lv.x = pack_lo(s[0], s[1], hv.x);
+      hv.y = pack_hi(s[2], s[3]); lv.y = pack_lo(s[2], s[3], hv.y);
+      hv.z = pack_hi(s[4], s[5]); lv.z = pack_lo(s[4], s[5], hv.z);
+      hv.w = pack_hi(s[6], s[7]); lv.w = pack_lo(s[6], s[7], hv.w);
+      *reinterpret_cast<uint4*>(SH + kc * 2048) = hv;
+      *reinterpret_cast<uint4*>(SL + kc * 2048) = lv;
+    };
+    // ---- init: state <- e0 (this thread: k in [64h, 64h+64)), noise ext of step 0
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      uint32_t hi[16];
-#pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + u * 8 + c);
-        S4[(h * 16 + u * 8 + c) * 128 + m] = v;
-        hi[2 * c] = pack_hi(v.x, v.y); hi[2 * c + 1] = pack_hi(v.z, v.w);
-      }
-      tmem_st16(AS + 32 * h + 16 * u, hi);
+    for (int c = 0; c < 8; ++c) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + 2 * c);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + 2 * c + 1);
+      const float s8[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      put_state8(8 * h + c, s8);
     }
     if (h == 0) noise_row(0);
     signal_a(true);
     for (int t = 0; t < p.T; ++t) {
-      // ---- G1 (N=128 in P) -> Q ; G2 (N=64 in P[0,64)) -> Q[0,32) ; G3 (N=128 in P) -> Q
-      wait_d(); t2_relu32(P + 64 * h, Q + 32 * h); t2_relu32(P + 64 * h + 32, Q + 32 * h + 16); signal_a();
-      wait_d(); t2_relu32(P + 32 * h, Q + 16 * h); signal_a();
-      wait_d(); t2_relu32(P + 64 * h, Q + 32 * h); t2_relu32(P + 64 * h + 32, Q + 32 * h + 16); signal_a();
-      // ---- G4 quarters (N=64 in P[0,64)) -> P[64,96)
-#pragma unroll 1
-      for (int i = 0; i < 4; ++i) { wait_d(); t2_relu32(P + 32 * h, P + 64 + 16 * h); signal_a(); }
-      // ---- G5 (4 real columns in P[96,100)): action -> ext slab; step-0 actions are the plan's a0
+      // ---- G1 (P) -> Q[0,64) ; G2 (P[0,64)) -> Q[64,96) ; G3 (P) -> Q[0,64) ; G4a (P) -> Q[64,128) ; G4b (P) -> Q[0,64)
+      wait_d(); t2_relu64(P + 64 * h, Q + 32 * h); signal_a();
+      wait_d(); t2_relu32(P + 32 * h, Q + 64 + 16 * h); signal_a();
+      wait_d(); t2_relu64(P + 64 * h, Q + 32 * h); signal_a();
+      wait_d(); t2_relu64(P + 64 * h, Q + 64 + 32 * h); signal_a();
+      wait_d(); t2_relu64(P + 64 * h, Q + 32 * h); signal_a();
+      // ---- G5 (4 real columns in P[0,4)): action -> ext slab; step-0 actions are the plan's a0
       wait_d();
       if (h == 0) {
         uint32_t av[4];
-        tmem_ld4(P + 96, av);
+        tmem_ld4(P, av);
         tmem_ld_wait();
         const float a0 = __uint_as_float(av[0]), a1 = __uint_as_float(av[1]), a2 = __uint_as_float(av[2]), a3 = __uint_as_float(av[3]);
         uint4 hv;
@@ -1061,10 +1102,10 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
           *reinterpret_cast<float4*>(p.a0 + ((size_t)g * p.K + cand) * 4) = make_float4(a0, a1, a2, a3);
       }
       signal_a(true);
-      // ---- forward model hidden chunks of 64: F1[c] accumulator in Q -> relu -> A of F2[c], in place
+      // ---- forward model hidden chunks of 128: F1[c] accumulator in Q -> relu -> A of F2[c], in place
 #pragma unroll 1
-      for (int c = 0; c < p.n_hid_chunks; ++c) { wait_d(); t2_relu32(Q + 32 * h, Q + 32 * h); signal_a(); }
-      // ---- END: state += residual (fp32, exact add; forward_encoder.py:113-114), new A operand, next noise
+      for (int c = 0; c < p.n_hid_chunks; ++c) { wait_d(); t2_relu64(Q + 64 * h, Q + 64 * h); signal_a(); }
+      // ---- END: state += residual (forward_encoder.py:113-114), re-split into hi / lo, next noise
       wait_d();
       const bool more = t + 1 < p.T;
       float cs = 0.f;
@@ -1072,38 +1113,36 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       for (int u = 0; u < 2; ++u) {
         uint32_t r[32];
         tmem_ld32(P + 64 * h + 32 * u, r);
-        float4 sv[8];
+        uint4 hv[4], lv[4];
 #pragma unroll
-        for (int c = 0; c < 8; ++c) sv[c] = S4[(h * 16 + u * 8 + c) * 128 + m];
-        tmem_ld_wait();
-        uint32_t hi[16];
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          float4 v = sv[c];
-          v.x += __uint_as_float(r[4 * c]); v.y += __uint_as_float(r[4 * c + 1]);
-          v.z += __uint_as_float(r[4 * c + 2]); v.w += __uint_as_float(r[4 * c + 3]);
-          sv[c] = v;
-          hi[2 * c] = pack_hi(v.x, v.y); hi[2 * c + 1] = pack_hi(v.z, v.w);
+        for (int c = 0; c < 4; ++c) {
+          hv[c] = *reinterpret_cast<const uint4*>(SH + (8 * h + 4 * u + c) * 2048);
+          lv[c] = *reinterpret_cast<const uint4*>(SL + (8 * h + 4 * u + c) * 2048);
         }
-        if (more) {
-          tmem_st16(AS + 32 * h + 16 * u, hi);
+        tmem_ld_wait();
 #pragma unroll
-          for (int c = 0; c < 8; ++c) S4[(h * 16 + u * 8 + c) * 128 + m] = sv[c];
-        } else {
-          // terminal cost: mean over E of squared error (nn.MSELoss, mpc_eval.py:161); same summation order as
-          // rollout_tc_kernel: one running fma chain over this thread's 64 columns
+        for (int c = 0; c < 4; ++c) {
+          const uint32_t hw[4] = {hv[c].x, hv[c].y, hv[c].z, hv[c].w}, lw[4] = {lv[c].x, lv[c].y, lv[c].z, lv[c].w};
+          float s8[8];
 #pragma unroll
-          for (int c = 0; c < 8; ++c) {
-            const float* gl = s_goal + 64 * h + 32 * u + 4 * c;
-            float df = sv[c].x - gl[0]; cs = fmaf(df, df, cs);
-            df = sv[c].y - gl[1]; cs = fmaf(df, df, cs);
-            df = sv[c].z - gl[2]; cs = fmaf(df, df, cs);
-            df = sv[c].w - gl[3]; cs = fmaf(df, df, cs);
+          for (int e = 0; e < 4; ++e) {
+            const float2 fh = __half22float2(*reinterpret_cast<const __half2*>(&hw[e]));
+            const float2 fl = __half22float2(*reinterpret_cast<const __half2*>(&lw[e]));
+            s8[2 * e] = (fh.x + fl.x) + __uint_as_float(r[8 * c + 2 * e]);
+            s8[2 * e + 1] = (fh.y + fl.y) + __uint_as_float(r[8 * c + 2 * e + 1]);
           }
-          if (p.state_T && valid) {
-            float4* o = reinterpret_cast<float4*>(p.state_T + ((size_t)g * p.K + cand) * 128) + h * 16 + u * 8;
+          if (more) {
+            put_state8(8 * h + 4 * u + c, s8);
+          } else {
+            // terminal cost: mean over E of squared error (nn.MSELoss, mpc_eval.py:161)
+            const float* gl = s_goal + 64 * h + 32 * u + 8 * c;
 #pragma unroll
-            for (int c = 0; c < 8; ++c) o[c] = sv[c];
+            for (int e = 0; e < 8; ++e) { const float df = s8[e] - gl[e]; cs = fmaf(df, df, cs); }
+            if (p.state_T && valid) {
+              float4* o = reinterpret_cast<float4*>(p.state_T + ((size_t)g * p.K + cand) * 128 + 64 * h + 32 * u + 8 * c);
+              o[0] = make_float4(s8[0], s8[1], s8[2], s8[3]);
+              o[1] = make_float4(s8[4], s8[5], s8[6], s8[7]);
+            }
           }
         }
       }
@@ -1131,9 +1170,9 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
 
 // host side: weight stream of the two-tile kernel (fp16 hi only), items in the kernel's consumption order
 static int tc2_build(TcPlan* P, int E, int nd, int H, const float* const* Wt, const float* const* bt, cudaStream_t s) {
-  const int nch = H / 64;
+  const int nch = H / 128;
   P->n_chunks2 = nch;
-  const size_t cap = (size_t)(2 * 16384 + 18432 + 20480 + 18432 + 3 * 20480 + 4096) + (size_t)nch * (18432 + 20480) + 128 * kTcMaxItems;
+  const size_t cap = (size_t)12 * 20480 + (size_t)nch * 4 * 20480 + 128 * kTcMaxItems;
   cudaError_t e = cudaMalloc(&P->stream2, cap);
   if (e == cudaSuccess) e = cudaMalloc(&P->items2, sizeof(TcItem) * kTcMaxItems);
   if (e != cudaSuccess) { set_error("two-tile plan: cudaMalloc failed: %s", cudaGetErrorString(e)); return NDP_ERR_CUDA; }
@@ -1165,7 +1204,7 @@ static int tc2_build(TcPlan* P, int E, int nd, int H, const float* const* Wt, co
   int rc;
   size_t b;
   ExtCols x;
-  // G1a, G1b (+ per-goal ext block from the workspace)
+  // G1: state columns 0..63 | 64..127 + per-goal ext block (from the workspace)
   b = main_blk(Wt[0], C1, 0, 128, 0, 128, 4, off);
   if ((rc = close_item(b, 0))) return rc;
   b = main_blk(Wt[0], C1, 0, 128, 64, 128, 4, off);
@@ -1175,29 +1214,34 @@ static int tc2_build(TcPlan* P, int E, int nd, int H, const float* const* Wt, co
   if ((rc = close_item(b, 0))) return rc;
   b = main_blk(Wt[2], 64, 0, 128, 0, 128, 4, off); x = bias_only(bt[2]); b += ext_blk(128, 128, x, off + b);
   if ((rc = close_item(b, 0))) return rc;
-  // G4 quarter 0; [G5 part i | G4 quarter i+1]; G5 part 3 + bias
-  b = main_blk(Wt[3], 128, 0, 64, 0, 64, 8, off); x = bias_only(bt[3]); b += ext_blk(64, 64, x, off + b);
-  if ((rc = close_item(b, 0))) return rc;
-  for (int i = 0; i < 3; ++i) {
-    b = main_blk(Wt[4], 256, 0, 4, 64 * i, 16, 4, off);                    // fc5 padded to N=16, K slice of quarter i
-    b += main_blk(Wt[3], 128, 64 * (i + 1), 64, 0, 64, 8, off + b);
-    x = bias_only(bt[3] + 64 * (i + 1)); b += ext_blk(64, 64, x, off + b);
+  // G4 halves, two items each
+  for (int hh = 0; hh < 2; ++hh) {
+    b = main_blk(Wt[3], 128, 128 * hh, 128, 0, 128, 4, off);
+    if ((rc = close_item(b, 0))) return rc;
+    b = main_blk(Wt[3], 128, 128 * hh, 128, 64, 128, 4, off); x = bias_only(bt[3] + 128 * hh); b += ext_blk(128, 128, x, off + b);
     if ((rc = close_item(b, 0))) return rc;
   }
-  b = main_blk(Wt[4], 256, 0, 4, 192, 16, 4, off); x = bias_only(bt[4]); b += ext_blk(16, 4, x, off + b);
+  // G5 padded to N=16 (4 real rows): k 0..127 | k 128..255 + bias
+  b = main_blk(Wt[4], 256, 0, 4, 0, 16, 8, off);
+  b += main_blk(Wt[4], 256, 0, 4, 128, 16, 8, off + b);
+  x = bias_only(bt[4]); b += ext_blk(16, 4, x, off + b);
   if ((rc = close_item(b, 0))) return rc;
   // forward model: F1[c] = fc1 rows of hidden chunk c (ext = [action cols | bias]); F2[c] = fc2 columns of chunk c
   auto F1 = [&](int c) -> int {
+    size_t bb = main_blk(Wt[5], E + 4, c * 128, 128, 0, 128, 4, off);
+    if (int r = close_item(bb, 0)) return r;
     ExtCols a;
     memset(&a, 0, sizeof(a));
-    for (int k = 0; k < 4; ++k) { a.p[k] = Wt[5] + (size_t)c * 64 * (E + 4) + E + k; a.stride[k] = E + 4; }
-    a.p[4] = bt[5] + c * 64; a.stride[4] = 1;
-    size_t bb = main_blk(Wt[5], E + 4, c * 64, 64, 0, 64, 8, off);
-    bb += ext_blk(64, 64, a, off + bb);
+    for (int k = 0; k < 4; ++k) { a.p[k] = Wt[5] + (size_t)c * 128 * (E + 4) + E + k; a.stride[k] = E + 4; }
+    a.p[4] = bt[5] + c * 128; a.stride[4] = 1;
+    bb = main_blk(Wt[5], E + 4, c * 128, 128, 64, 128, 4, off);
+    bb += ext_blk(128, 128, a, off + bb);
     return close_item(bb, 0);
   };
   auto F2 = [&](int c) -> int {
-    size_t bb = main_blk(Wt[6], H, 0, 128, c * 64, 128, 4, off);
+    size_t bb = main_blk(Wt[6], H, 0, 128, c * 128, 128, 4, off);
+    if (int r = close_item(bb, 0)) return r;
+    bb = main_blk(Wt[6], H, 0, 128, c * 128 + 64, 128, 4, off);
     if (c == nch - 1) { ExtCols bc = bias_only(bt[6]); bb += ext_blk(128, 128, bc, off + bb); }
     return close_item(bb, 0);
   };

@@ -1,5 +1,6 @@
-"""Dev check of the two-tile bulk kernel (rollout_tc2_kernel): costs / actions / terminal states must equal the one-tile
-kernel rollout_tc_kernel<1> BIT FOR BIT (same products, same accumulation order), for full, ragged and multi-goal shapes.
+"""Dev check of the two-tile bulk kernel (rollout_tc2_kernel) against the one-tile kernel rollout_tc_kernel<1>: same
+products and accumulation order; the only difference is the state master copy (fp16 hi + lo = 22 bits instead of fp32), so
+costs / actions / terminal states must agree to ~1e-6 relative, for full, ragged and multi-goal shapes.
 The one-tile reference runs in a child process with NDP_TC_ONE_TILE=1 (the switch is read once per process)."""
 import os
 import subprocess
@@ -47,9 +48,12 @@ if __name__ == "__main__":
         two, one = torch.load(a), torch.load(b)
         ok = True
         for i, cfg in enumerate(CFGS):
-            same = all((x is None and y is None) or torch.equal(x, y) for x, y in zip(two[i], one[i]))
+            bit = all((x is None and y is None) or torch.equal(x, y) for x, y in zip(two[i], one[i]))
             rel = ((two[i][0] - one[i][0]).abs() / one[i][0].abs()).max().item()
-            print(f"cfg {cfg}: bit-equal {same} (cost max rel diff {rel:.2e}) finite {bool(torch.isfinite(two[i][0]).all())}", flush=True)
-            ok &= same
+            arel = ((two[i][1] - one[i][1]).abs().max() / one[i][1].abs().max()).item()
+            srel = 0.0 if two[i][2] is None else ((two[i][2] - one[i][2]).abs().max() / one[i][2].abs().max()).item()
+            fin = bool(torch.isfinite(two[i][0]).all())
+            print(f"cfg {cfg}: cost max rel diff {rel:.2e}, a0 {arel:.2e}, state {srel:.2e}, bit-equal {bit}, finite {fin}", flush=True)
+            ok &= fin and rel < 5e-6 and arel < 5e-6 and srel < 5e-6
         print("tc2_check", "ok" if ok else "MISMATCH")
         sys.exit(0 if ok else 1)
