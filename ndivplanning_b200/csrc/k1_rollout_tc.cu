@@ -724,19 +724,17 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
 
 // ==========================================================================================================
 // Two-tile bulk kernel (NP = 1, the single-pass estimate of "f16" / "f16+refine"): TWO 128-candidate tiles of one
-// goal per CTA, 256 TMEM columns each, one MMA-issuing warp per tile.
+// goal per CTA, 256 TMEM columns each, their MMA bursts alternating in the tensor queue.
 //
 // Why: with one tile per SM the tensor pipe idles ~40 % of the time behind the strictly serial layer chain (every
 // layer's MMAs wait for the previous layer's TMEM -> ReLU -> fp16 -> TMEM epilogue; the round trip costs ~1100 clk in
-// this kernel, tools/tc2_prof.py) and one issuing thread cannot feed small-N MMAs faster than one per ~45 clk
-// (tools/tmem_probe.cu: two issuing threads reach the N/2-cycle floor).  Two independent tiles hide each other's round
+// this kernel, tools/tc2_prof.py).  Two independent tiles hide each other's round
 // trips as long as one tile's MMA burst is about as long as the other's round trip, so every event is made as large
 // as TMEM allows: N = 128 everywhere but fc2 / fc5, and 128-wide hidden chunks in the forward model.  That needs the
 // state operand OUT of TMEM: the state lives in shared memory as an fp16 pair hi + lo (22 significand bits; the
 // per-step rounding of 2^-22 is far below the fp16 rounding of the activations), and `hi` IS the MMA A operand
 // (canonical K-major core-matrix layout, SS-mode MMAs for generator fc1 and forward fc1) — same 64 KB per tile as an
-// fp32 state, no TMEM columns.  Both tiles consume the SAME weight ring slot (released when both issuers have
-// committed), so the L2 -> shared-memory weight traffic per candidate halves.
+// fp32 state, no TMEM columns.  Both tiles consume the SAME weight ring slot (released after the second tile's MMAs), so the L2 -> shared-memory weight traffic per candidate halves.
 //
 // TMEM per tile (base 256 * tile):  P [0,128)  Q [128,256)
 //   G1  D=P <- state(smem)             epilogue P -> Q[0,64)
@@ -748,7 +746,7 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
 //   F1[c] (hidden chunk of 128)  D=Q <- state(smem), epilogue in place;  F2[c]  DR=P += Q
 // Products and accumulation order per element equal rollout_tc_kernel<1>; only the state carries 22 instead of 24 bits.
 // ==========================================================================================================
-static constexpr int kT2Threads = 608;                   // 16 epilogue warps, 2 MMA issuers (16, 17), TMA producer (18)
+static constexpr int kT2Threads = 576;                   // 16 epilogue warps, MMA issuer (16), TMA producer (17)
 static constexpr uint32_t kT2P = 0, kT2Q = 128;
 static constexpr uint32_t kT2OffState = 0;               // per tile: hi image 32 KB (A operand layout) | lo image 32 KB
 static constexpr uint32_t kT2OffExt = 131072;            // noise[2], action[2], ones: 5 x 4 KB
@@ -760,20 +758,15 @@ static constexpr uint32_t kT2OffRed = kT2OffGoal + 512;          // 2 x 128 floa
 static constexpr uint32_t kT2OffBars = kT2OffRed + 1024;
 static constexpr uint32_t kT2SmemBytes = kT2OffBars + 256;
 
-struct Iss2 {
-  uint32_t slot, par;        // ring position / parity of the "full" barriers
-  uint32_t bars, ring16;
-  uint32_t tile, tb;         // tile index, TMEM base of the tile
-  uint32_t ext_noise, ext_act, ext_ones;   // (ext slab address >> 4) | LBO bits
-  uint32_t state16;          // (state hi image address >> 4) | LBO bits: A operand of the SS-mode MMAs
-  uint32_t ds, aw;           // "D full" events signalled / "A ready" events consumed
-  uint32_t next_ready;
+struct T2Tile {              // smem operand descriptors of one tile: (address >> 4) | LBO bits
+  uint32_t ext_noise, ext_act, ext_ones;
+  uint32_t state16;          // state hi image: A operand of the SS-mode MMAs
 };
 
 // MMAs of one weight group: NMAIN main slabs + optional ext slab (A from smem).
 // AMODE 0: A from TMEM at a + (s/SPC)*CPH + (s%SPC)*8;  AMODE 1: A = state hi image in smem, slabs a .. a+NMAIN-1
 template <int N, int NMAIN, int EXT, int AMODE, int SPC, int CPH>
-__device__ __forceinline__ void t2_group(const Iss2& st, uint32_t b16, uint32_t d, uint32_t a, uint32_t first) {
+__device__ __forceinline__ void t2_group(const T2Tile& st, uint32_t b16, uint32_t d, uint32_t a, uint32_t first) {
   constexpr uint32_t kDescHi = 0x4000u | (128u >> 4);
   constexpr uint32_t kIdesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   constexpr uint32_t step = 2 * N;                              // one slab = N*32 bytes, in 16-byte units
@@ -793,44 +786,8 @@ __device__ __forceinline__ void t2_group(const Iss2& st, uint32_t b16, uint32_t 
 }
 
 #ifdef NDP_TC_PROF
-__device__ unsigned long long g_t2_prof[8];   // issuer of tile 0: [0] wait_a [1] wait_full [2] total; epilogue warp 0: [4] wait_d [5] total
-#define T2_PROF_DECL long long t2p_a = 0, t2p_f = 0
-#define T2_PROF_ARGS , t2p_a, t2p_f
-#define T2_PROF_PARAMS , long long& t2p_a, long long& t2p_f
-#else
-#define T2_PROF_DECL
-#define T2_PROF_ARGS
-#define T2_PROF_PARAMS
+__device__ unsigned long long g_t2_prof[8];   // issuer: [0] wait_a [1] wait_full [2] total; epilogue warp 0: [4] wait_d [5] total
 #endif
-__device__ __forceinline__ void t2_begin(Iss2& st, uint32_t bar_aready0, bool wait_a T2_PROF_PARAMS) {
-#ifdef NDP_TC_PROF
-  long long c0 = clock64();
-#endif
-  if (wait_a) {
-    mbar_wait(bar_aready0 + 8 * (st.aw & 1), (st.aw >> 1) & 1);
-    ++st.aw;
-  }
-#ifdef NDP_TC_PROF
-  long long c1 = clock64();
-  t2p_a += c1 - c0;
-#endif
-  if (!st.next_ready) mbar_wait(st.bars + 8 * st.slot, st.par);
-#ifdef NDP_TC_PROF
-  t2p_f += clock64() - c1;
-#endif
-  fence_after_sync();
-}
-__device__ __forceinline__ void t2_end(Iss2& st, bool signal_d, bool elected) {
-  if (elected) {
-    mma_commit(st.bars + 8 * (3 + st.slot));                    // slot is free when BOTH issuers have committed
-    if (signal_d) mma_commit(st.bars + 8 * (6 + 2 * st.tile + (st.ds & 1)));
-  }
-  __syncwarp();
-  if (signal_d) ++st.ds;
-  if (++st.slot == kT2NSlot) { st.slot = 0; st.par ^= 1; }
-  st.next_ready = mbar_try_wait(st.bars + 8 * st.slot, st.par) ? 1u : 0u;
-}
-__device__ __forceinline__ uint32_t t2_slot16(const Iss2& st) { return st.ring16 + st.slot * (kT2Slot >> 4); }
 
 // 64 accumulator columns (src, src+32) -> relu -> 32 packed fp16 columns (dst, dst+16); both loads in flight at once
 __device__ __forceinline__ void t2_relu64(uint32_t src, uint32_t dst) {
@@ -881,7 +838,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     reinterpret_cast<uint4*>(ext_base)[i] = make_uint4(0, 0, 0, 0);
   if (tid < 128) s_goal[tid] = __ldg(p.goal + (size_t)g * 128 + tid);
   if (tid == 0) {
-    for (uint32_t s = 0; s < kT2NSlot; ++s) { mbar_init(bars + 8 * s, 1); mbar_init(bars + 8 * (3 + s), 2); }
+    for (uint32_t s = 0; s < kT2NSlot; ++s) { mbar_init(bars + 8 * s, 1); mbar_init(bars + 8 * (3 + s), 1); }
     for (uint32_t e = 0; e < 4; ++e) { mbar_init(bars + 8 * (6 + e), 1); mbar_init(bars + 8 * (10 + e), 8); }
     fence_mbar_init();
   }
@@ -894,7 +851,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   fence_after_sync();
   const uint32_t tmem = *tmem_slot;
 
-  if (warp == 18) {
+  if (warp == 17) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t it = 0;
@@ -911,90 +868,144 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         }
       }
     }
-  } else if (warp >= 16) {
-    // ===================== MMA issuers: warp 16 -> tile 0, warp 17 -> tile 1 =====================
-    Iss2 st;
-    st.tile = (uint32_t)(warp - 16);
-    st.tb = tmem + 256 * st.tile;
-    st.slot = 0; st.par = 0; st.next_ready = 0; st.bars = bars; st.ring16 = smem_u32(smem + kT2OffRing) >> 4;
-    st.ds = 0; st.aw = 0;
+  } else if (warp == 16) {
+    // ===================== MMA issuer (one warp, both tiles) =====================
+    // Per GEMM (a "section" of 1-2 ring items): tile 0's MMAs, then tile 1's, back to back in the tensor queue, so
+    // tile 0's epilogue round trip runs under tile 1's MMAs and vice versa.  (Two concurrently issuing warps would
+    // interleave the tiles' MMAs in the queue: both bursts would complete together and both round trips would idle the
+    // pipe at the same time — measured, tools/tc2_prof.py.)  A ring slot is released after tile 1's MMAs on it.
+    T2Tile td[2];
     const uint32_t ext_lbo = (2048u >> 4) << 16;               // smem A operands: LBO = 2 KB, SBO = 128 B
-    st.ext_noise = (smem_u32(ext_base + st.tile * kExtSlab) >> 4) | ext_lbo;
-    st.ext_act = (smem_u32(ext_base + (2 + st.tile) * kExtSlab) >> 4) | ext_lbo;
-    st.ext_ones = (smem_u32(ext_ones) >> 4) | ext_lbo;
-    st.state16 = (smem_u32(smem + kT2OffState + st.tile * 65536) >> 4) | ext_lbo;
-    const uint32_t bar_a = bars + 8 * (10 + 2 * st.tile);
-    const uint32_t P = st.tb + kT2P, Q = st.tb + kT2Q;
+#pragma unroll
+    for (int tl = 0; tl < 2; ++tl) {
+      td[tl].ext_noise = (smem_u32(ext_base + tl * kExtSlab) >> 4) | ext_lbo;
+      td[tl].ext_act = (smem_u32(ext_base + (2 + tl) * kExtSlab) >> 4) | ext_lbo;
+      td[tl].ext_ones = (smem_u32(ext_ones) >> 4) | ext_lbo;
+      td[tl].state16 = (smem_u32(smem + kT2OffState + tl * 65536) >> 4) | ext_lbo;
+    }
+    const uint32_t ring16 = smem_u32(smem + kT2OffRing) >> 4;
+    uint32_t slot = 0, par = 0, ds[2] = {0, 0}, aw[2] = {0, 0};
     const int nch = p.n_hid_chunks;                             // hidden chunks of 128
-    T2_PROF_DECL;
 #ifdef NDP_TC_PROF
+    long long t2p_a = 0, t2p_f = 0;
     const long long t2p_begin = clock64();
 #endif
+    auto wait_a = [&](int tl) {
+#ifdef NDP_TC_PROF
+      const long long c0 = clock64();
+#endif
+      mbar_wait(bars + 8 * (10 + 2 * tl + (aw[tl] & 1)), (aw[tl] >> 1) & 1);
+      ++aw[tl];
+#ifdef NDP_TC_PROF
+      t2p_a += clock64() - c0;
+#endif
+    };
+    auto wait_full = [&](uint32_t j) {                          // ring item `j` items ahead of the section start
+#ifdef NDP_TC_PROF
+      const long long c0 = clock64();
+#endif
+      const uint32_t sj = slot + j;
+      mbar_wait(bars + 8 * (sj >= kT2NSlot ? sj - kT2NSlot : sj), sj >= kT2NSlot ? (par ^ 1) : par);
+#ifdef NDP_TC_PROF
+      t2p_f += clock64() - c0;
+#endif
+    };
+    auto slot16 = [&](uint32_t j) { const uint32_t sj = slot + j; return ring16 + (sj >= kT2NSlot ? sj - kT2NSlot : sj) * (kT2Slot >> 4); };
+    auto free_slot = [&](uint32_t j) { const uint32_t sj = slot + j; mma_commit(bars + 8 * (3 + (sj >= kT2NSlot ? sj - kT2NSlot : sj))); };
+    auto signal_d = [&](int tl) { mma_commit(bars + 8 * (6 + 2 * tl + (ds[tl] & 1))); };
+    auto advance = [&](uint32_t n) { slot += n; if (slot >= kT2NSlot) { slot -= kT2NSlot; par ^= 1; } };
+    // a GEMM of two ring items: slabs 0..3 (item 0), slabs 4..7 + ext (item 1)
+    // AM: 1 = A from the state image (slabs a, a+4), 0 = A from TMEM (columns a, a + a_hi)
+#define T2_GEMM2(N_, EXT_, AM_, DOFF, A0, A1, FIRST, WAIT, SIGNAL)                                           \
+    for (int tl = 0; tl < 2; ++tl) {                                                                        \
+      const uint32_t tb_ = tmem + 256 * tl;                                                                 \
+      if (WAIT) wait_a(tl);                                                                                 \
+      if (tl == 0) wait_full(0);                                                                            \
+      fence_after_sync();                                                                                   \
+      if (elect_one()) {                                                                                    \
+        t2_group<N_, 4, 0, AM_, 16, 0>(td[tl], slot16(0), tb_ + (DOFF), (AM_) ? (A0) : tb_ + (A0), FIRST);   \
+        if (tl == 1) free_slot(0);                                                                          \
+      }                                                                                                     \
+      __syncwarp();                                                                                         \
+      if (tl == 0) wait_full(1);                                                                            \
+      fence_after_sync();                                                                                   \
+      if (elect_one()) {                                                                                    \
+        t2_group<N_, 4, EXT_, AM_, 16, 0>(td[tl], slot16(1), tb_ + (DOFF), (AM_) ? (A1) : tb_ + (A1), 0);    \
+        if (tl == 1) free_slot(1);                                                                          \
+        if (SIGNAL) signal_d(tl);                                                                           \
+      }                                                                                                     \
+      __syncwarp();                                                                                         \
+      if (SIGNAL) ++ds[tl];                                                                                 \
+    }                                                                                                       \
+    advance(2);
     for (int t = 0; t < p.T; ++t) {
-      bool el;
-      // ---- generator fc1: state slabs 0..3, then 4..7 + [noise | per-goal bias]
-      t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 0, 1, 1, 0>(st, t2_slot16(st), P, 0, 1);
-      t2_end(st, false, el);
-      t2_begin(st, bar_a, false T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 1, 1, 1, 0>(st, t2_slot16(st), P, 4, 0);
-      t2_end(st, true, el);
-      // ---- fc2 (N = 64): A1 = Q[0,64)
-      t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<64, 8, 3, 0, 16, 0>(st, t2_slot16(st), P, Q, 1);
-      t2_end(st, true, el);
-      // ---- fc3 (K = 64): A2 = Q[64,96)
-      t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 3, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 1);
-      t2_end(st, true, el);
-      // ---- fc4 halves (outputs 0..127, 128..255): A3 = Q[0,64), two items each
-#pragma unroll 1
-      for (int hh = 0; hh < 2; ++hh) {
-        t2_begin(st, bar_a, true T2_PROF_ARGS);
-        if ((el = elect_one())) t2_group<128, 4, 0, 0, 16, 0>(st, t2_slot16(st), P, Q, 1);
-        t2_end(st, false, el);
-        t2_begin(st, bar_a, false T2_PROF_ARGS);
-        if ((el = elect_one())) t2_group<128, 4, 3, 0, 16, 0>(st, t2_slot16(st), P, Q + 32, 0);
-        t2_end(st, true, el);
+      // ---- generator fc1: state slabs 0..3, then 4..7 + [noise | per-goal bias]  -> P
+      T2_GEMM2(128, 1, 1, kT2P, 0, 4, 1, true, true)
+      // ---- fc2 (N = 64, one item): A1 = Q[0,64) -> P[0,64)
+      for (int tl = 0; tl < 2; ++tl) {
+        const uint32_t tb_ = tmem + 256 * tl;
+        wait_a(tl);
+        if (tl == 0) wait_full(0);
+        fence_after_sync();
+        if (elect_one()) {
+          t2_group<64, 8, 3, 0, 16, 0>(td[tl], slot16(0), tb_ + kT2P, tb_ + kT2Q, 1);
+          if (tl == 1) free_slot(0);
+          signal_d(tl);
+        }
+        __syncwarp();
+        ++ds[tl];
       }
-      // ---- fc5 (N = 16, K = 256): A4a = Q[64,128) (k 0..127), A4b = Q[0,64) (k 128..255)
-      t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) {
-        t2_group<16, 8, 0, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 1);
-        t2_group<16, 8, 3, 0, 16, 0>(st, t2_slot16(st) + (4096 >> 4), P, Q, 0);
+      advance(1);
+      // ---- fc3 (K = 64, one item): A2 = Q[64,96) -> P
+      for (int tl = 0; tl < 2; ++tl) {
+        const uint32_t tb_ = tmem + 256 * tl;
+        wait_a(tl);
+        if (tl == 0) wait_full(0);
+        fence_after_sync();
+        if (elect_one()) {
+          t2_group<128, 4, 3, 0, 16, 0>(td[tl], slot16(0), tb_ + kT2P, tb_ + kT2Q + 64, 1);
+          if (tl == 1) free_slot(0);
+          signal_d(tl);
+        }
+        __syncwarp();
+        ++ds[tl];
       }
-      t2_end(st, true, el);
-      // ---- forward model: F1[0]; then F2[c], F1[c+1]   (two ring items per GEMM)
-      t2_begin(st, bar_a, true T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 0, 1, 1, 0>(st, t2_slot16(st), Q, 0, 1);
-      t2_end(st, false, el);
-      t2_begin(st, bar_a, false T2_PROF_ARGS);
-      if ((el = elect_one())) t2_group<128, 4, 2, 1, 1, 0>(st, t2_slot16(st), Q, 4, 0);
-      t2_end(st, true, el);
+      advance(1);
+      // ---- fc4 halves (outputs 0..127, 128..255): A3 = Q[0,64) -> P
+      T2_GEMM2(128, 3, 0, kT2P, kT2Q, kT2Q + 32, 1, true, true)
+      T2_GEMM2(128, 3, 0, kT2P, kT2Q, kT2Q + 32, 1, true, true)
+      // ---- fc5 (N = 16, K = 256, one item): A4a = Q[64,128) (k 0..127), A4b = Q[0,64) (k 128..255) -> P[0,16)
+      for (int tl = 0; tl < 2; ++tl) {
+        const uint32_t tb_ = tmem + 256 * tl;
+        wait_a(tl);
+        if (tl == 0) wait_full(0);
+        fence_after_sync();
+        if (elect_one()) {
+          t2_group<16, 8, 0, 0, 16, 0>(td[tl], slot16(0), tb_ + kT2P, tb_ + kT2Q + 64, 1);
+          t2_group<16, 8, 3, 0, 16, 0>(td[tl], slot16(0) + (4096 >> 4), tb_ + kT2P, tb_ + kT2Q, 0);
+          if (tl == 1) free_slot(0);
+          signal_d(tl);
+        }
+        __syncwarp();
+        ++ds[tl];
+      }
+      advance(1);
+      // ---- forward model: F1[0] -> Q; then per hidden chunk F2[c] (DR = P += Q), F1[c+1] -> Q
+      T2_GEMM2(128, 2, 1, kT2Q, 0, 4, 1, true, true)
 #pragma unroll 1
       for (int c = 0; c < nch; ++c) {
-        const bool last = (c == nch - 1);
-        t2_begin(st, bar_a, true T2_PROF_ARGS);
-        if ((el = elect_one())) t2_group<128, 4, 0, 0, 16, 0>(st, t2_slot16(st), P, Q, c == 0);          // Ah k 0..63: Q[0,32)
-        t2_end(st, false, el);
-        t2_begin(st, bar_a, false T2_PROF_ARGS);
-        if ((el = elect_one())) {
-          if (last) t2_group<128, 4, 3, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 0);                     // k 64..127: Q[64,96)
-          else t2_group<128, 4, 0, 0, 16, 0>(st, t2_slot16(st), P, Q + 64, 0);
-        }
-        t2_end(st, last, el);
-        if (!last) {
-          t2_begin(st, bar_a, false T2_PROF_ARGS);
-          if ((el = elect_one())) t2_group<128, 4, 0, 1, 1, 0>(st, t2_slot16(st), Q, 0, 1);
-          t2_end(st, false, el);
-          t2_begin(st, bar_a, false T2_PROF_ARGS);
-          if ((el = elect_one())) t2_group<128, 4, 2, 1, 1, 0>(st, t2_slot16(st), Q, 4, 0);
-          t2_end(st, true, el);
+        const uint32_t first = (c == 0) ? 1u : 0u;
+        if (c == nch - 1) {
+          T2_GEMM2(128, 3, 0, kT2P, kT2Q, kT2Q + 64, first, true, true)
+        } else {
+          T2_GEMM2(128, 0, 0, kT2P, kT2Q, kT2Q + 64, first, true, false)
+          T2_GEMM2(128, 2, 1, kT2Q, 0, 4, 1, false, true)
         }
       }
     }
+#undef T2_GEMM2
 #ifdef NDP_TC_PROF
-    if (warp == 16 && lane == 0) {
+    if (lane == 0) {
       atomicAdd(&g_t2_prof[0], (unsigned long long)t2p_a);
       atomicAdd(&g_t2_prof[1], (unsigned long long)t2p_f);
       atomicAdd(&g_t2_prof[2], (unsigned long long)(clock64() - t2p_begin));
