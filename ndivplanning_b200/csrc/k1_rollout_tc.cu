@@ -749,14 +749,17 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
 static constexpr int kT2Threads = 576;                   // 16 epilogue warps, MMA issuer (16), TMA producer (17)
 static constexpr uint32_t kT2P = 0, kT2Q = 128;
 static constexpr uint32_t kT2OffState = 0;               // per tile: hi image 32 KB (A operand layout) | lo image 32 KB
-static constexpr uint32_t kT2OffExt = 131072;            // noise[2], action[2], ones: 5 x 4 KB
-static constexpr uint32_t kT2OffRing = kT2OffExt + 5 * kExtSlab;
-static constexpr uint32_t kT2Slot = 20480, kT2NSlot = 3;
+static constexpr uint32_t kT2OffExt = 131072;            // noise[2] 2 x 4 KB | action[2] 2 x 2 KB | ones 2 KB | zeros 2 KB
+static constexpr uint32_t kT2ExtBytes = 16384;           // (action / ones use k < 8 only: their second k-chunk is the shared zero block)
+static constexpr uint32_t kT2OffRing = kT2OffExt + kT2ExtBytes;
+static constexpr uint32_t kT2Slot = 20480, kT2NSlot = 4;  // 4 slots: one GEMM (2 items) in use + one GEMM in flight
 static constexpr uint32_t kT2OffItems = kT2OffRing + kT2NSlot * kT2Slot;
-static constexpr uint32_t kT2OffGoal = kT2OffItems + kItemsBytes;
+static constexpr uint32_t kT2ItemsBytes = kTcMaxItems * 12;      // {src_off, bytes, ext_bytes} per item
+static constexpr uint32_t kT2OffGoal = kT2OffItems + kT2ItemsBytes;
 static constexpr uint32_t kT2OffRed = kT2OffGoal + 512;          // 2 x 128 floats
 static constexpr uint32_t kT2OffBars = kT2OffRed + 1024;
 static constexpr uint32_t kT2SmemBytes = kT2OffBars + 256;
+static_assert(kT2SmemBytes <= 232448, "two-tile kernel: shared memory map exceeds 227 KB");
 
 struct T2Tile {              // smem operand descriptors of one tile: (address >> 4) | LBO bits
   uint32_t ext_noise, ext_act, ext_ones;
@@ -823,23 +826,25 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   const int g = blockIdx.x / p.tiles_per_goal;                  // tiles_per_goal counts tile PAIRS here
   const int pair = blockIdx.x % p.tiles_per_goal;
 
-  uint8_t* ext_base = smem + kT2OffExt;                         // noise0, noise1, act0, act1, ones
-  uint8_t* ext_ones = ext_base + 4 * kExtSlab;
-  TcItem* items = reinterpret_cast<TcItem*>(smem + kT2OffItems);
+  uint8_t* ext_base = smem + kT2OffExt;                         // noise0, noise1 (4 KB each), act0, act1, ones, zeros (2 KB each)
+  uint8_t* ext_actb = ext_base + 2 * kExtSlab;
+  uint8_t* ext_ones = ext_actb + 4096;
+  uint8_t* ext_zero = ext_ones + 2048;
+  uint32_t* items = reinterpret_cast<uint32_t*>(smem + kT2OffItems);   // [n_items][3]: src_off, bytes, ext_bytes
   float* s_goal = reinterpret_cast<float*>(smem + kT2OffGoal);
   float* s_red = reinterpret_cast<float*>(smem + kT2OffRed);
   const uint32_t bars = smem_u32(smem + kT2OffBars);
-  // barrier map (8 bytes each): full[0..2] empty[3..5] d_full[tile][2] @6..9  a_ready[tile][2] @10..13; tmem base at +128
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kT2OffBars + 128);
 
-  for (int i = tid; i < p.n_items * 8; i += kT2Threads)
-    reinterpret_cast<uint32_t*>(items)[i] = reinterpret_cast<const uint32_t*>(p.items)[i];
-  for (int i = tid; i < 5 * (int)kExtSlab / 16; i += kT2Threads)
+  for (int i = tid; i < p.n_items * 3; i += kT2Threads)
+    items[i] = reinterpret_cast<const uint32_t*>(p.items)[(i / 3) * 8 + i % 3];      // TcItem: src_off, bytes, ext_bytes first
+  for (int i = tid; i < (int)kT2ExtBytes / 16; i += kT2Threads)
     reinterpret_cast<uint4*>(ext_base)[i] = make_uint4(0, 0, 0, 0);
   if (tid < 128) s_goal[tid] = __ldg(p.goal + (size_t)g * 128 + tid);
   if (tid == 0) {
-    for (uint32_t s = 0; s < kT2NSlot; ++s) { mbar_init(bars + 8 * s, 1); mbar_init(bars + 8 * (3 + s), 1); }
-    for (uint32_t e = 0; e < 4; ++e) { mbar_init(bars + 8 * (6 + e), 1); mbar_init(bars + 8 * (10 + e), 8); }
+    // barrier map (8 bytes each): full[0..3] empty[4..7] d_full[tile][2] @8..11  a_ready[tile][2] @12..15
+    for (uint32_t s = 0; s < kT2NSlot; ++s) { mbar_init(bars + 8 * s, 1); mbar_init(bars + 8 * (4 + s), 1); }
+    for (uint32_t e = 0; e < 4; ++e) { mbar_init(bars + 8 * (8 + e), 1); mbar_init(bars + 8 * (12 + e), 8); }
     fence_mbar_init();
   }
   if (warp == 16) tmem_alloc512(smem_u32((const void*)tmem_slot));
@@ -859,11 +864,11 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       for (int t = 0; t < p.T; ++t) {
         for (int i = 0; i < p.n_items; ++i, ++it) {
           const uint32_t slot = it % kT2NSlot, par = (it / kT2NSlot) & 1;
-          const uint32_t bytes = items[i].bytes, eb = items[i].ext_bytes;
-          mbar_wait(bars + 8 * (3 + slot), par ^ 1);
+          const uint32_t bytes = items[3 * i + 1], eb = items[3 * i + 2];
+          mbar_wait(bars + 8 * (4 + slot), par ^ 1);
           mbar_expect_tx(bars + 8 * slot, bytes + eb);
           const uint32_t dst = smem_u32(smem + kT2OffRing + slot * kT2Slot);
-          bulk_g2s(dst, p.stream + items[i].src_off, bytes, bars + 8 * slot);
+          bulk_g2s(dst, p.stream + items[3 * i], bytes, bars + 8 * slot);
           if (eb) bulk_g2s(dst + bytes, gsrc, eb, bars + 8 * slot);
         }
       }
@@ -879,8 +884,9 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
 #pragma unroll
     for (int tl = 0; tl < 2; ++tl) {
       td[tl].ext_noise = (smem_u32(ext_base + tl * kExtSlab) >> 4) | ext_lbo;
-      td[tl].ext_act = (smem_u32(ext_base + (2 + tl) * kExtSlab) >> 4) | ext_lbo;
-      td[tl].ext_ones = (smem_u32(ext_ones) >> 4) | ext_lbo;
+      // action / ones slabs hold k-chunk 0 only; LBO points their k-chunk 1 at the shared zero block
+      td[tl].ext_act = (smem_u32(ext_actb + tl * 2048) >> 4) | (((smem_u32(ext_zero) - smem_u32(ext_actb + tl * 2048)) >> 4) << 16);
+      td[tl].ext_ones = (smem_u32(ext_ones) >> 4) | (((smem_u32(ext_zero) - smem_u32(ext_ones)) >> 4) << 16);
       td[tl].state16 = (smem_u32(smem + kT2OffState + tl * 65536) >> 4) | ext_lbo;
     }
     const uint32_t ring16 = smem_u32(smem + kT2OffRing) >> 4;
@@ -894,7 +900,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
 #ifdef NDP_TC_PROF
       const long long c0 = clock64();
 #endif
-      mbar_wait(bars + 8 * (10 + 2 * tl + (aw[tl] & 1)), (aw[tl] >> 1) & 1);
+      mbar_wait(bars + 8 * (12 + 2 * tl + (aw[tl] & 1)), (aw[tl] >> 1) & 1);
       ++aw[tl];
 #ifdef NDP_TC_PROF
       t2p_a += clock64() - c0;
@@ -911,8 +917,8 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
 #endif
     };
     auto slot16 = [&](uint32_t j) { const uint32_t sj = slot + j; return ring16 + (sj >= kT2NSlot ? sj - kT2NSlot : sj) * (kT2Slot >> 4); };
-    auto free_slot = [&](uint32_t j) { const uint32_t sj = slot + j; mma_commit(bars + 8 * (3 + (sj >= kT2NSlot ? sj - kT2NSlot : sj))); };
-    auto signal_d = [&](int tl) { mma_commit(bars + 8 * (6 + 2 * tl + (ds[tl] & 1))); };
+    auto free_slot = [&](uint32_t j) { const uint32_t sj = slot + j; mma_commit(bars + 8 * (4 + (sj >= kT2NSlot ? sj - kT2NSlot : sj))); };
+    auto signal_d = [&](int tl) { mma_commit(bars + 8 * (8 + 2 * tl + (ds[tl] & 1))); };
     auto advance = [&](uint32_t n) { slot += n; if (slot >= kT2NSlot) { slot -= kT2NSlot; par ^= 1; } };
     // a GEMM of two ring items: slabs 0..3 (item 0), slabs 4..7 + ext (item 1)
     // AM: 1 = A from the state image (slabs a, a+4), 0 = A from TMEM (columns a, a + a_hi)
@@ -1021,10 +1027,10 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     uint8_t* SH = smem + kT2OffState + tile * 65536 + (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16;
     uint8_t* SL = SH + 32768;
     uint8_t* ext_noise = ext_base + tile * kExtSlab;
-    uint8_t* ext_act = ext_base + (2 + tile) * kExtSlab;
+    uint8_t* ext_act = ext_actb + tile * 2048;
     const uint32_t lane_base = tmem + 256 * tile + ((uint32_t)(q * 32) << 16);
     const uint32_t P = lane_base + kT2P, Q = lane_base + kT2Q;
-    const uint32_t bar_d = bars + 8 * (6 + 2 * tile), bar_a = bars + 8 * (10 + 2 * tile);
+    const uint32_t bar_d = bars + 8 * (8 + 2 * tile), bar_a = bars + 8 * (12 + 2 * tile);
     uint32_t dw = 0, ae = 0;
 #ifdef NDP_TC_PROF
     long long t2p_d = 0;
