@@ -998,14 +998,35 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       advance(1);
       // ---- forward model: F1[0] -> Q; then per hidden chunk F2[c] (DR = P += Q), F1[c+1] -> Q
       T2_GEMM2(128, 2, 1, kT2Q, 0, 4, 1, true, true)
+      // per hidden chunk a BURST of four ring items per tile: F2[c] (DR = P += Q) then F1[c+1] (-> Q); tile 0's whole
+      // burst, then tile 1's: a tile's epilogue round trip then runs under the other tile's 1088 tensor cycles.
+      // (All four ring slots hold the burst; slot j is released by tile 1 one burst before tile 0 needs item j + 4.)
 #pragma unroll 1
       for (int c = 0; c < nch; ++c) {
         const uint32_t first = (c == 0) ? 1u : 0u;
         if (c == nch - 1) {
           T2_GEMM2(128, 3, 0, kT2P, kT2Q, kT2Q + 64, first, true, true)
         } else {
-          T2_GEMM2(128, 0, 0, kT2P, kT2Q, kT2Q + 64, first, true, false)
-          T2_GEMM2(128, 2, 1, kT2Q, 0, 4, 1, false, true)
+          for (int tl = 0; tl < 2; ++tl) {
+            const uint32_t tb_ = tmem + 256 * tl;
+            wait_a(tl);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (tl == 0) wait_full(j);
+              fence_after_sync();
+              if (elect_one()) {
+                if (j == 0) t2_group<128, 4, 0, 0, 16, 0>(td[tl], slot16(0), tb_ + kT2P, tb_ + kT2Q, first);
+                if (j == 1) t2_group<128, 4, 0, 0, 16, 0>(td[tl], slot16(1), tb_ + kT2P, tb_ + kT2Q + 64, 0);
+                if (j == 2) t2_group<128, 4, 0, 1, 16, 0>(td[tl], slot16(2), tb_ + kT2Q, 0, 1);
+                if (j == 3) t2_group<128, 4, 2, 1, 16, 0>(td[tl], slot16(3), tb_ + kT2Q, 4, 0);
+                if (tl == 1) free_slot(j);
+                if (j == 3) signal_d(tl);
+              }
+              __syncwarp();
+            }
+            ++ds[tl];
+          }
+          advance(4);
         }
       }
     }
