@@ -203,10 +203,10 @@ def run_reference(args):
 # --------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------
-K1_KERNEL = {"fp32": "rollout_f32_kernel", "f16": "rollout_tc_kernel<1>", "f16x2": "rollout_tc_kernel<2>",
-             "f16x3": "rollout_tc_kernel<3>", "f16+refine": "rollout_tc_kernel<1>"}
+K1_KERNEL = {"fp32": "rollout_f32_kernel", "f16": "rollout_tc2_kernel", "f16x2": "rollout_tc_kernel<2>",
+             "f16x3": "rollout_tc_kernel<3>", "f16+refine": "rollout_tc2_kernel"}
 MMA_PASSES = {"fp32": 0, "f16": 1, "f16x2": 2, "f16x3": 3, "f16+refine": 1}
-NCU_TRAFFIC = {"rollout_tc_kernel<1>": 4.98e6, "rollout_f32_kernel": 5.69e6}   # bytes per launch, ncu (profiles/)
+NCU_TRAFFIC = {"rollout_tc2_kernel": None, "rollout_tc_kernel<1>": 4.98e6, "rollout_f32_kernel": 5.69e6}   # bytes per launch, ncu (profiles/)
 POOL = 40   # distinct noise sets rotated through the timed region: 40 x 4.2 MB = 168 MB > 126 MB of L2
 
 
@@ -454,14 +454,17 @@ def run_gpu(args):
     a, b = run_e2e(args.steps, 7)
     barrier()
     ms_e2e = a.elapsed_time(b) / args.steps
-    # ---- sustained: the same resident loop for >= 2 s
+    clocks = sampler.finish()                          # clocks of the headline + e2e timed regions
+    # ---- sustained: the same resident loop for >= 2 s (its own clock samples: a 2 s tensor-bound loop is power-capped)
     n_sus = max(args.steps, int(2000.0 / max(ms, 0.05)) + 1)
+    sampler2 = ClockSampler(local)
+    sampler2.start()
     barrier()
     a, b, plans = run_resident(n_sus, 0)
     barrier()
     ms_sus = a.elapsed_time(b) / n_sus
     del plans
-    clocks = sampler.finish()
+    clocks_sus = sampler2.finish()
     gc.enable()
 
     # ---- cfg4: K_total = 1,048,576 fixed, T=16, candidates sharded (strong scaling)
@@ -694,7 +697,8 @@ def run_gpu(args):
                                  "rollout kernel; fp16 and bf16 share the tcgen05 kind::f16 rate"},
             "sustained": {"seconds": ms_sus * n_sus / 1e3, "plans": n_sus, "ms_per_step": ms_sus,
                           "candidate_steps_per_s": units / (ms_sus * 1e-3), "tflops_per_gpu": sus_tflops,
-                          "peak": pk["bf16_sus"], "frac_of_sustained_peak": sus_tflops / pk["bf16_sus"]},
+                          "peak": pk["bf16_sus"], "frac_of_sustained_peak": sus_tflops / pk["bf16_sus"],
+                          "clocks": clocks_sus},
             "verify": verify,
             "cfg4": cfg4, "cfg5": cfg5, "k3": k3,
             "ndiv": {"metric": "ndiv_pairs_per_sec_fwd_bwd", "value": pairs / (ndiv_ms * 1e-3), "unit": "ordered pairs/s",
