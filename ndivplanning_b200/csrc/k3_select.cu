@@ -494,6 +494,63 @@ select2_kernel(const float* __restrict__ cost, const unsigned long long* __restr
   }
 }
 
+// argmin only, many goals of K <= 4096 (BASELINE cfg5: 4096 x 4096 costs = 67 MB): the HBM-bound stage in its purest
+// form.  Persistent blocks stride over the goals; the NEXT goal's 16 floats per thread are in flight while the current
+// goal is reduced (two register sets), so every SM keeps ~100 KB of loads outstanding instead of paying a block launch
+// and a load latency per 16 KB row.
+__global__ void __launch_bounds__(kSelThreads, 6)
+argmin_rows_kernel(const float* __restrict__ cost, int G, int K, long long idx_base, unsigned long long* __restrict__ out_min,
+                   const int* __restrict__ skip) {
+  __shared__ unsigned long long s_w[2][kSelThreads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const bool vec = ((K & 3) == 0) && ((reinterpret_cast<uintptr_t>(cost) & 15) == 0);
+  auto load_row = [&](int g, float (&c)[kS2Ept]) {
+    const float* src = cost + (size_t)g * (size_t)K;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int i0 = q * 1024 + tid * 4;
+      if (vec && i0 + 3 < K) {
+        const float4 v = __ldcs(reinterpret_cast<const float4*>(src + i0));      // streamed once: evict first
+        c[4 * q] = v.x; c[4 * q + 1] = v.y; c[4 * q + 2] = v.z; c[4 * q + 3] = v.w;
+      } else {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) c[4 * q + r] = (i0 + r < K) ? __ldcs(src + i0 + r) : __int_as_float(0x7fc00000);
+      }
+    }
+  };
+  float cur[kS2Ept], nxt[kS2Ept];
+  int g = blockIdx.x;
+  if (g < G) load_row(g, cur);
+  int it = 0;
+  for (; g < G; g += gridDim.x, ++it) {
+    const int gn = g + gridDim.x;
+    if (gn < G) load_row(gn, nxt);
+    unsigned long long m = kPadKey;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int i = q * 1024 + tid * 4 + r;
+        const unsigned long long kv = i < K ? (((unsigned long long)ordered_key(cur[4 * q + r] + 0.0f) << 32) | (unsigned)i) : kPadKey;
+        m = kv < m ? kv : m;
+      }
+    m = warp_min_u64(m);
+    if (lane == 0) s_w[it & 1][warp] = m;
+    __syncthreads();                                     // double-buffered partials: one barrier per goal
+    if (tid == 0 && !(skip && skip[g])) {
+      m = s_w[it & 1][0];
+#pragma unroll
+      for (int w = 1; w < kSelThreads / 32; ++w) m = s_w[it & 1][w] < m ? s_w[it & 1][w] : m;
+      const float c = key_to_float((uint32_t)(m >> 32));
+      if (m == kPadKey || !(c < 1e10f)) m = kInvalidPacked;      // mpc_eval.py:122,161-164
+      else m = (m & 0xFFFFFFFF00000000ull) | (unsigned long long)((long long)(m & 0xFFFFFFFFull) + idx_base);
+      out_min[g] = m;
+    }
+#pragma unroll
+    for (int e = 0; e < kS2Ept; ++e) cur[e] = nxt[e];
+  }
+}
+
 // the single-launch path takes: K <= 4096 per goal (one chunk), or chunks * max(topk,1) <= 4096 (in-kernel merge)
 static bool select2_eligible(int G, int K, int topk, int* chunks) {
   static const bool off = getenv("NDP_SELECT_OLD") != nullptr;     // diagnostics: force the two-stage kernels
@@ -559,7 +616,10 @@ static int select_impl(const float* cost, int G, int K, int topk, int64_t idx_ba
       part = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(ws) + toff);
       NDP_CUDA(cudaMemsetAsync(tickets, 0, (size_t)G * 4, s));
     }
-    if (topk == 0)
+    if (topk == 0 && c2 == 1 && G >= 64) {
+      const int blocks = G < 6 * num_sms() ? G : 6 * num_sms();
+      argmin_rows_kernel<<<blocks, kSelThreads, 0, s>>>(cost, G, K, (long long)idx_base, pm, skip);
+    } else if (topk == 0)
       select2_kernel<0, true><<<dim3(c2, G), kSelThreads, 0, s>>>(cost, nullptr, K, 0, (long long)idx_base, pm, nullptr, nullptr,
                                                                  part, tickets, skip);
     else

@@ -32,7 +32,8 @@ def _check(cost_cpu, topk, idx_base=0):
 
 @pytest.mark.parametrize("G,K,topk", [(1, 1, 0), (1, 5, 1), (3, 31, 4), (2, 1000, 16), (1, 4096, 128),
                                       (7, 5000, 8), (1, 65536, 16), (1, 1 << 20, 32), (64, 4096, 1),
-                                      (1, 100000, 0), (5, 3, 8)])
+                                      (1, 100000, 0), (5, 3, 8), (300, 4096, 0), (1000, 1001, 0), (128, 37, 0), (200, 4096, 16),
+                                      (90, 3000, 128)])
 def test_select_random(cuda, G, K, topk):
     torch.manual_seed(G * 1000 + K)
     _check(torch.rand(G, K), topk)
@@ -50,6 +51,17 @@ def test_select_ties_nan_and_threshold(cuda):
     c = torch.randn(2, 20000)                               # negative costs order correctly
     c[0, 77] = -0.0; c[0, 78] = 0.0
     _check(c, 16, idx_base=123456)
+
+
+def test_select_many_goals_special_values(cuda):
+    """the persistent argmin kernel of the many-goal case (G >= 64, K <= 4096): NaN rows, nothing below 1e10, ties,
+    negative costs, idx_base"""
+    torch.manual_seed(3)
+    c = torch.rand(130, 4096)
+    c[0, :] = float("nan"); c[1, :] = 1e10; c[2, 5] = c[2, 4000] = -3.0; c[3, ::2] = float("nan"); c[4, 100:] = float("inf")
+    c[5] = torch.randint(0, 4, (4096,)).float()
+    _check(c, 0, idx_base=777)
+    _check(c, 16)
 
 
 def test_select_empty_segments(cuda):
