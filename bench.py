@@ -294,7 +294,8 @@ def run_gpu(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
     c = CFG
     G, K, T, E, nd, topk = c["G"], c["K"], c["T"], c["E"], c["nd"], c["topk"]
     K_total = K * world
@@ -458,7 +459,7 @@ def run_gpu(args):
     ms_e2e = a.elapsed_time(b) / args.steps
     clocks = sampler.finish()                          # clocks of the headline + e2e timed regions
     # ---- sustained: the same resident loop for >= 2 s (its own clock samples: a 2 s tensor-bound loop is power-capped)
-    n_sus = max(args.steps, int(2000.0 / max(ms, 0.05)) + 1)
+    n_sus = max(args.steps, int(2000.0 / max(maxr(ms), 0.05)) + 1)      # the SAME count on every rank (one all-gather per plan)
     sampler2 = ClockSampler(local)
     sampler2.start()
     barrier()

@@ -288,8 +288,16 @@ extern "C" int ndp_rollout_score(ndp_planner* p, const float* e0, const float* g
   return launch_rollout_f32(rp, s);
 }
 
-static int ensure_scratch(ndp_planner* p, size_t floats) {
+// handle-owned activation scratch of the single-call entry points (grown on demand).  One planner handle must not be
+// used by two streams at once through these calls; growing is refused while the stream is being captured (warm the
+// call up eagerly with the largest batch first, as ClosedLoopSweep.capture does).
+static int ensure_scratch(ndp_planner* p, size_t floats, cudaStream_t s) {
   if (p->scratch_floats >= floats) return NDP_OK;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) {
+    set_error("generator_forward / forward_step: scratch must grow to %zu floats while the stream is capturing; run the call eagerly once first", floats);
+    return NDP_ERR_WORKSPACE;
+  }
   if (p->scratch) cudaFree(p->scratch);
   p->scratch = nullptr; p->scratch_floats = 0;
   NDP_CUDA(cudaMalloc(&p->scratch, floats * sizeof(float)));
@@ -314,7 +322,7 @@ extern "C" int ndp_generator_forward(ndp_planner* p, const float* z, int B, floa
   if (B == 0) return NDP_OK;
   NDP_CHECK_ARG(z && a, "generator_forward: null tensor");
   cudaStream_t s = (cudaStream_t)stream;
-  if (int rc = ensure_scratch(p, (size_t)B * 512)) return rc;
+  if (int rc = ensure_scratch(p, (size_t)B * 512, s)) return rc;
   float* h1 = p->scratch; float* h2 = h1 + (size_t)B * 256;
   const int C1 = 2 * p->d.E + p->d.nd;
   int rc;
@@ -333,7 +341,7 @@ extern "C" int ndp_forward_step(ndp_planner* p, const float* state, const float*
   if (B == 0) return NDP_OK;
   NDP_CHECK_ARG(state && action && next_state, "forward_step: null tensor");
   cudaStream_t s = (cudaStream_t)stream;
-  if (int rc = ensure_scratch(p, (size_t)B * (size_t)(p->d.H > 512 ? p->d.H : 512))) return rc;
+  if (int rc = ensure_scratch(p, (size_t)B * (size_t)(p->d.H > 512 ? p->d.H : 512), s)) return rc;
   int rc;
   if ((rc = linear(s, state, p->d.E, action, 4, p->Wt[5], p->bt[5], p->d.H, B, 1, nullptr, p->scratch))) return rc;
   return linear(s, p->scratch, p->d.H, nullptr, 0, p->Wt[6], p->bt[6], p->d.E, B, 0, state, next_state);

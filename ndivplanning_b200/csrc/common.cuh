@@ -44,6 +44,15 @@ inline void count_launch(int n = 1) { g_launches.fetch_add((unsigned long long)n
 int device_check();   // 0 if current device is sm_100
 int num_sms();
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is per device: returns true the first time `mask` sees the current
+// device (bit = device ordinal, 64 devices), so a process driving several GPUs sets the attribute on each of them
+inline bool first_use_on_device(std::atomic<unsigned long long>& mask) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  return (mask.fetch_or(bit) & bit) == 0;
+}
+
 // fp32 -> order-preserving uint32 (ascending). NaN -> 0xFFFFFFFF (sorts last).
 __host__ __device__ inline uint32_t ordered_key(float c) {
   if (c != c) return 0xFFFFFFFFu;

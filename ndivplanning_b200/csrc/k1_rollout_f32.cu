@@ -300,11 +300,10 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
 int rollout_f32_smem_bytes() { return (3 * 128 * kLd + 2 * kChunk + 4 * kLd) * (int)sizeof(float); }
 
 int launch_rollout_f32(const RolloutParams& p, cudaStream_t s) {
-  static bool attr_set = false;
+  static std::atomic<unsigned long long> attr_devs{0};
   const int smem = rollout_f32_smem_bytes();
-  if (!attr_set) {
+  if (first_use_on_device(attr_devs)) {
     NDP_CUDA(cudaFuncSetAttribute(rollout_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
   }
   const int grid = p.G * p.tiles_per_goal;
   rollout_f32_kernel<<<grid, kRThreads, smem, s>>>(p);

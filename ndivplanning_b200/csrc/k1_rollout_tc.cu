@@ -1325,10 +1325,9 @@ size_t tc_workspace_bytes(const TcPlan* p, int G) { return (size_t)(G > 0 ? G : 
 
 template <int NP>
 static int launch_np(const TcParams& tp, int grid, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_devs{0};
+  if (first_use_on_device(attr_devs)) {
     NDP_CUDA(cudaFuncSetAttribute(rollout_tc_kernel<NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
-    attr_set = true;
   }
   rollout_tc_kernel<NP><<<grid, kTcThreads, kTcSmemBytes, s>>>(tp);
   NDP_LAUNCH_CHECK();
@@ -1356,13 +1355,9 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
     tp.tiles_per_goal = (tp.tiles_per_goal + 1) / 2;            // tile pairs
     const long long grid2 = (long long)G * tp.tiles_per_goal;
     NDP_CHECK_ARG(grid2 <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
-    int dev = 0;
-    NDP_CUDA(cudaGetDevice(&dev));
-    static unsigned long long attr_mask = 0;
-    if (!(attr_mask >> (dev & 63) & 1ull)) {
+    static std::atomic<unsigned long long> attr_devs2{0};
+    if (first_use_on_device(attr_devs2))
       NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
-      attr_mask |= 1ull << (dev & 63);
-    }
     rollout_tc2_kernel<<<(int)grid2, kT2Threads, kT2SmemBytes, s>>>(tp);
     NDP_LAUNCH_CHECK();
     return NDP_OK;

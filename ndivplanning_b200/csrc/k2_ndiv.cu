@@ -866,10 +866,9 @@ extern "C" int ndp_ndiv_forward_backward(const float* x, const float* z, int N, 
   char* b = reinterpret_cast<char*>(ws);
   if (small_eligible(k, Dx, Dz)) {
     float* part = reinterpret_cast<float*>(b);          // N loss partials (ndiv_ws reserves >= 2N)
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<unsigned long long> attr_devs{0};
+    if (first_use_on_device(attr_devs)) {
       NDP_CUDA(cudaFuncSetAttribute(ndiv_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)small_smem(62, 2)));
-      attr_set = true;
     }
     ndiv_small_kernel<<<(N + kSmallWarps - 1) / kSmallWarps, kSmallWarps * 32, small_smem(Dx, Dz), s>>>(
         x, z, N, k, Dx, Dz, margin, sx, sz, part, grad_x);

@@ -596,7 +596,7 @@ static int select_impl(const float* cost, int G, int K, int topk, int64_t idx_ba
                        void* ws, size_t ws_bytes, void* stream, const int* skip) {
   NDP_CHECK_ARG(G >= 0 && K >= 0 && topk >= 0 && topk <= 128, "select: bad G/K/topk (topk<=128)");
   NDP_CHECK_ARG(G == 0 || ((cost || K == 0) && packed_min), "select: null cost/packed_min");
-  NDP_CHECK_ARG(idx_base >= 0 && idx_base + (int64_t)K <= 0xFFFFFFFFll, "select: global index must fit 32 bits");
+  NDP_CHECK_ARG(idx_base >= 0 && idx_base + (int64_t)K <= 0x7FFFFFFFll, "select: global index must fit int32 (topk_idx / best_idx are int32)");
   NDP_CHECK_ARG(G <= 65535, "select: G must be <= 65535 per call");
   if (int rc = device_check()) return rc;
   if (G == 0) return NDP_OK;

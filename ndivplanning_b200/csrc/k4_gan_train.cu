@@ -521,10 +521,9 @@ __global__ void __launch_bounds__(kThreads, 3) gemm_tc_kernel(const GemmP p) {
 
 template <int MODE>
 static int launch_gemm_tc(const GemmP& p, int splits, cudaStream_t s) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<unsigned long long> attr_devs{0};
+  if (first_use_on_device(attr_devs)) {
     NDP_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
-    attr_set = true;
   }
   const dim3 grid((p.I + 127) / 128, (p.J + 127) / 128, splits);
   gemm_tc_kernel<MODE><<<grid, kThreads, kTcSmem, s>>>(p);

@@ -380,10 +380,9 @@ int ndp_encoder_forward(ndp_encoder* e, const float* images, int B, float* codes
     const size_t MN = (size_t)p.M * p.Cout;
     const int big_tiles = ((p.M + kBM - 1) / kBM) * ((p.Cout + kBN - 1) / kBN);
     if (!p.nchw && p.Cin % kTK == 0 && big_tiles >= 32) {
-      static bool attr_set = false;
-      if (!attr_set) {
+      static std::atomic<unsigned long long> attr_devs{0};
+      if (first_use_on_device(attr_devs)) {
         NDP_CUDA(cudaFuncSetAttribute(conv_gemm_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBSmem));
-        attr_set = true;
       }
       int splits = (2 * num_sms() + big_tiles - 1) / big_tiles;      // two resident CTAs per SM
       if (big_tiles >= num_sms()) splits = 1;

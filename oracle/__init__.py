@@ -3,7 +3,7 @@ reference hot path of goodmattg/ndivplanning.
 
 Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
 ``cpu_baseline`` / ``--impl reference`` legs may import this package.  The
-product package ``ndivplanning_b200`` never does (tests/test_no_oracle_in_product.py
+product package ``ndivplanning_b200`` never does (tests/test_abi_host.py::test_product_never_imports_oracle
 greps for it).
 
 Parity status: the reference ships NO golden vectors or tests, so
