@@ -706,6 +706,9 @@ def run_gpu(args):
             "cfg4": cfg4, "cfg5": cfg5, "k3": k3,
             "ndiv": {"metric": "ndiv_pairs_per_sec_fwd_bwd", "value": pairs / (ndiv_ms * 1e-3), "unit": "ordered pairs/s",
                      "ms_per_step": ndiv_ms, "config": NDIV, "kernel_launches_per_step": ndiv_launches,
+                     "value_all_ranks": world * pairs / (ndiv_ms * 1e-3),
+                     "all_ranks_what": "one k=4096 group per rank at the same time, no exchange (groups shard without a "
+                                       "collective, SURVEY 8e); max over ranks of the per-step time",
                      "roofline": {"bound": "MUFU (3 special-function ops per ordered pair: 2 sqrt + 1 rcp; SURVEY 8d)",
                                   "floor_ms": floor_ms, "frac": floor_ms / ndiv_ms,
                                   "note": "Gram-form distances on tcgen05 (fp16 split operands), fused hinge/gradient "
