@@ -566,14 +566,22 @@ def run_gpu(args):
     ndiv_launches = launch_count() - l0
     ndiv_ms = time_steps(ndiv_step, args.steps)
     ndiv_sh = None
-    if world > 1:
-        op = ShardedNdiv(sharded.comm, NDIV["N"], NDIV["k"], NDIV["Dx"], NDIV["Dz"])
+    if True:                                               # N = 1: the same entry on a world-size-1 communicator
+        from ndivplanning_b200.sharded import Comm
+        ncomm = sharded.comm if sharded else Comm.solo(dev)
+        op = ShardedNdiv(ncomm, NDIV["N"], NDIV["k"], NDIV["Dx"], NDIV["Dz"])
         barrier()
         sh_ms = maxr(time_steps(lambda: op(x, z), args.steps))
         ndiv_sh = {"ms_per_step": sh_ms, "value": NDIV["N"] * NDIV["k"] ** 2 / (sh_ms * 1e-3), "unit": "ordered pairs/s",
-                   "rows_per_rank": op.block, "collectives_per_step": 2,
-                   "how": "ShardedNdiv: pass 1 on the rank's 128-aligned row block -> all-gather [sx|sz] -> pass 2 -> "
-                          "all-gather [grad rows | loss partial], libndivplan's NCCL communicator on the caller's stream"}
+                   "rows_per_rank": op.block, "collectives_per_step": 2, "fused_entry": bool(op.fused),
+                   "how": "ShardedNdiv -> ndp_ndiv_sharded_forward_backward (one C call per rank): pre-pack, pass 1 on "
+                          "the rank's 128-aligned row block writing into its exchange slot -> in-place all-gather "
+                          "[sx|sz] -> pass 2 -> in-place all-gather [grad rows | loss partial] -> unpack; column split "
+                          "sized to the rank's rows; libndivplan's NCCL communicator on the caller's stream"}
+        op_glue = ShardedNdiv(ncomm, NDIV["N"], NDIV["k"], NDIV["Dx"], NDIV["Dz"], fused=False)
+        barrier()
+        glue_ms = maxr(time_steps(lambda: op_glue(x, z), args.steps))
+        ndiv_sh["glue_path_ms"] = glue_ms       # the round-2a path: three library calls + torch copies per step
     ndiv_ms = maxr(ndiv_ms)
     # ---- context (rank 0, N=1 only): GAN step, encoder, other precisions, stock PyTorch on the same GPU
     gan_steps, enc_runs, modes, tgpu = {}, {}, {}, None

@@ -281,7 +281,20 @@ int ndp_comm_allgather_f32(ndp_comm* c, const float* send, float* recv, int coun
 /* rank-major all-gather of opaque bytes (the sharded plan's record exchange) */
 int ndp_comm_allgather_bytes(ndp_comm* c, const void* send, void* recv, size_t bytes_per_rank,
                              void* stream);
+int ndp_comm_rank(const ndp_comm* c);
+int ndp_comm_world(const ndp_comm* c);
 void ndp_comm_destroy(ndp_comm* c);
+
+/* ---- row-sharded ndiv loss, forward + backward, one group (diversity.py:12-19,36-41): x [k,Dx], z
+ * [k,Dz] replicated on every rank, rank r owns rows [r*B, (r+1)*B), B = ceil(k/world) rounded up to 128.  ONE stream-
+ * ordered call per rank: pre-pack, row sums of the local rows, all-gather of the [sx|sz] blocks, loss + gradient of
+ * the local rows, all-gather of [grad rows | loss partial]; sx, sz [k], loss[0] (sum of the partials in rank order) and
+ * grad_x [k,Dx] (nullable) are complete and bit-identical on every rank.  Shapes of the tensor-core path only
+ * (k >= 1536, Dx,Dz <= 32, Dx % 4 == 0); ws: ndp_ndiv_sharded_workspace_bytes(), 256-byte aligned. */
+int ndp_ndiv_sharded_workspace_bytes(int k, int Dx, int Dz, int world, size_t* bytes);
+int ndp_ndiv_sharded_forward_backward(ndp_comm* c, const float* x, const float* z, int k, int Dx, int Dz, float margin,
+                                      float* sx, float* sz, float* loss, float* grad_x, void* ws, size_t ws_bytes,
+                                      void* stream);
 
 /* number of kernels this library has launched in this process (bench gpu_launches) */
 uint64_t ndp_launch_count(void);

@@ -134,6 +134,9 @@ extern "C" int ndp_comm_allgather_bytes(ndp_comm* c, const void* send, void* rec
   return NDP_OK;
 }
 
+extern "C" int ndp_comm_rank(const ndp_comm* c) { return c ? c->rank : -1; }
+extern "C" int ndp_comm_world(const ndp_comm* c) { return c ? c->world : -1; }
+
 extern "C" void ndp_comm_destroy(ndp_comm* c) {
   if (!c) return;
   NcclApi* api = nccl();

@@ -755,9 +755,9 @@ int gram_prepare(const float* x, const float* z, int N, int k, int Dx, int Dz, v
 }
 
 static void gram_fill(GramParams& p, const float* x, const float* z, int N, int k, int Dx, int Dz, void* ws, int row0,
-                      int rows) {
+                      int rows, const GramPlan* plan = nullptr) {
   const GramWs w = gram_ws_layout(N, k, Dx, Dz);
-  const GramPlan g = gram_plan(N, k);
+  const GramPlan g = plan ? *plan : gram_plan(N, k);
   char* b = reinterpret_cast<char*>(ws);
   p.img = reinterpret_cast<const uint8_t*>(b + w.img);
   p.norms = reinterpret_cast<const float2*>(b + w.norms);
@@ -803,4 +803,120 @@ int gram_loss_grad(const float* x, const float* z, const float* sx, const float*
   return NDP_OK;
 }
 
+// ---------------------------------------------------------------- row-sharded forward + backward, one group (N = 1)
+// SURVEY 8e row 3 as ONE stream-ordered call per rank: pre-pack once, pass 1 on the rank's 128-aligned row block,
+// in-place all-gather of the [sx | sz] blocks, pass 2, in-place all-gather of [grad rows | loss partial]; the kernels
+// write straight into the rank's slot of the exchange buffers (pointer offsets), two tiny kernels unpack.  The column
+// split adapts to the rows of the CALL (a rank with 1/P of the rows still fills the GPU), so results equal the
+// single-GPU call to fp32 round-off of the split order, not bit for bit; they are identical on every rank.
+static GramPlan gram_plan_rows(int k, int row_tiles) {
+  GramPlan g;
+  g.tiles = (k + kGT - 1) / kGT;
+  long long want = (148 * 2) / (long long)(row_tiles > 0 ? row_tiles : 1);
+  if (want < 1) want = 1;
+  if (want > 16) want = 16;                              // bounds the partial buffers
+  if (want > g.tiles) want = g.tiles;
+  g.tps = (int)((g.tiles + want - 1) / want);
+  g.JS = (g.tiles + g.tps - 1) / g.tps;
+  return g;
+}
+struct ShardWs { size_t gram, part, psum, st_s, st_g, total; int B; };
+static ShardWs shard_ws_layout(int k, int Dx, int Dz, int world) {
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  ShardWs w;
+  w.B = ((k + world - 1) / world + kGT - 1) / kGT * kGT;
+  const size_t tiles = (size_t)(k + kGT - 1) / kGT;
+  w.gram = 0;
+  w.part = al(gram_ws_bytes(1, k, Dx, Dz));
+  w.psum = w.part + al(16 * tiles * sizeof(float));
+  const size_t ps = (size_t)2 * 16 * k * sizeof(float), gp = (size_t)16 * k * Dx * sizeof(float);
+  w.st_s = w.psum + al(ps > gp ? ps : gp);
+  w.st_g = w.st_s + al((size_t)world * 2 * w.B * sizeof(float));
+  w.total = w.st_g + al((size_t)world * ((size_t)w.B * Dx + 1) * sizeof(float));
+  return w;
+}
+__global__ void ndiv_unpack_s_kernel(const float* __restrict__ st, int B, int k, float* __restrict__ sx, float* __restrict__ sz) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= k) return;
+  const float* blk = st + (size_t)(j / B) * 2 * B;
+  sx[j] = blk[j % B];
+  sz[j] = blk[B + j % B];
+}
+__global__ void ndiv_unpack_g_kernel(const float* __restrict__ st, int P, int B, int k, int Dx, float* __restrict__ grad,
+                                     float* __restrict__ loss) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t per = (size_t)B * Dx + 1;
+  if (grad && e < (size_t)k * Dx) {
+    const size_t j = e / Dx;
+    grad[e] = st[(j / B) * per + (j % B) * Dx + e % Dx];
+  }
+  if (e == 0) {
+    float t = 0.f;
+    for (int r = 0; r < P; ++r) t += st[(size_t)r * per + per - 1];     // rank order: identical bits on every rank
+    loss[0] = t;
+  }
+}
 }  // namespace ndp
+
+using namespace ndp;
+extern "C" int ndp_ndiv_sharded_workspace_bytes(int k, int Dx, int Dz, int world, size_t* bytes) {
+  NDP_CHECK_ARG(bytes && k >= 1 && Dx >= 1 && Dz >= 1 && world >= 1, "ndiv_sharded: bad arguments");
+  *bytes = shard_ws_layout(k, Dx, Dz, world).total;
+  return NDP_OK;
+}
+extern "C" int ndp_ndiv_sharded_forward_backward(ndp_comm* c, const float* x, const float* z, int k, int Dx, int Dz,
+                                                 float margin, float* sx, float* sz, float* loss, float* grad_x, void* ws,
+                                                 size_t ws_bytes, void* stream) {
+  NDP_CHECK_ARG(c && x && z && sx && sz && loss, "ndiv_sharded: null argument");
+  if (int rc = device_check()) return rc;
+  NDP_CHECK_ARG(gram_eligible(1, k, Dx, Dz, 0), "ndiv_sharded: one group with k >= 1536, Dx,Dz <= 32, Dx %% 4 == 0 (use ShardedNdiv's generic path otherwise)");
+  const int world = ndp_comm_world(c), rank = ndp_comm_rank(c);
+  const ShardWs w = shard_ws_layout(k, Dx, Dz, world);
+  if (!ws || ws_bytes < w.total) { set_error("ndiv_sharded: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
+  NDP_CHECK_ARG(((uintptr_t)ws & 255) == 0, "ndiv_sharded: workspace must be 256-byte aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  char* b = reinterpret_cast<char*>(ws);
+  const int B = w.B;
+  const int row0 = rank * B < k ? rank * B : k;
+  const int rows = (row0 + B < k ? row0 + B : k) - row0;
+  float* st_s = reinterpret_cast<float*>(b + w.st_s);
+  float* st_g = reinterpret_cast<float*>(b + w.st_g);
+  const size_t per = (size_t)B * Dx + 1;
+  const GramPlan plan = gram_plan_rows(k, (rows + kGT - 1) / kGT);
+  float* psum = reinterpret_cast<float*>(b + w.psum);
+  if (int rc = gram_prepare(x, z, 1, k, Dx, Dz, b + w.gram, s)) return rc;
+  if (rows > 0) {
+    GramParams p{};
+    gram_fill(p, x, z, 1, k, Dx, Dz, b + w.gram, row0, rows, &plan);
+    p.psx = psum; p.psz = psum + (size_t)plan.JS * k;
+    p.out_sx = st_s + (size_t)rank * 2 * B - row0;               // row i lands at slot[rank][0][i - row0]
+    p.out_sz = st_s + (size_t)rank * 2 * B + B - row0;
+    const size_t sm = gram_smem(Dx, Dz, false);
+    if (int rc = gram_set_smem((const void*)ndiv_gram_kernel<false>, sm)) return rc;
+    ndiv_gram_kernel<false><<<dim3((rows + kGT - 1) / kGT, plan.JS, 1), kGNT, sm, s>>>(p);
+    NDP_LAUNCH_CHECK();
+  }
+  if (int rc = ndp_comm_allgather_f32(c, st_s + (size_t)rank * 2 * B, st_s, 2 * B, stream)) return rc;
+  ndiv_unpack_s_kernel<<<(k + 255) / 256, 256, 0, s>>>(st_s, B, k, sx, sz);
+  NDP_LAUNCH_CHECK();
+  if (rows > 0) {
+    GramParams p{};
+    gram_fill(p, x, z, 1, k, Dx, Dz, b + w.gram, row0, rows, &plan);
+    p.sx = sx; p.sz = sz; p.margin = margin;
+    p.loss_part = reinterpret_cast<float*>(b + w.part);
+    p.gpart = psum;
+    p.loss = st_g + (size_t)rank * per + per - 1;
+    p.grad = grad_x ? st_g + (size_t)rank * per - (size_t)row0 * Dx : nullptr;   // row i at slot[rank][(i - row0) * Dx]
+    const size_t sm = gram_smem(Dx, Dz, true);
+    if (int rc = gram_set_smem((const void*)ndiv_gram_kernel<true>, sm)) return rc;
+    ndiv_gram_kernel<true><<<dim3((rows + kGT - 1) / kGT, plan.JS, 1), kGNT, sm, s>>>(p);
+    NDP_LAUNCH_CHECK();
+  } else {
+    NDP_CUDA(cudaMemsetAsync(st_g + (size_t)rank * per + per - 1, 0, sizeof(float), s));
+  }
+  if (int rc = ndp_comm_allgather_f32(c, st_g + (size_t)rank * per, st_g, (int)per, stream)) return rc;
+  const size_t n = grad_x ? (size_t)k * Dx : 1;
+  ndiv_unpack_g_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(st_g, world, B, k, Dx, grad_x, loss);
+  NDP_LAUNCH_CHECK();
+  return NDP_OK;
+}

@@ -87,6 +87,19 @@ class Comm:
         with torch.cuda.device(self.device):
             check(lib().ndp_comm_create(C.byref(self._h), idb, self.rank, self.world))
 
+    @classmethod
+    def solo(cls, device):
+        """world-size-1 communicator without torch.distributed (single-GPU runs of the sharded entry points)"""
+        import ctypes as C
+        self = cls.__new__(cls)
+        self.rank, self.world, self.device = 0, 1, torch.device(device)
+        idb = (C.c_ubyte * 128)()
+        check(lib().ndp_comm_unique_id(idb))
+        self._h = C.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib().ndp_comm_create(C.byref(self._h), idb, 0, 1))
+        return self
+
     def allgather(self, send: torch.Tensor) -> torch.Tensor:
         """rank-major all-gather on the current stream: [..] -> [world, ..]"""
         send = send.contiguous()
@@ -189,9 +202,15 @@ class ShardedNdiv:
 
     The loss is the sum of the gathered partials in rank order, so every rank holds the same bits (no all-reduce
     rounding-order ambiguity) and — row blocks being 128-aligned — the same bits as the single-GPU call.  Buffers are
-    allocated once per (N, k, Dx, Dz)."""
+    allocated once per (N, k, Dx, Dz).
 
-    def __init__(self, comm: Comm, N: int, k: int, Dx: int, Dz: int):
+    One group on the Gram path (N == 1, k >= 1536, Dx, Dz <= 32) takes the FUSED entry instead: one C call per rank
+    (ndp_ndiv_sharded_forward_backward: pre-pack once, pass kernels writing straight into the exchange slots, in-place
+    all-gathers, two unpack kernels; column split sized to the rank's rows so 1/P of the rows still fills the GPU).
+    Its results are identical on every rank and equal the single-GPU call to fp32 round-off of the split order; the
+    returned tensors are owned by this object and overwritten by the next call."""
+
+    def __init__(self, comm: Comm, N: int, k: int, Dx: int, Dz: int, fused=None):
         import ctypes as C
         self.comm, self.N, self.k, self.Dx, self.Dz = comm, N, k, Dx, Dz
         dev = comm.device
@@ -208,6 +227,17 @@ class ShardedNdiv:
         n = C.c_size_t()
         check(lib().ndp_ndiv_workspace_bytes(N, k, Dx, Dz, C.byref(n)))
         self.ws = torch.empty(max(n.value, 256), dtype=torch.uint8, device=dev)
+        # one group on the tensor-core (Gram) path: ONE library call per rank does pre-pack, both passes and both
+        # exchanges with the kernels writing straight into the exchange slots (ndp_ndiv_sharded_forward_backward)
+        self.fused = fused if fused is not None else (N == 1 and k >= 1536 and Dx <= 32 and Dz <= 32 and Dx % 4 == 0)
+        if self.fused:
+            check(lib().ndp_ndiv_sharded_workspace_bytes(k, Dx, Dz, W, C.byref(n)))
+            self.fws = torch.empty(n.value + 256, dtype=torch.uint8, device=dev)
+            self.fws = self.fws[(-self.fws.data_ptr()) % 256:][:n.value]
+            self.f_sx = torch.empty(k, dtype=f32, device=dev)
+            self.f_sz = torch.empty(k, dtype=f32, device=dev)
+            self.f_loss = torch.empty(1, dtype=f32, device=dev)
+            self.f_grad = torch.empty(1, k, Dx, dtype=f32, device=dev)
 
     def __call__(self, x: torch.Tensor, z: torch.Tensor, want_grad: bool = True):
         """x [N,k,Dx], z [N,k,Dz] on this rank's device -> (loss[()], grad_x [N,k,Dx] | None), complete on every rank"""
@@ -215,7 +245,13 @@ class ShardedNdiv:
         dev = self.comm.device
         L, st = lib(), stream_ptr(dev)
         r0, rows = self.row0, self.rows
-        sxk, szk = self.sx[:, :k], self.sz[:, :k]
+        if self.fused:
+            with torch.cuda.device(dev):
+                check(L.ndp_ndiv_sharded_forward_backward(self.comm._h, ptr(x), ptr(z), k, Dx, Dz, _div.MARGIN,
+                                                          ptr(self.f_sx), ptr(self.f_sz), ptr(self.f_loss),
+                                                          ptr(self.f_grad) if want_grad else None, ptr(self.fws),
+                                                          self.fws.numel(), st))
+            return self.f_loss.reshape(()), (self.f_grad if want_grad else None)
         with torch.cuda.device(dev):
             if rows > 0:
                 sx_l = torch.empty(N, k, dtype=torch.float32, device=dev)

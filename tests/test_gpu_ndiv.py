@@ -190,6 +190,33 @@ def test_ndiv_gram_row_sharded_equals_full(cuda):
     assert torch.equal(xg.grad, full_grad)
 
 
+@pytest.mark.parametrize("k,Dx,Dz", [(4096, 32, 16), (1536, 32, 32), (2000, 8, 5), (1700, 4, 31)])
+def test_ndiv_sharded_fused_entry_world1(cuda, k, Dx, Dz):
+    """ndp_ndiv_sharded_forward_backward on a world-size-1 communicator (the same code the N-rank call runs: kernels
+    writing into exchange slots, in-place all-gathers, unpack): loss within 1e-4 of the fp64 oracle, gradient within
+    1e-4 of its max, row sums within 1e-5; loss-only call returns the same loss; near-duplicate rows stay finite"""
+    from ndivplanning_b200.sharded import Comm, ShardedNdiv
+    comm = Comm.solo("cuda:0")
+    try:
+        x, z = synthetic.make_ndiv_inputs(1, k, Dx, Dz, seed=k + Dx)
+        x[0, 11] = x[0, 3]                                   # one exact duplicate: the in-kernel exact path
+        op = ShardedNdiv(comm, 1, k, Dx, Dz)
+        assert op.fused
+        loss, grad = op(x.cuda(), z.cuda())
+        loss, grad = loss.cpu().clone(), grad.cpu().clone()
+        sx, sz = op.f_sx.cpu().clone(), op.f_sz.cpu().clone()
+        loss2, none = op(x.cuda(), z.cuda(), want_grad=False)
+        assert none is None and float(loss2) == float(loss)
+        l64, g64 = O.ndiv_fwd_bwd(x.double(), z.double())
+        np.testing.assert_allclose(loss.numpy(), l64.numpy(), rtol=RTOL)
+        assert torch.isfinite(grad).all()
+        _grad_close_arbiter(grad, x, z, g64.numpy())
+        np.testing.assert_allclose(sx.numpy(), torch.cdist(x.double(), x.double()).sum(-1)[0].numpy(), rtol=1e-5)
+        np.testing.assert_allclose(sz.numpy(), torch.cdist(z.double(), z.double()).sum(-1)[0].numpy(), rtol=1e-5)
+    finally:
+        comm.close()
+
+
 @pytest.mark.parametrize("N,k,Dx,Dz", [(56, 6, 4, 2), (3, 300, 32, 16), (1, 1536, 32, 16)])
 def test_ndiv_tight_cluster_far_from_origin(cuda, N, k, Dx, Dz):
     """the S samples of one code during GAN training: |x_i - x_j| ~ 1e-2 around a mean of size ~3.  The gradient

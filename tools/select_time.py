@@ -21,7 +21,10 @@ def timed(fn, reps=20):
 
 
 def main():
-    for G, K in ((1, 65536), (1, 131072), (1, 1 << 20), (64, 4096), (4096, 4096)):
+    shapes = ((1, 65536), (1, 131072), (1, 1 << 20), (64, 4096), (4096, 4096))
+    if os.environ.get("NDP_SELECT_ONLY"):                  # e.g. 4096x4096 (profiling runs)
+        shapes = (tuple(int(v) for v in os.environ["NDP_SELECT_ONLY"].split("x")),)
+    for G, K in shapes:
         bufs = [torch.rand(G, K, device="cuda") for _ in range(3 if G * K * 4 > (32 << 20) else 1)]
         it = [0]
 

@@ -50,22 +50,30 @@ def main():
               f"verified={sp.verified.tolist()}", flush=True)
         ok &= same
     comm = Comm(dev)
-    for (N, k, Dx, Dz) in ((2, 1000, 32, 16), (1, 4096, 32, 16), (3, 200, 12, 5)):
+    for (N, k, Dx, Dz, fused) in ((2, 1000, 32, 16, None), (1, 4096, 32, 16, False), (1, 4096, 32, 16, True),
+                                  (1, 2000, 8, 16, True), (3, 200, 12, 5, None)):
         x, z = synthetic.make_ndiv_inputs(N, k, Dx, Dz)
         xg = x.to(dev).requires_grad_(True)
         loss = diversity.compute_pairwise_divergence(xg, z.to(dev))
         loss.backward()
-        op = ShardedNdiv(comm, N, k, Dx, Dz)
+        op = ShardedNdiv(comm, N, k, Dx, Dz, fused=fused)
         sl, sg = op(x.to(dev), z.to(dev))
+        sl, sg = sl.clone(), sg.clone()             # the fused path returns buffers it owns
         sl2, _ = op(x.to(dev), z.to(dev), want_grad=False)
         torch.cuda.synchronize()
         lerr = abs(sl.item() - loss.item()) / abs(loss.item())
         gerr = (sg - xg.grad).abs().max().item() / xg.grad.abs().max().item()
         bit = torch.equal(sg, xg.grad)
-        print(f"[rank {rank}] ndiv N={N} k={k} sharded vs single: loss rel {lerr:.2e} grad rel {gerr:.2e} "
-              f"grad bit-equal {bit} loss-only equal {sl2.item() == sl.item()}", flush=True)
-        ok &= lerr < 1e-5 and gerr < 1e-5 and sl2.item() == sl.item()
-        if k >= 256 and Dx <= 32:              # Gram path, 128-aligned row blocks: same bits as the single-GPU call
+        # every rank must hold the same bits (rank-ordered sums, no all-reduce)
+        mine = torch.cat([sl.reshape(1), sg.reshape(-1)]).view(torch.int32)
+        lo, hi = mine.clone(), mine.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same_all = torch.equal(lo, hi)
+        print(f"[rank {rank}] ndiv N={N} k={k} Dx={Dx} fused={op.fused} sharded vs single: loss rel {lerr:.2e} grad rel "
+              f"{gerr:.2e} grad bit-equal {bit} loss-only equal {sl2.item() == sl.item()} same on all ranks {same_all}",
+              flush=True)
+        ok &= lerr < 1e-5 and gerr < 1e-5 and sl2.item() == sl.item() and same_all
+        if k >= 256 and Dx <= 32 and not op.fused:   # Gram path, 128-aligned row blocks: same bits as the single-GPU call
             ok &= bit
     comm.close()
     t = torch.tensor([1 if ok else 0], device=dev)
