@@ -283,12 +283,21 @@ int ndp_comm_allgather_bytes(ndp_comm* c, const void* send, void* recv, size_t b
                              void* stream);
 int ndp_comm_rank(const ndp_comm* c);
 int ndp_comm_world(const ndp_comm* c);
+/* Peer window (csrc/peer.cuh): on one node every rank maps every other rank's exchange window through CUDA IPC on first
+ * use, and the sharded entry points below exchange their results with loads / stores over NVLink and one flag word
+ * per (phase, rank) instead of library collectives; ranks that cannot map each other (or NDP_NO_PEER_WINDOW=1, or a
+ * stream under graph capture) use the NCCL collectives above.  *mapped = 1 when the window path is active.  Returns
+ * NDP_ERR_NCCL if a bounded in-kernel wait for a peer expired since the last call (a rank missed a collective
+ * call); synchronises `stream`. */
+int ndp_comm_peer_status(ndp_comm* c, int* mapped, void* stream);
 void ndp_comm_destroy(ndp_comm* c);
 
 /* ---- row-sharded ndiv loss, forward + backward, one group (diversity.py:12-19,36-41): x [k,Dx], z
  * [k,Dz] replicated on every rank, rank r owns rows [r*B, (r+1)*B), B = ceil(k/world) rounded up to 128.  ONE stream-
- * ordered call per rank: pre-pack, row sums of the local rows, all-gather of the [sx|sz] blocks, loss + gradient of
- * the local rows, all-gather of [grad rows | loss partial]; sx, sz [k], loss[0] (sum of the partials in rank order) and
+ * ordered call per rank: pre-pack, row sums of the local rows, exchange of the [sx|sz] blocks, loss + gradient of
+ * the local rows, exchange of [grad rows | loss partial] (peer window: the pass kernels' last CTA publishes the rank's
+ * slot, a pull kernel gathers every rank's slot over NVLink — 5 launches, no library collective; otherwise two
+ * in-place ncclAllGather); sx, sz [k], loss[0] (sum of the partials in rank order) and
  * grad_x [k,Dx] (nullable) are complete and bit-identical on every rank.  Shapes of the tensor-core path only
  * (k >= 1536, Dx,Dz <= 32, Dx % 4 == 0); ws: ndp_ndiv_sharded_workspace_bytes(), 256-byte aligned. */
 int ndp_ndiv_sharded_workspace_bytes(int k, int Dx, int Dz, int world, size_t* bytes);

@@ -83,6 +83,7 @@ _PROTOS = {
     "ndp_comm_allgather_bytes": (_i, [_vp, _vp, _vp, _sz, _vp]),
     "ndp_comm_rank": (_i, [_vp]),
     "ndp_comm_world": (_i, [_vp]),
+    "ndp_comm_peer_status": (_i, [_vp, C.POINTER(_i), _vp]),
     "ndp_comm_destroy": (None, [_vp]),
     "ndp_ndiv_sharded_workspace_bytes": (_i, [_i, _i, _i, _i, C.POINTER(_sz)]),
     "ndp_ndiv_sharded_forward_backward": (_i, [_vp, _vp, _vp, _i, _i, _i, _f, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

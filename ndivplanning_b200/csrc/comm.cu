@@ -6,6 +6,7 @@
 #include <dlfcn.h>
 #include <string.h>
 #include "common.cuh"
+#include "peer.cuh"
 
 namespace ndp {
 
@@ -52,11 +53,6 @@ static NcclApi* nccl() {
 
 }  // namespace ndp
 
-struct ndp_comm {
-  ndp::ncclComm_t comm;
-  int rank, world;
-};
-
 using namespace ndp;
 
 #define NDP_NCCL(call)                                                          \
@@ -85,7 +81,8 @@ extern "C" int ndp_comm_create(ndp_comm** out, const void* id128_host, int rank,
   if (!api) return NDP_ERR_NCCL;
   ncclUniqueId id;
   memcpy(&id, id128_host, sizeof(id));
-  ndp_comm* c = new ndp_comm{nullptr, rank, world};
+  ndp_comm* c = new ndp_comm{};
+  c->rank = rank; c->world = world;
   int r = api->CommInitRank(&c->comm, world, id, rank);
   if (r != 0) {
     set_error("ncclCommInitRank failed: %s", api->GetErrorString(r));
@@ -137,8 +134,96 @@ extern "C" int ndp_comm_allgather_bytes(ndp_comm* c, const void* send, void* rec
 extern "C" int ndp_comm_rank(const ndp_comm* c) { return c ? c->rank : -1; }
 extern "C" int ndp_comm_world(const ndp_comm* c) { return c ? c->world : -1; }
 
+// ---------------------------------------------------------------- peer window (peer.cuh)
+static void window_release(ndp_comm* c) {
+  for (int r = 0; r < c->world && r < kMaxPeers; ++r)
+    if (c->peer[r] && r != c->rank) cudaIpcCloseMemHandle(c->peer[r]);
+  if (c->win) cudaFree(c->win);
+  c->win = nullptr; c->win_bytes = 0;
+  for (int r = 0; r < kMaxPeers; ++r) c->peer[r] = nullptr;
+}
+
+namespace ndp {
+int comm_window(ndp_comm* c, size_t payload, cudaStream_t s, PeerWin* w) {
+  memset(w, 0, sizeof(*w));
+  if (c->win_state < 0 || c->world > kMaxPeers) { c->win_state = -1; return NDP_OK; }
+  static const bool off = getenv("NDP_NO_PEER_WINDOW") != nullptr;      // diagnostics: force the NCCL collectives
+  if (off) { c->win_state = -1; return NDP_OK; }
+  const size_t need = kWinHeader + payload;
+  if (!c->win || c->win_bytes < need) {
+    // collective re-allocation: every rank takes this branch in the same call (same arguments on every rank)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    NDP_CUDA(cudaStreamIsCapturing(s, &cap));
+    if (cap != cudaStreamCaptureStatusNone) { set_error("peer window: cannot (re)allocate under stream capture; run the call once eagerly first"); return NDP_ERR_ARG; }
+    NcclApi* api = nccl();
+    if (!api) return NDP_ERR_NCCL;
+    NDP_CUDA(cudaDeviceSynchronize());                       // nobody may still read the old window after the exchange below
+    size_t bytes = (need + (4u << 20) - 1) / (4u << 20) * (4u << 20);
+    char* nw = nullptr;
+    NDP_CUDA(cudaMalloc(&nw, bytes));
+    NDP_CUDA(cudaMemset(nw, 0, bytes));
+    struct Ex { cudaIpcMemHandle_t h; unsigned long long bytes; int ok; int pad; };
+    Ex mine{};
+    mine.bytes = bytes;
+    mine.ok = 1;
+    if (c->world > 1 && cudaIpcGetMemHandle(&mine.h, nw) != cudaSuccess) { mine.ok = 0; cudaGetLastError(); }
+    Ex* dex = nullptr;
+    Ex hex[kMaxPeers];
+    NDP_CUDA(cudaMalloc(&dex, sizeof(Ex) * c->world));
+    NDP_CUDA(cudaMemcpy(dex + c->rank, &mine, sizeof(Ex), cudaMemcpyHostToDevice));
+    NDP_NCCL(api->AllGather(dex + c->rank, dex, sizeof(Ex), kNcclInt8, c->comm, s));
+    NDP_CUDA(cudaStreamSynchronize(s));
+    NDP_CUDA(cudaMemcpy(hex, dex, sizeof(Ex) * c->world, cudaMemcpyDeviceToHost));
+    // every peer has synchronised its device before contributing: the old windows are idle everywhere
+    window_release(c);
+    int ok = 1;
+    for (int r = 0; r < c->world; ++r) ok &= hex[r].ok && hex[r].bytes == bytes;
+    c->win = nw; c->win_bytes = bytes; c->peer[c->rank] = nw;
+    for (int r = 0; r < c->world && ok; ++r) {
+      if (r == c->rank) continue;
+      void* pp = nullptr;
+      if (cudaIpcOpenMemHandle(&pp, hex[r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { ok = 0; cudaGetLastError(); break; }
+      c->peer[r] = reinterpret_cast<char*>(pp);
+    }
+    // agree on the outcome (a rank that could not map a peer takes everyone to the NCCL path)
+    unsigned long long vote = ok ? 1ull : 0ull;
+    NDP_CUDA(cudaMemcpy(dex, &vote, 8, cudaMemcpyHostToDevice));
+    NDP_NCCL(api->AllReduce(dex, dex, 1, kNcclUint64, kNcclMin, c->comm, s));
+    NDP_CUDA(cudaStreamSynchronize(s));
+    NDP_CUDA(cudaMemcpy(&vote, dex, 8, cudaMemcpyDeviceToHost));
+    cudaFree(dex);
+    if (!vote) { window_release(c); c->win_state = -1; return NDP_OK; }
+    c->win_state = 1;
+  }
+  for (int r = 0; r < c->world; ++r) w->peer[r] = c->peer[r];
+  w->rank = c->rank; w->world = c->world;
+  return NDP_OK;
+}
+
+int comm_window_check(ndp_comm* c, cudaStream_t s) {
+  if (!c->win) return NDP_OK;
+  unsigned err = 0;
+  NDP_CUDA(cudaMemcpyAsync(&err, c->win + kWinErrOff, 4, cudaMemcpyDeviceToHost, s));
+  NDP_CUDA(cudaStreamSynchronize(s));
+  if (err) {
+    NDP_CUDA(cudaMemsetAsync(c->win + kWinErrOff, 0, 4, s));
+    set_error("peer window: rank %d timed out waiting for rank %u (a peer did not make the matching call)", c->rank, err - 1);
+    return NDP_ERR_NCCL;
+  }
+  return NDP_OK;
+}
+}  // namespace ndp
+
+extern "C" int ndp_comm_peer_status(ndp_comm* c, int* mapped, void* stream) {
+  NDP_CHECK_ARG(c, "comm_peer_status: null communicator");
+  if (mapped) *mapped = c->win_state == 1 ? 1 : 0;
+  return comm_window_check(c, (cudaStream_t)stream);
+}
+
 extern "C" void ndp_comm_destroy(ndp_comm* c) {
   if (!c) return;
+  cudaDeviceSynchronize();
+  window_release(c);
   NcclApi* api = nccl();
   if (api && c->comm) api->CommDestroy(c->comm);
   delete c;

@@ -28,6 +28,7 @@
 #include <stdlib.h>
 #include "common.cuh"
 #include "tc_common.cuh"
+#include "peer.cuh"
 
 namespace ndp {
 using namespace tc;
@@ -212,7 +213,13 @@ struct GramParams {
   float* loss;                 // pass 2: final loss
   float* gpart;                // pass 2: [JS][N][k][Dx] (JS > 1)
   float* grad;                 // pass 2: final gradient [N][k][Dx] (nullable: loss only)
-  unsigned* tickets;           // [2 * N * tiles + 1]: pass-1 row-tile tickets, pass-2 row-tile tickets, grid ticket
+  unsigned* tickets;           // [2 * N * tiles + 2]: pass-1 row-tile tickets, pass-2 row-tile tickets, grid tickets of
+                               // pass 2 and pass 1
+  // row-sharded call over a peer window (peer.cuh): the LAST CTA of the grid publishes `sig_epoch` in flag slot
+  // `sig_slot` of every rank once this rank's results are written (pw.world == 0: single-GPU call, no signal)
+  PeerWin pw;
+  int sig_slot;
+  unsigned sig_epoch;
 };
 
 // exact squared distance of two fp32 rows (the reference's own form: sum of squared differences)
@@ -616,6 +623,13 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
         }
       }
     }
+    if (p.pw.world > 0) {                                  // sharded: the grid's last CTA signals every rank
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) s_ticket[1] = atomicAdd(p.tickets + 2 * (size_t)N * p.tiles + 1, 1u);
+      __syncthreads();
+      if (s_ticket[1] == gridDim.x * gridDim.y * gridDim.z - 1 && warp == 0) peer_signal_all(p.pw, p.sig_slot, p.sig_epoch);
+    }
   } else {
     float lsum = st.lsum;
     lsum = lsum + __shfl_xor_sync(0xffffffffu, lsum, 16);
@@ -659,10 +673,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
     }
     __threadfence();
     __syncthreads();
-    if (tid == 0) {
-      s_ticket[0] = (grad && p.JS > 1) ? atomicAdd(p.tickets + tk_row, 1u) : 0u;
-      s_ticket[1] = atomicAdd(p.tickets + 2 * (size_t)N * p.tiles, 1u);
-    }
+    if (tid == 0) s_ticket[0] = (grad && p.JS > 1) ? atomicAdd(p.tickets + tk_row, 1u) : 0u;
     __syncthreads();
     if (grad && p.JS > 1 && s_ticket[0] == (unsigned)(p.JS - 1)) {
       __threadfence();
@@ -676,7 +687,13 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
           p.grad[off] = a;
         }
       }
+      __threadfence();
     }
+    // grid ticket AFTER this CTA's last global write (the combined gradient rows above), so that whoever draws the
+    // last ticket may publish the whole call's results
+    __syncthreads();
+    if (tid == 0) s_ticket[1] = atomicAdd(p.tickets + 2 * (size_t)N * p.tiles, 1u);
+    __syncthreads();
     if (s_ticket[1] == (unsigned)(n_parts - 1)) {        // last CTA of the grid: the loss, fixed summation order
       __threadfence();
       float t = 0.f;
@@ -690,6 +707,10 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
         __syncthreads();
       }
       if (tid == 0) p.loss[0] = sf[0];
+      if (p.pw.world > 0) {
+        __syncthreads();
+        if (warp == 0) peer_signal_all(p.pw, p.sig_slot, p.sig_epoch);
+      }
     }
   }
   fence_before_sync();
@@ -724,7 +745,7 @@ static GramWs gram_ws_layout(int N, int k, int Dx, int Dz) {
   auto al = [](size_t v) { return (v + 255) / 256 * 256; };
   GramWs w;
   w.tickets = 0;
-  w.mu = al((2 * (size_t)N * tiles + 1) * sizeof(unsigned));
+  w.mu = al((2 * (size_t)N * tiles + 2) * sizeof(unsigned));
   w.norms = w.mu + al((size_t)N * 64 * 4);
   w.img = w.norms + al((size_t)N * tiles * kGNS * 8);
   w.imgT = w.img + al((size_t)N * tiles * gd.img_bytes);
@@ -749,7 +770,7 @@ int gram_prepare(const float* x, const float* z, int N, int k, int Dx, int Dz, v
                                                       reinterpret_cast<uint8_t*>(b + w.imgT),
                                                       reinterpret_cast<float*>(b + w.mu),
                                                       reinterpret_cast<float2*>(b + w.norms),
-                                                      reinterpret_cast<unsigned*>(b + w.tickets), 2 * N * tiles + 1);
+                                                      reinterpret_cast<unsigned*>(b + w.tickets), 2 * N * tiles + 2);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }
@@ -856,6 +877,49 @@ __global__ void ndiv_unpack_g_kernel(const float* __restrict__ st, int P, int B,
     loss[0] = t;
   }
 }
+// ---- the same exchange over the peer window (peer.cuh): the pass kernels' last CTA publishes the rank's slot, these
+// kernels wait for every rank's flag and PULL the slots over NVLink (no staging copy, no library collective)
+struct ShardWin { size_t s_off, g_off, half, need; };
+static ShardWin shard_win_layout(int B, int Dx, size_t win_bytes) {
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  ShardWin w;
+  const size_t per_parity = al((size_t)2 * B * 4) + al(((size_t)B * Dx + 1) * 4);
+  w.need = 2 * per_parity;
+  // the parity halves split the window's CAPACITY (identical on every rank), not this shape's need, so calls of
+  // different shapes on one communicator never overlap a region a slower peer may still be pulling from
+  w.half = win_bytes > kWinHeader ? ((win_bytes - kWinHeader) / 2) / 256 * 256 : 0;
+  w.s_off = 0;
+  w.g_off = al((size_t)2 * B * 4);
+  return w;
+}
+__global__ void peer_signal_kernel(PeerWin w, int slot, unsigned epoch) { peer_signal_all(w, slot, epoch); }
+__global__ void ndiv_pull_s_kernel(PeerWin w, size_t off, unsigned epoch, int B, int k, float* __restrict__ sx,
+                                   float* __restrict__ sz) {
+  if ((int)threadIdx.x < w.world) peer_wait(w, 0, threadIdx.x, epoch);
+  __syncthreads();
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= k) return;
+  const float* blk = reinterpret_cast<const float*>(w.peer[j / B] + off);
+  sx[j] = ld_peer(blk + j % B);
+  sz[j] = ld_peer(blk + B + j % B);
+}
+__global__ void ndiv_pull_g_kernel(PeerWin w, size_t off, unsigned epoch, int B, int k, int Dx, float* __restrict__ grad,
+                                   float* __restrict__ loss) {
+  if ((int)threadIdx.x < w.world) peer_wait(w, 1, threadIdx.x, epoch);
+  __syncthreads();
+  const size_t e = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;       // Dx % 4 == 0
+  if (grad && e < (size_t)k * Dx) {
+    const size_t j = e / Dx;
+    const float* slot = reinterpret_cast<const float*>(w.peer[j / B] + off);
+    *reinterpret_cast<float4*>(grad + e) = ld_peer4(reinterpret_cast<const float4*>(slot + (j % B) * Dx + e % Dx));
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    float t = 0.f;
+    for (int r = 0; r < w.world; ++r)                       // rank order: identical bits on every rank
+      t += ld_peer(reinterpret_cast<const float*>(w.peer[r] + off) + (size_t)B * Dx);
+    loss[0] = t;
+  }
+}
 }  // namespace ndp
 
 using namespace ndp;
@@ -874,6 +938,7 @@ extern "C" int ndp_ndiv_sharded_forward_backward(ndp_comm* c, const float* x, co
   const ShardWs w = shard_ws_layout(k, Dx, Dz, world);
   if (!ws || ws_bytes < w.total) { set_error("ndiv_sharded: workspace %zu < %zu", ws_bytes, w.total); return NDP_ERR_WORKSPACE; }
   NDP_CHECK_ARG(((uintptr_t)ws & 255) == 0, "ndiv_sharded: workspace must be 256-byte aligned");
+  NDP_CHECK_ARG(!grad_x || ((uintptr_t)grad_x & 15) == 0, "ndiv_sharded: grad_x must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
   char* b = reinterpret_cast<char*>(ws);
   const int B = w.B;
@@ -884,6 +949,59 @@ extern "C" int ndp_ndiv_sharded_forward_backward(ndp_comm* c, const float* x, co
   const size_t per = (size_t)B * Dx + 1;
   const GramPlan plan = gram_plan_rows(k, (rows + kGT - 1) / kGT);
   float* psum = reinterpret_cast<float*>(b + w.psum);
+  // ---- exchange over the peer window when the ranks can map each other (one node, NVLink) and no graph is being
+  // captured (the epoch is a launch argument); otherwise the NCCL all-gathers below
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  NDP_CUDA(cudaStreamIsCapturing(s, &cap));
+  PeerWin pw{};
+  if (cap == cudaStreamCaptureStatusNone) {
+    if (int rc = comm_window(c, shard_win_layout(B, Dx, 0).need, s, &pw)) return rc;
+  }
+  if (pw.world > 0) {
+    const ShardWin wl = shard_win_layout(B, Dx, c->win_bytes);
+    const unsigned epoch = ++c->epoch;
+    const size_t base = kWinHeader + (size_t)(epoch & 1u) * wl.half;
+    float* my_s = reinterpret_cast<float*>(c->win + base + wl.s_off);
+    float* my_g = reinterpret_cast<float*>(c->win + base + wl.g_off);
+    if (int rc = gram_prepare(x, z, 1, k, Dx, Dz, b + w.gram, s)) return rc;
+    if (rows > 0) {
+      GramParams p{};
+      gram_fill(p, x, z, 1, k, Dx, Dz, b + w.gram, row0, rows, &plan);
+      p.psx = psum; p.psz = psum + (size_t)plan.JS * k;
+      p.out_sx = my_s - row0;                                 // row i lands at slot[i - row0]
+      p.out_sz = my_s + B - row0;
+      p.pw = pw; p.sig_slot = 0; p.sig_epoch = epoch;
+      const size_t sm = gram_smem(Dx, Dz, false);
+      if (int rc = gram_set_smem((const void*)ndiv_gram_kernel<false>, sm)) return rc;
+      ndiv_gram_kernel<false><<<dim3((rows + kGT - 1) / kGT, plan.JS, 1), kGNT, sm, s>>>(p);
+    } else {
+      peer_signal_kernel<<<1, 32, 0, s>>>(pw, 0, epoch);
+    }
+    NDP_LAUNCH_CHECK();
+    ndiv_pull_s_kernel<<<(k + 255) / 256, 256, 0, s>>>(pw, base + wl.s_off, epoch, B, k, sx, sz);
+    NDP_LAUNCH_CHECK();
+    if (rows > 0) {
+      GramParams p{};
+      gram_fill(p, x, z, 1, k, Dx, Dz, b + w.gram, row0, rows, &plan);
+      p.sx = sx; p.sz = sz; p.margin = margin;
+      p.loss_part = reinterpret_cast<float*>(b + w.part);
+      p.gpart = psum;
+      p.loss = my_g + (size_t)B * Dx;
+      p.grad = grad_x ? my_g - (size_t)row0 * Dx : nullptr;
+      p.pw = pw; p.sig_slot = 1; p.sig_epoch = epoch;
+      const size_t sm = gram_smem(Dx, Dz, true);
+      if (int rc = gram_set_smem((const void*)ndiv_gram_kernel<true>, sm)) return rc;
+      ndiv_gram_kernel<true><<<dim3((rows + kGT - 1) / kGT, plan.JS, 1), kGNT, sm, s>>>(p);
+    } else {
+      NDP_CUDA(cudaMemsetAsync(my_g + (size_t)B * Dx, 0, sizeof(float), s));
+      peer_signal_kernel<<<1, 32, 0, s>>>(pw, 1, epoch);
+    }
+    NDP_LAUNCH_CHECK();
+    const size_t n4 = grad_x ? (size_t)k * Dx / 4 : 1;
+    ndiv_pull_g_kernel<<<(unsigned)((n4 + 255) / 256), 256, 0, s>>>(pw, base + wl.g_off, epoch, B, k, Dx, grad_x, loss);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
   if (int rc = gram_prepare(x, z, 1, k, Dx, Dz, b + w.gram, s)) return rc;
   if (rows > 0) {
     GramParams p{};

@@ -525,15 +525,24 @@ argmin_rows_kernel(const float* __restrict__ cost, int G, int K, long long idx_b
   for (; g < G; g += gridDim.x, ++it) {
     const int gn = g + gridDim.x;
     if (gn < G) load_row(gn, nxt);
-    unsigned long long m = kPadKey;
+    // Per thread in the float domain (2-3 instructions per element instead of ~10 for packed 64-bit keys — the packed
+    // form made this kernel issue-bound at 79 % issue-active, profiles/r02_ncu_full_argmin_rows_raw.csv): the thread's
+    // indices ascend in (q, r), so a strict `<` keeps the first occurrence; NaN and the padded tail never compare
+    // below; -0 == +0 tie like their canonical keys.  A thread whose best stays +inf contributes the pad key — any
+    // winner >= 1e10 is reported as "none" below anyway (mpc_eval.py:122,161-164), so +inf needs no index.
+    float best = __int_as_float(0x7f800000);
+    int bi = 0;
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
       for (int r = 0; r < 4; ++r) {
-        const int i = q * 1024 + tid * 4 + r;
-        const unsigned long long kv = i < K ? (((unsigned long long)ordered_key(cur[4 * q + r] + 0.0f) << 32) | (unsigned)i) : kPadKey;
-        m = kv < m ? kv : m;
+        const float c = cur[4 * q + r];
+        const bool lt = c < best;
+        best = lt ? c : best;
+        bi = lt ? q * 1024 + r : bi;                       // + tid * 4 once, below
       }
+    unsigned long long m = best < __int_as_float(0x7f800000)
+                               ? (((unsigned long long)ordered_key(best + 0.0f) << 32) | (unsigned)(bi + tid * 4)) : kPadKey;
     m = warp_min_u64(m);
     if (lane == 0) s_w[it & 1][warp] = m;
     __syncthreads();                                     // double-buffered partials: one barrier per goal

@@ -109,6 +109,15 @@ class Comm:
                                                  stream_ptr(self.device)))
         return out
 
+    def peer_status(self) -> bool:
+        """True when the exchanges run over the mapped peer window (NVLink loads/stores + flags) instead of NCCL;
+        raises if an in-kernel wait for a peer expired since the last call.  Synchronises the current stream."""
+        import ctypes as C
+        m = C.c_int(0)
+        with torch.cuda.device(self.device):
+            check(lib().ndp_comm_peer_status(self._h, C.byref(m), stream_ptr(self.device)))
+        return bool(m.value)
+
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:
             lib().ndp_comm_destroy(self._h)

@@ -72,9 +72,27 @@ def main():
         print(f"[rank {rank}] ndiv N={N} k={k} Dx={Dx} fused={op.fused} sharded vs single: loss rel {lerr:.2e} grad rel "
               f"{gerr:.2e} grad bit-equal {bit} loss-only equal {sl2.item() == sl.item()} same on all ranks {same_all}",
               flush=True)
-        ok &= lerr < 1e-5 and gerr < 1e-5 and sl2.item() == sl.item() and same_all
+        if op.fused:
+            # the column split follows the rank's row count, so pairs whose hinge argument is within fp32 round-off of
+            # zero may land on the other side than in the single-GPU call (they may in ANY fp32 evaluation): rows get
+            # the fp64 arbiter's slack (tests/test_gpu_ndiv.py::_grad_close_arbiter), everything else must match
+            x64, z64 = x[0].double(), z[0].double()
+            dx, dz = torch.cdist(x64, x64), torch.cdist(z64, z64)
+            sx64, sz64 = dx.sum(-1, keepdim=True), dz.sum(-1, keepdim=True)
+            h = 0.8 * dz / sz64 - dx / sx64
+            amb = (h.abs() < 4e-6 * (dx / sx64)) & (dx > 0)
+            inv = (1.0 / sx64).expand_as(h)
+            slack = ((amb * inv).sum(-1) + (amb * inv).sum(-2)).to(dev)
+            err = (sg - xg.grad)[0].abs().amax(-1).double()
+            gok = bool((err <= 2e-5 * xg.grad.abs().max().double() + 2 * slack).all())
+            print(f"[rank {rank}]   fused: {int(amb.sum())} ambiguous hinge pairs, rows within arbiter bound: {gok}", flush=True)
+        else:
+            gok = gerr < 1e-5
+        ok &= lerr < 1e-5 and gok and sl2.item() == sl.item() and same_all
         if k >= 256 and Dx <= 32 and not op.fused:   # Gram path, 128-aligned row blocks: same bits as the single-GPU call
             ok &= bit
+    torch.cuda.synchronize()
+    print(f"[rank {rank}] peer window mapped: {comm.peer_status()}", flush=True)
     comm.close()
     t = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
