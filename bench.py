@@ -548,13 +548,20 @@ def run_gpu(args):
         loss.backward()
         return loss
 
-    def time_steps(fn, n):
+    align = torch.zeros(1, device=dev)
+
+    def time_steps(fn, n, aligned=False):
+        """aligned: a device-side all-reduce right before the start event, so that every rank's timed region begins
+        when ALL ranks are ready (a step that exchanges data would otherwise be charged the host-side skew between
+        the ranks' flush + sleep, which has nothing to do with the step)"""
         for _ in range(3):
             fn()
         pairs_ = []
         for _ in range(n):
             flush()
             torch.cuda._sleep(1_000_000)                   # the step's launches are queued before `a` is reached
+            if aligned and world > 1:
+                dist.all_reduce(align)
             a, b = ev(), ev()
             a.record(); fn(); b.record()
             pairs_.append((a, b))
@@ -571,16 +578,19 @@ def run_gpu(args):
         ncomm = sharded.comm if sharded else Comm.solo(dev)
         op = ShardedNdiv(ncomm, NDIV["N"], NDIV["k"], NDIV["Dx"], NDIV["Dz"])
         barrier()
-        sh_ms = maxr(time_steps(lambda: op(x, z), args.steps))
+        sh_ms = maxr(time_steps(lambda: op(x, z), args.steps, aligned=True))
         ndiv_sh = {"ms_per_step": sh_ms, "value": NDIV["N"] * NDIV["k"] ** 2 / (sh_ms * 1e-3), "unit": "ordered pairs/s",
                    "rows_per_rank": op.block, "collectives_per_step": 2, "fused_entry": bool(op.fused),
-                   "how": "ShardedNdiv -> ndp_ndiv_sharded_forward_backward (one C call per rank): pre-pack, pass 1 on "
-                          "the rank's 128-aligned row block writing into its exchange slot -> in-place all-gather "
-                          "[sx|sz] -> pass 2 -> in-place all-gather [grad rows | loss partial] -> unpack; column split "
-                          "sized to the rank's rows; libndivplan's NCCL communicator on the caller's stream"}
+                   "peer_window": bool(ncomm.peer_status()),
+                   "timing": "per step: L2 flush, device-side all-reduce to align the ranks, CUDA events around the call, max over ranks",
+                   "how": "ShardedNdiv -> ndp_ndiv_sharded_forward_backward (one C call per rank, 5 launches): pre-pack, "
+                          "pass 1 on the rank's 128-aligned row block writing into its slot of the peer window, last CTA "
+                          "publishes a flag to every rank -> pull kernel gathers [sx|sz] over NVLink -> pass 2 -> pull "
+                          "kernel gathers [grad rows | loss partial]; column split sized to the rank's rows; no library "
+                          "collective (NCCL all-gathers when the ranks cannot map each other)"}
         op_glue = ShardedNdiv(ncomm, NDIV["N"], NDIV["k"], NDIV["Dx"], NDIV["Dz"], fused=False)
         barrier()
-        glue_ms = maxr(time_steps(lambda: op_glue(x, z), args.steps))
+        glue_ms = maxr(time_steps(lambda: op_glue(x, z), args.steps, aligned=True))
         ndiv_sh["glue_path_ms"] = glue_ms       # the round-2a path: three library calls + torch copies per step
     ndiv_ms = maxr(ndiv_ms)
     # ---- context (rank 0, N=1 only): GAN step, encoder, other precisions, stock PyTorch on the same GPU

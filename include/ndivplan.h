@@ -177,6 +177,16 @@ int ndp_shard_pack(const uint64_t* packed_min, const float* best_action, const i
                    void* stream);
 int ndp_shard_merge(const uint64_t* rec_all, int P, int G, int topk, uint64_t* packed_min, int32_t* best_idx,
                     float* best_action, int32_t* topk_idx, float* topk_cost, int32_t* verified, void* stream);
+/* pack -> exchange -> merge as ONE stream-ordered call on communicator `c` (a collective: every rank calls it once per
+ * plan, in the same order).  Over the peer window (ndp_comm_peer_status) it is two launches and no library collective:
+ * the pack kernel stores the record words straight into EVERY rank's window over NVLink and publishes a flag, the merge
+ * kernel waits (bounded) for every rank's flag and merges from its own window; up to 8 exchanges may be in flight
+ * (PlanRing depth <= 7).  Otherwise: ndp_shard_pack -> ncclAllGather -> ndp_shard_merge through the scratch buffers
+ * rec [G,4+topk] and rec_all [world,G,4+topk] (may be NULL only if the window path is known to be active). */
+int ndp_shard_exchange(ndp_comm* c, const uint64_t* packed_min, const float* best_action, const int32_t* verified,
+                       const int32_t* topk_idx, const float* topk_cost, int G, int topk, uint64_t* rec,
+                       uint64_t* rec_all, uint64_t* out_packed_min, int32_t* out_best_idx, float* out_best_action,
+                       int32_t* out_topk_idx, float* out_topk_cost, int32_t* out_verified, void* stream);
 
 /* ---- normalized diversification loss: replaces diversity.py:8-41 -----------------
  * x = recodes [N,k,Dx] (outputs), z = codes [N,k,Dz] (latents) — argument order of

@@ -52,6 +52,7 @@ _PROTOS = {
     "ndp_gather_best_action": (_i, [_vp, _vp, _i, _i, _i64, _vp, _vp, _vp]),
     "ndp_shard_pack": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp]),
     "ndp_shard_merge": (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "ndp_shard_exchange": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ndp_ndiv_workspace_bytes": (_i, [_i, _i, _i, _i, C.POINTER(_sz)]),
     "ndp_ndiv_rowsums": (_i, [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _sz, _vp]),
     "ndp_ndiv_loss_grad": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _f, _i, _i, _vp, _vp, _vp, _sz, _vp]),

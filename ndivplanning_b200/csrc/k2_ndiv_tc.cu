@@ -885,9 +885,10 @@ static ShardWin shard_win_layout(int B, int Dx, size_t win_bytes) {
   ShardWin w;
   const size_t per_parity = al((size_t)2 * B * 4) + al(((size_t)B * Dx + 1) * 4);
   w.need = 2 * per_parity;
-  // the parity halves split the window's CAPACITY (identical on every rank), not this shape's need, so calls of
-  // different shapes on one communicator never overlap a region a slower peer may still be pulling from
-  w.half = win_bytes > kWinHeader ? ((win_bytes - kWinHeader) / 2) / 256 * 256 : 0;
+  // the ndiv region is the first half of the window's CAPACITY (the second half holds plan records, k3_select.cu);
+  // its parity halves split the capacity (identical on every rank), not this shape's need, so calls of different
+  // shapes on one communicator never overlap a region a slower peer may still be pulling from
+  w.half = win_bytes > kWinHeader ? ((win_bytes - kWinHeader) / 4) / 256 * 256 : 0;
   w.s_off = 0;
   w.g_off = al((size_t)2 * B * 4);
   return w;
@@ -955,7 +956,7 @@ extern "C" int ndp_ndiv_sharded_forward_backward(ndp_comm* c, const float* x, co
   NDP_CUDA(cudaStreamIsCapturing(s, &cap));
   PeerWin pw{};
   if (cap == cudaStreamCaptureStatusNone) {
-    if (int rc = comm_window(c, shard_win_layout(B, Dx, 0).need, s, &pw)) return rc;
+    if (int rc = comm_window(c, 2 * shard_win_layout(B, Dx, 0).need + 4096, s, &pw)) return rc;
   }
   if (pw.world > 0) {
     const ShardWin wl = shard_win_layout(B, Dx, c->win_bytes);

@@ -6,6 +6,7 @@
 // min-allreduce exchanges.  HBM-bound: G*K*4 bytes read once, float4-vectorised.
 #include <stdlib.h>
 #include "common.cuh"
+#include "peer.cuh"
 
 namespace ndp {
 
@@ -808,6 +809,152 @@ extern "C" int ndp_shard_merge(const uint64_t* rec, int P, int G, int topk, uint
       best_idx, best_action, topk_idx, topk_cost, verified);
   NDP_LAUNCH_CHECK();
   return NDP_OK;
+}
+
+// ---------------------------------------------------------------- sharded plan: the exchange as ONE entry point
+// pack -> exchange -> merge.  Over the peer window (peer.cuh) it is two launches and no library collective: the pack
+// kernel stores each record word straight into EVERY rank's window over NVLink and publishes a flag; the merge kernel
+// waits (bounded) for every rank's flag on its own window and merges from local memory.  Records of up to
+// kRecSlots plans may be in flight (slot = sequence number % kRecSlots; a PlanRing of depth d keeps at most d + 1
+// alive).  Ranks that cannot map each other, or a stream under capture, take pack -> ncclAllGather -> merge.
+namespace ndp {
+constexpr int kRecSlots = 8;
+constexpr int kRecFlag0 = 2;                               // flag slots 2 .. 9 (0, 1: the ndiv phases)
+constexpr int kMergeDirect = 256;                          // up to this many keys are merged without shared memory
+struct RecWin { size_t off, slot_bytes; };
+static RecWin rec_win_layout(size_t win_bytes) {           // second half of the window's capacity, kRecSlots slots
+  RecWin r;
+  const size_t cap = win_bytes > kWinHeader ? win_bytes - kWinHeader : 0;
+  r.slot_bytes = (cap / 2 / kRecSlots) / 256 * 256;
+  r.off = kWinHeader + (cap / 2 + 255) / 256 * 256;
+  if (r.off + r.slot_bytes * kRecSlots > win_bytes) r.slot_bytes = r.slot_bytes >= 256 ? r.slot_bytes - 256 : 0;
+  return r;
+}
+
+__global__ void __launch_bounds__(256)
+shard_pack_push_kernel(const unsigned long long* __restrict__ packed_min, const float* __restrict__ best_action,
+                       const int* __restrict__ verified, const int* __restrict__ topk_idx,
+                       const float* __restrict__ topk_cost, int G, int topk, PeerWin w, size_t off, int flag_slot,
+                       unsigned epoch) {
+  const int W = 4 + topk, n = G * W;
+  for (int t = threadIdx.x; t < n; t += blockDim.x) {
+    const int g = t / W, c = t % W;
+    unsigned long long v;
+    if (c == 0) v = packed_min[g];
+    else if (c <= 2) {
+      const float a = best_action[(size_t)g * 4 + (c - 1) * 2], b = best_action[(size_t)g * 4 + (c - 1) * 2 + 1];
+      v = (unsigned long long)__float_as_uint(a) | ((unsigned long long)__float_as_uint(b) << 32);
+    } else if (c == 3) v = verified ? (unsigned long long)(unsigned)verified[g] : 1ull;
+    else {
+      const int i = topk_idx[(size_t)g * topk + c - 4];
+      v = i < 0 ? kPadKey : (((unsigned long long)ordered_key(topk_cost[(size_t)g * topk + c - 4]) << 32) | (unsigned)i);
+    }
+    for (int r = 0; r < w.world; ++r)                      // rank-major [P][G][W] in every rank's window
+      reinterpret_cast<unsigned long long*>(w.peer[r] + off)[(size_t)w.rank * n + t] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) peer_signal_all(w, flag_slot, epoch);
+}
+
+// shard_merge_kernel over the local window after every rank's record has arrived
+__global__ void __launch_bounds__(kSelThreads)
+shard_wait_merge_kernel(PeerWin w, size_t off, int flag_slot, unsigned epoch, int G, int topk,
+                        unsigned long long* __restrict__ packed_min, int* __restrict__ best_idx,
+                        float* __restrict__ best_action, int* __restrict__ topk_idx, float* __restrict__ topk_cost,
+                        int* __restrict__ verified) {
+  // keys staged in (dynamic) shared memory only when there are many (n > kMergeDirect): the bulk rollout leaves
+  // 128 B of shared memory per SM, and a merge block without any can run NEXT to a rollout CTA instead of waiting
+  // for an SM to drain; n <= 256 keys are re-read from the L2-resident window (n^2 / 256 loads per thread)
+  extern __shared__ unsigned long long keys[];
+  const int P = w.world;
+  if ((int)threadIdx.x < P) peer_wait(w, flag_slot, threadIdx.x, epoch);
+  __syncthreads();
+  const unsigned long long* rec = reinterpret_cast<const unsigned long long*>(w.peer[w.rank] + off);
+  const int g = blockIdx.x, W = 4 + topk, n = P * topk;
+  const bool staged = n > kMergeDirect;
+  auto key_at = [&](int i) { return ld_peer_u64(rec + ((size_t)(i / topk) * G + g) * W + 4 + i % topk); };
+  if (staged)
+    for (int i = threadIdx.x; i < n; i += kSelThreads) keys[i] = key_at(i);
+  if (threadIdx.x == 0) {
+    unsigned long long m = kPadKey;
+    int owner = 0, ok = 1;
+    for (int r = 0; r < P; ++r) {                        // strict '<': lowest rank == lowest index range wins ties
+      const unsigned long long* q = rec + ((size_t)r * G + g) * W;
+      const unsigned long long q0 = ld_peer_u64(q);
+      if (q0 < m) { m = q0; owner = r; }
+      ok &= (ld_peer_u64(q + 3) != 0ull) ? 1 : 0;
+    }
+    if (m == kInvalidPacked) owner = 0;                  // nothing valid anywhere: global index 0 (mpc_eval.py:122,159)
+    const unsigned long long q1 = ld_peer_u64(rec + ((size_t)owner * G + g) * W + 1);
+    const unsigned long long q2 = ld_peer_u64(rec + ((size_t)owner * G + g) * W + 2);
+    packed_min[g] = m;
+    if (best_idx) best_idx[g] = (m == kInvalidPacked) ? 0 : (int)(m & 0xFFFFFFFFull);
+    if (best_action) {
+      best_action[(size_t)g * 4 + 0] = __uint_as_float((unsigned)(q1 & 0xFFFFFFFFull));
+      best_action[(size_t)g * 4 + 1] = __uint_as_float((unsigned)(q1 >> 32));
+      best_action[(size_t)g * 4 + 2] = __uint_as_float((unsigned)(q2 & 0xFFFFFFFFull));
+      best_action[(size_t)g * 4 + 3] = __uint_as_float((unsigned)(q2 >> 32));
+    }
+    if (verified) verified[g] = ok;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < n; i += kSelThreads) {
+    const unsigned long long v = staged ? keys[i] : key_at(i);
+    int r = 0;
+    for (int j = 0; j < n; ++j) {
+      const unsigned long long u = staged ? keys[j] : key_at(j);
+      r += (u < v) || (u == v && j < i);
+    }
+    if (r < topk) {
+      topk_idx[(size_t)g * topk + r] = (v == kPadKey) ? -1 : (int)(v & 0xFFFFFFFFull);
+      topk_cost[(size_t)g * topk + r] = (v == kPadKey) ? __int_as_float(0x7fc00000) : key_to_float((uint32_t)(v >> 32));
+    }
+  }
+}
+}  // namespace ndp
+
+extern "C" int ndp_shard_exchange(ndp_comm* c, const uint64_t* packed_min, const float* best_action,
+                                  const int32_t* verified, const int32_t* topk_idx, const float* topk_cost, int G,
+                                  int topk, uint64_t* rec, uint64_t* rec_all, uint64_t* out_packed_min,
+                                  int32_t* out_best_idx, float* out_best_action, int32_t* out_topk_idx,
+                                  float* out_topk_cost, int32_t* out_verified, void* stream) {
+  NDP_CHECK_ARG(c && G >= 0 && topk >= 0 && topk <= 128, "shard_exchange: bad communicator/G/topk");
+  const int P = ndp_comm_world(c);
+  NDP_CHECK_ARG((long long)P * topk <= kSelTile, "shard_exchange: need world*topk <= 1024 (world=%d topk=%d)", P, topk);
+  if (int rc = device_check()) return rc;
+  if (G == 0) return NDP_OK;
+  NDP_CHECK_ARG(packed_min && best_action && out_packed_min && (topk == 0 || (topk_idx && topk_cost && out_topk_idx && out_topk_cost)),
+                "shard_exchange: null pointer");
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t rec_bytes = (size_t)G * (4 + topk) * 8;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  NDP_CUDA(cudaStreamIsCapturing(s, &cap));
+  PeerWin pw{};
+  if (cap == cudaStreamCaptureStatusNone) {
+    // the record region is half of the window's capacity in kRecSlots slots of [world][G][W] words
+    if (int rc = comm_window(c, 2 * kRecSlots * ((size_t)P * rec_bytes + 512), s, &pw)) return rc;
+  }
+  if (pw.world > 0) {
+    const RecWin rl = rec_win_layout(c->win_bytes);
+    if (rl.slot_bytes < (size_t)P * rec_bytes) { set_error("shard_exchange: window slot %zu < %zu", rl.slot_bytes, (size_t)P * rec_bytes); return NDP_ERR_WORKSPACE; }
+    const unsigned epoch = ++c->epoch_rec;
+    const int slot = (int)(epoch % kRecSlots);
+    const size_t off = rl.off + (size_t)slot * rl.slot_bytes;
+    shard_pack_push_kernel<<<1, 256, 0, s>>>(reinterpret_cast<const unsigned long long*>(packed_min), best_action, verified,
+                                              topk_idx, topk_cost, G, topk, pw, off, kRecFlag0 + slot, epoch);
+    NDP_LAUNCH_CHECK();
+    const int nk = P * topk;
+    shard_wait_merge_kernel<<<G, kSelThreads, nk > kMergeDirect ? (size_t)nk * 8 : 0, s>>>(pw, off, kRecFlag0 + slot, epoch, G, topk,
+                                                      reinterpret_cast<unsigned long long*>(out_packed_min), out_best_idx,
+                                                      out_best_action, out_topk_idx, out_topk_cost, out_verified);
+    NDP_LAUNCH_CHECK();
+    return NDP_OK;
+  }
+  NDP_CHECK_ARG(rec && rec_all, "shard_exchange: rec / rec_all scratch needed for the NCCL path");
+  if (int rc = ndp_shard_pack(packed_min, best_action, verified, topk_idx, topk_cost, G, topk, rec, stream)) return rc;
+  if (int rc = ndp_comm_allgather_bytes(c, rec, rec_all, rec_bytes, stream)) return rc;
+  return ndp_shard_merge(rec_all, P, G, topk, out_packed_min, out_best_idx, out_best_action, out_topk_idx, out_topk_cost,
+                         out_verified, stream);
 }
 
 extern "C" int ndp_gather_best_action(const float* a0, const uint64_t* packed_min, int G, int K,

@@ -4,7 +4,7 @@
 //
 //   window = [ header 4 KB : flags[kWinSlots][kMaxPeers] u32 | error word ] [ payload ]
 //
-// Protocol ("epochs"): every collective entry point bumps the communicator's epoch on the host (all ranks make the
+// Protocol ("epochs"): every collective entry point bumps its sequence number ("epoch") on the host (all ranks make the
 // same calls in the same order, like any collective).  A producer finishes its stores, fences at system scope and
 // stores the epoch into flags[slot][its rank] of EVERY rank's window; a consumer spins on its OWN window's flag
 // (local memory) until it reaches the epoch, then reads the producer's payload through the mapped pointer.  Spins are
@@ -86,7 +86,8 @@ struct ndp_comm {
   char* win;                       // this rank's window (cudaMalloc), nullptr until first use
   char* peer[ndp::kMaxPeers];      // mapped windows (peer[rank] == win)
   size_t win_bytes;                // header + payload
-  unsigned epoch;                  // bumped by every windowed collective entry point
+  unsigned epoch;                  // sequence number of the windowed ndiv calls (payload parity = epoch & 1)
+  unsigned epoch_rec;              // sequence number of the windowed plan-record exchanges (slot = epoch % 8)
   int win_state;                   // 0 = untried, 1 = mapped, -1 = peers not reachable (callers use NCCL)
 };
 

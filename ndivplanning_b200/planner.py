@@ -249,7 +249,7 @@ class FusedPlanner:
 
 class _Slot:
     __slots__ = ("cost", "a0", "packed", "tk_idx", "tk_cost", "verified", "ws", "best_action", "best_idx", "ready",
-                 "bulk_done", "inputs", "used", "tail", "gather", "plan", "rec", "rec_all", "pack", "merge", "head", "side")
+                 "bulk_done", "inputs", "used", "tail", "gather", "plan", "rec", "rec_all", "exch", "head", "side")
 
 
 class PlanRing:
@@ -285,6 +285,8 @@ class PlanRing:
         world = comm.world if comm is not None else 1
         if world * topk > 1024:
             raise _lib.NdpError("sharded top-k needs world*topk <= 1024")
+        if comm is not None and depth > 7:
+            raise _lib.NdpError("a sharded ring keeps depth + 1 record exchanges in flight: depth <= 7")
         self.slots = []
         f32, i32, i64 = torch.float32, torch.int32, torch.int64
         for _ in range(depth):
@@ -313,10 +315,10 @@ class PlanRing:
                 g_act, g_ver = torch.empty(G, 4, dtype=f32, device=dev), torch.empty(G, dtype=i32, device=dev)
                 g_tki = torch.empty(G, topk, dtype=i32, device=dev) if topk else None
                 g_tkc = torch.empty(G, topk, dtype=f32, device=dev) if topk else None
-                s.pack = (ptr(s.packed), ptr(s.best_action), ptr(s.verified), ptr(s.tk_idx), ptr(s.tk_cost), G, topk,
-                          ptr(s.rec))
-                s.merge = (ptr(s.rec_all), world, G, topk, ptr(g_packed), ptr(g_idx), ptr(g_act), ptr(g_tki),
-                           ptr(g_tkc), ptr(g_ver))
+                # ndp_shard_exchange: pack -> exchange (peer window over NVLink, or ncclAllGather) -> merge
+                s.exch = (ptr(s.packed), ptr(s.best_action), ptr(s.verified), ptr(s.tk_idx), ptr(s.tk_cost), G, topk,
+                          ptr(s.rec), ptr(s.rec_all), ptr(g_packed), ptr(g_idx), ptr(g_act), ptr(g_tki), ptr(g_tkc),
+                          ptr(g_ver))
                 s.plan = Plan(g_idx, g_act, g_packed, s.cost, s.a0, g_tki, g_tkc, None, g_ver, s.ready)
             self.slots.append(s)
 
@@ -364,9 +366,7 @@ class PlanRing:
                 check(L.ndp_plan_fallback(*head, *s.tail, sp))
             check(L.ndp_gather_best_action(*s.gather, sp))
             if self.comm is not None:
-                check(L.ndp_shard_pack(*s.pack, sp))
-                check(L.ndp_comm_allgather_bytes(self.comm._h, ptr(s.rec), ptr(s.rec_all), s.rec.numel() * 8, sp))
-                check(L.ndp_shard_merge(*s.merge, sp))
+                check(L.ndp_shard_exchange(self.comm._h, *s.exch, sp))
             if self.vlog is not None:
                 with torch.cuda.stream(side):
                     self.vlog[(i - self.vlog_base) % self.vlog.shape[0]].copy_(s.plan.verified, non_blocking=True)

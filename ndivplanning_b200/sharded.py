@@ -154,10 +154,31 @@ def merge_records(rec_all: torch.Tensor, topk: int):
     return packed, best_idx, best_action, tk_idx, tk_cost, verified
 
 
+def exchange_plan(p: Plan, topk: int, comm: "Comm"):
+    """local plan -> global plan on the current stream through ndp_shard_exchange (ONE library call: pack, exchange
+    over the peer window — or ncclAllGather — and merge).  Same results as pack_records -> exchange_records ->
+    merge_records."""
+    G = p.packed_min.shape[0]
+    dev, W, P = p.packed_min.device, 4 + topk, comm.world
+    i64, i32, f32 = torch.int64, torch.int32, torch.float32
+    rec = torch.empty(G, W, dtype=i64, device=dev)
+    rec_all = torch.empty(P, G, W, dtype=i64, device=dev)
+    packed, best_idx = torch.empty(G, dtype=i64, device=dev), torch.empty(G, dtype=i32, device=dev)
+    best_action, verified = torch.empty(G, 4, dtype=f32, device=dev), torch.empty(G, dtype=i32, device=dev)
+    tk_idx = torch.empty(G, topk, dtype=i32, device=dev) if topk else None
+    tk_cost = torch.empty(G, topk, dtype=f32, device=dev) if topk else None
+    with torch.cuda.device(dev):
+        check(lib().ndp_shard_exchange(comm._h, ptr(p.packed_min), ptr(p.best_action), ptr(p.verified), ptr(p.topk_idx),
+                                       ptr(p.topk_cost), G, topk, ptr(rec), ptr(rec_all), ptr(packed), ptr(best_idx),
+                                       ptr(best_action), ptr(tk_idx), ptr(tk_cost), ptr(verified), stream_ptr(dev)))
+    return packed, best_idx, best_action, tk_idx, tk_cost, verified
+
+
 class ShardedPlanner:
     """Candidate-sharded planning: every rank holds the weights, e0 and goal; noise is per shard.
-    Per plan: local K1/K3 (+refine), ndp_shard_pack, ONE all-gather of (4+topk)*8 bytes per goal and
-    rank, ndp_shard_merge.  With `refine_stream` the refine half, the exchange and the merge all run
+    Per plan: local K1/K3 (+refine), then ndp_shard_exchange: the pack kernel stores the (4+topk)*8-byte record per goal
+    into every rank's peer window over NVLink, the merge kernel waits for every rank's flag (ncclAllGather between
+    ndp_shard_pack and ndp_shard_merge when the ranks cannot map each other).  With `refine_stream` the refine half, the exchange and the merge all run
     on that stream under the bulk rollout of the next plan (Plan.ready / Plan.wait())."""
 
     def __init__(self, planner: FusedPlanner, group=None):
@@ -180,8 +201,7 @@ class ShardedPlanner:
         dev = p.cost.device
         side = refine_stream if p.ready is not None else None
         with torch.cuda.stream(side if side is not None else torch.cuda.current_stream(dev)):
-            rec_all = exchange_records(pack_records(p, topk), self.group, self.comm)
-            packed, best_idx, best_action, tk_idx, tk_cost, verified = merge_records(rec_all, topk)
+            packed, best_idx, best_action, tk_idx, tk_cost, verified = exchange_plan(p, topk, self.comm)
             ready = None
             if side is not None:
                 ready = torch.cuda.Event()
