@@ -683,7 +683,8 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
         if (ii >= p.row0 && ii < iend) {
           const size_t off = ((size_t)n * p.k + ii) * p.Dx + dim;
           float a = 0.f;
-          for (int s = 0; s < p.JS; ++s) a += __ldcg(p.gpart + (size_t)s * N * p.k * p.Dx + off);
+#pragma unroll 8
+          for (int s = 0; s < p.JS; ++s) a += __ldcg(p.gpart + (size_t)s * N * p.k * p.Dx + off);   // fixed split order
           p.grad[off] = a;
         }
       }
@@ -830,12 +831,13 @@ int gram_loss_grad(const float* x, const float* z, const float* sx, const float*
 // write straight into the rank's slot of the exchange buffers (pointer offsets), two tiny kernels unpack.  The column
 // split adapts to the rows of the CALL (a rank with 1/P of the rows still fills the GPU), so results equal the
 // single-GPU call to fp32 round-off of the split order, not bit for bit; they are identical on every rank.
+constexpr int kShardMaxJS = 32;
 static GramPlan gram_plan_rows(int k, int row_tiles) {
   GramPlan g;
   g.tiles = (k + kGT - 1) / kGT;
   long long want = (148 * 2) / (long long)(row_tiles > 0 ? row_tiles : 1);
   if (want < 1) want = 1;
-  if (want > 16) want = 16;                              // bounds the partial buffers
+  if (want > kShardMaxJS) want = kShardMaxJS;            // bounds the partial buffers
   if (want > g.tiles) want = g.tiles;
   g.tps = (int)((g.tiles + want - 1) / want);
   g.JS = (g.tiles + g.tps - 1) / g.tps;
@@ -849,8 +851,8 @@ static ShardWs shard_ws_layout(int k, int Dx, int Dz, int world) {
   const size_t tiles = (size_t)(k + kGT - 1) / kGT;
   w.gram = 0;
   w.part = al(gram_ws_bytes(1, k, Dx, Dz));
-  w.psum = w.part + al(16 * tiles * sizeof(float));
-  const size_t ps = (size_t)2 * 16 * k * sizeof(float), gp = (size_t)16 * k * Dx * sizeof(float);
+  w.psum = w.part + al(kShardMaxJS * tiles * sizeof(float));
+  const size_t ps = (size_t)2 * kShardMaxJS * k * sizeof(float), gp = (size_t)kShardMaxJS * k * Dx * sizeof(float);
   w.st_s = w.psum + al(ps > gp ? ps : gp);
   w.st_g = w.st_s + al((size_t)world * 2 * w.B * sizeof(float));
   w.total = w.st_g + al((size_t)world * ((size_t)w.B * Dx + 1) * sizeof(float));
