@@ -388,6 +388,15 @@ __device__ __forceinline__ void gram_chunk(RowState<PASS2>& st, const uint32_t (
   }
 }
 
+#ifdef NDP_TC_PROF
+// dev build: per-CTA phase clocks of thread 0, summed over CTAs ([pass][0] CTAs, [1] prologue, [2] first operands
+// landed, [3] main loop, [4] per-CTA results + row-tile reduction, [5] grid tail) and the max over CTAs of the total [6]
+__device__ unsigned long long g_gram_prof[2][8];
+#define GPROF(k_) do { if (tid == 0) { const long long c_ = clock64(); atomicAdd(&g_gram_prof[PASS2][k_], (unsigned long long)(c_ - gp_last)); gp_last = c_; } } while (0)
+#else
+#define GPROF(k_) do { } while (0)
+#endif
+
 // grid (row tiles of the call, JS, N), 256 threads, 2 CTAs / SM
 template <bool PASS2>
 __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) {
@@ -400,6 +409,11 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
   const int jt0 = js * p.tps, jt1 = (jt0 + p.tps) < p.tiles ? (jt0 + p.tps) : p.tiles;
   const int ntl = jt1 - jt0;
   const bool grad = PASS2 && p.grad != nullptr;
+#ifdef NDP_TC_PROF
+  const long long gp_begin = clock64();
+  long long gp_last = gp_begin;
+  if (tid == 0) atomicAdd(&g_gram_prof[PASS2][0], 1ull);
+#endif
 
   // shared memory: A image | 2 x { B image, norms, [XT] } | srx, srz | sred | slos | barriers
   const uint32_t buf_bytes = (uint32_t)gd.img_bytes + kNormBytes + (PASS2 ? (uint32_t)kXTBytes : 0u);
@@ -478,6 +492,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
   for (int d = 0; d < 16; ++d) g[d] = 0.f;
   if (PASS2 && hf == 0 && ivalid) st.lsum = nanprobe;
   const bool rows_full = itile * kGT >= p.row0 && itile * kGT + kGT <= iend;
+  GPROF(1);
 
   for (int t = 0; t < ntl; ++t) {
     const int jt = jt0 + t, j0 = jt * kGT;
@@ -517,6 +532,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       __syncwarp();
     }
     mbar_wait(bar_full, phf);                          // norms landed (every thread reads them)
+    if (t == 0) GPROF(2);
     __syncthreads();                                   // srx / srz visible
     mbar_wait(bar_d, ph);
     fence_after_sync();
@@ -590,6 +606,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
     if (tid == 0 && t + 2 < ntl) issue_tile(t + 2);    // lands under the whole of tile t+1
   }
 
+  GPROF(3);
   // ---- per-CTA results, then the LAST CTA of the row tile combines the column splits in fixed order
   const size_t tk_row = (size_t)(PASS2 ? N * p.tiles : 0) + (size_t)n * p.tiles + itile;
   if (!PASS2) {
@@ -614,6 +631,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
           const int ii = itile * kGT + tid;
           if (ii >= p.row0 && ii < iend) {
             float a = 0.f, b = 0.f;
+#pragma unroll 8
             for (int s = 0; s < p.JS; ++s) {
               const size_t o = ((size_t)s * N + n) * p.k + ii;
               a += __ldcg(p.psx + o); b += __ldcg(p.psz + o);
@@ -623,6 +641,7 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
         }
       }
     }
+    GPROF(4);
     if (p.pw.world > 0) {                                  // sharded: the grid's last CTA signals every rank
       __threadfence();
       __syncthreads();
@@ -678,18 +697,44 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
     if (grad && p.JS > 1 && s_ticket[0] == (unsigned)(p.JS - 1)) {
       __threadfence();
       const int r0c = itile * kGT;
-      for (int e = tid; e < kGT * p.Dx; e += kGNT) {
-        const int ii = r0c + e / p.Dx, dim = e % p.Dx;
-        if (ii >= p.row0 && ii < iend) {
-          const size_t off = ((size_t)n * p.k + ii) * p.Dx + dim;
-          float a = 0.f;
+      const size_t split = (size_t)N * p.k * p.Dx;                    // floats between two column splits' partials
+      const size_t tile_off = ((size_t)n * p.k + r0c) * p.Dx;
+      const float* __restrict__ gp = p.gpart + tile_off;
+      float* __restrict__ go = p.grad + tile_off;
+      if ((reinterpret_cast<uintptr_t>(go) & 15) == 0) {
+        // 128-bit loads, eight splits in flight per element group: this tail is latency-bound (JS x 16 KB read by ONE
+        // CTA while the others have left) and was the largest fixed cost of the pass (profiles/r02_summary.md)
+        const int nv = kGT * p.Dx / 4;                                // Dx % 4 == 0
+#pragma unroll 2
+        for (int e4 = tid; e4 < nv; e4 += kGNT) {
+          const int ii = r0c + (e4 * 4) / p.Dx;
+          if (ii < p.row0 || ii >= iend) continue;
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int s0 = 0; s0 < p.JS; s0 += 8) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+              if (s0 + u < p.JS) v[u] = __ldcg(reinterpret_cast<const float4*>(gp + (size_t)(s0 + u) * split) + e4);
+#pragma unroll
+            for (int u = 0; u < 8; ++u)                               // fixed split order
+              if (s0 + u < p.JS) { a.x += v[u].x; a.y += v[u].y; a.z += v[u].z; a.w += v[u].w; }
+          }
+          reinterpret_cast<float4*>(go)[e4] = a;
+        }
+      } else {
+        for (int e = tid; e < kGT * p.Dx; e += kGNT) {
+          const int ii = r0c + e / p.Dx;
+          if (ii >= p.row0 && ii < iend) {
+            float a = 0.f;
 #pragma unroll 8
-          for (int s = 0; s < p.JS; ++s) a += __ldcg(p.gpart + (size_t)s * N * p.k * p.Dx + off);   // fixed split order
-          p.grad[off] = a;
+            for (int s = 0; s < p.JS; ++s) a += __ldcg(gp + (size_t)s * split + e);   // fixed split order
+            go[e] = a;
+          }
         }
       }
       __threadfence();
     }
+    GPROF(4);
     // grid ticket AFTER this CTA's last global write (the combined gradient rows above), so that whoever draws the
     // last ticket may publish the whole call's results
     __syncthreads();
@@ -714,6 +759,10 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       }
     }
   }
+  GPROF(5);
+#ifdef NDP_TC_PROF
+  if (tid == 0) atomicMax(&g_gram_prof[PASS2][6], (unsigned long long)(clock64() - gp_begin));
+#endif
   fence_before_sync();
   __syncthreads();
   if (warp == 0) tmem_dealloc256(tmem);
@@ -926,6 +975,14 @@ __global__ void ndiv_pull_g_kernel(PeerWin w, size_t off, unsigned epoch, int B,
 }  // namespace ndp
 
 using namespace ndp;
+#ifdef NDP_TC_PROF
+extern "C" int ndp_debug_gram_prof(unsigned long long* out16, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out16, g_gram_prof, sizeof(unsigned long long) * 16);
+  if (reset) { unsigned long long z[16] = {}; cudaMemcpyToSymbol(g_gram_prof, z, sizeof(z)); }
+  return NDP_OK;
+}
+#endif
 extern "C" int ndp_ndiv_sharded_workspace_bytes(int k, int Dx, int Dz, int world, size_t* bytes) {
   NDP_CHECK_ARG(bytes && k >= 1 && Dx >= 1 && Dz >= 1 && world >= 1, "ndiv_sharded: bad arguments");
   *bytes = shard_ws_layout(k, Dx, Dz, world).total;

@@ -112,3 +112,36 @@ def test_shard_records_merge_equals_global_selection(cuda, P, G, K, topk):
             assert torch.equal(torch.nan_to_num(tk_cost[g, :kk].cpu(), nan=-7.0), torch.nan_to_num(cost[g][wt], nan=-7.0))
             assert (tk_idx[g, kk:] == -1).all()
     assert verified.cpu().tolist() == [0 if P > 1 else 1] * G
+
+
+@pytest.mark.parametrize("G,K,topk", [(3, 1001, 8), (1, 65536, 16), (5, 64, 0), (2, 300, 128)])
+def test_shard_exchange_entry_world1(cuda, G, K, topk):
+    """ndp_shard_exchange on a world-size-1 communicator runs the peer-window kernels (pack+push into the window,
+    wait+merge from it) exactly as an N-rank call does: the global plan must equal the local one, over several
+    back-to-back exchanges (slot reuse after 8)"""
+    from ndivplanning_b200 import select_plan
+    from ndivplanning_b200.planner import Plan
+    from ndivplanning_b200.sharded import Comm, exchange_plan, merge_records, pack_records
+    comm = Comm.solo("cuda:0")
+    try:
+        for it in range(11):
+            torch.manual_seed(G * 1000 + K + it)
+            cost = torch.rand(G, K)
+            if G > 1 and it % 2:
+                cost[1, :] = float("nan")
+            loc = cost.cuda()
+            packed, tk_idx, tk_cost = select_plan(loc, topk, 0)
+            act = torch.randn(G, 4).cuda()
+            ver = torch.randint(0, 2, (G,), dtype=torch.int32).cuda()
+            p = Plan(None, act, packed, loc, None, tk_idx, tk_cost, None, ver)
+            got = exchange_plan(p, topk, comm)
+            want = merge_records(pack_records(p, topk).unsqueeze(0).contiguous(), topk)
+            for a, b in zip(got, want):
+                if a is None:
+                    assert b is None
+                else:
+                    assert torch.equal(torch.nan_to_num(a.float(), nan=-7.0) if a.is_floating_point() else a,
+                                       torch.nan_to_num(b.float(), nan=-7.0) if b.is_floating_point() else b)
+        assert comm.peer_status() is True
+    finally:
+        comm.close()

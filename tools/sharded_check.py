@@ -49,6 +49,36 @@ def main():
         print(f"[rank {rank}] {prec} G={G} K={K} topk={topk}: sharded==single {same} best={sp.best_idx.tolist()} "
               f"verified={sp.verified.tolist()}", flush=True)
         ok &= same
+    # ---- record exchange under skew: 24 pipelined plans on a depth-4 ring, a different rank delayed before every plan
+    # (the peer window keeps up to 8 exchanges in flight by sequence number; a late or early rank must never be merged
+    # with another plan's records)
+    gen, fwd = synthetic.make_models(nd=2, E=128, H=256)
+    pl = FusedPlanner(gen, fwd, horizon=4, device=dev, precision="f16+refine")
+    G, K, topk = 2, 8192, 16
+    start, count = shard_range(K, rank, world)
+    sp_ = ShardedPlanner(pl)
+    ring = sp_.ring(G, K, topk, depth=4)
+    wants, gots = [], []
+    for i in range(24):
+        e0, goal, noise = synthetic.make_plan_inputs(G, K, 4, 2, 128, seed=100 + i)
+        full = pl.plan(e0.to(dev), goal.to(dev), noise.to(dev), topk=topk)
+        wants.append((full.best_idx.clone(), full.best_action.clone(), full.topk_idx.clone()))
+        if i % world == rank:
+            torch.cuda._sleep(4_000_000)
+        rp = ring.plan(e0.to(dev), goal.to(dev), noise[:, :, start:start + count].contiguous().to(dev))
+        if i % 3 == 2:                               # consume in bursts: several exchanges stay in flight
+            rp.wait()
+        gots.append(rp)
+        if len(gots) >= 3:                           # a ring plan is valid until depth-1 further plans were issued
+            g_ = gots[-3]
+            g_.wait()
+            w_ = wants[len(gots) - 3]
+            skew_ok = torch.equal(g_.best_idx, w_[0]) and torch.equal(g_.best_action, w_[1]) and torch.equal(g_.topk_idx, w_[2])
+            ok &= skew_ok
+            if not skew_ok:
+                print(f"[rank {rank}] skewed ring: plan {len(gots) - 3} differs from the single-GPU plan", flush=True)
+    torch.cuda.synchronize()
+    print(f"[rank {rank}] skewed ring of 24 plans: ok={ok} peer window {sp_.comm.peer_status()}", flush=True)
     comm = Comm(dev)
     for (N, k, Dx, Dz, fused) in ((2, 1000, 32, 16, None), (1, 4096, 32, 16, False), (1, 4096, 32, 16, True),
                                   (1, 2000, 8, 16, True), (3, 200, 12, 5, None)):
