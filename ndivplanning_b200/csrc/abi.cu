@@ -255,14 +255,17 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
 extern "C" int ndp_planner_workspace_bytes(const ndp_planner* p, int G, int K, size_t* bytes) {
   NDP_CHECK_ARG(p && bytes && G >= 0 && K >= 0, "planner_workspace_bytes: bad arguments");
   *bytes = (size_t)(G > 0 ? G : 1) * 128 * sizeof(float) + 256;
-  if (p->tc) { const size_t t = tc_workspace_bytes(p->tc, G); if (t > *bytes) *bytes = t; }
-  if (p->tc_refine) { const size_t t = tc_workspace_bytes(p->tc_refine, G); if (t > *bytes) *bytes = t; }
+  if (p->tc) { const size_t t = tc_workspace_bytes(p->tc, G, K); if (t > *bytes) *bytes = t; }
+  if (p->tc_refine) { const size_t t = tc_workspace_bytes(p->tc_refine, G, K); if (t > *bytes) *bytes = t; }
   return NDP_OK;
 }
 
-extern "C" int ndp_rollout_score(ndp_planner* p, const float* e0, const float* goal, const float* noise,
-                                 int G, int K, float* cost, float* a0, float* state_T,
-                                 void* ws, size_t ws_bytes, void* stream) {
+// balance: split the pairs of the two-tile kernel's last waves in time (k1_rollout_tc.cu: t2_split).  It shortens a
+// rollout that has the GPU to itself (3 % at cfg2) and costs as much when the tail would have been filled by the next
+// plan's CTAs anyway, so the pipelined entry (ndp_plan_select_bulk, PlanRing) leaves it off.
+static int rollout_score_impl(ndp_planner* p, const float* e0, const float* goal, const float* noise,
+                              int G, int K, float* cost, float* a0, float* state_T,
+                              void* ws, size_t ws_bytes, void* stream, bool balance) {
   NDP_CHECK_ARG(p && p->loaded, "rollout_score: planner has no weights (call ndp_planner_load)");
   NDP_CHECK_ARG(G >= 0 && K >= 0, "rollout_score: bad G/K");
   if (int rc = device_check()) return rc;
@@ -270,7 +273,8 @@ extern "C" int ndp_rollout_score(ndp_planner* p, const float* e0, const float* g
   NDP_CHECK_ARG(e0 && goal && cost && a0, "rollout_score: null tensor");
   NDP_CHECK_ARG(noise || p->d.nd == 0, "rollout_score: noise is required (noise_dim=%d)", p->d.nd);
   if (p->tc)
-    return launch_rollout_tc(p->tc, e0, goal, noise, G, K, p->d.T, cost, a0, state_T, ws, ws_bytes, (cudaStream_t)stream);
+    return launch_rollout_tc(p->tc, e0, goal, noise, G, K, p->d.T, cost, a0, state_T, ws, ws_bytes, (cudaStream_t)stream,
+                             nullptr, 0, nullptr, nullptr, balance);
   const size_t need = (size_t)G * 128 * sizeof(float);
   if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
   const long long tiles = (long long)G * ((K + 127) / 128);
@@ -286,6 +290,12 @@ extern "C" int ndp_rollout_score(ndp_planner* p, const float* e0, const float* g
   rp.G = G; rp.K = K; rp.T = p->d.T; rp.nd = p->d.nd; rp.H = p->d.H;
   rp.tiles_per_goal = (K + 127) / 128; rp.nq = p->nq;
   return launch_rollout_f32(rp, s);
+}
+
+extern "C" int ndp_rollout_score(ndp_planner* p, const float* e0, const float* goal, const float* noise,
+                                 int G, int K, float* cost, float* a0, float* state_T,
+                                 void* ws, size_t ws_bytes, void* stream) {
+  return rollout_score_impl(p, e0, goal, noise, G, K, cost, a0, state_T, ws, ws_bytes, stream, true);
 }
 
 // handle-owned activation scratch of the single-call entry points (grown on demand).  One planner handle must not be
@@ -405,7 +415,8 @@ static int plan_select_impl(int phase, ndp_planner* p, const float* e0, const fl
   unsigned long long* pm_est = packed_c + (size_t)G * R;
   float* margin = reinterpret_cast<float*>(base + w.rollout + w.select + w.list + w.est + w.packed);
   if (phase & 1) {
-    if (int rc = ndp_rollout_score(p, e0, goal, noise, G, K, cost, a0, nullptr, ws_roll, w.rollout, stream)) return rc;
+    if (int rc = rollout_score_impl(p, e0, goal, noise, G, K, cost, a0, nullptr, ws_roll, w.rollout, stream,
+                                    /*balance=*/phase != 1)) return rc;
     if (!p->tc_refine) {
       if (int rc = ndp_select(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws_sel, w.select, stream)) return rc;
       if (verified)   // K=0 <= R marks every goal verified: nothing was estimated

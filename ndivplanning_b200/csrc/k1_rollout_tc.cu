@@ -79,9 +79,12 @@ __global__ void tc_pack_ext_kernel(__half* __restrict__ hi, __half* __restrict__
 // mpc_eval.py:133,136-138).  One block per goal, one warp per output row.
 __global__ void tc_goal_ext_kernel(const float* __restrict__ W1, const float* __restrict__ b1,
                                    const float* __restrict__ goal, int E, int nd, int with_lo,
-                                   __half* __restrict__ gext, size_t stride_halfs) {
+                                   __half* __restrict__ gext, size_t stride_halfs,
+                                   unsigned* __restrict__ clear_flags, int n_flags) {
   const int g = blockIdx.x;
   const int lane = threadIdx.x & 31;
+  if (blockIdx.x == 0 && blockIdx.y == 0)                  // hand-over flags of the split pairs (two-tile kernel)
+    for (int i = threadIdx.x; i < n_flags; i += blockDim.x) clear_flags[i] = 0u;
   const int C1 = 2 * E + nd;
   __half* hi = gext + (size_t)g * stride_halfs;
   __half* lo = with_lo ? hi + 128 * 16 : nullptr;
@@ -823,8 +826,23 @@ __device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
 __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int g = blockIdx.x / p.tiles_per_goal;                  // tiles_per_goal counts tile PAIRS here
-  const int pair = blockIdx.x % p.tiles_per_goal;
+  // ---- job of this CTA: a tile pair and a step range [t0, t1).  Without a split (p.sp_n == 0) CTA b rolls pair b over
+  // all T steps.  With one, the pairs of the last two waves are laid out so that the SMs finish together instead of
+  // leaving the last wave partly empty (t2_split() below): CTAs are dispatched in index order, one per SM —
+  //   [base full pairs] [A: n full pairs] [n first pieces, steps [0,a)] [H full pairs] [n continuations, steps [a,T)]
+  // the H "helper" SMs run the first pieces of the n split pairs BEFORE their own full pair; the n other SMs append
+  // a continuation to theirs.  A first piece leaves the pair's state images (the fp16 hi/lo split the next step
+  // would read anyway: bit-identical to the unsplit roll) in global scratch and raises a flag per tile.
+  int job = blockIdx.x, t0 = 0, t1 = p.T, sp_id = -1;
+  if (p.sp_n > 0 && job >= p.sp_base) {
+    const int b = job - p.sp_base, n = p.sp_n;
+    if (b < n) job = p.sp_base + b;
+    else if (b < 2 * n) { sp_id = b - n; job = p.sp_base + n + sp_id; t1 = p.sp_a; }
+    else if (b < 2 * n + p.sp_h) job = p.sp_base + 2 * n + (b - 2 * n);
+    else { sp_id = b - 2 * n - p.sp_h; job = p.sp_base + n + sp_id; t0 = p.sp_a; }
+  }
+  const int g = job / p.tiles_per_goal;                         // tiles_per_goal counts tile PAIRS here
+  const int pair = job % p.tiles_per_goal;
 
   uint8_t* ext_base = smem + kT2OffExt;                         // noise0, noise1 (4 KB each), act0, act1, ones, zeros (2 KB each)
   uint8_t* ext_actb = ext_base + 2 * kExtSlab;
@@ -861,7 +879,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     if (lane == 0) {
       uint32_t it = 0;
       const uint8_t* gsrc = p.gext + (size_t)g * p.gext_stride;
-      for (int t = 0; t < p.T; ++t) {
+      for (int t = t0; t < t1; ++t) {
         for (int i = 0; i < p.n_items; ++i, ++it) {
           const uint32_t slot = it % kT2NSlot, par = (it / kT2NSlot) & 1;
           const uint32_t bytes = items[3 * i + 1], eb = items[3 * i + 2];
@@ -944,7 +962,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       if (SIGNAL) ++ds[tl];                                                                                 \
     }                                                                                                       \
     advance(2);
-    for (int t = 0; t < p.T; ++t) {
+    for (int t = t0; t < t1; ++t) {
       // ---- generator fc1: state slabs 0..3, then 4..7 + [noise | per-goal bias]  -> P
       T2_GEMM2(128, 1, 1, kT2P, 0, 4, 1, true, true)
       // ---- fc2 (N = 64, one item): A1 = Q[0,64) -> P[0,64)
@@ -1109,17 +1127,36 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       *reinterpret_cast<uint4*>(SH + kc * 2048) = hv;
       *reinterpret_cast<uint4*>(SL + kc * 2048) = lv;
     };
-    // ---- init: state <- e0 (this thread: k in [64h, 64h+64)), noise ext of step 0
+    // ---- init: state <- e0 (this thread: k in [64h, 64h+64)) or the images a first piece left; noise ext of step t0
+    const int tt = (warp & 7) * 32 + lane;                      // thread of the tile (256)
+    auto tile_bar = [&]() {
+      if (tile == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
+      else asm volatile("bar.sync 2, 256;" ::: "memory");
+    };
+    if (t0 == 0) {
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + 2 * c);
-      const float4 b = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + 2 * c + 1);
-      const float s8[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-      put_state8(8 * h + c, s8);
+      for (int c = 0; c < 8; ++c) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + 2 * c);
+        const float4 b = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + 2 * c + 1);
+        const float s8[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        put_state8(8 * h + c, s8);
+      }
+    } else {
+      // continuation: wait (bounded) for the first piece of this tile, then copy its 64 KB of state images back
+      unsigned* flag = p.sp_flags + 2 * sp_id + tile;
+      if (tt == 0) {
+        const long long c0 = clock64();
+        while (ld_acquire_gpu(flag) == 0u && clock64() - c0 < 4000000000ll) __nanosleep(128);
+      }
+      tile_bar();
+      const uint4* src = reinterpret_cast<const uint4*>(p.sp_state + ((size_t)sp_id * 2 + tile) * 65536);
+      uint4* dst = reinterpret_cast<uint4*>(smem + kT2OffState + tile * 65536);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = __ldcg(src + tt + 256 * j);
     }
-    if (h == 0) noise_row(0);
+    if (h == 0) noise_row(t0);
     signal_a(true);
-    for (int t = 0; t < p.T; ++t) {
+    for (int t = t0; t < t1; ++t) {
       // ---- G1 (P) -> Q[0,64) ; G2 (P[0,64)) -> Q[64,96) ; G3 (P) -> Q[0,64) ; G4a (P) -> Q[64,128) ; G4b (P) -> Q[0,64)
       wait_d(); t2_relu64(P + 64 * h, Q + 32 * h); signal_a();
       wait_d(); t2_relu32(P + 32 * h, Q + 64 + 16 * h); signal_a();
@@ -1193,6 +1230,17 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         else asm volatile("bar.sync 2, 256;" ::: "memory");
         if (h == 0 && valid) p.cost[(size_t)g * p.K + cand] = (cs + s_red[tile * 128 + m]) * (1.0f / 128.0f);
       }
+    }
+    if (t1 < p.T) {
+      // first piece of a split pair: leave the state images for the continuation, then raise this tile's flag
+      tile_bar();                                               // every thread's put_state8 of the last step
+      const uint4* src = reinterpret_cast<const uint4*>(smem + kT2OffState + tile * 65536);
+      uint4* dst = reinterpret_cast<uint4*>(p.sp_state + ((size_t)sp_id * 2 + tile) * 65536);
+#pragma unroll
+      for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = src[tt + 256 * j];
+      __threadfence();
+      tile_bar();
+      if (tt == 0) st_release_gpu(p.sp_flags + 2 * sp_id + tile, 1u);
     }
 #ifdef NDP_TC_PROF
     if (warp == 0 && lane == 0) {
@@ -1321,7 +1369,39 @@ extern "C" int ndp_debug_tc_prof(unsigned long long* out8, int reset) {
 }
 #endif
 
-size_t tc_workspace_bytes(const TcPlan* p, int G) { return (size_t)(G > 0 ? G : 1) * p->gext_stride + 256; }
+// ---- balanced last waves of the two-tile kernel.  P pairs on S SMs (one CTA per SM) take w = ceil(P/S) waves and the
+// last one is only partly filled (cfg2: 256 pairs on 148 SMs = 1.73 waves, 16 steps of makespan for 13.8 of work).
+// H = w*S - P SMs would idle through it: instead they ("helpers") roll the first `a` steps of m = ceil(n/H) of the
+// n = S - H last-wave pairs BEFORE their own last full pair, and each of the other n SMs appends the remaining T - a
+// steps of one of those pairs to its own: makespan (w-1)*T + max(T - a, m*a) instead of w*T (cfg2: 14 instead of 16).
+struct T2Split { int n, base, h, a; };
+static T2Split t2_split(long long P, int T) {             // T <= 0: sizing only (n, base, h)
+  T2Split r{0, 0, 0, 0};
+  static const bool off = getenv("NDP_TC2_NOSPLIT") != nullptr;
+  const long long S = num_sms();
+  if (off || S <= 0 || P <= S || P % S == 0) return r;
+  const long long w = (P + S - 1) / S, H = w * S - P, n = S - H;
+  const long long m = (n + H - 1) / H;
+  if ((w - 2) * S > 0x7FFFFFFF) return r;
+  long long best = T, best_a = 0;
+  for (long long a = 1; a < T; ++a) {
+    const long long len = (T - a) > m * a ? (T - a) : m * a;
+    if (len < best) { best = len; best_a = a; }
+  }
+  if (T > 0 && best_a == 0) return r;                      // no split point shortens the last wave (T = 1, or m >= T)
+  r.n = (int)n; r.base = (int)((w - 2) * S); r.h = (int)H; r.a = (int)best_a;
+  return r;
+}
+static constexpr size_t kT2SplitFlags = 2048;               // 2 flags per split pair, < 148 pairs
+static size_t t2_split_bytes(const TcPlan* p, int G, int K) {
+  if (!(p->np == 1 && p->stream2) || G <= 0 || K <= 0) return 0;
+  const long long P = (long long)G * (((K + 127) / 128 + 1) / 2);
+  const T2Split sp = t2_split(P, 0);                         // n does not depend on T
+  return sp.n > 0 ? kT2SplitFlags + (size_t)sp.n * 131072 + 256 : 0;
+}
+size_t tc_workspace_bytes(const TcPlan* p, int G, int K) {
+  return ((size_t)(G > 0 ? G : 1) * p->gext_stride + 255) / 256 * 256 + 256 + t2_split_bytes(p, G, K);
+}
 
 template <int NP>
 static int launch_np(const TcParams& tp, int grid, cudaStream_t s) {
@@ -1336,24 +1416,36 @@ static int launch_np(const TcParams& tp, int grid, cudaStream_t s) {
 
 int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const float* noise, int G, int K, int T,
                       float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s,
-                      const int* list, int R, unsigned long long* packed_c, const int* skip) {
+                      const int* list, int R, unsigned long long* packed_c, const int* skip, bool balance) {
   const size_t need = (size_t)G * P->gext_stride;
   if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
   NDP_CHECK_ARG(((uintptr_t)ws & 15) == 0, "rollout_score: workspace must be 16-byte aligned");
+  // the split hand-over area sits behind the per-goal ext blocks when the caller's workspace has room for it
+  // (tc_workspace_bytes); its flags are cleared by the ext kernel, i.e. in stream order before every rollout
+  const bool two_tile = P->np == 1 && P->stream2 && !list && !skip;
+  const size_t sp_off = (need + 255) / 256 * 256;
+  T2Split sp{0, 0, 0, 0};
+  if (two_tile && balance) {
+    sp = t2_split((long long)G * (((K + 127) / 128 + 1) / 2), T);
+    if (sp.n > 0 && ws_bytes < sp_off + kT2SplitFlags + (size_t)sp.n * 131072) sp.n = 0;
+  }
+  unsigned* sp_flags = sp.n > 0 ? reinterpret_cast<unsigned*>(reinterpret_cast<uint8_t*>(ws) + sp_off) : nullptr;
   tc_goal_ext_kernel<<<dim3(G, 16), 256, 0, s>>>(P->W1, P->b1, goal, 128, P->nd, P->np == 3, reinterpret_cast<__half*>(ws),
-                                        P->gext_stride / 2);
+                                        P->gext_stride / 2, sp_flags, 2 * sp.n);
   NDP_LAUNCH_CHECK();
   TcParams tp;
+  tp.sp_n = sp.n; tp.sp_base = sp.base; tp.sp_h = sp.h; tp.sp_a = sp.a; tp.sp_flags = sp_flags;
+  tp.sp_state = sp.n > 0 ? reinterpret_cast<uint8_t*>(ws) + sp_off + kT2SplitFlags : nullptr;
   tp.stream = P->stream; tp.items = P->items; tp.gext = reinterpret_cast<const uint8_t*>(ws);
   tp.gext_stride = P->gext_stride; tp.e0 = e0; tp.goal = goal; tp.noise = noise; tp.cost = cost; tp.a0 = a0;
   tp.state_T = state_T; tp.G = G; tp.K = K; tp.T = T; tp.nd = P->nd; tp.n_items = P->n_items;
   tp.list = list; tp.R = R; tp.packed_c = packed_c; tp.skip = skip;
   tp.tiles_per_goal = ((list ? R : K) + 127) / 128; tp.n_hid_chunks = P->n_chunks;
-  if (P->np == 1 && P->stream2 && !list && !skip) {
+  if (two_tile) {
     // bulk estimate: two tiles per CTA (rollout_tc2_kernel)
     tp.stream = P->stream2; tp.items = P->items2; tp.n_items = P->n_items2; tp.n_hid_chunks = P->n_chunks2;
     tp.tiles_per_goal = (tp.tiles_per_goal + 1) / 2;            // tile pairs
-    const long long grid2 = (long long)G * tp.tiles_per_goal;
+    const long long grid2 = (long long)G * tp.tiles_per_goal + sp.n;      // a split pair is two CTAs
     NDP_CHECK_ARG(grid2 <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
     static std::atomic<unsigned long long> attr_devs2{0};
     if (first_use_on_device(attr_devs2))

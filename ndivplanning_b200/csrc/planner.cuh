@@ -67,17 +67,22 @@ struct TcParams {
   int R;
   const int* skip;          // nullable [G]: CTAs of goals with skip[g] != 0 exit at once (fallback pass)
   int G, K, T, nd, n_items, tiles_per_goal, n_hid_chunks;
+  // two-tile kernel, balanced last waves (k1_rollout_tc.cu: t2_split): sp_n pairs are rolled in two pieces
+  // [0, sp_a) and [sp_a, T) by different CTAs; sp_state holds their state images in between, sp_flags[2 * id + tile]
+  int sp_n, sp_base, sp_h, sp_a;
+  unsigned* sp_flags;
+  uint8_t* sp_state;
 };
 
 struct TcPlan;   // host-side: packed stream + item table of one precision mode
 int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* const* Wt, const float* const* bt,
                    cudaStream_t s);
 void tc_plan_destroy(TcPlan* p);
-size_t tc_workspace_bytes(const TcPlan* p, int G);
+size_t tc_workspace_bytes(const TcPlan* p, int G, int K);
 int launch_rollout_tc(const TcPlan* plan, const float* e0, const float* goal, const float* noise, int G, int K,
                       int T, float* cost, float* a0, float* state_T, void* ws, size_t ws_bytes, cudaStream_t s,
                       const int* list = nullptr, int R = 0, unsigned long long* packed_c = nullptr,
-                      const int* skip = nullptr);
+                      const int* skip = nullptr, bool balance = true);
 int select_masked(const float* cost, int G, int K, int topk, long long idx_base, unsigned long long* pm, int* topk_idx,
                   float* topk_cost, void* ws, size_t ws_bytes, const int* skip, cudaStream_t s);
 int mark_fallback(int* verified, int G, cudaStream_t s);

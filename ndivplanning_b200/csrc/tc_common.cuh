@@ -184,4 +184,14 @@ __device__ __forceinline__ uint32_t pack_lo(float x0, float x1, uint32_t hi) {
 }
 
 }  // namespace tc
+// device-scope flag handshakes between CTAs of one kernel
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned* p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 }  // namespace ndp

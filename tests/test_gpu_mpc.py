@@ -251,10 +251,13 @@ def test_refined_plan_matches_oracle(cuda, G, K, T, H, topk):
             assert best == int(exact.best_idx[g])
 
 
-@pytest.mark.parametrize("prec,G,K,T,topk", [("f16+refine", 1, 4096, 4, 16), ("fp32", 2, 300, 3, 4), ("f16x3", 1, 1000, 2, 0)])
+@pytest.mark.parametrize("prec,G,K,T,topk", [("f16+refine", 1, 4096, 4, 16), ("fp32", 2, 300, 3, 4), ("f16x3", 1, 1000, 2, 0),
+                                             ("f16+refine", 1, 40000, 4, 16), ("f16+refine", 2, 30000, 3, 8)])
 def test_plan_ring_equals_plain_plan(cuda, prec, G, K, T, topk):
     """PlanRing (pre-allocated slots, tails on two side streams) must return exactly what FusedPlanner.plan
-    returns, for more plans than the ring has slots (slot reuse) and with results read late."""
+    returns, for more plans than the ring has slots (slot reuse) and with results read late.  The two large cases have
+    more tile pairs (157, 236) than SMs: FusedPlanner.plan rolls the pairs of the last waves in two pieces on different
+    SMs (state images handed over through global memory), the ring does not — every cost must still be the same bits."""
     from ndivplanning_b200 import FusedPlanner
     gen, fwd = synthetic.make_models(nd=2, E=128, H=256)
     pl = FusedPlanner(gen, fwd, horizon=T, precision=prec)

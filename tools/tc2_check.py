@@ -14,7 +14,9 @@ import torch  # noqa: E402
 from ndivplanning_b200 import FusedPlanner, synthetic  # noqa: E402
 
 CFGS = [(1, 256, 1, 128, 2), (1, 256, 3, 256, 2), (2, 300, 4, 256, 2), (1, 1024, 8, 1024, 2), (3, 130, 3, 384, 5),
-        (1, 257, 5, 2048, 15), (1, 65536, 8, 1024, 2)]
+        (1, 257, 5, 2048, 15), (1, 65536, 8, 1024, 2),
+        # more tile pairs than SMs: the last two waves are split in time (t2_split) — 236, 157 and 352 pairs
+        (2, 30000, 3, 256, 2), (1, 40000, 8, 256, 2), (1, 90000, 4, 256, 2), (1, 131072, 16, 256, 2)]
 
 
 def run(path):
@@ -32,7 +34,7 @@ def run(path):
                 a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a_.record(); pl.rollout_score(e0, goal, noise); b_.record(); torch.cuda.synchronize()
                 ts.append(a_.elapsed_time(b_))
-            print(f"[{os.environ.get('NDP_TC_ONE_TILE', 'two-tile')}] K=65536 T=8 rollout: min {min(ts):.4f} ms "
+            print(f"[{'one-tile' if os.environ.get('NDP_TC_ONE_TILE') else 'two-tile'}{' unsplit' if os.environ.get('NDP_TC2_NOSPLIT') else ''}] K=65536 T=8 rollout: min {min(ts):.4f} ms "
                   f"({G * K * T / min(ts) / 1e6:.3f} Gsteps/s)", flush=True)
     torch.save(out, path)
 
@@ -46,8 +48,16 @@ if __name__ == "__main__":
         run(a)
         env = dict(os.environ, NDP_TC_ONE_TILE="1")
         subprocess.check_call([sys.executable, os.path.abspath(__file__), b], env=env)
-        two, one = torch.load(a), torch.load(b)
+        c = os.path.join(d, "nosplit.pt")
+        subprocess.check_call([sys.executable, os.path.abspath(__file__), c], env=dict(os.environ, NDP_TC2_NOSPLIT="1"))
+        two, one, uns = torch.load(a), torch.load(b), torch.load(c)
         ok = True
+        for i, cfg in enumerate(CFGS):                  # the time split hands the exact state images over: same bits
+            same = all((x is None and y is None) or torch.equal(x, y) for x, y in zip(two[i], uns[i]))
+            ok &= same
+            if not same:
+                print(f"cfg {cfg}: split and unsplit two-tile results DIFFER", flush=True)
+        print("split == unsplit bit for bit:", ok, flush=True)
         for i, cfg in enumerate(CFGS):
             bit = all((x is None and y is None) or torch.equal(x, y) for x, y in zip(two[i], one[i]))
             rel = ((two[i][0] - one[i][0]).abs() / one[i][0].abs()).max().item()
