@@ -13,6 +13,7 @@
 // ReLU): deterministic, no atomics.  Exact fp32 FFMA in this slice; the tcgen05 variant follows the K4 kernels.
 #include <vector>
 #include "common.cuh"
+#include "encoder_tc.cuh"
 
 namespace ndp {
 namespace enc {
@@ -28,6 +29,7 @@ struct ConvP {
   const float* Wt;      // [Cout][KH*KW*Cin], k = (kh*KW + kw)*Cin + ci
   float* part;          // [splits][M][Cout]
   int M, K, k_per_split;
+  float* amax;          // nullable [1]: running maximum of the direct (fused-epilogue) outputs, for the tcgen05 layers
 };
 
 __device__ __forceinline__ void cp_async4(float* smem_dst, const float* src, bool valid) {
@@ -112,6 +114,7 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const ConvP p, cons
     }
   }
   float* out = direct_out ? direct_out : p.part + (size_t)blockIdx.z * p.M * p.Cout;   // direct: one split, epilogue here
+  float mx = 0.f;
 #pragma unroll
   for (int x = 0; x < 4; x++) {
     const int m = m0 + ti * 4 + x;
@@ -121,9 +124,13 @@ __global__ void __launch_bounds__(kThreads) conv_gemm_kernel(const ConvP p, cons
       const int n = n0 + tj * 4 + y;
       if (n >= p.Cout) continue;
       float v = acc[x][y];
-      if (direct_out) { v += __ldg(bias + n); if (relu) v = fmaxf(v, 0.f); }
+      if (direct_out) { v += __ldg(bias + n); if (relu) v = fmaxf(v, 0.f); mx = fmaxf(mx, v); }
       out[(size_t)m * p.Cout + n] = v;
     }
+  }
+  if (direct_out && p.amax) {                              // post-ReLU values: non-negative, ordered like their bits
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((t & 31) == 0 && mx > 0.f) atomicMax(reinterpret_cast<int*>(p.amax), __float_as_int(mx));
   }
 }
 
@@ -288,7 +295,16 @@ struct ndp_encoder {
   float* act[2];        // NHWC activations, ping-pong
   float* part;          // split-K partial slots
   size_t part_floats;
+  // tcgen05 path of conv2..conv5 (k5_encoder_tc.cu), batches of >= kTcMinB images
+  __half* act_hi;       // scaled fp16 planes of the current layer's input
+  __half* act_lo;
+  uint8_t* wpack[6];    // MMA-ready weight tiles (layers 1..4)
+  float* wsinv[6];      // per-output-channel 1 / weight scale
+  float* ws_tmp;        // [1024] weight scales during packing
+  float* amax;          // [8] per-layer running maximum of the layer's INPUT activation
+  float* ainv;          // [8] per-layer 1 / activation scale
 };
+static constexpr int kTcMinB = 16;
 
 static int plan_splits(int M, int Cout, int K, size_t part_floats) {
   const int tiles = ((M + kTM - 1) / kTM) * ((Cout + kTN - 1) / kTN);
@@ -326,7 +342,12 @@ int ndp_encoder_create(ndp_encoder** out, int max_images, int img) {
     max_mn = mn > max_mn ? mn : max_mn;
   }
   e->part_floats = max_mn * 4 > ((size_t)16 << 20) ? max_mn * 4 : ((size_t)16 << 20);   // >= 64 MB of partial slots
-  const size_t bytes = (off + 2 * max_act + e->part_floats) * sizeof(float) + 1024;
+  size_t tc_floats = 0;                                    // fp16 planes (2 x max_act halves) + packed weights + scales
+  if (max_images >= kTcMinB) {
+    tc_floats = max_act + 2048 + 64;
+    for (int l = 1; l <= 4; l++) tc_floats += conv_tc_pack_bytes(e->ly[l].Cout, e->ly[l].KH * e->ly[l].KW * e->ly[l].Cin) / 4 + e->ly[l].Cout + 64;
+  }
+  const size_t bytes = (off + 2 * max_act + e->part_floats + tc_floats) * sizeof(float) + 4096;
   cudaError_t err = cudaMalloc(&e->arena, bytes);
   if (err != cudaSuccess) {
     set_error("ndp_encoder_create: cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(err));
@@ -338,6 +359,23 @@ int ndp_encoder_create(ndp_encoder** out, int max_images, int img) {
   e->act[1] = e->act[0] + max_act;
   e->part = e->act[1] + max_act;
   e->part_floats -= 64;
+  e->act_hi = nullptr;
+  if (tc_floats) {
+    float* q = e->part + e->part_floats + 64;
+    q = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(q) + 255) & ~(uintptr_t)255);
+    e->act_hi = reinterpret_cast<__half*>(q);
+    e->act_lo = e->act_hi + max_act;
+    q += max_act;
+    e->ws_tmp = q; q += 1024;
+    e->amax = q; e->ainv = q + 8; q += 64;
+    for (int l = 1; l <= 4; l++) {
+      const Layer& y = e->ly[l];
+      q = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(q) + 255) & ~(uintptr_t)255);
+      e->wpack[l] = reinterpret_cast<uint8_t*>(q);
+      q += conv_tc_pack_bytes(y.Cout, y.KH * y.KW * y.Cin) / 4;
+      e->wsinv[l] = q; q += y.Cout;
+    }
+  }
   *out = e;
   return NDP_OK;
 }
@@ -358,6 +396,11 @@ int ndp_encoder_load(ndp_encoder* e, const float* const* W, const float* const* 
     NDP_CUDA(cudaMemcpyAsync(e->params + y.w_off, W[l], (size_t)y.Cout * y.KH * y.KW * y.Cin * 4, cudaMemcpyDeviceToDevice, s));
     NDP_CUDA(cudaMemcpyAsync(e->params + y.b_off, b[l], (size_t)y.Cout * 4, cudaMemcpyDeviceToDevice, s));
   }
+  if (e->act_hi)
+    for (int l = 1; l <= 4; l++) {
+      const Layer& y = e->ly[l];
+      if (int rc = conv_tc_pack(e->params + y.w_off, y.Cout, y.KH * y.KW * y.Cin, e->wpack[l], e->wsinv[l], e->ws_tmp, s)) return rc;
+    }
   return NDP_OK;
 }
 
@@ -367,9 +410,26 @@ int ndp_encoder_forward(ndp_encoder* e, const float* images, int B, float* codes
   NDP_CHECK_ARG(B > 0 && B <= e->max_B, "ndp_encoder_forward: B=%d outside (0, %d]", B, e->max_B);
   cudaStream_t s = (cudaStream_t)stream;
   const float* in = images;
+  static const bool tc_off = getenv("NDP_ENC_NO_TC") != nullptr;      // diagnostics: force the CUDA-core kernels
+  const bool use_tc = e->act_hi && !tc_off && B >= kTcMinB;
+  if (use_tc) NDP_CUDA(cudaMemsetAsync(e->amax, 0, 8 * sizeof(float), s));
   for (int l = 0; l < e->L; l++) {
     const Layer& y = e->ly[l];
+    if (use_tc && l >= 1 && l <= 4) {
+      // tcgen05 layer: split the fp32 input into scaled fp16 hi / lo planes, implicit GEMM, fp32 NHWC output
+      ConvTcP t{};
+      t.B = B; t.H = y.H; t.W = y.W; t.Cin = y.Cin; t.OH = y.OH; t.OW = y.OW; t.Cout = y.Cout; t.KW = y.KW;
+      t.stride = y.stride; t.pad = y.pad; t.M = B * y.OH * y.OW; t.K = y.KH * y.KW * y.Cin;
+      if (int rc = conv_tc_split(in, (size_t)B * y.H * y.W * y.Cin, e->amax + l, e->ainv + l, e->act_hi, e->act_lo, s)) return rc;
+      t.in_hi = e->act_hi; t.in_lo = e->act_lo; t.wpack = e->wpack[l]; t.wsinv = e->wsinv[l]; t.ainv = e->ainv + l;
+      t.bias = e->params + y.b_off; t.relu = y.relu;
+      t.out = e->act[l & 1]; t.part = e->part; t.amax_out = l < 4 ? e->amax + l + 1 : nullptr;
+      if (int rc = conv_tc_forward(t, e->part_floats, s)) return rc;
+      in = t.out;
+      continue;
+    }
     ConvP p;
+    p.amax = (use_tc && l == 0) ? e->amax + 1 : nullptr;
     p.in = in; p.nchw = l == 0;
     p.B = B; p.H = y.H; p.W = y.W; p.Cin = y.Cin; p.OH = y.OH; p.OW = y.OW; p.Cout = y.Cout;
     p.KH = y.KH; p.KW = y.KW; p.stride = y.stride; p.pad = y.pad;
