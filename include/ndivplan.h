@@ -111,6 +111,17 @@ int ndp_select_workspace_bytes(int G, int K, int topk, size_t* bytes);
 int ndp_select(const float* cost, int G, int K, int topk, int64_t idx_base,
                uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
                void* ws, size_t ws_bytes, void* stream);
+/* ---- ndp_select without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same arguments, results and kernels as ndp_select, but the scratch is a file-scope `static __device__` array of
+ * ndp_select_static_max_bytes() = 1 MiB inside the library (held by every GPU that loads it, until exit); the entry
+ * point calls no cudaMalloc / cudaFree / allocating routine.  Shapes whose ndp_select_workspace_bytes() exceeds the
+ * array are rejected with NDP_ERR_WORKSPACE (e.g. G=4096, K=65,536, topk=16; every BASELINE config fits).  All calls on
+ * one GPU share the array: what must start at zero is cleared in stream order by the call itself, and calls that
+ * OVERLAP on the GPU (different streams) race — serialise them or use ndp_select with one workspace per stream. */
+int ndp_select_static_max_bytes(size_t* bytes);
+int ndp_select_static(const float* cost, int G, int K, int topk, int64_t idx_base, uint64_t* packed_min,
+                      int32_t* topk_idx, float* topk_cost, void* stream);
 /* ---- one-call plan: rollout + selection (mpc_eval.py:124-165 minus the action gather) --------------
  * = ndp_rollout_score followed by ndp_select for every precision; with NDP_PREC_F16_REFINE the bulk
  * costs are single-pass estimates, the NDP_REFINE_R best estimates per goal are re-rolled with split

@@ -43,6 +43,8 @@ _PROTOS = {
     "ndp_sample_uniform": (_i, [C.c_uint64, C.c_uint64, _vp, _sz, _vp]),
     "ndp_select_workspace_bytes": (_i, [_i, _i, _i, C.POINTER(_sz)]),
     "ndp_select": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "ndp_select_static_max_bytes": (_i, [C.POINTER(_sz)]),
+    "ndp_select_static": (_i, [_vp, _i, _i, _i, _i64, _vp, _vp, _vp, _vp]),
     "ndp_plan_workspace_bytes": (_i, [_vp, _i, _i, _i, C.POINTER(_sz)]),
     "ndp_plan_select": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "ndp_plan_fallback": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _f, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),

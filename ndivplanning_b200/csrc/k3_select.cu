@@ -5,6 +5,7 @@
 // implements (cost, index) lexicographic order; the same word is what the multi-GPU
 // min-allreduce exchanges.  HBM-bound: G*K*4 bytes read once, float4-vectorised.
 #include <stdlib.h>
+#include <mutex>
 #include "common.cuh"
 #include "peer.cuh"
 
@@ -670,6 +671,59 @@ extern "C" int ndp_select(const float* cost, int G, int K, int topk, int64_t idx
                           uint64_t* packed_min, int32_t* topk_idx, float* topk_cost,
                           void* ws, size_t ws_bytes, void* stream) {
   return select_impl(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws, ws_bytes, stream, nullptr);
+}
+
+// ---------------------------------------------------------------- ndp_select without any allocation
+// For callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the
+// workspace of ndp_select lives in a file-scope device array of kSelectStaticBytes that every GPU loading the library
+// holds until exit.  In host code the array's NAME is a host-side stand-in, not a device address: its device address is
+// resolved once per device with cudaGetSymbolAddress (with that device current) and that pointer is what the kernels
+// get.  Every call on a device shares the array and it keeps the last call's contents: select_impl clears the ticket
+// words it needs at zero in stream order before the kernel; calls that overlap on the GPU (different streams) race.
+namespace ndp {
+constexpr size_t kSelectStaticBytes = (size_t)1 << 20;     // 1 MiB per GPU
+static __device__ __align__(256) unsigned char g_select_static_ws[kSelectStaticBytes];
+
+static int select_static_ptr(void** out) {
+  static std::mutex mu;
+  static void* ptrs[64] = {};
+  int dev = 0;
+  NDP_CUDA(cudaGetDevice(&dev));
+  NDP_CHECK_ARG(dev >= 0 && dev < 64, "select_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_select_static_ws);
+    if (e != cudaSuccess || !p) {
+      set_error("select_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return NDP_ERR_CUDA;
+    }
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return NDP_OK;
+}
+}  // namespace ndp
+
+extern "C" int ndp_select_static_max_bytes(size_t* bytes) {
+  NDP_CHECK_ARG(bytes, "select_static_max_bytes: null");
+  *bytes = kSelectStaticBytes;
+  return NDP_OK;
+}
+
+extern "C" int ndp_select_static(const float* cost, int G, int K, int topk, int64_t idx_base, uint64_t* packed_min,
+                                 int32_t* topk_idx, float* topk_cost, void* stream) {
+  size_t need = 0;
+  if (int rc = ndp_select_workspace_bytes(G, K, topk, &need)) return rc;
+  if (need > kSelectStaticBytes) {
+    set_error("select_static: G=%d K=%d topk=%d needs %zu bytes of scratch, the static array holds %zu; use ndp_select "
+              "with a caller workspace", G, K, topk, need, (size_t)kSelectStaticBytes);
+    return NDP_ERR_WORKSPACE;
+  }
+  if (int rc = device_check()) return rc;
+  void* ws = nullptr;
+  if (int rc = select_static_ptr(&ws)) return rc;
+  return select_impl(cost, G, K, topk, idx_base, packed_min, topk_idx, topk_cost, ws, kSelectStaticBytes, stream, nullptr);
 }
 
 namespace ndp {
