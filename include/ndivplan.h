@@ -51,7 +51,8 @@ typedef struct {
   int E;          /* state-embedding width (128; image_autoencoder.py:27)            */
   int nd;         /* noise_dim (evaluation.noise_dim; mpc_eval.py:65)                */
   int A;          /* action width, must be 4 (gan.py:71)                             */
-  int H;          /* latent forward model hidden width, multiple of 128              */
+  int H;          /* latent forward model hidden width, any value in [1,8192] (padded inside
+                     the library to a multiple of 128 with zero units: exact)          */
   int T;          /* mpc.time_horizon (mpc_eval.py:68)                               */
   int precision;  /* NDP_PREC_*                                                      */
 } ndp_planner_desc;

@@ -99,7 +99,8 @@ __global__ void linear_kernel(const float* __restrict__ in0, int K0, const float
 //   sees it / sqrt(E).  It only guards against a degenerate sample (all 128 observed deviations ~0 by coincidence);
 //   the generator's share, the action path and the gain of the dynamics are left to the data-derived term.
 __global__ void __launch_bounds__(1024)
-error_floor_kernel(const float* __restrict__ W1, const float* __restrict__ W2, int E, int H, int T, float* __restrict__ errc) {
+error_floor_kernel(const float* __restrict__ W1, const float* __restrict__ W2, int E, int H, int H_user, int T,
+                   float* __restrict__ errc) {   // H: padded width of the copies; the RMS is over the caller's H_user rows
   __shared__ float s_sum[32], s_max[32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   float sum1 = 0.f, max2 = 0.f;
@@ -121,7 +122,7 @@ error_floor_kernel(const float* __restrict__ W1, const float* __restrict__ W2, i
   if (tid == 0) {
     float a = 0.f, m = 0.f;
     for (int w = 0; w < 32; ++w) { a += s_sum[w]; m = fmaxf(m, s_max[w]); }
-    const float rho1 = sqrtf(a / (float)H), rho2 = sqrtf(m);
+    const float rho1 = sqrtf(a / (float)H_user), rho2 = sqrtf(m);
     const float u = 1.f / 2048.f;
     errc[0] = u * 1.1547005f * rho1 * rho2 * sqrtf((float)T / (float)E);
   }
@@ -141,7 +142,7 @@ extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) 
   NDP_CHECK_ARG(d->E == 128, "planner_create: E must be 128 (got %d); the generator consumes [state 128 | goal 128 | noise] (gan.py:67)", d->E);
   NDP_CHECK_ARG(d->A == 4, "planner_create: A must be 4 (gan.py:71)");
   NDP_CHECK_ARG(d->nd >= 0 && d->nd <= 64, "planner_create: noise_dim must be in [0,64]");
-  NDP_CHECK_ARG(d->H >= 128 && d->H % 128 == 0 && d->H <= 8192, "planner_create: H must be a multiple of 128 in [128,8192]");
+  NDP_CHECK_ARG(d->H >= 1 && d->H <= 8192, "planner_create: H must be in [1,8192]");
   NDP_CHECK_ARG(d->T >= 1 && d->T <= 4096, "planner_create: T must be in [1,4096]");
   NDP_CHECK_ARG(d->precision >= NDP_PREC_FP32 && d->precision <= NDP_PREC_F16_REFINE, "planner_create: unknown precision mode %d", d->precision);
   if (d->precision != NDP_PREC_FP32)
@@ -150,7 +151,12 @@ extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) 
   ndp_planner* p = new ndp_planner();
   memset(p, 0, sizeof(*p));
   p->d = *d;
-  const int E = d->E, H = d->H, nd = d->nd;
+  // Any hidden width: the forward model is padded to the next multiple of 128 hidden units with zero fc1 rows, zero
+  // fc1 bias and zero fc2 columns at load.  A padded unit is relu(0) = 0 and multiplies a zero weight: every sum gets
+  // exact +0 terms, results are those of the caller's model (forward_encoder.py:107-114 has no width constraint).
+  p->H_user = d->H;
+  p->d.H = (d->H + 127) / 128 * 128;
+  const int E = d->E, H = p->d.H, nd = d->nd;
   p->nq = 32 + 16 * (H / 128);
   const size_t sizes[] = {
       (size_t)p->nq * 2048,      // wstream
@@ -203,11 +209,20 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
   for (int i = 0; i < 7; ++i) NDP_CHECK_ARG(W[i] && b[i], "planner_load: tensor %d is null", i);
   if (int rc = device_check()) return rc;
   cudaStream_t s = (cudaStream_t)stream;
-  const int E = p->d.E, H = p->d.H, nd = p->d.nd, C1 = 2 * E + nd;
-  const size_t wt[7] = {(size_t)128 * C1, 64 * 128, 128 * 64, 256 * 128, 4 * 256, (size_t)H * (E + 4), (size_t)E * H};
-  const size_t bt[7] = {128, 64, 128, 256, 4, (size_t)H, (size_t)E};
+  const int E = p->d.E, H = p->d.H, Hu = p->H_user, nd = p->d.nd, C1 = 2 * E + nd;
+  // caller's tensors have the caller's hidden width Hu; the internal copies are padded to H (zeros)
+  const size_t wt[7] = {(size_t)128 * C1, 64 * 128, 128 * 64, 256 * 128, 4 * 256, (size_t)Hu * (E + 4), (size_t)E * Hu};
+  const size_t bt[7] = {128, 64, 128, 256, 4, (size_t)Hu, (size_t)E};
   for (int i = 0; i < 7; ++i) {
-    NDP_CUDA(cudaMemcpyAsync(p->Wt[i], W[i], wt[i] * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    if (i == 6 && Hu != H) {                               // fc2 [E, Hu] -> [E, H]: pitched copy, zero tail columns
+      NDP_CUDA(cudaMemsetAsync(p->Wt[6], 0, (size_t)E * H * sizeof(float), s));
+      NDP_CUDA(cudaMemcpy2DAsync(p->Wt[6], (size_t)H * sizeof(float), W[6], (size_t)Hu * sizeof(float),
+                                 (size_t)Hu * sizeof(float), E, cudaMemcpyDeviceToDevice, s));
+    } else {
+      if (i == 5 && Hu != H) NDP_CUDA(cudaMemsetAsync(p->Wt[5], 0, (size_t)H * (E + 4) * sizeof(float), s));   // zero tail rows
+      NDP_CUDA(cudaMemcpyAsync(p->Wt[i], W[i], wt[i] * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    }
+    if (i == 5 && Hu != H) NDP_CUDA(cudaMemsetAsync(p->bt[5], 0, (size_t)H * sizeof(float), s));
     NDP_CUDA(cudaMemcpyAsync(p->bt[i], b[i], bt[i] * sizeof(float), cudaMemcpyDeviceToDevice, s));
   }
   // ---- weight stream in consumption order (see k1_rollout_f32.cu), all blocks are W^T [K][N] row-major
@@ -237,7 +252,7 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
   NDP_CUDA(cudaMemcpyAsync(p->b5, p->bt[4], 4 * sizeof(float), cudaMemcpyDeviceToDevice, s));
   NDP_CUDA(cudaMemcpyAsync(p->bf1, p->bt[5], (size_t)H * sizeof(float), cudaMemcpyDeviceToDevice, s));
   NDP_CUDA(cudaMemcpyAsync(p->bf2, p->bt[6], (size_t)E * sizeof(float), cudaMemcpyDeviceToDevice, s));
-  error_floor_kernel<<<1, 1024, 0, s>>>(p->Wt[5], p->Wt[6], E, H, p->d.T, p->errc);
+  error_floor_kernel<<<1, 1024, 0, s>>>(p->Wt[5], p->Wt[6], E, H, Hu, p->d.T, p->errc);
   NDP_LAUNCH_CHECK();
   if (p->d.precision != NDP_PREC_FP32) {
     if (p->tc) { tc_plan_destroy(p->tc); p->tc = nullptr; }

@@ -96,7 +96,8 @@ int verify_refine(const float* est_topR, const unsigned long long* packed_c, con
 }  // namespace ndp
 
 struct ndp_planner {
-  ndp_planner_desc d;
+  ndp_planner_desc d;     // d.H is the PADDED hidden width (multiple of 128); H_user is what the caller described
+  int H_user;
   bool loaded;
   float* blob;            // one device allocation holding everything below
   size_t blob_floats;

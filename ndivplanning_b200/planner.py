@@ -82,8 +82,8 @@ class FusedPlanner:
     def __init__(self, generator, fwd_model, *, horizon: int, precision: Optional[str] = None, device=None):
         """precision: None (default) = "f16+refine" — tcgen05 bulk estimate of all K, split-operand re-roll of the 128
         best, data-derived proof per goal, exact re-roll of the goals that cannot be proven (`plan(fallback=True)`) —
-        whenever the shape is one the tensor-core kernels take (E=128, noise_dim<=15, H a multiple of 128 up to
-        2048), else "fp32".  "fp32" (CUDA-core, every cost fp32), "f16x3", "f16x2", "f16" by request."""
+        whenever the shape is one the tensor-core kernels take (E=128, noise_dim<=15, H <= 2048; any hidden
+        width — the library pads it to a multiple of 128 with zero units, exactly), else "fp32".  "fp32" (CUDA-core, every cost fp32), "f16x3", "f16x2", "f16" by request."""
         g, f = generator.state_dict(), fwd_model.state_dict()
         names = ["fc1", "fc2", "fc3", "fc4", "fc5"]
         Ws = [g[f"{n}.weight"] for n in names] + [f["fc1.weight"], f["fc2.weight"]]
@@ -103,7 +103,7 @@ class FusedPlanner:
         self.device = torch.device(device)
         self.E, self.H, self.nd, self.T = E, H, nd, int(horizon)
         if precision is None:
-            precision = "f16+refine" if (E == 128 and 0 <= nd <= 15 and H % 128 == 0 and H <= 2048) else "fp32"
+            precision = "f16+refine" if (E == 128 and 0 <= nd <= 15 and 1 <= H <= 2048) else "fp32"
         prec = {"fp32": _lib.PREC_FP32, "f16x3": _lib.PREC_F16X3, "f16x2": _lib.PREC_F16X2,
                 "f16": _lib.PREC_F16, "f16+refine": _lib.PREC_F16_REFINE}[precision]
         self.precision = precision

@@ -194,6 +194,37 @@ def test_tensor_rollout_matches_oracle(cuda, mode, G, K, T, H, nd):
         np.testing.assert_allclose(sT[g].cpu().numpy(), ref64["state_T"].numpy(), rtol=0, atol=20 * rtol * sscale)
 
 
+@pytest.mark.parametrize("H", [64, 192, 1000, 1])
+def test_any_hidden_width(cuda, H):
+    """forward_encoder.py:107-114 has no constraint on the hidden width: the library pads it to a multiple of 128 with
+    zero units (exact).  fp32 against the fp32 / fp64 oracle; the default mode (f16+refine) selects the same plan with
+    every goal verified or exactly re-rolled."""
+    from ndivplanning_b200 import FusedPlanner
+    E, nd, G, K, T = 128, 2, 2, 700, 3
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
+    e0, goal, noise = synthetic.make_plan_inputs(G, K, T, nd, E, seed=H)
+    pl = FusedPlanner(gen_p, fwd_p, horizon=T, precision="fp32")
+    plan = pl.plan(e0.cuda(), goal.cuda(), noise.cuda(), topk=8, want_state=True)
+    dflt = FusedPlanner(gen_p, fwd_p, horizon=T)
+    assert dflt.precision == "f16+refine"
+    pd = dflt.plan(e0.cuda(), goal.cuda(), noise.cuda(), topk=8)
+    gen, fwd = _oracle_models(gen_p, fwd_p, nd, E, H)
+    g64, f64 = _oracle_models(gen_p, fwd_p, nd, E, H, double=True)
+    for g in range(G):
+        ref = O.mpc_plan(gen, fwd, e0[g], goal[g], noise[:, g], topk=8)
+        ref64 = O.mpc_plan(g64, f64, e0[g].double(), goal[g].double(), noise[:, g].double())
+        np.testing.assert_allclose(plan.cost[g].cpu().numpy(), ref64["cost"].numpy(), rtol=COST_RTOL)
+        np.testing.assert_allclose(plan.state_T[g].cpu().numpy(), ref64["state_T"].numpy(), rtol=1e-3, atol=1e-4)
+        assert int(plan.best_idx[g]) == int(ref["best_idx"]) == int(pd.best_idx[g])
+        assert int(pd.verified[g]) in (1, 2)
+    # the single-call module semantics go through the padded copies too
+    st, ac = torch.randn(5, E, 1, 1), torch.randn(5, 4)
+    with torch.no_grad():
+        want = f64(st.double(), ac.double())
+    got = pl.forward_model(st.cuda(), ac.cuda()).cpu().double()
+    np.testing.assert_allclose(got.numpy(), want.numpy(), rtol=1e-4, atol=1e-5)
+
+
 def test_tensor_mode_rejects_unsupported_shapes(cuda):
     from ndivplanning_b200 import FusedPlanner, NdpError
     gen_p, fwd_p = synthetic.make_models(nd=16, E=128, H=128, seed=0)
