@@ -12,6 +12,7 @@ from .gan_train import GanTrainer, train_gan_epoch  # noqa: F401
 from .models import ActionDiscriminator, GeneratorMLP, ImageEncoder, LatentForward  # noqa: F401
 from .mpc_eval import fetch_push_control_evaluation, sample_noise, sample_noise_device  # noqa: F401
 from .planner import FusedPlanner, Plan, PlanRing, select_plan, unpack_index  # noqa: F401
+from .trajectory_loader import PushDataset  # noqa: F401
 
 __all__ = ["diversity", "FusedPlanner", "Plan", "PlanRing", "select_plan", "unpack_index", "GeneratorMLP", "LatentForward", "ActionDiscriminator", "GanTrainer", "train_gan_epoch", "FusedEncoder", "ImageEncoder",
-           "fetch_push_control_evaluation", "sample_noise", "sample_noise_device", "NdpError", "launch_count", "LIB_PATH"]
+           "fetch_push_control_evaluation", "sample_noise", "sample_noise_device", "NdpError", "launch_count", "LIB_PATH", "PushDataset"]

@@ -113,6 +113,35 @@ def test_closed_loop_from_frames_matches_oracle(cuda):
     np.testing.assert_allclose([a, i], [want_a, want_i], rtol=1e-4)
 
 
+def test_closed_loop_from_push_dataset_bundles(cuda, tmp_path):
+    """the same loop fed by the PushDataset drop-in reading trajectory bundles from disk (decoded uint8 frames ->
+    the reference's [-1,1] normalisation -> device encoder): equals the oracle loop on the oracle's codes of exactly
+    those normalised frames"""
+    from ndivplanning_b200 import PushDataset, fetch_push_control_evaluation, trajectory_loader
+    from oracle.ref_stubs import DotMap
+    K, Th, seq, n_traj, nd, seed = 64, 3, 4, 3, 2, 29
+    enc = synthetic.make_image_encoder(seed=7)
+    gen_p, fwd_p = synthetic.make_models(nd=nd, E=128, H=256, seed=0)
+    rng = np.random.default_rng(5)
+    base = ((synthetic.make_frames(n_traj * seq, seed=23) * 0.5 + 0.5).clamp(0, 1) * 255).round().to(torch.uint8)
+    u8 = base.view(n_traj, seq, 3, 128, 128).permute(0, 1, 3, 4, 2).contiguous().numpy()
+    acts = rng.random((n_traj, seq, 4)).astype(np.float32)
+    trajs = [(u8[i], np.zeros((seq, 25), np.float32), acts[i], np.zeros(3, np.float32)) for i in range(n_traj)]
+    trajectory_loader.write_npz_bundle(str(tmp_path / "trajectory_bundle_00000.npz"), trajs[:2])
+    trajectory_loader.write_npz_bundle(str(tmp_path / "trajectory_bundle_00001.npz"), trajs[2:])
+    ds = PushDataset(str(tmp_path), seq_length=seq)
+    frames = torch.stack([ds[i][0] for i in range(n_traj)])
+    with torch.no_grad():
+        codes = O.encoder_forward(enc.state_dict(), frames.flatten(0, 1)).view(n_traj, seq, 128)
+        want_a, want_i, want_best = O.closed_loop_eval(gen_p, fwd_p, codes, torch.from_numpy(acts), K, Th, nd, seed)
+    cfg = DotMap(random_seed=seed, gpu_id=0, log_port=0,
+                 evaluation=dict(num_sample=1, noise_dim=nd, batch_size=1, threshold=0.05),
+                 mpc=dict(rollouts=K, time_horizon=Th))
+    a, i, best = fetch_push_control_evaluation(enc, fwd_p, gen_p, ds, cfg, return_indices=True)
+    assert best.numpy().tolist() == [list(r) for r in want_best]
+    np.testing.assert_allclose([a, i], [want_a, want_i], rtol=1e-4)
+
+
 def test_gan_epoch_from_frames_matches_oracle(cuda, fused):
     """train_gan.py:114-209 with a real image encoder in front of the step (:152-155): FusedEncoder feeds
     GanTrainer on the device; the oracle epoch encodes with oracle.encoder_forward on the CPU."""
