@@ -14,14 +14,14 @@
 //   canonical K-major no-swizzle layout (core matrix = 8 channels-out x 16 B), so ONE 16 KB bulk copy (TMA engine)
 //   fills a stage's B operand.
 // * The im2col matrix is never materialised: a k chunk of 32 lies inside one kernel cell (Cin % 32 == 0), i.e. 32
-//   contiguous channels of one input pixel = 64 B per plane; producer thread r gathers row r of the A tile with 8
-//   zero-filling 16-byte async copies per stage (padding and rows beyond M arrive as zeros) straight into the
-//   canonical layout.
+//   contiguous channels of one input pixel = 64 B per plane; a producer warp instruction fetches 8 rows x four 16-byte
+//   segments (8 lines per instruction, quarter warps write 128 contiguous shared bytes; a row per lane cost 32 lines,
+//   a row per 4 consecutive lanes 4-way bank conflicts — either made the gather, not the tensor pipe, the bound) with zero-filling async copies (padding and rows beyond M arrive as zeros) straight into
+//   the canonical layout.
 // * One CTA = 128 output pixels x 128 output channels (x a range of k chunks when the layer has few tiles: split-K
 //   into partial slots that a finalize kernel adds in fixed order).  160 threads: warps 0-3 gather, then run the
 //   epilogue (TMEM lane quadrant = warp); warp 4 issues 6 tcgen05.mma per stage (2 K-slabs x 3 products) and
-//   releases the stage with tcgen05.commit.  3 stages x 32 KB, two CTAs per SM (one's prologue / epilogue runs under
-//   the other's main loop).
+//   releases the stage with tcgen05.commit.  6 stages x 32 KB with 4 gather groups in flight, one CTA per SM.
 // * hi.hi goes into one TMEM accumulator, the two cross products (2^-11 of it) into another, added in the epilogue:
 //   the tensor pipe truncates when it aligns an addend to the accumulator, so the small terms never pass through the
 //   large accumulator (measured, tools/encoder_tc_check.py: 8.5e-6 -> 1.3e-6 max error at B = 64).
@@ -36,10 +36,14 @@ namespace ndp {
 namespace enc {
 using namespace ndp::tc;
 
-constexpr int kCM = 128, kCN = 128, kCK = 32, kCStages = 3, kCThreads = 160;
+constexpr int kCM = 128, kCN = 128, kCK = 32, kCStages = 6, kCLag = 4, kCThreads = 160;
+// kCLag gather groups stay in flight; kCStages > kCLag + 1, so the slot the producers wait for at iteration i was handed
+// to the tensor pipe TWO iterations earlier and its MMAs run under the issue of the next loads (with 3 stages / lag 2
+// the slot was the one whose MMAs had just started: gather and MMA alternated instead of overlapping)
+static_assert(kCK == 32, "the gather maps 4 lanes x 16 B to one row of a k chunk");
 constexpr uint32_t kCPlane = 128 * kCK * 2;               // one [128 x 32] fp16 operand plane (8 KB)
 constexpr uint32_t kCStageBytes = 4 * kCPlane;            // A hi | A lo | B hi | B lo
-constexpr uint32_t kCSmem = kCStages * kCStageBytes + 128;   // 96 KB: two CTAs per SM
+constexpr uint32_t kCSmem = kCStages * kCStageBytes + 128;   // 192 KB: one CTA per SM
 
 __device__ __forceinline__ void cp_async16z(uint32_t smem_dst, const void* src, bool valid) {
   const int n = valid ? 16 : 0;
@@ -132,20 +136,21 @@ int conv_tc_split(const float* act, size_t n, const float* amax, float* ainv, __
 }
 
 // ---------------------------------------------------------------- the layer
-__global__ void __launch_bounds__(kCThreads, 2) conv_tc_kernel(const ConvTcP p) {
+__global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t sbase = smem_u32(smem);
-  const uint32_t bars = sbase + kCStages * kCStageBytes;        // full[3] @0, empty[3] @24, acc @48, tmem slot @64
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kCStages * kCStageBytes + 64);
+  const uint32_t bars = sbase + kCStages * kCStageBytes;        // full[6] @0, empty[6] @48, acc @96, tmem slot @112
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kCStages * kCStageBytes + 112);
+  constexpr uint32_t kEmpty = 8 * kCStages, kAcc = 16 * kCStages;
   const int m0 = blockIdx.x * kCM, nt = blockIdx.y;
   const int c_begin = blockIdx.z * p.chunks_per_split;
   const int c_end = min(p.n_chunks, c_begin + p.chunks_per_split);
   const int nloc = c_end - c_begin;
 
   if (tid == 0) {
-    for (int s = 0; s < kCStages; ++s) { mbar_init(bars + 8 * s, 129); mbar_init(bars + 24 + 8 * s, 1); }
-    mbar_init(bars + 48, 1);
+    for (int s = 0; s < kCStages; ++s) { mbar_init(bars + 8 * s, 129); mbar_init(bars + kEmpty + 8 * s, 1); }
+    mbar_init(bars + kAcc, 1);
     fence_mbar_init();
   }
   if (warp == 4) tmem_alloc256(smem_u32((const void*)tmem_slot));   // [0,128) hi.hi, [128,256) the two cross products
@@ -156,52 +161,62 @@ __global__ void __launch_bounds__(kCThreads, 2) conv_tc_kernel(const ConvTcP p) 
   const uint32_t tmem = *tmem_slot;
 
   if (warp < 4) {
-    // ===================== gather producers (thread r = row r of the A tile) =====================
-    const int r = tid, m = m0 + r;
-    const bool rvalid = m < p.M;
-    int ih0 = 0, iw0 = 0;
-    size_t pix0 = 0;
-    if (rvalid) {
-      const int b = m / (p.OH * p.OW), q = m % (p.OH * p.OW);
-      ih0 = (q / p.OW) * p.stride - p.pad; iw0 = (q % p.OW) * p.stride - p.pad;
-      pix0 = (size_t)b * p.H * p.W;
+    // ===================== gather producers =====================
+    // Lane l of warp w fetches 16-byte segment l / 8 of rows q*32 + w*8 + l % 8 (q = 0..3).  One warp instruction
+    // reads 8 rows x 64 contiguous bytes (8 lines; a row per lane touched 32 lines per instruction), and each quarter
+    // warp writes 8 rows x one segment = 128 contiguous bytes of the canonical layout (the 4 segments of ONE row are
+    // 2048 B apart, i.e. on the same banks: a quarter warp holding them cost 4 wavefronts — ncu: 20 shared wavefronts
+    // per LDGSTS with the l % 4 mapping, profiles/r02d_ncu_conv_tc_before_raw.csv).
+    const int seg = lane >> 3;
+    int ih0[4], iw0[4];
+    size_t pix0[4];
+    bool rowok[4];
+    uint32_t row_off[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int r = q * 32 + warp * 8 + (lane & 7), mm = m0 + r;
+      rowok[q] = mm < p.M;
+      ih0[q] = iw0[q] = 0; pix0[q] = 0;
+      if (rowok[q]) {
+        const int b = mm / (p.OH * p.OW), qq = mm % (p.OH * p.OW);
+        ih0[q] = (qq / p.OW) * p.stride - p.pad; iw0[q] = (qq % p.OW) * p.stride - p.pad;
+        pix0[q] = (size_t)b * p.H * p.W;
+      }
+      row_off[q] = (uint32_t)seg * 2048 + (uint32_t)(r >> 3) * 128 + (uint32_t)(r & 7) * 16;
     }
-    const uint32_t row_off = (uint32_t)(r >> 3) * 128 + (uint32_t)(r & 7) * 16;
     const uint8_t* wsrc = p.wpack + (size_t)nt * p.n_chunks * (2 * kCPlane);
     for (int i = 0; i < nloc; ++i) {
       const int c = c_begin + i, stage = i % kCStages;
-      if (i >= kCStages) mbar_wait(bars + 24 + 8 * stage, (uint32_t)((i / kCStages) - 1) & 1u);
-      const int k0 = c * kCK, cell = k0 / p.Cin, ci0 = k0 - cell * p.Cin;
+      if (i >= kCStages) mbar_wait(bars + kEmpty + 8 * stage, (uint32_t)((i / kCStages) - 1) & 1u);
+      const int k0 = c * kCK, cell = k0 / p.Cin, ci0 = k0 - cell * p.Cin + seg * 8;
       const int kh = cell / p.KW, kw = cell - kh * p.KW;
-      const int ih = ih0 + kh, iw = iw0 + kw;
-      const bool ok = rvalid && ih >= 0 && ih < p.H && iw >= 0 && iw < p.W;
-      const size_t off = ok ? ((pix0 + (size_t)ih * p.W + iw) * p.Cin + ci0) : 0;
-      const uint32_t a_hi = sbase + stage * kCStageBytes + row_off, a_lo = a_hi + kCPlane;
-      const __half* sh = p.in_hi + off;
-      const __half* sl = p.in_lo + off;
+      const uint32_t a_hi = sbase + stage * kCStageBytes, a_lo = a_hi + kCPlane;
 #pragma unroll
-      for (int j = 0; j < kCK / 8; ++j) {
-        cp_async16z(a_hi + j * 2048, sh + j * 8, ok);
-        cp_async16z(a_lo + j * 2048, sl + j * 8, ok);
+      for (int q = 0; q < 4; ++q) {
+        const int ih = ih0[q] + kh, iw = iw0[q] + kw;
+        const bool ok = rowok[q] && ih >= 0 && ih < p.H && iw >= 0 && iw < p.W;
+        const size_t off = ok ? ((pix0[q] + (size_t)ih * p.W + iw) * p.Cin + ci0) : 0;
+        cp_async16z(a_hi + row_off[q], p.in_hi + off, ok);
+        cp_async16z(a_lo + row_off[q], p.in_lo + off, ok);
       }
       if (tid == 0) {
         mbar_expect_tx(bars + 8 * stage, 2 * kCPlane);
         bulk_g2s(sbase + stage * kCStageBytes + 2 * kCPlane, wsrc + (size_t)c * (2 * kCPlane), 2 * kCPlane, bars + 8 * stage);
       }
       cp_commit();
-      if (i >= kCStages - 1) {                              // the group of chunk i - 2 has landed
-        cp_wait<kCStages - 1>();
+      if (i >= kCLag) {                                     // the group of chunk i - kCLag has landed
+        cp_wait<kCLag>();
         fence_proxy_async();
-        mbar_arrive(bars + 8 * ((i - (kCStages - 1)) % kCStages));
+        mbar_arrive(bars + 8 * ((i - kCLag) % kCStages));
       }
     }
-    {
-      int done = nloc - (kCStages - 1) > 0 ? nloc - (kCStages - 1) : 0;
-      if (nloc - done == 2) { cp_wait<1>(); fence_proxy_async(); mbar_arrive(bars + 8 * (done % kCStages)); ++done; }
-      if (nloc - done == 1) { cp_wait<0>(); fence_proxy_async(); mbar_arrive(bars + 8 * (done % kCStages)); }
-    }
+    cp_wait<0>();                                           // tail: the last kCLag groups
+    fence_proxy_async();
+    for (int d = nloc - kCLag > 0 ? nloc - kCLag : 0; d < nloc; ++d) mbar_arrive(bars + 8 * (d % kCStages));
     // ===================== epilogue: row r of the tile, 128 output channels =====================
-    mbar_wait(bars + 48, 0);
+    const int m = m0 + tid;                                 // epilogue: thread = TMEM lane = row of the tile
+    const bool rvalid = m < p.M;
+    mbar_wait(bars + kAcc, 0);
     fence_after_sync();
     const float ainv = __ldg(p.ainv);
     const int n0 = nt * kCN;
@@ -249,9 +264,9 @@ __global__ void __launch_bounds__(kCThreads, 2) conv_tc_kernel(const ConvTcP p) 
         mma_ss(tmem + 128, ah, bl, idesc, (i | s) != 0);
         mma_ss(tmem + 128, al, bh, idesc, 1);
       }
-      mma_commit(bars + 24 + 8 * stage);                     // the stage may be refilled
+      mma_commit(bars + kEmpty + 8 * stage);                 // the stage may be refilled
     }
-    mma_commit(bars + 48);                                   // accumulators complete
+    mma_commit(bars + kAcc);                                 // accumulators complete
   }
   fence_before_sync();
   __syncthreads();
@@ -287,8 +302,8 @@ int conv_tc_forward(ConvTcP p, size_t part_floats, cudaStream_t s) {
   p.n_chunks = p.K / kCK;
   const int mt = (p.M + kCM - 1) / kCM, ntl = p.Cout / kCN, tiles = mt * ntl;
   int splits = 1;
-  if (tiles < 2 * num_sms()) {                             // two resident CTAs per SM
-    splits = 2 * num_sms() / tiles;
+  if (tiles < num_sms()) {                                 // one resident CTA per SM
+    splits = num_sms() / tiles;
     const int max_by_k = p.n_chunks / 12 > 0 ? p.n_chunks / 12 : 1;        // at least 12 chunks (K = 384) per split
     if (splits > max_by_k) splits = max_by_k;
     while (splits > 1 && (size_t)splits * p.M * p.Cout > part_floats) --splits;
