@@ -14,14 +14,13 @@
 //   canonical K-major no-swizzle layout (core matrix = 8 channels-out x 16 B), so ONE 16 KB bulk copy (TMA engine)
 //   fills a stage's B operand.
 // * The im2col matrix is never materialised: a k chunk of 32 lies inside one kernel cell (Cin % 32 == 0), i.e. 32
-//   contiguous channels of one input pixel = 64 B per plane; a producer warp instruction fetches 8 rows x four 16-byte
-//   segments (8 lines per instruction, quarter warps write 128 contiguous shared bytes; a row per lane cost 32 lines,
-//   a row per 4 consecutive lanes 4-way bank conflicts — either made the gather, not the tensor pipe, the bound) with zero-filling async copies (padding and rows beyond M arrive as zeros) straight into
-//   the canonical layout.
-// * One CTA = 128 output pixels x 128 output channels (x a range of k chunks when the layer has few tiles: split-K
+//   contiguous channels of one input pixel = 64 B per plane; four consecutive producer lanes fetch the four 16-byte
+//   segments of a row with zero-filling async copies (padding and rows beyond M arrive as zeros) straight into the
+//   canonical layout (the lane mapping is measured, see the producer loop).
+// * One CTA = 128 output pixels x 128 or 256 output channels (NT = 1 / 2 tiles from one gathered A tile; x a range of k chunks when the layer has few tiles: split-K
 //   into partial slots that a finalize kernel adds in fixed order).  160 threads: warps 0-3 gather, then run the
 //   epilogue (TMEM lane quadrant = warp); warp 4 issues 6 tcgen05.mma per stage (2 K-slabs x 3 products) and
-//   releases the stage with tcgen05.commit.  6 stages x 32 KB with 4 gather groups in flight, one CTA per SM.
+//   releases the stage with tcgen05.commit.  6 stages x 32 KB (NT = 1) or 4 x 48 KB (NT = 2), one CTA per SM.
 // * hi.hi goes into one TMEM accumulator, the two cross products (2^-11 of it) into another, added in the epilogue:
 //   the tensor pipe truncates when it aligns an addend to the accumulator, so the small terms never pass through the
 //   large accumulator (measured, tools/encoder_tc_check.py: 8.5e-6 -> 1.3e-6 max error at B = 64).
@@ -36,14 +35,19 @@ namespace ndp {
 namespace enc {
 using namespace ndp::tc;
 
-constexpr int kCM = 128, kCN = 128, kCK = 32, kCStages = 6, kCLag = 4, kCThreads = 160;
-// kCLag gather groups stay in flight; kCStages > kCLag + 1, so the slot the producers wait for at iteration i was handed
-// to the tensor pipe TWO iterations earlier and its MMAs run under the issue of the next loads (with 3 stages / lag 2
-// the slot was the one whose MMAs had just started: gather and MMA alternated instead of overlapping)
+constexpr int kCM = 128, kCN = 128, kCK = 32, kCThreads = 160;
+// One CTA computes NT = 1 or 2 adjacent 128-channel tiles from ONE gathered A tile.  cp.async writes shared memory one
+// wavefront per fetched 32-byte sector (ncu: 16 KB of gathered A = 512-640 shared wavefronts against 384 tensor cycles
+// at NT = 1, profiles/r02d_ncu_conv_tc_*_raw.csv), so the gather, not the tensor pipe, bounds a 128-wide tile; NT = 2
+// halves the gathered bytes per MMA.  lag(NT) gather groups stay in flight and stages(NT) > lag + 1, so the slot the
+// producers wait for at iteration i was handed to the tensor pipe TWO iterations earlier and its MMAs run under the
+// issue of the next loads.
+__host__ __device__ constexpr int conv_stages(int NT) { return NT == 1 ? 6 : 4; }
+__host__ __device__ constexpr int conv_lag(int NT) { return NT == 1 ? 4 : 2; }
 static_assert(kCK == 32, "the gather maps 4 lanes x 16 B to one row of a k chunk");
 constexpr uint32_t kCPlane = 128 * kCK * 2;               // one [128 x 32] fp16 operand plane (8 KB)
-constexpr uint32_t kCStageBytes = 4 * kCPlane;            // A hi | A lo | B hi | B lo
-constexpr uint32_t kCSmem = kCStages * kCStageBytes + 128;   // 192 KB: one CTA per SM
+__host__ __device__ constexpr uint32_t conv_stage_bytes(int NT) { return (2 + 2 * NT) * kCPlane; }   // A hi | A lo | NT x (B hi | B lo)
+__host__ __device__ constexpr uint32_t conv_smem(int NT) { return conv_stages(NT) * conv_stage_bytes(NT) + 128; }   // 192 KB: one CTA per SM
 
 __device__ __forceinline__ void cp_async16z(uint32_t smem_dst, const void* src, bool valid) {
   const int n = valid ? 16 : 0;
@@ -136,14 +140,17 @@ int conv_tc_split(const float* act, size_t n, const float* amax, float* ainv, __
 }
 
 // ---------------------------------------------------------------- the layer
+template <int NT>
 __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) {
+  constexpr int kCStages = conv_stages(NT), kCLag = conv_lag(NT);
+  constexpr uint32_t kCStageBytes = conv_stage_bytes(NT);
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t sbase = smem_u32(smem);
-  const uint32_t bars = sbase + kCStages * kCStageBytes;        // full[6] @0, empty[6] @48, acc @96, tmem slot @112
+  const uint32_t bars = sbase + kCStages * kCStageBytes;        // full[S] @0, empty[S] @8S, acc @16S, tmem slot @112
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kCStages * kCStageBytes + 112);
   constexpr uint32_t kEmpty = 8 * kCStages, kAcc = 16 * kCStages;
-  const int m0 = blockIdx.x * kCM, nt = blockIdx.y;
+  const int m0 = blockIdx.x * kCM, nt0 = blockIdx.y * NT;       // first of this CTA's NT output-channel tiles
   const int c_begin = blockIdx.z * p.chunks_per_split;
   const int c_end = min(p.n_chunks, c_begin + p.chunks_per_split);
   const int nloc = c_end - c_begin;
@@ -153,7 +160,8 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
     mbar_init(bars + kAcc, 1);
     fence_mbar_init();
   }
-  if (warp == 4) tmem_alloc256(smem_u32((const void*)tmem_slot));   // [0,128) hi.hi, [128,256) the two cross products
+  // TMEM: tile j's hi.hi accumulator at columns [128 j, 128 j + 128), its cross products at [128 (NT + j), ...)
+  if (warp == 4) { if (NT == 1) tmem_alloc256(smem_u32((const void*)tmem_slot)); else tmem_alloc512(smem_u32((const void*)tmem_slot)); }
   fence_proxy_async();
   fence_before_sync();
   __syncthreads();
@@ -162,19 +170,19 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
 
   if (warp < 4) {
     // ===================== gather producers =====================
-    // Lane l of warp w fetches 16-byte segment l / 8 of rows q*32 + w*8 + l % 8 (q = 0..3).  One warp instruction
-    // reads 8 rows x 64 contiguous bytes (8 lines; a row per lane touched 32 lines per instruction), and each quarter
-    // warp writes 8 rows x one segment = 128 contiguous bytes of the canonical layout (the 4 segments of ONE row are
-    // 2048 B apart, i.e. on the same banks: a quarter warp holding them cost 4 wavefronts — ncu: 20 shared wavefronts
-    // per LDGSTS with the l % 4 mapping, profiles/r02d_ncu_conv_tc_before_raw.csv).
-    const int seg = lane >> 3;
+    // Lane l of warp w fetches 16-byte segment l % 4 of rows q*32 + w*8 + l/4 (q = 0..3): the 4 lanes of a row read its
+    // 64 contiguous bytes.  Measured (B = 64, 3-stage build): a row per lane 300 us for the four layers, this mapping
+    // 249 us, 8 rows x one segment per quarter warp 272 us — the shared-memory side of LDGSTS takes one wavefront
+    // per fetched sector, so fewer sectors per quarter warp win even though the 4 segments of a row (2048 B apart)
+    // share banks.
+    const int seg = lane & 3;
     int ih0[4], iw0[4];
     size_t pix0[4];
     bool rowok[4];
     uint32_t row_off[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const int r = q * 32 + warp * 8 + (lane & 7), mm = m0 + r;
+      const int r = q * 32 + warp * 8 + (lane >> 2), mm = m0 + r;
       rowok[q] = mm < p.M;
       ih0[q] = iw0[q] = 0; pix0[q] = 0;
       if (rowok[q]) {
@@ -184,7 +192,7 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
       }
       row_off[q] = (uint32_t)seg * 2048 + (uint32_t)(r >> 3) * 128 + (uint32_t)(r & 7) * 16;
     }
-    const uint8_t* wsrc = p.wpack + (size_t)nt * p.n_chunks * (2 * kCPlane);
+    const uint8_t* wsrc = p.wpack + (size_t)nt0 * p.n_chunks * (2 * kCPlane);
     for (int i = 0; i < nloc; ++i) {
       const int c = c_begin + i, stage = i % kCStages;
       if (i >= kCStages) mbar_wait(bars + kEmpty + 8 * stage, (uint32_t)((i / kCStages) - 1) & 1u);
@@ -200,8 +208,11 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
         cp_async16z(a_lo + row_off[q], p.in_lo + off, ok);
       }
       if (tid == 0) {
-        mbar_expect_tx(bars + 8 * stage, 2 * kCPlane);
-        bulk_g2s(sbase + stage * kCStageBytes + 2 * kCPlane, wsrc + (size_t)c * (2 * kCPlane), 2 * kCPlane, bars + 8 * stage);
+        mbar_expect_tx(bars + 8 * stage, NT * 2 * kCPlane);
+#pragma unroll
+        for (int j = 0; j < NT; ++j)
+          bulk_g2s(sbase + stage * kCStageBytes + (2 + 2 * j) * kCPlane,
+                   wsrc + ((size_t)j * p.n_chunks + c) * (2 * kCPlane), 2 * kCPlane, bars + 8 * stage);
       }
       cp_commit();
       if (i >= kCLag) {                                     // the group of chunk i - kCLag has landed
@@ -219,15 +230,15 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
     mbar_wait(bars + kAcc, 0);
     fence_after_sync();
     const float ainv = __ldg(p.ainv);
-    const int n0 = nt * kCN;
-    float* dst = (p.splits > 1 ? p.part + (size_t)blockIdx.z * p.M * p.Cout : p.out) + (size_t)m * p.Cout + n0;
+    float* dst = (p.splits > 1 ? p.part + (size_t)blockIdx.z * p.M * p.Cout : p.out) + (size_t)m * p.Cout;
     const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
     float mx = 0.f;
 #pragma unroll 1
-    for (int cc = 0; cc < 4; ++cc) {
+    for (int cc = 0; cc < 4 * NT; ++cc) {                   // 32 output channels at a time
+      const int j = cc >> 2, n0 = (nt0 + j) * kCN + (cc & 3) * 32;
       uint32_t v[32], vc[32];
-      tmem_ld32(lane_base + cc * 32, v);
-      tmem_ld32(lane_base + 128 + cc * 32, vc);
+      tmem_ld32(lane_base + j * 128 + (cc & 3) * 32, v);
+      tmem_ld32(lane_base + (NT + j) * 128 + (cc & 3) * 32, vc);
       tmem_ld_wait();
       if (rvalid) {
 #pragma unroll
@@ -235,12 +246,12 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
           float o[4];
 #pragma unroll
           for (int u = 0; u < 4; ++u) {
-            const int n = n0 + cc * 32 + q4 * 4 + u;
+            const int n = n0 + q4 * 4 + u;
             float x = (__uint_as_float(v[q4 * 4 + u]) + __uint_as_float(vc[q4 * 4 + u])) * (ainv * __ldg(p.wsinv + n));
             if (p.splits == 1) { x += __ldg(p.bias + n); if (p.relu) x = fmaxf(x, 0.f); mx = fmaxf(mx, x); }
             o[u] = x;
           }
-          *reinterpret_cast<float4*>(dst + cc * 32 + q4 * 4) = make_float4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<float4*>(dst + n0 + q4 * 4) = make_float4(o[0], o[1], o[2], o[3]);
         }
       }
     }
@@ -255,14 +266,21 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
       const int stage = i % kCStages;
       mbar_wait(bars + 8 * stage, (uint32_t)(i / kCStages) & 1u);
       fence_after_sync();
-      const uint32_t a_hi = sbase + stage * kCStageBytes, a_lo = a_hi + kCPlane, b_hi = a_lo + kCPlane, b_lo = b_hi + kCPlane;
+      const uint32_t a_hi = sbase + stage * kCStageBytes, a_lo = a_hi + kCPlane;
+      // hi.hi into one accumulator, the two cross products (2^-11 of it) into another: the tensor pipe truncates when it
+      // aligns an addend to the accumulator, so the main chain is kept to K/16 additions and the small terms never
+      // pass through the large accumulator (measured: tools/encoder_tc_check.py)
 #pragma unroll
       for (int s = 0; s < kCK / 16; ++s) {
         const uint64_t ah = smem_desc(a_hi + s * 4096, 2048, 128), al = smem_desc(a_lo + s * 4096, 2048, 128);
-        const uint64_t bh = smem_desc(b_hi + s * 4096, 2048, 128), bl = smem_desc(b_lo + s * 4096, 2048, 128);
-        mma_ss(tmem, ah, bh, idesc, (i | s) != 0);
-        mma_ss(tmem + 128, ah, bl, idesc, (i | s) != 0);
-        mma_ss(tmem + 128, al, bh, idesc, 1);
+#pragma unroll
+        for (int j = 0; j < NT; ++j) {
+          const uint32_t b_hi = a_lo + (1 + 2 * j) * kCPlane, b_lo = b_hi + kCPlane;
+          const uint64_t bh = smem_desc(b_hi + s * 4096, 2048, 128), bl = smem_desc(b_lo + s * 4096, 2048, 128);
+          mma_ss(tmem + j * 128, ah, bh, idesc, (i | s) != 0);
+          mma_ss(tmem + (NT + j) * 128, ah, bl, idesc, (i | s) != 0);
+          mma_ss(tmem + (NT + j) * 128, al, bh, idesc, 1);
+        }
       }
       mma_commit(bars + kEmpty + 8 * stage);                 // the stage may be refilled
     }
@@ -270,7 +288,7 @@ __global__ void __launch_bounds__(kCThreads, 1) conv_tc_kernel(const ConvTcP p) 
   }
   fence_before_sync();
   __syncthreads();
-  if (warp == 4) tmem_dealloc256(tmem);
+  if (warp == 4) { if (NT == 1) tmem_dealloc256(tmem); else tmem_dealloc512(tmem); }
 }
 
 // out[m][n] = act(sum_s part[s][m][n] + bias[n]), splits added in order; keeps the running maximum
@@ -300,7 +318,10 @@ __global__ void __launch_bounds__(256) conv_tc_finalize_kernel(const float4* __r
 int conv_tc_forward(ConvTcP p, size_t part_floats, cudaStream_t s) {
   NDP_CHECK_ARG(p.Cin % kCK == 0 && p.Cout % kCN == 0 && p.K % kCK == 0, "conv_tc: Cin %% 32, Cout %% 128");
   p.n_chunks = p.K / kCK;
-  const int mt = (p.M + kCM - 1) / kCM, ntl = p.Cout / kCN, tiles = mt * ntl;
+  const int mt = (p.M + kCM - 1) / kCM;
+  static const bool nt1 = getenv("NDP_ENC_NT1") != nullptr;               // diagnostics: 128-wide tiles only
+  const int NT = (!nt1 && p.Cout % (2 * kCN) == 0) ? 2 : 1;
+  const int ntl = p.Cout / (kCN * NT), tiles = mt * ntl;
   int splits = 1;
   if (tiles < num_sms()) {                                 // one resident CTA per SM
     splits = num_sms() / tiles;
@@ -312,9 +333,12 @@ int conv_tc_forward(ConvTcP p, size_t part_floats, cudaStream_t s) {
   p.chunks_per_split = (p.n_chunks + splits - 1) / splits;
   p.splits = (p.n_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
   static std::atomic<unsigned long long> attr_devs{0};
-  if (first_use_on_device(attr_devs))
-    NDP_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kCSmem));
-  conv_tc_kernel<<<dim3(mt, ntl, p.splits), kCThreads, kCSmem, s>>>(p);
+  if (first_use_on_device(attr_devs)) {
+    NDP_CUDA(cudaFuncSetAttribute(conv_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)conv_smem(1)));
+    NDP_CUDA(cudaFuncSetAttribute(conv_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)conv_smem(2)));
+  }
+  if (NT == 1) conv_tc_kernel<1><<<dim3(mt, ntl, p.splits), kCThreads, conv_smem(1), s>>>(p);
+  else conv_tc_kernel<2><<<dim3(mt, ntl, p.splits), kCThreads, conv_smem(2), s>>>(p);
   NDP_LAUNCH_CHECK();
   if (p.splits > 1) {
     const size_t MN4 = (size_t)p.M * p.Cout / 4;
