@@ -673,21 +673,41 @@ __global__ void __launch_bounds__(kGNT, 2) ndiv_gram_kernel(const GramParams p) 
       for (int w = 0; w < 8; ++w) t += slos[w];
       p.loss_part[((size_t)n * gridDim.y + js) * gridDim.x + blockIdx.x] = t;
     }
-    if (grad && ivalid) {
-      // grad_i = c_i * sum_j What_ij - sum_j What_ij c_j (+ the directly accumulated terms); dims hf*16 .. hf*16+15
-      const float sw = sred[row].x + sred[kGT + row].x;
+    if (grad) {
+      // grad_i = c_i * sum_j What_ij - sum_j What_ij c_j (+ the directly accumulated terms).  Each thread holds dims
+      // hf*16 .. hf*16+15 of ITS row: written to global memory from here, a warp instruction touched 32 different
+      // lines (row stride 128 B) for the x loads and the stores alike.  The tile goes through shared memory instead
+      // (behind the exchange area of the direct terms) and leaves with coalesced 128-bit loads / stores.
+      float* gout = gxch + 2 * kGT * 33;                        // [128 rows][33]
       const float ia = 1.f / alpha;
-      const size_t off = ((size_t)n * p.k + i) * p.Dx;
-      float* dst = (p.JS == 1 ? p.grad : p.gpart + (size_t)js * N * p.k * p.Dx) + off;
-      const float* mu = p.mu + (size_t)n * 64;
 #pragma unroll
       for (int d = 0; d < 16; ++d) {
         const int dim = hf * 16 + d;
-        if (dim < p.Dx) {
-          float v = fmaf(__ldg(p.x + off + dim) - __ldg(mu + dim), sw, -g[d] * ia);
-          if (any_direct) v += gxch[row * 33 + dim] + gxch[(kGT + row) * 33 + dim];
-          dst[dim] = v;
-        }
+        float v = -g[d] * ia;
+        if (any_direct) v += gxch[row * 33 + dim] + gxch[(kGT + row) * 33 + dim];
+        gout[row * 33 + dim] = v;
+      }
+      __syncthreads();
+      const int r0c = itile * kGT;
+      float* dstt = (p.JS == 1 ? p.grad : p.gpart + (size_t)js * N * p.k * p.Dx) + ((size_t)n * p.k + r0c) * p.Dx;
+      const float* xt = p.x + ((size_t)n * p.k + r0c) * p.Dx;
+      const float* mu = p.mu + (size_t)n * 64;
+      const bool vec = (reinterpret_cast<uintptr_t>(dstt) & 15) == 0 && (reinterpret_cast<uintptr_t>(xt) & 15) == 0;
+      for (int e4 = tid; e4 < kGT * p.Dx / 4; e4 += kGNT) {     // Dx % 4 == 0
+        const int rr = (e4 * 4) / p.Dx, dim = (e4 * 4) % p.Dx, ii = r0c + rr;
+        if (ii < p.row0 || ii >= iend) continue;
+        const float sw = sred[rr].x + sred[kGT + rr].x;
+        const float* go = gout + rr * 33 + dim;
+        float4 xv;
+        if (vec) xv = __ldg(reinterpret_cast<const float4*>(xt) + e4);
+        else { xv.x = __ldg(xt + e4 * 4); xv.y = __ldg(xt + e4 * 4 + 1); xv.z = __ldg(xt + e4 * 4 + 2); xv.w = __ldg(xt + e4 * 4 + 3); }
+        float4 o;
+        o.x = fmaf(xv.x - __ldg(mu + dim), sw, go[0]);
+        o.y = fmaf(xv.y - __ldg(mu + dim + 1), sw, go[1]);
+        o.z = fmaf(xv.z - __ldg(mu + dim + 2), sw, go[2]);
+        o.w = fmaf(xv.w - __ldg(mu + dim + 3), sw, go[3]);
+        if (vec) reinterpret_cast<float4*>(dstt)[e4] = o;
+        else { dstt[e4 * 4] = o.x; dstt[e4 * 4 + 1] = o.y; dstt[e4 * 4 + 2] = o.z; dstt[e4 * 4 + 3] = o.w; }
       }
     }
     __threadfence();
