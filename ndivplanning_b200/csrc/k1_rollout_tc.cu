@@ -752,10 +752,20 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
 static constexpr int kT2Threads = 576;                   // 16 epilogue warps, MMA issuer (16), TMA producer (17)
 static constexpr uint32_t kT2P = 0, kT2Q = 128;
 static constexpr uint32_t kT2OffState = 0;               // per tile: hi image 32 KB (A operand layout) | lo image 32 KB
-static constexpr uint32_t kT2OffExt = 131072;            // noise[2] 2 x 4 KB | action[2] 2 x 2 KB | ones 2 KB | zeros 2 KB
+#ifdef NDP_T2_EXPERIMENT_ALIAS_LO
+// TIMING EXPERIMENT ONLY (results are garbage): both tiles share one lo image, the freed 32 KB hold a fifth ring slot
+static constexpr uint32_t kT2HiStride = 32768, kT2LoBase = 65536, kT2LoStride = 0, kT2StateBytes = 98304;
+static constexpr uint32_t kT2NSlot = 5;
+#else
+static constexpr uint32_t kT2HiStride = 65536, kT2LoBase = 32768, kT2LoStride = 65536, kT2StateBytes = 131072;
+static constexpr uint32_t kT2NSlot = 4;                   // 4 slots: one GEMM (2 items) in use + one GEMM in flight
+#endif
+static constexpr uint32_t kT2OffExt = kT2StateBytes;     // noise[2] 2 x 4 KB | action[2] 2 x 2 KB | ones 2 KB | zeros 2 KB
 static constexpr uint32_t kT2ExtBytes = 16384;           // (action / ones use k < 8 only: their second k-chunk is the shared zero block)
 static constexpr uint32_t kT2OffRing = kT2OffExt + kT2ExtBytes;
-static constexpr uint32_t kT2Slot = 20480, kT2NSlot = 4;  // 4 slots: one GEMM (2 items) in use + one GEMM in flight
+static constexpr uint32_t kT2Slot = 20480;
+// barrier indices (8 bytes each): full[NSlot] | empty[NSlot] | d_full[tile][2] | a_ready[tile][2]
+static constexpr uint32_t kT2BarEmpty = kT2NSlot, kT2BarD = 2 * kT2NSlot, kT2BarA = 2 * kT2NSlot + 4;
 static constexpr uint32_t kT2OffItems = kT2OffRing + kT2NSlot * kT2Slot;
 static constexpr uint32_t kT2ItemsBytes = kTcMaxItems * 12;      // {src_off, bytes, ext_bytes} per item
 static constexpr uint32_t kT2OffGoal = kT2OffItems + kT2ItemsBytes;
@@ -823,9 +833,25 @@ __device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
   tmem_st16(dst, hi);
 }
 
+// CL = 1 (default): every CTA streams the weights on its own.  CL = 2 (NDP_TC2_CLUSTER=1, measured slower, kept as a
+// reproducible negative result): the two CTAs of a thread-block cluster share the stream —
+// each fetches HALF of every ring item and multicasts it into both CTAs' shared memory (data and mbarrier signal land
+// at the same CTA-relative offsets), so the L2 -> SM traffic of the weight stream (24.6 B/clk/SM = 6 TB/s chip-wide at
+// cfg2, the reason the issuer waited 14 % of its time for ring slots) is halved.  A slot is refilled once BOTH CTAs have
+// released it (the issuers' tcgen05.commit arrives on the empty barrier of both CTAs, barrier count CL).
+template <int CL>
 __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t crank = CL > 1 ? cluster_ctarank() : 0u;
+  constexpr uint16_t kClusterMask = (uint16_t)((1u << CL) - 1u);
+  const bool ghost = (int)blockIdx.x >= p.n_ctas;
+#ifdef NDP_TC_PROF
+  // whole-CTA life time in SM clocks [7] and in nanoseconds [6] (their ratio is the effective SM clock), CTA count [3]
+  const long long t2p_cta0 = clock64();
+  unsigned long long t2p_ns0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2p_ns0));
+#endif
   // ---- job of this CTA: a tile pair and a step range [t0, t1).  Without a split (p.sp_n == 0) CTA b rolls pair b over
   // all T steps.  With one, the pairs of the last two waves are laid out so that the SMs finish together instead of
   // leaving the last wave partly empty (t2_split() below): CTAs are dispatched in index order, one per SM —
@@ -833,7 +859,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   // the H "helper" SMs run the first pieces of the n split pairs BEFORE their own full pair; the n other SMs append
   // a continuation to theirs.  A first piece leaves the pair's state images (the fp16 hi/lo split the next step
   // would read anyway: bit-identical to the unsplit roll) in global scratch and raises a flag per tile.
-  int job = blockIdx.x, t0 = 0, t1 = p.T, sp_id = -1;
+  int job = ghost ? p.n_ctas - 1 : (int)blockIdx.x, t0 = 0, t1 = p.T, sp_id = -1;
   if (p.sp_n > 0 && job >= p.sp_base) {
     const int b = job - p.sp_base, n = p.sp_n;
     if (b < n) job = p.sp_base + b;
@@ -852,7 +878,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   float* s_goal = reinterpret_cast<float*>(smem + kT2OffGoal);
   float* s_red = reinterpret_cast<float*>(smem + kT2OffRed);
   const uint32_t bars = smem_u32(smem + kT2OffBars);
-  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kT2OffBars + 128);
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kT2OffBars + 192);
 
   for (int i = tid; i < p.n_items * 3; i += kT2Threads)
     items[i] = reinterpret_cast<const uint32_t*>(p.items)[(i / 3) * 8 + i % 3];      // TcItem: src_off, bytes, ext_bytes first
@@ -861,8 +887,8 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   if (tid < 128) s_goal[tid] = __ldg(p.goal + (size_t)g * 128 + tid);
   if (tid == 0) {
     // barrier map (8 bytes each): full[0..3] empty[4..7] d_full[tile][2] @8..11  a_ready[tile][2] @12..15
-    for (uint32_t s = 0; s < kT2NSlot; ++s) { mbar_init(bars + 8 * s, 1); mbar_init(bars + 8 * (4 + s), 1); }
-    for (uint32_t e = 0; e < 4; ++e) { mbar_init(bars + 8 * (8 + e), 1); mbar_init(bars + 8 * (12 + e), 8); }
+    for (uint32_t s = 0; s < kT2NSlot; ++s) { mbar_init(bars + 8 * s, 1); mbar_init(bars + 8 * (kT2BarEmpty + s), CL); }
+    for (uint32_t e = 0; e < 4; ++e) { mbar_init(bars + 8 * (kT2BarD + e), 1); mbar_init(bars + 8 * (kT2BarA + e), 8); }
     fence_mbar_init();
   }
   if (warp == 16) tmem_alloc512(smem_u32((const void*)tmem_slot));
@@ -871,6 +897,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   fence_proxy_async();
   fence_before_sync();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();                              // the peer's barriers exist before anything is sent to them
   fence_after_sync();
   const uint32_t tmem = *tmem_slot;
 
@@ -883,11 +910,16 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         for (int i = 0; i < p.n_items; ++i, ++it) {
           const uint32_t slot = it % kT2NSlot, par = (it / kT2NSlot) & 1;
           const uint32_t bytes = items[3 * i + 1], eb = items[3 * i + 2];
-          mbar_wait(bars + 8 * (4 + slot), par ^ 1);
+          mbar_wait(bars + 8 * (kT2BarEmpty + slot), par ^ 1);
           mbar_expect_tx(bars + 8 * slot, bytes + eb);
           const uint32_t dst = smem_u32(smem + kT2OffRing + slot * kT2Slot);
-          bulk_g2s(dst, p.stream + items[3 * i], bytes, bars + 8 * slot);
-          if (eb) bulk_g2s(dst + bytes, gsrc, eb, bars + 8 * slot);
+          if (CL == 1 || (p.dbg & 1)) {
+            bulk_g2s(dst, p.stream + items[3 * i], bytes, bars + 8 * slot);
+          } else {                                          // my 1/CL of the item, to every CTA of the cluster
+            const uint32_t part = bytes / CL, o = crank * part;
+            bulk_g2s_mc(dst + o, p.stream + items[3 * i] + o, part, bars + 8 * slot, kClusterMask);
+          }
+          if (eb) bulk_g2s(dst + bytes, gsrc, eb, bars + 8 * slot);   // per-goal block: this CTA only
         }
       }
     }
@@ -899,15 +931,19 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     // pipe at the same time — measured, tools/tc2_prof.py.)  A ring slot is released after tile 1's MMAs on it.
     T2Tile td[2];
     const uint32_t ext_lbo = (2048u >> 4) << 16;               // smem A operands: LBO = 2 KB, SBO = 128 B
+    // descriptor start-address field: 14 bits of (address >> 4).  Inside a thread-block cluster the shared::cta
+    // addresses of a CTA carry its window's high bits; unmasked they would spill into the LBO field (rank 1 of a
+    // cluster computed garbage until these were masked)
+    auto a16 = [](uint32_t saddr) { return (saddr >> 4) & 0x3FFFu; };
 #pragma unroll
     for (int tl = 0; tl < 2; ++tl) {
-      td[tl].ext_noise = (smem_u32(ext_base + tl * kExtSlab) >> 4) | ext_lbo;
+      td[tl].ext_noise = a16(smem_u32(ext_base + tl * kExtSlab)) | ext_lbo;
       // action / ones slabs hold k-chunk 0 only; LBO points their k-chunk 1 at the shared zero block
-      td[tl].ext_act = (smem_u32(ext_actb + tl * 2048) >> 4) | (((smem_u32(ext_zero) - smem_u32(ext_actb + tl * 2048)) >> 4) << 16);
-      td[tl].ext_ones = (smem_u32(ext_ones) >> 4) | (((smem_u32(ext_zero) - smem_u32(ext_ones)) >> 4) << 16);
-      td[tl].state16 = (smem_u32(smem + kT2OffState + tl * 65536) >> 4) | ext_lbo;
+      td[tl].ext_act = a16(smem_u32(ext_actb + tl * 2048)) | (((smem_u32(ext_zero) - smem_u32(ext_actb + tl * 2048)) >> 4) << 16);
+      td[tl].ext_ones = a16(smem_u32(ext_ones)) | (((smem_u32(ext_zero) - smem_u32(ext_ones)) >> 4) << 16);
+      td[tl].state16 = a16(smem_u32(smem + kT2OffState + tl * kT2HiStride)) | ext_lbo;
     }
-    const uint32_t ring16 = smem_u32(smem + kT2OffRing) >> 4;
+    const uint32_t ring16 = a16(smem_u32(smem + kT2OffRing));
     uint32_t slot = 0, par = 0, ds[2] = {0, 0}, aw[2] = {0, 0};
     const int nch = p.n_hid_chunks;                             // hidden chunks of 128
 #ifdef NDP_TC_PROF
@@ -918,7 +954,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
 #ifdef NDP_TC_PROF
       const long long c0 = clock64();
 #endif
-      mbar_wait(bars + 8 * (12 + 2 * tl + (aw[tl] & 1)), (aw[tl] >> 1) & 1);
+      mbar_wait(bars + 8 * (kT2BarA + 2 * tl + (aw[tl] & 1)), (aw[tl] >> 1) & 1);
       ++aw[tl];
 #ifdef NDP_TC_PROF
       t2p_a += clock64() - c0;
@@ -935,8 +971,11 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
 #endif
     };
     auto slot16 = [&](uint32_t j) { const uint32_t sj = slot + j; return ring16 + (sj >= kT2NSlot ? sj - kT2NSlot : sj) * (kT2Slot >> 4); };
-    auto free_slot = [&](uint32_t j) { const uint32_t sj = slot + j; mma_commit(bars + 8 * (4 + (sj >= kT2NSlot ? sj - kT2NSlot : sj))); };
-    auto signal_d = [&](int tl) { mma_commit(bars + 8 * (8 + 2 * tl + (ds[tl] & 1))); };
+    auto free_slot = [&](uint32_t j) {
+      const uint32_t sj = slot + j, b = bars + 8 * (kT2BarEmpty + (sj >= kT2NSlot ? sj - kT2NSlot : sj));
+      if (CL == 1) mma_commit(b); else mma_commit_mc(b, kClusterMask);
+    };
+    auto signal_d = [&](int tl) { mma_commit(bars + 8 * (kT2BarD + 2 * tl + (ds[tl] & 1))); };
     auto advance = [&](uint32_t n) { slot += n; if (slot >= kT2NSlot) { slot -= kT2NSlot; par ^= 1; } };
     // a GEMM of two ring items: slabs 0..3 (item 0), slabs 4..7 + ext (item 1)
     // AM: 1 = A from the state image (slabs a, a+4), 0 = A from TMEM (columns a, a + a_hi)
@@ -1061,15 +1100,16 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     const int tile = warp >> 3, q = warp & 3, h = (warp >> 2) & 1;
     const int m = q * 32 + lane;                                // candidate row = TMEM lane
     const int cand = (pair * 2 + tile) * 128 + m;
-    const bool valid = cand < p.K;
+    const bool valid = cand < p.K && !ghost;
     // state images of this tile: element (row m, k) at (k/8)*2048 + (m/8)*128 + (m%8)*16 + (k%8)*2
-    uint8_t* SH = smem + kT2OffState + tile * 65536 + (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16;
-    uint8_t* SL = SH + 32768;
+    const uint32_t rowoff = (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16;
+    uint8_t* SH = smem + kT2OffState + tile * kT2HiStride + rowoff;
+    uint8_t* SL = smem + kT2OffState + kT2LoBase + tile * kT2LoStride + rowoff;
     uint8_t* ext_noise = ext_base + tile * kExtSlab;
     uint8_t* ext_act = ext_actb + tile * 2048;
     const uint32_t lane_base = tmem + 256 * tile + ((uint32_t)(q * 32) << 16);
     const uint32_t P = lane_base + kT2P, Q = lane_base + kT2Q;
-    const uint32_t bar_d = bars + 8 * (8 + 2 * tile), bar_a = bars + 8 * (12 + 2 * tile);
+    const uint32_t bar_d = bars + 8 * (kT2BarD + 2 * tile), bar_a = bars + 8 * (kT2BarA + 2 * tile);
     uint32_t dw = 0, ae = 0;
 #ifdef NDP_TC_PROF
     long long t2p_d = 0;
@@ -1231,7 +1271,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         if (h == 0 && valid) p.cost[(size_t)g * p.K + cand] = (cs + s_red[tile * 128 + m]) * (1.0f / 128.0f);
       }
     }
-    if (t1 < p.T) {
+    if (t1 < p.T && !ghost) {
       // first piece of a split pair: leave the state images for the continuation, then raise this tile's flag
       tile_bar();                                               // every thread's put_state8 of the last step
       const uint4* src = reinterpret_cast<const uint4*>(smem + kT2OffState + tile * 65536);
@@ -1251,7 +1291,17 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   }
   fence_before_sync();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();        // no CTA leaves while its peer may still multicast into it or arrive on its barriers
   if (warp == 16) tmem_dealloc512(tmem);
+#ifdef NDP_TC_PROF
+  if (tid == 0) {
+    unsigned long long ns1;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(ns1));
+    atomicAdd(&g_t2_prof[7], (unsigned long long)(clock64() - t2p_cta0));
+    atomicAdd(&g_t2_prof[6], ns1 - t2p_ns0);
+    atomicAdd(&g_t2_prof[3], 1ull);
+  }
+#endif
 }
 
 // host side: weight stream of the two-tile kernel (fp16 hi only), items in the kernel's consumption order
@@ -1446,11 +1496,37 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
     tp.stream = P->stream2; tp.items = P->items2; tp.n_items = P->n_items2; tp.n_hid_chunks = P->n_chunks2;
     tp.tiles_per_goal = (tp.tiles_per_goal + 1) / 2;            // tile pairs
     const long long grid2 = (long long)G * tp.tiles_per_goal + sp.n;      // a split pair is two CTAs
-    NDP_CHECK_ARG(grid2 <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
+    NDP_CHECK_ARG(grid2 + 1 <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
+    tp.n_ctas = (int)grid2;
+    { const char* d = getenv("NDP_TC2_DBG"); tp.dbg = d ? atoi(d) : 0; }
     static std::atomic<unsigned long long> attr_devs2{0};
-    if (first_use_on_device(attr_devs2))
-      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
-    rollout_tc2_kernel<<<(int)grid2, kT2Threads, kT2SmemBytes, s>>>(tp);
+    if (first_use_on_device(attr_devs2)) {
+      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
+      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
+    }
+    // clusters of two CTAs share the weight stream (TMA multicast).  The CTAs of a cluster must run the same number of
+    // steps (they feed each other's ring), so with a time split its groups (n, H) must be even; the grid is padded to
+    // an even size with a ghost CTA
+    // MEASURED SLOWER (cfg2: 0.337 vs 0.326 ms; the issuer's wait for ring slots grows from 4.6 k to 5.4 k cycles per
+    // pair-step: the wait is latency-, not bandwidth-bound, and a slot now waits for BOTH CTAs) — off unless
+    // NDP_TC2_CLUSTER=1; bit-identical results either way (tools/tc2_check.py)
+    static const bool want_cluster = getenv("NDP_TC2_CLUSTER") != nullptr;
+    const bool cluster = want_cluster && grid2 >= 2 && (sp.n == 0 || (sp.n % 2 == 0 && sp.h % 2 == 0 && sp.base % 2 == 0));
+    if (!cluster) {
+      rollout_tc2_kernel<1><<<(int)grid2, kT2Threads, kT2SmemBytes, s>>>(tp);
+    } else {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)((grid2 + 1) / 2 * 2));
+      cfg.blockDim = dim3(kT2Threads);
+      cfg.dynamicSmemBytes = kT2SmemBytes;
+      cfg.stream = s;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      if (tp.dbg & 2) { NDP_CUDA(cudaLaunchKernelEx(&cfg, rollout_tc2_kernel<1>, tp)); }   // dev: plain kernel, cluster launch
+      else NDP_CUDA(cudaLaunchKernelEx(&cfg, rollout_tc2_kernel<2>, tp));
+    }
     NDP_LAUNCH_CHECK();
     return NDP_OK;
   }

@@ -70,6 +70,9 @@ struct TcParams {
   // two-tile kernel, balanced last waves (k1_rollout_tc.cu: t2_split): sp_n pairs are rolled in two pieces
   // [0, sp_a) and [sp_a, T) by different CTAs; sp_state holds their state images in between, sp_flags[2 * id + tile]
   int sp_n, sp_base, sp_h, sp_a;
+  int dbg;                  // development switches (0 in production)
+  int n_ctas;               // CTAs that own a job; the grid may be padded to a multiple of the cluster size ("ghost" CTAs
+                            // mirror the last job without writing anything, to keep the cluster's weight ring in step)
   unsigned* sp_flags;
   uint8_t* sp_state;
 };

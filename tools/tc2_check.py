@@ -34,7 +34,7 @@ def run(path):
                 a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 a_.record(); pl.rollout_score(e0, goal, noise); b_.record(); torch.cuda.synchronize()
                 ts.append(a_.elapsed_time(b_))
-            print(f"[{'one-tile' if os.environ.get('NDP_TC_ONE_TILE') else 'two-tile'}{' unsplit' if os.environ.get('NDP_TC2_NOSPLIT') else ''}] K=65536 T=8 rollout: min {min(ts):.4f} ms "
+            print(f"[{'one-tile' if os.environ.get('NDP_TC_ONE_TILE') else 'two-tile'}{' unsplit' if os.environ.get('NDP_TC2_NOSPLIT') else ''}{' cluster' if os.environ.get('NDP_TC2_CLUSTER') else ''}] K=65536 T=8 rollout: min {min(ts):.4f} ms "
                   f"({G * K * T / min(ts) / 1e6:.3f} Gsteps/s)", flush=True)
     torch.save(out, path)
 
@@ -52,6 +52,12 @@ if __name__ == "__main__":
         subprocess.check_call([sys.executable, os.path.abspath(__file__), c], env=dict(os.environ, NDP_TC2_NOSPLIT="1"))
         two, one, uns = torch.load(a), torch.load(b), torch.load(c)
         ok = True
+        e = os.path.join(d, "nocluster.pt")
+        subprocess.check_call([sys.executable, os.path.abspath(__file__), e], env=dict(os.environ, NDP_TC2_CLUSTER="1"))
+        ncl = torch.load(e)
+        same_cl = all(all((x is None and y is None) or torch.equal(x, y) for x, y in zip(two[i], ncl[i])) for i in range(len(CFGS)))
+        print("2-CTA cluster with multicast weights (NDP_TC2_CLUSTER=1) == default, bit for bit:", same_cl, flush=True)
+        ok &= same_cl
         for i, cfg in enumerate(CFGS):                  # the time split hands the exact state images over: same bits
             same = all((x is None and y is None) or torch.equal(x, y) for x, y in zip(two[i], uns[i]))
             ok &= same
