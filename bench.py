@@ -528,7 +528,8 @@ def run_gpu(args):
             select_plan(big, tk); select_plan(big2, tk)
             torch.cuda.synchronize()
             a, b = ev(), ev()
-            a.record()
+            torch.cuda._sleep(2_000_000)                      # the 10 launches are queued before `a` is reached (device time,
+            a.record()                                        # not the host's ~20 us per Python call)
             for i in range(10):
                 select_plan(big if i & 1 else big2, tk)       # 2 x 67 MB alternate: > L2
             b.record(); torch.cuda.synchronize()
