@@ -225,6 +225,38 @@ def test_any_hidden_width(cuda, H):
     np.testing.assert_allclose(got.numpy(), want.numpy(), rtol=1e-4, atol=1e-5)
 
 
+def test_two_tile_kernel_variants_are_bit_identical(cuda):
+    """the bulk kernel's launch variants — time-split last waves (default for un-pipelined rollouts), unsplit
+    (NDP_TC2_NOSPLIT=1, what the pipelined ring launches) and the opt-in 2-CTA cluster with a multicast weight stream
+    (NDP_TC2_CLUSTER=1) — must produce the same bits: each runs in its own process (the switches are read once)"""
+    import os
+    import subprocess
+    import sys
+    import tempfile
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = (
+        "import sys, torch; sys.path.insert(0, %r)\n"
+        "from ndivplanning_b200 import FusedPlanner, synthetic\n"
+        "out = []\n"
+        "for (G, K, T, H) in ((1, 40000, 3, 256), (2, 300, 4, 256), (1, 513, 2, 128)):\n"
+        "    gen, fwd = synthetic.make_models(nd=2, E=128, H=H)\n"
+        "    e0, goal, noise = (t.cuda() for t in synthetic.make_plan_inputs(G, K, T, 2, 128, seed=7))\n"
+        "    c, a, _ = FusedPlanner(gen, fwd, horizon=T, precision='f16').rollout_score(e0, goal, noise)\n"
+        "    out.append((c.cpu(), a.cpu()))\n"
+        "torch.save(out, sys.argv[1])\n" % root)
+    with tempfile.TemporaryDirectory() as d:
+        res = {}
+        for name, env in (("default", {}), ("nosplit", {"NDP_TC2_NOSPLIT": "1"}), ("cluster", {"NDP_TC2_CLUSTER": "1"}),
+                          ("cluster_nosplit", {"NDP_TC2_CLUSTER": "1", "NDP_TC2_NOSPLIT": "1"})):
+            pth = os.path.join(d, name + ".pt")
+            subprocess.run([sys.executable, "-c", code, pth], env=dict(os.environ, **env), check=True, timeout=300)
+            res[name] = torch.load(pth)
+        for name in ("nosplit", "cluster", "cluster_nosplit"):
+            for (c, a), (c0, a0) in zip(res[name], res["default"]):
+                assert torch.isfinite(c0).all()
+                assert torch.equal(c, c0) and torch.equal(a, a0), name
+
+
 def test_tensor_mode_rejects_unsupported_shapes(cuda):
     from ndivplanning_b200 import FusedPlanner, NdpError
     gen_p, fwd_p = synthetic.make_models(nd=16, E=128, H=128, seed=0)
