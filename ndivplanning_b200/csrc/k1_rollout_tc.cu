@@ -839,13 +839,16 @@ __device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
 // at the same CTA-relative offsets), so the L2 -> SM traffic of the weight stream (24.6 B/clk/SM = 6 TB/s chip-wide at
 // cfg2, the reason the issuer waited 14 % of its time for ring slots) is halved.  A slot is refilled once BOTH CTAs have
 // released it (the issuers' tcgen05.commit arrives on the empty barrier of both CTAs, barrier count CL).
-template <int CL>
+// SPLIT = false: the launch has no time-split pairs (every pipelined PlanRing launch) — none of the job mapping /
+// hand-over code is compiled in (with it, the un-split kernel ran 2.5 % slower in the pipelined loop: same-box A/B of
+// the round-2b and round-2e builds, 1.757 vs 1.712e9 sustained).
+template <int CL, bool SPLIT>
 __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t crank = CL > 1 ? cluster_ctarank() : 0u;
   constexpr uint16_t kClusterMask = (uint16_t)((1u << CL) - 1u);
-  const bool ghost = (int)blockIdx.x >= p.n_ctas;
+  const bool ghost = CL > 1 && (int)blockIdx.x >= p.n_ctas;
 #ifdef NDP_TC_PROF
   // whole-CTA life time in SM clocks [7] and in nanoseconds [6] (their ratio is the effective SM clock), CTA count [3]
   const long long t2p_cta0 = clock64();
@@ -860,7 +863,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
   // a continuation to theirs.  A first piece leaves the pair's state images (the fp16 hi/lo split the next step
   // would read anyway: bit-identical to the unsplit roll) in global scratch and raises a flag per tile.
   int job = ghost ? p.n_ctas - 1 : (int)blockIdx.x, t0 = 0, t1 = p.T, sp_id = -1;
-  if (p.sp_n > 0 && job >= p.sp_base) {
+  if (SPLIT && p.sp_n > 0 && job >= p.sp_base) {
     const int b = job - p.sp_base, n = p.sp_n;
     if (b < n) job = p.sp_base + b;
     else if (b < 2 * n) { sp_id = b - n; job = p.sp_base + n + sp_id; t1 = p.sp_a; }
@@ -913,7 +916,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
           mbar_wait(bars + 8 * (kT2BarEmpty + slot), par ^ 1);
           mbar_expect_tx(bars + 8 * slot, bytes + eb);
           const uint32_t dst = smem_u32(smem + kT2OffRing + slot * kT2Slot);
-          if (CL == 1 || (p.dbg & 1)) {
+          if (CL == 1 || (p.dbg & 1)) {   // (CL == 1: decided at compile time)
             bulk_g2s(dst, p.stream + items[3 * i], bytes, bars + 8 * slot);
           } else {                                          // my 1/CL of the item, to every CTA of the cluster
             const uint32_t part = bytes / CL, o = crank * part;
@@ -1173,7 +1176,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       if (tile == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
       else asm volatile("bar.sync 2, 256;" ::: "memory");
     };
-    if (t0 == 0) {
+    if (!SPLIT || t0 == 0) {
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
         const float4 a = __ldg(reinterpret_cast<const float4*>(p.e0 + (size_t)g * 128) + h * 16 + 2 * c);
@@ -1271,7 +1274,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         if (h == 0 && valid) p.cost[(size_t)g * p.K + cand] = (cs + s_red[tile * 128 + m]) * (1.0f / 128.0f);
       }
     }
-    if (t1 < p.T && !ghost) {
+    if (SPLIT && t1 < p.T && !ghost) {
       // first piece of a split pair: leave the state images for the continuation, then raise this tile's flag
       tile_bar();                                               // every thread's put_state8 of the last step
       const uint4* src = reinterpret_cast<const uint4*>(smem + kT2OffState + tile * 65536);
@@ -1501,8 +1504,9 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
     { const char* d = getenv("NDP_TC2_DBG"); tp.dbg = d ? atoi(d) : 0; }
     static std::atomic<unsigned long long> attr_devs2{0};
     if (first_use_on_device(attr_devs2)) {
-      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
-      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
+      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
+      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
+      NDP_CUDA(cudaFuncSetAttribute(rollout_tc2_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kT2SmemBytes));
     }
     // clusters of two CTAs share the weight stream (TMA multicast).  The CTAs of a cluster must run the same number of
     // steps (they feed each other's ring), so with a time split its groups (n, H) must be even; the grid is padded to
@@ -1513,7 +1517,8 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
     static const bool want_cluster = getenv("NDP_TC2_CLUSTER") != nullptr;
     const bool cluster = want_cluster && grid2 >= 2 && (sp.n == 0 || (sp.n % 2 == 0 && sp.h % 2 == 0 && sp.base % 2 == 0));
     if (!cluster) {
-      rollout_tc2_kernel<1><<<(int)grid2, kT2Threads, kT2SmemBytes, s>>>(tp);
+      if (sp.n > 0) rollout_tc2_kernel<1, true><<<(int)grid2, kT2Threads, kT2SmemBytes, s>>>(tp);
+      else rollout_tc2_kernel<1, false><<<(int)grid2, kT2Threads, kT2SmemBytes, s>>>(tp);
     } else {
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3((unsigned)((grid2 + 1) / 2 * 2));
@@ -1524,8 +1529,8 @@ int launch_rollout_tc(const TcPlan* P, const float* e0, const float* goal, const
       at[0].id = cudaLaunchAttributeClusterDimension;
       at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
       cfg.attrs = at; cfg.numAttrs = 1;
-      if (tp.dbg & 2) { NDP_CUDA(cudaLaunchKernelEx(&cfg, rollout_tc2_kernel<1>, tp)); }   // dev: plain kernel, cluster launch
-      else NDP_CUDA(cudaLaunchKernelEx(&cfg, rollout_tc2_kernel<2>, tp));
+      if (tp.dbg & 2) { NDP_CUDA(cudaLaunchKernelEx(&cfg, rollout_tc2_kernel<1, true>, tp)); }   // dev: plain kernel, cluster launch
+      else NDP_CUDA(cudaLaunchKernelEx(&cfg, rollout_tc2_kernel<2, true>, tp));
     }
     NDP_LAUNCH_CHECK();
     return NDP_OK;
