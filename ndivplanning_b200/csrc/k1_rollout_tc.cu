@@ -839,6 +839,34 @@ __device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
 // at the same CTA-relative offsets), so the L2 -> SM traffic of the weight stream (24.6 B/clk/SM = 6 TB/s chip-wide at
 // cfg2, the reason the issuer waited 14 % of its time for ring slots) is halved.  A slot is refilled once BOTH CTAs have
 // released it (the issuers' tcgen05.commit arrives on the empty barrier of both CTAs, barrier count CL).
+// hand-over of a split pair's state images (64 KB per tile) through global memory.  __noinline__: kept out of the
+// kernel body so that the step loops of the SPLIT instantiation are scheduled / register-allocated like the lean one
+__device__ __forceinline__ void t2_tile_bar(int tile) {
+  if (tile == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
+  else asm volatile("bar.sync 2, 256;" ::: "memory");
+}
+__device__ __noinline__ void t2_state_restore(uint8_t* tile_smem, const uint8_t* src_g, const unsigned* flag, int tt, int tile) {
+  if (tt == 0) {                                            // bounded wait for the first piece of this tile
+    const long long c0 = clock64();
+    while (ld_acquire_gpu(flag) == 0u && clock64() - c0 < 4000000000ll) __nanosleep(128);
+  }
+  t2_tile_bar(tile);
+  const uint4* src = reinterpret_cast<const uint4*>(src_g);
+  uint4* dst = reinterpret_cast<uint4*>(tile_smem);
+#pragma unroll 4
+  for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = __ldcg(src + tt + 256 * j);
+}
+__device__ __noinline__ void t2_state_dump(const uint8_t* tile_smem, uint8_t* dst_g, unsigned* flag, int tt, int tile) {
+  t2_tile_bar(tile);                                        // every thread's put_state8 of the last step
+  const uint4* src = reinterpret_cast<const uint4*>(tile_smem);
+  uint4* dst = reinterpret_cast<uint4*>(dst_g);
+#pragma unroll 4
+  for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = src[tt + 256 * j];
+  __threadfence();
+  t2_tile_bar(tile);
+  if (tt == 0) st_release_gpu(flag, 1u);
+}
+
 // SPLIT = false: the launch has no time-split pairs (every pipelined PlanRing launch) — none of the job mapping /
 // hand-over code is compiled in (with it, the un-split kernel ran 2.5 % slower in the pipelined loop: same-box A/B of
 // the round-2b and round-2e builds, 1.757 vs 1.712e9 sustained).
@@ -1186,16 +1214,8 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       }
     } else {
       // continuation: wait (bounded) for the first piece of this tile, then copy its 64 KB of state images back
-      unsigned* flag = p.sp_flags + 2 * sp_id + tile;
-      if (tt == 0) {
-        const long long c0 = clock64();
-        while (ld_acquire_gpu(flag) == 0u && clock64() - c0 < 4000000000ll) __nanosleep(128);
-      }
-      tile_bar();
-      const uint4* src = reinterpret_cast<const uint4*>(p.sp_state + ((size_t)sp_id * 2 + tile) * 65536);
-      uint4* dst = reinterpret_cast<uint4*>(smem + kT2OffState + tile * 65536);
-#pragma unroll
-      for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = __ldcg(src + tt + 256 * j);
+      t2_state_restore(smem + kT2OffState + tile * 65536, p.sp_state + ((size_t)sp_id * 2 + tile) * 65536,
+                       p.sp_flags + 2 * sp_id + tile, tt, tile);
     }
     if (h == 0) noise_row(t0);
     signal_a(true);
@@ -1276,14 +1296,8 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     }
     if (SPLIT && t1 < p.T && !ghost) {
       // first piece of a split pair: leave the state images for the continuation, then raise this tile's flag
-      tile_bar();                                               // every thread's put_state8 of the last step
-      const uint4* src = reinterpret_cast<const uint4*>(smem + kT2OffState + tile * 65536);
-      uint4* dst = reinterpret_cast<uint4*>(p.sp_state + ((size_t)sp_id * 2 + tile) * 65536);
-#pragma unroll
-      for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = src[tt + 256 * j];
-      __threadfence();
-      tile_bar();
-      if (tt == 0) st_release_gpu(p.sp_flags + 2 * sp_id + tile, 1u);
+      t2_state_dump(smem + kT2OffState + tile * 65536, p.sp_state + ((size_t)sp_id * 2 + tile) * 65536,
+                    p.sp_flags + 2 * sp_id + tile, tt, tile);
     }
 #ifdef NDP_TC_PROF
     if (warp == 0 && lane == 0) {
