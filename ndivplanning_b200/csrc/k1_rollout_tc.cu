@@ -1200,10 +1200,6 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     };
     // ---- init: state <- e0 (this thread: k in [64h, 64h+64)) or the images a first piece left; noise ext of step t0
     const int tt = (warp & 7) * 32 + lane;                      // thread of the tile (256)
-    auto tile_bar = [&]() {
-      if (tile == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
-      else asm volatile("bar.sync 2, 256;" ::: "memory");
-    };
     if (!SPLIT || t0 == 0) {
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
