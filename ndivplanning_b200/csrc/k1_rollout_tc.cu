@@ -1188,6 +1188,37 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         *reinterpret_cast<uint4*>(ext_noise + c * 2048 + off) = hv;
       }
     };
+    // noise_dim <= 4 (the reference's is 2): the NEXT step's noise is fetched into registers at the top of the step, so
+    // that the END phase (on the step's critical path: the issuer waits for it before the next G1) does not expose
+    // the global-load latency
+    const bool npf = p.nd <= 4;
+    float npre[4] = {0.f, 0.f, 0.f, 0.f};
+    auto noise_prefetch = [&](int t) {
+      if (t < p.T && valid) {
+        const float* src = p.noise + (((size_t)t * p.G + g) * p.K + cand) * p.nd;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) npre[k] = k < p.nd ? __ldg(src + k) : 0.f;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) npre[k] = 0.f;
+      }
+    };
+    auto noise_row_pre = [&](int t) {                           // == noise_row(t) from the prefetched values
+      float x[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) x[k] = k < 4 ? npre[k] : 0.f;
+      if (t < p.T) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+          if (k == p.nd) x[k] = 1.f;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) x[k] = 0.f;
+      }
+      uint4 hv;
+      hv.x = pack_hi(x[0], x[1]); hv.y = pack_hi(x[2], x[3]); hv.z = pack_hi(x[4], x[5]); hv.w = pack_hi(x[6], x[7]);
+      *reinterpret_cast<uint4*>(ext_noise + (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16) = hv;
+    };
     // 8 consecutive state values (k = 8*kc .. 8*kc+7) -> hi / lo images
     auto put_state8 = [&](int kc, const float (&s)[8]) {
       uint4 hv, lv;
@@ -1216,6 +1247,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     if (h == 0) noise_row(t0);
     signal_a(true);
     for (int t = t0; t < t1; ++t) {
+      if (h == 0 && npf) noise_prefetch(t + 1);
       // ---- G1 (P) -> Q[0,64) ; G2 (P[0,64)) -> Q[64,96) ; G3 (P) -> Q[0,64) ; G4a (P) -> Q[64,128) ; G4b (P) -> Q[0,64)
       wait_d(); t2_relu64(P + 64 * h, Q + 32 * h); signal_a();
       wait_d(); t2_relu32(P + 32 * h, Q + 64 + 16 * h); signal_a();
@@ -1281,7 +1313,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
         }
       }
       if (more) {
-        if (h == 0) noise_row(t + 1);
+        if (h == 0) { if (npf) noise_row_pre(t + 1); else noise_row(t + 1); }
         signal_a(true);
       } else {
         if (h == 1) s_red[tile * 128 + m] = cs;
