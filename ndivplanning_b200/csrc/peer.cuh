@@ -8,7 +8,7 @@
 // same calls in the same order, like any collective).  A producer finishes its stores, fences at system scope and
 // stores the epoch into flags[slot][its rank] of EVERY rank's window; a consumer spins on its OWN window's flag
 // (local memory) until it reaches the epoch, then reads the producer's payload through the mapped pointer.  Spins are
-// bounded (kSpinLimit cycles): on expiry the consumer records an error word the host reports at the next call, and
+// bounded (kSpinLimit cycles, ~30 s): on expiry the consumer records an error word the host reports at the next call, and
 // carries on, so a missing peer cannot hang the GPU.  Payloads are double-buffered by epoch parity by the callers.
 #pragma once
 #include <stdint.h>
@@ -20,7 +20,8 @@ constexpr int kMaxPeers = 8;
 constexpr int kWinSlots = 16;
 constexpr size_t kWinHeader = 4096;
 constexpr size_t kWinErrOff = 2048;                 // u32 error word inside the header
-constexpr long long kSpinLimit = 4000000000ll;      // ~2 s of SM clocks
+constexpr long long kSpinLimit = 60000000000ll;     // ~30 s of SM clocks: a hang guard (a dead peer), not a latency bound —
+                                                    // ranks may legitimately be seconds apart (start-up, data loading)
 
 struct PeerWin {
   char* peer[kMaxPeers];                            // base of every rank's window as mapped in THIS process
