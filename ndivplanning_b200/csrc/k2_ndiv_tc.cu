@@ -284,9 +284,17 @@ __device__ __forceinline__ void gram_chunk(RowState<PASS2>& st, const uint32_t (
         if (j + 1 == i) { a1 = 0.f; b1 = 0.f; }
       }
       illm = fminf(illm, fminf(fminf(e0, e1), fminf(f0, f1)));
-      const float lo = PASS2 ? kTinyD2 : 0.f;
-      d2x[2 * pq] = fmaxf(a0, lo); d2x[2 * pq + 1] = fmaxf(a1, lo);
-      d2z[2 * pq] = fmaxf(b0, lo); d2z[2 * pq + 1] = fmaxf(b1, lo);
+      if (EDGE) {                                      // diagonal zeros / padded columns must stay sqrt- and rsqrt-safe
+        const float lo = PASS2 ? kTinyD2 : 0.f;
+        d2x[2 * pq] = fmaxf(a0, lo); d2x[2 * pq + 1] = fmaxf(a1, lo);
+        d2z[2 * pq] = fmaxf(b0, lo); d2z[2 * pq + 1] = fmaxf(b1, lo);
+      } else {
+        // interior tile: no clamp.  A value that is not comfortably positive (d2 <= tau (n_i + n_j), negative
+        // round-off and NaN included) fails the conditioning test above and is REPLACED by the exact, clamped
+        // distance in the slow path below before any sqrt / rsqrt sees it
+        d2x[2 * pq] = a0; d2x[2 * pq + 1] = a1;
+        d2z[2 * pq] = b0; d2z[2 * pq + 1] = b1;
+      }
     }
   }
   uint32_t direct = 0;                                 // pairs whose gradient term is accumulated directly
