@@ -48,7 +48,7 @@ typedef struct ndp_planner ndp_planner;
 typedef struct ndp_comm ndp_comm;
 
 typedef struct {
-  int E;          /* state-embedding width (128; image_autoencoder.py:27)            */
+  int E;          /* state-embedding width: 128 (image_autoencoder.py:27) or 256 (fp32 mode only) */
   int nd;         /* noise_dim (evaluation.noise_dim; mpc_eval.py:65)                */
   int A;          /* action width, must be 4 (gan.py:71)                             */
   int H;          /* latent forward model hidden width, any value in [1,8192] (padded inside

@@ -139,14 +139,14 @@ extern "C" uint64_t ndp_launch_count(void) { return g_launches.load(); }
 
 extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) {
   NDP_CHECK_ARG(out && d, "planner_create: null argument");
-  NDP_CHECK_ARG(d->E == 128, "planner_create: E must be 128 (got %d); the generator consumes [state 128 | goal 128 | noise] (gan.py:67)", d->E);
+  NDP_CHECK_ARG(d->E == 128 || d->E == 256, "planner_create: E must be 128 (the reference: the generator consumes [state 128 | goal 128 | noise], gan.py:67) or 256 (got %d)", d->E);
   NDP_CHECK_ARG(d->A == 4, "planner_create: A must be 4 (gan.py:71)");
   NDP_CHECK_ARG(d->nd >= 0 && d->nd <= 64, "planner_create: noise_dim must be in [0,64]");
   NDP_CHECK_ARG(d->H >= 1 && d->H <= 8192, "planner_create: H must be in [1,8192]");
   NDP_CHECK_ARG(d->T >= 1 && d->T <= 4096, "planner_create: T must be in [1,4096]");
   NDP_CHECK_ARG(d->precision >= NDP_PREC_FP32 && d->precision <= NDP_PREC_F16_REFINE, "planner_create: unknown precision mode %d", d->precision);
   if (d->precision != NDP_PREC_FP32)
-    NDP_CHECK_ARG(d->nd <= 15 && d->H <= 2048, "planner_create: tensor-core modes need noise_dim<=15 and H<=2048 (got nd=%d H=%d); use NDP_PREC_FP32", d->nd, d->H);
+    NDP_CHECK_ARG(d->E == 128 && d->nd <= 15 && d->H <= 2048, "planner_create: tensor-core modes need E=128, noise_dim<=15 and H<=2048 (got E=%d nd=%d H=%d); use NDP_PREC_FP32", d->E, d->nd, d->H);
   if (int rc = device_check()) return rc;
   ndp_planner* p = new ndp_planner();
   memset(p, 0, sizeof(*p));
@@ -157,7 +157,9 @@ extern "C" int ndp_planner_create(ndp_planner** out, const ndp_planner_desc* d) 
   p->H_user = d->H;
   p->d.H = (d->H + 127) / 128 * 128;
   const int E = d->E, H = p->d.H, nd = d->nd;
-  p->nq = 32 + 16 * (H / 128);
+  // 8 KB chunks of the fp32 weight stream per step: fc1 state columns E*128, fc2, fc3, fc4 (two halves); per hidden
+  // chunk fwd.fc1 E*128 and fwd.fc2 128*E
+  p->nq = (E / 16 + 4 + 4 + 16) + (E / 8) * (H / 128);
   const size_t sizes[] = {
       (size_t)p->nq * 2048,      // wstream
       (size_t)128 * E,           // w1g
@@ -228,7 +230,7 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
   // ---- weight stream in consumption order (see k1_rollout_f32.cu), all blocks are W^T [K][N] row-major
   float* ws = p->wstream;
   int rc;
-  if ((rc = pack(s, ws, p->Wt[0], C1, 0, 0, 128, 128))) return rc;  ws += 128 * 128;   // gen.fc1 state cols
+  if ((rc = pack(s, ws, p->Wt[0], C1, 0, 0, E, 128))) return rc;    ws += E * 128;     // gen.fc1 state cols
   if ((rc = pack(s, ws, p->Wt[1], 128, 0, 0, 128, 64))) return rc;  ws += 128 * 64;    // gen.fc2
   if ((rc = pack(s, ws, p->Wt[2], 64, 0, 0, 64, 128))) return rc;   ws += 64 * 128;    // gen.fc3
   for (int h = 0; h < 2; ++h) {                                                       // gen.fc4 halves
@@ -236,8 +238,11 @@ extern "C" int ndp_planner_load(ndp_planner* p, const float* const* W, const flo
     ws += 128 * 128;
   }
   for (int c = 0; c < H / 128; ++c) {
-    if ((rc = pack(s, ws, p->Wt[5], E + 4, c * 128, 0, 128, 128))) return rc;  ws += 128 * 128;  // fwd.fc1 state cols, hidden chunk c
-    if ((rc = pack(s, ws, p->Wt[6], H, 0, c * 128, 128, 128))) return rc;      ws += 128 * 128;  // fwd.fc2 rows of hidden chunk c
+    if ((rc = pack(s, ws, p->Wt[5], E + 4, c * 128, 0, E, 128))) return rc;    ws += E * 128;    // fwd.fc1 state cols, hidden chunk c
+    for (int nh = 0; nh < E / 128; ++nh) {                                                       // fwd.fc2 rows of hidden chunk c, outputs in halves of 128
+      if ((rc = pack(s, ws, p->Wt[6], H, nh * 128, c * 128, 128, 128))) return rc;
+      ws += 128 * 128;
+    }
   }
   // ---- side parameters
   NDP_CUDA(cudaMemcpy2DAsync(p->w1g, E * sizeof(float), p->Wt[0] + E, C1 * sizeof(float), E * sizeof(float), 128,
@@ -292,7 +297,8 @@ static int rollout_score_impl(ndp_planner* p, const float* e0, const float* goal
                              nullptr, 0, nullptr, nullptr, balance);
   const size_t need = (size_t)G * 128 * sizeof(float);
   if (!ws || ws_bytes < need) { set_error("rollout_score: workspace %zu < %zu", ws_bytes, need); return NDP_ERR_WORKSPACE; }
-  const long long tiles = (long long)G * ((K + 127) / 128);
+  const int tile = rollout_f32_tile(p->d.E);
+  const long long tiles = (long long)G * ((K + tile - 1) / tile);
   NDP_CHECK_ARG(tiles <= 0x7FFFFFFF, "rollout_score: G*K too large for one launch");
   cudaStream_t s = (cudaStream_t)stream;
   float* b1g = reinterpret_cast<float*>(ws);
@@ -302,8 +308,8 @@ static int rollout_score_impl(ndp_planner* p, const float* e0, const float* goal
   rp.wstream = p->wstream; rp.b1g = b1g; rp.w1n = p->w1n; rp.b2 = p->b2; rp.b3 = p->b3; rp.b4 = p->b4;
   rp.w5 = p->w5; rp.b5 = p->b5; rp.wf1a = p->wf1a; rp.bf1 = p->bf1; rp.bf2 = p->bf2;
   rp.e0 = e0; rp.goal = goal; rp.noise = noise; rp.cost = cost; rp.a0 = a0; rp.state_T = state_T;
-  rp.G = G; rp.K = K; rp.T = p->d.T; rp.nd = p->d.nd; rp.H = p->d.H;
-  rp.tiles_per_goal = (K + 127) / 128; rp.nq = p->nq;
+  rp.G = G; rp.K = K; rp.T = p->d.T; rp.nd = p->d.nd; rp.H = p->d.H; rp.E = p->d.E;
+  rp.tiles_per_goal = (K + tile - 1) / tile; rp.nq = p->nq;
   return launch_rollout_f32(rp, s);
 }
 

@@ -1,7 +1,9 @@
 // K1 (fp32 parity mode) — fused generator MLP + T-step latent rollout + terminal cost.
 //
-// One CTA owns a tile of 128 candidates of one goal for the WHOLE horizon: the state
-// [128 x E] never leaves shared memory between steps, hidden activations never touch HBM.
+// One CTA owns a tile of M candidates of one goal for the WHOLE horizon: the state
+// [M x E] never leaves shared memory between steps, hidden activations never touch HBM.
+// E = 128 (the reference's latent width, M = 128, 256 threads) or E = 256 (the alternative reading of BASELINE cfg2's
+// "embedding dim 256"; the state image doubles, so M = 64 with 128 threads keeps the CTA inside 227 KB).
 // Replaces the reference loop mpc_eval.py:124-157 (+ :161 per-candidate MSE):
 //   per step  z = [state | goal | noise]  -> gan.Decoder.forward (gan.py:79-86) -> action
 //             state <- state + fc2(relu(fc1([state | action])))   (forward_encoder.py:105-114 contract)
@@ -16,10 +18,8 @@
 
 namespace ndp {
 
-static constexpr int kM = 128;          // candidates per CTA
-static constexpr int kLd = 132;         // activation buffer stride (floats)
 static constexpr int kChunk = 2048;     // floats per weight chunk (8 KB)
-static constexpr int kRThreads = 256;
+// M candidates per CTA, 2 M threads (16 column groups x M/8 row groups of 8x8 register tiles), activation stride M + 4
 
 __device__ __forceinline__ void cp_async16(float* dst_smem, const float* src) {
   unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
@@ -28,6 +28,7 @@ __device__ __forceinline__ void cp_async16(float* dst_smem, const float* src) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;\n" ::: "memory"); }
 
+template <int M>
 struct Stream {
   const float* base;   // packed weights of one step
   float* ring;         // 2 x kChunk floats in smem
@@ -36,17 +37,19 @@ struct Stream {
   __device__ __forceinline__ void prefetch(int chunk) {
     const float* src = base + (size_t)chunk * kChunk;
     float* dst = ring + (chunk & 1) * kChunk;
-    cp_async16(dst + threadIdx.x * 4, src + threadIdx.x * 4);
-    cp_async16(dst + (threadIdx.x + kRThreads) * 4, src + (threadIdx.x + kRThreads) * 4);
+#pragma unroll
+    for (int i = 0; i < kChunk / 4 / (2 * M); ++i)
+      cp_async16(dst + (threadIdx.x + i * 2 * M) * 4, src + (threadIdx.x + i * 2 * M) * 4);
     cp_async_commit();
   }
 };
 
-// acc[8][NT] += X[128 x K] * Wt[K x N]; X k-major in smem; N = 16*NT; consumes K*N/kChunk chunks.
+// acc[8][NT] += X[M x K] * Wt[K x N]; X k-major in smem; N = 16*NT; consumes K*N/kChunk chunks.
 // NOTE: chunk parity (q & 1) must stay consistent with prefetch(): nq is even.
-template <int NT>
-__device__ __forceinline__ void gemm_stream(float (&acc)[8][NT], const float* __restrict__ Xs, int K, Stream& st) {
+template <int NT, int M>
+__device__ __forceinline__ void gemm_stream(float (&acc)[8][NT], const float* __restrict__ Xs, int K, Stream<M>& st) {
   constexpr int N = 16 * NT;
+  constexpr int kLd = M + 4;
   constexpr int KPC = kChunk / N;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
   for (int k0 = 0; k0 < K; k0 += KPC) {
@@ -93,8 +96,9 @@ __device__ __forceinline__ void zero_acc(float (&acc)[8][NT]) {
 }
 
 // Out[n][m] = relu(acc[m][n])  (k-major for the next layer)
-template <int NT>
+template <int NT, int M>
 __device__ __forceinline__ void store_relu(const float (&acc)[8][NT], float* __restrict__ Out) {
+  constexpr int kLd = M + 4;
   const int ty = threadIdx.x >> 4;
 #pragma unroll
   for (int j = 0; j < NT; ++j) {
@@ -106,10 +110,12 @@ __device__ __forceinline__ void store_relu(const float (&acc)[8][NT], float* __r
   }
 }
 
-__global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const RolloutParams p) {
+template <int EC>
+__global__ void __launch_bounds__(EC == 1 ? 256 : 128, 1) rollout_f32_kernel(const RolloutParams p) {
+  constexpr int kM = EC == 1 ? 128 : 64, kLd = kM + 4, kRThreads = 2 * kM, E = 128 * EC;
   extern __shared__ __align__(16) float smem[];
-  float* S = smem;                       // state        [E=128][kLd]
-  float* bufA = S + 128 * kLd;           // activations  [128][kLd]
+  float* S = smem;                       // state        [E][kLd]
+  float* bufA = S + E * kLd;             // activations  [128][kLd]
   float* bufB = bufA + 128 * kLd;        // activations  [128][kLd]
   float* ring = bufB + 128 * kLd;        // weight ring  2 x kChunk
   float* s_act = ring + 2 * kChunk;      // action       [4][kLd]
@@ -117,12 +123,11 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int g = blockIdx.x / p.tiles_per_goal;
   const int m0 = (blockIdx.x % p.tiles_per_goal) * kM;
-  const int E = 128;
 
-  Stream st{p.wstream, ring, 0, p.nq};
+  Stream<kM> st{p.wstream, ring, 0, p.nq};
   st.prefetch(0);
   for (int idx = tid; idx < E * kM; idx += kRThreads) {
-    const int e = idx >> 7, m = idx & 127;
+    const int e = idx / kM, m = idx % kM;
     S[e * kLd + m] = __ldg(p.e0 + (size_t)g * E + e);
   }
 
@@ -130,7 +135,7 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
   for (int t = 0; t < p.T; ++t) {
     // ---------------- generator fc1: [state | goal | noise] -> 128   (gan.py:81)
     zero_acc<8>(acc);
-    gemm_stream<8>(acc, S, 128, st);
+    gemm_stream<8, kM>(acc, S, E, st);
     {
       float nz[8][4];
       const float* nbase = p.noise + (((size_t)t * p.G + g) * p.K) * p.nd;
@@ -161,44 +166,44 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
           }
         }
       }
-      store_relu<8>(acc, bufA);
+      store_relu<8, kM>(acc, bufA);
     }
     // ---------------- fc2: 128 -> 64   (gan.py:82)
     {
       float acc4[8][4];
       zero_acc<4>(acc4);
-      gemm_stream<4>(acc4, bufA, 128, st);
+      gemm_stream<4, kM>(acc4, bufA, 128, st);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const float bias = __ldg(p.b2 + col_of<4>(j));
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc4[i][j] += bias;
       }
-      store_relu<4>(acc4, bufB);
+      store_relu<4, kM>(acc4, bufB);
     }
     // ---------------- fc3: 64 -> 128   (gan.py:83)
     zero_acc<8>(acc);
-    gemm_stream<8>(acc, bufB, 64, st);
+    gemm_stream<8, kM>(acc, bufB, 64, st);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const float bias = __ldg(p.b3 + col_of<8>(j));
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[i][j] += bias;
     }
-    store_relu<8>(acc, bufA);
+    store_relu<8, kM>(acc, bufA);
     // ---------------- fc4: 128 -> 256 in two halves, fc5 (256 -> 4) folded in   (gan.py:84-85)
-    const int am = tid & 127, ap = (tid >> 7) * 2;   // this thread's (candidate, action pair)
+    const int am = tid % kM, ap = (tid / kM) * 2;   // this thread's (candidate, action pair)
     float av0 = 0.f, av1 = 0.f;
     for (int h = 0; h < 2; ++h) {
       zero_acc<8>(acc);
-      gemm_stream<8>(acc, bufA, 128, st);
+      gemm_stream<8, kM>(acc, bufA, 128, st);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float bias = __ldg(p.b4 + h * 128 + col_of<8>(j));
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[i][j] += bias;
       }
-      store_relu<8>(acc, bufB);
+      store_relu<8, kM>(acc, bufB);
       __syncthreads();
       const float* w5a = p.w5 + (size_t)ap * 256 + h * 128;
       const float* w5b = w5a + 256;
@@ -219,11 +224,12 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
       a0p[1] = av1;
     }
     // ---------------- forward model: state += fc2(relu(fc1([state | action])))
-    float acc2[8][8];
-    zero_acc<8>(acc2);
+    float acc2[EC][8][8];                    // residual accumulators: E outputs in halves of 128
+#pragma unroll
+    for (int nh = 0; nh < EC; ++nh) zero_acc<8>(acc2[nh]);
     for (int c = 0; c < p.H / 128; ++c) {
       zero_acc<8>(acc);
-      gemm_stream<8>(acc, S, 128, st);     // first chunk barrier also publishes s_act
+      gemm_stream<8, kM>(acc, S, E, st);   // first chunk barrier also publishes s_act
       {
         float a4[8][4];
 #pragma unroll
@@ -248,25 +254,29 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
           }
         }
       }
-      store_relu<8>(acc, bufA);
-      gemm_stream<8>(acc2, bufA, 128, st);
+      store_relu<8, kM>(acc, bufA);
+#pragma unroll
+      for (int nh = 0; nh < EC; ++nh) gemm_stream<8, kM>(acc2[nh], bufA, 128, st);
     }
     // ---------------- residual update (eval mode: state + residual, forward_encoder.py:113-114)
     const bool last = (t == p.T - 1);
     float csum[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int n = col_of<8>(j);
-      const float bias = __ldg(p.bf2 + n);
-      float* sp = S + (size_t)n * kLd + ty * 8;
-      const float gl = last ? __ldg(p.goal + (size_t)g * E + n) : 0.f;
+    for (int nh = 0; nh < EC; ++nh) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const float v = sp[i] + (acc2[i][j] + bias);
-        sp[i] = v;
-        acc2[i][j] = v;
-        const float df = v - gl;
-        csum[i] = fmaf(df, df, csum[i]);
+      for (int j = 0; j < 8; ++j) {
+        const int n = nh * 128 + col_of<8>(j);
+        const float bias = __ldg(p.bf2 + n);
+        float* sp = S + (size_t)n * kLd + ty * 8;
+        const float gl = last ? __ldg(p.goal + (size_t)g * E + n) : 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float v = sp[i] + (acc2[nh][i][j] + bias);
+          sp[i] = v;
+          acc2[nh][i][j] = v;
+          const float df = v - gl;
+          csum[i] = fmaf(df, df, csum[i]);
+        }
       }
     }
     if (last) {
@@ -279,7 +289,7 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
         v += __shfl_xor_sync(0xffffffffu, v, 2);
         v += __shfl_xor_sync(0xffffffffu, v, 1);
         const int cand = m0 + ty * 8 + i;
-        if (tx == 0 && cand < p.K) p.cost[(size_t)g * p.K + cand] = v * (1.0f / 128.0f);
+        if (tx == 0 && cand < p.K) p.cost[(size_t)g * p.K + cand] = v * (1.0f / (float)E);
       }
       if (p.state_T) {
 #pragma unroll
@@ -288,7 +298,9 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
           if (cand < p.K) {
             float* o = p.state_T + ((size_t)g * p.K + cand) * E;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) o[col_of<8>(j)] = acc2[i][j];
+            for (int nh = 0; nh < EC; ++nh)
+#pragma unroll
+              for (int j = 0; j < 8; ++j) o[nh * 128 + col_of<8>(j)] = acc2[nh][i][j];
           }
         }
       }
@@ -297,16 +309,22 @@ __global__ void __launch_bounds__(kRThreads, 1) rollout_f32_kernel(const Rollout
   cp_async_wait_all();
 }
 
-int rollout_f32_smem_bytes() { return (3 * 128 * kLd + 2 * kChunk + 4 * kLd) * (int)sizeof(float); }
+int rollout_f32_tile(int E) { return E == 128 ? 128 : 64; }
+int rollout_f32_smem_bytes(int E) {
+  const int ld = rollout_f32_tile(E) + 4;
+  return ((E + 2 * 128) * ld + 2 * kChunk + 4 * ld) * (int)sizeof(float);
+}
 
 int launch_rollout_f32(const RolloutParams& p, cudaStream_t s) {
   static std::atomic<unsigned long long> attr_devs{0};
-  const int smem = rollout_f32_smem_bytes();
   if (first_use_on_device(attr_devs)) {
-    NDP_CUDA(cudaFuncSetAttribute(rollout_f32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    NDP_CUDA(cudaFuncSetAttribute(rollout_f32_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, rollout_f32_smem_bytes(128)));
+    NDP_CUDA(cudaFuncSetAttribute(rollout_f32_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, rollout_f32_smem_bytes(256)));
   }
-  const int grid = p.G * p.tiles_per_goal;
-  rollout_f32_kernel<<<grid, kRThreads, smem, s>>>(p);
+  const int grid = p.G * p.tiles_per_goal, smem = rollout_f32_smem_bytes(p.E);
+  if (p.E == 128) rollout_f32_kernel<1><<<grid, 256, smem, s>>>(p);
+  else if (p.E == 256) rollout_f32_kernel<2><<<grid, 128, smem, s>>>(p);
+  else { set_error("rollout_f32: E must be 128 or 256 (got %d)", p.E); return NDP_ERR_ARG; }
   NDP_LAUNCH_CHECK();
   return NDP_OK;
 }

@@ -22,11 +22,12 @@ struct RolloutParams {
   float* cost;            // [G][K]
   float* a0;              // [G][K][4]
   float* state_T;         // [G][K][E] or null
-  int G, K, T, nd, H, tiles_per_goal, nq;
+  int G, K, T, nd, H, E, tiles_per_goal, nq;   // E: 128 or 256; tiles of rollout_f32_tile(E) candidates
 };
 
 int launch_rollout_f32(const RolloutParams& p, cudaStream_t s);
-int rollout_f32_smem_bytes();
+int rollout_f32_smem_bytes(int E);
+int rollout_f32_tile(int E);             // candidates per CTA of the fp32 kernel
 
 // ---- tensor-core rollout (k1_rollout_tc.cu) --------------------------------------------------
 // One stream item = one weight block landing in one ring slot, consumed by n_main (+1 ext) K=16 slabs.

@@ -19,7 +19,7 @@ COST_RTOL = 1e-4
 
 
 def _oracle_models(gen_p, fwd_p, nd, E, H, double=False):
-    gen, fwd = O.GeneratorMLP(nd).eval(), O.LatentForward(E, H).eval()
+    gen, fwd = O.GeneratorMLP(nd, cond_dim=2 * E).eval(), O.LatentForward(E, H).eval()
     gen.load_state_dict(gen_p.state_dict()); fwd.load_state_dict(fwd_p.state_dict())
     return (gen.double(), fwd.double()) if double else (gen, fwd)
 
@@ -42,11 +42,14 @@ def _check_selection(cost_gpu, best_gpu, topk_gpu, cost64, topk):
     return klass
 
 
-@pytest.mark.parametrize("G,K,T,H,nd", [(1, 64, 1, 128, 2), (1, 128, 3, 256, 2), (2, 300, 4, 256, 2),
-                                        (1, 1024, 8, 1024, 2), (3, 130, 2, 384, 5), (1, 257, 5, 128, 1)])
-def test_rollout_matches_oracle(cuda, G, K, T, H, nd):
+# E = 256: the alternative reading of BASELINE cfg2's "embedding dim 256" (SURVEY.md 8a note) — fp32 kernel, 64-candidate
+# tiles; K = 65 / 130 / 257 are ragged against that tile, H = 200 is padded to 256 inside the library
+@pytest.mark.parametrize("G,K,T,H,nd,E", [(1, 64, 1, 128, 2, 128), (1, 128, 3, 256, 2, 128), (2, 300, 4, 256, 2, 128),
+                                          (1, 1024, 8, 1024, 2, 128), (3, 130, 2, 384, 5, 128), (1, 257, 5, 128, 1, 128),
+                                          (1, 65, 1, 128, 2, 256), (2, 130, 3, 256, 2, 256), (1, 257, 4, 200, 5, 256),
+                                          (1, 1024, 8, 1024, 2, 256)])
+def test_rollout_matches_oracle(cuda, G, K, T, H, nd, E):
     from ndivplanning_b200 import FusedPlanner
-    E = 128
     gen_p, fwd_p = synthetic.make_models(nd=nd, E=E, H=H, seed=0)
     e0, goal, noise = synthetic.make_plan_inputs(G, K, T, nd, E, seed=K + T)
     pl = FusedPlanner(gen_p, fwd_p, horizon=T, precision="fp32")
@@ -263,6 +266,38 @@ def test_tensor_mode_rejects_unsupported_shapes(cuda):
     with pytest.raises(NdpError):
         FusedPlanner(gen_p, fwd_p, horizon=2, precision="f16x3")     # noise_dim > 15: fp32 mode only
     FusedPlanner(gen_p, fwd_p, horizon=2, precision="fp32")
+    gen_p, fwd_p = synthetic.make_models(nd=2, E=256, H=128, seed=0)
+    with pytest.raises(NdpError):
+        FusedPlanner(gen_p, fwd_p, horizon=2, precision="f16+refine")  # E = 256: fp32 mode only
+    assert FusedPlanner(gen_p, fwd_p, horizon=2).precision == "fp32"  # and that is what the default picks
+    gen_p, fwd_p = synthetic.make_models(nd=2, E=64, H=128, seed=0)
+    with pytest.raises(NdpError):
+        FusedPlanner(gen_p, fwd_p, horizon=2, precision="fp32")        # E must be 128 or 256
+
+
+def test_embedding_256_entry_points(cuda):
+    """E = 256 through the other entry points: single-call generator / forward model against the torch modules, the
+    pre-allocated ring against plan(), plan() against the fp64 oracle"""
+    from ndivplanning_b200 import FusedPlanner
+    E, H, nd, G, K, T = 256, 256, 2, 2, 300, 3
+    gen, fwd = synthetic.make_models(nd=nd, E=E, H=H, seed=3)
+    pl = FusedPlanner(gen, fwd, horizon=T)
+    z = torch.randn(11, 2 * E + nd)
+    s, act = torch.randn(9, E, 1, 1), torch.randn(9, 4)
+    with torch.no_grad():
+        want_a, want_s = gen(z), fwd(s, act)
+    np.testing.assert_allclose(pl.generator(z.cuda()).cpu().numpy(), want_a.numpy(), rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(pl.forward_model(s.cuda(), act.cuda()).cpu().numpy(), want_s.numpy(), rtol=1e-4, atol=1e-5)
+    ring = pl.ring(G, K, 4, depth=2)
+    for i in range(3):
+        e0, goal, noise = (t.cuda() for t in synthetic.make_plan_inputs(G, K, T, nd, E, seed=40 + i))
+        q = ring.plan(e0, goal, noise).wait()
+        w = pl.plan(e0, goal, noise, topk=4)
+        for a, b in ((q.best_idx, w.best_idx), (q.best_action, w.best_action), (q.topk_idx, w.topk_idx), (q.cost, w.cost)):
+            assert torch.equal(a, b)
+        o = O.mpc_plan(*_oracle_models(gen, fwd, nd, E, H, double=True), e0[0].cpu().double(), goal[0].cpu().double(),
+                       noise[:, 0].cpu().double())
+        np.testing.assert_allclose(w.cost[0].cpu().numpy(), o["cost"].numpy(), rtol=COST_RTOL)
 
 
 def _check_selection_bound(cost64, best, topk_list, topk, bound):
