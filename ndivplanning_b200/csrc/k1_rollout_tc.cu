@@ -747,19 +747,19 @@ int tc_plan_create(TcPlan** out, int np, int E, int nd, int H, const float* cons
 //   G4b D=P <- Q[0,64)                 epilogue P -> Q[0,64)        (fc4 outputs 128..255)
 //   G5  D=P[0,16) <- Q[64,128) | Q[0,64)
 //   F1[c] (hidden chunk of 128)  D=Q <- state(smem), epilogue in place;  F2[c]  DR=P += Q
-// Products and accumulation order per element equal rollout_tc_kernel<1>; only the state carries 22 instead of 24 bits.
+// Products and accumulation order per element equal rollout_tc_kernel<1>; only the state is carried as fp16 hi + 8-bit lo (14 bits) instead of fp32.
 // ==========================================================================================================
 static constexpr int kT2Threads = 576;                   // 16 epilogue warps, MMA issuer (16), TMA producer (17)
 static constexpr uint32_t kT2P = 0, kT2Q = 128;
-static constexpr uint32_t kT2OffState = 0;               // per tile: hi image 32 KB (A operand layout) | lo image 32 KB
-#ifdef NDP_T2_EXPERIMENT_ALIAS_LO
-// TIMING EXPERIMENT ONLY (results are garbage): both tiles share one lo image, the freed 32 KB hold a fifth ring slot
-static constexpr uint32_t kT2HiStride = 32768, kT2LoBase = 65536, kT2LoStride = 0, kT2StateBytes = 98304;
-static constexpr uint32_t kT2NSlot = 5;
-#else
-static constexpr uint32_t kT2HiStride = 65536, kT2LoBase = 32768, kT2LoStride = 65536, kT2StateBytes = 131072;
-static constexpr uint32_t kT2NSlot = 4;                   // 4 slots: one GEMM (2 items) in use + one GEMM in flight
-#endif
+// per tile: hi image 32 KB (fp16, A operand layout) | lo image 16 KB.  The lo image is private to the epilogue threads
+// (no MMA reads it): it only carries the state's rounding residual s - hi from one step's END to the next, so it is kept
+// in 8 bits per element — the high byte of fp16(s - hi), i.e. e5m2 with round-to-nearest: the state is carried at
+// 11 + 3 bits instead of 11 + 11, an error of <= 2^-14 |s| per step against the 2^-12 |s| operand rounding of every product
+// of this single-pass estimate.  The 32 KB this frees hold a fifth ring slot (ring waits 4.6 k -> 3.3 k cycles per step).
+// lo element (row m, k): byte (k/8)*1024 + m*8 + k%8.
+static constexpr uint32_t kT2OffState = 0;
+static constexpr uint32_t kT2TileState = 49152, kT2LoBase = 32768, kT2StateBytes = 2 * kT2TileState;
+static constexpr uint32_t kT2NSlot = 5;                   // one GEMM (2 items) in use + one in flight + one spare
 static constexpr uint32_t kT2OffExt = kT2StateBytes;     // noise[2] 2 x 4 KB | action[2] 2 x 2 KB | ones 2 KB | zeros 2 KB
 static constexpr uint32_t kT2ExtBytes = 16384;           // (action / ones use k < 8 only: their second k-chunk is the shared zero block)
 static constexpr uint32_t kT2OffRing = kT2OffExt + kT2ExtBytes;
@@ -839,7 +839,7 @@ __device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
 // at the same CTA-relative offsets), so the L2 -> SM traffic of the weight stream (24.6 B/clk/SM = 6 TB/s chip-wide at
 // cfg2, the reason the issuer waited 14 % of its time for ring slots) is halved.  A slot is refilled once BOTH CTAs have
 // released it (the issuers' tcgen05.commit arrives on the empty barrier of both CTAs, barrier count CL).
-// hand-over of a split pair's state images (64 KB per tile) through global memory.  __noinline__: kept out of the
+// hand-over of a split pair's state images (48 KB per tile) through global memory.  __noinline__: kept out of the
 // kernel body so that the step loops of the SPLIT instantiation are scheduled / register-allocated like the lean one
 __device__ __forceinline__ void t2_tile_bar(int tile) {
   if (tile == 0) asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -854,14 +854,14 @@ __device__ __noinline__ void t2_state_restore(uint8_t* tile_smem, const uint8_t*
   const uint4* src = reinterpret_cast<const uint4*>(src_g);
   uint4* dst = reinterpret_cast<uint4*>(tile_smem);
 #pragma unroll 4
-  for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = __ldcg(src + tt + 256 * j);
+  for (int j = 0; j < (int)(kT2TileState / 4096); ++j) dst[tt + 256 * j] = __ldcg(src + tt + 256 * j);
 }
 __device__ __noinline__ void t2_state_dump(const uint8_t* tile_smem, uint8_t* dst_g, unsigned* flag, int tt, int tile) {
   t2_tile_bar(tile);                                        // every thread's put_state8 of the last step
   const uint4* src = reinterpret_cast<const uint4*>(tile_smem);
   uint4* dst = reinterpret_cast<uint4*>(dst_g);
 #pragma unroll 4
-  for (int j = 0; j < 16; ++j) dst[tt + 256 * j] = src[tt + 256 * j];
+  for (int j = 0; j < (int)(kT2TileState / 4096); ++j) dst[tt + 256 * j] = src[tt + 256 * j];
   __threadfence();
   t2_tile_bar(tile);
   if (tt == 0) st_release_gpu(flag, 1u);
@@ -972,7 +972,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       // action / ones slabs hold k-chunk 0 only; LBO points their k-chunk 1 at the shared zero block
       td[tl].ext_act = a16(smem_u32(ext_actb + tl * 2048)) | (((smem_u32(ext_zero) - smem_u32(ext_actb + tl * 2048)) >> 4) << 16);
       td[tl].ext_ones = a16(smem_u32(ext_ones)) | (((smem_u32(ext_zero) - smem_u32(ext_ones)) >> 4) << 16);
-      td[tl].state16 = a16(smem_u32(smem + kT2OffState + tl * kT2HiStride)) | ext_lbo;
+      td[tl].state16 = a16(smem_u32(smem + kT2OffState + tl * kT2TileState)) | ext_lbo;
     }
     const uint32_t ring16 = a16(smem_u32(smem + kT2OffRing));
     uint32_t slot = 0, par = 0, ds[2] = {0, 0}, aw[2] = {0, 0};
@@ -1134,8 +1134,8 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     const bool valid = cand < p.K && !ghost;
     // state images of this tile: element (row m, k) at (k/8)*2048 + (m/8)*128 + (m%8)*16 + (k%8)*2
     const uint32_t rowoff = (uint32_t)(m >> 3) * 128 + (uint32_t)(m & 7) * 16;
-    uint8_t* SH = smem + kT2OffState + tile * kT2HiStride + rowoff;
-    uint8_t* SL = smem + kT2OffState + kT2LoBase + tile * kT2LoStride + rowoff;
+    uint8_t* SH = smem + kT2OffState + tile * kT2TileState + rowoff;
+    uint8_t* SL = smem + kT2OffState + tile * kT2TileState + kT2LoBase + m * 8;      // 8-bit lo image: 8 bytes per (k-chunk, row)
     uint8_t* ext_noise = ext_base + tile * kExtSlab;
     uint8_t* ext_act = ext_actb + tile * 2048;
     const uint32_t lane_base = tmem + 256 * tile + ((uint32_t)(q * 32) << 16);
@@ -1227,7 +1227,11 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       hv.z = pack_hi(s[4], s[5]); lv.z = pack_lo(s[4], s[5], hv.z);
       hv.w = pack_hi(s[6], s[7]); lv.w = pack_lo(s[6], s[7], hv.w);
       *reinterpret_cast<uint4*>(SH + kc * 2048) = hv;
-      *reinterpret_cast<uint4*>(SL + kc * 2048) = lv;
+      // fp16 residuals -> their high bytes, rounded to nearest (+0x80 per half; residuals are far from the fp16 maximum)
+      uint2 l8;
+      l8.x = __byte_perm(lv.x + 0x00800080u, lv.y + 0x00800080u, 0x7531);
+      l8.y = __byte_perm(lv.z + 0x00800080u, lv.w + 0x00800080u, 0x7531);
+      *reinterpret_cast<uint2*>(SL + kc * 1024) = l8;
     };
     // ---- init: state <- e0 (this thread: k in [64h, 64h+64)) or the images a first piece left; noise ext of step t0
     const int tt = (warp & 7) * 32 + lane;                      // thread of the tile (256)
@@ -1241,7 +1245,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       }
     } else {
       // continuation: wait (bounded) for the first piece of this tile, then copy its 64 KB of state images back
-      t2_state_restore(smem + kT2OffState + tile * 65536, p.sp_state + ((size_t)sp_id * 2 + tile) * 65536,
+      t2_state_restore(smem + kT2OffState + tile * kT2TileState, p.sp_state + ((size_t)sp_id * 2 + tile) * 65536,
                        p.sp_flags + 2 * sp_id + tile, tt, tile);
     }
     if (h == 0) noise_row(t0);
@@ -1279,16 +1283,20 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
       for (int u = 0; u < 2; ++u) {
         uint32_t r[32];
         tmem_ld32(P + 64 * h + 32 * u, r);
-        uint4 hv[4], lv[4];
+        uint4 hv[4];
+        uint2 l8[4];
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           hv[c] = *reinterpret_cast<const uint4*>(SH + (8 * h + 4 * u + c) * 2048);
-          lv[c] = *reinterpret_cast<const uint4*>(SL + (8 * h + 4 * u + c) * 2048);
+          l8[c] = *reinterpret_cast<const uint2*>(SL + (8 * h + 4 * u + c) * 1024);
         }
         tmem_ld_wait();
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-          const uint32_t hw[4] = {hv[c].x, hv[c].y, hv[c].z, hv[c].w}, lw[4] = {lv[c].x, lv[c].y, lv[c].z, lv[c].w};
+          const uint32_t hw[4] = {hv[c].x, hv[c].y, hv[c].z, hv[c].w};
+          // bytes back into the high halves of fp16 pairs
+          const uint32_t lw[4] = {__byte_perm(l8[c].x, 0u, 0x1404), __byte_perm(l8[c].x, 0u, 0x3424),
+                                  __byte_perm(l8[c].y, 0u, 0x1404), __byte_perm(l8[c].y, 0u, 0x3424)};
           float s8[8];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
@@ -1324,7 +1332,7 @@ __global__ void __launch_bounds__(kT2Threads, 1) rollout_tc2_kernel(const TcPara
     }
     if (SPLIT && t1 < p.T && !ghost) {
       // first piece of a split pair: leave the state images for the continuation, then raise this tile's flag
-      t2_state_dump(smem + kT2OffState + tile * 65536, p.sp_state + ((size_t)sp_id * 2 + tile) * 65536,
+      t2_state_dump(smem + kT2OffState + tile * kT2TileState, p.sp_state + ((size_t)sp_id * 2 + tile) * 65536,
                     p.sp_flags + 2 * sp_id + tile, tt, tile);
     }
 #ifdef NDP_TC_PROF

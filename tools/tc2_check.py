@@ -71,6 +71,8 @@ if __name__ == "__main__":
             srel = 0.0 if two[i][2] is None else ((two[i][2] - one[i][2]).abs().max() / one[i][2].abs().max()).item()
             fin = bool(torch.isfinite(two[i][0]).all())
             print(f"cfg {cfg}: cost max rel diff {rel:.2e}, a0 {arel:.2e}, state {srel:.2e}, bit-equal {bit}, finite {fin}", flush=True)
-            ok &= fin and rel < 5e-4 and arel < 1e-6 and srel < 1e-3     # one fp16 ulp of a re-rounded state element
+            # both kernels round every operand to fp16; their states differ by the 8-bit lo image (2^-14 |s| per step), which
+            # re-rounds a few state elements by one fp16 ulp per step: up to 2.5e-4 at T = 8, 6.1e-4 at T = 16 over 131,072 candidates
+            ok &= fin and rel < 1e-3 and arel < 1e-6 and srel < 1e-3
         print("tc2_check", "ok" if ok else "MISMATCH")
         sys.exit(0 if ok else 1)
