@@ -206,7 +206,8 @@ def run_reference(args):
 K1_KERNEL = {"fp32": "rollout_f32_kernel", "f16": "rollout_tc2_kernel", "f16x2": "rollout_tc_kernel<2>",
              "f16x3": "rollout_tc_kernel<3>", "f16+refine": "rollout_tc2_kernel"}
 MMA_PASSES = {"fp32": 0, "f16": 1, "f16x2": 2, "f16x3": 3, "f16+refine": 1}
-NCU_TRAFFIC = {"rollout_tc2_kernel": 5.075e6, "rollout_tc_kernel<1>": 4.98e6, "rollout_f32_kernel": 5.69e6}   # bytes per launch, ncu (profiles/)
+NCU_TRAFFIC = {"rollout_tc2_kernel": 6.55e6,   # profiles/r02h_ncu_full_rollout_tc2_raw.csv: 5.01 MB read + 1.54 MB written
+                "rollout_tc_kernel<1>": 4.98e6, "rollout_f32_kernel": 5.69e6}   # bytes per launch, ncu (profiles/)
 POOL = 40   # distinct noise sets rotated through the timed region: 40 x 4.2 MB = 168 MB > 126 MB of L2
 
 
