@@ -669,6 +669,22 @@ def run_gpu(args):
             planner.plan(e0, goal, pool[i], topk=topk)
         b.record(); torch.cuda.synchronize()
         modes["single_plan_unpipelined_ms"] = a.elapsed_time(b) / 10
+        # secondary row: cfg2 with "embedding dim 256" read as the state width E (SURVEY.md 8a note); fp32 kernel only
+        g256, f256 = synthetic.make_models(nd=CFG["nd"], E=256, H=CFG["H"], seed=0)
+        pl = FusedPlanner(g256, f256, horizon=T, device=dev)
+        e0b, goalb, _ = synthetic.make_plan_inputs(G, 8, T, CFG["nd"], 256, seed=9)
+        e0b, goalb = e0b.to(dev), goalb.to(dev)
+        pl.plan(e0b, goalb, pool[0], topk=topk)
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        a.record()
+        for i in range(3):
+            pl.plan(e0b, goalb, pool[1 + i], topk=topk)
+        b.record(); torch.cuda.synchronize()
+        pms = a.elapsed_time(b) / 3
+        modes["E256"] = {"precision": pl.precision, "plan_ms": pms, "candidate_steps_per_s": G * K * T / (pms * 1e-3),
+                         "what": "same G, K, T, H, nd with a 256-wide state (generator input 512 + nd): rollout_f32_kernel<2>"}
+        del pl
         tgpu = torch_gpu_block(dev, gen, fwd, e0, goal, pool[0], x, z, args.steps)
 
     ms, ms_e2e, ms_sus = maxr(ms), maxr(ms_e2e), maxr(ms_sus)

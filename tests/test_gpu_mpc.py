@@ -384,13 +384,13 @@ def test_plan_ring_equals_plain_plan(cuda, prec, G, K, T, topk):
         ring.plan(inputs[0][0], inputs[0][1], inputs[0][2][:, :, : K - 1])
 
 
-@pytest.mark.parametrize("prec", ["fp32", "f16+refine"])
-def test_closed_loop_sweep_matches_oracle_loop(cuda, prec):
+@pytest.mark.parametrize("prec,E", [("fp32", 128), ("f16+refine", 128), ("fp32", 256)])
+def test_closed_loop_sweep_matches_oracle_loop(cuda, prec, E):
     """N1 driver: G goals swept together on the device == the reference's receding-horizon loop
     (mpc_eval.py:112-176, oracle restatement) run goal by goal with the same noise, incl. the truncated
     horizon near the end (:127)."""
     from ndivplanning_b200.closed_loop import ClosedLoopSweep
-    G, K, Th, S, nd, E, H = 3, 256, 3, 5, 2, 128, 256
+    G, K, Th, S, nd, H = 3, 256, 3, 5, 2, 256
     gen, fwd = synthetic.make_models(nd=nd, E=E, H=H)
     og, of = _oracle_models(gen, fwd, nd, E, H)
     torch.manual_seed(11)
