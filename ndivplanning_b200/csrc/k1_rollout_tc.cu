@@ -805,6 +805,13 @@ __device__ __forceinline__ void t2_group(const T2Tile& st, uint32_t b16, uint32_
 __device__ unsigned long long g_t2_prof[8];   // issuer: [0] wait_a [1] wait_full [2] total; epilogue warp 0: [4] wait_d [5] total
 #endif
 
+// relu after the fp16 rounding, on the packed pair: cvt + HMNMX2 = 2 instructions per pair instead of 2 FMNMX + cvt.
+// Same bits as pack_hi(max(x0, 0), max(x1, 0)) — rounding to nearest is monotonic and keeps the sign — up to the sign of
+// a zero (an MMA operand: no effect) and NaN -> 0 either way.
+__device__ __forceinline__ uint32_t relu_pack(uint32_t x0, uint32_t x1) {
+  __half2 h = __hmax2(__floats2half2_rn(__uint_as_float(x0), __uint_as_float(x1)), __float2half2_rn(0.f));
+  return *reinterpret_cast<uint32_t*>(&h);
+}
 // 64 accumulator columns (src, src+32) -> relu -> 32 packed fp16 columns (dst, dst+16); both loads in flight at once
 __device__ __forceinline__ void t2_relu64(uint32_t src, uint32_t dst) {
   uint32_t v[32], w[32];
@@ -814,11 +821,11 @@ __device__ __forceinline__ void t2_relu64(uint32_t src, uint32_t dst) {
   uint32_t hi[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j)
-    hi[j] = pack_hi(fmaxf(__uint_as_float(v[2 * j]), 0.f), fmaxf(__uint_as_float(v[2 * j + 1]), 0.f));
+    hi[j] = relu_pack(v[2 * j], v[2 * j + 1]);
   tmem_st16(dst, hi);
 #pragma unroll
   for (int j = 0; j < 16; ++j)
-    hi[j] = pack_hi(fmaxf(__uint_as_float(w[2 * j]), 0.f), fmaxf(__uint_as_float(w[2 * j + 1]), 0.f));
+    hi[j] = relu_pack(w[2 * j], w[2 * j + 1]);
   tmem_st16(dst + 16, hi);
 }
 // 32 accumulator columns -> relu -> 16 packed fp16 columns
@@ -829,7 +836,7 @@ __device__ __forceinline__ void t2_relu32(uint32_t src, uint32_t dst) {
   uint32_t hi[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j)
-    hi[j] = pack_hi(fmaxf(__uint_as_float(v[2 * j]), 0.f), fmaxf(__uint_as_float(v[2 * j + 1]), 0.f));
+    hi[j] = relu_pack(v[2 * j], v[2 * j + 1]);
   tmem_st16(dst, hi);
 }
 
