@@ -805,12 +805,13 @@ __device__ __forceinline__ void t2_group(const T2Tile& st, uint32_t b16, uint32_
 __device__ unsigned long long g_t2_prof[8];   // issuer: [0] wait_a [1] wait_full [2] total; epilogue warp 0: [4] wait_d [5] total
 #endif
 
-// relu after the fp16 rounding, on the packed pair: cvt + HMNMX2 = 2 instructions per pair instead of 2 FMNMX + cvt.
-// Same bits as pack_hi(max(x0, 0), max(x1, 0)) — rounding to nearest is monotonic and keeps the sign — up to the sign of
-// a zero (an MMA operand: no effect) and NaN -> 0 either way.
+// relu fused into the fp16 pack: ONE instruction per pair (cvt.rn.relu.f16x2.f32) instead of 2 FMNMX + cvt.
+// Same bits as pack_hi(max(x0, 0), max(x1, 0)) — rounding to nearest is monotonic and keeps the sign — except that a NaN
+// stays a NaN (torch's relu keeps it too).
 __device__ __forceinline__ uint32_t relu_pack(uint32_t x0, uint32_t x1) {
-  __half2 h = __hmax2(__floats2half2_rn(__uint_as_float(x0), __uint_as_float(x1)), __float2half2_rn(0.f));
-  return *reinterpret_cast<uint32_t*>(&h);
+  uint32_t d;                                                   // one F2FP with the relu modifier (x1 -> upper half)
+  asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(__uint_as_float(x1)), "f"(__uint_as_float(x0)));
+  return d;
 }
 // 64 accumulator columns (src, src+32) -> relu -> 32 packed fp16 columns (dst, dst+16); both loads in flight at once
 __device__ __forceinline__ void t2_relu64(uint32_t src, uint32_t dst) {
